@@ -1,0 +1,217 @@
+/*
+ * regcm_dyn.h — C ABI of the B200-native RegCM dynamical-core step.
+ *
+ * This is the drop-in boundary for the reference's dyn-core hot path.  The
+ * reference exposes that path as argument-less Fortran module procedures that
+ * operate on module-global pointer arrays; each entry point below cites the
+ * reference interface it replaces (paths relative to the reference tree).
+ * A Fortran `bind(C)` interface block for these functions is shown in
+ * INTEGRATION.md.
+ *
+ * Conventions
+ *  - all reals are IEEE double (`real(rkx)`, rkx = rk8,
+ *    Share/mod_realkinds.F90:42-66); integers are 32-bit (`ik4`).
+ *  - arrays cross the boundary as a pointer to the first element plus explicit
+ *    Fortran bounds lb[3]/ub[3] (inclusive, GLOBAL model indices), column
+ *    major (j,i,k) with j fastest — exactly `c_loc(a(lb1,lb2,lb3))` of a
+ *    contiguous `getmem3d` array (Share/mod_memutil.F90).  2-D arrays pass
+ *    lb[2]=ub[2]=1, 1-D vertical arrays pass lb[0]=lb[1]=ub[0]=ub[1]=1.
+ *  - host arrays are borrowed for the duration of the call only.
+ *  - every function returns 0 on success or a negative RCM_ERR_* code;
+ *    rcm_dyn_last_error() gives the message (the Fortran shim turns non-zero
+ *    into `call fatal(__FILE__,__LINE__,msg)`, Share/mod_message.F90:90).
+ *  - one handle per MPI rank / GPU; calls are collective across ranks.
+ */
+#ifndef REGCM_DYN_H
+#define REGCM_DYN_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RCM_OK 0
+#define RCM_ERR_ARG (-1)   /* bad argument / unsupported option            */
+#define RCM_ERR_CUDA (-2)  /* CUDA runtime failure or no device            */
+#define RCM_ERR_CFL (-3)   /* Main/mod_sound.F90:650-665 'CFL violation'   */
+#define RCM_ERR_NAN (-4)   /* Main/mod_tendency.F90:625-703 NaN detection  */
+#define RCM_ERR_NCCL (-5)  /* halo exchange / communicator failure         */
+#define RCM_ERR_BDY (-6)   /* boundary record needed but not staged        */
+#define RCM_ERR_STATE (-7) /* call sequence error (e.g. step before init)  */
+
+/* prognostic fields: members of atm1/atm2 (`atmstate_a/b`,
+ * Main/mpplib/mod_regcm_types.F90:65-120; Main/mod_atm_interface.F90:617-672)
+ * and the boundary structures xub,xvb,xtb,xqb,xppb,xwwb
+ * (Main/mod_atm_interface.F90:544-573). */
+enum rcm_field {
+  RCM_F_U = 0,  /* dot   (jx  ,iy  ,kz)   p*·u  */
+  RCM_F_V = 1,  /* dot   (jx  ,iy  ,kz)   p*·v  */
+  RCM_F_T = 2,  /* cross (jx-1,iy-1,kz)   p*·T  */
+  RCM_F_QV = 3, /* cross                  p*·qv */
+  RCM_F_QC = 4, /* cross                  p*·qc */
+  RCM_F_PP = 5, /* cross                  p*·p' */
+  RCM_F_W = 6,  /* cross (jx-1,iy-1,kz+1) p*·w  */
+  RCM_F_COUNT = 7
+};
+
+/* static domain fields: members of `mddom` read by read_domain_info
+ * (Main/mod_params.F90:1733) plus the sigma vector. */
+enum rcm_static {
+  RCM_S_HT = 0,     /* terrain height [m], cross grid stored on (jx,iy)   */
+  RCM_S_MSFX = 1,   /* map factor at cross points                         */
+  RCM_S_MSFD = 2,   /* map factor at dot points                           */
+  RCM_S_CORIOL = 3, /* Coriolis parameter at dot points [1/s]             */
+  RCM_S_XLAT = 4,   /* latitude  of cross points [deg]                    */
+  RCM_S_XLON = 5,   /* longitude of cross points [deg]                    */
+  RCM_S_DLAT = 6,   /* latitude  of dot points [deg]                      */
+  RCM_S_SIGMA = 7,  /* full sigma levels, kz+1 values (k = 1 is the top)  */
+  RCM_S_COUNT = 8
+};
+
+/* time levels of the leapfrog state (atm1 = "a" = tau, atm2 = "b" = tau-1) */
+enum rcm_level { RCM_LEVEL_A = 0, RCM_LEVEL_B = 1 };
+
+/* boundary-record slots of v3dbound (b0, b1); RCM_BDY_NEXT stages the record
+ * that the state part of `bdyin` (Main/mod_bdycod.F90:669-690,772-831) will
+ * move into b1 when the boundary alarm fires. */
+enum rcm_bdy_slot { RCM_BDY_B0 = 0, RCM_BDY_B1 = 1, RCM_BDY_NEXT = 2 };
+
+/* intermediate arrays that can be read back after a step for operator-level
+ * parity checks (debug taps; no reference equivalent other than the module
+ * variables named in the comments). */
+enum rcm_work {
+  RCM_W_CR = 0,    /* mdv%cr     Main/mod_tendency.F90:1179-1191          */
+  RCM_W_QDOT = 1,  /* qdot       Main/mod_tendency.F90:1167-1178  (kz+1)  */
+  RCM_W_XKC = 2,   /* xkc before the rdxsq*p* scaling mod_diffusion:212-230 */
+  RCM_W_TH = 3,    /* th         Main/mod_tendency.F90:1350-1353          */
+  RCM_W_RHO1 = 4,  /* atm1%rho   Main/mod_tendency.F90:1057-1058          */
+  RCM_W_PR1 = 5,   /* atm1%pr                                             */
+  RCM_W_UTEN = 6,  /* aten%u(:,:,:,pc_total) as handed to sound (x dts)   */
+  RCM_W_VTEN = 7,
+  RCM_W_PPTEN = 8,
+  RCM_W_WTEN = 9,  /* (kz+1) */
+  RCM_W_COUNT = 10
+};
+
+/* Flat copy of the namelist scalars the dyn-core reads
+ * (Share/mod_dynparam.F90:453-476, Main/mod_params.F90:87-118,190-300,645-665)
+ * plus the decomposition (Main/mpplib/mod_mppparam.F90:1053-1401). */
+typedef struct rcm_cfg {
+  int32_t struct_size; /* = sizeof(rcm_cfg), ABI check                     */
+  /* &dimparam */
+  int32_t jx, iy, kz;
+  int32_t nqx;      /* number of water species carried (2: qv,qc)          */
+  /* &coreparam */
+  int32_t idynamic; /* 1 hydrostatic, 2 non-hydrostatic, 3 MOLOCH          */
+  /* &physicsparam (dynamics-relevant switches only) */
+  int32_t iboudy;   /* 0 fixed, 1 linear relax., 5 exponential relax.      */
+  int32_t idiffu;   /* 1 = 4th-order (only value implemented)              */
+  int32_t ipptls;   /* >0: hydrometeors advected, water loading in w       */
+  /* &nonhydroparam */
+  int32_t ifupr;    /* upper radiative boundary condition                  */
+  int32_t ifrayd;   /* Rayleigh damping at the model top                   */
+  int32_t rayndamp;
+  /* &boundaryparam */
+  int32_t nspgx, nspgd;
+  /* &globdatparam */
+  int32_t ibdyfrq;  /* hours between boundary records                      */
+  /* &dynparam */
+  int32_t upstream_mode, stability_enhance, diffu_hgtf;
+  /* decomposition: rank layout on the (jx,iy) plane, set_nproc rules      */
+  int32_t nproc, myid;
+  int32_t cpus_j, cpus_i; /* 0,0 = choose like set_nproc                   */
+  int32_t device;         /* CUDA device ordinal, -1 = myid % device count */
+  int32_t reserved_i[8];
+  /* &geoparam */
+  double ds;    /* grid spacing [km]                                       */
+  double ptop;  /* model top pressure [cb]                                 */
+  /* &timeparam */
+  double dt;    /* dtsec [s]                                               */
+  /* &dynparam */
+  double gnu1, gnu2, ckh, adyndif, uoffc, t_extrema, q_rel_extrema;
+  /* &nonhydroparam */
+  double nhbet, nhxkd, rayalpha0, rayhd;
+  /* &boundaryparam */
+  double high_nudge, medium_nudge, low_nudge, bdy_nm, bdy_dm;
+  /* &referenceatm + DOMAIN-file base state surface temperature */
+  double base_state_pressure, logp_lrate, base_state_ts0;
+  double reserved_d[8];
+} rcm_cfg;
+
+/* health metrics the reference prints (Main/mod_sound.F90:634-646) */
+typedef struct rcm_diag {
+  int64_t lcount;     /* rcmtimer%lcount                                   */
+  double xbctime;     /* seconds since boundary record b0                  */
+  double dt;          /* current leapfrog dt (dtsec, then 2*dtsec)         */
+  double max_cfl;     /* max over sub-steps of last step                   */
+  int32_t istep;      /* acoustic sub-steps of last step                   */
+  int32_t nan_flag;
+  int64_t neg_q_points; /* points repaired by the negative-q fix, last step */
+} rcm_diag;
+
+typedef struct rcm_dyn rcm_dyn; /* opaque */
+
+/* Fill cfg with the reference defaults (Main/mod_params.F90:190-300,645-665;
+ * Share/mod_dynparam.F90:147-154,502-508) for the given core. */
+int rcm_dyn_default_cfg(rcm_cfg* cfg, int idynamic);
+
+/* replaces: allocate_mod_atm_interface / _tend / _bdycon / _sound /
+ * _diffusion, setup_model_indexes, setup_boundaries, set_nproc
+ * (Main/mod_params.F90:1554-1590; Main/mod_atm_interface.F90:181-542). */
+int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** handle);
+
+/* replaces: read_domain_info → mddom%{ht,msfx,msfd,coriol,xlat,xlon,dlat},
+ * sigma (Main/mod_params.F90:1733). */
+int rcm_dyn_set_static(rcm_dyn* h, int static_id, const double* a,
+                       const int32_t lb[3], const int32_t ub[3]);
+
+/* replaces: read_icbc into x?b%b0 / x?b%b1 (Main/mod_bdycod.F90:325-369,
+ * 452-496,712-760).  Values are DECOUPLED (u,v [m/s], T [K], qv [kg/kg],
+ * p' [Pa], w [m/s]); the library couples them with p* like
+ * `couple` (Main/mod_bdycod.F90:4938-4951). */
+int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a,
+                    const int32_t lb[3], const int32_t ub[3]);
+
+/* replaces: the static part of `param` (map-factor inversion, xmsf/dmsf,
+ * hsigma/dsigma/twt/qcon, init_advection, setup_bdycon,
+ * make_reference_atmosphere, compute_full_coriolis_coefficients —
+ * Main/mod_params.F90:1981-2074,2208-2215,2613-2741), the state part of
+ * `init_bdy` (Main/mod_bdycod.F90:393-435,522-559,625-640), `init`
+ * (Main/mod_init.F90:96-178,878-903), initialize_diffusion, init_sound, and
+ * the first `bdyval` (Main/mod_regcm_interface.F90:146). */
+int rcm_dyn_init(rcm_dyn* h);
+
+/* replaces: nsteps x { call tend ; [call bdyin] ; call bdyval }
+ * (Main/mod_regcm_interface.F90:172-228; Main/mod_tendency.F90:212;
+ * Main/mod_bdycod.F90:654,1109).  Synchronous: the state is observable with
+ * rcm_dyn_get_state on return. */
+int rcm_dyn_step(rcm_dyn* h, int nsteps);
+
+/* state export/import = what write_savefile/read_savefile carry for the
+ * dynamics (Main/mod_savefile.F90:564-1264): COUPLED atm1/atm2 fields. */
+int rcm_dyn_get_state(rcm_dyn* h, int field, int level, double* a,
+                      const int32_t lb[3], const int32_t ub[3]);
+int rcm_dyn_set_state(rcm_dyn* h, int field, int level, const double* a,
+                      const int32_t lb[3], const int32_t ub[3]);
+
+/* debug tap, see enum rcm_work */
+int rcm_dyn_get_work(rcm_dyn* h, int work_id, double* a, const int32_t lb[3],
+                     const int32_t ub[3]);
+
+int rcm_dyn_diag(rcm_dyn* h, rcm_diag* out);
+int rcm_dyn_last_error(rcm_dyn* h, char* buf, int len);
+
+/* number of CUDA kernels launched by this handle so far, and the device time
+ * of the last rcm_dyn_step call in milliseconds (CUDA events on the library's
+ * own stream). */
+int64_t rcm_dyn_launch_count(rcm_dyn* h);
+double rcm_dyn_last_step_ms(rcm_dyn* h);
+
+/* replaces: memory_destroy (Main/mod_regcm_interface.F90:264). */
+int rcm_dyn_destroy(rcm_dyn* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* REGCM_DYN_H */

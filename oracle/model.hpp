@@ -1,0 +1,235 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.
+// CPU (double precision) restatement of the reference's dyn-core state and
+// step for idynamic = 2 (non-hydrostatic MM5 core), single rank.
+// "parity unpinned": the reference ships no golden vectors for this path
+// (SURVEY.md §8c); this restatement IS the pin.
+//
+// Data model follows Main/mod_atm_interface.F90:39-60 (atm1, atm2, atmc, aten,
+// atmx, atm0, atms, sfs, mddom, mdv, x?b) and Main/mpplib/mod_regcm_types.F90.
+#pragma once
+#include <cstdint>
+#include <string>
+
+#include "../include/regcm_dyn.h"
+#include "arr.hpp"
+#include "consts.hpp"
+
+namespace orc {
+
+struct V3dBound {  // type v3dbound, Main/mpplib/mod_regcm_types.F90
+  A3 b0, b1, bt;
+};
+
+struct BoundArea {  // type bound_area, Main/mod_atm_interface.F90:383-542
+  int nsp = 0, ns = 0, nn = 0, nw = 0, ne = 0;
+  bool havebound = false;
+  I2 ibnd, bsouth, bnorth, bwest, beast;
+};
+
+struct Oracle {
+  rcm_cfg cfg{};
+  std::string err;
+
+  // ---- dimensions / run switches (Share/mod_dynparam.F90, mod_runparams) ----
+  int jx = 0, iy = 0, kz = 0, kzp1 = 0, nqx = 2;
+  int iqv = 1, iqc = 2, iqfrst = 2, iqlst = 2;
+  int idif = 2;
+  int iqxvadv = 1;  // Main/mod_tendency.F90:148
+  double dx = 0, dx2 = 0, dx4 = 0, dx8 = 0, dx16 = 0, dxsq = 0, rdx = 0,
+         rdxsq = 0;
+  double dtsec = 0, dt = 0, dt2 = 0;
+  double ptop = 0;
+  double xbctime = 0, dtbdys = 0, rdtbdy = 0;
+  int64_t lcount = 0;          // rcmtimer%lcount
+  int64_t model_time = 0;      // rcmtimer%model_internal_time [s]
+  // alarm_day (86400 s) and alarm_in_bdy (ibdyfrq h): mod_timer.F90:277-337
+  int64_t day_lastact = 0, day_now = 0;
+  int64_t bdy_lastact = 0, bdy_now = -1;
+  bool have_next = false;
+
+  // ---- index families (Main/mod_atm_interface.F90:181-381), single rank ----
+  int jde1, jde2, ide1, ide2, jdi1, jdi2, idi1, idi2, jdii1, jdii2, idii1,
+      idii2;
+  int jce1, jce2, ice1, ice2, jci1, jci2, ici1, ici2, jcii1, jcii2, icii1,
+      icii2;
+  int jcross1, jcross2, icross1, icross2;
+  bool has_bdyleft = true, has_bdyright = true, has_bdytop = true,
+       has_bdybottom = true;
+
+  // ---- vertical coordinate (Main/mod_params.F90:2005-2010,2208-2215) ----
+  A1 sigma, hsigma, dsigma, qcon, dds, xds;
+  A2 twt;  // twt(k,1:2)
+
+  // ---- mddom ----
+  A2 ht, msfx, msfd, coriol, xlat, xlon, dlat, xmsf, dmsf;
+  A2 ef, ddx, ddy, dmdx, dmdy, ex, crx, cry;
+  A2 dpsdxm, dpsdym;
+
+  // ---- sfs ----
+  A2 psa, psb, psc, psdota, psdotb;
+  A2 rpsa, rpsb, rpsda;  // Main/mod_tendency.F90:63-64
+
+  // ---- atm0 reference atmosphere ----
+  A2 a0_ps, a0_psdot;
+  A3 a0_t, a0_pr, a0_rho, a0_z, a0_tf, a0_pf, a0_rhof, a0_zf, a0_dzf,
+      a0_dprddx, a0_dprddy;
+
+  // ---- atm1 (a), atm2 (b), atmc (c) ----
+  A3 a1_u, a1_v, a1_t, a1_pp, a1_w, a1_pr, a1_rho;
+  A4 a1_qx;
+  A3 a2_u, a2_v, a2_t, a2_pp, a2_w, a2_pr;
+  A4 a2_qx;
+  A3 ac_u, ac_v, ac_t, ac_pp, ac_w;
+  A4 ac_qx;
+
+  // ---- atmx decoupled ----
+  A3 ax_uc, ax_vc, ax_umc, ax_vmc, ax_ud, ax_vd, ax_umd, ax_vmd, ax_t, ax_tv,
+      ax_pr, ax_pp, ax_w;
+  A4 ax_qx;
+
+  // ---- aten: three components pc_total=1, pc_dynamic=2, pc_physic=3 ----
+  A3 uten, vten, tten, ppten, wten, udyn, vdyn, tdyn, ppdyn, wdyn;
+  A4 qxten, qxdyn;
+
+  // ---- atms slices used by the dynamics (Main/mod_slice.F90:167-263) ----
+  A3 ubd3d, vbd3d, tb3d, ppb3d, wb3d;
+  A4 qxb3d;
+
+  // ---- misc work arrays ----
+  A3 qdot, cr, omega;                  // mod_atm_interface qdot, mdv%cr
+  A3 ucc, vcc, th, tha, thten;         // mod_tendency.F90:57-62
+  A3 fg, uavg1, uavg2, vavg1, vavg2;   // mod_advection.F90:71-73
+  A3 xkc, xkd, xkcf;                   // mod_diffusion
+  A3 xkc_raw;  // tap: xkc before the rdxsq*p* scaling (tests only)
+  A2 hgfact;
+  double dydc = 0, xkhmax = 0;
+  double ul = 0;                       // mod_advection.F90:106
+
+  // ---- boundary (mod_bdycod) ----
+  V3dBound xub, xvb, xtb, xqb, xppb, xwwb;
+  A3 nx_u, nx_v, nx_t, nx_q, nx_pp, nx_ww;  // staged next record (decoupled)
+  A2 xpsb_b0;
+  A2 psdot;                            // bdycon:psdot
+  A2 wue, wui, eue, eui, wve, wvi, eve, evi;  // (i,k)
+  A2 sue, sui, nue, nui, sve, svi, nve, nvi;  // (j,k)
+  A1 fcx, gcx, fcd, gcd;
+  A2 hefc, hegc, hefd, hegd;
+  A3 fg1, fg2;
+  double fnudge = 0, gnudge = 0;
+  BoundArea ba_cr, ba_dt;
+
+  // ---- sound (mod_sound.F90:41-78) ----
+  A3 s_aa, s_b, s_c, s_rhs, s_sigdot, s_wo, s_ca, s_g1, s_g2, s_ptend, s_pxup,
+      s_pyvp, s_ucrs, s_vcrs, s_tk, s_cc, s_cdd, s_cj, s_pi, s_e, s_f;
+  A2 s_astore, s_estore, s_estore_g, s_wpval, s_rpsb;
+  A2 tmask;  // (-6:6,-6:6)
+  double fi[13], fj[13], fk[7], fl[7];
+  double xmsf_mean = 0;
+  double bet = 0.4, xkd_snd = 0.1, cs = 0, bp = 0, bm = 0, bpxbm = 0,
+         bpxbp = 0, dtsmax = 0, rnpts = 0;
+  double xgamma = 0;
+  double max_cfl_step = 0;
+  int last_istep = 0;
+  bool cfl_error = false;
+  int64_t neg_q_points = 0;
+
+  // ---- life cycle (oracle/setup.cpp) ----
+  int create(const rcm_cfg& c);
+  int set_static(int id, const double* a, const int32_t lb[3],
+                 const int32_t ub[3]);
+  int set_bdy(int field, int slot, const double* a, const int32_t lb[3],
+              const int32_t ub[3]);
+  int init();
+  int step(int n);
+  int get_state(int field, int level, double* a, const int32_t lb[3],
+                const int32_t ub[3]);
+  int get_work(int id, double* a, const int32_t lb[3], const int32_t ub[3]);
+
+  // ---- setup pieces ----
+  void setup_model_indexes();
+  void setup_boundaries(bool ldotx, bool ldoty, BoundArea& ba);
+  void allocate_all();
+  void param_static();
+  void make_reference_atmosphere();
+  void compute_full_coriolis_coefficients();
+  void init_advection();
+  void setup_bdycon();
+  void init_bdy();
+  void init_state();
+  void initialize_diffusion();
+  void init_sound();
+  void psc2psd(const A2& pc, A2& pd);
+  void nhbase(int i1, int i2, int j1, int j2, int kx, const A1& sig,
+              const A2& ter, A2& ps0, A3& pr0, A3& t0, A3& rho0, A3& z0);
+
+  // ---- tend and its internal procedures (oracle/tendency.cpp) ----
+  void tend();
+  void surface_pressures();
+  void decouple();
+  void compute_omega();
+  void mkslice();
+  void init_tendencies();
+  void advection();
+  void curvature();
+  void adiabatic();
+  void boundary();
+  void diffusion();
+
+  // ---- mod_advection (oracle/advection.cpp) ----
+  void start_advect();
+  void hadvuv(A3& ut, A3& vt, const A3& u, const A3& v);
+  void vadvuv(A3& ut, A3& vt, const A3& ud, const A3& vd);
+  void hadvt(A3& ften, const A3& f);
+  void hadv3d(A3& ften, const A3& f, int ind);
+  void hadvqv(A4& ften, const A4& f, int iv);
+  void hadvqx(A4& ften, const A4& f, int n1, int n2);
+  void vadv3d(A3& ften, const A3& f, int nk, int ind);
+  void vadvqv(A4& ften, const A4& f, int n);
+  void vadv4d(A4& ften, const A4& f, int n1, int n2, int ind);
+
+  // ---- mod_diffusion (oracle/diffusion.cpp) ----
+  void calc_coeff();
+  void diffu_d(A3& ut, A3& vt, const A3& u, const A3& v);
+  void diffu_x3d(A3& ften, const A3& f);
+  void diffu_x3df(A3& ften, const A3& f, double fac);
+  void diffu_x4d(A4& ften, const A4& f, int n1, int n2, double fac);
+
+  // ---- mod_bdycod (oracle/bdycod.cpp) ----
+  void nudge3d(int ibdy, const A3& f, const V3dBound& bnd, A3& ften);
+  void nudge4d3d(int ibdy, const A4& f, const V3dBound& bnd, A4& ften, int n);
+  void nudgeuv(int ibdy, const A3& fu, const A3& fv, const V3dBound& bu,
+               const V3dBound& bv, A3& ftu, A3& ftv);
+  void raydamp3(const A3& z, const A3& var, A3& vten, const V3dBound& bnd);
+  void raydamp3f(const A3& z, const A3& var, A3& vten, double sval);
+  void raydampuv(const A3& z, const A3& u, const A3& v, A3& ut, A3& vt,
+                 const V3dBound& ub, const V3dBound& vb);
+  void raydampqv(const A3& z, const A4& var, A4& vten, const V3dBound& bnd);
+  double tau(double z, double zmax) const;
+  void bdyin();
+  void bdyuv(double xt);
+  void bdyval();
+  void timeint(const A3& a, const A3& b, A3& c, int j1, int j2, int i1, int i2,
+               int k1, int k2);
+  void couple(A3& a, const A2& c, int j1, int j2, int i1, int i2, int k1,
+              int k2);
+
+  // ---- mod_timefilter (oracle/timefilter.cpp) ----
+  void filter_ra_3d(A3& phin, A3& phinm1, const A3& phinp1, double alpha);
+  void filter_ra_uv(A3& un, A3& unm1, const A3& unp1, A3& vn, A3& vnm1,
+                    const A3& vnp1, double alpha);
+  void filter_raw_qv(A4& phin, A4& phinm1, const A4& phinp1, double alpha,
+                     double beta, const A2& psa_, const A2& psb_);
+  void filter_raw_4d(A4& phin, A4& phinm1, const A4& phinp1, double alpha,
+                     double beta, int n1, int n2, double low);
+
+  // ---- mod_sound (oracle/sound.cpp) ----
+  void sound();
+
+  // timers
+  bool integrating() const { return lcount > 0; }
+  bool alarm_day_act() const { return day_now == model_time; }
+  bool alarm_bdy_act() const { return bdy_now == model_time; }
+  void timer_advance();
+};
+
+}  // namespace orc

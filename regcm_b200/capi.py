@@ -1,0 +1,272 @@
+"""ctypes binding of the C ABI declared in include/regcm_dyn.h.
+
+`DynCore` is the host-side mirror of the reference's interface for the dyn-core
+path: the reference drives it with argument-less module procedures
+(`call tend`, `call bdyin`, `call bdyval`, Main/mod_regcm_interface.F90:172-228)
+acting on the public arrays of mod_atm_interface (Main/mod_atm_interface.F90:39-60);
+here the same life cycle is create -> set_static -> set_bdy -> init -> step ->
+get_state.  All compute happens in the CUDA library; this module contains no
+numerical fallback and raises if the library cannot be loaded.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Sequence
+
+import numpy as np
+
+# enum rcm_field / rcm_static / rcm_work (include/regcm_dyn.h)
+F_U, F_V, F_T, F_QV, F_QC, F_PP, F_W = range(7)
+FIELD_NAMES = ("u", "v", "t", "qv", "qc", "pp", "w")
+S_HT, S_MSFX, S_MSFD, S_CORIOL, S_XLAT, S_XLON, S_DLAT, S_SIGMA = range(8)
+LEVEL_A, LEVEL_B = 0, 1
+BDY_B0, BDY_B1, BDY_NEXT = 0, 1, 2
+W_CR, W_QDOT, W_XKC, W_TH, W_RHO1, W_PR1, W_UTEN, W_VTEN, W_PPTEN, W_WTEN = range(10)
+WORK_NAMES = ("cr", "qdot", "xkc", "th", "rho1", "pr1", "uten", "vten", "ppten", "wten")
+
+ERRORS = {0: "RCM_OK", -1: "RCM_ERR_ARG", -2: "RCM_ERR_CUDA", -3: "RCM_ERR_CFL",
+          -4: "RCM_ERR_NAN", -5: "RCM_ERR_NCCL", -6: "RCM_ERR_BDY", -7: "RCM_ERR_STATE"}
+
+
+class RcmCfg(C.Structure):
+    _fields_ = [
+        ("struct_size", C.c_int32),
+        ("jx", C.c_int32), ("iy", C.c_int32), ("kz", C.c_int32), ("nqx", C.c_int32),
+        ("idynamic", C.c_int32),
+        ("iboudy", C.c_int32), ("idiffu", C.c_int32), ("ipptls", C.c_int32),
+        ("ifupr", C.c_int32), ("ifrayd", C.c_int32), ("rayndamp", C.c_int32),
+        ("nspgx", C.c_int32), ("nspgd", C.c_int32),
+        ("ibdyfrq", C.c_int32),
+        ("upstream_mode", C.c_int32), ("stability_enhance", C.c_int32), ("diffu_hgtf", C.c_int32),
+        ("nproc", C.c_int32), ("myid", C.c_int32),
+        ("cpus_j", C.c_int32), ("cpus_i", C.c_int32),
+        ("device", C.c_int32),
+        ("reserved_i", C.c_int32 * 8),
+        ("ds", C.c_double), ("ptop", C.c_double),
+        ("dt", C.c_double),
+        ("gnu1", C.c_double), ("gnu2", C.c_double), ("ckh", C.c_double), ("adyndif", C.c_double),
+        ("uoffc", C.c_double), ("t_extrema", C.c_double), ("q_rel_extrema", C.c_double),
+        ("nhbet", C.c_double), ("nhxkd", C.c_double), ("rayalpha0", C.c_double), ("rayhd", C.c_double),
+        ("high_nudge", C.c_double), ("medium_nudge", C.c_double), ("low_nudge", C.c_double),
+        ("bdy_nm", C.c_double), ("bdy_dm", C.c_double),
+        ("base_state_pressure", C.c_double), ("logp_lrate", C.c_double), ("base_state_ts0", C.c_double),
+        ("reserved_d", C.c_double * 8),
+    ]
+
+
+class RcmDiag(C.Structure):
+    _fields_ = [
+        ("lcount", C.c_int64), ("xbctime", C.c_double), ("dt", C.c_double),
+        ("max_cfl", C.c_double), ("istep", C.c_int32), ("nan_flag", C.c_int32),
+        ("neg_q_points", C.c_int64),
+    ]
+
+
+def default_cfg(idynamic: int = 2, **kw) -> RcmCfg:
+    """Reference defaults (Main/mod_params.F90:190-300,645-665;
+    Share/mod_dynparam.F90:147-154,502-508).  Pure data, no library call."""
+    c = RcmCfg()
+    c.struct_size = C.sizeof(RcmCfg)
+    c.nqx = 2
+    c.idynamic = idynamic
+    c.iboudy, c.idiffu, c.ipptls = 5, 1, 1
+    c.ifupr, c.ifrayd, c.rayndamp = 1, 1, 5
+    c.nspgx = c.nspgd = 12
+    c.ibdyfrq = 6
+    c.upstream_mode = c.stability_enhance = 1
+    c.nproc, c.myid, c.cpus_j, c.cpus_i, c.device = 1, 0, 0, 0, -1
+    c.ptop = 5.0
+    if idynamic == 2:
+        c.gnu1 = c.gnu2 = 0.1
+        c.diffu_hgtf = 0
+    else:
+        c.gnu1 = c.gnu2 = 0.0625
+        c.diffu_hgtf = 1
+    c.ckh = c.adyndif = 1.0
+    c.uoffc, c.t_extrema, c.q_rel_extrema = 0.25, 5.0, 0.20
+    c.nhbet, c.nhxkd, c.rayalpha0, c.rayhd = 0.4, 0.1, 0.0003, 10000.0
+    c.high_nudge, c.medium_nudge, c.low_nudge = 3.0, 2.0, 1.0
+    c.bdy_nm = c.bdy_dm = -1.0
+    c.base_state_pressure, c.logp_lrate, c.base_state_ts0 = 101325.0, 47.70, 288.15
+    for k, v in kw.items():
+        if not hasattr(c, k):
+            raise AttributeError(f"rcm_cfg has no field {k}")
+        setattr(c, k, v)
+    return c
+
+
+class RcmError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"{ERRORS.get(code, code)}: {msg}")
+        self.code = code
+
+
+_I3 = C.c_int32 * 3
+_DP = C.POINTER(C.c_double)
+
+
+def _bounds(lb: Sequence[int], ub: Sequence[int]):
+    return _I3(*lb), _I3(*ub)
+
+
+class CoreLib:
+    """One shared library exporting the regcm_dyn C ABI under `prefix`.
+
+    prefix = "rcm_dyn_" for the CUDA product library.  (The CPU restatement
+    under oracle/ exports the same call shapes with prefix "orc_"; only the
+    tests and the bench's cpu_baseline leg construct that one.)"""
+
+    def __init__(self, path: str, prefix: str):
+        if not os.path.exists(path):
+            raise FileNotFoundError(
+                f"{path} not found: build it first (python -c 'import __graft_entry__ as g; g.build()')")
+        self.path, self.prefix = path, prefix
+        self.lib = C.CDLL(path, mode=C.RTLD_GLOBAL)
+        p = prefix
+        vp = C.c_void_p
+        sig = {
+            "create": ([C.POINTER(RcmCfg), C.POINTER(vp)], C.c_int),
+            "set_static": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
+            "set_bdy": ([vp, C.c_int, C.c_int, _DP, _I3, _I3], C.c_int),
+            "init": ([vp], C.c_int),
+            "step": ([vp, C.c_int], C.c_int),
+            "get_state": ([vp, C.c_int, C.c_int, _DP, _I3, _I3], C.c_int),
+            "get_work": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
+            "diag": ([vp, C.POINTER(RcmDiag)], C.c_int),
+            "last_error": ([vp, C.c_char_p, C.c_int], C.c_int),
+            "destroy": ([vp], C.c_int),
+        }
+        for name, (args, res) in sig.items():
+            fn = getattr(self.lib, p + name)
+            fn.argtypes, fn.restype = args, res
+            setattr(self, name, fn)
+        for opt, (args, res) in {
+            "set_state": ([vp, C.c_int, C.c_int, _DP, _I3, _I3], C.c_int),
+            "launch_count": ([vp], C.c_int64),
+            "last_step_ms": ([vp], C.c_double),
+        }.items():
+            if hasattr(self.lib, p + opt):
+                fn = getattr(self.lib, p + opt)
+                fn.argtypes, fn.restype = args, res
+                setattr(self, opt, fn)
+
+
+class DynCore:
+    """Handle on one dyn-core instance (one rank / one GPU)."""
+
+    def __init__(self, lib: CoreLib, cfg: RcmCfg):
+        self.lib, self.cfg = lib, cfg
+        self.h = C.c_void_p()
+        rc = lib.create(C.byref(cfg), C.byref(self.h))
+        if rc != 0 or not self.h:
+            raise RcmError(rc, f"{lib.prefix}create failed")
+        self.jx, self.iy, self.kz = cfg.jx, cfg.iy, cfg.kz
+
+    # -- helpers ---------------------------------------------------------
+    def _check(self, rc: int):
+        if rc != 0:
+            buf = C.create_string_buffer(512)
+            self.lib.last_error(self.h, buf, 512)
+            raise RcmError(rc, buf.value.decode(errors="replace"))
+
+    @staticmethod
+    def _f(a: np.ndarray) -> np.ndarray:
+        a = np.asarray(a, dtype=np.float64)
+        if not a.flags.f_contiguous:
+            a = np.asfortranarray(a)
+        return a
+
+    def field_shape(self, field: int):
+        jx, iy, kz = self.jx, self.iy, self.kz
+        if field in (F_U, F_V):
+            return (jx, iy, kz)
+        if field == F_W:
+            return (jx - 1, iy - 1, kz + 1)
+        return (jx - 1, iy - 1, kz)
+
+    # -- API ---------------------------------------------------------------
+    def set_static(self, sid: int, a: np.ndarray, lb=None):
+        a = self._f(a)
+        if sid == S_SIGMA:
+            lb3, ub3 = (1, 1, 1), (1, 1, a.size)
+        else:
+            l = lb or (1, 1)
+            lb3, ub3 = (l[0], l[1], 1), (l[0] + a.shape[0] - 1, l[1] + a.shape[1] - 1, 1)
+        self._check(self.lib.set_static(self.h, sid, a.ctypes.data_as(_DP), *_bounds(lb3, ub3)))
+
+    def set_bdy(self, field: int, slot: int, a: np.ndarray, lb=(1, 1, 1)):
+        a = self._f(a)
+        ub = tuple(lb[d] + a.shape[d] - 1 for d in range(3))
+        self._check(self.lib.set_bdy(self.h, field, slot, a.ctypes.data_as(_DP), *_bounds(lb, ub)))
+
+    def init(self):
+        self._check(self.lib.init(self.h))
+
+    def step(self, n: int = 1):
+        self._check(self.lib.step(self.h, n))
+
+    def get_state(self, field: int, level: int = LEVEL_A, lb=None, ub=None) -> np.ndarray:
+        shp = self.field_shape(field)
+        lb = lb or (1, 1, 1)
+        ub = ub or shp
+        out = np.zeros(tuple(ub[d] - lb[d] + 1 for d in range(3)), dtype=np.float64, order="F")
+        self._check(self.lib.get_state(self.h, field, level, out.ctypes.data_as(_DP), *_bounds(lb, ub)))
+        return out
+
+    def set_state(self, field: int, level: int, a: np.ndarray, lb=(1, 1, 1)):
+        a = self._f(a)
+        ub = tuple(lb[d] + a.shape[d] - 1 for d in range(3))
+        self._check(self.lib.set_state(self.h, field, level, a.ctypes.data_as(_DP), *_bounds(lb, ub)))
+
+    def get_work(self, wid: int) -> np.ndarray:
+        jx, iy, kz = self.jx, self.iy, self.kz
+        if wid in (W_UTEN, W_VTEN):
+            lb, ub = (2, 2, 1), (jx - 1, iy - 1, kz)
+        elif wid in (W_PPTEN,):
+            lb, ub = (2, 2, 1), (jx - 2, iy - 2, kz)
+        elif wid == W_WTEN:
+            lb, ub = (2, 2, 1), (jx - 2, iy - 2, kz + 1)
+        elif wid == W_QDOT:
+            lb, ub = (1, 1, 1), (jx - 1, iy - 1, kz + 1)
+        else:
+            lb, ub = (1, 1, 1), (jx - 1, iy - 1, kz)
+        out = np.zeros(tuple(ub[d] - lb[d] + 1 for d in range(3)), dtype=np.float64, order="F")
+        self._check(self.lib.get_work(self.h, wid, out.ctypes.data_as(_DP), *_bounds(lb, ub)))
+        return out
+
+    def diag(self) -> RcmDiag:
+        d = RcmDiag()
+        self._check(self.lib.diag(self.h, C.byref(d)))
+        return d
+
+    def launch_count(self) -> int:
+        return int(self.lib.launch_count(self.h))
+
+    def last_step_ms(self) -> float:
+        return float(self.lib.last_step_ms(self.h))
+
+    def close(self):
+        if self.h:
+            self.lib.destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+CUDA_LIB_PATH = os.path.join(_PKG_DIR, "csrc", "libregcm_dyn.so")
+_cuda_lib = None
+
+
+def cuda_lib() -> CoreLib:
+    """The product library.  Fails loudly when it has not been built: there is
+    no CPU fallback behind this API."""
+    global _cuda_lib
+    if _cuda_lib is None:
+        _cuda_lib = CoreLib(CUDA_LIB_PATH, "rcm_dyn_")
+    return _cuda_lib

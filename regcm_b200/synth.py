@@ -1,0 +1,169 @@
+"""Synthetic analytic DOMAIN + ICBC generator.
+
+Replaces the reference's pre-processing chain (PreProc/Terrain, PreProc/ICBC,
+read_domain_info / read_icbc in Main/mod_ncio.F90) with in-memory analytic
+fields: Gaussian terrain, Lambert-conformal map factors, a balanced reference
+temperature profile plus a smooth jet / thermal / moisture perturbation and
+seeded round-off-scale noise, and boundary records 6 h apart so that the
+boundary tendency `bt` is non-zero.  The reference's own precedent for
+"analytic ICBC, physics off" is moloch_static_test1/2
+(Main/mod_bdycod.F90:5157-5199).
+
+Everything is generated on the GLOBAL grid so that every rank count sees
+identical data.  Arrays are Fortran-ordered (j,i[,k]) float64.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict
+
+import numpy as np
+
+from . import capi
+
+SEED = 20261104
+
+# hard-coded full-sigma tables of the reference (data, Share/mod_sigma.F90:92-205)
+_SIGMA = {
+    14: [0.0, 0.04, 0.10, 0.17, 0.25, 0.35, 0.46, 0.56, 0.67, 0.77, 0.86, 0.93, 0.97, 0.99, 1.0],
+    18: [0.0, 0.05, 0.10, 0.16, 0.23, 0.31, 0.39, 0.47, 0.55, 0.63, 0.71, 0.78, 0.84, 0.89, 0.93,
+         0.96, 0.98, 0.99, 1.0],
+    23: [0.0, 0.05, 0.1, 0.15, 0.2, 0.25, 0.3, 0.35, 0.4, 0.45, 0.5, 0.55, 0.6, 0.65, 0.7, 0.75,
+         0.8, 0.85, 0.89, 0.93, 0.96, 0.98, 0.99, 1.0],
+    41: [0.0000, 0.0500, 0.0978, 0.1436, 0.1875, 0.2295, 0.2697, 0.3082, 0.3451, 0.3804, 0.4143,
+         0.4468, 0.4779, 0.5078, 0.5364, 0.5639, 0.5903, 0.6156, 0.6399, 0.6632, 0.6856, 0.7071,
+         0.7277, 0.7476, 0.7667, 0.7850, 0.8027, 0.8196, 0.8359, 0.8516, 0.8667, 0.8812, 0.8952,
+         0.9087, 0.9216, 0.9341, 0.9461, 0.9577, 0.9689, 0.9796, 0.9900, 1.0000],
+}
+
+
+def sigma_levels(kz: int) -> np.ndarray:
+    if kz in _SIGMA:
+        return np.array(_SIGMA[kz], dtype=np.float64)
+    s = np.linspace(0.0, 1.0, kz + 1)
+    return 1.0 - (1.0 - s) ** 1.5  # finer spacing near the surface
+
+
+# named workloads (C2, C3, C4) + small cases for the test-suite
+CASES = {
+    # name: jx, iy, kz, ds[km], dt[s], nspg
+    "tiny": dict(jx=20, iy=16, kz=8, ds=60.0, dt=120.0, nspg=4),
+    "small": dict(jx=40, iy=30, kz=14, ds=60.0, dt=120.0, nspg=6),
+    "C2": dict(jx=64, iy=34, kz=18, ds=60.0, dt=120.0, nspg=8),
+    "C3": dict(jx=250, iy=200, kz=23, ds=50.0, dt=120.0, nspg=12),
+    "C4": dict(jx=1000, iy=1000, kz=41, ds=3.0, dt=6.0, nspg=12),
+    "C4q": dict(jx=500, iy=500, kz=41, ds=3.0, dt=6.0, nspg=12),
+}
+
+
+@dataclass
+class Case:
+    name: str
+    cfg: capi.RcmCfg
+    statics: Dict[int, np.ndarray] = field(default_factory=dict)
+    bdy: Dict[int, Dict[int, np.ndarray]] = field(default_factory=dict)  # slot -> field -> array
+
+    @property
+    def cells(self) -> int:
+        return self.cfg.jx * self.cfg.iy * self.cfg.kz
+
+
+def _lambert_msf(lat_deg: np.ndarray, tl1=30.0, tl2=60.0) -> np.ndarray:
+    d2r = np.pi / 180.0
+    p1, p2 = tl1 * d2r, tl2 * d2r
+    n = np.log(np.cos(p1) / np.cos(p2)) / np.log(np.tan(np.pi / 4 + p2 / 2) / np.tan(np.pi / 4 + p1 / 2))
+    phi = lat_deg * d2r
+    return (np.cos(p1) / np.cos(phi)) * (np.tan(np.pi / 4 + p1 / 2) / np.tan(np.pi / 4 + phi / 2)) ** n
+
+
+def make_case(name: str = "C2", *, flat: bool = False, unit_map: bool = False, noise: bool = True,
+              ibdyfrq: int = 6, **cfg_over) -> Case:
+    p = dict(CASES[name])
+    jx, iy, kz = p["jx"], p["iy"], p["kz"]
+    cfg = capi.default_cfg(2, jx=jx, iy=iy, kz=kz, ds=p["ds"], dt=p["dt"],
+                           nspgx=p["nspg"], nspgd=p["nspg"], ibdyfrq=ibdyfrq)
+    for k, v in cfg_over.items():
+        setattr(cfg, k, v)
+    dx = cfg.ds * 1000.0
+    rearth = 6.371229e6
+    clat, clon = 45.0, 13.0
+    # dot points j=1..jx, i=1..iy ; cross point (j,i) = centre of dots (j..j+1, i..i+1)
+    xd = (np.arange(1, jx + 1) - 0.5 * (jx + 1)) * dx
+    yd = (np.arange(1, iy + 1) - 0.5 * (iy + 1)) * dx
+    xc, yc = xd + 0.5 * dx, yd + 0.5 * dx
+    Xd, Yd = np.meshgrid(xd, yd, indexing="ij")
+    Xc, Yc = np.meshgrid(xc, yc, indexing="ij")
+    dlat = clat + np.degrees(Yd / rearth)
+    xlat = clat + np.degrees(Yc / rearth)
+    xlon = clon + np.degrees(Xc / (rearth * np.cos(np.radians(xlat))))
+    if unit_map:
+        msfd = np.ones((jx, iy)); msfx = np.ones((jx, iy)); coriol = np.zeros((jx, iy))
+    else:
+        msfd, msfx = _lambert_msf(dlat), _lambert_msf(xlat)
+        coriol = 2.0 * 7.2921159e-5 * np.sin(np.radians(dlat))
+    if flat:
+        ht = np.zeros((jx, iy))
+    else:
+        L = 0.15 * min(jx, iy) * dx
+        ht = 1500.0 * np.exp(-(Xc ** 2 + Yc ** 2) / L ** 2)
+    sigma = sigma_levels(kz)
+    case = Case(name=name, cfg=cfg)
+    F = np.asfortranarray
+    case.statics = {capi.S_HT: F(ht), capi.S_MSFX: F(msfx), capi.S_MSFD: F(msfd), capi.S_CORIOL: F(coriol),
+                    capi.S_XLAT: F(xlat), capi.S_XLON: F(xlon), capi.S_DLAT: F(dlat), capi.S_SIGMA: sigma}
+
+    # ---- reference-like thermodynamic profile (same closed form as nhbase) ----
+    rgas = 6.02214129e23 * 1.3806504e-23 / 28.96454 * 1000.0
+    g = 9.80665
+    p0, tlp, ts0, ptop_pa = cfg.base_state_pressure, cfg.logp_lrate, cfg.base_state_ts0, cfg.ptop * 1000.0
+    hs = 0.5 * (sigma[1:] + sigma[:-1])
+    htc = ht[: jx - 1, : iy - 1]
+    b = ts0 / tlp
+    alnp = -b + np.sqrt(b * b - 4.0 * (0.5 * g / rgas * htc / tlp))
+    ps0 = p0 * np.exp(alnp) - ptop_pa
+    pr0 = ps0[:, :, None] * hs[None, None, :] + ptop_pa
+    t0 = np.maximum(ts0 + tlp * np.log(pr0 / p0), 216.65)
+    a = np.log(pr0 / p0)
+    z = np.maximum(-(0.5 * rgas / g * tlp * a * a + rgas / g * ts0 * a), 0.0)
+
+    Lx, Ly = jx * dx, iy * dx
+    Xcc, Ycc = Xc[: jx - 1, : iy - 1], Yc[: jx - 1, : iy - 1]
+    sh = np.sin(np.pi * hs)[None, None, :]
+    rng = np.random.default_rng(SEED)
+    nz_t = rng.uniform(-1.0, 1.0, size=(jx - 1, iy - 1, kz)) if noise else 0.0
+    nz_u = rng.uniform(-1.0, 1.0, size=(jx, iy, kz)) if noise else 0.0
+    nz_v = rng.uniform(-1.0, 1.0, size=(jx, iy, kz)) if noise else 0.0
+
+    def record(phase: float):
+        """fields of one boundary record; `phase` shifts the smooth modes (U*6h)."""
+        xs_c, xs_d = Xcc[:, :, None] - phase, Xd[:, :, None] - phase
+        wave = 2.0 * np.sin(2 * np.pi * xs_c / Lx) * np.cos(2 * np.pi * Ycc[:, :, None] / Ly) * sh
+        r2 = ((xs_c - 0.2 * Lx) ** 2 + (Ycc[:, :, None] + 0.15 * Ly) ** 2) / (0.08 * min(Lx, Ly)) ** 2
+        bubble = 1.0 * np.exp(-r2) * sh
+        t = t0 + wave + bubble
+        t = t * (1.0 + 1.0e-3 * 1.0e-2 * nz_t)   # ±1e-5 relative (≈3 mK) noise
+        u = 20.0 * sh ** 2 * np.ones((jx, iy, 1)) + \
+            2.0 * np.sin(2 * np.pi * xs_d / Lx + 0.7) * np.sin(2 * np.pi * Yd[:, :, None] / Ly + 0.3)
+        v = 5.0 * np.sin(2 * np.pi * xs_d / Lx) * np.ones((1, 1, kz))
+        u = u + 2.0e-2 * nz_u
+        v = v + 2.0e-2 * nz_v
+        qv = np.maximum(0.012 * np.exp(-z / 2500.0) * (1.0 + 0.2 * np.sin(2 * np.pi * xs_c / Lx)), 1.0e-8)
+        pp = np.zeros((jx - 1, iy - 1, kz))
+        ww = np.zeros((jx - 1, iy - 1, kz + 1))
+        return {capi.F_U: F(u), capi.F_V: F(v), capi.F_T: F(t), capi.F_QV: F(qv),
+                capi.F_PP: F(pp), capi.F_W: F(ww)}
+
+    shift = 20.0 * 3600.0 * ibdyfrq * 0.25  # a quarter of the jet advection distance per record
+    case.bdy = {capi.BDY_B0: record(0.0), capi.BDY_B1: record(shift), capi.BDY_NEXT: record(2 * shift)}
+    return case
+
+
+def load_case(core: capi.DynCore, case: Case, stage_next: bool = True) -> None:
+    """Feed statics and boundary records into a core and initialise it
+    (= read_domain_info + init_bdy + init + first bdyval of the reference)."""
+    for sid, a in case.statics.items():
+        core.set_static(sid, a)
+    for slot in (capi.BDY_B0, capi.BDY_B1) + ((capi.BDY_NEXT,) if stage_next else ()):
+        for fid, a in case.bdy[slot].items():
+            core.set_bdy(fid, slot, a)
+    core.init()
