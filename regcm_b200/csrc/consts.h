@@ -1,0 +1,42 @@
+// Physical constants of the dyn-core (Share/mod_constants.F90:20-375).
+// Derived constants are built with the same operations as the reference so
+// that their last bits agree.
+#pragma once
+
+#ifdef __CUDACC__
+#define RCM_HD __host__ __device__
+#else
+#define RCM_HD
+#endif
+
+namespace rcm {
+constexpr double minqq = 1.0e-8;      // mod_constants.F90:57
+constexpr double dlowval = 1.0e-20;   // :68
+constexpr double egrav = 9.80665;     // :85
+constexpr double boltzk = 1.3806504e-23;
+constexpr double navgdr = 6.02214129e23;
+constexpr double amd = 28.96454;
+constexpr double amw = 18.01528;
+constexpr double rgasmol = navgdr * boltzk;
+constexpr double c287 = rgasmol / amd;
+constexpr double rgas = c287 * 1000.0;
+constexpr double cpd = 3.5 * rgas;
+constexpr double regrav = 1.0 / egrav;
+constexpr double rcpd = 1.0 / cpd;
+constexpr double rovcp = rgas * rcpd;
+constexpr double rovg = rgas / egrav;
+constexpr double govr = egrav / rgas;
+constexpr double tiso = 216.65;
+constexpr double p00 = 1.0e5;
+constexpr double mathpi = 3.1415926535897932384626433832795029;
+constexpr double halfpi = mathpi * 0.5;
+constexpr double degrad = mathpi / 180.0;
+constexpr double earthrad = 6.371229e6;
+constexpr double rearthrad = 1.0 / earthrad;
+constexpr double eomeg = 7.2921159e-5;
+constexpr double eomeg2 = 2.0 * eomeg;
+constexpr double vonkar = 0.4;
+constexpr double ep1 = amd / amw - 1.0;
+// Share/cpmf.inc
+RCM_HD inline double cpmf(double qv) { return cpd * (1.0 + 0.80 * qv); }
+}  // namespace rcm

@@ -1,0 +1,73 @@
+// Device-side helpers shared by all kernels of the dyn-core.
+#pragma once
+#include "consts.h"
+#include "dyn_types.h"
+#include "launch.h"
+
+// origin-shifted addressing with the reference's global 1-based indices
+#define P3(p, j, i, k) (p)[(long long)(j) + (long long)(i) * si + (long long)(k) * sk]
+#define P2(p, j, i) (p)[(long long)(j) + (long long)(i) * si]
+
+#define RCM_BX 32
+#define RCM_BY 4
+
+namespace rcm {
+
+// flux-form horizontal advection of a cross-point scalar
+// (Main/mod_advection.F90:336-351 upstream branch, :352-357 centred branch).
+// f1,f2 are the upstream weights 0.5*ul*(uavg2+uavg1)/ps and the v analogue.
+__device__ __forceinline__ double hflux(const bool up, const double f1, const double f2, const double xmsf,
+                                        const double ua1, const double ua2, const double va1, const double va2,
+                                        const double fc, const double fjm, const double fjp, const double fim,
+                                        const double fip) {
+  double fx1, fx2, fy1, fy2;
+  if (up) {
+    fx1 = (1.0 + f1) * fjm + (1.0 - f1) * fc;
+    fx2 = (1.0 + f1) * fc + (1.0 - f1) * fjp;
+    fy1 = (1.0 + f2) * fim + (1.0 - f2) * fc;
+    fy2 = (1.0 + f2) * fc + (1.0 - f2) * fip;
+  } else {
+    fx1 = fjm + fc;
+    fx2 = fc + fjp;
+    fy1 = fim + fc;
+    fy2 = fc + fip;
+  }
+  return -xmsf * (ua2 * fx2 - ua1 * fx1 + va2 * fy2 - va1 * fy1);
+}
+
+// local-extrema limiter of hadvt / hadvqv (Main/mod_advection.F90:359-386,
+// 566-596): i-direction first, then j-direction (order matters).
+__device__ __forceinline__ double extrema_limit(double fg, const double fc, const double fjm, const double fjp,
+                                                const double fim, const double fip, const double scale,
+                                                const double thr) {
+  if (fabs(fip + fim - 2.0 * fc) / scale > thr) {
+    if ((fc > fip) && (fc > fim)) fg = fmin(fg, 0.0);
+    else if ((fc < fip) && (fc < fim)) fg = fmax(fg, 0.0);
+  }
+  if (fabs(fjp + fjm - 2.0 * fc) / scale > thr) {
+    if ((fc > fjp) && (fc > fjm)) fg = fmin(fg, 0.0);
+    else if ((fc < fjp) && (fc < fjm)) fg = fmax(fg, 0.0);
+  }
+  return fg;
+}
+
+// number of times the 2nd-order boundary-ring form of diffu_* applies to a
+// point (corner points of the ring receive it twice,
+// Main/mod_diffusion.F90:689-725), for cross (dot=false) or dot points.
+__device__ __forceinline__ int ring_count(const Geom& g, int j, int i, bool dot) {
+  const int j1 = dot ? g.jdi1 : g.jci1, j2 = dot ? g.jdi2 : g.jci2;
+  const int i1 = dot ? g.idi1 : g.ici1, i2 = dot ? g.idi2 : g.ici2;
+  int n = 0;
+  if (g.has_bdyleft && j == j1) n++;
+  if (g.has_bdyright && j == j2) n++;
+  if (g.has_bdybottom && i == i1) n++;
+  if (g.has_bdytop && i == i2) n++;
+  return n;
+}
+
+__device__ __forceinline__ bool diff_interior(const Geom& g, int j, int i, bool dot) {
+  if (dot) return j >= g.jdii1 && j <= g.jdii2 && i >= g.idii1 && i <= g.idii2;
+  return j >= g.jcii1 && j <= g.jcii2 && i >= g.icii1 && i <= g.icii2;
+}
+
+}  // namespace rcm

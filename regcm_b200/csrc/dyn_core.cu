@@ -1,0 +1,1064 @@
+// libregcm_dyn.so — host side of the B200 dyn-core: handle, static setup,
+// time stepping driver and the C ABI of include/regcm_dyn.h.
+//
+// There is NO CPU fallback in this library: every entry point that computes
+// runs CUDA kernels and fails with RCM_ERR_CUDA when no device is usable.
+// The static setup (reference atmosphere, map-factor products, relaxation
+// weights, Rayleigh coefficients) is evaluated once on the host in double
+// precision exactly as `param` does (Main/mod_params.F90:1960-2074,2613-2741)
+// and uploaded; everything that runs per step is on the device.
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/regcm_dyn.h"
+#include "consts.h"
+#include "dyn_types.h"
+#include "halo.h"
+#include "launch.h"
+
+using namespace rcm;
+
+// kernel launchers (k_*.cu)
+void launch_prep(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_uv(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_tq(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_ppw(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_snd_init(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_snd_uv(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_snd_wfwd_only(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_snd_wback_only(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_snd_final(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_couple(const Geom&, double*, const double*, int, int, int, int, int, cudaStream_t);
+void launch_timeint(const Geom&, const double*, const double*, double*, double, int, int, int, int, int, cudaStream_t);
+void launch_bdyval(const Geom&, const Fields&, const double*, const double*, const double*, const int2*, int,
+                   const int2*, int, double, int, int, cudaStream_t);
+
+#define CUDA_OK(call)                                                                   \
+  do {                                                                                  \
+    cudaError_t e_ = (call);                                                            \
+    if (e_ != cudaSuccess) {                                                            \
+      h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                      \
+      return RCM_ERR_CUDA;                                                              \
+    }                                                                                   \
+  } while (0)
+
+struct rcm_dyn {
+  rcm_cfg cfg{};
+  Geom g{};
+  Fields f{};
+  StepScalars s{};
+  std::string err;
+  int device = 0;
+  bool inited = false;
+  // geometry helpers
+  int nj_pad = 0, ni_pad = 0;
+  long long off2 = 0, off3 = 0;  // origin shifts (elements)
+  long long eoff = 0; int eni = 0;
+  // host statics in the padded geometry (origin-shifted accessors below)
+  std::vector<double> h_ht, h_msfx, h_msfd, h_coriol, h_xlat, h_xlon, h_dlat, h_sigma;
+  // device memory
+  std::vector<void*> allocs;
+  double* b1[6] = {nullptr};   // boundary record b1 per bdy field (u v t qv pp w)
+  double* nx[6] = {nullptr};   // staged next record (decoupled)
+  double* psdot_bdy = nullptr; // bdycon psdot = atm0%psdot*1e-3 (Main/mod_bdycod.F90:425-431)
+  double* xpsb = nullptr;      // xpsb%b0 = atm0%ps*1e-3
+  int2 *rim_d = nullptr, *rim_c = nullptr;
+  int nrim_d = 0, nrim_c = 0;
+  std::vector<double> stage;   // host staging, one 3-D field
+  // time bookkeeping (rcmtimer, alarms: Main/mpplib/mod_timer.F90)
+  int64_t lcount = 0, model_time = 0;
+  int64_t day_lastact = 0, day_now = 0, bdy_lastact = 0, bdy_now = 0;
+  double dtsec = 0, dt = 0, dt2 = 0, xbctime = 0, dtbdys = 0, rdtbdy = 0;
+  bool have_next = false;
+  // sound
+  double dtsmax = 0, cs = 0, rnpts = 0, xmsf_mean = 0;
+  double fi[13], fj[13], fk[7], fl[7];
+  int last_istep = 0;
+  double max_cfl = 0;
+  int64_t neg_q = 0;
+  int nan_flag = 0;
+  // stream / timing
+  cudaStream_t st = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int64_t launches = 0;
+  double last_ms = 0;
+  Halo halo;
+};
+
+// host accessors in the padded geometry
+#define H2(v, j, i) (v)[h->off2 + (long long)(j) + (long long)(i) * h->g.si]
+#define H3(v, j, i, k) (v)[h->off3 + (long long)(j) + (long long)(i) * h->g.si + (long long)(k) * h->g.sk]
+
+static int fail(rcm_dyn* h, int code, const std::string& msg) {
+  if (h) h->err = msg;
+  return code;
+}
+
+// ---------------------------------------------------------------------------
+extern "C" int rcm_dyn_default_cfg(rcm_cfg* c, int idynamic) {
+  if (!c) return RCM_ERR_ARG;
+  std::memset(c, 0, sizeof(*c));
+  c->struct_size = (int32_t)sizeof(rcm_cfg);
+  c->nqx = 2;
+  c->idynamic = idynamic;
+  c->iboudy = 5; c->idiffu = 1; c->ipptls = 1;
+  c->ifupr = 1; c->ifrayd = 1; c->rayndamp = 5;
+  c->nspgx = c->nspgd = 12;
+  c->ibdyfrq = 6;
+  c->upstream_mode = c->stability_enhance = 1;
+  c->nproc = 1; c->myid = 0; c->cpus_j = c->cpus_i = 0; c->device = -1;
+  c->ptop = 5.0;
+  if (idynamic == 2) { c->gnu1 = c->gnu2 = 0.1; c->diffu_hgtf = 0; }
+  else { c->gnu1 = c->gnu2 = 0.0625; c->diffu_hgtf = 1; }
+  c->ckh = c->adyndif = 1.0;
+  c->uoffc = 0.25; c->t_extrema = 5.0; c->q_rel_extrema = 0.20;
+  c->nhbet = 0.4; c->nhxkd = 0.1; c->rayalpha0 = 0.0003; c->rayhd = 10000.0;
+  c->high_nudge = 3.0; c->medium_nudge = 2.0; c->low_nudge = 1.0;
+  c->bdy_nm = c->bdy_dm = -1.0;
+  c->base_state_pressure = 101325.0; c->logp_lrate = 47.70; c->base_state_ts0 = 288.15;
+  return RCM_OK;
+}
+
+// ---------------------------------------------------------------------------
+// decomposition: set_nproc rules (Main/mpplib/mod_mppparam.F90:1152-1172,1302-1360)
+static void choose_layout(int nproc, int jx, int iy, int& cj, int& ci) {
+  if (nproc == 1) { cj = ci = 1; return; }
+  if (nproc == 2) { cj = 2; ci = 1; return; }  // :1152-1160 (split jx)
+  cj = (int)std::lround(std::sqrt((double)nproc));
+  ci = nproc / cj;
+  if (jx > (int)(1.5 * iy)) { cj = cj - 1; do { cj = cj + 1; if (nproc % cj == 0) break; } while (cj < nproc); ci = nproc / cj; }
+  else if (iy > (int)(1.5 * jx)) { ci = ci - 1; do { ci = ci + 1; if (nproc % ci == 0) break; } while (ci < nproc); cj = nproc / ci; }
+  else { while (cj * ci != nproc && cj > 1) { cj--; ci = nproc / cj; } if (cj * ci != nproc) { cj = nproc; ci = 1; } if (cj > ci && jx <= iy) std::swap(cj, ci); }
+}
+
+static void split_range(int n, int parts, int coord, int& lo, int& hi) {
+  // remainders go to the low-coordinate ranks (:1302-1328)
+  const int base = n / parts, rem = n % parts;
+  lo = 1 + coord * base + std::min(coord, rem);
+  hi = lo + base - 1 + (coord < rem ? 1 : 0);
+}
+
+static double* dev_alloc3(rcm_dyn* h, int nk, bool shifted = true) {
+  double* p = nullptr;
+  const size_t n = (size_t)h->g.sk * (size_t)nk;
+  if (cudaMalloc(&p, n * sizeof(double)) != cudaSuccess) return nullptr;
+  cudaMemset(p, 0, n * sizeof(double));
+  h->allocs.push_back(p);
+  return shifted ? p + h->off3 : p;
+}
+static double* dev_alloc2(rcm_dyn* h) {
+  double* p = nullptr;
+  const size_t n = (size_t)h->g.sk;
+  if (cudaMalloc(&p, n * sizeof(double)) != cudaSuccess) return nullptr;
+  cudaMemset(p, 0, n * sizeof(double));
+  h->allocs.push_back(p);
+  return p + h->off2;
+}
+template <class T>
+static T* dev_alloc_raw(rcm_dyn* h, size_t n) {
+  T* p = nullptr;
+  if (cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)) != cudaSuccess) return nullptr;
+  cudaMemset(p, 0, std::max<size_t>(n, 1) * sizeof(T));
+  h->allocs.push_back(p);
+  return p;
+}
+
+extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
+  if (!cfg || !out) return RCM_ERR_ARG;
+  *out = nullptr;
+  rcm_dyn* h = new rcm_dyn();
+  auto bail = [&](int code, const char* msg) { std::fprintf(stderr, "rcm_dyn_create: %s\n", msg); delete h; return code; };
+  h->cfg = *cfg;
+  const rcm_cfg& c = h->cfg;
+  if (c.struct_size != (int)sizeof(rcm_cfg)) return bail(RCM_ERR_ARG, "rcm_cfg size mismatch");
+  if (c.idynamic != 2) return bail(RCM_ERR_ARG, "only idynamic=2 (non-hydrostatic core) is implemented");
+  if (c.idiffu != 1) return bail(RCM_ERR_ARG, "only idiffu=1 is implemented");
+  if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 5)) return bail(RCM_ERR_ARG, "iboudy must be 0, 1 or 5");
+  if (c.nqx != 2) return bail(RCM_ERR_ARG, "nqx must be 2 (qv,qc)");
+  if (c.jx < 2 * c.nspgx || c.iy < 2 * c.nspgx || c.kz < 3) return bail(RCM_ERR_ARG, "domain too small for the relaxation zone");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return bail(RCM_ERR_CUDA, "no CUDA device (this library has no CPU fallback)");
+  h->device = (c.device >= 0) ? c.device : (c.myid % ndev);
+  if (cudaSetDevice(h->device) != cudaSuccess) return bail(RCM_ERR_CUDA, "cudaSetDevice failed");
+
+  Geom& g = h->g;
+  g.jx = c.jx; g.iy = c.iy; g.kz = c.kz; g.kzp1 = c.kz + 1;
+  int cj = c.cpus_j, ci = c.cpus_i;
+  if (cj <= 0 || ci <= 0) choose_layout(c.nproc, c.jx, c.iy, cj, ci);
+  if (cj * ci != c.nproc) return bail(RCM_ERR_ARG, "cpus_j*cpus_i != nproc");
+  const int pj = c.myid % cj, pi = c.myid / cj;
+  split_range(c.jx, cj, pj, g.jde1, g.jde2);
+  split_range(c.iy, ci, pi, g.ide1, g.ide2);
+  g.has_bdyleft = (pj == 0); g.has_bdyright = (pj == cj - 1);
+  g.has_bdybottom = (pi == 0); g.has_bdytop = (pi == ci - 1);
+  g.gl = g.has_bdyleft ? 0 : 1; g.gr = g.has_bdyright ? 0 : 1;
+  g.gb = g.has_bdybottom ? 0 : 1; g.gt = g.has_bdytop ? 0 : 1;
+  // Main/mod_atm_interface.F90:203-353
+  g.jdi1 = g.jde1 + (g.has_bdyleft ? 1 : 0); g.jdii1 = g.jde1 + (g.has_bdyleft ? 2 : 0);
+  g.jdi2 = g.jde2 - (g.has_bdyright ? 1 : 0); g.jdii2 = g.jde2 - (g.has_bdyright ? 2 : 0);
+  g.idi1 = g.ide1 + (g.has_bdybottom ? 1 : 0); g.idii1 = g.ide1 + (g.has_bdybottom ? 2 : 0);
+  g.idi2 = g.ide2 - (g.has_bdytop ? 1 : 0); g.idii2 = g.ide2 - (g.has_bdytop ? 2 : 0);
+  g.jce1 = g.jde1; g.jce2 = g.has_bdyright ? g.jde2 - 1 : g.jde2;
+  g.ice1 = g.ide1; g.ice2 = g.has_bdytop ? g.ide2 - 1 : g.ide2;
+  g.jci1 = g.jce1 + (g.has_bdyleft ? 1 : 0); g.jcii1 = g.jce1 + (g.has_bdyleft ? 2 : 0);
+  g.jci2 = g.jce2 - (g.has_bdyright ? 1 : 0); g.jcii2 = g.jce2 - (g.has_bdyright ? 2 : 0);
+  g.ici1 = g.ice1 + (g.has_bdybottom ? 1 : 0); g.icii1 = g.ice1 + (g.has_bdybottom ? 2 : 0);
+  g.ici2 = g.ice2 - (g.has_bdytop ? 1 : 0); g.icii2 = g.ice2 - (g.has_bdytop ? 2 : 0);
+  g.jcross1 = 1; g.jcross2 = c.jx - 1; g.icross1 = 1; g.icross2 = c.iy - 1;
+
+  const int nj = g.jde2 - g.jde1 + 1, ni = g.ide2 - g.ide1 + 1;
+  h->nj_pad = ((nj + 2 * RCM_HALO + 15) / 16) * 16;
+  h->ni_pad = ni + 2 * RCM_HALO;
+  g.si = h->nj_pad;
+  g.sk = (long long)h->nj_pad * h->ni_pad;
+  h->off2 = -((long long)(g.jde1 - RCM_HALO) + (long long)g.si * (g.ide1 - RCM_HALO));
+  h->off3 = h->off2 - g.sk;
+  g.esi = ((nj + 2 * RCM_EHALO + 15) / 16) * 16;
+  h->eni = ni + 2 * RCM_EHALO;
+  h->eoff = -((long long)(g.jde1 - RCM_EHALO) + (long long)g.esi * (g.ide1 - RCM_EHALO));
+
+  h->dtsec = c.dt; h->dt = c.dt; h->dt2 = 2.0 * c.dt;
+  h->dtbdys = (double)c.ibdyfrq * 3600.0;
+  h->rdtbdy = 1.0 / h->dtbdys;
+
+  // ---- device memory ----
+  Fields& f = h->f;
+  const int kzp1 = g.kzp1;
+  bool ok = true;
+  auto A3 = [&](double*& p) { p = dev_alloc3(h, kzp1); ok = ok && p; };
+  auto A2 = [&](double*& p) { p = dev_alloc2(h); ok = ok && p; };
+  for (double** p : {&f.au, &f.av, &f.at, &f.aqv, &f.aqc, &f.app, &f.aw, &f.bu, &f.bv, &f.bt, &f.bqv, &f.bqc, &f.bpp,
+                     &f.bw, &f.nat, &f.naqv, &f.naqc, &f.nbt, &f.nbqv, &f.nbqc, &f.xub0, &f.xubt, &f.xvb0, &f.xvbt,
+                     &f.xtb0, &f.xtbt, &f.xqb0, &f.xqbt, &f.xpb0, &f.xpbt, &f.xwb0, &f.xwbt, &f.pr0, &f.t0, &f.rho0,
+                     &f.rhof0, &f.pr1, &f.rho1, &f.th, &f.qdot, &f.cr, &f.xkc, &f.uten, &f.vten, &f.ppten, &f.wten,
+                     &f.cu, &f.cv, &f.cpp, &f.cppd, &f.cw, &f.ct, &f.se, &f.sf})
+    A3(*p);
+  for (int q = 0; q < 6; ++q) { A3(h->b1[q]); A3(h->nx[q]); }
+  for (double** p : {&f.psa, &f.rpsa, &f.psdota, &f.rpsda, &f.msfx, &f.msfd, &f.xmsf, &f.dmsf, &f.coriol, &f.ef, &f.ddx,
+                     &f.ddy, &f.dmdx, &f.dmdy, &f.ex, &f.crx, &f.cry, &f.dpsdxm, &f.dpsdym, &f.ht, &f.ps0, &f.hgfact,
+                     &f.astore, &f.wpval, &h->psdot_bdy, &h->xpsb})
+    A2(*p);
+  f.psb = f.psa; f.rpsb = f.rpsa; f.psdotb = f.psdota;  // idynamic = 2: p* is the constant reference p*
+  {
+    int* z = dev_alloc_raw<int>(h, (size_t)g.sk); ok = ok && z; f.zone_c = z ? z + h->off2 : nullptr;
+    z = dev_alloc_raw<int>(h, (size_t)g.sk); ok = ok && z; f.zone_d = z ? z + h->off2 : nullptr;
+  }
+  const int rl = std::max(1, std::min(kzp1, c.rayndamp));
+  f.tau_c = dev_alloc3(h, rl); f.tau_d = dev_alloc3(h, rl); f.tau_f = dev_alloc3(h, rl);
+  ok = ok && f.tau_c && f.tau_d && f.tau_f;
+  const size_t nv = (size_t)g.kz + 3;
+  for (double** p : {&f.sigma, &f.dsigma, &f.twt1, &f.twt2, &f.qcon, &f.xds, &f.dds}) { *p = dev_alloc_raw<double>(h, nv); ok = ok && *p; }
+  f.hefc = dev_alloc_raw<double>(h, (size_t)c.nspgx * g.kz + 1); f.hegc = dev_alloc_raw<double>(h, (size_t)c.nspgx * g.kz + 1);
+  f.hefd = dev_alloc_raw<double>(h, (size_t)c.nspgd * g.kz + 1); f.hegd = dev_alloc_raw<double>(h, (size_t)c.nspgd * g.kz + 1);
+  {
+    double* e = dev_alloc_raw<double>(h, (size_t)g.esi * h->eni); ok = ok && e; f.estore = e ? e + h->eoff : nullptr;
+  }
+  f.tmask = dev_alloc_raw<double>(h, 169);
+  f.cflbits = dev_alloc_raw<unsigned long long>(h, 1);
+  f.negq = dev_alloc_raw<unsigned long long>(h, 1);
+  f.nanflag = dev_alloc_raw<int>(h, 1);
+  ok = ok && f.hefc && f.hegc && f.hefd && f.hegd && f.tmask && f.cflbits && f.negq && f.nanflag;
+  if (!ok) {
+    for (void* p : h->allocs) cudaFree(p);
+    return bail(RCM_ERR_CUDA, "device memory allocation failed");
+  }
+  const size_t n2 = (size_t)g.sk;
+  for (auto* v : {&h->h_ht, &h->h_msfx, &h->h_msfd, &h->h_coriol, &h->h_xlat, &h->h_xlon, &h->h_dlat}) v->assign(n2, 0.0);
+  for (auto* v : {&h->h_msfx, &h->h_msfd}) v->assign(n2, 1.0);
+  h->h_sigma.assign(nv, 0.0);
+  h->stage.assign((size_t)g.sk * kzp1, 0.0);
+  cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking);
+  cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
+  h->halo.init(g, c.nproc, c.myid, cj, ci);
+  *out = h;
+  return RCM_OK;
+}
+
+// ---------------------------------------------------------------------------
+// window copies between a caller array (Fortran bounds lb/ub) and the padded
+// geometry
+static void win_in(rcm_dyn* h, std::vector<double>& dst, long long off, int nk, const double* a, const int32_t* lb,
+                   const int32_t* ub, int k0 /* k of plane 0 in dst */) {
+  const Geom& g = h->g;
+  const int jlo = std::max(lb[0], g.jde1 - RCM_HALO), jhi = std::min(ub[0], g.jde2 + RCM_HALO);
+  const int ilo = std::max(lb[1], g.ide1 - RCM_HALO), ihi = std::min(ub[1], g.ide2 + RCM_HALO);
+  const long long n1 = ub[0] - lb[0] + 1, n2 = ub[1] - lb[1] + 1;
+  for (int k = std::max(lb[2], k0); k <= std::min(ub[2], k0 + nk - 1); ++k)
+    for (int i = ilo; i <= ihi; ++i)
+      for (int j = jlo; j <= jhi; ++j)
+        dst[off + j + (long long)i * g.si + (long long)(k - k0) * g.sk] =
+            a[(j - lb[0]) + n1 * ((i - lb[1]) + n2 * (long long)(k - lb[2]))];
+}
+
+extern "C" int rcm_dyn_set_static(rcm_dyn* h, int id, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a || !lb || !ub) return RCM_ERR_ARG;
+  std::vector<double>* dst = nullptr;
+  switch (id) {
+    case RCM_S_HT: dst = &h->h_ht; break;
+    case RCM_S_MSFX: dst = &h->h_msfx; break;
+    case RCM_S_MSFD: dst = &h->h_msfd; break;
+    case RCM_S_CORIOL: dst = &h->h_coriol; break;
+    case RCM_S_XLAT: dst = &h->h_xlat; break;
+    case RCM_S_XLON: dst = &h->h_xlon; break;
+    case RCM_S_DLAT: dst = &h->h_dlat; break;
+    case RCM_S_SIGMA:
+      for (int k = lb[2]; k <= ub[2] && k <= h->g.kzp1; ++k) if (k >= 1) h->h_sigma[k] = a[k - lb[2]];
+      return RCM_OK;
+    default: return fail(h, RCM_ERR_ARG, "bad static id");
+  }
+  int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
+  win_in(h, *dst, h->off2, 1, a, l3, u3, 1);
+  return RCM_OK;
+}
+
+static int bdy_index(int field) {
+  switch (field) {
+    case RCM_F_U: return 0; case RCM_F_V: return 1; case RCM_F_T: return 2;
+    case RCM_F_QV: return 3; case RCM_F_PP: return 4; case RCM_F_W: return 5;
+  }
+  return -1;
+}
+static double** bdy_b0(rcm_dyn* h, int q) {
+  Fields& f = h->f;
+  double** t[6] = {&f.xub0, &f.xvb0, &f.xtb0, &f.xqb0, &f.xpb0, &f.xwb0};
+  return t[q];
+}
+static double** bdy_bt(rcm_dyn* h, int q) {
+  Fields& f = h->f;
+  double** t[6] = {&f.xubt, &f.xvbt, &f.xtbt, &f.xqbt, &f.xpbt, &f.xwbt};
+  return t[q];
+}
+
+static int upload3(rcm_dyn* h, double* dev_shifted, const double* a, const int32_t* lb, const int32_t* ub, int nk) {
+  std::fill(h->stage.begin(), h->stage.end(), 0.0);
+  // stage plane 0 is k = 1: off = off2
+  win_in(h, h->stage, h->off2, nk, a, lb, ub, 1);
+  CUDA_OK(cudaMemcpy(dev_shifted - h->off3, h->stage.data(), (size_t)h->g.sk * nk * sizeof(double), cudaMemcpyHostToDevice));
+  return RCM_OK;
+}
+
+extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a) return RCM_ERR_ARG;
+  const int q = bdy_index(field);
+  if (q < 0) return fail(h, RCM_ERR_ARG, "no boundary data for this field");
+  cudaSetDevice(h->device);
+  double* dst = nullptr;
+  if (slot == RCM_BDY_B0) dst = *bdy_b0(h, q);
+  else if (slot == RCM_BDY_B1) dst = h->b1[q];
+  else if (slot == RCM_BDY_NEXT) { dst = h->nx[q]; h->have_next = true; }
+  else return fail(h, RCM_ERR_ARG, "bad slot");
+  const int nk = (field == RCM_F_W) ? h->g.kzp1 : h->g.kz;
+  return upload3(h, dst, a, lb, ub, nk);
+}
+
+// ---------------------------------------------------------------------------
+// helpers for the static setup
+static int up2(rcm_dyn* h, double* dev_shifted, const std::vector<double>& v) {
+  CUDA_OK(cudaMemcpy(dev_shifted - h->off2, v.data(), (size_t)h->g.sk * sizeof(double), cudaMemcpyHostToDevice));
+  return RCM_OK;
+}
+static int up3(rcm_dyn* h, double* dev_shifted, const std::vector<double>& v, int nk) {
+  CUDA_OK(cudaMemcpy(dev_shifted - h->off3, v.data(), (size_t)h->g.sk * nk * sizeof(double), cudaMemcpyHostToDevice));
+  return RCM_OK;
+}
+static int up1(rcm_dyn* h, double* dev, const std::vector<double>& v) {
+  CUDA_OK(cudaMemcpy(dev, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice));
+  return RCM_OK;
+}
+
+// relaxation-zone distance index (setup_boundaries, Main/mod_atm_interface.F90:383-542)
+static void build_zone(rcm_dyn* h, bool dot, std::vector<int>& z) {
+  const Geom& g = h->g;
+  const rcm_cfg& c = h->cfg;
+  z.assign((size_t)g.sk, 0);
+  const int jx = g.jx, iy = g.iy;
+  const int icx = dot ? 0 : 1, icy = dot ? 0 : 1;
+  const int nsp = dot ? c.nspgd : c.nspgx;
+  const int igbb1 = 2, igbb2 = nsp - 1, jgbl1 = 2, jgbl2 = nsp - 1;
+  const int igbt1 = iy - icy - nsp + 2, igbt2 = iy - icy - 1;
+  const int jgbr1 = jx - icx - nsp + 2, jgbr2 = jx - icx - 1;
+  // the zones are computed on this rank's dot extent (jde1:jde2,ide1:ide2)
+  for (int i = g.ide1; i <= g.ide2; ++i)
+    for (int j = g.jde1; j <= g.jde2; ++j) {
+      int v = 0;
+      if (i >= igbb1 && i <= igbb2 && j >= jgbl1 && j <= jgbr2 && !(j <= jgbl2 && i >= j) && !(j >= jgbr1 && i >= (jgbr2 - j + 2)))
+        v = i - igbb1 + 2;  // south
+      if (i >= igbt1 && i <= igbt2 && j >= jgbl1 && j <= jgbr2 && !(j <= jgbl2 && (igbt2 - i + 2) >= j) && !(j >= jgbr1 && (igbt2 - i) >= (jgbr2 - j)))
+        v = igbt2 - i + 2;  // north
+      if (i >= igbb1 && i <= igbt2 && j >= jgbl1 && j <= jgbl2 && !(i < igbb2 && j > i) && !(i > igbt1 && j > (igbt2 - i + 2)))
+        v = j - jgbl1 + 2;  // west
+      if (i >= igbb1 && i <= igbt2 && j >= jgbr1 && j <= jgbr2 && !(i < igbb2 && (jgbr2 - j + 2) > i) && !(i > igbt1 && (jgbr2 - j) > (igbt2 - i)))
+        v = jgbr2 - j + 2;  // east
+      z[h->off2 + j + (long long)i * g.si] = v;
+    }
+}
+
+static double tau_fn(const rcm_cfg& c, double z, double zmax) {  // Main/mod_bdycod.F90:5115-5123
+  if (z > zmax - c.rayhd) {
+    const double s = std::sin(halfpi * (1.0 - (zmax - z) / c.rayhd));
+    return c.rayalpha0 * (s * s);
+  }
+  return 0.0;
+}
+
+static int bdyval(rcm_dyn* h, const double* oat, const double* oaqv, const double* oaqc);
+
+// exchange call sites (the reference's are listed in SURVEY.md §2.4)
+static int exch_sound_pp(rcm_dyn* h) {  // atmc%t, atmc%pp  (Main/mod_sound.F90:265-266)
+  if (h->cfg.nproc <= 1) return RCM_OK;
+  const int kz = h->g.kz;
+  if (h->halo.exchange({{h->f.cppd, kz, 0}, {h->f.ct, kz, 0}}, 1, h->st)) return fail(h, RCM_ERR_NCCL, "halo exchange (pp) failed");
+  return RCM_OK;
+}
+static int exch_sound_uv(rcm_dyn* h) {  // atmc%u, atmc%v  (Main/mod_sound.F90:300-301)
+  if (h->cfg.nproc <= 1) return RCM_OK;
+  const int kz = h->g.kz;
+  if (h->halo.exchange({{h->f.cu, kz, 1}, {h->f.cv, kz, 1}}, 1, h->st)) return fail(h, RCM_ERR_NCCL, "halo exchange (uv) failed");
+  return RCM_OK;
+}
+static int exch_state(rcm_dyn* h) {  // atm1/atm2 all prognostics, width 2 (Main/mod_tendency.F90:866-869,1046-1083)
+  if (h->cfg.nproc <= 1) return RCM_OK;
+  const int kz = h->g.kz, kzp1 = h->g.kzp1;
+  Fields& f = h->f;
+  if (h->halo.exchange({{f.au, kz, 1}, {f.av, kz, 1}, {f.at, kz, 0}, {f.aqv, kz, 0}, {f.aqc, kz, 0}, {f.app, kz, 0}, {f.aw, kzp1, 0},
+                        {f.bu, kz, 1}, {f.bv, kz, 1}, {f.bt, kz, 0}, {f.bqv, kz, 0}, {f.bqc, kz, 0}, {f.bpp, kz, 0}, {f.bw, kzp1, 0}},
+                       RCM_HALO, h->st))
+    return fail(h, RCM_ERR_NCCL, "halo exchange (state) failed");
+  return RCM_OK;
+}
+static int exch_estore(rcm_dyn* h) {
+  if (h->cfg.nproc <= 1) return RCM_OK;
+  if (h->halo.exchange_estore(h->f, h->st)) return fail(h, RCM_ERR_NCCL, "halo exchange (estore) failed");
+  return RCM_OK;
+}
+
+extern "C" int rcm_dyn_init(rcm_dyn* h) {
+  if (!h) return RCM_ERR_ARG;
+  cudaSetDevice(h->device);
+  const Geom& g = h->g;
+  const rcm_cfg& c = h->cfg;
+  Fields& f = h->f;
+  const int kz = g.kz, kzp1 = g.kzp1;
+  const size_t n2 = (size_t)g.sk;
+  const double dx = c.ds * 1000.0, dx4 = 4.0 * dx, dx8 = 8.0 * dx, dx16 = 16.0 * dx, dxsq = dx * dx;
+  const double ptop = c.ptop;
+  // valid (inside the global domain) part of the padded tile
+  const int jdlo = std::max(1, g.jde1 - RCM_HALO), jdhi = std::min(g.jx, g.jde2 + RCM_HALO);
+  const int idlo = std::max(1, g.ide1 - RCM_HALO), idhi = std::min(g.iy, g.ide2 + RCM_HALO);
+  const int jclo = jdlo, jchi = std::min(g.jx - 1, g.jde2 + RCM_HALO);
+  const int iclo = idlo, ichi = std::min(g.iy - 1, g.ide2 + RCM_HALO);
+
+  // ---- vertical tables (Main/mod_params.F90:2005-2010,2208-2215; mod_advection.F90:77-107) ----
+  const size_t nv = (size_t)kz + 3;
+  std::vector<double> sigma = h->h_sigma, hsigma(nv, 0.0), dsigma(nv, 0.0), twt1(nv, 0.0), twt2(nv, 0.0), qcon(nv, 0.0),
+                      xds(nv, 0.0), dds(nv, 0.0);
+  for (int k = 1; k <= kz; ++k) { hsigma[k] = (sigma[k + 1] + sigma[k]) * 0.5; dsigma[k] = (sigma[k + 1] - sigma[k]); }
+  for (int k = 2; k <= kz; ++k) {
+    twt1[k] = (sigma[k] - hsigma[k - 1]) / (hsigma[k] - hsigma[k - 1]);
+    twt2[k] = 1.0 - twt1[k];
+    qcon[k] = (sigma[k] - hsigma[k]) / (hsigma[k - 1] - hsigma[k]);
+  }
+  for (int k = 1; k <= kz; ++k) xds[k] = 1.0 / dsigma[k];
+  for (int k = 2; k <= kz; ++k) dds[k] = 1.0 / (dsigma[k] + dsigma[k - 1]);
+  int rc;
+  if ((rc = up1(h, f.sigma, sigma))) return rc;
+  if ((rc = up1(h, f.dsigma, dsigma))) return rc;
+  if ((rc = up1(h, f.twt1, twt1))) return rc;
+  if ((rc = up1(h, f.twt2, twt2))) return rc;
+  if ((rc = up1(h, f.qcon, qcon))) return rc;
+  if ((rc = up1(h, f.xds, xds))) return rc;
+  if ((rc = up1(h, f.dds, dds))) return rc;
+
+  // ---- map factors (stored inverted), xmsf, dmsf, geopotential ht (:1981-2000) ----
+  std::vector<double> ht(n2, 0.0), msfx(n2, 1.0), msfd(n2, 1.0), xmsf(n2, 0.0), dmsf(n2, 0.0);
+  for (int i = idlo; i <= idhi; ++i)
+    for (int j = jdlo; j <= jdhi; ++j) {
+      H2(ht, j, i) = H2(h->h_ht, j, i) * egrav;
+      H2(msfd, j, i) = 1.0 / H2(h->h_msfd, j, i);
+      H2(msfx, j, i) = 1.0 / H2(h->h_msfx, j, i);
+      H2(dmsf, j, i) = 1.0 / (H2(msfd, j, i) * H2(msfd, j, i) * dx16);
+      H2(xmsf, j, i) = 1.0 / (H2(msfx, j, i) * H2(msfx, j, i) * dx4);
+    }
+
+  // ---- reference atmosphere (make_reference_atmosphere :2613-2694, nhbase) ----
+  std::vector<double> ps0(n2, 1.0), psdot0(n2, 1.0);
+  std::vector<double> pr0((size_t)g.sk * kzp1, 1.0), t0((size_t)g.sk * kzp1, 1.0), rho0((size_t)g.sk * kzp1, 1.0),
+      z0((size_t)g.sk * kzp1, 0.0), rhof0((size_t)g.sk * kzp1, 1.0), zf0((size_t)g.sk * kzp1, 0.0);
+  {
+    const double p0 = c.base_state_pressure, tlp = c.logp_lrate, st0 = c.base_state_ts0, ptoppa = ptop * 1000.0;
+    auto nhbase = [&](int kx, const std::vector<double>& sig, std::vector<double>& pr, std::vector<double>* tt,
+                      std::vector<double>& rho, std::vector<double>& zz) {
+      for (int i = iclo; i <= ichi; ++i)
+        for (int j = jclo; j <= jchi; ++j) {
+          const double ter = (H2(ht, j, i) * regrav);
+          const double ac = 0.5 * govr * ter / tlp;
+          const double b = st0 / tlp;
+          double alnp = -b + std::sqrt(b * b - 4.0 * ac);
+          const double ps = p0 * std::exp(alnp) - ptoppa;
+          H2(ps0, j, i) = ps;
+          for (int k = 1; k <= kx; ++k) {
+            const double p = ps * sig[k] + ptoppa;
+            const double t = std::max(st0 + tlp * std::log(p / p0), tiso);
+            H3(pr, j, i, k) = p;
+            if (tt) H3(*tt, j, i, k) = t;
+            H3(rho, j, i, k) = p / rgas / t;
+            alnp = std::log(p / (ps + ptoppa));
+            H3(zz, j, i, k) = std::max(-(0.5 * rovg * tlp * alnp * alnp + rovg * st0 * alnp), 0.0);
+          }
+        }
+    };
+    std::vector<double> prf((size_t)g.sk * kzp1, 1.0);
+    nhbase(kz, hsigma, pr0, &t0, rho0, z0);
+    nhbase(kzp1, sigma, prf, nullptr, rhof0, zf0);
+  }
+  // Note: the reference multiplies ht by regrav and back by egrav around
+  // nhbase (:2621,2634); (ht*egrav)*regrav is what `ter` holds above, and
+  // mddom%ht afterwards is ((ht*egrav)*regrav)*egrav.
+  for (int i = idlo; i <= idhi; ++i)
+    for (int j = jdlo; j <= jdhi; ++j) H2(ht, j, i) = (H2(ht, j, i) * regrav) * egrav;
+
+  // psc2psd (Main/mpplib/mod_mppparam.F90:13811-13862) on global indices
+  auto psc2psd = [&](const std::vector<double>& pc, std::vector<double>& pd) {
+    const int jx = g.jx, iy = g.iy;
+    for (int i = idlo; i <= idhi; ++i)
+      for (int j = jdlo; j <= jdhi; ++j) {
+        const bool jl = (j == 1), jr = (j == jx), ib_ = (i == 1), it_ = (i == iy);
+        // cross neighbours must lie inside the padded tile
+        if ((!jl && j - 1 < jclo) || (!ib_ && i - 1 < iclo) || (!jr && j > jchi) || (!it_ && i > ichi)) continue;
+        double v;
+        if ((jl || jr) && (ib_ || it_)) v = H2(pc, jl ? 1 : jx - 1, ib_ ? 1 : iy - 1);
+        else if (it_) v = (H2(pc, j, iy - 1) + H2(pc, j - 1, iy - 1)) * 0.5;
+        else if (ib_) v = (H2(pc, j, 1) + H2(pc, j - 1, 1)) * 0.5;
+        else if (jl) v = (H2(pc, 1, i) + H2(pc, 1, i - 1)) * 0.5;
+        else if (jr) v = (H2(pc, jx - 1, i) + H2(pc, jx - 1, i - 1)) * 0.5;
+        else v = (H2(pc, j, i) + H2(pc, j, i - 1) + H2(pc, j - 1, i) + H2(pc, j - 1, i - 1)) * 0.25;
+        H2(pd, j, i) = v;
+      }
+  };
+  psc2psd(ps0, psdot0);
+
+  std::vector<double> dpsdxm(n2, 0.0), dpsdym(n2, 0.0);
+  {
+    const int gjce1 = 1, gjce2 = g.jx - 1, gice1 = 1, gice2 = g.iy - 1;
+    for (int i = iclo; i <= ichi; ++i)
+      for (int j = jclo; j <= jchi; ++j) {
+        const double den = (H2(ps0, j, i) * dx8 * H2(msfx, j, i));
+        if (j == gjce1) H2(dpsdxm, j, i) = (H2(ps0, j + 1, i) - H2(ps0, j, i)) / den;
+        else if (j == gjce2) H2(dpsdxm, j, i) = (H2(ps0, j, i) - H2(ps0, j - 1, i)) / den;
+        else if (j - 1 >= jclo && j + 1 <= jchi) H2(dpsdxm, j, i) = (H2(ps0, j + 1, i) - H2(ps0, j - 1, i)) / den;
+        if (i == gice1) H2(dpsdym, j, i) = (H2(ps0, j, i + 1) - H2(ps0, j, i)) / den;
+        else if (i == gice2) H2(dpsdym, j, i) = (H2(ps0, j, i) - H2(ps0, j, i - 1)) / den;
+        else if (i - 1 >= iclo && i + 1 <= ichi) H2(dpsdym, j, i) = (H2(ps0, j, i + 1) - H2(ps0, j, i - 1)) / den;
+      }
+  }
+
+  // ---- full Coriolis coefficients (:2696-2741) ----
+  std::vector<double> ef(n2, 0.0), ddx(n2, 0.0), ddy(n2, 0.0), dmdx(n2, 0.0), dmdy(n2, 0.0), ex(n2, 0.0), crx(n2, 0.0), cry(n2, 0.0);
+  for (int i = std::max(2, idlo + 1); i <= std::min(g.iy - 1, idhi); ++i)
+    for (int j = std::max(2, jdlo + 1); j <= std::min(g.jx - 1, jdhi); ++j) {
+      if (j > jchi || i > ichi) continue;
+      const double dlat = H2(h->h_dlat, j, i);
+      double dlatdy = 0.5 * (H2(h->h_xlat, j - 1, i) + H2(h->h_xlat, j, i) - H2(h->h_xlat, j - 1, i - 1) - H2(h->h_xlat, j, i - 1));
+      if (std::fabs(dlatdy) < 1.0e-8) dlatdy = std::copysign(1.0e-8, dlatdy);
+      double dlondy = 0.5 * (H2(h->h_xlon, j - 1, i) + H2(h->h_xlon, j, i) - H2(h->h_xlon, j - 1, i - 1) - H2(h->h_xlon, j, i - 1));
+      if (dlondy > 180.0) dlondy = dlondy - 360.0;
+      if (dlondy < -180.0) dlondy = dlondy + 360.0;
+      double rotang = -std::atan(dlondy / dlatdy * std::cos(degrad * dlat));
+      if (dlatdy < 0.0) rotang = rotang + mathpi;
+      H2(ef, j, i) = eomeg2 * std::cos(degrad * dlat);
+      H2(ddx, j, i) = std::cos(rotang);
+      H2(ddy, j, i) = std::sin(rotang);
+      H2(dmdx, j, i) = -0.5 * (H2(msfx, j, i) + H2(msfx, j, i - 1) - H2(msfx, j - 1, i) - H2(msfx, j - 1, i - 1)) / (dx * H2(msfd, j, i) * H2(msfd, j, i));
+      H2(dmdy, j, i) = -0.5 * (H2(msfx, j, i) + H2(msfx, j - 1, i) - H2(msfx, j, i - 1) - H2(msfx, j - 1, i - 1)) / (dx * H2(msfd, j, i) * H2(msfd, j, i));
+    }
+  for (int i = std::max(2, iclo); i <= std::min(g.iy - 2, ichi); ++i)
+    for (int j = std::max(2, jclo); j <= std::min(g.jx - 2, jchi); ++j) {
+      if (j + 1 > jdhi || i + 1 > idhi) continue;
+      H2(ex, j, i) = 0.25 * (H2(ef, j, i) + H2(ef, j, i + 1) + H2(ef, j + 1, i) + H2(ef, j + 1, i + 1));
+      H2(crx, j, i) = 0.25 * (H2(ddx, j, i) + H2(ddx, j, i + 1) + H2(ddx, j + 1, i) + H2(ddx, j + 1, i + 1));
+      H2(cry, j, i) = 0.25 * (H2(ddy, j, i) + H2(ddy, j, i + 1) + H2(ddy, j + 1, i) + H2(ddy, j + 1, i + 1));
+    }
+
+  // ---- p* (constant for idynamic = 2; Main/mod_init.F90:149-155,173-178) ----
+  std::vector<double> psa(n2, 1.0), rpsa(n2, 1.0), psdota(n2, 1.0), rpsda(n2, 1.0), psdot_b(n2, 1.0), xpsb(n2, 1.0);
+  for (int i = iclo; i <= ichi; ++i)
+    for (int j = jclo; j <= jchi; ++j) { H2(psa, j, i) = H2(ps0, j, i) * 0.001; H2(rpsa, j, i) = 1.0 / H2(psa, j, i); H2(xpsb, j, i) = H2(ps0, j, i) * 0.001; }
+  psc2psd(psa, psdota);
+  for (int i = idlo; i <= idhi; ++i)
+    for (int j = jdlo; j <= jdhi; ++j) { H2(rpsda, j, i) = 1.0 / H2(psdota, j, i); H2(psdot_b, j, i) = H2(psdot0, j, i) * 0.001; }
+
+  // ---- horizontal diffusion constants (initialize_diffusion, mod_diffusion.F90:93-167) ----
+  StepScalars& s = h->s;
+  s.xkhmax = dxsq / (64.0 * h->dtsec);
+  s.dydc = c.adyndif * vonkar * vonkar * dx * 0.25;
+  const double xkhz = c.ckh * dx;
+  s.xkhmax = 2.0 * s.xkhmax;
+  std::vector<double> hgfact(n2, xkhz);
+  if (c.diffu_hgtf == 1)
+    for (int i = std::max(2, iclo + 1); i <= std::min(g.iy - 2, ichi - 1); ++i)
+      for (int j = std::max(2, jclo + 1); j <= std::min(g.jx - 2, jchi - 1); ++j) {
+        const double hg1 = std::fabs((H2(ht, j, i) - H2(ht, j, i - 1)) / dx), hg2 = std::fabs((H2(ht, j, i) - H2(ht, j, i + 1)) / dx);
+        const double hg3 = std::fabs((H2(ht, j, i) - H2(ht, j - 1, i)) / dx), hg4 = std::fabs((H2(ht, j, i) - H2(ht, j + 1, i)) / dx);
+        const double hgmax = std::max(std::max(hg1, hg2), std::max(hg3, hg4)) * regrav * 1.0e3;
+        H2(hgfact, j, i) = xkhz / (1.0 + hgmax * hgmax);
+      }
+
+  // ---- relaxation weights (setup_bdycon, Main/mod_bdycod.F90:183-278) ----
+  {
+    double fnudge = 0.0, gnudge = 0.0;
+    if (c.iboudy == 1 || c.iboudy == 5) {
+      fnudge = (c.bdy_nm > 0.0) ? c.bdy_nm : 0.1 / h->dt;
+      gnudge = (c.bdy_dm > 0.0) ? c.bdy_dm : 1.0 / (h->dt * 50.0);
+    }
+    auto table = [&](int nsp, std::vector<double>& F, std::vector<double>& G) {
+      F.assign((size_t)nsp * kz + 1, 0.0); G.assign((size_t)nsp * kz + 1, 0.0);
+      for (int k = 1; k <= kz; ++k) {
+        double an = (hsigma[k] < 0.4) ? c.high_nudge : ((hsigma[k] < 0.8) ? c.medium_nudge : c.low_nudge);
+        for (int n = 2; n <= nsp - 1; ++n) {
+          double xfun;
+          if (c.iboudy == 5) xfun = std::exp(-((double)(n - 2) / an));
+          else xfun = (double)(nsp - n) / (double)(nsp - 2);
+          F[n + (size_t)nsp * (k - 1)] = fnudge * xfun;
+          G[n + (size_t)nsp * (k - 1)] = gnudge * xfun;
+        }
+      }
+    };
+    std::vector<double> F, G;
+    table(c.nspgx, F, G);
+    if ((rc = up1(h, f.hefc, F))) return rc;
+    if ((rc = up1(h, f.hegc, G))) return rc;
+    table(c.nspgd, F, G);
+    if ((rc = up1(h, f.hefd, F))) return rc;
+    if ((rc = up1(h, f.hegd, G))) return rc;
+  }
+  {
+    std::vector<int> z;
+    build_zone(h, false, z);
+    CUDA_OK(cudaMemcpy(f.zone_c - h->off2, z.data(), n2 * sizeof(int), cudaMemcpyHostToDevice));
+    build_zone(h, true, z);
+    CUDA_OK(cudaMemcpy(f.zone_d - h->off2, z.data(), n2 * sizeof(int), cudaMemcpyHostToDevice));
+  }
+
+  // ---- Rayleigh coefficients tau(z) on the static reference heights ----
+  {
+    const int rl = std::max(1, std::min(kzp1, c.rayndamp));
+    std::vector<double> tc((size_t)g.sk * rl, 0.0), td((size_t)g.sk * rl, 0.0), tf((size_t)g.sk * rl, 0.0);
+    for (int k = 1; k <= rl; ++k)
+      for (int i = iclo; i <= ichi; ++i)
+        for (int j = jclo; j <= jchi; ++j) {
+          if (k <= kz) H3(tc, j, i, k) = tau_fn(c, H3(z0, j, i, k), H3(z0, j, i, 1));
+          H3(tf, j, i, k) = tau_fn(c, H3(zf0, j, i, k), H3(zf0, j, i, 1));
+          if (k <= kz && j - 1 >= jclo && i - 1 >= iclo) {
+            const double zz = 0.25 * (H3(z0, j, i, k) + H3(z0, j - 1, i, k) + H3(z0, j, i - 1, k) + H3(z0, j - 1, i - 1, k));
+            const double zm = 0.25 * (H3(z0, j, i, 1) + H3(z0, j - 1, i, 1) + H3(z0, j, i - 1, 1) + H3(z0, j - 1, i - 1, 1));
+            H3(td, j, i, k) = tau_fn(c, zz, zm);
+          }
+        }
+    if ((rc = up3(h, f.tau_c, tc, rl))) return rc;
+    if ((rc = up3(h, f.tau_d, td, rl))) return rc;
+    if ((rc = up3(h, f.tau_f, tf, rl))) return rc;
+  }
+
+  // ---- acoustic constants (init_sound, Main/mod_sound.F90:115-161) ----
+  {
+    h->rnpts = 1.0 / (double)((g.iy - 1 - 2) * (g.jx - 1 - 2));
+    for (int q = 1; q <= 5; ++q) { h->fk[q] = 2.0; h->fl[q] = 2.0; }
+    h->fk[0] = h->fl[0] = h->fk[6] = h->fl[6] = 1.0;
+    for (int q = 0; q < 13; ++q) { h->fi[q] = 1.0; h->fj[q] = 1.0; }
+    h->fi[0] = h->fj[0] = h->fi[12] = h->fj[12] = 0.5;
+    double loc = 0.0;
+    for (int i = g.ici1; i <= g.ici2; ++i)
+      for (int j = g.jci1; j <= g.jci2; ++j) loc += H2(msfx, j, i);
+    double maxt = -1e300;
+    for (int k = 1; k <= kz; ++k)
+      for (int i = g.ice1; i <= g.ice2; ++i)
+        for (int j = g.jce1; j <= g.jce2; ++j) maxt = std::max(maxt, H3(t0, j, i, k));
+    if (c.nproc > 1) {
+      if ((rc = h->halo.allreduce_host(&loc, 1, 0)) || (rc = h->halo.allreduce_host(&maxt, 1, 1)))
+        return fail(h, RCM_ERR_NCCL, "allreduce failed in init (communicator not set?)");
+    }
+    h->xmsf_mean = loc * h->rnpts;
+    s.xgamma = 1.0 / (1.0 - rovcp);
+    h->cs = std::sqrt(s.xgamma * rgas * maxt);
+    s.xkd_snd = c.nhxkd;
+    h->dtsmax = dx / h->cs / (1.0 + s.xkd_snd);
+    s.bp = (1.0 + c.nhbet) * 0.5;
+    s.bm = (1.0 - c.nhbet) * 0.5;
+    s.bpxbp = s.bp * s.bp;
+    s.bpxbm = s.bp * s.bm;
+  }
+
+  // ---- static scalars ----
+  s.dtsec = h->dtsec;
+  s.ul = c.uoffc * 0.5 * h->dt / dx;
+  s.dx = dx; s.dx2 = 2.0 * dx; s.dx4 = dx4; s.dx8 = dx8; s.dx16 = dx16; s.dxsq = dxsq; s.rdx = 1.0 / dx; s.rdxsq = 1.0 / dxsq;
+  s.gnu1 = c.gnu1; s.gnu2 = c.gnu2; s.t_extrema = c.t_extrema; s.q_rel_extrema = c.q_rel_extrema;
+  s.ptop = ptop;
+  s.upstream_mode = c.upstream_mode; s.stability_enhance = c.stability_enhance; s.ipptls = c.ipptls;
+  s.iboudy = c.iboudy; s.ifrayd = c.ifrayd; s.ifupr = c.ifupr;
+  s.kt_ray = std::min(kz, c.rayndamp); s.ktf_ray = std::min(kzp1, c.rayndamp);
+  s.nspgx = c.nspgx; s.nspgd = c.nspgd;
+
+  // ---- upload statics ----
+  if ((rc = up2(h, f.ht, ht)) || (rc = up2(h, f.msfx, msfx)) || (rc = up2(h, f.msfd, msfd)) || (rc = up2(h, f.xmsf, xmsf)) ||
+      (rc = up2(h, f.dmsf, dmsf)) || (rc = up2(h, f.coriol, h->h_coriol)) || (rc = up2(h, f.ef, ef)) || (rc = up2(h, f.ddx, ddx)) ||
+      (rc = up2(h, f.ddy, ddy)) || (rc = up2(h, f.dmdx, dmdx)) || (rc = up2(h, f.dmdy, dmdy)) || (rc = up2(h, f.ex, ex)) ||
+      (rc = up2(h, f.crx, crx)) || (rc = up2(h, f.cry, cry)) || (rc = up2(h, f.dpsdxm, dpsdxm)) || (rc = up2(h, f.dpsdym, dpsdym)) ||
+      (rc = up2(h, f.ps0, ps0)) || (rc = up2(h, f.hgfact, hgfact)) || (rc = up2(h, f.psa, psa)) || (rc = up2(h, f.rpsa, rpsa)) ||
+      (rc = up2(h, f.psdota, psdota)) || (rc = up2(h, f.rpsda, rpsda)) || (rc = up2(h, h->psdot_bdy, psdot_b)) ||
+      (rc = up2(h, h->xpsb, xpsb)))
+    return rc;
+  if ((rc = up3(h, f.pr0, pr0, kzp1)) || (rc = up3(h, f.t0, t0, kzp1)) || (rc = up3(h, f.rho0, rho0, kzp1)) ||
+      (rc = up3(h, f.rhof0, rhof0, kzp1)))
+    return rc;
+
+  // ---- rim point lists (global physical boundary rows owned by this rank) ----
+  {
+    std::vector<int2> rd, rcx;
+    // own rim points plus their extension into the ghost rows (so that no
+    // second exchange is needed after bdyval)
+    for (int i = idlo; i <= idhi; ++i)
+      for (int j = jdlo; j <= jdhi; ++j)
+        if (j == 1 || j == g.jx || i == 1 || i == g.iy) rd.push_back(make_int2(j, i));
+    for (int i = iclo; i <= ichi; ++i)
+      for (int j = jclo; j <= jchi; ++j)
+        if (j == 1 || j == g.jx - 1 || i == 1 || i == g.iy - 1) rcx.push_back(make_int2(j, i));
+    h->nrim_d = (int)rd.size(); h->nrim_c = (int)rcx.size();
+    h->rim_d = dev_alloc_raw<int2>(h, rd.size()); h->rim_c = dev_alloc_raw<int2>(h, rcx.size());
+    if (!h->rim_d || !h->rim_c) return fail(h, RCM_ERR_CUDA, "rim allocation failed");
+    if (!rd.empty()) CUDA_OK(cudaMemcpy(h->rim_d, rd.data(), rd.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    if (!rcx.empty()) CUDA_OK(cudaMemcpy(h->rim_c, rcx.data(), rcx.size() * sizeof(int2), cudaMemcpyHostToDevice));
+  }
+
+  // ---- boundary records: couple with p*, tendencies (init_bdy :393-435,522-559,625-640) ----
+  h->xbctime = 0.0;
+  for (int q = 0; q < 6; ++q) {
+    const bool dot = (q < 2);
+    const int nk = (q == 5) ? kzp1 : kz;
+    const double* cpl = dot ? h->psdot_bdy : h->xpsb;
+    const int j1 = dot ? jdlo : jclo, j2 = dot ? jdhi : jchi, i1 = dot ? idlo : iclo, i2 = dot ? idhi : ichi;
+    launch_couple(g, *bdy_b0(h, q), cpl, nk, j1, j2, i1, i2, h->st);
+    launch_couple(g, h->b1[q], cpl, nk, j1, j2, i1, i2, h->st);
+    launch_timeint(g, h->b1[q], *bdy_b0(h, q), *bdy_bt(h, q), h->rdtbdy, nk, j1, j2, i1, i2, h->st);
+    h->launches += 3;
+  }
+  // ---- initial state: atm1 = atm2 = b0 (Main/mod_init.F90:96-172) ----
+  {
+    const size_t nb = (size_t)g.sk * kzp1 * sizeof(double);
+    double* a[6] = {f.au, f.av, f.at, f.aqv, f.app, f.aw};
+    double* b[6] = {f.bu, f.bv, f.bt, f.bqv, f.bpp, f.bw};
+    for (int q = 0; q < 6; ++q) {
+      CUDA_OK(cudaMemcpyAsync(a[q] - h->off3, *bdy_b0(h, q) - h->off3, nb, cudaMemcpyDeviceToDevice, h->st));
+      CUDA_OK(cudaMemcpyAsync(b[q] - h->off3, *bdy_b0(h, q) - h->off3, nb, cudaMemcpyDeviceToDevice, h->st));
+    }
+    CUDA_OK(cudaMemsetAsync(f.aqc - h->off3, 0, nb, h->st));
+    CUDA_OK(cudaMemsetAsync(f.bqc - h->off3, 0, nb, h->st));
+    double one[169]; for (double& x : one) x = 0.0;
+    CUDA_OK(cudaMemcpyAsync(f.tmask, one, sizeof(one), cudaMemcpyHostToDevice, h->st));
+  }
+  h->lcount = 0; h->model_time = 0;
+  h->day_lastact = 0; h->day_now = 0; h->bdy_lastact = 0; h->bdy_now = 0;
+  h->inited = true;
+  // first bdyval (Main/mod_regcm_interface.F90:146)
+  if ((rc = bdyval(h, f.at, f.aqv, f.aqc))) return rc;
+  CUDA_OK(cudaStreamSynchronize(h->st));
+  return RCM_OK;
+}
+
+// ---------------------------------------------------------------------------
+static int bdyval(rcm_dyn* h, const double* oat, const double* oaqv, const double* oaqc) {
+  const double xt = h->xbctime + h->dt;
+  launch_bdyval(h->g, h->f, oat, oaqv, oaqc, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, xt, h->lcount > 0 ? 1 : 0,
+                h->cfg.iboudy, h->st);
+  h->launches += 2;
+  h->xbctime = h->xbctime + h->dtsec;
+  return RCM_OK;
+}
+
+// state part of bdyin (Main/mod_bdycod.F90:669-690,772-831)
+static int bdyin(rcm_dyn* h) {
+  const Geom& g = h->g;
+  const int kz = g.kz, kzp1 = g.kzp1;
+  const int jdlo = std::max(1, g.jde1 - RCM_HALO), jdhi = std::min(g.jx, g.jde2 + RCM_HALO);
+  const int idlo = std::max(1, g.ide1 - RCM_HALO), idhi = std::min(g.iy, g.ide2 + RCM_HALO);
+  const int jclo = jdlo, jchi = std::min(g.jx - 1, g.jde2 + RCM_HALO);
+  const int iclo = idlo, ichi = std::min(g.iy - 1, g.ide2 + RCM_HALO);
+  h->xbctime = 0.0;
+  for (int q = 0; q < 6; ++q) {
+    // b0 <- b1 (pointer swap), b1 <- staged record
+    std::swap(*bdy_b0(h, q), h->b1[q]);
+    std::swap(h->b1[q], h->nx[q]);
+    const bool dot = (q < 2);
+    const int nk = (q == 5) ? kzp1 : kz;
+    const double* cpl = dot ? h->psdot_bdy : h->xpsb;
+    const int j1 = dot ? jdlo : jclo, j2 = dot ? jdhi : jchi, i1 = dot ? idlo : iclo, i2 = dot ? idhi : ichi;
+    launch_couple(g, h->b1[q], cpl, nk, j1, j2, i1, i2, h->st);
+    launch_timeint(g, h->b1[q], *bdy_b0(h, q), *bdy_bt(h, q), h->rdtbdy, nk, j1, j2, i1, i2, h->st);
+    h->launches += 2;
+  }
+  h->have_next = false;
+  return RCM_OK;
+}
+
+// daily update of the upper-radiative-BC mask (Main/mod_sound.F90:500-547)
+static int update_tmask(rcm_dyn* h) {
+  const Geom& g = h->g;
+  Fields& f = h->f;
+  const size_t n2 = (size_t)g.sk;
+  std::vector<double> astore(n2), rho1(n2), bt1(n2), psb(n2);
+  CUDA_OK(cudaStreamSynchronize(h->st));
+  CUDA_OK(cudaMemcpy(astore.data(), f.astore - h->off2, n2 * sizeof(double), cudaMemcpyDeviceToHost));
+  CUDA_OK(cudaMemcpy(rho1.data(), f.rho1 - h->off3, n2 * sizeof(double), cudaMemcpyDeviceToHost));  // plane k = 1
+  CUDA_OK(cudaMemcpy(bt1.data(), f.nbt - h->off3, n2 * sizeof(double), cudaMemcpyDeviceToHost));
+  CUDA_OK(cudaMemcpy(psb.data(), f.psb - h->off2, n2 * sizeof(double), cudaMemcpyDeviceToHost));
+  double atot = 0.0, rhontot = 0.0;
+  for (int i = g.ici1; i <= g.ici2; ++i)
+    for (int j = g.jci1; j <= g.jci2; ++j) {
+      atot = atot + H2(astore, j, i);
+      const double rpsb = 1.0 / H2(psb, j, i);
+      const double ensq = egrav * egrav / cpd / (H2(bt1, j, i) * rpsb);
+      rhontot = rhontot + H2(rho1, j, i) * std::sqrt(ensq);
+    }
+  if (h->cfg.nproc > 1) {
+    double v[2] = {atot, rhontot};
+    if (h->halo.allreduce_host(v, 2, 0)) return fail(h, RCM_ERR_NCCL, "allreduce failed (tmask)");
+    atot = v[0]; rhontot = v[1];
+  }
+  const double abar = atot * h->rnpts, rhon = rhontot * h->rnpts;
+  const double dxmsfb = 2.0 / h->s.dxsq / h->xmsf_mean;
+  double tmask[169];
+  for (double& x : tmask) x = 0.0;
+  for (int kk = 0; kk <= 6; ++kk) {
+    const double rkk = (double)kk;
+    for (int ll = 0; ll <= 6; ++ll) {
+      const double rll = (double)ll;
+      const double xkeff = dxmsfb * std::sin(mathpi * rkk / 12.0) * std::cos(mathpi * rll / 12.0);
+      const double xleff = dxmsfb * std::sin(mathpi * rll / 12.0) * std::cos(mathpi * rkk / 12.0);
+      const double xkleff = std::sqrt(xkeff * xkeff + xleff * xleff);
+      for (int i = -6; i <= 6; ++i) {
+        const double ri = (double)i;
+        for (int j = -6; j <= 6; ++j) {
+          const double rj = (double)j;
+          tmask[(j + 6) + 13 * (i + 6)] = tmask[(j + 6) + 13 * (i + 6)] +
+              (h->fi[i + 6] * h->fj[j + 6] * h->fk[kk] * h->fl[ll]) / 144.0 * std::cos(2.0 * mathpi * rkk * ri / 12.0) *
+                  std::cos(2.0 * mathpi * rll * rj / 12.0) * xkleff / (rhon - abar * xkleff);
+        }
+      }
+    }
+  }
+  CUDA_OK(cudaMemcpy(f.tmask, tmask, sizeof(tmask), cudaMemcpyHostToDevice));
+  return RCM_OK;
+}
+
+static void timer_advance(rcm_dyn* h) {  // Main/mpplib/mod_timer.F90:152-177,306-327
+  h->model_time += (int64_t)h->dtsec;
+  h->lcount += 1;
+  auto check = [&](int64_t& lastact, int64_t& now, int64_t actint) {
+    if (now == h->model_time) return;
+    const double t1 = (double)h->model_time, t2 = (double)(lastact + actint);
+    if (t1 >= t2) { lastact = (h->model_time / actint) * actint; now = h->model_time; }
+  };
+  check(h->day_lastact, h->day_now, 86400);
+  check(h->bdy_lastact, h->bdy_now, (int64_t)h->dtbdys);
+}
+
+// one call of `tend` (Main/mod_tendency.F90:212-616), physics off
+static int tend(rcm_dyn* h) {
+  const Geom& g = h->g;
+  Fields& f = h->f;
+  StepScalars& s = h->s;
+  int istep = std::max((int)(h->dt / h->dtsmax), 2);
+  if (h->lcount > 0) istep = std::max(4, istep);
+  s.dt = h->dt;
+  s.xt = h->xbctime + h->dt;
+  s.dts = h->dt / (double)istep;
+  s.istep = istep; s.it = 0;
+  h->last_istep = istep;
+  int rc;
+  launch_prep(g, f, s, h->st); h->launches += 2;
+  launch_uv(g, f, s, h->st); h->launches += 1;
+  launch_tq(g, f, s, h->st); h->launches += 1;
+  launch_ppw(g, f, s, h->st); h->launches += 1;
+  launch_snd_init(g, f, s, h->st); h->launches += 1;
+  if ((rc = exch_sound_pp(h))) return rc;
+  for (int it = 1; it <= istep; ++it) {
+    s.it = it;
+    launch_snd_uv(g, f, s, h->st); h->launches += 1;
+    if ((rc = exch_sound_uv(h))) return rc;
+    launch_snd_wfwd_only(g, f, s, h->st); h->launches += 1;
+    if (h->cfg.ifupr == 1) {
+      if ((rc = exch_estore(h))) return rc;
+      if (h->day_now == h->model_time && it == 1)
+        if ((rc = update_tmask(h))) return rc;
+    }
+    launch_snd_wback_only(g, f, s, h->st); h->launches += 2;
+    if (it < istep && (rc = exch_sound_pp(h))) return rc;
+  }
+  launch_snd_final(g, f, s, h->st); h->launches += 1;
+  // swap in the filtered t, qv, qc (the old buffers keep the previous rim)
+  std::swap(f.at, f.nat); std::swap(f.aqv, f.naqv); std::swap(f.aqc, f.naqc);
+  std::swap(f.bt, f.nbt); std::swap(f.bqv, f.nbqv); std::swap(f.bqc, f.nbqc);
+  timer_advance(h);
+  if (h->lcount == 2) h->dt = h->dt2;
+  return RCM_OK;
+}
+
+extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
+  if (!h) return RCM_ERR_ARG;
+  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_step before rcm_dyn_init");
+  cudaSetDevice(h->device);
+  Fields& f = h->f;
+  CUDA_OK(cudaMemsetAsync(f.cflbits, 0, sizeof(unsigned long long), h->st));
+  CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
+  CUDA_OK(cudaMemsetAsync(f.nanflag, 0, sizeof(int), h->st));
+  CUDA_OK(cudaEventRecord(h->ev0, h->st));
+  int rc = RCM_OK;
+  for (int n = 0; n < nsteps; ++n) {
+    if ((rc = tend(h))) break;
+    if (h->bdy_now == h->model_time) {
+      if (!h->have_next) { rc = fail(h, RCM_ERR_BDY, "boundary record needed but not staged"); break; }
+      if ((rc = bdyin(h))) break;
+    }
+    // after the swap in tend(): n?? hold the previous level-a buffers
+    if ((rc = exch_state(h))) break;
+    if ((rc = bdyval(h, f.nat, f.naqv, f.naqc))) break;
+  }
+  CUDA_OK(cudaEventRecord(h->ev1, h->st));
+  CUDA_OK(cudaStreamSynchronize(h->st));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+  h->last_ms = ms;
+  if (rc) return rc;
+  unsigned long long bits = 0, nq = 0; int nanf = 0;
+  CUDA_OK(cudaMemcpy(&bits, f.cflbits, sizeof(bits), cudaMemcpyDeviceToHost));
+  CUDA_OK(cudaMemcpy(&nq, f.negq, sizeof(nq), cudaMemcpyDeviceToHost));
+  CUDA_OK(cudaMemcpy(&nanf, f.nanflag, sizeof(nanf), cudaMemcpyDeviceToHost));
+  double cfl; std::memcpy(&cfl, &bits, sizeof(cfl));
+  h->max_cfl = cfl; h->neg_q = (int64_t)nq; h->nan_flag = nanf;
+  CUDA_OK(cudaGetLastError());
+  if (nanf || cfl != cfl) return fail(h, RCM_ERR_NAN, "NaN in the acoustic solver");
+  if (cfl > 1.0) {
+    char buf[128]; std::snprintf(buf, sizeof(buf), "CFL violation: max sigma-dot CFL = %g", cfl);
+    return fail(h, RCM_ERR_CFL, buf);
+  }
+  return RCM_OK;
+}
+
+// ---------------------------------------------------------------------------
+static double* state_ptr(rcm_dyn* h, int field, int level) {
+  Fields& f = h->f;
+  const bool A = (level == RCM_LEVEL_A);
+  switch (field) {
+    case RCM_F_U: return A ? f.au : f.bu;
+    case RCM_F_V: return A ? f.av : f.bv;
+    case RCM_F_T: return A ? f.at : f.bt;
+    case RCM_F_QV: return A ? f.aqv : f.bqv;
+    case RCM_F_QC: return A ? f.aqc : f.bqc;
+    case RCM_F_PP: return A ? f.app : f.bpp;
+    case RCM_F_W: return A ? f.aw : f.bw;
+  }
+  return nullptr;
+}
+
+static int download3(rcm_dyn* h, const double* dev_shifted, double* a, const int32_t* lb, const int32_t* ub, int nk) {
+  const Geom& g = h->g;
+  CUDA_OK(cudaMemcpy(h->stage.data(), dev_shifted - h->off3, (size_t)g.sk * nk * sizeof(double), cudaMemcpyDeviceToHost));
+  const int jlo = std::max(lb[0], g.jde1 - RCM_HALO), jhi = std::min(ub[0], g.jde2 + RCM_HALO);
+  const int ilo = std::max(lb[1], g.ide1 - RCM_HALO), ihi = std::min(ub[1], g.ide2 + RCM_HALO);
+  const long long n1 = ub[0] - lb[0] + 1, n2 = ub[1] - lb[1] + 1;
+  for (int k = std::max(lb[2], 1); k <= std::min(ub[2], nk); ++k)
+    for (int i = ilo; i <= ihi; ++i)
+      for (int j = jlo; j <= jhi; ++j)
+        a[(j - lb[0]) + n1 * ((i - lb[1]) + n2 * (long long)(k - lb[2]))] =
+            h->stage[h->off2 + j + (long long)i * g.si + (long long)(k - 1) * g.sk];
+  return RCM_OK;
+}
+
+extern "C" int rcm_dyn_get_state(rcm_dyn* h, int field, int level, double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a) return RCM_ERR_ARG;
+  cudaSetDevice(h->device);
+  double* p = state_ptr(h, field, level);
+  if (!p) return fail(h, RCM_ERR_ARG, "bad field");
+  return download3(h, p, a, lb, ub, h->g.kzp1);
+}
+
+extern "C" int rcm_dyn_set_state(rcm_dyn* h, int field, int level, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a) return RCM_ERR_ARG;
+  cudaSetDevice(h->device);
+  double* p = state_ptr(h, field, level);
+  if (!p) return fail(h, RCM_ERR_ARG, "bad field");
+  // read-modify-write so that a window smaller than the tile keeps the rest
+  const Geom& g = h->g;
+  const int nk = h->g.kzp1;
+  CUDA_OK(cudaMemcpy(h->stage.data(), p - h->off3, (size_t)g.sk * nk * sizeof(double), cudaMemcpyDeviceToHost));
+  win_in(h, h->stage, h->off2, nk, a, lb, ub, 1);
+  CUDA_OK(cudaMemcpy(p - h->off3, h->stage.data(), (size_t)g.sk * nk * sizeof(double), cudaMemcpyHostToDevice));
+  return RCM_OK;
+}
+
+extern "C" int rcm_dyn_get_work(rcm_dyn* h, int id, double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a) return RCM_ERR_ARG;
+  cudaSetDevice(h->device);
+  Fields& f = h->f;
+  const double* p = nullptr;
+  switch (id) {
+    case RCM_W_CR: p = f.cr; break;
+    case RCM_W_QDOT: p = f.qdot; break;
+    case RCM_W_XKC: p = f.xkc; break;
+    case RCM_W_TH: p = f.th; break;
+    case RCM_W_RHO1: p = f.rho1; break;
+    case RCM_W_PR1: p = f.pr1; break;
+    case RCM_W_UTEN: p = f.uten; break;
+    case RCM_W_VTEN: p = f.vten; break;
+    case RCM_W_PPTEN: p = f.ppten; break;
+    case RCM_W_WTEN: p = f.wten; break;
+    default: return fail(h, RCM_ERR_ARG, "bad work id");
+  }
+  return download3(h, p, a, lb, ub, h->g.kzp1);
+}
+
+extern "C" int rcm_dyn_diag(rcm_dyn* h, rcm_diag* d) {
+  if (!h || !d) return RCM_ERR_ARG;
+  std::memset(d, 0, sizeof(*d));
+  d->lcount = h->lcount; d->xbctime = h->xbctime; d->dt = h->dt;
+  d->max_cfl = h->max_cfl; d->istep = h->last_istep; d->nan_flag = h->nan_flag;
+  d->neg_q_points = h->neg_q;
+  return RCM_OK;
+}
+
+extern "C" int rcm_dyn_last_error(rcm_dyn* h, char* buf, int len) {
+  if (!buf || len <= 0) return RCM_ERR_ARG;
+  const std::string m = h ? h->err : std::string("null handle");
+  std::strncpy(buf, m.c_str(), (size_t)len - 1);
+  buf[len - 1] = 0;
+  return RCM_OK;
+}
+
+extern "C" int64_t rcm_dyn_launch_count(rcm_dyn* h) { return h ? h->launches : 0; }
+extern "C" double rcm_dyn_last_step_ms(rcm_dyn* h) { return h ? h->last_ms : 0.0; }
+
+extern "C" int rcm_dyn_comm_init(rcm_dyn* h, const void* nccl_unique_id, int id_bytes) {
+  if (!h) return RCM_ERR_ARG;
+  cudaSetDevice(h->device);
+  if (h->halo.comm_init(nccl_unique_id, id_bytes, h->err)) return RCM_ERR_NCCL;
+  return RCM_OK;
+}
+extern "C" int rcm_dyn_comm_unique_id(void* out, int out_bytes) { return Halo::unique_id(out, out_bytes); }
+
+extern "C" int rcm_dyn_destroy(rcm_dyn* h) {
+  if (!h) return RCM_OK;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  h->halo.destroy();
+  for (void* p : h->allocs) cudaFree(p);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->st) cudaStreamDestroy(h->st);
+  delete h;
+  return RCM_OK;
+}

@@ -1,0 +1,87 @@
+// Shared host/device types of the B200 dyn-core library (libregcm_dyn.so).
+//
+// Data layout in HBM.  Every 3-D field, whatever grid it lives on (dot or
+// cross, half or full levels), is stored in ONE uniform padded geometry per
+// rank: (j,i,k) with j fastest as in the reference
+// (Main/mod_atm_interface.F90:617-641), pitch `si` doubles per i-row (tile
+// width + 2*HALO, rounded up to 16 doubles = 128 B), `sk` doubles per k-plane,
+// kz+1 planes.  Ghost rows are always allocated (HALO = 2 on every side), so a
+// stencil never needs a bounds test on the array, only on the index family it
+// loops over.  Kernels receive ORIGIN-SHIFTED pointers: element (j,i,k) in the
+// reference's GLOBAL 1-based indices is p[j + si*i + sk*k].  2-D fields use
+// the same (j,i) geometry: p[j + si*i].
+#pragma once
+#include <stdint.h>
+
+#define RCM_HALO 2
+#define RCM_EHALO 6 /* estore halo for the upper radiative BC, mod_sound.F90:551-561 */
+
+struct Geom {
+  int jx, iy, kz, kzp1;
+  // index families of Main/mod_atm_interface.F90:181-381 (global indices)
+  int jde1, jde2, ide1, ide2, jdi1, jdi2, idi1, idi2, jdii1, jdii2, idii1, idii2;
+  int jce1, jce2, ice1, ice2, jci1, jci2, ici1, ici2, jcii1, jcii2, icii1, icii2;
+  int jcross1, jcross2, icross1, icross2;
+  int has_bdyleft, has_bdyright, has_bdybottom, has_bdytop;
+  // ghost ring actually usable on each side: 1 where a neighbour rank exists,
+  // 0 on a physical boundary ("ga" suffix of the reference)
+  int gl, gr, gb, gt;
+  int si;        // doubles per i-row
+  long long sk;  // doubles per k-plane
+  int esi;       // pitch of the wide-halo 2-D estore array
+};
+
+// per-step scalars
+struct StepScalars {
+  double dt;     // current leapfrog dt (dtsec, then 2*dtsec)
+  double dtsec;
+  double xt;     // xbctime + dt (boundary interpolation time)
+  double dts;    // acoustic sub-step
+  double ul;     // uoffc*0.5*dt0/dx (start-up dt, mod_advection.F90:106)
+  double dx, dx2, dx4, dx8, dx16, dxsq, rdx, rdxsq;
+  double gnu1, gnu2;
+  double t_extrema, q_rel_extrema;
+  double dydc, xkhmax;
+  double xgamma, bp, bm, bpxbp, bpxbm, xkd_snd;
+  double ptop;
+  int upstream_mode, stability_enhance, ipptls, iboudy, ifrayd, ifupr;
+  int kt_ray;   // min(kz, rayndamp)
+  int ktf_ray;  // min(kzp1, rayndamp)
+  int nspgx, nspgd;
+  int it, istep;
+};
+
+// Device pointers (origin-shifted).  Names follow the reference's structures:
+// a* = atm1 (time level a), b* = atm2 (level b), c* = atmc, n?* = the
+// double-buffered "next" a/b copies of t,qv,qc written by the fused slow
+// kernels and swapped in at the end of the step.
+struct Fields {
+  // prognostic state
+  double *au, *av, *at, *aqv, *aqc, *app, *aw;
+  double *bu, *bv, *bt, *bqv, *bqc, *bpp, *bw;
+  double *nat, *naqv, *naqc, *nbt, *nbqv, *nbqc;
+  // boundary records b0, bt (coupled) per field: u v t qv pp w
+  double *xub0, *xubt, *xvb0, *xvbt, *xtb0, *xtbt, *xqb0, *xqbt, *xpb0, *xpbt, *xwb0, *xwbt;
+  // atm0 reference atmosphere
+  double *pr0, *t0, *rho0, *rhof0;
+  // 2-D
+  double *psa, *rpsa, *psb, *rpsb, *psdota, *rpsda, *psdotb;
+  double *msfx, *msfd, *xmsf, *dmsf, *coriol, *ef, *ddx, *ddy, *dmdx, *dmdy, *ex, *crx, *cry;
+  double *dpsdxm, *dpsdym, *ht, *ps0, *hgfact;
+  int *zone_c, *zone_d;  // relaxation-zone distance index ibnd (0 = outside)
+  // 1-D vertical tables (index k = 1-based, element [k])
+  double *sigma, *dsigma, *twt1, *twt2, *qcon, *xds, *dds;
+  double *hefc, *hegc, *hefd, *hegd;  // [ib + nspg*(k-1)] ; iboudy=1: same value for all k
+  // Rayleigh coefficients tau(z) precomputed from the static heights
+  double *tau_c, *tau_d, *tau_f;  // same geometry, levels 1..rayndamp
+  // slow-part work fields
+  double *pr1, *rho1, *th, *qdot, *cr, *xkc;
+  double *uten, *vten, *ppten, *wten;
+  // acoustic work fields
+  double *cu, *cv, *cpp, *cppd, *cw, *ct, *se, *sf;
+  double *estore, *astore, *wpval, *tmask;  // estore: wide-halo 2-D; tmask 13x13
+  // diagnostics
+  unsigned long long *cflbits;  // max CFL as ordered bits
+  unsigned long long *negq;     // negative-q repairs
+  int *nanflag;
+};
