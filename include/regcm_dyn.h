@@ -208,6 +208,17 @@ int rcm_dyn_last_error(rcm_dyn* h, char* buf, int len);
 int64_t rcm_dyn_launch_count(rcm_dyn* h);
 double rcm_dyn_last_step_ms(rcm_dyn* h);
 
+/* replaces: the communicator set-up of set_nproc / mpi_cart_create
+ * (Main/mpplib/mod_mppparam.F90:1053-1401) for nproc > 1.  Rank 0 obtains a
+ * 128-byte NCCL unique id with rcm_dyn_comm_unique_id, the caller broadcasts
+ * it with whatever it already has (the Fortran driver: `call bcast`, i.e.
+ * MPI_Bcast; the Python harness: torch.distributed), then EVERY rank calls
+ * rcm_dyn_comm_init after rcm_dyn_create and before rcm_dyn_init.  Halo
+ * exchanges (the `exchange*` family, mod_mppparam.F90:209-271) then run inside
+ * rcm_dyn_init / rcm_dyn_step as NCCL send/recv on packed edge buffers. */
+int rcm_dyn_comm_unique_id(void* out128, int out_bytes);
+int rcm_dyn_comm_init(rcm_dyn* h, const void* nccl_unique_id, int id_bytes);
+
 /* replaces: memory_destroy (Main/mod_regcm_interface.F90:264). */
 int rcm_dyn_destroy(rcm_dyn* h);
 

@@ -30,6 +30,9 @@ int orc_step(void* h, int n) { return ((Oracle*)h)->step(n); }
 int orc_get_state(void* h, int field, int level, double* a, const int32_t* lb, const int32_t* ub) {
   return ((Oracle*)h)->get_state(field, level, a, lb, ub);
 }
+int orc_set_state(void* h, int field, int level, const double* a, const int32_t* lb, const int32_t* ub) {
+  return ((Oracle*)h)->set_state(field, level, a, lb, ub);
+}
 int orc_get_work(void* h, int id, double* a, const int32_t* lb, const int32_t* ub) {
   return ((Oracle*)h)->get_work(id, a, lb, ub);
 }

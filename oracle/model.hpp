@@ -144,6 +144,8 @@ struct Oracle {
   int get_state(int field, int level, double* a, const int32_t lb[3],
                 const int32_t ub[3]);
   int get_work(int id, double* a, const int32_t lb[3], const int32_t ub[3]);
+  int set_state(int field, int level, const double* a, const int32_t lb[3],
+                const int32_t ub[3]);
 
   // ---- setup pieces ----
   void setup_model_indexes();

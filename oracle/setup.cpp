@@ -277,4 +277,27 @@ int Oracle::set_bdy(int field, int slot, const double* a, const int32_t lb[3], c
   err = "bad slot"; return RCM_ERR_ARG;
 }
 
+// state import (tests only): the coupled atm1/atm2 fields
+int Oracle::set_state(int field, int level, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  const bool A = (level == RCM_LEVEL_A);
+  auto in4 = [&](A4& dst, int n) {
+    const int n1 = ub[0] - lb[0] + 1, n2 = ub[1] - lb[1] + 1;
+    for (int k = std::max(lb[2], dst.l3); k <= std::min(ub[2], dst.l3 + dst.n3 - 1); ++k)
+      for (int i = std::max(lb[1], dst.l2); i <= std::min(ub[1], dst.l2 + dst.n2 - 1); ++i)
+        for (int j = std::max(lb[0], dst.l1); j <= std::min(ub[0], dst.l1 + dst.n1 - 1); ++j)
+          dst(j, i, k, n) = a[(size_t)(j - lb[0]) + (size_t)n1 * ((size_t)(i - lb[1]) + (size_t)n2 * (size_t)(k - lb[2]))];
+    return RCM_OK;
+  };
+  switch (field) {
+    case RCM_F_U: return copy_in_3d(A ? a1_u : a2_u, a, lb, ub);
+    case RCM_F_V: return copy_in_3d(A ? a1_v : a2_v, a, lb, ub);
+    case RCM_F_T: return copy_in_3d(A ? a1_t : a2_t, a, lb, ub);
+    case RCM_F_QV: return in4(A ? a1_qx : a2_qx, iqv);
+    case RCM_F_QC: return in4(A ? a1_qx : a2_qx, iqc);
+    case RCM_F_PP: return copy_in_3d(A ? a1_pp : a2_pp, a, lb, ub);
+    case RCM_F_W: return copy_in_3d(A ? a1_w : a2_w, a, lb, ub);
+  }
+  err = "bad field"; return RCM_ERR_ARG;
+}
+
 }  // namespace orc

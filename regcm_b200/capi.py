@@ -122,7 +122,7 @@ class CoreLib:
             raise FileNotFoundError(
                 f"{path} not found: build it first (python -c 'import __graft_entry__ as g; g.build()')")
         self.path, self.prefix = path, prefix
-        self.lib = C.CDLL(path, mode=C.RTLD_GLOBAL)
+        self.lib = C.CDLL(path, mode=C.RTLD_LOCAL)
         p = prefix
         vp = C.c_void_p
         sig = {

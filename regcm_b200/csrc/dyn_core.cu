@@ -259,7 +259,7 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
     double* e = dev_alloc_raw<double>(h, (size_t)g.esi * h->eni); ok = ok && e; f.estore = e ? e + h->eoff : nullptr;
   }
   f.tmask = dev_alloc_raw<double>(h, 169);
-  f.cflbits = dev_alloc_raw<unsigned long long>(h, 1);
+  f.cflbits = dev_alloc_raw<unsigned long long>(h, 2);
   f.negq = dev_alloc_raw<unsigned long long>(h, 1);
   f.nanflag = dev_alloc_raw<int>(h, 1);
   ok = ok && f.hefc && f.hegc && f.hefd && f.hegd && f.tmask && f.cflbits && f.negq && f.nanflag;
@@ -271,7 +271,9 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   for (auto* v : {&h->h_ht, &h->h_msfx, &h->h_msfd, &h->h_coriol, &h->h_xlat, &h->h_xlon, &h->h_dlat}) v->assign(n2, 0.0);
   for (auto* v : {&h->h_msfx, &h->h_msfd}) v->assign(n2, 1.0);
   h->h_sigma.assign(nv, 0.0);
+#ifdef RCM_EMU
   h->stage.assign((size_t)g.sk * kzp1, 0.0);
+#endif
   cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking);
   cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
   h->halo.init(g, c.nproc, c.myid, cj, ci);
@@ -334,12 +336,41 @@ static double** bdy_bt(rcm_dyn* h, int q) {
   return t[q];
 }
 
+#ifndef RCM_EMU
+// strided 3-D copy between a caller window (Fortran bounds lb/ub) and the
+// padded device geometry: one cudaMemcpy3DAsync, no host staging.
+static int copy3d(rcm_dyn* h, double* dev_shifted, const double* host, const int32_t* lb, const int32_t* ub, int nk, bool to_device) {
+  const Geom& g = h->g;
+  const int jlo = std::max(lb[0], g.jde1 - RCM_HALO), jhi = std::min(ub[0], g.jde2 + RCM_HALO);
+  const int ilo = std::max(lb[1], g.ide1 - RCM_HALO), ihi = std::min(ub[1], g.ide2 + RCM_HALO);
+  const int klo = std::max(lb[2], 1), khi = std::min(ub[2], nk);
+  if (jhi < jlo || ihi < ilo || khi < klo) return RCM_OK;
+  const size_t n1 = (size_t)(ub[0] - lb[0] + 1), n2 = (size_t)(ub[1] - lb[1] + 1);
+  cudaMemcpy3DParms p;
+  std::memset(&p, 0, sizeof(p));
+  cudaPitchedPtr hp = make_cudaPitchedPtr((void*)host, n1 * sizeof(double), n1, n2);
+  cudaPitchedPtr dp = make_cudaPitchedPtr((void*)(dev_shifted - h->off3), (size_t)g.si * sizeof(double), (size_t)g.si, (size_t)h->ni_pad);
+  cudaPos hpos = make_cudaPos((size_t)(jlo - lb[0]) * sizeof(double), (size_t)(ilo - lb[1]), (size_t)(klo - lb[2]));
+  cudaPos dpos = make_cudaPos((size_t)(jlo - (g.jde1 - RCM_HALO)) * sizeof(double), (size_t)(ilo - (g.ide1 - RCM_HALO)), (size_t)(klo - 1));
+  p.srcPtr = to_device ? hp : dp; p.srcPos = to_device ? hpos : dpos;
+  p.dstPtr = to_device ? dp : hp; p.dstPos = to_device ? dpos : hpos;
+  p.extent = make_cudaExtent((size_t)(jhi - jlo + 1) * sizeof(double), (size_t)(ihi - ilo + 1), (size_t)(khi - klo + 1));
+  p.kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+  CUDA_OK(cudaMemcpy3DAsync(&p, h->st));
+  CUDA_OK(cudaStreamSynchronize(h->st));
+  return RCM_OK;
+}
+#endif
+
 static int upload3(rcm_dyn* h, double* dev_shifted, const double* a, const int32_t* lb, const int32_t* ub, int nk) {
-  std::fill(h->stage.begin(), h->stage.end(), 0.0);
-  // stage plane 0 is k = 1: off = off2
-  win_in(h, h->stage, h->off2, nk, a, lb, ub, 1);
+#ifndef RCM_EMU
+  return copy3d(h, dev_shifted, a, lb, ub, nk, true);
+#else
+  CUDA_OK(cudaMemcpy(h->stage.data(), dev_shifted - h->off3, (size_t)h->g.sk * nk * sizeof(double), cudaMemcpyDeviceToHost));
+  win_in(h, h->stage, h->off2, nk, a, lb, ub, 1);  // stage plane 0 is k = 1
   CUDA_OK(cudaMemcpy(dev_shifted - h->off3, h->stage.data(), (size_t)h->g.sk * nk * sizeof(double), cudaMemcpyHostToDevice));
   return RCM_OK;
+#endif
 }
 
 extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a, const int32_t lb[3], const int32_t ub[3]) {
@@ -880,6 +911,8 @@ static int tend(rcm_dyn* h) {
   s.istep = istep; s.it = 0;
   h->last_istep = istep;
   int rc;
+  CUDA_OK(cudaMemsetAsync(f.cflbits, 0, sizeof(unsigned long long), h->st));
+  CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
   launch_prep(g, f, s, h->st); h->launches += 2;
   launch_uv(g, f, s, h->st); h->launches += 1;
   launch_tq(g, f, s, h->st); h->launches += 1;
@@ -913,7 +946,7 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
   if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_step before rcm_dyn_init");
   cudaSetDevice(h->device);
   Fields& f = h->f;
-  CUDA_OK(cudaMemsetAsync(f.cflbits, 0, sizeof(unsigned long long), h->st));
+  CUDA_OK(cudaMemsetAsync(f.cflbits, 0, 2 * sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.nanflag, 0, sizeof(int), h->st));
   CUDA_OK(cudaEventRecord(h->ev0, h->st));
@@ -934,12 +967,12 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
   cudaEventElapsedTime(&ms, h->ev0, h->ev1);
   h->last_ms = ms;
   if (rc) return rc;
-  unsigned long long bits = 0, nq = 0; int nanf = 0;
-  CUDA_OK(cudaMemcpy(&bits, f.cflbits, sizeof(bits), cudaMemcpyDeviceToHost));
+  unsigned long long bits2[2] = {0, 0}, nq = 0; int nanf = 0;
+  CUDA_OK(cudaMemcpy(bits2, f.cflbits, sizeof(bits2), cudaMemcpyDeviceToHost));
   CUDA_OK(cudaMemcpy(&nq, f.negq, sizeof(nq), cudaMemcpyDeviceToHost));
   CUDA_OK(cudaMemcpy(&nanf, f.nanflag, sizeof(nanf), cudaMemcpyDeviceToHost));
-  double cfl; std::memcpy(&cfl, &bits, sizeof(cfl));
-  h->max_cfl = cfl; h->neg_q = (int64_t)nq; h->nan_flag = nanf;
+  double cfl, cfl_last; std::memcpy(&cfl, &bits2[1], sizeof(cfl)); std::memcpy(&cfl_last, &bits2[0], sizeof(cfl_last));
+  h->max_cfl = cfl_last; h->neg_q = (int64_t)nq; h->nan_flag = nanf;
   CUDA_OK(cudaGetLastError());
   if (nanf || cfl != cfl) return fail(h, RCM_ERR_NAN, "NaN in the acoustic solver");
   if (cfl > 1.0) {
@@ -966,6 +999,9 @@ static double* state_ptr(rcm_dyn* h, int field, int level) {
 }
 
 static int download3(rcm_dyn* h, const double* dev_shifted, double* a, const int32_t* lb, const int32_t* ub, int nk) {
+#ifndef RCM_EMU
+  return copy3d(h, const_cast<double*>(dev_shifted), a, lb, ub, nk, false);
+#else
   const Geom& g = h->g;
   CUDA_OK(cudaMemcpy(h->stage.data(), dev_shifted - h->off3, (size_t)g.sk * nk * sizeof(double), cudaMemcpyDeviceToHost));
   const int jlo = std::max(lb[0], g.jde1 - RCM_HALO), jhi = std::min(ub[0], g.jde2 + RCM_HALO);
@@ -977,6 +1013,7 @@ static int download3(rcm_dyn* h, const double* dev_shifted, double* a, const int
         a[(j - lb[0]) + n1 * ((i - lb[1]) + n2 * (long long)(k - lb[2]))] =
             h->stage[h->off2 + j + (long long)i * g.si + (long long)(k - 1) * g.sk];
   return RCM_OK;
+#endif
 }
 
 extern "C" int rcm_dyn_get_state(rcm_dyn* h, int field, int level, double* a, const int32_t lb[3], const int32_t ub[3]) {
@@ -992,13 +1029,7 @@ extern "C" int rcm_dyn_set_state(rcm_dyn* h, int field, int level, const double*
   cudaSetDevice(h->device);
   double* p = state_ptr(h, field, level);
   if (!p) return fail(h, RCM_ERR_ARG, "bad field");
-  // read-modify-write so that a window smaller than the tile keeps the rest
-  const Geom& g = h->g;
-  const int nk = h->g.kzp1;
-  CUDA_OK(cudaMemcpy(h->stage.data(), p - h->off3, (size_t)g.sk * nk * sizeof(double), cudaMemcpyDeviceToHost));
-  win_in(h, h->stage, h->off2, nk, a, lb, ub, 1);
-  CUDA_OK(cudaMemcpy(p - h->off3, h->stage.data(), (size_t)g.sk * nk * sizeof(double), cudaMemcpyHostToDevice));
-  return RCM_OK;
+  return upload3(h, p, a, lb, ub, h->g.kzp1);
 }
 
 extern "C" int rcm_dyn_get_work(rcm_dyn* h, int id, double* a, const int32_t lb[3], const int32_t ub[3]) {

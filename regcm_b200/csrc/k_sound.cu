@@ -294,7 +294,8 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
   // block-level max, one atomic per block (order-independent => exact)
   unsigned long long bits = (unsigned long long)__double_as_longlong(cfl);  // cfl >= 0: bit order == value order
   if (cfl != cfl) { *f.nanflag = 1; bits = 0x7ff8000000000000ULL; }
-  atomicMax(f.cflbits, bits);
+  atomicMax(f.cflbits, bits);      // max over the sub-steps of this step
+  atomicMax(f.cflbits + 1, bits);  // max over the whole rcm_dyn_step call
 }
 
 // ---------------------------------------------------------------------------

@@ -1,0 +1,42 @@
+"""Generates tests/golden/*.npz from the CPU oracle (oracle/).
+
+The reference ships no golden vectors for the dyn-core ("parity unpinned",
+SURVEY.md §8c) and cannot be built here (no Fortran compiler), so these
+fixtures pin the oracle restatement against itself over time (regression pin)
+and let the GPU tests compare against committed numbers without importing the
+oracle.  Run from the repo root:  python tests/golden/make_golden.py
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from regcm_b200 import capi, synth  # noqa: E402
+from oracle import pyoracle  # noqa: E402
+
+CASES = [("tiny", 12, {}), ("tiny", 6, {"iboudy": 1, "ifupr": 0}), ("small", 4, {})]
+
+
+def main():
+    for name, nsteps, kw in CASES:
+        case = synth.make_case(name, **kw)
+        o = pyoracle.make_oracle(case.cfg)
+        synth.load_case(o, case)
+        o.step(nsteps)
+        out = {"nsteps": nsteps}
+        for f in range(7):
+            for lv in (0, 1):
+                # float64, stored exactly
+                out[capi.FIELD_NAMES[f] + "_" + "ab"[lv]] = o.get_state(f, lv)
+        d = o.diag()
+        out["max_cfl"] = d.max_cfl
+        out["istep"] = d.istep
+        tag = name + "".join(f"_{k}{v}" for k, v in sorted(kw.items()))
+        np.savez_compressed(os.path.join(ROOT, "tests", "golden", f"nh_{tag}_{nsteps}.npz"), **out)
+        print("wrote", tag, nsteps)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,42 @@
+import numpy as np
+
+from regcm_b200 import capi, synth
+
+
+def rel_errors(core, ref, levels=(capi.LEVEL_A, capi.LEVEL_B)):
+    """Per prognostic field: L-inf and L2 error normalised by the reference."""
+    out = {}
+    for f in range(7):
+        for lv in levels:
+            a, b = core.get_state(f, lv), ref.get_state(f, lv)
+            sc = max(float(np.abs(b).max()), 1e-300)
+            l2 = float(np.sqrt(np.mean((a - b) ** 2))) / sc
+            out[capi.FIELD_NAMES[f] + "ab"[lv]] = (float(np.abs(a - b).max()) / sc, l2)
+    return out
+
+
+def work_errors(core, ref):
+    out = {}
+    for w in range(10):
+        a, b = core.get_work(w), ref.get_work(w)
+        sc = max(float(np.abs(b).max()), 1e-300)
+        out[capi.WORK_NAMES[w]] = float(np.abs(a - b).max()) / sc
+    return out
+
+
+def make_pair(lib, name, oracle_checked=False, **kw):
+    from oracle import pyoracle
+    case = synth.make_case(name, **kw)
+    core = capi.DynCore(lib, case.cfg)
+    synth.load_case(core, case)
+    ref = pyoracle.make_oracle(case.cfg, checked=oracle_checked)
+    synth.load_case(ref, case)
+    return case, core, ref
+
+
+def smooth_qc(case):
+    """Smooth positive coupled cloud-water field (kept away from the negative-q guard)."""
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    J, I, K = np.meshgrid(np.arange(jx - 1), np.arange(iy - 1), np.arange(kz), indexing="ij")
+    return np.asfortranarray(96.0 * 1e-4 * (1.0 + 0.5 * np.sin(2 * np.pi * J / (jx - 1)) * np.cos(2 * np.pi * I / (iy - 1)))
+                             * np.sin(np.pi * (K + 0.5) / kz))
