@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""Benchmark of the RegCM non-hydrostatic dyn-core step on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C4|C3|C2] [--impl reference]
+
+One "step" = one full model step (`tend` + `bdyval`: slow tendencies, istep acoustic
+sub-steps, filters, boundary update) over the whole synthetic domain.  Prints ONE JSON
+line on rank 0.  With torchrun (N > 1) the domain is decomposed over the ranks like
+set_nproc does (strong scaling: the total work is fixed).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from regcm_b200 import capi, synth  # noqa: E402
+
+METRIC = "dyn-core grid-point-steps/s"
+UNIT = "grid-point-steps/s"
+# compulsory HBM bytes per grid-point-step of the NH core, nqx = 2
+ALG_BYTES_STEP = lambda istep: 352 + 192 * istep  # noqa: E731
+# per-kernel algorithmic bytes per grid point and launch = 8 B x (distinct 3-D fields
+# read + written by that kernel), listed in DESIGN.md §Kernels
+ALG_BYTES_KERNEL = {
+    "k_prep": 104, "k_xkc": 32, "k_uv": 80, "k_tq": 144, "k_ppw": 136, "k_snd_init": 88,
+    "k_snd_uv": 80, "k_snd_wfwd": 120, "k_snd_wback": 168, "k_snd_final": 160,
+}
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU with NVML during the timed region."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            pass
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4)}
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.05)
+
+    def stop(self):
+        self._stop_evt.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        return {"sm_mhz": (float(np.median(self.samples)) if self.samples else None),
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def tile_window(cfgdict, nproc, myid):
+    """Window of the synthetic data a rank needs = its tile + ghost rows (the library
+    reproduces set_nproc; this mirrors rcm_dyn_create's split)."""
+    return None if nproc == 1 else "lib"
+
+
+# ----------------------------------------------------------------------------- CPU oracle legs
+def _oracle_sample_case(workload, side):
+    base = synth.CASES[workload]
+    side_j = min(side, base["jx"]); side_i = min(side, base["iy"])
+    return synth.make_case(workload, jx=side_j, iy=side_i, records=(capi.BDY_B0, capi.BDY_B1))
+
+
+def oracle_throughput(workload, side, nthreads, nsteps, nwarm):
+    """grid-point-steps/s of the CPU oracle: `nthreads` independent instances (one per
+    host thread, like MPI ranks without the halo cost), each on a side x side x kz
+    sub-domain of the workload.  Returns (value, per-step ms)."""
+    from oracle import pyoracle
+    case = _oracle_sample_case(workload, side)
+    cores = []
+    for _ in range(nthreads):
+        o = pyoracle.make_oracle(case.cfg)
+        synth.load_case(o, case, stage_next=False)
+        cores.append(o)
+
+    def run(n):
+        th = [threading.Thread(target=o.step, args=(n,)) for o in cores]
+        [t.start() for t in th]
+        [t.join() for t in th]
+
+    if nwarm:
+        run(nwarm)
+    t0 = time.perf_counter()
+    run(nsteps)
+    dt = time.perf_counter() - t0
+    cells = case.cells * nthreads
+    return cells * nsteps / dt, dt / nsteps * 1e3, case
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import pyoracle
+    pyoracle.build()
+    nthreads = host_threads()
+    total_steps = args.steps + args.warmup
+    kz = synth.CASES[args.workload]["kz"]
+    # ~1.1 M grid-point-steps/s per thread; bound the whole run to ~150 s and the memory to
+    # ~1.5 kB per grid point per instance
+    budget_cells = 1.0e6 * 150.0 / max(total_steps, 1)
+    try:
+        import psutil
+        mem_cells = 0.4 * psutil.virtual_memory().available / 1500.0 / nthreads
+        budget_cells = min(budget_cells, mem_cells)
+    except Exception:
+        pass
+    side = int(max(40, min(256, np.sqrt(budget_cells / kz))))
+    value, ms, case = oracle_throughput(args.workload, side, nthreads, args.steps, args.warmup)
+    sample = (f"{nthreads} independent oracle instances (1 host thread each, no halo exchange), each a "
+              f"{case.cfg.jx}x{case.cfg.iy}x{case.cfg.kz} sub-domain of workload {args.workload} (same ds, dt, options)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_desc(args.workload), "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": nthreads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference Fortran/MPI build unavailable (no Fortran compiler, MPI or NetCDF in the image): "
+                "the timed CPU code is the C++ restatement of the reference's dyn-core (oracle/, kind=port)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_desc(w):
+    c = synth.CASES[w]
+    return (f"{w}: {c['jx']}x{c['iy']}x{c['kz']} non-hydrostatic (idynamic=2), ds={c['ds']} km, dt={c['dt']} s, "
+            f"physics off, synthetic analytic ICBC")
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def run_gpu(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the dyn-core has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = capi.cuda_lib()
+    base = synth.CASES[args.workload]
+    cfgkw = dict(nproc=world, myid=rank, device=local)
+    # the rank's tile (+ghost rows): ask the library for the decomposition by creating the handle first
+    probe_cfg = synth.make_case("tiny").cfg  # only for struct defaults
+    del probe_cfg
+    cfg = capi.default_cfg(2, jx=base["jx"], iy=base["iy"], kz=base["kz"], ds=base["ds"], dt=base["dt"],
+                           nspgx=base["nspg"], nspgd=base["nspg"], **cfgkw)
+    core = capi.DynCore(lib, cfg)
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(capi.nccl_unique_id(lib)), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        core.comm_init(bytes(uid.cpu().numpy().tobytes()))
+        j1, j2, i1, i2 = core.tile()
+        window = (j1 - 3, j2 + 3, i1 - 3, i2 + 3)
+    else:
+        window = None
+    t_gen = time.perf_counter()
+    case = synth.make_case(args.workload, window=window, **cfgkw)
+    t_gen = time.perf_counter() - t_gen
+    synth.load_case(core, case, stage_next=False)
+    cells = base["jx"] * base["iy"] * base["kz"]
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- warm-up (includes the two start-up steps with dt = dtsec and the first tmask update) ----
+    for _ in range(max(args.warmup, 3)):
+        core.step(1)
+    istep = core.diag().istep
+    # ---- timed region 1: device-resident steps (value) ----
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    l0 = core.launch_count()
+    t0 = time.perf_counter()
+    core.step(args.steps)
+    wall = time.perf_counter() - t0
+    dev_ms = core.last_step_ms()
+    barrier()
+    clocks = sampler.stop()
+    launches = core.launch_count() - l0
+    ms_total = max_over_ranks(dev_ms)
+    wall = max_over_ranks(wall)
+    ms_per_step = ms_total / args.steps
+    value = cells * args.steps / (ms_total * 1e-3)
+
+    # ---- timed region 2: same K steps with per-kernel CUDA events (roofline) ----
+    core.profile(True)
+    barrier()
+    core.step(args.steps)
+    barrier()
+    prof = core.profile_report()
+    prof_ms = core.last_step_ms()
+    core.profile(False)
+    peak, peak_src = peaks()
+    local_cells = core.tile_cells()
+    kern = {k: v for k, v in prof.items() if v[1] > 0 and k in ALG_BYTES_KERNEL}
+    top = max(kern, key=lambda k: kern[k][0])
+    top_ms = kern[top][0] / kern[top][1]
+    achieved = ALG_BYTES_KERNEL[top] * local_cells / (top_ms * 1e-3) / 1e9
+    roofline = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "avg_launch_ms": top_ms,
+                "alg_bytes_per_launch": ALG_BYTES_KERNEL[top] * local_cells,
+                "share_of_step": kern[top][0] / max(sum(v[0] for v in prof.values()), 1e-30),
+                "per_kernel": {k: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps,
+                                   "GBs": (ALG_BYTES_KERNEL[k] * local_cells / (v[0] / v[1] * 1e-3) / 1e9 if k in ALG_BYTES_KERNEL and v[1] else None)}
+                               for k, v in prof.items() if v[1] > 0}}
+    step_bytes = ALG_BYTES_STEP(istep)
+    step_roof = {"alg_bytes_per_grid_point_step": step_bytes, "achieved_GBs": step_bytes * value / world / 1e9,
+                 "frac_of_peak_per_gpu": step_bytes * value / world / 1e9 / peak}
+
+    # ---- timed region 3: end to end through the C ABI with HOST (pinned) buffers ----
+    e2e = None
+    if not args.no_e2e:
+        # one coupling interval as the Fortran driver would run it: stage the next ICBC record from
+        # pinned host memory (H2D), K x {rcm_dyn_step(1); rcm_dyn_diag}, read the whole level-a
+        # prognostic state back into pinned host memory (D2H).
+        rec = synth.make_case(args.workload, window=window, records=(capi.BDY_NEXT,), **cfgkw).bdy[capi.BDY_NEXT]
+        lb = getattr(case, "lb", (1, 1))
+        pinned_in, pinned_out = {}, {}
+        for fid, a in rec.items():
+            t = torch.empty(a.shape[::-1], dtype=torch.float64).pin_memory()
+            v = t.numpy().T
+            v[...] = a
+            pinned_in[fid] = v
+        j1, j2, i1, i2 = core.tile()
+        out_lbub = {}
+        for fid in range(7):
+            dot = fid in (capi.F_U, capi.F_V)
+            lbs = (j1, i1, 1)
+            ubs = (j2 if dot else min(j2, base["jx"] - 1), i2 if dot else min(i2, base["iy"] - 1),
+                   base["kz"] + (1 if fid == capi.F_W else 0))
+            shp = tuple(ubs[d] - lbs[d] + 1 for d in range(3))
+            t = torch.empty(shp[::-1], dtype=torch.float64).pin_memory()
+            pinned_out[fid] = t.numpy().T
+            out_lbub[fid] = (lbs, ubs)
+        h2d = sum(v.nbytes for v in pinned_in.values())
+        d2h = sum(v.nbytes for v in pinned_out.values())
+        barrier()
+        t0 = time.perf_counter()
+        for fid, v in pinned_in.items():
+            core.set_bdy(fid, capi.BDY_NEXT, v, lb=(lb[0], lb[1], 1))
+        for _ in range(args.steps):
+            core.step(1)
+            core.diag()
+        for fid, v in pinned_out.items():
+            core.get_state(fid, capi.LEVEL_A, lb=out_lbub[fid][0], ub=out_lbub[fid][1], out=v)
+        torch.cuda.synchronize()
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": cells * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d / args.steps,
+               "d2h_bytes_per_step": d2h / args.steps, "ms_per_step": e2e_s / args.steps * 1e3,
+               "what": "per rank: stage one ICBC record (6 fields) from pinned host memory, K x {rcm_dyn_step(1); rcm_dyn_diag}, "
+                       "download the 7 level-a prognostic fields to pinned host memory; bytes amortised over the K steps"}
+
+    # ---- CPU baseline (rank 0, N = 1 only): the oracle on a bounded sample ----
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        side = 160
+        v, ms, ccase = oracle_throughput(args.workload, side, 1, 3, 1)
+        cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": f"CPU oracle (C++ restatement, 1 thread) on a {ccase.cfg.jx}x{ccase.cfg.iy}x{ccase.cfg.kz} sub-domain of "
+                         f"{args.workload}, 3 timed steps after 1 warm-up ({ms:.0f} ms/step)"}
+
+    bad = [r for r in clocks["reasons"] if r in ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown")]
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_desc(args.workload), "istep": istep,
+                       "decomposition": f"{world} rank(s), set_nproc layout", "l2": "inputs larger than L2 (no flush)"
+                       if cells * 8 * 20 > 126e6 else "working set fits L2; not flushed (launch-bound case)",
+                       "sim_days_per_day": value / cells * base["dt"]},
+            "clocks": clocks, "clock_reject": bool(bad),
+            "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "step_roofline": step_roof, "cpu_baseline": cpu,
+            "timing": {"device_ms_total": ms_total, "wall_ms_total": wall * 1e3, "profiled_pass_ms_total": prof_ms,
+                       "synth_gen_s": t_gen},
+        }
+        print(json.dumps(line), flush=True)
+    core.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C4", choices=sorted(synth.CASES))
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

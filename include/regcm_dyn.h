@@ -208,6 +208,21 @@ int rcm_dyn_last_error(rcm_dyn* h, char* buf, int len);
 int64_t rcm_dyn_launch_count(rcm_dyn* h);
 double rcm_dyn_last_step_ms(rcm_dyn* h);
 
+/* replaces: the tile extents set_nproc / setup_model_indexes give a rank
+ * (global_dot_jstart..jend, istart..iend; Main/mpplib/mod_mppparam.F90:1302-1360):
+ * out = {jde1, jde2, ide1, ide2} in global dot indices. */
+int rcm_dyn_get_tile(rcm_dyn* h, int32_t out[4]);
+
+/* per-kernel device timing (no reference equivalent; the reference has no
+ * timers in production builds).  While enabled, every kernel
+ * launch of rcm_dyn_step is bracketed by CUDA events on the library's stream;
+ * rcm_dyn_profile_get returns the accumulated milliseconds and launch count
+ * of kernel `kid` in [0, rcm_dyn_profile_kernels()). */
+int rcm_dyn_profile(rcm_dyn* h, int enable);
+int rcm_dyn_profile_get(rcm_dyn* h, int kid, double* ms, int64_t* count,
+                        char* name, int len);
+int rcm_dyn_profile_kernels(void);
+
 /* replaces: the communicator set-up of set_nproc / mpi_cart_create
  * (Main/mpplib/mod_mppparam.F90:1053-1401) for nproc > 1.  Rank 0 obtains a
  * 128-byte NCCL unique id with rcm_dyn_comm_unique_id, the caller broadcasts

@@ -145,6 +145,12 @@ class CoreLib:
             "set_state": ([vp, C.c_int, C.c_int, _DP, _I3, _I3], C.c_int),
             "launch_count": ([vp], C.c_int64),
             "last_step_ms": ([vp], C.c_double),
+            "get_tile": ([vp, C.POINTER(C.c_int32)], C.c_int),
+            "profile": ([vp, C.c_int], C.c_int),
+            "profile_get": ([vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_char_p, C.c_int], C.c_int),
+            "profile_kernels": ([], C.c_int),
+            "comm_unique_id": ([C.c_void_p, C.c_int], C.c_int),
+            "comm_init": ([vp, C.c_void_p, C.c_int], C.c_int),
         }.items():
             if hasattr(self.lib, p + opt):
                 fn = getattr(self.lib, p + opt)
@@ -206,11 +212,13 @@ class DynCore:
     def step(self, n: int = 1):
         self._check(self.lib.step(self.h, n))
 
-    def get_state(self, field: int, level: int = LEVEL_A, lb=None, ub=None) -> np.ndarray:
+    def get_state(self, field: int, level: int = LEVEL_A, lb=None, ub=None, out=None) -> np.ndarray:
         shp = self.field_shape(field)
         lb = lb or (1, 1, 1)
         ub = ub or shp
-        out = np.zeros(tuple(ub[d] - lb[d] + 1 for d in range(3)), dtype=np.float64, order="F")
+        if out is None:
+            out = np.zeros(tuple(ub[d] - lb[d] + 1 for d in range(3)), dtype=np.float64, order="F")
+        assert out.flags.f_contiguous and out.shape == tuple(ub[d] - lb[d] + 1 for d in range(3))
         self._check(self.lib.get_state(self.h, field, level, out.ctypes.data_as(_DP), *_bounds(lb, ub)))
         return out
 
@@ -240,6 +248,32 @@ class DynCore:
         self._check(self.lib.diag(self.h, C.byref(d)))
         return d
 
+    def tile(self):
+        """(jde1, jde2, ide1, ide2): this rank's dot-point extent in global indices."""
+        out = (C.c_int32 * 4)()
+        self._check(self.lib.get_tile(self.h, out))
+        return tuple(int(x) for x in out)
+
+    def tile_cells(self) -> int:
+        j1, j2, i1, i2 = self.tile()
+        return (j2 - j1 + 1) * (i2 - i1 + 1) * self.kz
+
+    def profile(self, enable: bool):
+        self._check(self.lib.profile(self.h, 1 if enable else 0))
+
+    def profile_report(self):
+        """{kernel name: (total ms, launches)} accumulated since profile(True)."""
+        out = {}
+        for kid in range(self.lib.profile_kernels()):
+            ms, n, nm = C.c_double(), C.c_int64(), C.create_string_buffer(64)
+            self._check(self.lib.profile_get(self.h, kid, C.byref(ms), C.byref(n), nm, 64))
+            out[nm.value.decode()] = (ms.value, n.value)
+        return out
+
+    def comm_init(self, unique_id: bytes):
+        buf = C.create_string_buffer(unique_id, 128)
+        self._check(self.lib.comm_init(self.h, buf, 128))
+
     def launch_count(self) -> int:
         return int(self.lib.launch_count(self.h))
 
@@ -256,6 +290,14 @@ class DynCore:
             self.close()
         except Exception:
             pass
+
+
+def nccl_unique_id(lib: "CoreLib") -> bytes:
+    buf = C.create_string_buffer(128)
+    rc = lib.comm_unique_id(buf, 128)
+    if rc != 0:
+        raise RcmError(rc, "rcm_dyn_comm_unique_id failed (libnccl.so.2 not loadable?)")
+    return buf.raw
 
 
 _PKG_DIR = os.path.dirname(os.path.abspath(__file__))

@@ -30,8 +30,10 @@ void launch_tq(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_ppw(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_init(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_uv(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
-void launch_snd_wfwd_only(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
-void launch_snd_wback_only(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_xkc(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_snd_wfwd(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_snd_wpval(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_snd_wback(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_final(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_couple(const Geom&, double*, const double*, int, int, int, int, int, cudaStream_t);
 void launch_timeint(const Geom&, const double*, const double*, double*, double, int, int, int, int, int, cudaStream_t);
@@ -47,7 +49,20 @@ void launch_bdyval(const Geom&, const Fields&, const double*, const double*, con
     }                                                                                   \
   } while (0)
 
+// per-kernel device timing (CUDA events on the library's stream), enabled by
+// rcm_dyn_profile(); used by bench.py for the per-kernel roofline
+enum { KID_PREP, KID_XKC, KID_UV, KID_TQ, KID_PPW, KID_SND_INIT, KID_SND_UV, KID_SND_WFWD, KID_SND_WPVAL, KID_SND_WBACK,
+       KID_SND_FINAL, KID_BDY, KID_HALO, KID_COUNT };
+static const char* const kKernelNames[KID_COUNT] = {"k_prep", "k_xkc", "k_uv", "k_tq", "k_ppw", "k_snd_init", "k_snd_uv",
+                                                    "k_snd_wfwd", "k_snd_wpval", "k_snd_wback", "k_snd_final", "k_bdy", "halo"};
+struct ProfRec { int kid; cudaEvent_t a, b; };
+
 struct rcm_dyn {
+  bool prof_on = false;
+  std::vector<ProfRec> prof_recs;
+  std::vector<cudaEvent_t> prof_pool;
+  double prof_ms[KID_COUNT] = {0};
+  int64_t prof_n[KID_COUNT] = {0};
   rcm_cfg cfg{};
   Geom g{};
   Fields f{};
@@ -93,6 +108,29 @@ struct rcm_dyn {
 // host accessors in the padded geometry
 #define H2(v, j, i) (v)[h->off2 + (long long)(j) + (long long)(i) * h->g.si]
 #define H3(v, j, i, k) (v)[h->off3 + (long long)(j) + (long long)(i) * h->g.si + (long long)(k) * h->g.sk]
+
+static cudaEvent_t prof_event(rcm_dyn* h) {
+  if (!h->prof_pool.empty()) { cudaEvent_t e = h->prof_pool.back(); h->prof_pool.pop_back(); return e; }
+  cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+#define TIMED(kid_, n_, call)                                             \
+  do {                                                                    \
+    if (h->prof_on) {                                                     \
+      ProfRec r_; r_.kid = (kid_); r_.a = prof_event(h); r_.b = prof_event(h); \
+      cudaEventRecord(r_.a, h->st); call; cudaEventRecord(r_.b, h->st);   \
+      h->prof_recs.push_back(r_);                                         \
+    } else { call; }                                                      \
+    h->launches += (n_);                                                  \
+  } while (0)
+static void prof_collect(rcm_dyn* h) {
+  for (ProfRec& r : h->prof_recs) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.a, r.b);
+    h->prof_ms[r.kid] += ms; h->prof_n[r.kid] += 1;
+    h->prof_pool.push_back(r.a); h->prof_pool.push_back(r.b);
+  }
+  h->prof_recs.clear();
+}
 
 static int fail(rcm_dyn* h, int code, const std::string& msg) {
   if (h) h->err = msg;
@@ -804,9 +842,8 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
 // ---------------------------------------------------------------------------
 static int bdyval(rcm_dyn* h, const double* oat, const double* oaqv, const double* oaqc) {
   const double xt = h->xbctime + h->dt;
-  launch_bdyval(h->g, h->f, oat, oaqv, oaqc, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, xt, h->lcount > 0 ? 1 : 0,
-                h->cfg.iboudy, h->st);
-  h->launches += 2;
+  TIMED(KID_BDY, 2, launch_bdyval(h->g, h->f, oat, oaqv, oaqc, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, xt,
+                                  h->lcount > 0 ? 1 : 0, h->cfg.iboudy, h->st));
   h->xbctime = h->xbctime + h->dtsec;
   return RCM_OK;
 }
@@ -913,26 +950,28 @@ static int tend(rcm_dyn* h) {
   int rc;
   CUDA_OK(cudaMemsetAsync(f.cflbits, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
-  launch_prep(g, f, s, h->st); h->launches += 2;
-  launch_uv(g, f, s, h->st); h->launches += 1;
-  launch_tq(g, f, s, h->st); h->launches += 1;
-  launch_ppw(g, f, s, h->st); h->launches += 1;
-  launch_snd_init(g, f, s, h->st); h->launches += 1;
+  TIMED(KID_PREP, 1, launch_prep(g, f, s, h->st));
+  TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
+  TIMED(KID_UV, 1, launch_uv(g, f, s, h->st));
+  TIMED(KID_TQ, 1, launch_tq(g, f, s, h->st));
+  TIMED(KID_PPW, 1, launch_ppw(g, f, s, h->st));
+  TIMED(KID_SND_INIT, 1, launch_snd_init(g, f, s, h->st));
   if ((rc = exch_sound_pp(h))) return rc;
   for (int it = 1; it <= istep; ++it) {
     s.it = it;
-    launch_snd_uv(g, f, s, h->st); h->launches += 1;
+    TIMED(KID_SND_UV, 1, launch_snd_uv(g, f, s, h->st));
     if ((rc = exch_sound_uv(h))) return rc;
-    launch_snd_wfwd_only(g, f, s, h->st); h->launches += 1;
+    TIMED(KID_SND_WFWD, 1, launch_snd_wfwd(g, f, s, h->st));
     if (h->cfg.ifupr == 1) {
       if ((rc = exch_estore(h))) return rc;
       if (h->day_now == h->model_time && it == 1)
         if ((rc = update_tmask(h))) return rc;
     }
-    launch_snd_wback_only(g, f, s, h->st); h->launches += 2;
+    TIMED(KID_SND_WPVAL, 1, launch_snd_wpval(g, f, s, h->st));
+    TIMED(KID_SND_WBACK, 1, launch_snd_wback(g, f, s, h->st));
     if (it < istep && (rc = exch_sound_pp(h))) return rc;
   }
-  launch_snd_final(g, f, s, h->st); h->launches += 1;
+  TIMED(KID_SND_FINAL, 1, launch_snd_final(g, f, s, h->st));
   // swap in the filtered t, qv, qc (the old buffers keep the previous rim)
   std::swap(f.at, f.nat); std::swap(f.aqv, f.naqv); std::swap(f.aqc, f.naqc);
   std::swap(f.bt, f.nbt); std::swap(f.bqv, f.nbqv); std::swap(f.bqc, f.nbqc);
@@ -966,6 +1005,7 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
   float ms = 0.f;
   cudaEventElapsedTime(&ms, h->ev0, h->ev1);
   h->last_ms = ms;
+  prof_collect(h);
   if (rc) return rc;
   unsigned long long bits2[2] = {0, 0}, nq = 0; int nanf = 0;
   CUDA_OK(cudaMemcpy(bits2, f.cflbits, sizeof(bits2), cudaMemcpyDeviceToHost));
@@ -1070,6 +1110,27 @@ extern "C" int rcm_dyn_last_error(rcm_dyn* h, char* buf, int len) {
   return RCM_OK;
 }
 
+extern "C" int rcm_dyn_get_tile(rcm_dyn* h, int32_t out[4]) {
+  if (!h || !out) return RCM_ERR_ARG;
+  out[0] = h->g.jde1; out[1] = h->g.jde2; out[2] = h->g.ide1; out[3] = h->g.ide2;
+  return RCM_OK;
+}
+
+extern "C" int rcm_dyn_profile(rcm_dyn* h, int enable) {
+  if (!h) return RCM_ERR_ARG;
+  h->prof_on = enable != 0;
+  for (int q = 0; q < KID_COUNT; ++q) { h->prof_ms[q] = 0; h->prof_n[q] = 0; }
+  return RCM_OK;
+}
+extern "C" int rcm_dyn_profile_get(rcm_dyn* h, int kid, double* ms, int64_t* count, char* name, int len) {
+  if (!h || kid < 0 || kid >= KID_COUNT) return RCM_ERR_ARG;
+  if (ms) *ms = h->prof_ms[kid];
+  if (count) *count = h->prof_n[kid];
+  if (name && len > 0) { std::strncpy(name, kKernelNames[kid], (size_t)len - 1); name[len - 1] = 0; }
+  return RCM_OK;
+}
+extern "C" int rcm_dyn_profile_kernels(void) { return KID_COUNT; }
+
 extern "C" int64_t rcm_dyn_launch_count(rcm_dyn* h) { return h ? h->launches : 0; }
 extern "C" double rcm_dyn_last_step_ms(rcm_dyn* h) { return h ? h->last_ms : 0.0; }
 
@@ -1086,6 +1147,7 @@ extern "C" int rcm_dyn_destroy(rcm_dyn* h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   h->halo.destroy();
+  for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
   for (void* p : h->allocs) cudaFree(p);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);

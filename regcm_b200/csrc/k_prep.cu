@@ -113,6 +113,9 @@ void launch_prep(const Geom& g, const Fields& f, const StepScalars& s, cudaStrea
   const int nj = (g.jce2 + g.gr) - (g.jce1 - g.gl) + 1, ni = (g.ice2 + g.gt) - (g.ice1 - g.gb) + 1;
   dim3 b(RCM_BX, RCM_BY), gr((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY);
   RCM_LAUNCH(k_prep, gr, b, st, g, f, s);
-  dim3 gr3(gr.x, gr.y, g.kz);
+}
+void launch_xkc(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
+  const int nj = (g.jce2 + g.gr) - (g.jce1 - g.gl) + 1, ni = (g.ice2 + g.gt) - (g.ice1 - g.gb) + 1;
+  dim3 b(RCM_BX, RCM_BY), gr3((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY, g.kz);
   RCM_LAUNCH(k_xkc, gr3, b, st, g, f, s);
 }

@@ -358,24 +358,19 @@ void launch_snd_uv(const Geom& g, const Fields& f, const StepScalars& s, cudaStr
   dim3 b(32, 4, 2), gr((nj + 31) / 32, (ni + 3) / 4, (g.kz + 1) / 2);
   RCM_LAUNCH(k_snd_uv, gr, b, st, g, f, s);
 }
-void launch_snd_w(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
-  const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
-  dim3 b(RCM_BX, RCM_BY), gr((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY);
-  RCM_LAUNCH(k_snd_wfwd, gr, b, st, g, f, s);
-  dim3 b2(32, 8), gr2((nj + 31) / 32, (ni + 7) / 8);
-  RCM_LAUNCH(k_snd_wpval, gr2, b2, st, g, f, s);
-  RCM_LAUNCH(k_snd_wback, gr, b, st, g, f, s);
-}
-void launch_snd_wfwd_only(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
+void launch_snd_wfwd(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
   dim3 b(RCM_BX, RCM_BY), gr((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY);
   RCM_LAUNCH(k_snd_wfwd, gr, b, st, g, f, s);
 }
-void launch_snd_wback_only(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
+void launch_snd_wpval(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
-  dim3 b(RCM_BX, RCM_BY), gr((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY);
   dim3 b2(32, 8), gr2((nj + 31) / 32, (ni + 7) / 8);
   RCM_LAUNCH(k_snd_wpval, gr2, b2, st, g, f, s);
+}
+void launch_snd_wback(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
+  const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
+  dim3 b(RCM_BX, RCM_BY), gr((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY);
   RCM_LAUNCH(k_snd_wback, gr, b, st, g, f, s);
 }
 void launch_snd_final(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {

@@ -62,6 +62,7 @@ class Case:
     cfg: capi.RcmCfg
     statics: Dict[int, np.ndarray] = field(default_factory=dict)
     bdy: Dict[int, Dict[int, np.ndarray]] = field(default_factory=dict)  # slot -> field -> array
+    lb: tuple = (1, 1)
 
     @property
     def cells(self) -> int:
@@ -76,38 +77,65 @@ def _lambert_msf(lat_deg: np.ndarray, tl1=30.0, tl2=60.0) -> np.ndarray:
     return (np.cos(p1) / np.cos(phi)) * (np.tan(np.pi / 4 + p1 / 2) / np.tan(np.pi / 4 + phi / 2)) ** n
 
 
+def _hash_noise(fid: int, j, i, k) -> np.ndarray:
+    """Counter-based uniform noise in [-1,1): a pure function of the GLOBAL grid
+    index (splitmix64 finaliser), so that any window of any decomposition sees
+    identical data."""
+    with np.errstate(over="ignore"):
+        x = (np.uint64(SEED) + np.uint64(fid) * np.uint64(0x9E3779B97F4A7C15)
+             + j.astype(np.uint64) * np.uint64(0xBF58476D1CE4E5B9)
+             + i.astype(np.uint64) * np.uint64(0x94D049BB133111EB)
+             + k.astype(np.uint64) * np.uint64(0xD6E8FEB86659FD93))
+        x ^= x >> np.uint64(30); x *= np.uint64(0xBF58476D1CE4E5B9)
+        x ^= x >> np.uint64(27); x *= np.uint64(0x94D049BB133111EB)
+        x ^= x >> np.uint64(31)
+    return (x >> np.uint64(11)).astype(np.float64) * (2.0 / 9007199254740992.0) - 1.0
+
+
 def make_case(name: str = "C2", *, flat: bool = False, unit_map: bool = False, noise: bool = True,
-              ibdyfrq: int = 6, **cfg_over) -> Case:
+              ibdyfrq: int = 6, window=None, records=(capi.BDY_B0, capi.BDY_B1, capi.BDY_NEXT),
+              **cfg_over) -> Case:
+    """`window` = (j1, j2, i1, i2): inclusive GLOBAL dot-index range to generate
+    (default: the whole domain).  Cross-point arrays cover j1..min(j2, jx-1)."""
     p = dict(CASES[name])
+    for k in ("jx", "iy", "kz", "ds", "dt"):
+        if k in cfg_over:
+            p[k] = cfg_over.pop(k)
     jx, iy, kz = p["jx"], p["iy"], p["kz"]
     cfg = capi.default_cfg(2, jx=jx, iy=iy, kz=kz, ds=p["ds"], dt=p["dt"],
                            nspgx=p["nspg"], nspgd=p["nspg"], ibdyfrq=ibdyfrq)
     for k, v in cfg_over.items():
         setattr(cfg, k, v)
+    j1, j2, i1, i2 = window or (1, jx, 1, iy)
+    j1, i1, j2, i2 = max(1, j1), max(1, i1), min(jx, j2), min(iy, i2)
+    jc2, ic2 = min(j2, jx - 1), min(i2, iy - 1)
     dx = cfg.ds * 1000.0
     rearth = 6.371229e6
     clat, clon = 45.0, 13.0
     # dot points j=1..jx, i=1..iy ; cross point (j,i) = centre of dots (j..j+1, i..i+1)
-    xd = (np.arange(1, jx + 1) - 0.5 * (jx + 1)) * dx
-    yd = (np.arange(1, iy + 1) - 0.5 * (iy + 1)) * dx
-    xc, yc = xd + 0.5 * dx, yd + 0.5 * dx
+    jd, idd = np.arange(j1, j2 + 1), np.arange(i1, i2 + 1)
+    jc, ic = np.arange(j1, jc2 + 1), np.arange(i1, ic2 + 1)
+    xd = (jd - 0.5 * (jx + 1)) * dx
+    yd = (idd - 0.5 * (iy + 1)) * dx
+    xc, yc = (jc - 0.5 * (jx + 1)) * dx + 0.5 * dx, (ic - 0.5 * (iy + 1)) * dx + 0.5 * dx
     Xd, Yd = np.meshgrid(xd, yd, indexing="ij")
     Xc, Yc = np.meshgrid(xc, yc, indexing="ij")
     dlat = clat + np.degrees(Yd / rearth)
     xlat = clat + np.degrees(Yc / rearth)
     xlon = clon + np.degrees(Xc / (rearth * np.cos(np.radians(xlat))))
     if unit_map:
-        msfd = np.ones((jx, iy)); msfx = np.ones((jx, iy)); coriol = np.zeros((jx, iy))
+        msfd = np.ones_like(Xd); msfx = np.ones_like(Xc); coriol = np.zeros_like(Xd)
     else:
         msfd, msfx = _lambert_msf(dlat), _lambert_msf(xlat)
         coriol = 2.0 * 7.2921159e-5 * np.sin(np.radians(dlat))
     if flat:
-        ht = np.zeros((jx, iy))
+        ht = np.zeros_like(Xc)
     else:
         L = 0.15 * min(jx, iy) * dx
         ht = 1500.0 * np.exp(-(Xc ** 2 + Yc ** 2) / L ** 2)
     sigma = sigma_levels(kz)
     case = Case(name=name, cfg=cfg)
+    case.lb = (j1, i1)
     F = np.asfortranarray
     case.statics = {capi.S_HT: F(ht), capi.S_MSFX: F(msfx), capi.S_MSFD: F(msfd), capi.S_CORIOL: F(coriol),
                     capi.S_XLAT: F(xlat), capi.S_XLON: F(xlon), capi.S_DLAT: F(dlat), capi.S_SIGMA: sigma}
@@ -117,53 +145,61 @@ def make_case(name: str = "C2", *, flat: bool = False, unit_map: bool = False, n
     g = 9.80665
     p0, tlp, ts0, ptop_pa = cfg.base_state_pressure, cfg.logp_lrate, cfg.base_state_ts0, cfg.ptop * 1000.0
     hs = 0.5 * (sigma[1:] + sigma[:-1])
-    htc = ht[: jx - 1, : iy - 1]
     b = ts0 / tlp
-    alnp = -b + np.sqrt(b * b - 4.0 * (0.5 * g / rgas * htc / tlp))
+    alnp = -b + np.sqrt(b * b - 4.0 * (0.5 * g / rgas * ht / tlp))
     ps0 = p0 * np.exp(alnp) - ptop_pa
     pr0 = ps0[:, :, None] * hs[None, None, :] + ptop_pa
     t0 = np.maximum(ts0 + tlp * np.log(pr0 / p0), 216.65)
     a = np.log(pr0 / p0)
     z = np.maximum(-(0.5 * rgas / g * tlp * a * a + rgas / g * ts0 * a), 0.0)
+    del a, pr0
 
     Lx, Ly = jx * dx, iy * dx
-    Xcc, Ycc = Xc[: jx - 1, : iy - 1], Yc[: jx - 1, : iy - 1]
     sh = np.sin(np.pi * hs)[None, None, :]
-    rng = np.random.default_rng(SEED)
-    nz_t = rng.uniform(-1.0, 1.0, size=(jx - 1, iy - 1, kz)) if noise else 0.0
-    nz_u = rng.uniform(-1.0, 1.0, size=(jx, iy, kz)) if noise else 0.0
-    nz_v = rng.uniform(-1.0, 1.0, size=(jx, iy, kz)) if noise else 0.0
+    kk = np.arange(1, kz + 1)
+    if noise:
+        Jc, Ic, Kc = np.meshgrid(jc, ic, kk, indexing="ij", sparse=True)
+        Jd, Id, Kd = np.meshgrid(jd, idd, kk, indexing="ij", sparse=True)
+        nz_t = _hash_noise(1, Jc + 0 * Ic + 0 * Kc, Ic + 0 * Jc + 0 * Kc, Kc + 0 * Jc + 0 * Ic)
+        nz_u = _hash_noise(2, Jd + 0 * Id + 0 * Kd, Id + 0 * Jd + 0 * Kd, Kd + 0 * Jd + 0 * Id)
+        nz_v = _hash_noise(3, Jd + 0 * Id + 0 * Kd, Id + 0 * Jd + 0 * Kd, Kd + 0 * Jd + 0 * Id)
+    else:
+        nz_t = nz_u = nz_v = 0.0
 
     def record(phase: float):
         """fields of one boundary record; `phase` shifts the smooth modes (U*6h)."""
-        xs_c, xs_d = Xcc[:, :, None] - phase, Xd[:, :, None] - phase
-        wave = 2.0 * np.sin(2 * np.pi * xs_c / Lx) * np.cos(2 * np.pi * Ycc[:, :, None] / Ly) * sh
-        r2 = ((xs_c - 0.2 * Lx) ** 2 + (Ycc[:, :, None] + 0.15 * Ly) ** 2) / (0.08 * min(Lx, Ly)) ** 2
+        xs_c, xs_d = Xc[:, :, None] - phase, Xd[:, :, None] - phase
+        wave = 2.0 * np.sin(2 * np.pi * xs_c / Lx) * np.cos(2 * np.pi * Yc[:, :, None] / Ly) * sh
+        r2 = ((xs_c - 0.2 * Lx) ** 2 + (Yc[:, :, None] + 0.15 * Ly) ** 2) / (0.08 * min(Lx, Ly)) ** 2
         bubble = 1.0 * np.exp(-r2) * sh
         t = t0 + wave + bubble
-        t = t * (1.0 + 1.0e-3 * 1.0e-2 * nz_t)   # ±1e-5 relative (≈3 mK) noise
-        u = 20.0 * sh ** 2 * np.ones((jx, iy, 1)) + \
+        t = t * (1.0 + 1.0e-3 * 1.0e-2 * nz_t)   # +-1e-5 relative (~3 mK) noise
+        u = 20.0 * sh ** 2 * np.ones(Xd.shape + (1,)) + \
             2.0 * np.sin(2 * np.pi * xs_d / Lx + 0.7) * np.sin(2 * np.pi * Yd[:, :, None] / Ly + 0.3)
         v = 5.0 * np.sin(2 * np.pi * xs_d / Lx) * np.ones((1, 1, kz))
         u = u + 2.0e-2 * nz_u
         v = v + 2.0e-2 * nz_v
         qv = np.maximum(0.012 * np.exp(-z / 2500.0) * (1.0 + 0.2 * np.sin(2 * np.pi * xs_c / Lx)), 1.0e-8)
-        pp = np.zeros((jx - 1, iy - 1, kz))
-        ww = np.zeros((jx - 1, iy - 1, kz + 1))
+        pp = np.zeros(Xc.shape + (kz,))
+        ww = np.zeros(Xc.shape + (kz + 1,))
         return {capi.F_U: F(u), capi.F_V: F(v), capi.F_T: F(t), capi.F_QV: F(qv),
                 capi.F_PP: F(pp), capi.F_W: F(ww)}
 
     shift = 20.0 * 3600.0 * ibdyfrq * 0.25  # a quarter of the jet advection distance per record
-    case.bdy = {capi.BDY_B0: record(0.0), capi.BDY_B1: record(shift), capi.BDY_NEXT: record(2 * shift)}
+    phases = {capi.BDY_B0: 0.0, capi.BDY_B1: shift, capi.BDY_NEXT: 2 * shift}
+    case.bdy = {slot: record(phases[slot]) for slot in records}
     return case
 
 
 def load_case(core: capi.DynCore, case: Case, stage_next: bool = True) -> None:
     """Feed statics and boundary records into a core and initialise it
     (= read_domain_info + init_bdy + init + first bdyval of the reference)."""
+    lb = getattr(case, "lb", (1, 1))
     for sid, a in case.statics.items():
-        core.set_static(sid, a)
+        core.set_static(sid, a, lb=lb)
     for slot in (capi.BDY_B0, capi.BDY_B1) + ((capi.BDY_NEXT,) if stage_next else ()):
+        if slot not in case.bdy:
+            continue
         for fid, a in case.bdy[slot].items():
-            core.set_bdy(fid, slot, a)
+            core.set_bdy(fid, slot, a, lb=(lb[0], lb[1], 1))
     core.init()
