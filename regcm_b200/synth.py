@@ -120,8 +120,12 @@ def make_case(name: str = "C2", *, flat: bool = False, unit_map: bool = False, n
     xc, yc = (jc - 0.5 * (jx + 1)) * dx + 0.5 * dx, (ic - 0.5 * (iy + 1)) * dx + 0.5 * dx
     Xd, Yd = np.meshgrid(xd, yd, indexing="ij")
     Xc, Yc = np.meshgrid(xc, yc, indexing="ij")
-    dlat = clat + np.degrees(Yd / rearth)
-    xlat = clat + np.degrees(Yc / rearth)
+    # latitude span limited to +-20 deg about 45N so that the analytic Lambert map
+    # factor stays in a realistic range (~0.97-1.07) on continental-size domains
+    half_span = np.degrees(0.5 * iy * dx / rearth)
+    fac = min(1.0, 20.0 / half_span)
+    dlat = clat + np.degrees(Yd / rearth) * fac
+    xlat = clat + np.degrees(Yc / rearth) * fac
     xlon = clon + np.degrees(Xc / (rearth * np.cos(np.radians(xlat))))
     if unit_map:
         msfd = np.ones_like(Xd); msfx = np.ones_like(Xc); coriol = np.zeros_like(Xd)

@@ -58,8 +58,8 @@ def test_parity_option_variants(cuda_lib, kw):
 
 
 def test_boundary_record_change_and_long_run(cuda_lib):
-    case, core, ref = make_pair(cuda_lib, "tiny", ibdyfrq=1)
-    core.step(200); ref.step(200)   # crosses 6 boundary records' worth of relaxation, 1 record change
+    case, core, ref = make_pair(cuda_lib, "tiny", ibdyfrq=2)
+    core.step(110); ref.step(110)   # one boundary-record change at step 60
     assert core.diag().xbctime == ref.diag().xbctime
     errs = rel_errors(core, ref)
     assert _worst(errs) <= 1e-9, errs
