@@ -7,6 +7,18 @@
 // origin-shifted addressing with the reference's global 1-based indices
 #define P3(p, j, i, k) (p)[(long long)(j) + (long long)(i) * si + (long long)(k) * sk]
 #define P2(p, j, i) (p)[(long long)(j) + (long long)(i) * si]
+// read-only loads (ld.global.nc): the array is not written by the running
+// kernel, so the compiler may hoist these above stores and pipeline them
+// across the k loop
+#ifdef RCM_EMU
+#define L3(p, j, i, k) P3(p, j, i, k)
+#define L2(p, j, i) P2(p, j, i)
+#define LD1(p) (*(p))
+#else
+#define L3(p, j, i, k) __ldg(&P3(p, j, i, k))
+#define L2(p, j, i) __ldg(&P2(p, j, i))
+#define LD1(p) __ldg(p)
+#endif
 
 #define RCM_BX 32
 #define RCM_BY 4

@@ -26,15 +26,15 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
   const bool up = s.upstream_mode != 0;
   const double ul = s.ul, xt = s.xt;
 
-  const double psa = P2(f.psa, j, i), psb = P2(f.psb, j, i);
-  const double rpsa_c = P2(f.rpsa, j, i), rpsa_jm = P2(f.rpsa, j - 1, i), rpsa_jp = P2(f.rpsa, j + 1, i),
-               rpsa_im = P2(f.rpsa, j, i - 1), rpsa_ip = P2(f.rpsa, j, i + 1);
-  const double rpsb_c = P2(f.rpsb, j, i), rpsb_jm = P2(f.rpsb, j - 1, i), rpsb_jp = P2(f.rpsb, j + 1, i),
-               rpsb_im = P2(f.rpsb, j, i - 1), rpsb_ip = P2(f.rpsb, j, i + 1);
-  const double xmsf = P2(f.xmsf, j, i);
-  const double m00 = P2(f.msfd, j, i), m01 = P2(f.msfd, j, i + 1), m10 = P2(f.msfd, j + 1, i), m11 = P2(f.msfd, j + 1, i + 1);
-  const double ex = P2(f.ex, j, i), crx = P2(f.crx, j, i), cry = P2(f.cry, j, i);
-  const int ib = (s.iboudy == 1 || s.iboudy == 5) ? P2(f.zone_c, j, i) : 0;
+  const double psa = L2(f.psa, j, i), psb = L2(f.psb, j, i);
+  const double rpsa_c = L2(f.rpsa, j, i), rpsa_jm = L2(f.rpsa, j - 1, i), rpsa_jp = L2(f.rpsa, j + 1, i),
+               rpsa_im = L2(f.rpsa, j, i - 1), rpsa_ip = L2(f.rpsa, j, i + 1);
+  const double rpsb_c = L2(f.rpsb, j, i), rpsb_jm = L2(f.rpsb, j - 1, i), rpsb_jp = L2(f.rpsb, j + 1, i),
+               rpsb_im = L2(f.rpsb, j, i - 1), rpsb_ip = L2(f.rpsb, j, i + 1);
+  const double xmsf = L2(f.xmsf, j, i);
+  const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i), m11 = L2(f.msfd, j + 1, i + 1);
+  const double ex = L2(f.ex, j, i), crx = L2(f.crx, j, i), cry = L2(f.cry, j, i);
+  const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_c, j, i) : 0;
   const bool dint = diff_interior(g, j, i, false);
   const int nring = ring_count(g, j, i, false);
 
@@ -46,15 +46,15 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
   double fx_pp_k = 0.0;    // vertical pp flux at full level k
   double fxw_m = 0.0;      // vertical w flux of loop index k-1
   double xkc_m = 0.0;      // raw xkc(k-1)
-  double aw_k = P3(f.aw, j, i, 1);
+  double aw_k = L3(f.aw, j, i, 1);
 
   for (int k = 1; k <= kzp1; ++k) {
     const bool half = (k <= kz);  // a half level k exists (pp, T, u, v live there)
     double uavg1 = 0, uavg2 = 0, vavg1 = 0, vavg2 = 0, ucc = 0, vcc = 0, f1 = 0, f2 = 0;
     double cr = 0, xkc_raw = 0;
     if (half) {
-      const double u00 = P3(f.au, j, i, k), u01 = P3(f.au, j, i + 1, k), u10 = P3(f.au, j + 1, i, k), u11 = P3(f.au, j + 1, i + 1, k);
-      const double v00 = P3(f.av, j, i, k), v01 = P3(f.av, j, i + 1, k), v10 = P3(f.av, j + 1, i, k), v11 = P3(f.av, j + 1, i + 1, k);
+      const double u00 = L3(f.au, j, i, k), u01 = L3(f.au, j, i + 1, k), u10 = L3(f.au, j + 1, i, k), u11 = L3(f.au, j + 1, i + 1, k);
+      const double v00 = L3(f.av, j, i, k), v01 = L3(f.av, j, i + 1, k), v10 = L3(f.av, j + 1, i, k), v11 = L3(f.av, j + 1, i + 1, k);
       const double ua00 = u00 * m00, ua01 = u01 * m01, ua10 = u10 * m10, ua11 = u11 * m11;
       const double va00 = v00 * m00, va01 = v01 * m01, va10 = v10 * m10, va11 = v11 * m11;
       uavg1 = ua01 + ua00; uavg2 = ua11 + ua10;
@@ -64,35 +64,35 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
       // adiabatic's ucc/vcc are sums of the COUPLED winds (atmx%uc), :1630-1638
       ucc = (u00 + u01 + u10 + u11);
       vcc = (v00 + v01 + v10 + v11);
-      cr = P3(f.cr, j, i, k);
-      xkc_raw = P3(f.xkc, j, i, k);
+      cr = L3(f.cr, j, i, k);
+      xkc_raw = L3(f.xkc, j, i, k);
     }
     const int kk = half ? k : kz;  // min(k,kz)
     double xf = 0.0, xg = 0.0;
     if (ib > 0) { xf = f.hefc[ib + s.nspgx * (kk - 1)]; xg = f.hegc[ib + s.nspgx * (kk - 1)]; }
-    const double qdot_k = P3(f.qdot, j, i, k);
-    const double qdot_n = half ? P3(f.qdot, j, i, k + 1) : 0.0;
+    const double qdot_k = L3(f.qdot, j, i, k);
+    const double qdot_n = half ? L3(f.qdot, j, i, k + 1) : 0.0;
 
     // =================== pressure perturbation (half level k) ===================
     double app_c = 0.0;
     if (half) {
-      app_c = P3(f.app, j, i, k);
-      const double p_c = app_c * rpsa_c, p_jm = P3(f.app, j - 1, i, k) * rpsa_jm, p_jp = P3(f.app, j + 1, i, k) * rpsa_jp,
-                   p_im = P3(f.app, j, i - 1, k) * rpsa_im, p_ip = P3(f.app, j, i + 1, k) * rpsa_ip;
+      app_c = L3(f.app, j, i, k);
+      const double p_c = app_c * rpsa_c, p_jm = L3(f.app, j - 1, i, k) * rpsa_jm, p_jp = L3(f.app, j + 1, i, k) * rpsa_jp,
+                   p_im = L3(f.app, j, i - 1, k) * rpsa_im, p_ip = L3(f.app, j, i + 1, k) * rpsa_ip;
       double ten = hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, p_c, p_jm, p_jp, p_im, p_ip);
       const double xdsk = f.xds[k];
       if (k >= 2) ten = ten + fx_pp_k * xdsk;
       double fx_n = 0.0;
       if (k < kz) {
-        fx_n = qdot_n * (f.twt1[k + 1] * P3(f.app, j, i, k + 1) + f.twt2[k + 1] * app_c);
+        fx_n = qdot_n * (f.twt1[k + 1] * L3(f.app, j, i, k + 1) + f.twt2[k + 1] * app_c);
         ten = ten - fx_n * xdsk;
       }
       fx_pp_k = fx_n;
       ten = ten + p_c * cr;
-      const double b_c = P3(f.bpp, j, i, k);
-      const double b_jm = P3(f.bpp, j - 1, i, k), b_jp = P3(f.bpp, j + 1, i, k), b_im = P3(f.bpp, j, i - 1, k), b_ip = P3(f.bpp, j, i + 1, k);
+      const double b_c = L3(f.bpp, j, i, k);
+      const double b_jm = L3(f.bpp, j - 1, i, k), b_jp = L3(f.bpp, j + 1, i, k), b_im = L3(f.bpp, j, i - 1, k), b_ip = L3(f.bpp, j, i + 1, k);
       if (ib > 0) {
-#define FG(jj, ii, bval) ((P3(f.xpb0, jj, ii, k) + xt * P3(f.xpbt, jj, ii, k)) - (bval))
+#define FG(jj, ii, bval) ((L3(f.xpb0, jj, ii, k) + xt * L3(f.xpbt, jj, ii, k)) - (bval))
         const double fls0 = FG(j, i, b_c), fls1 = FG(j - 1, i, b_jm), fls2 = FG(j + 1, i, b_jp), fls3 = FG(j, i - 1, b_im), fls4 = FG(j, i + 1, b_ip);
 #undef FG
         ten = ten + xf * fls0 - xg * (fls1 + fls2 + fls3 + fls4 - 4.0 * fls0);
@@ -101,14 +101,14 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
         const double xkc = xkc_raw * s.rdxsq * psb;
         const double d_c = b_c * rpsb_c, d_jm = b_jm * rpsb_jm, d_jp = b_jp * rpsb_jp, d_im = b_im * rpsb_im, d_ip = b_ip * rpsb_ip;
         if (dint) {
-          const double d_jp2 = P3(f.bpp, j + 2, i, k) * P2(f.rpsb, j + 2, i), d_jm2 = P3(f.bpp, j - 2, i, k) * P2(f.rpsb, j - 2, i);
-          const double d_ip2 = P3(f.bpp, j, i + 2, k) * P2(f.rpsb, j, i + 2), d_im2 = P3(f.bpp, j, i - 2, k) * P2(f.rpsb, j, i - 2);
+          const double d_jp2 = L3(f.bpp, j + 2, i, k) * L2(f.rpsb, j + 2, i), d_jm2 = L3(f.bpp, j - 2, i, k) * L2(f.rpsb, j - 2, i);
+          const double d_ip2 = L3(f.bpp, j, i + 2, k) * L2(f.rpsb, j, i + 2), d_im2 = L3(f.bpp, j, i - 2, k) * L2(f.rpsb, j, i - 2);
           ten = ten - xkc * (1.0 * (d_jp2 + d_jm2 + d_ip2 + d_im2) + (-4.0) * (d_jp + d_jm + d_ip + d_im) + 12.0 * (d_c));
         }
         for (int r = 0; r < nring; ++r) ten = ten + xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * (d_c));
       }
       if (s.ifrayd == 1 && k <= s.kt_ray)
-        ten = ten + P3(f.tau_c, j, i, k) * ((P3(f.xpb0, j, i, k) + xt * P3(f.xpbt, j, i, k)) - b_c);
+        ten = ten + L3(f.tau_c, j, i, k) * ((L3(f.xpb0, j, i, k) + xt * L3(f.xpbt, j, i, k)) - b_c);
       P3(f.ppten, j, i, k) = (ten * rpsa_c) * s.dts;
     }
 
@@ -117,16 +117,16 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
       // decoupled state needed by the buoyancy term at half level k
       double axpr = 0, rho0 = 0, rho1 = 0, qc = 0;
       if (half) {
-        const double t = P3(f.at, j, i, k) * rpsa_c;
-        const double qv = fmax(P3(f.aqv, j, i, k) * rpsa_c, minqq);
+        const double t = L3(f.at, j, i, k) * rpsa_c;
+        const double qv = fmax(L3(f.aqv, j, i, k) * rpsa_c, minqq);
         const double tv = t * (1.0 + ep1 * qv);
         const double pp = app_c * rpsa_c;
-        rho0 = P3(f.rho0, j, i, k);
-        rho1 = P3(f.rho1, j, i, k);
-        axpr = (tv - P3(f.t0, j, i, k) - pp / (cpd * rho0)) / t;
-        qc = fmax(P3(f.aqc, j, i, k) * rpsa_c, 0.0);
+        rho0 = L3(f.rho0, j, i, k);
+        rho1 = L3(f.rho1, j, i, k);
+        axpr = (tv - L3(f.t0, j, i, k) - pp / (cpd * rho0)) / t;
+        qc = fmax(L3(f.aqc, j, i, k) * rpsa_c, 0.0);
       }
-      const double aw_n = half ? P3(f.aw, j, i, k + 1) : 0.0;
+      const double aw_n = half ? L3(f.aw, j, i, k + 1) : 0.0;
       double ten = 0.0;
       const double w_c = aw_k * rpsa_c;
       if (k >= 2 && k <= kz) {
@@ -135,8 +135,8 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
         const double uaz2 = (t1 * uavg2 + t2 * uavg2_m);
         const double vaz1 = (t1 * vavg1 + t2 * vavg1_m);
         const double vaz2 = (t1 * vavg2 + t2 * vavg2_m);
-        const double w_jm = P3(f.aw, j - 1, i, k) * rpsa_jm, w_jp = P3(f.aw, j + 1, i, k) * rpsa_jp,
-                     w_im = P3(f.aw, j, i - 1, k) * rpsa_im, w_ip = P3(f.aw, j, i + 1, k) * rpsa_ip;
+        const double w_jm = L3(f.aw, j - 1, i, k) * rpsa_jm, w_jp = L3(f.aw, j + 1, i, k) * rpsa_jp,
+                     w_im = L3(f.aw, j, i - 1, k) * rpsa_im, w_ip = L3(f.aw, j, i + 1, k) * rpsa_ip;
         double fx1, fx2, fy1, fy2;
         if (up) {
           fx1 = (1.0 + f1) * w_jm + (1.0 - f1) * w_c;
@@ -167,10 +167,10 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
               (uaq * uaq + vaq * vaq) * rearthrad * rpsa_c + w_c * (t1 * cr + t2 * cr_m);
         if (s.ipptls > 0) ten = ten - egrav * psa * (t2 * qc_m + t1 * qc);
       }
-      const double b_c = P3(f.bw, j, i, k);
-      const double b_jm = P3(f.bw, j - 1, i, k), b_jp = P3(f.bw, j + 1, i, k), b_im = P3(f.bw, j, i - 1, k), b_ip = P3(f.bw, j, i + 1, k);
+      const double b_c = L3(f.bw, j, i, k);
+      const double b_jm = L3(f.bw, j - 1, i, k), b_jp = L3(f.bw, j + 1, i, k), b_im = L3(f.bw, j, i - 1, k), b_ip = L3(f.bw, j, i + 1, k);
       if (ib > 0) {
-#define FG(jj, ii, bval) ((P3(f.xwb0, jj, ii, k) + xt * P3(f.xwbt, jj, ii, k)) - (bval))
+#define FG(jj, ii, bval) ((L3(f.xwb0, jj, ii, k) + xt * L3(f.xwbt, jj, ii, k)) - (bval))
         const double fls0 = FG(j, i, b_c), fls1 = FG(j - 1, i, b_jm), fls2 = FG(j + 1, i, b_jp), fls3 = FG(j, i - 1, b_im), fls4 = FG(j, i + 1, b_ip);
 #undef FG
         ten = ten + xf * fls0 - xg * (fls1 + fls2 + fls3 + fls4 - 4.0 * fls0);
@@ -180,13 +180,13 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
         const double xkcf = ((k == 1) ? xkc_raw : xkc_m) * s.rdxsq * psb;
         const double d_c = b_c * rpsb_c, d_jm = b_jm * rpsb_jm, d_jp = b_jp * rpsb_jp, d_im = b_im * rpsb_im, d_ip = b_ip * rpsb_ip;
         if (dint) {
-          const double d_jp2 = P3(f.bw, j + 2, i, k) * P2(f.rpsb, j + 2, i), d_jm2 = P3(f.bw, j - 2, i, k) * P2(f.rpsb, j - 2, i);
-          const double d_ip2 = P3(f.bw, j, i + 2, k) * P2(f.rpsb, j, i + 2), d_im2 = P3(f.bw, j, i - 2, k) * P2(f.rpsb, j, i - 2);
+          const double d_jp2 = L3(f.bw, j + 2, i, k) * L2(f.rpsb, j + 2, i), d_jm2 = L3(f.bw, j - 2, i, k) * L2(f.rpsb, j - 2, i);
+          const double d_ip2 = L3(f.bw, j, i + 2, k) * L2(f.rpsb, j, i + 2), d_im2 = L3(f.bw, j, i - 2, k) * L2(f.rpsb, j, i - 2);
           ten = ten - 1.0 * xkcf * (1.0 * (d_jp2 + d_jm2 + d_ip2 + d_im2) + (-4.0) * (d_jp + d_jm + d_ip + d_im) + 12.0 * (d_c));
         }
         for (int r = 0; r < nring; ++r) ten = ten + 1.0 * xkcf * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * (d_c));
       }
-      if (s.ifrayd == 1 && k <= s.ktf_ray) ten = ten + P3(f.tau_f, j, i, k) * (0.0 - b_c);
+      if (s.ifrayd == 1 && k <= s.ktf_ray) ten = ten + L3(f.tau_f, j, i, k) * (0.0 - b_c);
       P3(f.wten, j, i, k) = (ten * rpsa_c) * s.dts;
 
       // shift the carried state

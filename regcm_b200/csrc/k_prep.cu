@@ -30,20 +30,20 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
   if (j > g.jce2 + g.gr || i > g.ice2 + g.gt) return;
   const int kz = g.kz;
 
-  const double rpsa = P2(f.rpsa, j, i), psa = P2(f.psa, j, i), ps0 = P2(f.ps0, j, i);
-  const double msfx = P2(f.msfx, j, i);
+  const double rpsa = L2(f.rpsa, j, i), psa = L2(f.psa, j, i), ps0 = L2(f.ps0, j, i);
+  const double msfx = L2(f.msfx, j, i);
   const double dummy = 1.0 / (s.dx2 * msfx * msfx);
-  const double dpsdxm = P2(f.dpsdxm, j, i), dpsdym = P2(f.dpsdym, j, i);
+  const double dpsdxm = L2(f.dpsdxm, j, i), dpsdym = L2(f.dpsdym, j, i);
   // dots around the cross point: 00=(j,i) 01=(j,i+1) 10=(j+1,i) 11=(j+1,i+1)
-  const double m00 = P2(f.msfd, j, i), m01 = P2(f.msfd, j, i + 1), m10 = P2(f.msfd, j + 1, i),
-               m11 = P2(f.msfd, j + 1, i + 1);
-  const double r00 = P2(f.rpsda, j, i), r01 = P2(f.rpsda, j, i + 1), r10 = P2(f.rpsda, j + 1, i),
-               r11 = P2(f.rpsda, j + 1, i + 1);
+  const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i),
+               m11 = L2(f.msfd, j + 1, i + 1);
+  const double r00 = L2(f.rpsda, j, i), r01 = L2(f.rpsda, j, i + 1), r10 = L2(f.rpsda, j + 1, i),
+               r11 = L2(f.rpsda, j + 1, i + 1);
 
-  double u00 = P3(f.au, j, i, 1), u01 = P3(f.au, j, i + 1, 1), u10 = P3(f.au, j + 1, i, 1),
-         u11 = P3(f.au, j + 1, i + 1, 1);
-  double v00 = P3(f.av, j, i, 1), v01 = P3(f.av, j, i + 1, 1), v10 = P3(f.av, j + 1, i, 1),
-         v11 = P3(f.av, j + 1, i + 1, 1);
+  double u00 = L3(f.au, j, i, 1), u01 = L3(f.au, j, i + 1, 1), u10 = L3(f.au, j + 1, i, 1),
+         u11 = L3(f.au, j + 1, i + 1, 1);
+  double v00 = L3(f.av, j, i, 1), v01 = L3(f.av, j, i + 1, 1), v10 = L3(f.av, j + 1, i, 1),
+         v11 = L3(f.av, j + 1, i + 1, 1);
   // ucc = sum of umd = (u*rpsda)*msfd over the 4 dots, reference order
   double ucc_k = (u00 * r00) * m00 + (u01 * r01) * m01 + (u10 * r10) * m10 + (u11 * r11) * m11;
   double vcc_k = (v00 * r00) * m00 + (v01 * r01) * m01 + (v10 * r10) * m10 + (v11 * r11) * m11;
@@ -52,11 +52,11 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
 
   for (int k = 1; k <= kz; ++k) {
     // ---- decouple + theta ----
-    const double t = P3(f.at, j, i, k) * rpsa;
-    const double qv = fmax(P3(f.aqv, j, i, k) * rpsa, minqq);
+    const double t = L3(f.at, j, i, k) * rpsa;
+    const double qv = fmax(L3(f.aqv, j, i, k) * rpsa, minqq);
     const double tv = t * (1.0 + ep1 * qv);
-    const double pp = P3(f.app, j, i, k) * rpsa;
-    const double pr1 = P3(f.pr0, j, i, k) + pp;
+    const double pp = L3(f.app, j, i, k) * rpsa;
+    const double pr1 = L3(f.pr0, j, i, k) + pp;
     P3(f.pr1, j, i, k) = pr1;
     P3(f.rho1, j, i, k) = pr1 / (rgas * tv);
     P3(f.th, j, i, k) = t * pow(p00 / pr1, rovcp);
@@ -65,13 +65,13 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
     double n00 = 0, n01 = 0, n10 = 0, n11 = 0, w00 = 0, w01 = 0, w10 = 0, w11 = 0;
     if (k < kz) {
       const int kn = k + 1;
-      n00 = P3(f.au, j, i, kn); n01 = P3(f.au, j, i + 1, kn); n10 = P3(f.au, j + 1, i, kn); n11 = P3(f.au, j + 1, i + 1, kn);
-      w00 = P3(f.av, j, i, kn); w01 = P3(f.av, j, i + 1, kn); w10 = P3(f.av, j + 1, i, kn); w11 = P3(f.av, j + 1, i + 1, kn);
+      n00 = L3(f.au, j, i, kn); n01 = L3(f.au, j, i + 1, kn); n10 = L3(f.au, j + 1, i, kn); n11 = L3(f.au, j + 1, i + 1, kn);
+      w00 = L3(f.av, j, i, kn); w01 = L3(f.av, j, i + 1, kn); w10 = L3(f.av, j + 1, i, kn); w11 = L3(f.av, j + 1, i + 1, kn);
       ucc_n = (n00 * r00) * m00 + (n01 * r01) * m01 + (n10 * r10) * m10 + (n11 * r11) * m11;
       vcc_n = (w00 * r00) * m00 + (w01 * r01) * m01 + (w10 * r10) * m10 + (w11 * r11) * m11;
-      const double w = P3(f.aw, j, i, kn) * rpsa;
+      const double w = L3(f.aw, j, i, kn) * rpsa;
       const double t1 = f.twt1[kn], t2 = f.twt2[kn];
-      qd_n = -P3(f.rhof0, j, i, kn) * egrav * w / ps0 -
+      qd_n = -L3(f.rhof0, j, i, kn) * egrav * w / ps0 -
              f.sigma[kn] * (dpsdxm * (t1 * ucc_n + t2 * ucc_k) + dpsdym * (t1 * vcc_n + t2 * vcc_k));
     }
     P3(f.qdot, j, i, k + 1) = qd_n;
@@ -93,20 +93,20 @@ k_xkc(const Geom g, const Fields f, const StepScalars s) {
   const int k = 1 + blockIdx.z;
   if (j > g.jce2 + g.gr || i > g.ice2 + g.gt) return;
   // ubd3d = atm2%u * (1/psdotb), wb3d = atm2%w * (1/psb)  (Main/mod_slice.F90:169-263)
-  const double r00 = 1.0 / P2(f.psdotb, j, i), r01 = 1.0 / P2(f.psdotb, j, i + 1),
-               r10 = 1.0 / P2(f.psdotb, j + 1, i), r11 = 1.0 / P2(f.psdotb, j + 1, i + 1);
-  const double rpsb = 1.0 / P2(f.psb, j, i);
-  const double u00 = P3(f.bu, j, i, k) * r00, u01 = P3(f.bu, j, i + 1, k) * r01, u10 = P3(f.bu, j + 1, i, k) * r10,
-               u11 = P3(f.bu, j + 1, i + 1, k) * r11;
-  const double v00 = P3(f.bv, j, i, k) * r00, v01 = P3(f.bv, j, i + 1, k) * r01, v10 = P3(f.bv, j + 1, i, k) * r10,
-               v11 = P3(f.bv, j + 1, i + 1, k) * r11;
+  const double r00 = 1.0 / L2(f.psdotb, j, i), r01 = 1.0 / L2(f.psdotb, j, i + 1),
+               r10 = 1.0 / L2(f.psdotb, j + 1, i), r11 = 1.0 / L2(f.psdotb, j + 1, i + 1);
+  const double rpsb = 1.0 / L2(f.psb, j, i);
+  const double u00 = L3(f.bu, j, i, k) * r00, u01 = L3(f.bu, j, i + 1, k) * r01, u10 = L3(f.bu, j + 1, i, k) * r10,
+               u11 = L3(f.bu, j + 1, i + 1, k) * r11;
+  const double v00 = L3(f.bv, j, i, k) * r00, v01 = L3(f.bv, j, i + 1, k) * r01, v10 = L3(f.bv, j + 1, i, k) * r10,
+               v11 = L3(f.bv, j + 1, i + 1, k) * r11;
   const double dudx = u10 + u11 - u00 - u01;
   const double dvdx = v10 + v11 - v00 - v01;
   const double dudy = u01 + u11 - u00 - u10;
   const double dvdy = v01 + v11 - v00 - v10;
-  const double dwdz = P3(f.bw, j, i, k) * rpsb - P3(f.bw, j, i, k + 1) * rpsb;
+  const double dwdz = L3(f.bw, j, i, k) * rpsb - L3(f.bw, j, i, k + 1) * rpsb;
   const double duv = sqrt(fmax((dudx - dvdy) * (dudx - dvdy) + (dvdx + dudy) * (dvdx + dudy) - dwdz * dwdz, 0.0));
-  P3(f.xkc, j, i, k) = fmin((P2(f.hgfact, j, i) + s.dydc * duv), s.xkhmax);
+  P3(f.xkc, j, i, k) = fmin((L2(f.hgfact, j, i) + s.dydc * duv), s.xkhmax);
 }
 
 void launch_prep(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {

@@ -30,25 +30,25 @@ k_snd_init(const Geom g, const Fields f, const StepScalars s) {
   const int i = (g.ide1 - g.gb) + blockIdx.y * 8 + threadIdx.y;
   if (j > g.jde2 + g.gr || i > g.ide2 + g.gt) return;
   const int kz = g.kz;
-  const double psdotb = P2(f.psdotb, j, i);
+  const double psdotb = L2(f.psdotb, j, i);
   for (int k = 1; k <= kz; ++k) {
-    P3(f.cu, j, i, k) = P3(f.bu, j, i, k) / psdotb;
-    P3(f.cv, j, i, k) = P3(f.bv, j, i, k) / psdotb;
+    P3(f.cu, j, i, k) = L3(f.bu, j, i, k) / psdotb;
+    P3(f.cv, j, i, k) = L3(f.bv, j, i, k) / psdotb;
   }
   if (j <= g.jce2 + g.gr && i <= g.ice2 + g.gt) {
-    const double rpsb = 1.0 / P2(f.psb, j, i);
-    double pm = 0.0, pc = P3(f.bpp, j, i, 1) * rpsb, pn;
+    const double rpsb = 1.0 / L2(f.psb, j, i);
+    double pm = 0.0, pc = L3(f.bpp, j, i, 1) * rpsb, pn;
     for (int k = 1; k <= kz; ++k) {
-      pn = (k < kz) ? P3(f.bpp, j, i, k + 1) * rpsb : 0.0;
+      pn = (k < kz) ? L3(f.bpp, j, i, k + 1) * rpsb : 0.0;
       P3(f.cpp, j, i, k) = pc;
       P3(f.cppd, j, i, k) = pc;
       const int km1 = max(1, k - 1), kp1 = min(kz, k + 1);
       const double a = (k == 1) ? pc : pm, b = (k == kz) ? pc : pn;
-      P3(f.ct, j, i, k) = (a - b) / (P3(f.pr0, j, i, km1) - P3(f.pr0, j, i, kp1));
-      P3(f.cw, j, i, k) = P3(f.bw, j, i, k) * rpsb;
+      P3(f.ct, j, i, k) = (a - b) / (L3(f.pr0, j, i, km1) - L3(f.pr0, j, i, kp1));
+      P3(f.cw, j, i, k) = L3(f.bw, j, i, k) * rpsb;
       pm = pc; pc = pn;
     }
-    P3(f.cw, j, i, kz + 1) = P3(f.bw, j, i, kz + 1) * rpsb;
+    P3(f.cw, j, i, kz + 1) = L3(f.bw, j, i, kz + 1) * rpsb;
   }
 }
 
@@ -61,19 +61,19 @@ k_snd_uv(const Geom g, const Fields f, const StepScalars s) {
   const int i = g.idi1 + blockIdx.y * 4 + threadIdx.y;
   const int k = 1 + blockIdx.z * 2 + threadIdx.z;
   if (j > g.jdi2 || i > g.idi2 || k > g.kz) return;
-  const double rho = 0.25 * (P3(f.rho1, j, i, k) + P3(f.rho1, j - 1, i, k) + P3(f.rho1, j, i - 1, k) + P3(f.rho1, j - 1, i - 1, k));
-  const double dppdp0 = 0.25 * (P3(f.ct, j, i, k) + P3(f.ct, j - 1, i, k) + P3(f.ct, j, i - 1, k) + P3(f.ct, j - 1, i - 1, k));
-  const double chh = 0.5 * s.dts / (rho * s.dx) / P2(f.msfd, j, i);
-  const double p11 = P3(f.cppd, j, i, k), p01 = P3(f.cppd, j - 1, i, k), p10 = P3(f.cppd, j, i - 1, k), p00_ = P3(f.cppd, j - 1, i - 1, k);
+  const double rho = 0.25 * (L3(f.rho1, j, i, k) + L3(f.rho1, j - 1, i, k) + L3(f.rho1, j, i - 1, k) + L3(f.rho1, j - 1, i - 1, k));
+  const double dppdp0 = 0.25 * (L3(f.ct, j, i, k) + L3(f.ct, j - 1, i, k) + L3(f.ct, j, i - 1, k) + L3(f.ct, j - 1, i - 1, k));
+  const double chh = 0.5 * s.dts / (rho * s.dx) / L2(f.msfd, j, i);
+  const double p11 = L3(f.cppd, j, i, k), p01 = L3(f.cppd, j - 1, i, k), p10 = L3(f.cppd, j, i - 1, k), p00_ = L3(f.cppd, j - 1, i - 1, k);
   // atm0%dprddx/dprddy (Main/mod_params.F90:2680-2693) recomputed from pr0
-  const double r11 = P3(f.pr0, j, i, k), r01 = P3(f.pr0, j - 1, i, k), r10 = P3(f.pr0, j, i - 1, k), r00 = P3(f.pr0, j - 1, i - 1, k);
+  const double r11 = L3(f.pr0, j, i, k), r01 = L3(f.pr0, j - 1, i, k), r10 = L3(f.pr0, j, i - 1, k), r00 = L3(f.pr0, j - 1, i - 1, k);
   const double dprddx = r11 - r01 + r10 - r00;
   const double dprddy = r11 - r10 + r01 - r00;
   double u = P3(f.cu, j, i, k), v = P3(f.cv, j, i, k);
   u = u - chh * (p11 - p01 + p10 - p00_ - dprddx * dppdp0);
   v = v - chh * (p11 - p10 + p01 - p00_ - dprddy * dppdp0);
-  P3(f.cu, j, i, k) = u + P3(f.uten, j, i, k);
-  P3(f.cv, j, i, k) = v + P3(f.vten, j, i, k);
+  P3(f.cu, j, i, k) = u + L3(f.uten, j, i, k);
+  P3(f.cv, j, i, k) = v + L3(f.vten, j, i, k);
 }
 
 // ---------------------------------------------------------------------------
@@ -93,54 +93,54 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
   const int kz = g.kz, kzp1 = g.kzp1;
   const double dts = s.dts, dx = s.dx, xgamma = s.xgamma, bp = s.bp, bm = s.bm, bpxbp = s.bpxbp, bpxbm = s.bpxbm;
 
-  const double ps0 = P2(f.ps0, j, i), msfx = P2(f.msfx, j, i);
-  const double rpsb = 1.0 / P2(f.psb, j, i);
-  const double m00 = P2(f.msfd, j, i), m01 = P2(f.msfd, j, i + 1), m10 = P2(f.msfd, j + 1, i), m11 = P2(f.msfd, j + 1, i + 1);
+  const double ps0 = L2(f.ps0, j, i), msfx = L2(f.msfx, j, i);
+  const double rpsb = 1.0 / L2(f.psb, j, i);
+  const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i), m11 = L2(f.msfd, j + 1, i + 1);
 
   // winds at the four surrounding dots: [0]=(j,i) [1]=(j+1,i) [2]=(j,i+1) [3]=(j+1,i+1)
   double up_[4], uc_[4], um_[4], vp_[4], vc_[4], vm_[4];  // levels m+1, m, m-1 of the record being built
 #define LOADUV(U, V, kk)                                                            \
-  U[0] = P3(f.cu, j, i, kk); U[1] = P3(f.cu, j + 1, i, kk); U[2] = P3(f.cu, j, i + 1, kk); U[3] = P3(f.cu, j + 1, i + 1, kk); \
-  V[0] = P3(f.cv, j, i, kk); V[1] = P3(f.cv, j + 1, i, kk); V[2] = P3(f.cv, j, i + 1, kk); V[3] = P3(f.cv, j + 1, i + 1, kk);
+  U[0] = L3(f.cu, j, i, kk); U[1] = L3(f.cu, j + 1, i, kk); U[2] = L3(f.cu, j, i + 1, kk); U[3] = L3(f.cu, j + 1, i + 1, kk); \
+  V[0] = L3(f.cv, j, i, kk); V[1] = L3(f.cv, j + 1, i, kk); V[2] = L3(f.cv, j, i + 1, kk); V[3] = L3(f.cv, j + 1, i + 1, kk);
 
   // build the k-local record of level m; needs u,v at m+1 (or kz), m, m-1 (or 1)
   auto build = [&](int m, SndLevel& L) {
-    const double pr1 = P3(f.pr1, j, i, m), rho0 = P3(f.rho0, j, i, m), pr0 = P3(f.pr0, j, i, m);
-    L.tk = (0.5 * ps0 * P3(f.t0, j, i, m)) / (xgamma * pr0 * P3(f.nbt, j, i, m) * rpsb);
+    const double pr1 = L3(f.pr1, j, i, m), rho0 = L3(f.rho0, j, i, m), pr0 = L3(f.pr0, j, i, m);
+    L.tk = (0.5 * ps0 * L3(f.t0, j, i, m)) / (xgamma * pr0 * L3(f.nbt, j, i, m) * rpsb);
     L.cc = xgamma * pr1 * dts / (dx * msfx);
     L.cdd = xgamma * pr1 * rho0 * egrav * dts / (ps0 * f.dsigma[m]);
     L.cj = 0.5 * rho0 * egrav * dts;
     double pxup, pyvp;
     if (m == 1) {
-      const double den = (pr0 - P3(f.pr0, j, i, 2));
-      pxup = 0.0625 * (P3(f.pr0, j + 1, i, 1) - P3(f.pr0, j - 1, i, 1)) *
+      const double den = (pr0 - L3(f.pr0, j, i, 2));
+      pxup = 0.0625 * (L3(f.pr0, j + 1, i, 1) - L3(f.pr0, j - 1, i, 1)) *
              (uc_[0] + uc_[1] + uc_[2] + uc_[3] - up_[0] - up_[1] - up_[2] - up_[3]) / den;
-      pyvp = 0.0625 * (P3(f.pr0, j, i + 1, 1) - P3(f.pr0, j, i - 1, 1)) *
+      pyvp = 0.0625 * (L3(f.pr0, j, i + 1, 1) - L3(f.pr0, j, i - 1, 1)) *
              (vc_[0] + vc_[1] + vc_[2] + vc_[3] - vp_[0] - vp_[1] - vp_[2] - vp_[3]) / den;
     } else {
       const int kp1 = min(m + 1, kz), km1 = m - 1;
-      const double den = (P3(f.pr0, j, i, km1) - P3(f.pr0, j, i, kp1));
+      const double den = (L3(f.pr0, j, i, km1) - L3(f.pr0, j, i, kp1));
       // at m = kz the "kp1" level is kz itself: up_ then aliases uc_ (set by caller)
-      pyvp = 0.125 * (P3(f.pr0, j, i + 1, m) - P3(f.pr0, j, i - 1, m)) *
+      pyvp = 0.125 * (L3(f.pr0, j, i + 1, m) - L3(f.pr0, j, i - 1, m)) *
              (vm_[0] + vm_[1] + vm_[2] + vm_[3] - vp_[0] - vp_[1] - vp_[2] - vp_[3]) / den;
-      pxup = 0.125 * (P3(f.pr0, j + 1, i, m) - P3(f.pr0, j - 1, i, m)) *
+      pxup = 0.125 * (L3(f.pr0, j + 1, i, m) - L3(f.pr0, j - 1, i, m)) *
              (um_[0] + um_[1] + um_[2] + um_[3] - up_[0] - up_[1] - up_[2] - up_[3]) / den;
       if (m == kz) { pyvp = pyvp * 0.5; pxup = pxup * 0.5; }
     }
-    L.ptend = P3(f.ppten, j, i, m) -
+    L.ptend = L3(f.ppten, j, i, m) -
               0.5 * L.cc * ((vc_[2] * m01 - vc_[0] * m00 + vc_[3] * m11 - vc_[1] * m10 +
                              uc_[1] * m10 - uc_[0] * m00 + uc_[3] * m11 - uc_[2] * m01) / msfx -
                             2.0 * (pyvp + pxup));
-    L.pp = P3(f.cpp, j, i, m);
-    L.wo = P3(f.cw, j, i, m);
+    L.pp = L3(f.cpp, j, i, m);
+    L.wo = L3(f.cw, j, i, m);
   };
 
   // ---- bottom boundary condition (:323-334) ----
   LOADUV(uc_, vc_, kz);
-  const double wo_bot = P3(f.cw, j, i, kzp1);
+  const double wo_bot = L3(f.cw, j, i, kzp1);
   const double w_bot = 0.5 * 0.25 * regrav *
-                       ((vc_[2] + vc_[0] + vc_[3] + vc_[1]) * (P2(f.ht, j, i + 1) - P2(f.ht, j, i - 1)) +
-                        (uc_[2] + uc_[0] + uc_[3] + uc_[1]) * (P2(f.ht, j + 1, i) - P2(f.ht, j - 1, i))) /
+                       ((vc_[2] + vc_[0] + vc_[3] + vc_[1]) * (L2(f.ht, j, i + 1) - L2(f.ht, j, i - 1)) +
+                        (uc_[2] + uc_[0] + uc_[3] + uc_[1]) * (L2(f.ht, j + 1, i) - L2(f.ht, j - 1, i))) /
                        (dx * msfx);
   double e_k = 0.0, f_k = w_bot;
   P3(f.se, j, i, kz) = e_k;
@@ -162,18 +162,18 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
     build(k - 1, Lm);
     // ---- coefficients of level k (:373-401) ----
     const int km1 = k - 1;
-    const double rho0_k = P3(f.rho0, j, i, k), rho0_m = P3(f.rho0, j, i, km1);
-    const double rho1_k = P3(f.rho1, j, i, k), rho1_m = P3(f.rho1, j, i, km1);
+    const double rho0_k = L3(f.rho0, j, i, k), rho0_m = L3(f.rho0, j, i, km1);
+    const double rho1_k = L3(f.rho1, j, i, k), rho1_m = L3(f.rho1, j, i, km1);
     const double dsk = f.dsigma[k], dsm = f.dsigma[km1];
     const double rofac = (dsm * rho0_k + dsk * rho0_m) / (dsm * rho1_k + dsk * rho1_m);
-    const double ca = egrav * dts / (P3(f.pr0, j, i, k) - P3(f.pr0, j, i, km1)) * rofac;
+    const double ca = egrav * dts / (L3(f.pr0, j, i, k) - L3(f.pr0, j, i, km1)) * rofac;
     const double g1 = 1.0 - dsm * Lk.tk;
     const double g2 = 1.0 + dsk * Lm.tk;
     const double c = -ca * (Lm.cdd - Lm.cj) * g2 * bpxbp;
     const double b = 1.0 + ca * (g1 * (Lk.cdd - Lk.cj) + g2 * (Lm.cdd + Lm.cj)) * bpxbp;
     const double aa = -ca * (Lk.cdd + Lk.cj) * g1 * bpxbp;
     // rhs (:440-453): atmc%w(k) still equals wo(k) for k <= kz
-    const double rhs = Lk.wo + P3(f.wten, j, i, k) +
+    const double rhs = Lk.wo + L3(f.wten, j, i, k) +
                        ca * (bpxbm * ((Lm.cdd - Lm.cj) * g2 * Lm.wo -
                                       ((Lm.cdd + Lm.cj) * g2 + (Lk.cdd - Lk.cj) * g1) * Lk.wo +
                                       (Lk.cdd + Lk.cj) * g1 * wo_kp1) +
@@ -231,25 +231,25 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
   if (j > g.jci2 || i > g.ici2) return;
   const int kz = g.kz;
   const double dts = s.dts, xgamma = s.xgamma, bp = s.bp, xkd = s.xkd_snd;
-  const double ps0 = P2(f.ps0, j, i), psb = P2(f.psb, j, i);
+  const double ps0 = L2(f.ps0, j, i), psb = L2(f.psb, j, i);
   const double rpsb = 1.0 / psb;
-  const double dpsdxm = P2(f.dpsdxm, j, i), dpsdym = P2(f.dpsdym, j, i);
+  const double dpsdxm = L2(f.dpsdxm, j, i), dpsdym = L2(f.dpsdym, j, i);
   const bool last = (s.it == s.istep);
 
-  double w_k = P2(f.wpval, j, i);
+  double w_k = L2(f.wpval, j, i);
   P3(f.cw, j, i, 1) = w_k;
   double ucrs_m = 0.0, vcrs_m = 0.0;
   double cfl = 0.0;
   double ppd_m2 = 0.0, ppd_m1 = 0.0;  // damped p' at k-2, k-1 (for ct of level k-1)
   for (int k = 1; k <= kz; ++k) {
-    const double w_n = P3(f.se, j, i, k) * w_k + P3(f.sf, j, i, k);
+    const double w_n = L3(f.se, j, i, k) * w_k + L3(f.sf, j, i, k);
     P3(f.cw, j, i, k + 1) = w_n;
     // ---- CFL diagnostic (:613-633) ----
-    const double ucrs = P3(f.cu, j, i, k) + P3(f.cu, j, i + 1, k) + P3(f.cu, j + 1, i, k) + P3(f.cu, j + 1, i + 1, k);
-    const double vcrs = P3(f.cv, j, i, k) + P3(f.cv, j, i + 1, k) + P3(f.cv, j + 1, i, k) + P3(f.cv, j + 1, i + 1, k);
+    const double ucrs = L3(f.cu, j, i, k) + L3(f.cu, j, i + 1, k) + L3(f.cu, j + 1, i, k) + L3(f.cu, j + 1, i + 1, k);
+    const double vcrs = L3(f.cv, j, i, k) + L3(f.cv, j, i + 1, k) + L3(f.cv, j + 1, i, k) + L3(f.cv, j + 1, i + 1, k);
     if (k >= 2) {
       const double t1 = f.twt1[k], t2 = f.twt2[k];
-      const double sigdot = -P3(f.rhof0, j, i, k) * egrav * w_k / ps0 -
+      const double sigdot = -L3(f.rhof0, j, i, k) * egrav * w_k / ps0 -
                             f.sigma[k] * (dpsdxm * (t1 * ucrs + t2 * ucrs_m) + dpsdym * (t1 * vcrs + t2 * vcrs_m));
       const double check = fabs(sigdot) * s.dt / (f.dsigma[k] + f.dsigma[k - 1]);
       cfl = fmax(check, cfl);
@@ -257,14 +257,14 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
     ucrs_m = ucrs; vcrs_m = vcrs;
     // ---- new pressure and temperature correction (:669-689) ----
     const double ppold = P3(f.cpp, j, i, k);
-    const double pr1 = P3(f.pr1, j, i, k), rho0 = P3(f.rho0, j, i, k);
+    const double pr1 = L3(f.pr1, j, i, k), rho0 = L3(f.rho0, j, i, k);
     const double cddtmp = xgamma * pr1 * rho0 * egrav * dts / (ps0 * f.dsigma[k]);
     const double cjtmp = rho0 * egrav * dts * 0.5;
     const double ppn = P3(f.cppd, j, i, k) + (cjtmp * (w_n + w_k) + cddtmp * (w_n - w_k)) * bp;
-    const double ppten = P3(f.ppten, j, i, k);
+    const double ppten = L3(f.ppten, j, i, k);
     const double pi = ppn - ppold - ppten;
-    const double cpm = cpmf(P3(f.nbqv, j, i, k) * rpsb);
-    const double dpterm = psb * (ppn - ppold) / (cpm * P3(f.rho1, j, i, k));
+    const double cpm = cpmf(L3(f.nbqv, j, i, k) * rpsb);
+    const double dpterm = psb * (ppn - ppold) / (cpm * L3(f.rho1, j, i, k));
     P3(f.nbt, j, i, k) = P3(f.nbt, j, i, k) + s.gnu1 * dpterm;
     P3(f.nat, j, i, k) = P3(f.nat, j, i, k) + dpterm;
     // ---- prepare the next sub-step: divergence damping (:252-256,302-306) and
@@ -278,12 +278,12 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
         const int m = k - 1;  // ct(m) = (ppd(max(m-1,1)) - ppd(m+1)) / (pr0(max(m-1,1)) - pr0(m+1))
         const int mm1 = max(1, m - 1);
         const double a = (m == 1) ? ppd_m1 : ppd_m2;
-        P3(f.ct, j, i, m) = (a - ppd) / (P3(f.pr0, j, i, mm1) - P3(f.pr0, j, i, k));
+        P3(f.ct, j, i, m) = (a - ppd) / (L3(f.pr0, j, i, mm1) - L3(f.pr0, j, i, k));
       }
       if (k == kz) {
         const int km1 = max(1, kz - 1);
         const double a = (kz == 1) ? ppd : ppd_m1;
-        P3(f.ct, j, i, kz) = (a - ppd) / (P3(f.pr0, j, i, km1) - P3(f.pr0, j, i, kz));
+        P3(f.ct, j, i, kz) = (a - ppd) / (L3(f.pr0, j, i, km1) - L3(f.pr0, j, i, kz));
       }
       ppd_m2 = ppd_m1; ppd_m1 = ppd;
     } else {
@@ -311,8 +311,8 @@ k_snd_final(const Geom g, const Fields f, const StepScalars s) {
   if (j > g.jde2 || i > g.ide2 || k > g.kzp1) return;
   const int kz = g.kz;
   if (k <= kz && j >= g.jdi1 && j <= g.jdi2 && i >= g.idi1 && i <= g.idi2) {
-    const double psdotb = P2(f.psdotb, j, i);
-    const double cu = psdotb * P3(f.cu, j, i, k), cv = psdotb * P3(f.cv, j, i, k);
+    const double psdotb = L2(f.psdotb, j, i);
+    const double cu = psdotb * L3(f.cu, j, i, k), cv = psdotb * L3(f.cv, j, i, k);
     const double au = P3(f.au, j, i, k), av = P3(f.av, j, i, k);
     double d = s.gnu1 * (cu + P3(f.bu, j, i, k) - 2.0 * au);
     P3(f.bu, j, i, k) = au + d;
@@ -323,9 +323,9 @@ k_snd_final(const Geom g, const Fields f, const StepScalars s) {
   }
   if (j <= g.jce2 && i <= g.ice2) {
     const bool interior = (j >= g.jci1 && j <= g.jci2 && i >= g.ici1 && i <= g.ici2);
-    const double psb = P2(f.psb, j, i);
+    const double psb = L2(f.psb, j, i);
     if (interior && k <= kz) {
-      const double cp = psb * P3(f.cpp, j, i, k);
+      const double cp = psb * L3(f.cpp, j, i, k);
       const double ap = P3(f.app, j, i, k);
       const double d = s.gnu1 * (cp + P3(f.bpp, j, i, k) - 2.0 * ap);
       P3(f.bpp, j, i, k) = ap + d;
@@ -333,7 +333,7 @@ k_snd_final(const Geom g, const Fields f, const StepScalars s) {
     }
     double aw = P3(f.aw, j, i, k), bw = P3(f.bw, j, i, k);
     if (interior) {
-      double cw = P3(f.cw, j, i, k);
+      double cw = L3(f.cw, j, i, k);
       if (fabs(cw) < dlowval) cw = 0.0;
       cw = psb * cw;
       const double d = s.gnu2 * (cw + bw - 2.0 * aw);

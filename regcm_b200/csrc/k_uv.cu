@@ -31,19 +31,19 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
 #pragma unroll
   for (int a = 0; a < 3; ++a)
 #pragma unroll
-    for (int b = 0; b < 3; ++b) md[a][b] = P2(f.msfd, j + a - 1, i + b - 1);
-  const double rp_c = P2(f.rpsda, j, i), rp_jm = P2(f.rpsda, j - 1, i), rp_jp = P2(f.rpsda, j + 1, i),
-               rp_im = P2(f.rpsda, j, i - 1), rp_ip = P2(f.rpsda, j, i + 1);
-  const double dmsf = P2(f.dmsf, j, i), coriol = P2(f.coriol, j, i), ef = P2(f.ef, j, i);
-  const double ddx = P2(f.ddx, j, i), ddy = P2(f.ddy, j, i), dmdx = P2(f.dmdx, j, i), dmdy = P2(f.dmdy, j, i);
-  const double psdotb = P2(f.psdotb, j, i);
-  const int ib = (s.iboudy == 1 || s.iboudy == 5) ? P2(f.zone_d, j, i) : 0;
+    for (int b = 0; b < 3; ++b) md[a][b] = L2(f.msfd, j + a - 1, i + b - 1);
+  const double rp_c = L2(f.rpsda, j, i), rp_jm = L2(f.rpsda, j - 1, i), rp_jp = L2(f.rpsda, j + 1, i),
+               rp_im = L2(f.rpsda, j, i - 1), rp_ip = L2(f.rpsda, j, i + 1);
+  const double dmsf = L2(f.dmsf, j, i), coriol = L2(f.coriol, j, i), ef = L2(f.ef, j, i);
+  const double ddx = L2(f.ddx, j, i), ddy = L2(f.ddy, j, i), dmdx = L2(f.dmdx, j, i), dmdy = L2(f.dmdy, j, i);
+  const double psdotb = L2(f.psdotb, j, i);
+  const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_d, j, i) : 0;
   const bool dint = diff_interior(g, j, i, true);
   const int nring = ring_count(g, j, i, true);
 
   // vertical-advection flux at the upper interface of level k (full level k)
   double uu_k = 0.0, vv_k = 0.0;  // uu(1) = 0: loop starts at k = 2
-  double wadot_k = 0.125 * (P3(f.aw, j - 1, i - 1, 1) + P3(f.aw, j - 1, i, 1) + P3(f.aw, j, i - 1, 1) + P3(f.aw, j, i, 1));
+  double wadot_k = 0.125 * (L3(f.aw, j - 1, i - 1, 1) + L3(f.aw, j - 1, i, 1) + L3(f.aw, j, i - 1, 1) + L3(f.aw, j, i, 1));
 
   for (int k = 1; k <= kz; ++k) {
     // ---- level-a raw momentum on the 3x3 box ----
@@ -52,13 +52,13 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
     for (int a = 0; a < 3; ++a)
 #pragma unroll
       for (int b = 0; b < 3; ++b) {
-        au[a][b] = P3(f.au, j + a - 1, i + b - 1, k);
-        av[a][b] = P3(f.av, j + a - 1, i + b - 1, k);
+        au[a][b] = L3(f.au, j + a - 1, i + b - 1, k);
+        av[a][b] = L3(f.av, j + a - 1, i + b - 1, k);
       }
     // ua = umc = u*msfd ; [a][b] = (j+a-1, i+b-1)
 #define UA(a, b) (au[a][b] * md[a][b])
 #define VA(a, b) (av[a][b] * md[a][b])
-    const double divd = 0.25 * (P3(f.cr, j, i, k) + P3(f.cr, j, i - 1, k) + P3(f.cr, j - 1, i, k) + P3(f.cr, j - 1, i - 1, k));
+    const double divd = 0.25 * (L3(f.cr, j, i, k) + L3(f.cr, j, i - 1, k) + L3(f.cr, j - 1, i, k) + L3(f.cr, j - 1, i - 1, k));
     const double ucmona = UA(1, 2) + 2.0 * UA(1, 1) + UA(1, 0);
     double ucmonb = UA(2, 2) + 2.0 * UA(2, 1) + UA(2, 0);
     double ucmonc = UA(0, 2) + 2.0 * UA(0, 1) + UA(0, 0);
@@ -98,15 +98,15 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
     double uu_n = 0.0, vv_n = 0.0;
     if (k < kz) {
       const int kn = k + 1;
-      const double qq = 0.25 * (P3(f.qdot, j, i, kn) + P3(f.qdot, j, i - 1, kn) + P3(f.qdot, j - 1, i, kn) + P3(f.qdot, j - 1, i - 1, kn));
+      const double qq = 0.25 * (L3(f.qdot, j, i, kn) + L3(f.qdot, j, i - 1, kn) + L3(f.qdot, j - 1, i, kn) + L3(f.qdot, j - 1, i - 1, kn));
       const double t1 = f.twt1[kn], t2 = f.twt2[kn];
-      uu_n = qq * (t1 * P3(f.au, j, i, kn) + t2 * uc);
-      vv_n = qq * (t1 * P3(f.av, j, i, kn) + t2 * vc);
+      uu_n = qq * (t1 * L3(f.au, j, i, kn) + t2 * uc);
+      vv_n = qq * (t1 * L3(f.av, j, i, kn) + t2 * vc);
       ut = ut - uu_n * xdsk;
       vt = vt - vv_n * xdsk;
     }
     // ---- curvature / Coriolis (NH) ----
-    const double wadot_n = 0.125 * (P3(f.aw, j - 1, i - 1, k + 1) + P3(f.aw, j - 1, i, k + 1) + P3(f.aw, j, i - 1, k + 1) + P3(f.aw, j, i, k + 1));
+    const double wadot_n = 0.125 * (L3(f.aw, j - 1, i - 1, k + 1) + L3(f.aw, j - 1, i, k + 1) + L3(f.aw, j, i - 1, k + 1) + L3(f.aw, j, i, k + 1));
     {
       const double wabar = wadot_k + wadot_n;
       const double amfac = wabar * rp_c * rearthrad;
@@ -116,14 +116,14 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
       vt = vt - coriol * uc + ef * ddy * wabar - umd * duv - vc * amfac;
     }
     // ---- level-b values needed by nudging, diffusion and Rayleigh damping ----
-    const double bu_c = P3(f.bu, j, i, k), bv_c = P3(f.bv, j, i, k);
-    const double bu_jm = P3(f.bu, j - 1, i, k), bu_jp = P3(f.bu, j + 1, i, k), bu_im = P3(f.bu, j, i - 1, k), bu_ip = P3(f.bu, j, i + 1, k);
-    const double bv_jm = P3(f.bv, j - 1, i, k), bv_jp = P3(f.bv, j + 1, i, k), bv_im = P3(f.bv, j, i - 1, k), bv_ip = P3(f.bv, j, i + 1, k);
+    const double bu_c = L3(f.bu, j, i, k), bv_c = L3(f.bv, j, i, k);
+    const double bu_jm = L3(f.bu, j - 1, i, k), bu_jp = L3(f.bu, j + 1, i, k), bu_im = L3(f.bu, j, i - 1, k), bu_ip = L3(f.bu, j, i + 1, k);
+    const double bv_jm = L3(f.bv, j - 1, i, k), bv_jp = L3(f.bv, j + 1, i, k), bv_im = L3(f.bv, j, i - 1, k), bv_ip = L3(f.bv, j, i + 1, k);
     const double xt = s.xt;
     if (ib > 0) {
       const double xf = f.hefd[ib + s.nspgd * (k - 1)], xg = f.hegd[ib + s.nspgd * (k - 1)];
-#define FGU(jj, ii, bval) ((P3(f.xub0, jj, ii, k) + xt * P3(f.xubt, jj, ii, k)) - (bval))
-#define FGV(jj, ii, bval) ((P3(f.xvb0, jj, ii, k) + xt * P3(f.xvbt, jj, ii, k)) - (bval))
+#define FGU(jj, ii, bval) ((L3(f.xub0, jj, ii, k) + xt * L3(f.xubt, jj, ii, k)) - (bval))
+#define FGV(jj, ii, bval) ((L3(f.xvb0, jj, ii, k) + xt * L3(f.xvbt, jj, ii, k)) - (bval))
       double fls0 = FGU(j, i, bu_c), fls1 = FGU(j - 1, i, bu_jm), fls2 = FGU(j + 1, i, bu_jp), fls3 = FGU(j, i - 1, bu_im), fls4 = FGU(j, i + 1, bu_ip);
       ut = ut + xf * fls0 - xg * (fls1 + fls2 + fls3 + fls4 - 4.0 * fls0);
       fls0 = FGV(j, i, bv_c); fls1 = FGV(j - 1, i, bv_jm); fls2 = FGV(j + 1, i, bv_jp); fls3 = FGV(j, i - 1, bv_im); fls4 = FGV(j, i + 1, bv_ip);
@@ -134,16 +134,16 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
     // ---- 4th-order diffusion on level-b decoupled winds, each neighbour
     //      divided by its own (inverted) map factor ----
     {
-      double xkd = 0.25 * (P3(f.xkc, j, i, k) + P3(f.xkc, j - 1, i - 1, k) + P3(f.xkc, j - 1, i, k) + P3(f.xkc, j, i - 1, k));
+      double xkd = 0.25 * (L3(f.xkc, j, i, k) + L3(f.xkc, j - 1, i - 1, k) + L3(f.xkc, j - 1, i, k) + L3(f.xkc, j, i - 1, k));
       xkd = xkd * s.rdxsq * psdotb;
-#define DN(bval, jj, ii) (((bval) * (1.0 / P2(f.psdotb, jj, ii))) / P2(f.msfd, jj, ii))
+#define DN(bval, jj, ii) (((bval) * (1.0 / L2(f.psdotb, jj, ii))) / L2(f.msfd, jj, ii))
       const double du_c = DN(bu_c, j, i), du_jm = DN(bu_jm, j - 1, i), du_jp = DN(bu_jp, j + 1, i), du_im = DN(bu_im, j, i - 1), du_ip = DN(bu_ip, j, i + 1);
       const double dv_c = DN(bv_c, j, i), dv_jm = DN(bv_jm, j - 1, i), dv_jp = DN(bv_jp, j + 1, i), dv_im = DN(bv_im, j, i - 1), dv_ip = DN(bv_ip, j, i + 1);
       if (dint) {
-        const double du_jp2 = DN(P3(f.bu, j + 2, i, k), j + 2, i), du_jm2 = DN(P3(f.bu, j - 2, i, k), j - 2, i);
-        const double du_ip2 = DN(P3(f.bu, j, i + 2, k), j, i + 2), du_im2 = DN(P3(f.bu, j, i - 2, k), j, i - 2);
-        const double dv_jp2 = DN(P3(f.bv, j + 2, i, k), j + 2, i), dv_jm2 = DN(P3(f.bv, j - 2, i, k), j - 2, i);
-        const double dv_ip2 = DN(P3(f.bv, j, i + 2, k), j, i + 2), dv_im2 = DN(P3(f.bv, j, i - 2, k), j, i - 2);
+        const double du_jp2 = DN(L3(f.bu, j + 2, i, k), j + 2, i), du_jm2 = DN(L3(f.bu, j - 2, i, k), j - 2, i);
+        const double du_ip2 = DN(L3(f.bu, j, i + 2, k), j, i + 2), du_im2 = DN(L3(f.bu, j, i - 2, k), j, i - 2);
+        const double dv_jp2 = DN(L3(f.bv, j + 2, i, k), j + 2, i), dv_jm2 = DN(L3(f.bv, j - 2, i, k), j - 2, i);
+        const double dv_ip2 = DN(L3(f.bv, j, i + 2, k), j, i + 2), dv_im2 = DN(L3(f.bv, j, i - 2, k), j, i - 2);
         ut = ut - xkd * (1.0 * (du_jp2 + du_jm2 + du_ip2 + du_im2) + (-4.0) * (du_jp + du_jm + du_ip + du_im) + 12.0 * (du_c));
         vt = vt - xkd * (1.0 * (dv_jp2 + dv_jm2 + dv_ip2 + dv_im2) + (-4.0) * (dv_jp + dv_jm + dv_ip + dv_im) + 12.0 * (dv_c));
       }
@@ -155,9 +155,9 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
     }
     // ---- Rayleigh damping toward the boundary fields in the top levels ----
     if (s.ifrayd == 1 && k <= s.kt_ray) {
-      const double tau = P3(f.tau_d, j, i, k);
-      ut = ut + tau * ((P3(f.xub0, j, i, k) + xt * P3(f.xubt, j, i, k)) - bu_c);
-      vt = vt + tau * ((P3(f.xvb0, j, i, k) + xt * P3(f.xvbt, j, i, k)) - bv_c);
+      const double tau = L3(f.tau_d, j, i, k);
+      ut = ut + tau * ((L3(f.xub0, j, i, k) + xt * L3(f.xubt, j, i, k)) - bu_c);
+      vt = vt + tau * ((L3(f.xvb0, j, i, k) + xt * L3(f.xvbt, j, i, k)) - bv_c);
     }
     // ---- hand over to the acoustic loop: decouple and premultiply by dts ----
     P3(f.uten, j, i, k) = (ut * rp_c) * s.dts;
