@@ -211,7 +211,7 @@ def run_gpu(args):
     t_gen = time.perf_counter()
     case = synth.make_case(args.workload, window=window, **cfgkw)
     t_gen = time.perf_counter() - t_gen
-    synth.load_case(core, case, stage_next=False)
+    synth.load_case(core, case, stage_next=True)   # long runs of the small workloads cross a record change
     cells = base["jx"] * base["iy"] * base["kz"]
 
     def barrier():

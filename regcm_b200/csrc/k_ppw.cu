@@ -69,7 +69,7 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
     }
     const int kk = half ? k : kz;  // min(k,kz)
     double xf = 0.0, xg = 0.0;
-    if (ib > 0) { xf = f.hefc[ib + s.nspgx * (kk - 1)]; xg = f.hegc[ib + s.nspgx * (kk - 1)]; }
+    if (ib > 0) { xf = LD1(&f.hefc[ib + s.nspgx * (kk - 1)]); xg = LD1(&f.hegc[ib + s.nspgx * (kk - 1)]); }
     const double qdot_k = L3(f.qdot, j, i, k);
     const double qdot_n = half ? L3(f.qdot, j, i, k + 1) : 0.0;
 
@@ -80,11 +80,11 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
       const double p_c = app_c * rpsa_c, p_jm = L3(f.app, j - 1, i, k) * rpsa_jm, p_jp = L3(f.app, j + 1, i, k) * rpsa_jp,
                    p_im = L3(f.app, j, i - 1, k) * rpsa_im, p_ip = L3(f.app, j, i + 1, k) * rpsa_ip;
       double ten = hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, p_c, p_jm, p_jp, p_im, p_ip);
-      const double xdsk = f.xds[k];
+      const double xdsk = LD1(&f.xds[k]);
       if (k >= 2) ten = ten + fx_pp_k * xdsk;
       double fx_n = 0.0;
       if (k < kz) {
-        fx_n = qdot_n * (f.twt1[k + 1] * L3(f.app, j, i, k + 1) + f.twt2[k + 1] * app_c);
+        fx_n = qdot_n * (LD1(&f.twt1[k + 1]) * L3(f.app, j, i, k + 1) + LD1(&f.twt2[k + 1]) * app_c);
         ten = ten - fx_n * xdsk;
       }
       fx_pp_k = fx_n;
@@ -130,7 +130,7 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
       double ten = 0.0;
       const double w_c = aw_k * rpsa_c;
       if (k >= 2 && k <= kz) {
-        const double t1 = f.twt1[k], t2 = f.twt2[k];
+        const double t1 = LD1(&f.twt1[k]), t2 = LD1(&f.twt2[k]);
         const double uaz1 = (t1 * uavg1 + t2 * uavg1_m);
         const double uaz2 = (t1 * uavg2 + t2 * uavg2_m);
         const double vaz1 = (t1 * vavg1 + t2 * vavg1_m);
@@ -149,7 +149,7 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
         ten = ten - xmsf * (uaz2 * fx2 - uaz1 * fx1 + vaz2 * fy2 - vaz1 * fy1);
       }
       // vadv3d nk = kzp1: loop index k-1 adds, loop index k subtracts
-      const double ddsk = f.dds[k];
+      const double ddsk = LD1(&f.dds[k]);
       if (k >= 2) ten = ten + fxw_m * ddsk;
       double fxw = 0.0;
       if (half) {
@@ -158,8 +158,8 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
         ten = ten - fxw * ddsk;
       }
       if (k >= 2 && k <= kz) {
-        const double t1 = f.twt1[k], t2 = f.twt2[k];
-        const double dsk = f.dsigma[k], dsm = f.dsigma[k - 1];
+        const double t1 = LD1(&f.twt1[k]), t2 = LD1(&f.twt2[k]);
+        const double dsk = LD1(&f.dsigma[k]), dsm = LD1(&f.dsigma[k - 1]);
         const double rofac = (dsm * rho0 + dsk * rho0_m) / (dsm * rho1 + dsk * rho1_m);
         const double uaq = 0.25 * (t1 * ucc + t2 * ucc_m);
         const double vaq = 0.25 * (t1 * vcc + t2 * vcc_m);

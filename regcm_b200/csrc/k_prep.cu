@@ -70,14 +70,14 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
       ucc_n = (n00 * r00) * m00 + (n01 * r01) * m01 + (n10 * r10) * m10 + (n11 * r11) * m11;
       vcc_n = (w00 * r00) * m00 + (w01 * r01) * m01 + (w10 * r10) * m10 + (w11 * r11) * m11;
       const double w = L3(f.aw, j, i, kn) * rpsa;
-      const double t1 = f.twt1[kn], t2 = f.twt2[kn];
+      const double t1 = LD1(&f.twt1[kn]), t2 = LD1(&f.twt2[kn]);
       qd_n = -L3(f.rhof0, j, i, kn) * egrav * w / ps0 -
-             f.sigma[kn] * (dpsdxm * (t1 * ucc_n + t2 * ucc_k) + dpsdym * (t1 * vcc_n + t2 * vcc_k));
+             LD1(&f.sigma[kn]) * (dpsdxm * (t1 * ucc_n + t2 * ucc_k) + dpsdym * (t1 * vcc_n + t2 * vcc_k));
     }
     P3(f.qdot, j, i, k + 1) = qd_n;
     P3(f.cr, j, i, k) = ((u11 * m11 + u10 * m10 - u01 * m01 - u00 * m00) +
                          (v11 * m11 + v01 * m01 - v10 * m10 - v00 * m00)) * dummy +
-                        (qd_n - qd_k) * psa / f.dsigma[k];
+                        (qd_n - qd_k) * psa / LD1(&f.dsigma[k]);
     u00 = n00; u01 = n01; u10 = n10; u11 = n11;
     v00 = w00; v01 = w01; v10 = w10; v11 = w11;
     ucc_k = ucc_n; vcc_k = vcc_n; qd_k = qd_n;

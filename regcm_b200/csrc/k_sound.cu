@@ -108,7 +108,7 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
     const double pr1 = L3(f.pr1, j, i, m), rho0 = L3(f.rho0, j, i, m), pr0 = L3(f.pr0, j, i, m);
     L.tk = (0.5 * ps0 * L3(f.t0, j, i, m)) / (xgamma * pr0 * L3(f.nbt, j, i, m) * rpsb);
     L.cc = xgamma * pr1 * dts / (dx * msfx);
-    L.cdd = xgamma * pr1 * rho0 * egrav * dts / (ps0 * f.dsigma[m]);
+    L.cdd = xgamma * pr1 * rho0 * egrav * dts / (ps0 * LD1(&f.dsigma[m]));
     L.cj = 0.5 * rho0 * egrav * dts;
     double pxup, pyvp;
     if (m == 1) {
@@ -164,7 +164,7 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
     const int km1 = k - 1;
     const double rho0_k = L3(f.rho0, j, i, k), rho0_m = L3(f.rho0, j, i, km1);
     const double rho1_k = L3(f.rho1, j, i, k), rho1_m = L3(f.rho1, j, i, km1);
-    const double dsk = f.dsigma[k], dsm = f.dsigma[km1];
+    const double dsk = LD1(&f.dsigma[k]), dsm = LD1(&f.dsigma[km1]);
     const double rofac = (dsm * rho0_k + dsk * rho0_m) / (dsm * rho1_k + dsk * rho1_m);
     const double ca = egrav * dts / (L3(f.pr0, j, i, k) - L3(f.pr0, j, i, km1)) * rofac;
     const double g1 = 1.0 - dsm * Lk.tk;
@@ -214,7 +214,7 @@ k_snd_wpval(const Geom g, const Fields f, const StepScalars s) {
       const int inn = min(max(g.icross1 + 1, i + nsi), g.icross2 - 1);
       for (int nsj = -6; nsj <= 6; ++nsj) {
         const int jnn = min(max(g.jcross1 + 1, j + nsj), g.jcross2 - 1);
-        wp = wp + f.estore[(long long)jnn + (long long)inn * g.esi] * f.tmask[(nsj + 6) + 13 * (nsi + 6)];
+        wp = wp + f.estore[(long long)jnn + (long long)inn * g.esi] * LD1(&f.tmask[(nsj + 6) + 13 * (nsi + 6)]);
       }
     }
   }
@@ -236,60 +236,83 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
   const double dpsdxm = L2(f.dpsdxm, j, i), dpsdym = L2(f.dpsdym, j, i);
   const bool last = (s.it == s.istep);
 
+  // Inputs of one level, loaded as ONE batch and double-buffered: the loads of
+  // level k+1 are in flight while level k is computed (the loop is otherwise a
+  // chain of ~8 serialized DRAM round trips per level; ncu: 88% long-scoreboard).
+  struct In {
+    double se, sf, u0, u1, u2, u3, v0, v1, v2, v3, rhof0, cpp, cppd, pr1, rho0, rho1, ppten, nbqv, nbt, nat, pr0;
+    double t1, t2, sig, ds;
+  };
+  auto load = [&](int k) {
+    In r;
+    r.se = L3(f.se, j, i, k); r.sf = L3(f.sf, j, i, k);
+    r.u0 = L3(f.cu, j, i, k); r.u1 = L3(f.cu, j, i + 1, k); r.u2 = L3(f.cu, j + 1, i, k); r.u3 = L3(f.cu, j + 1, i + 1, k);
+    r.v0 = L3(f.cv, j, i, k); r.v1 = L3(f.cv, j, i + 1, k); r.v2 = L3(f.cv, j + 1, i, k); r.v3 = L3(f.cv, j + 1, i + 1, k);
+    r.rhof0 = L3(f.rhof0, j, i, k);
+    r.cpp = P3(f.cpp, j, i, k); r.cppd = P3(f.cppd, j, i, k);
+    r.pr1 = L3(f.pr1, j, i, k); r.rho0 = L3(f.rho0, j, i, k); r.rho1 = L3(f.rho1, j, i, k);
+    r.ppten = L3(f.ppten, j, i, k); r.nbqv = L3(f.nbqv, j, i, k);
+    r.nbt = P3(f.nbt, j, i, k); r.nat = P3(f.nat, j, i, k);
+    r.pr0 = L3(f.pr0, j, i, k);
+    r.t1 = LD1(&f.twt1[k]); r.t2 = LD1(&f.twt2[k]); r.sig = LD1(&f.sigma[k]); r.ds = LD1(&f.dsigma[k]);
+    return r;
+  };
+
   double w_k = L2(f.wpval, j, i);
   P3(f.cw, j, i, 1) = w_k;
   double ucrs_m = 0.0, vcrs_m = 0.0;
   double cfl = 0.0;
   double ppd_m2 = 0.0, ppd_m1 = 0.0;  // damped p' at k-2, k-1 (for ct of level k-1)
+  double pr0_m1 = 0.0, pr0_m2 = 0.0, ds_m = 1.0;
+  In c = load(1);
   for (int k = 1; k <= kz; ++k) {
-    const double w_n = L3(f.se, j, i, k) * w_k + L3(f.sf, j, i, k);
+    const In n = load(min(k + 1, kz));
+    const double w_n = c.se * w_k + c.sf;
     P3(f.cw, j, i, k + 1) = w_n;
     // ---- CFL diagnostic (:613-633) ----
-    const double ucrs = L3(f.cu, j, i, k) + L3(f.cu, j, i + 1, k) + L3(f.cu, j + 1, i, k) + L3(f.cu, j + 1, i + 1, k);
-    const double vcrs = L3(f.cv, j, i, k) + L3(f.cv, j, i + 1, k) + L3(f.cv, j + 1, i, k) + L3(f.cv, j + 1, i + 1, k);
+    const double ucrs = c.u0 + c.u1 + c.u2 + c.u3;
+    const double vcrs = c.v0 + c.v1 + c.v2 + c.v3;
     if (k >= 2) {
-      const double t1 = f.twt1[k], t2 = f.twt2[k];
-      const double sigdot = -L3(f.rhof0, j, i, k) * egrav * w_k / ps0 -
-                            f.sigma[k] * (dpsdxm * (t1 * ucrs + t2 * ucrs_m) + dpsdym * (t1 * vcrs + t2 * vcrs_m));
-      const double check = fabs(sigdot) * s.dt / (f.dsigma[k] + f.dsigma[k - 1]);
+      const double sigdot = -c.rhof0 * egrav * w_k / ps0 -
+                            c.sig * (dpsdxm * (c.t1 * ucrs + c.t2 * ucrs_m) + dpsdym * (c.t1 * vcrs + c.t2 * vcrs_m));
+      const double check = fabs(sigdot) * s.dt / (c.ds + ds_m);
       cfl = fmax(check, cfl);
     }
     ucrs_m = ucrs; vcrs_m = vcrs;
     // ---- new pressure and temperature correction (:669-689) ----
-    const double ppold = P3(f.cpp, j, i, k);
-    const double pr1 = L3(f.pr1, j, i, k), rho0 = L3(f.rho0, j, i, k);
-    const double cddtmp = xgamma * pr1 * rho0 * egrav * dts / (ps0 * f.dsigma[k]);
-    const double cjtmp = rho0 * egrav * dts * 0.5;
-    const double ppn = P3(f.cppd, j, i, k) + (cjtmp * (w_n + w_k) + cddtmp * (w_n - w_k)) * bp;
-    const double ppten = L3(f.ppten, j, i, k);
-    const double pi = ppn - ppold - ppten;
-    const double cpm = cpmf(L3(f.nbqv, j, i, k) * rpsb);
-    const double dpterm = psb * (ppn - ppold) / (cpm * L3(f.rho1, j, i, k));
-    P3(f.nbt, j, i, k) = P3(f.nbt, j, i, k) + s.gnu1 * dpterm;
-    P3(f.nat, j, i, k) = P3(f.nat, j, i, k) + dpterm;
+    const double ppold = c.cpp;
+    const double cddtmp = xgamma * c.pr1 * c.rho0 * egrav * dts / (ps0 * c.ds);
+    const double cjtmp = c.rho0 * egrav * dts * 0.5;
+    const double ppn = c.cppd + (cjtmp * (w_n + w_k) + cddtmp * (w_n - w_k)) * bp;
+    const double pi = ppn - ppold - c.ppten;
+    const double cpm = cpmf(c.nbqv * rpsb);
+    const double dpterm = psb * (ppn - ppold) / (cpm * c.rho1);
+    P3(f.nbt, j, i, k) = c.nbt + s.gnu1 * dpterm;
+    P3(f.nat, j, i, k) = c.nat + dpterm;
     // ---- prepare the next sub-step: divergence damping (:252-256,302-306) and
     //      d p'/d p0 (:257-264) ----
-    double ppd = ppn;
     if (!last) {
-      ppd = ppn + xkd * pi;
+      const double ppd = ppn + xkd * pi;
       P3(f.cppd, j, i, k) = ppd;
       P3(f.cpp, j, i, k) = ppd - xkd * pi;
       if (k >= 2) {
-        const int m = k - 1;  // ct(m) = (ppd(max(m-1,1)) - ppd(m+1)) / (pr0(max(m-1,1)) - pr0(m+1))
-        const int mm1 = max(1, m - 1);
-        const double a = (m == 1) ? ppd_m1 : ppd_m2;
-        P3(f.ct, j, i, m) = (a - ppd) / (L3(f.pr0, j, i, mm1) - L3(f.pr0, j, i, k));
+        // ct(m), m = k-1: (ppd(max(m-1,1)) - ppd(m+1)) / (pr0(max(m-1,1)) - pr0(m+1))
+        const double a = (k == 2) ? ppd_m1 : ppd_m2;
+        const double pa = (k == 2) ? pr0_m1 : pr0_m2;
+        P3(f.ct, j, i, k - 1) = (a - ppd) / (pa - c.pr0);
       }
       if (k == kz) {
-        const int km1 = max(1, kz - 1);
         const double a = (kz == 1) ? ppd : ppd_m1;
-        P3(f.ct, j, i, kz) = (a - ppd) / (L3(f.pr0, j, i, km1) - L3(f.pr0, j, i, kz));
+        const double pa = (kz == 1) ? c.pr0 : pr0_m1;
+        P3(f.ct, j, i, kz) = (a - ppd) / (pa - c.pr0);
       }
       ppd_m2 = ppd_m1; ppd_m1 = ppd;
     } else {
       P3(f.cpp, j, i, k) = ppn;
     }
+    pr0_m2 = pr0_m1; pr0_m1 = c.pr0; ds_m = c.ds;
     w_k = w_n;
+    c = n;
   }
   // block-level max, one atomic per block (order-independent => exact)
   unsigned long long bits = (unsigned long long)__double_as_longlong(cfl);  // cfl >= 0: bit order == value order

@@ -60,11 +60,11 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
     const double f1 = 0.5 * ul * (uavg2 + uavg1) / psa;
     const double f2 = 0.5 * ul * (vavg2 + vavg1) / psa;
     const double cr = L3(f.cr, j, i, k);
-    const double xdsk = f.xds[k];
+    const double xdsk = LD1(&f.xds[k]);
     const double svv_n = (k < kz) ? L3(f.qdot, j, i, k + 1) : 0.0;
     const int kk = k;  // min(k,kz) for the nudging table
     double xf = 0.0, xg = 0.0;
-    if (ib > 0) { xf = f.hefc[ib + s.nspgx * (kk - 1)]; xg = f.hegc[ib + s.nspgx * (kk - 1)]; }
+    if (ib > 0) { xf = LD1(&f.hefc[ib + s.nspgx * (kk - 1)]); xg = LD1(&f.hegc[ib + s.nspgx * (kk - 1)]); }
     double xkc = L3(f.xkc, j, i, k);
     xkc = xkc * s.rdxsq * psb;
     const double tauc = (s.ifrayd == 1 && k <= s.kt_ray) ? L3(f.tau_c, j, i, k) : 0.0;
@@ -81,7 +81,7 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
       double fx_th_n = 0.0, tha_n = 0.0;
       if (k < kz) {
         tha_n = L3(f.th, j, i, k + 1) * psa;
-        fx_th_n = svv_n * (f.twt1[k + 1] * tha_n + f.twt2[k + 1] * tha_k);
+        fx_th_n = svv_n * (LD1(&f.twt1[k + 1]) * tha_n + LD1(&f.twt2[k + 1]) * tha_k);
         thten = thten - fx_th_n * xdsk;
       }
       thten = thten + th_c * cr;
@@ -127,7 +127,7 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
       if (k < kz) {
         aqv_n = L3(f.aqv, j, i, k + 1);
         double fgv = 0.0;
-        if (aqv_n > qthr && aq_c > qthr) fgv = aqv_n * pow(aq_c / aqv_n, f.qcon[k + 1]);
+        if (aqv_n > qthr && aq_c > qthr) fgv = aqv_n * pow(aq_c / aqv_n, LD1(&f.qcon[k + 1]));
         fl_n = svv_n * fgv;
         ten = ten - fl_n * xdsk;
       }
@@ -177,7 +177,7 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
         ten = hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, q_c, q_jm, q_jp, q_im, q_ip);
         if (k >= 2) ten = ten + fl_qc_k * xdsk;
         if (k < kz) {
-          const double t1 = f.twt1[k + 1], t2 = f.twt2[k + 1];
+          const double t1 = LD1(&f.twt1[k + 1]), t2 = LD1(&f.twt2[k + 1]);
           if (svv_n > 0.0) {
             if (aq_c > cthr) fl_n = svv_n * (t1 * aqc_n + t2 * aq_c);
           } else {

@@ -90,7 +90,7 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
     double vt = v_c * diag - dmsf * (v_jp * ucmonb - v_jm * ucmonc + v_ip * vcmonb - v_im * vcmonc);
     // ---- vadvuv: + flux(k)*xds(k) then - flux(k+1)*xds(k) ----
     const double uc = au[1][1], vc = av[1][1];
-    const double xdsk = f.xds[k];
+    const double xdsk = LD1(&f.xds[k]);
     if (k >= 2) {
       ut = ut + uu_k * xdsk;
       vt = vt + vv_k * xdsk;
@@ -99,7 +99,7 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
     if (k < kz) {
       const int kn = k + 1;
       const double qq = 0.25 * (L3(f.qdot, j, i, kn) + L3(f.qdot, j, i - 1, kn) + L3(f.qdot, j - 1, i, kn) + L3(f.qdot, j - 1, i - 1, kn));
-      const double t1 = f.twt1[kn], t2 = f.twt2[kn];
+      const double t1 = LD1(&f.twt1[kn]), t2 = LD1(&f.twt2[kn]);
       uu_n = qq * (t1 * L3(f.au, j, i, kn) + t2 * uc);
       vv_n = qq * (t1 * L3(f.av, j, i, kn) + t2 * vc);
       ut = ut - uu_n * xdsk;
@@ -121,7 +121,7 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
     const double bv_jm = L3(f.bv, j - 1, i, k), bv_jp = L3(f.bv, j + 1, i, k), bv_im = L3(f.bv, j, i - 1, k), bv_ip = L3(f.bv, j, i + 1, k);
     const double xt = s.xt;
     if (ib > 0) {
-      const double xf = f.hefd[ib + s.nspgd * (k - 1)], xg = f.hegd[ib + s.nspgd * (k - 1)];
+      const double xf = LD1(&f.hefd[ib + s.nspgd * (k - 1)]), xg = LD1(&f.hegd[ib + s.nspgd * (k - 1)]);
 #define FGU(jj, ii, bval) ((L3(f.xub0, jj, ii, k) + xt * L3(f.xubt, jj, ii, k)) - (bval))
 #define FGV(jj, ii, bval) ((L3(f.xvb0, jj, ii, k) + xt * L3(f.xvbt, jj, ii, k)) - (bval))
       double fls0 = FGU(j, i, bu_c), fls1 = FGU(j - 1, i, bu_jm), fls2 = FGU(j + 1, i, bu_jp), fls3 = FGU(j, i - 1, bu_im), fls4 = FGU(j, i + 1, bu_ip);
