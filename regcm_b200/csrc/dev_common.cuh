@@ -14,14 +14,33 @@
 #define L3(p, j, i, k) P3(p, j, i, k)
 #define L2(p, j, i) P2(p, j, i)
 #define LD1(p) (*(p))
+#define PF3(p, j, i, k) ((void)0)
 #else
 #define L3(p, j, i, k) __ldg(&P3(p, j, i, k))
 #define L2(p, j, i) __ldg(&P2(p, j, i))
 #define LD1(p) __ldg(p)
+// L2 prefetch of the 128-B line holding (j,i,k): the column-marching kernels
+// request level k+pfd while they work on level k, so that the demand loads hit
+// L2 instead of paying a DRAM round trip per dependent load phase
+#define PF3(p, j, i, k) asm volatile("prefetch.global.L2 [%0];" ::"l"(&P3(p, j, i, k)))
 #endif
 
-#define RCM_BX 32
-#define RCM_BY 4
+#define RCM_MAXT 256
+#include <cstdio>
+#include <cstdlib>
+namespace rcm {
+// thread-block shape of the column-marching kernels (x along j, y along i);
+// RCM_BLOCK="bx,by" overrides it for tuning runs
+inline dim3 col_block() {
+  static int bx = 0, by = 0;
+  if (bx == 0) {
+    bx = 32; by = 4;
+    const char* e = std::getenv("RCM_BLOCK");
+    if (e) { int a = 0, b = 0; if (std::sscanf(e, "%d,%d", &a, &b) == 2 && a > 0 && b > 0 && a * b <= RCM_MAXT) { bx = a; by = b; } }
+  }
+  return dim3(bx, by);
+}
+}  // namespace rcm
 
 namespace rcm {
 
@@ -75,6 +94,27 @@ __device__ __forceinline__ int ring_count(const Geom& g, int j, int i, bool dot)
   if (g.has_bdybottom && i == i1) n++;
   if (g.has_bdytop && i == i2) n++;
   return n;
+}
+
+// Fold one thread's CFL number (>= 0, so the bit pattern orders like the value)
+// into the two running maxima: [0] over the sub-steps of this step, [1] over
+// the whole rcm_dyn_step call.  Warp-reduced first: one same-address atomic per
+// warp instead of one per column (max is order-independent => exact).  Must be
+// reached by every thread of the block.
+__device__ __forceinline__ void commit_cfl(const Fields& f, const double cfl, const bool valid) {
+  unsigned long long bits = valid ? (unsigned long long)__double_as_longlong(cfl) : 0ULL;
+  if (valid && cfl != cfl) { *f.nanflag = 1; bits = 0x7ff8000000000000ULL; }
+#ifndef RCM_EMU
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long other = __shfl_xor_sync(0xffffffffu, bits, o);
+    bits = other > bits ? other : bits;
+  }
+  if (((threadIdx.x + blockDim.x * threadIdx.y) & 31) != 0) return;
+#endif
+  if (bits == 0ULL) return;
+  atomicMax(f.cflbits, bits);
+  atomicMax(f.cflbits + 1, bits);
 }
 
 __device__ __forceinline__ bool diff_interior(const Geom& g, int j, int i, bool dot) {

@@ -257,6 +257,8 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   h->off2 = -((long long)(g.jde1 - RCM_HALO) + (long long)g.si * (g.ide1 - RCM_HALO));
   h->off3 = h->off2 - g.sk;
   g.esi = ((nj + 2 * RCM_EHALO + 15) / 16) * 16;
+  g.pfd = 2;
+  if (const char* e = std::getenv("RCM_PFD")) g.pfd = std::max(0, std::min(8, std::atoi(e)));
   h->eni = ni + 2 * RCM_EHALO;
   h->eoff = -((long long)(g.jde1 - RCM_EHALO) + (long long)g.esi * (g.ide1 - RCM_EHALO));
 

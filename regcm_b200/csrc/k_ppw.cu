@@ -15,12 +15,12 @@
 
 using namespace rcm;
 
-__global__ void __launch_bounds__(RCM_BX* RCM_BY)
+__global__ void __launch_bounds__(RCM_MAXT)
 k_ppw(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
-  const int j = g.jci1 + blockIdx.x * RCM_BX + threadIdx.x;
-  const int i = g.ici1 + blockIdx.y * RCM_BY + threadIdx.y;
+  const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jci2 || i > g.ici2) return;
   const int kz = g.kz, kzp1 = g.kzp1;
   const bool up = s.upstream_mode != 0;
@@ -202,6 +202,6 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
 
 void launch_ppw(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
-  dim3 b(RCM_BX, RCM_BY), gr((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY);
+  const dim3 b = rcm::col_block(); dim3 gr((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y);
   RCM_LAUNCH(k_ppw, gr, b, st, g, f, s);
 }

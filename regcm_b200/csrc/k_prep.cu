@@ -21,12 +21,12 @@
 
 using namespace rcm;
 
-__global__ void __launch_bounds__(RCM_BX* RCM_BY)
+__global__ void __launch_bounds__(RCM_MAXT)
 k_prep(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
-  const int j = (g.jce1 - g.gl) + blockIdx.x * RCM_BX + threadIdx.x;
-  const int i = (g.ice1 - g.gb) + blockIdx.y * RCM_BY + threadIdx.y;
+  const int j = (g.jce1 - g.gl) + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (g.ice1 - g.gb) + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jce2 + g.gr || i > g.ice2 + g.gt) return;
   const int kz = g.kz;
 
@@ -84,12 +84,12 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
   }
 }
 
-__global__ void __launch_bounds__(RCM_BX* RCM_BY)
+__global__ void __launch_bounds__(RCM_MAXT)
 k_xkc(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
-  const int j = (g.jce1 - g.gl) + blockIdx.x * RCM_BX + threadIdx.x;
-  const int i = (g.ice1 - g.gb) + blockIdx.y * RCM_BY + threadIdx.y;
+  const int j = (g.jce1 - g.gl) + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (g.ice1 - g.gb) + blockIdx.y * blockDim.y + threadIdx.y;
   const int k = 1 + blockIdx.z;
   if (j > g.jce2 + g.gr || i > g.ice2 + g.gt) return;
   // ubd3d = atm2%u * (1/psdotb), wb3d = atm2%w * (1/psb)  (Main/mod_slice.F90:169-263)
@@ -111,11 +111,11 @@ k_xkc(const Geom g, const Fields f, const StepScalars s) {
 
 void launch_prep(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = (g.jce2 + g.gr) - (g.jce1 - g.gl) + 1, ni = (g.ice2 + g.gt) - (g.ice1 - g.gb) + 1;
-  dim3 b(RCM_BX, RCM_BY), gr((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY);
+  const dim3 b = rcm::col_block(); dim3 gr((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y);
   RCM_LAUNCH(k_prep, gr, b, st, g, f, s);
 }
 void launch_xkc(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = (g.jce2 + g.gr) - (g.jce1 - g.gl) + 1, ni = (g.ice2 + g.gt) - (g.ice1 - g.gb) + 1;
-  dim3 b(RCM_BX, RCM_BY), gr3((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY, g.kz);
+  const dim3 b = rcm::col_block(); dim3 gr3((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y, g.kz);
   RCM_LAUNCH(k_xkc, gr3, b, st, g, f, s);
 }

@@ -83,12 +83,12 @@ struct SndLevel {
   double tk, cc, cdd, cj, ptend, pp, wo;
 };
 
-__global__ void __launch_bounds__(RCM_BX* RCM_BY)
+__global__ void __launch_bounds__(RCM_MAXT)
 k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
-  const int j = g.jci1 + blockIdx.x * RCM_BX + threadIdx.x;
-  const int i = g.ici1 + blockIdx.y * RCM_BY + threadIdx.y;
+  const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jci2 || i > g.ici2) return;
   const int kz = g.kz, kzp1 = g.kzp1;
   const double dts = s.dts, dx = s.dx, xgamma = s.xgamma, bp = s.bp, bm = s.bm, bpxbp = s.bpxbp, bpxbm = s.bpxbm;
@@ -135,6 +135,16 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
     L.wo = L3(f.cw, j, i, m);
   };
 
+  // request level kk of every streamed field into L2 (see PF3)
+  auto prefetch = [&](int kk) {
+    PF3(f.cu, j, i, kk); PF3(f.cv, j, i, kk); PF3(f.pr1, j, i, kk); PF3(f.rho0, j, i, kk);
+    PF3(f.pr0, j, i, kk); PF3(f.t0, j, i, kk); PF3(f.nbt, j, i, kk); PF3(f.ppten, j, i, kk);
+    PF3(f.cpp, j, i, kk); PF3(f.cw, j, i, kk); PF3(f.rho1, j, i, kk); PF3(f.wten, j, i, kk);
+  };
+  const int pfd = g.pfd;
+  if (pfd > 0)
+    for (int kk = kz; kk >= max(kz - pfd, 1); --kk) prefetch(kk);
+
   // ---- bottom boundary condition (:323-334) ----
   LOADUV(uc_, vc_, kz);
   const double wo_bot = L3(f.cw, j, i, kzp1);
@@ -155,6 +165,7 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
   double wo_kp1 = wo_bot;  // wo(k+1)
 
   for (int k = kz; k >= 2; --k) {
+    if (pfd > 0 && k - 1 - pfd >= 1) prefetch(k - 1 - pfd);
     // shift the wind window down one level and build the record of k-1
 #pragma unroll
     for (int q = 0; q < 4; ++q) { up_[q] = uc_[q]; vp_[q] = vc_[q]; uc_[q] = um_[q]; vc_[q] = vm_[q]; }
@@ -222,13 +233,15 @@ k_snd_wpval(const Geom g, const Fields f, const StepScalars s) {
 }
 
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(RCM_BX* RCM_BY)
+__global__ void __launch_bounds__(RCM_MAXT)
 k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
-  const int j = g.jci1 + blockIdx.x * RCM_BX + threadIdx.x;
-  const int i = g.ici1 + blockIdx.y * RCM_BY + threadIdx.y;
-  if (j > g.jci2 || i > g.ici2) return;
+  const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const bool valid = (j <= g.jci2 && i <= g.ici2);
+  double cfl = 0.0;
+  if (valid) {
   const int kz = g.kz;
   const double dts = s.dts, xgamma = s.xgamma, bp = s.bp, xkd = s.xkd_snd;
   const double ps0 = L2(f.ps0, j, i), psb = L2(f.psb, j, i);
@@ -236,9 +249,9 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
   const double dpsdxm = L2(f.dpsdxm, j, i), dpsdym = L2(f.dpsdym, j, i);
   const bool last = (s.it == s.istep);
 
-  // Inputs of one level, loaded as ONE batch and double-buffered: the loads of
-  // level k+1 are in flight while level k is computed (the loop is otherwise a
-  // chain of ~8 serialized DRAM round trips per level; ncu: 88% long-scoreboard).
+  // Inputs of one level, loaded as ONE batch at the top of the iteration (the
+  // loop is otherwise a chain of ~8 serialized memory round trips per level, ncu:
+  // 88% long-scoreboard); level k+pfd is requested into L2 at the same time.
   struct In {
     double se, sf, u0, u1, u2, u3, v0, v1, v2, v3, rhof0, cpp, cppd, pr1, rho0, rho1, ppten, nbqv, nbt, nat, pr0;
     double t1, t2, sig, ds;
@@ -258,15 +271,24 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
     return r;
   };
 
+  // request level kk of every streamed field into L2
+  auto prefetch = [&](int kk) {
+    PF3(f.se, j, i, kk); PF3(f.sf, j, i, kk); PF3(f.cu, j, i, kk); PF3(f.cv, j, i, kk);
+    PF3(f.rhof0, j, i, kk); PF3(f.cpp, j, i, kk); PF3(f.cppd, j, i, kk); PF3(f.pr1, j, i, kk);
+    PF3(f.rho0, j, i, kk); PF3(f.rho1, j, i, kk); PF3(f.ppten, j, i, kk); PF3(f.nbqv, j, i, kk);
+    PF3(f.nbt, j, i, kk); PF3(f.nat, j, i, kk); PF3(f.pr0, j, i, kk);
+  };
+  const int pfd = g.pfd;
+  if (pfd > 0)
+    for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
   double w_k = L2(f.wpval, j, i);
   P3(f.cw, j, i, 1) = w_k;
   double ucrs_m = 0.0, vcrs_m = 0.0;
-  double cfl = 0.0;
   double ppd_m2 = 0.0, ppd_m1 = 0.0;  // damped p' at k-2, k-1 (for ct of level k-1)
   double pr0_m1 = 0.0, pr0_m2 = 0.0, ds_m = 1.0;
-  In c = load(1);
   for (int k = 1; k <= kz; ++k) {
-    const In n = load(min(k + 1, kz));
+    if (pfd > 0 && k + pfd <= kz) prefetch(k + pfd);
+    const In c = load(k);
     const double w_n = c.se * w_k + c.sf;
     P3(f.cw, j, i, k + 1) = w_n;
     // ---- CFL diagnostic (:613-633) ----
@@ -312,13 +334,9 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
     }
     pr0_m2 = pr0_m1; pr0_m1 = c.pr0; ds_m = c.ds;
     w_k = w_n;
-    c = n;
   }
-  // block-level max, one atomic per block (order-independent => exact)
-  unsigned long long bits = (unsigned long long)__double_as_longlong(cfl);  // cfl >= 0: bit order == value order
-  if (cfl != cfl) { *f.nanflag = 1; bits = 0x7ff8000000000000ULL; }
-  atomicMax(f.cflbits, bits);      // max over the sub-steps of this step
-  atomicMax(f.cflbits + 1, bits);  // max over the whole rcm_dyn_step call
+  }  // valid
+  rcm::commit_cfl(f, cfl, valid);
 }
 
 // ---------------------------------------------------------------------------
@@ -383,7 +401,7 @@ void launch_snd_uv(const Geom& g, const Fields& f, const StepScalars& s, cudaStr
 }
 void launch_snd_wfwd(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
-  dim3 b(RCM_BX, RCM_BY), gr((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY);
+  const dim3 b = rcm::col_block(); dim3 gr((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y);
   RCM_LAUNCH(k_snd_wfwd, gr, b, st, g, f, s);
 }
 void launch_snd_wpval(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
@@ -393,7 +411,7 @@ void launch_snd_wpval(const Geom& g, const Fields& f, const StepScalars& s, cuda
 }
 void launch_snd_wback(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
-  dim3 b(RCM_BX, RCM_BY), gr((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY);
+  const dim3 b = rcm::col_block(); dim3 gr((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y);
   RCM_LAUNCH(k_snd_wback, gr, b, st, g, f, s);
 }
 void launch_snd_final(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {

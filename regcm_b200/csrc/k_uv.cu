@@ -15,12 +15,12 @@
 
 using namespace rcm;
 
-__global__ void __launch_bounds__(RCM_BX* RCM_BY)
+__global__ void __launch_bounds__(RCM_MAXT)
 k_uv(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
-  const int j = g.jdi1 + blockIdx.x * RCM_BX + threadIdx.x;
-  const int i = g.idi1 + blockIdx.y * RCM_BY + threadIdx.y;
+  const int j = g.jdi1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.idi1 + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jdi2 || i > g.idi2) return;
   const int kz = g.kz;
   const bool up = s.upstream_mode != 0;
@@ -170,6 +170,6 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
 
 void launch_uv(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jdi2 - g.jdi1 + 1, ni = g.idi2 - g.idi1 + 1;
-  dim3 b(RCM_BX, RCM_BY), gr((nj + RCM_BX - 1) / RCM_BX, (ni + RCM_BY - 1) / RCM_BY);
+  const dim3 b = rcm::col_block(); dim3 gr((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y);
   RCM_LAUNCH(k_uv, gr, b, st, g, f, s);
 }
