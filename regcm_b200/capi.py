@@ -301,7 +301,8 @@ def nccl_unique_id(lib: "CoreLib") -> bytes:
 
 
 _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-CUDA_LIB_PATH = os.path.join(_PKG_DIR, "csrc", "libregcm_dyn.so")
+# RCM_DYN_LIB selects another build of the same library (kernel tuning runs only)
+CUDA_LIB_PATH = os.environ.get("RCM_DYN_LIB") or os.path.join(_PKG_DIR, "csrc", "libregcm_dyn.so")
 _cuda_lib = None
 
 

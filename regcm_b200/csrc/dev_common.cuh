@@ -25,7 +25,32 @@
 #define PF3(p, j, i, k) asm volatile("prefetch.global.L2 [%0];" ::"l"(&P3(p, j, i, k)))
 #endif
 
-#define RCM_MAXT 256
+// Column kernels run 32x4-thread blocks; RCM_MB_* = minimum resident blocks per
+// SM asked of ptxas (register cap 65536 / (128 * RCM_MB)), tuned per kernel on
+// B200 (scripts/build_variant.sh): the slow-tendency kernels are latency-bound
+// and want occupancy, the tridiagonal forward sweep wants registers.
+#define RCM_MAXT 128
+#ifndef RCM_MB_PREP
+#define RCM_MB_PREP 4
+#endif
+#ifndef RCM_MB_XKC
+#define RCM_MB_XKC 8
+#endif
+#ifndef RCM_MB_UV
+#define RCM_MB_UV 4
+#endif
+#ifndef RCM_MB_TQ
+#define RCM_MB_TQ 4
+#endif
+#ifndef RCM_MB_PPW
+#define RCM_MB_PPW 4
+#endif
+#ifndef RCM_MB_WFWD
+#define RCM_MB_WFWD 3
+#endif
+#ifndef RCM_MB_WBACK
+#define RCM_MB_WBACK 4
+#endif
 #include <cstdio>
 #include <cstdlib>
 namespace rcm {

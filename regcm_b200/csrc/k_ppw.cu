@@ -15,7 +15,7 @@
 
 using namespace rcm;
 
-__global__ void __launch_bounds__(RCM_MAXT)
+__global__ void __launch_bounds__(RCM_MAXT, RCM_MB_PPW)
 k_ppw(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
@@ -48,7 +48,15 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
   double xkc_m = 0.0;      // raw xkc(k-1)
   double aw_k = L3(f.aw, j, i, 1);
 
+  // request level kk of every streamed field into L2 (see PF3)
+  auto prefetch = [&](int kk) {
+    PF3(f.au, j, i, kk); PF3(f.av, j, i, kk); PF3(f.aw, j, i, kk); PF3(f.app, j, i, kk); PF3(f.bpp, j, i, kk); PF3(f.bw, j, i, kk); PF3(f.qdot, j, i, kk); PF3(f.cr, j, i, kk); PF3(f.xkc, j, i, kk); PF3(f.at, j, i, kk); PF3(f.aqv, j, i, kk); PF3(f.aqc, j, i, kk); PF3(f.rho0, j, i, kk); PF3(f.rho1, j, i, kk); PF3(f.t0, j, i, kk);
+  };
+  const int pfd = g.pfd;
+  if (pfd > 0)
+    for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
   for (int k = 1; k <= kzp1; ++k) {
+    if (pfd > 0 && k + pfd <= kz) prefetch(k + pfd);
     const bool half = (k <= kz);  // a half level k exists (pp, T, u, v live there)
     double uavg1 = 0, uavg2 = 0, vavg1 = 0, vavg2 = 0, ucc = 0, vcc = 0, f1 = 0, f2 = 0;
     double cr = 0, xkc_raw = 0;

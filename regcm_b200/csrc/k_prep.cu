@@ -21,7 +21,7 @@
 
 using namespace rcm;
 
-__global__ void __launch_bounds__(RCM_MAXT)
+__global__ void __launch_bounds__(RCM_MAXT, RCM_MB_PREP)
 k_prep(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
@@ -50,7 +50,15 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
   double qd_k = 0.0;
   P3(f.qdot, j, i, 1) = 0.0;
 
+  // request level kk of every streamed field into L2 (see PF3)
+  auto prefetch = [&](int kk) {
+    PF3(f.au, j, i, kk); PF3(f.av, j, i, kk); PF3(f.at, j, i, kk); PF3(f.aqv, j, i, kk); PF3(f.app, j, i, kk); PF3(f.aw, j, i, kk); PF3(f.pr0, j, i, kk); PF3(f.rhof0, j, i, kk);
+  };
+  const int pfd = g.pfd;
+  if (pfd > 0)
+    for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
   for (int k = 1; k <= kz; ++k) {
+    if (pfd > 0 && k + pfd <= kz) prefetch(k + pfd);
     // ---- decouple + theta ----
     const double t = L3(f.at, j, i, k) * rpsa;
     const double qv = fmax(L3(f.aqv, j, i, k) * rpsa, minqq);
@@ -84,22 +92,32 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
   }
 }
 
-__global__ void __launch_bounds__(RCM_MAXT)
+// Smagorinsky coefficient on cross points (calc_coeff) and, for diffu_d, the
+// level-b winds decoupled and divided by the dot-point map factor,
+// (u*(1/psdotb))/msfd (Main/mod_diffusion.F90:266-385 reads ud/mapfd at 9
+// stencil points; evaluating the quotient once per dot point here instead of at
+// every stencil reference removes 18 divisions per point from k_uv and gives
+// the same bits).  1/psdotb and 1/psb are the host tables rpsda, rpsb (p* is
+// constant for idynamic = 2).
+__global__ void __launch_bounds__(RCM_MAXT, RCM_MB_XKC)
 k_xkc(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
-  const int j = (g.jce1 - g.gl) + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = (g.ice1 - g.gb) + blockIdx.y * blockDim.y + threadIdx.y;
+  const int j = (g.jde1 - 2 * g.gl) + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (g.ide1 - 2 * g.gb) + blockIdx.y * blockDim.y + threadIdx.y;
   const int k = 1 + blockIdx.z;
-  if (j > g.jce2 + g.gr || i > g.ice2 + g.gt) return;
+  if (j > g.jde2 + 2 * g.gr || i > g.ide2 + 2 * g.gt) return;
   // ubd3d = atm2%u * (1/psdotb), wb3d = atm2%w * (1/psb)  (Main/mod_slice.F90:169-263)
-  const double r00 = 1.0 / L2(f.psdotb, j, i), r01 = 1.0 / L2(f.psdotb, j, i + 1),
-               r10 = 1.0 / L2(f.psdotb, j + 1, i), r11 = 1.0 / L2(f.psdotb, j + 1, i + 1);
-  const double rpsb = 1.0 / L2(f.psb, j, i);
-  const double u00 = L3(f.bu, j, i, k) * r00, u01 = L3(f.bu, j, i + 1, k) * r01, u10 = L3(f.bu, j + 1, i, k) * r10,
-               u11 = L3(f.bu, j + 1, i + 1, k) * r11;
-  const double v00 = L3(f.bv, j, i, k) * r00, v01 = L3(f.bv, j, i + 1, k) * r01, v10 = L3(f.bv, j + 1, i, k) * r10,
-               v11 = L3(f.bv, j + 1, i + 1, k) * r11;
+  const double u00 = L3(f.bu, j, i, k) * L2(f.rpsda, j, i);
+  const double v00 = L3(f.bv, j, i, k) * L2(f.rpsda, j, i);
+  const double md = L2(f.msfd, j, i);
+  P3(f.dub, j, i, k) = u00 / md;
+  P3(f.dvb, j, i, k) = v00 / md;
+  if (j < g.jce1 - g.gl || j > g.jce2 + g.gr || i < g.ice1 - g.gb || i > g.ice2 + g.gt) return;
+  const double r01 = L2(f.rpsda, j, i + 1), r10 = L2(f.rpsda, j + 1, i), r11 = L2(f.rpsda, j + 1, i + 1);
+  const double rpsb = L2(f.rpsb, j, i);
+  const double u01 = L3(f.bu, j, i + 1, k) * r01, u10 = L3(f.bu, j + 1, i, k) * r10, u11 = L3(f.bu, j + 1, i + 1, k) * r11;
+  const double v01 = L3(f.bv, j, i + 1, k) * r01, v10 = L3(f.bv, j + 1, i, k) * r10, v11 = L3(f.bv, j + 1, i + 1, k) * r11;
   const double dudx = u10 + u11 - u00 - u01;
   const double dvdx = v10 + v11 - v00 - v01;
   const double dudy = u01 + u11 - u00 - u10;
@@ -115,7 +133,7 @@ void launch_prep(const Geom& g, const Fields& f, const StepScalars& s, cudaStrea
   RCM_LAUNCH(k_prep, gr, b, st, g, f, s);
 }
 void launch_xkc(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
-  const int nj = (g.jce2 + g.gr) - (g.jce1 - g.gl) + 1, ni = (g.ice2 + g.gt) - (g.ice1 - g.gb) + 1;
+  const int nj = (g.jde2 + 2 * g.gr) - (g.jde1 - 2 * g.gl) + 1, ni = (g.ide2 + 2 * g.gt) - (g.ide1 - 2 * g.gb) + 1;
   const dim3 b = rcm::col_block(); dim3 gr3((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y, g.kz);
   RCM_LAUNCH(k_xkc, gr3, b, st, g, f, s);
 }

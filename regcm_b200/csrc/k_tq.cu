@@ -21,7 +21,7 @@
 
 using namespace rcm;
 
-__global__ void __launch_bounds__(RCM_MAXT)
+__global__ void __launch_bounds__(RCM_MAXT, RCM_MB_TQ)
 k_tq(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
@@ -49,7 +49,15 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
   double fx_th_k = 0.0, fl_qv_k = 0.0, fl_qc_k = 0.0;
   double tha_k = L3(f.th, j, i, 1) * psa;
 
+  // request level kk of every streamed field into L2 (see PF3)
+  auto prefetch = [&](int kk) {
+    PF3(f.au, j, i, kk); PF3(f.av, j, i, kk); PF3(f.cr, j, i, kk); PF3(f.qdot, j, i, kk); PF3(f.xkc, j, i, kk); PF3(f.th, j, i, kk); PF3(f.at, j, i, kk); PF3(f.bt, j, i, kk); PF3(f.aqv, j, i, kk); PF3(f.bqv, j, i, kk); PF3(f.aqc, j, i, kk); PF3(f.bqc, j, i, kk);
+  };
+  const int pfd = g.pfd;
+  if (pfd > 0)
+    for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
   for (int k = 1; k <= kz; ++k) {
+    if (pfd > 0 && k + pfd <= kz) prefetch(k + pfd);
     // ---- start_advect: ua = umc = u*msfd at the four surrounding dots ----
     const double ua00 = L3(f.au, j, i, k) * m00, ua01 = L3(f.au, j, i + 1, k) * m01, ua10 = L3(f.au, j + 1, i, k) * m10,
                  ua11 = L3(f.au, j + 1, i + 1, k) * m11;

@@ -15,7 +15,7 @@
 
 using namespace rcm;
 
-__global__ void __launch_bounds__(RCM_MAXT)
+__global__ void __launch_bounds__(RCM_MAXT, RCM_MB_UV)
 k_uv(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
@@ -45,7 +45,15 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
   double uu_k = 0.0, vv_k = 0.0;  // uu(1) = 0: loop starts at k = 2
   double wadot_k = 0.125 * (L3(f.aw, j - 1, i - 1, 1) + L3(f.aw, j - 1, i, 1) + L3(f.aw, j, i - 1, 1) + L3(f.aw, j, i, 1));
 
+  // request level kk of every streamed field into L2 (see PF3)
+  auto prefetch = [&](int kk) {
+    PF3(f.au, j, i, kk); PF3(f.av, j, i, kk); PF3(f.cr, j, i, kk); PF3(f.qdot, j, i, kk); PF3(f.aw, j, i, kk); PF3(f.xkc, j, i, kk); PF3(f.dub, j, i, kk); PF3(f.dvb, j, i, kk);
+  };
+  const int pfd = g.pfd;
+  if (pfd > 0)
+    for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
   for (int k = 1; k <= kz; ++k) {
+    if (pfd > 0 && k + pfd <= kz) prefetch(k + pfd);
     // ---- level-a raw momentum on the 3x3 box ----
     double au[3][3], av[3][3];
 #pragma unroll
@@ -115,12 +123,12 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
       ut = ut + coriol * vc - ef * ddx * wabar + vmd * duv - uc * amfac;
       vt = vt - coriol * uc + ef * ddy * wabar - umd * duv - vc * amfac;
     }
-    // ---- level-b values needed by nudging, diffusion and Rayleigh damping ----
-    const double bu_c = L3(f.bu, j, i, k), bv_c = L3(f.bv, j, i, k);
-    const double bu_jm = L3(f.bu, j - 1, i, k), bu_jp = L3(f.bu, j + 1, i, k), bu_im = L3(f.bu, j, i - 1, k), bu_ip = L3(f.bu, j, i + 1, k);
-    const double bv_jm = L3(f.bv, j - 1, i, k), bv_jp = L3(f.bv, j + 1, i, k), bv_im = L3(f.bv, j, i - 1, k), bv_ip = L3(f.bv, j, i + 1, k);
+    // ---- relaxation toward the boundary fields in the lateral zone ----
     const double xt = s.xt;
     if (ib > 0) {
+      const double bu_c = L3(f.bu, j, i, k), bv_c = L3(f.bv, j, i, k);
+      const double bu_jm = L3(f.bu, j - 1, i, k), bu_jp = L3(f.bu, j + 1, i, k), bu_im = L3(f.bu, j, i - 1, k), bu_ip = L3(f.bu, j, i + 1, k);
+      const double bv_jm = L3(f.bv, j - 1, i, k), bv_jp = L3(f.bv, j + 1, i, k), bv_im = L3(f.bv, j, i - 1, k), bv_ip = L3(f.bv, j, i + 1, k);
       const double xf = LD1(&f.hefd[ib + s.nspgd * (k - 1)]), xg = LD1(&f.hegd[ib + s.nspgd * (k - 1)]);
 #define FGU(jj, ii, bval) ((L3(f.xub0, jj, ii, k) + xt * L3(f.xubt, jj, ii, k)) - (bval))
 #define FGV(jj, ii, bval) ((L3(f.xvb0, jj, ii, k) + xt * L3(f.xvbt, jj, ii, k)) - (bval))
@@ -132,18 +140,18 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
 #undef FGV
     }
     // ---- 4th-order diffusion on level-b decoupled winds, each neighbour
-    //      divided by its own (inverted) map factor ----
+    //      divided by its own (inverted) map factor: the quotients
+    //      (ub/psdotb)/msfd come precomputed from k_xkc ----
     {
       double xkd = 0.25 * (L3(f.xkc, j, i, k) + L3(f.xkc, j - 1, i - 1, k) + L3(f.xkc, j - 1, i, k) + L3(f.xkc, j, i - 1, k));
       xkd = xkd * s.rdxsq * psdotb;
-#define DN(bval, jj, ii) (((bval) * (1.0 / L2(f.psdotb, jj, ii))) / L2(f.msfd, jj, ii))
-      const double du_c = DN(bu_c, j, i), du_jm = DN(bu_jm, j - 1, i), du_jp = DN(bu_jp, j + 1, i), du_im = DN(bu_im, j, i - 1), du_ip = DN(bu_ip, j, i + 1);
-      const double dv_c = DN(bv_c, j, i), dv_jm = DN(bv_jm, j - 1, i), dv_jp = DN(bv_jp, j + 1, i), dv_im = DN(bv_im, j, i - 1), dv_ip = DN(bv_ip, j, i + 1);
+      const double du_c = L3(f.dub, j, i, k), du_jm = L3(f.dub, j - 1, i, k), du_jp = L3(f.dub, j + 1, i, k), du_im = L3(f.dub, j, i - 1, k), du_ip = L3(f.dub, j, i + 1, k);
+      const double dv_c = L3(f.dvb, j, i, k), dv_jm = L3(f.dvb, j - 1, i, k), dv_jp = L3(f.dvb, j + 1, i, k), dv_im = L3(f.dvb, j, i - 1, k), dv_ip = L3(f.dvb, j, i + 1, k);
       if (dint) {
-        const double du_jp2 = DN(L3(f.bu, j + 2, i, k), j + 2, i), du_jm2 = DN(L3(f.bu, j - 2, i, k), j - 2, i);
-        const double du_ip2 = DN(L3(f.bu, j, i + 2, k), j, i + 2), du_im2 = DN(L3(f.bu, j, i - 2, k), j, i - 2);
-        const double dv_jp2 = DN(L3(f.bv, j + 2, i, k), j + 2, i), dv_jm2 = DN(L3(f.bv, j - 2, i, k), j - 2, i);
-        const double dv_ip2 = DN(L3(f.bv, j, i + 2, k), j, i + 2), dv_im2 = DN(L3(f.bv, j, i - 2, k), j, i - 2);
+        const double du_jp2 = L3(f.dub, j + 2, i, k), du_jm2 = L3(f.dub, j - 2, i, k);
+        const double du_ip2 = L3(f.dub, j, i + 2, k), du_im2 = L3(f.dub, j, i - 2, k);
+        const double dv_jp2 = L3(f.dvb, j + 2, i, k), dv_jm2 = L3(f.dvb, j - 2, i, k);
+        const double dv_ip2 = L3(f.dvb, j, i + 2, k), dv_im2 = L3(f.dvb, j, i - 2, k);
         ut = ut - xkd * (1.0 * (du_jp2 + du_jm2 + du_ip2 + du_im2) + (-4.0) * (du_jp + du_jm + du_ip + du_im) + 12.0 * (du_c));
         vt = vt - xkd * (1.0 * (dv_jp2 + dv_jm2 + dv_ip2 + dv_im2) + (-4.0) * (dv_jp + dv_jm + dv_ip + dv_im) + 12.0 * (dv_c));
       }
@@ -151,13 +159,12 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
         ut = ut + xkd * (1.0 * (du_jp + du_jm + du_ip + du_im) + (-4.0) * (du_c));
         vt = vt + xkd * (1.0 * (dv_jp + dv_jm + dv_ip + dv_im) + (-4.0) * (dv_c));
       }
-#undef DN
     }
     // ---- Rayleigh damping toward the boundary fields in the top levels ----
     if (s.ifrayd == 1 && k <= s.kt_ray) {
       const double tau = L3(f.tau_d, j, i, k);
-      ut = ut + tau * ((L3(f.xub0, j, i, k) + xt * L3(f.xubt, j, i, k)) - bu_c);
-      vt = vt + tau * ((L3(f.xvb0, j, i, k) + xt * L3(f.xvbt, j, i, k)) - bv_c);
+      ut = ut + tau * ((L3(f.xub0, j, i, k) + xt * L3(f.xubt, j, i, k)) - L3(f.bu, j, i, k));
+      vt = vt + tau * ((L3(f.xvb0, j, i, k) + xt * L3(f.xvbt, j, i, k)) - L3(f.bv, j, i, k));
     }
     // ---- hand over to the acoustic loop: decouple and premultiply by dts ----
     P3(f.uten, j, i, k) = (ut * rp_c) * s.dts;
