@@ -787,6 +787,14 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
   if ((rc = up3(h, f.pr0, pr0, kzp1)) || (rc = up3(h, f.t0, t0, kzp1)) || (rc = up3(h, f.rho0, rho0, kzp1)) ||
       (rc = up3(h, f.rhof0, rhof0, kzp1)))
     return rc;
+  // dot-point p* on the outermost ghost columns needs cross-point p* one column
+  // further out than the host window reaches: take those values from the rank
+  // that owns them (the reference does the same: psc2psd then exchange)
+  if (c.nproc > 1) {
+    if (h->halo.exchange({{f.psdota - g.sk, 1, 1}, {f.rpsda - g.sk, 1, 1}, {h->psdot_bdy - g.sk, 1, 1}}, RCM_HALO, h->st))
+      return fail(h, RCM_ERR_NCCL, "halo exchange (psdot) failed");
+    CUDA_OK(cudaStreamSynchronize(h->st));
+  }
 
   // ---- rim point lists (global physical boundary rows owned by this rank) ----
   {

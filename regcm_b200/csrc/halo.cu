@@ -50,6 +50,18 @@ struct Nccl {
 Nccl g_nccl;
 const int kNcclDouble = 8, kNcclSum = 0, kNcclMax = 2;
 }  // namespace
+#else
+// Host harness (tests/emu): the transport is a pair of callbacks the test
+// registers (torch.distributed/gloo in tests/test_multirank_emu.py), so that the
+// decomposition, the edge-box arithmetic and the two-phase ordering below are
+// exercised with world_size > 1 on machines without a GPU.
+extern "C" {
+typedef int (*rcm_emu_sendrecv_t)(int peer, const double* sendbuf, long long nsend, double* recvbuf, long long nrecv);
+typedef int (*rcm_emu_allreduce_t)(double* v, int n, int op);
+}
+static rcm_emu_sendrecv_t g_emu_sendrecv = nullptr;
+static rcm_emu_allreduce_t g_emu_allreduce = nullptr;
+extern "C" void rcm_emu_set_transport(rcm_emu_sendrecv_t sr, rcm_emu_allreduce_t ar) { g_emu_sendrecv = sr; g_emu_allreduce = ar; }
 #endif
 
 struct Box {
@@ -108,16 +120,19 @@ int Halo::unique_id(void* out, int out_bytes) {
 }
 
 int Halo::comm_init(const void* id, int id_bytes, std::string& err) {
-#ifdef RCM_EMU
-  (void)id; (void)id_bytes; err = "no NCCL in the host harness"; return -5;
-#else
   if (nproc <= 1) return 0;
+#ifdef RCM_EMU
+  (void)id; (void)id_bytes;
+  if (!g_emu_sendrecv || !g_emu_allreduce) { err = "host harness: no transport registered"; return -5; }
+  comm = (void*)1;
+#else
   if (id_bytes < 128) { err = "NCCL unique id must be 128 bytes"; return -5; }
   if (!g_nccl.load()) { err = "cannot load libnccl.so.2"; return -5; }
   ncclUniqueId_ uid;
   std::memcpy(&uid, id, 128);
   int rc = g_nccl.CommInitRank(&comm, nproc, uid, myid);
   if (rc != 0) { err = std::string("ncclCommInitRank: ") + (g_nccl.ErrStr ? g_nccl.ErrStr(rc) : "error"); return -5; }
+#endif
   const int nj = g.jde2 - g.jde1 + 1 + 2 * RCM_EHALO, ni = g.ide2 - g.ide1 + 1 + 2 * RCM_EHALO;
   cap = (size_t)16 * RCM_HALO * (size_t)std::max(nj, ni) * (size_t)g.kzp1;
   for (int q = 0; q < 4; ++q) {
@@ -127,25 +142,24 @@ int Halo::comm_init(const void* id, int id_bytes, std::string& err) {
   }
   if (cudaMalloc(&red, 16 * sizeof(double)) != cudaSuccess) { err = "halo buffer allocation failed"; return -5; }
   return 0;
-#endif
 }
 
 void Halo::destroy() {
-#ifndef RCM_EMU
   for (int q = 0; q < 4; ++q) { if (sbuf[q]) cudaFree(sbuf[q]); if (rbuf[q]) cudaFree(rbuf[q]); sbuf[q] = rbuf[q] = nullptr; }
   if (red) cudaFree(red);
   red = nullptr;
+#ifndef RCM_EMU
   if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
-  comm = nullptr;
 #endif
+  comm = nullptr;
 }
 
 int Halo::allreduce_host(double* v, int n, int op) {
-#ifdef RCM_EMU
-  (void)v; (void)n; (void)op; return -5;
-#else
   if (nproc <= 1) return 0;
   if (!comm || n > 16) return -5;
+#ifdef RCM_EMU
+  return g_emu_allreduce(v, n, op) ? -5 : 0;
+#else
   if (cudaMemcpy(red, v, n * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) return -5;
   if (g_nccl.AllReduce(red, red, (size_t)n, kNcclDouble, op == 1 ? kNcclMax : kNcclSum, comm, (cudaStream_t)0) != 0) return -5;
   if (cudaStreamSynchronize((cudaStream_t)0) != cudaSuccess) return -5;
@@ -154,7 +168,6 @@ int Halo::allreduce_host(double* v, int n, int op) {
 #endif
 }
 
-#ifndef RCM_EMU
 static int run_phase(Halo& H, BoxList& spack, BoxList& runpack, const long long scount[4], const long long rcount[4],
                      const int nb[4], int side0, cudaStream_t st) {
   if (spack.total > 0) {
@@ -162,6 +175,12 @@ static int run_phase(Halo& H, BoxList& spack, BoxList& runpack, const long long 
     RCM_LAUNCH(k_halo_copy, gr, b, st, spack, 0);
     H.launches++;
   }
+#ifdef RCM_EMU
+  for (int s = side0; s < side0 + 2; ++s) {  // low side first on every rank: the chain of pairwise exchanges cannot deadlock
+    if (nb[s] < 0) continue;
+    if (g_emu_sendrecv(nb[s], H.sbuf[s], scount[s], H.rbuf[s], rcount[s])) return -5;
+  }
+#else
   g_nccl.GroupStart();
   for (int s = side0; s < side0 + 2; ++s) {
     if (nb[s] < 0) continue;
@@ -169,6 +188,7 @@ static int run_phase(Halo& H, BoxList& spack, BoxList& runpack, const long long 
     if (g_nccl.Recv(H.rbuf[s], (size_t)rcount[s], kNcclDouble, nb[s], H.comm, st) != 0) return -5;
   }
   if (g_nccl.GroupEnd() != 0) return -5;
+#endif
   if (runpack.total > 0) {
     dim3 b(256), gr((unsigned)((runpack.total + 255) / 256));
     RCM_LAUNCH(k_halo_copy, gr, b, st, runpack, 1);
@@ -176,13 +196,9 @@ static int run_phase(Halo& H, BoxList& spack, BoxList& runpack, const long long 
   }
   return 0;
 }
-#endif
 
 // sides: 0 = west, 1 = east, 2 = south, 3 = north
 int Halo::exchange(const std::vector<HaloField>& fl, int width, cudaStream_t st) {
-#ifdef RCM_EMU
-  (void)fl; (void)width; (void)st; return 0;
-#else
   if (nproc <= 1) return 0;
   if (!comm) return -5;
   const int nb[4] = {nb_w, nb_e, nb_s, nb_n};
@@ -232,15 +248,11 @@ int Halo::exchange(const std::vector<HaloField>& fl, int width, cudaStream_t st)
     if (run_phase(*this, sp, ru, sc, rcnt, nb, 2, st)) return -5;
   }
   return 0;
-#endif
 }
 
 // width-6 halo of the 2-D estore array (replaces grid_collect + bcast of
 // estore_g, Main/mod_sound.F90:494-495: only +-6 neighbours are ever read)
 int Halo::exchange_estore(const Fields& f, cudaStream_t st) {
-#ifdef RCM_EMU
-  (void)f; (void)st; return 0;
-#else
   if (nproc <= 1) return 0;
   if (!comm) return -5;
   const int nb[4] = {nb_w, nb_e, nb_s, nb_n};
@@ -272,5 +284,4 @@ int Halo::exchange_estore(const Fields& f, cudaStream_t st) {
     if (run_phase(*this, sp, ru, sc, rcnt, nb, 2 * phase, st)) return -5;
   }
   return 0;
-#endif
 }

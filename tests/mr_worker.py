@@ -1,0 +1,140 @@
+"""Worker of the multi-rank tests: one process = one rank = one tile.
+
+Runs the dyn-core on a 2-D decomposition and writes this rank's tile of every
+prognostic to <outdir>/rank<r>.npz.  Two transports:
+  --lib emu   host harness (tests/emu) + torch.distributed/gloo callbacks  (CPU, no GPU)
+  --lib cuda  the product library + NCCL                                   (one GPU per rank)
+Launched by tests/test_multirank_emu.py / test_gpu_multirank.py with RANK,
+WORLD_SIZE, MASTER_ADDR, MASTER_PORT in the environment.
+"""
+import argparse
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from regcm_b200 import capi, synth  # noqa: E402
+
+FIELDS = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PP, capi.F_W)
+
+
+def tile_window(tile, jx, iy, pad=3):
+    j1, j2, i1, i2 = tile
+    return (max(1, j1 - pad), min(jx, j2 + pad), max(1, i1 - pad), min(iy, i2 + pad))
+
+
+def owned_bounds(core, field):
+    """Global index range of the points of `field` this rank owns."""
+    j1, j2, i1, i2 = core.tile()
+    kz = core.kz
+    if field in (capi.F_U, capi.F_V):
+        return (j1, i1, 1), (j2, i2, kz)
+    nk = kz + 1 if field == capi.F_W else kz
+    return (j1, i1, 1), (min(j2, core.jx - 1), min(i2, core.iy - 1), nk)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--lib", choices=("emu", "cuda"), required=True)
+    ap.add_argument("--case", default="tiny")
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--cpus-j", type=int, default=0)
+    ap.add_argument("--cpus-i", type=int, default=0)
+    ap.add_argument("--ibdyfrq", type=int, default=6)
+    ap.add_argument("--work", action="store_true", help="also dump the per-step work arrays")
+    ap.add_argument("--out", required=True)
+    args = ap.parse_args()
+
+    import torch
+    import torch.distributed as dist
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+
+    if args.lib == "emu":
+        lib = capi.CoreLib(os.path.join(ROOT, "tests", "emu", "libregcm_dyn_emu.so"), "rcm_dyn_")
+
+        def as_tensor(ptr, n):
+            arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(n,))
+            return torch.from_numpy(arr)
+
+        @C.CFUNCTYPE(C.c_int, C.c_int, C.c_void_p, C.c_longlong, C.c_void_p, C.c_longlong)
+        def sendrecv(peer, sbuf, ns, rbuf, nr):
+            try:
+                reqs = [dist.isend(as_tensor(sbuf, ns), peer), dist.irecv(as_tensor(rbuf, nr), peer)]
+                for r in reqs:
+                    r.wait()
+                return 0
+            except Exception as e:  # pragma: no cover
+                print("sendrecv failed:", e, flush=True)
+                return 1
+
+        @C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int)
+        def allreduce(v, n, op):
+            try:
+                dist.all_reduce(as_tensor(v, n), op=dist.ReduceOp.MAX if op == 1 else dist.ReduceOp.SUM)
+                return 0
+            except Exception as e:  # pragma: no cover
+                print("allreduce failed:", e, flush=True)
+                return 1
+
+        lib.lib.rcm_emu_set_transport(sendrecv, allreduce)
+        uid = b"\0" * 128
+    else:
+        lib = capi.cuda_lib()
+        box = [capi.nccl_unique_id(lib) if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        uid = box[0]
+
+    base = synth.make_case(args.case, records=(), ibdyfrq=args.ibdyfrq)  # cfg only
+    cfg = base.cfg
+    cfg.nproc, cfg.myid, cfg.cpus_j, cfg.cpus_i = world, rank, args.cpus_j, args.cpus_i
+    if args.lib == "cuda":
+        cfg.device = int(os.environ.get("LOCAL_RANK", rank))
+    core = capi.DynCore(lib, cfg)
+    core.comm_init(uid)
+    win = tile_window(core.tile(), cfg.jx, cfg.iy)
+    case = synth.make_case(args.case, window=win, ibdyfrq=args.ibdyfrq)
+    case.cfg = cfg
+    synth.load_case(core, case, stage_next=True)
+    core.step(args.steps)
+    out = {"tile": np.array(core.tile())}
+    for fld in FIELDS:
+        for lev, tag in ((capi.LEVEL_A, "a"), (capi.LEVEL_B, "b")):
+            lb, ub = owned_bounds(core, fld)
+            out[f"f{fld}{tag}"] = core.get_state(fld, lev, lb=lb, ub=ub)
+            out[f"lb{fld}"] = np.array(lb)
+    if args.work:
+        jx, iy, kz = cfg.jx, cfg.iy, cfg.kz
+        j1, j2, i1, i2 = core.tile()
+        for wid in range(10):
+            if wid in (capi.W_UTEN, capi.W_VTEN):
+                glb, gub = (2, 2, 1), (jx - 1, iy - 1, kz)
+            elif wid == capi.W_PPTEN:
+                glb, gub = (2, 2, 1), (jx - 2, iy - 2, kz)
+            elif wid == capi.W_WTEN:
+                glb, gub = (2, 2, 1), (jx - 2, iy - 2, kz + 1)
+            elif wid == capi.W_QDOT:
+                glb, gub = (1, 1, 1), (jx - 1, iy - 1, kz + 1)
+            else:
+                glb, gub = (1, 1, 1), (jx - 1, iy - 1, kz)
+            lb = (max(glb[0], j1), max(glb[1], i1), 1)
+            ub = (min(gub[0], j2), min(gub[1], i2), gub[2])
+            a = np.zeros(tuple(ub[q] - lb[q] + 1 for q in range(3)), order="F")
+            rc = lib.get_work(core.h, wid, a.ctypes.data_as(C.POINTER(C.c_double)), *capi._bounds(lb, ub))
+            assert rc == 0
+            out[f"w{wid}"] = a
+            out[f"wlb{wid}"] = np.array(lb)
+    d = core.diag()
+    out["max_cfl"] = np.array(d.max_cfl)
+    np.savez(os.path.join(args.out, f"rank{rank}.npz"), **out)
+    core.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
