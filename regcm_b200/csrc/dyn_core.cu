@@ -59,6 +59,7 @@ struct ProfRec { int kid; cudaEvent_t a, b; };
 
 struct rcm_dyn {
   bool prof_on = false;
+  bool overlap_slow = true;  // RCM_OVERLAP=0 serialises the slow-tendency kernels
   std::vector<ProfRec> prof_recs;
   std::vector<cudaEvent_t> prof_pool;
   double prof_ms[KID_COUNT] = {0};
@@ -99,7 +100,8 @@ struct rcm_dyn {
   int nan_flag = 0;
   // stream / timing
   cudaStream_t st = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaStream_t st_b = nullptr, st_c = nullptr;  // side streams: the three slow-tendency kernels are independent
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_jb = nullptr, ev_jc = nullptr;
   int64_t launches = 0;
   double last_ms = 0;
   Halo halo;
@@ -258,6 +260,7 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   h->off3 = h->off2 - g.sk;
   g.esi = ((nj + 2 * RCM_EHALO + 15) / 16) * 16;
   g.pfd = 2;
+  if (const char* e = std::getenv("RCM_OVERLAP")) h->overlap_slow = std::atoi(e) != 0;
   if (const char* e = std::getenv("RCM_PFD")) g.pfd = std::max(0, std::min(8, std::atoi(e)));
   h->eni = ni + 2 * RCM_EHALO;
   h->eoff = -((long long)(g.jde1 - RCM_EHALO) + (long long)g.esi * (g.ide1 - RCM_EHALO));
@@ -315,7 +318,10 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   h->stage.assign((size_t)g.sk * kzp1, 0.0);
 #endif
   cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&h->st_b, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&h->st_c, cudaStreamNonBlocking);
   cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
+  cudaEventCreate(&h->ev_fork); cudaEventCreate(&h->ev_jb); cudaEventCreate(&h->ev_jc);
   h->halo.init(g, c.nproc, c.myid, cj, ci);
   *out = h;
   return RCM_OK;
@@ -962,24 +968,46 @@ static int tend(rcm_dyn* h) {
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
   TIMED(KID_PREP, 1, launch_prep(g, f, s, h->st));
   TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
-  TIMED(KID_UV, 1, launch_uv(g, f, s, h->st));
-  TIMED(KID_TQ, 1, launch_tq(g, f, s, h->st));
-  TIMED(KID_PPW, 1, launch_ppw(g, f, s, h->st));
+  if (h->prof_on || !h->overlap_slow) {
+    TIMED(KID_UV, 1, launch_uv(g, f, s, h->st));
+    TIMED(KID_TQ, 1, launch_tq(g, f, s, h->st));
+    TIMED(KID_PPW, 1, launch_ppw(g, f, s, h->st));
+  } else {
+    // k_uv, k_tq, k_ppw read the same inputs and write disjoint outputs: run
+    // them side by side so that one kernel's tail wave is filled by the others
+    CUDA_OK(cudaEventRecord(h->ev_fork, h->st));
+    CUDA_OK(cudaStreamWaitEvent(h->st_b, h->ev_fork, 0));
+    CUDA_OK(cudaStreamWaitEvent(h->st_c, h->ev_fork, 0));
+    launch_tq(g, f, s, h->st);
+    launch_ppw(g, f, s, h->st_b);
+    launch_uv(g, f, s, h->st_c);
+    h->launches += 3;
+    CUDA_OK(cudaEventRecord(h->ev_jb, h->st_b));
+    CUDA_OK(cudaEventRecord(h->ev_jc, h->st_c));
+    CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jb, 0));
+    CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jc, 0));
+  }
   TIMED(KID_SND_INIT, 1, launch_snd_init(g, f, s, h->st));
-  if ((rc = exch_sound_pp(h))) return rc;
+  TIMED(KID_HALO, 0, rc = exch_sound_pp(h));
+  if (rc) return rc;
   for (int it = 1; it <= istep; ++it) {
     s.it = it;
     TIMED(KID_SND_UV, 1, launch_snd_uv(g, f, s, h->st));
-    if ((rc = exch_sound_uv(h))) return rc;
+    TIMED(KID_HALO, 0, rc = exch_sound_uv(h));
+    if (rc) return rc;
     TIMED(KID_SND_WFWD, 1, launch_snd_wfwd(g, f, s, h->st));
     if (h->cfg.ifupr == 1) {
-      if ((rc = exch_estore(h))) return rc;
+      TIMED(KID_HALO, 0, rc = exch_estore(h));
+      if (rc) return rc;
       if (h->day_now == h->model_time && it == 1)
         if ((rc = update_tmask(h))) return rc;
     }
     TIMED(KID_SND_WPVAL, 1, launch_snd_wpval(g, f, s, h->st));
     TIMED(KID_SND_WBACK, 1, launch_snd_wback(g, f, s, h->st));
-    if (it < istep && (rc = exch_sound_pp(h))) return rc;
+    if (it < istep) {
+      TIMED(KID_HALO, 0, rc = exch_sound_pp(h));
+      if (rc) return rc;
+    }
   }
   TIMED(KID_SND_FINAL, 1, launch_snd_final(g, f, s, h->st));
   // swap in the filtered t, qv, qc (the old buffers keep the previous rim)
@@ -1007,7 +1035,8 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
       if ((rc = bdyin(h))) break;
     }
     // after the swap in tend(): n?? hold the previous level-a buffers
-    if ((rc = exch_state(h))) break;
+    TIMED(KID_HALO, 0, rc = exch_state(h));
+    if (rc) break;
     if ((rc = bdyval(h, f.nat, f.naqv, f.naqc))) break;
   }
   CUDA_OK(cudaEventRecord(h->ev1, h->st));
@@ -1017,6 +1046,7 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
   h->last_ms = ms;
   prof_collect(h);
   if (rc) return rc;
+  if (h->halo.take_error()) return fail(h, RCM_ERR_NCCL, "halo exchange: timed out waiting for a neighbour's edge data");
   unsigned long long bits2[2] = {0, 0}, nq = 0; int nanf = 0;
   CUDA_OK(cudaMemcpy(bits2, f.cflbits, sizeof(bits2), cudaMemcpyDeviceToHost));
   CUDA_OK(cudaMemcpy(&nq, f.negq, sizeof(nq), cudaMemcpyDeviceToHost));
@@ -1162,6 +1192,9 @@ extern "C" int rcm_dyn_destroy(rcm_dyn* h) {
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->st) cudaStreamDestroy(h->st);
+  if (h->st_b) cudaStreamDestroy(h->st_b);
+  if (h->st_c) cudaStreamDestroy(h->st_c);
+  for (cudaEvent_t e : {h->ev_fork, h->ev_jb, h->ev_jc}) if (e) cudaEventDestroy(e);
   delete h;
   return RCM_OK;
 }

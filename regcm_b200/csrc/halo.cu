@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "launch.h"
@@ -20,6 +21,7 @@ typedef int (*fn_CommDestroy)(void*);
 typedef int (*fn_Group)(void);
 typedef int (*fn_SendRecv)(void*, size_t, int, int, void*, cudaStream_t);
 typedef int (*fn_AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*fn_AllGather)(const void*, void*, size_t, int, void*, cudaStream_t);
 typedef const char* (*fn_ErrStr)(int);
 struct Nccl {
   void* lib = nullptr;
@@ -29,6 +31,7 @@ struct Nccl {
   fn_Group GroupStart = nullptr, GroupEnd = nullptr;
   fn_SendRecv Send = nullptr, Recv = nullptr;
   fn_AllReduce AllReduce = nullptr;
+  fn_AllGather AllGather = nullptr;
   fn_ErrStr ErrStr = nullptr;
   bool load() {
     if (lib) return true;
@@ -43,12 +46,13 @@ struct Nccl {
     Send = (fn_SendRecv)dlsym(lib, "ncclSend");
     Recv = (fn_SendRecv)dlsym(lib, "ncclRecv");
     AllReduce = (fn_AllReduce)dlsym(lib, "ncclAllReduce");
+    AllGather = (fn_AllGather)dlsym(lib, "ncclAllGather");
     ErrStr = (fn_ErrStr)dlsym(lib, "ncclGetErrorString");
     return GetUniqueId && CommInitRank && CommDestroy && GroupStart && GroupEnd && Send && Recv && AllReduce;
   }
 };
 Nccl g_nccl;
-const int kNcclDouble = 8, kNcclSum = 0, kNcclMax = 2;
+const int kNcclDouble = 8, kNcclChar = 0, kNcclSum = 0, kNcclMax = 2;
 }  // namespace
 #else
 // Host harness (tests/emu): the transport is a pair of callbacks the test
@@ -141,6 +145,9 @@ int Halo::comm_init(const void* id, int id_bytes, std::string& err) {
     }
   }
   if (cudaMalloc(&red, 16 * sizeof(double)) != cudaSuccess) { err = "halo buffer allocation failed"; return -5; }
+#ifndef RCM_EMU
+  if (setup_p2p(err)) return -5;
+#endif
   return 0;
 }
 
@@ -149,9 +156,30 @@ void Halo::destroy() {
   if (red) cudaFree(red);
   red = nullptr;
 #ifndef RCM_EMU
+  for (int d = 0; d < 8; ++d) {
+    bool first = peer_block[d] != nullptr;
+    for (int q = 0; q < d; ++q) if (peer_block[q] == peer_block[d]) first = false;
+    if (first) cudaIpcCloseMemHandle(peer_block[d]);
+    peer_block[d] = nullptr;
+  }
+  if (pblock) cudaFree(pblock);
+  if (errflag) cudaFree(errflag);
+  pblock = nullptr; errflag = nullptr; p2p = false;
   if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
 #endif
   comm = nullptr;
+}
+
+int Halo::take_error() {
+#ifdef RCM_EMU
+  return 0;
+#else
+  if (!p2p || !errflag) return 0;
+  int e = 0;
+  if (cudaMemcpy(&e, errflag, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return 1;
+  if (e) cudaMemset(errflag, 0, sizeof(int));
+  return e;
+#endif
 }
 
 int Halo::allreduce_host(double* v, int n, int op) {
@@ -197,10 +225,237 @@ static int run_phase(Halo& H, BoxList& spack, BoxList& runpack, const long long 
   return 0;
 }
 
+
+#ifndef RCM_EMU
+// ===========================================================================
+// NVLink peer-memory transport (see halo.h).  Directions: 0 W, 1 E, 2 S, 3 N,
+// 4 SW, 5 SE, 6 NW, 7 NE; the opposite of d is kOpp[d].
+namespace {
+const int kOpp[8] = {1, 0, 3, 2, 7, 6, 5, 4};
+const int kDj[8] = {-1, 1, 0, 0, -1, 1, -1, 1};
+const int kDi[8] = {0, 0, -1, 1, -1, -1, 1, 1};
+
+struct XField {
+  double* p;     // element (j,i,kk) = p[j + si*i + sk*kk], kk from 0
+  long long sk;
+  int si, nk, grid;  // grid: 0 cross, 1 dot, 2 estore
+};
+struct XList {
+  XField f[16];
+  int nf;
+  int s_ja[8][3], s_ia[8][3], r_ja[8][3], r_ia[8][3], nj[8][3], ni[8][3];
+  double* sendbuf[8];                 // neighbour's receive buffer for what I send towards d
+  double* recvbuf[8];                 // my receive buffer for what arrives from d
+  unsigned long long* flag_peer[8];   // neighbour's arrival flag for my message
+  unsigned long long* flag_mine;      // my 8 arrival flags
+  unsigned long long seq;
+  unsigned int* done;                 // block counter of the pack kernel
+  int* err;
+  int active[8];
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// offset (doubles) of field fi inside the message of direction d
+__device__ __forceinline__ long long x_offset(const XList& L, int d, int fi) {
+  long long off = 0;
+  for (int q = 0; q < fi; ++q) {
+    const int gq = L.f[q].grid;
+    off += (long long)L.nj[d][gq] * L.ni[d][gq] * L.f[q].nk;
+  }
+  return off;
+}
+
+// pack: own edge cells -> the neighbour's receive buffer (stores over NVLink);
+// the last block to finish raises the neighbours' arrival flags.
+__global__ void __launch_bounds__(256) k_x_pack(const XList L) {
+  const int d = blockIdx.z, fi = blockIdx.y;
+  if (L.active[d]) {
+    const XField F = L.f[fi];
+    const int nj = L.nj[d][F.grid], ni = L.ni[d][F.grid];
+    const long long n = (long long)nj * ni * F.nk;
+    const long long off = x_offset(L, d, fi);
+    const int ja = L.s_ja[d][F.grid], ia = L.s_ia[d][F.grid];
+    double* dst = L.sendbuf[d] + off;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+      const int jj = (int)(t % nj);
+      const long long r2 = t / nj;
+      const int ii = (int)(r2 % ni), kk = (int)(r2 / ni);
+      dst[t] = F.p[(long long)(ja + jj) + (long long)(ia + ii) * F.si + (long long)kk * F.sk];
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int total = gridDim.x * gridDim.y * gridDim.z;
+    if (atomicAdd(L.done, 1u) == total - 1) {
+      *L.done = 0;
+      __threadfence_system();
+      for (int q = 0; q < 8; ++q)
+        if (L.active[q]) st_release_sys(L.flag_peer[q], L.seq);
+    }
+  }
+}
+
+// unpack: wait for the message of this block's direction, then copy it into the ghost cells
+__global__ void __launch_bounds__(256) k_x_unpack(const XList L) {
+  const int d = blockIdx.z, fi = blockIdx.y;
+  if (!L.active[d]) return;
+  if (threadIdx.x == 0) {
+    const long long t0 = clock64();
+    while (ld_acquire_sys(L.flag_mine + d) < L.seq) {
+      if (clock64() - t0 > 20000000000LL) { atomicExch(L.err, 1); break; }  // ~10 s: report instead of hanging
+    }
+  }
+  __syncthreads();
+  const XField F = L.f[fi];
+  const int nj = L.nj[d][F.grid], ni = L.ni[d][F.grid];
+  const long long n = (long long)nj * ni * F.nk;
+  const long long off = x_offset(L, d, fi);
+  const int ja = L.r_ja[d][F.grid], ia = L.r_ia[d][F.grid];
+  const double* src = L.recvbuf[d] + off;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+    const int jj = (int)(t % nj);
+    const long long r2 = t / nj;
+    const int ii = (int)(r2 % ni), kk = (int)(r2 / ni);
+    F.p[(long long)(ja + jj) + (long long)(ia + ii) * F.si + (long long)kk * F.sk] = __ldcv(src + t);
+  }
+}
+const size_t kFlagBytes = 256;
+}  // namespace
+
+int Halo::setup_p2p(std::string& err) {
+  p2p = false;
+  if (const char* e = std::getenv("RCM_HALO")) { if (std::strcmp(e, "nccl") == 0) return 0; }
+  if (!g_nccl.AllGather) return 0;
+  // neighbours in the 8 directions
+  for (int d = 0; d < 8; ++d) {
+    const int qj = pj + kDj[d], qi = pi + kDi[d];
+    nb8[d] = (qj >= 0 && qj < cj && qi >= 0 && qi < ci) ? qj + cj * qi : -1;
+  }
+  struct Card { char bus[32]; cudaIpcMemHandle_t h; int ok; };
+  Card mine{};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (cudaDeviceGetPCIBusId(mine.bus, sizeof(mine.bus), dev) != cudaSuccess) mine.bus[0] = 0;
+  pcap = cap;
+  const size_t bytes = kFlagBytes + (size_t)16 * pcap * sizeof(double);
+  mine.ok = (cudaMalloc(&pblock, bytes) == cudaSuccess) && (cudaMemset(pblock, 0, bytes) == cudaSuccess) &&
+            (cudaMalloc(&errflag, 2 * sizeof(int)) == cudaSuccess) && (cudaMemset(errflag, 0, 2 * sizeof(int)) == cudaSuccess) &&
+            (cudaIpcGetMemHandle(&mine.h, pblock) == cudaSuccess);
+  cudaDeviceSynchronize();
+  // gather every rank's card
+  Card* dcards = nullptr;
+  std::vector<Card> cards(nproc);
+  if (cudaMalloc(&dcards, sizeof(Card) * (nproc + 1)) != cudaSuccess) { err = "p2p: allocation failed"; return -5; }
+  cudaMemcpy(dcards + nproc, &mine, sizeof(Card), cudaMemcpyHostToDevice);
+  if (g_nccl.AllGather(dcards + nproc, dcards, sizeof(Card), kNcclChar, comm, (cudaStream_t)0) != 0 ||
+      cudaStreamSynchronize((cudaStream_t)0) != cudaSuccess) { cudaFree(dcards); err = "p2p: allgather failed"; return -5; }
+  cudaMemcpy(cards.data(), dcards, sizeof(Card) * nproc, cudaMemcpyDeviceToHost);
+  cudaFree(dcards);
+  bool good = true;
+  for (int r = 0; r < nproc; ++r) {
+    if (!cards[r].ok || cards[r].bus[0] == 0) good = false;
+    for (int q = 0; q < r; ++q)
+      if (std::strncmp(cards[r].bus, cards[q].bus, sizeof(mine.bus)) == 0) good = false;  // two ranks on one GPU: no spin-waits
+  }
+  double okv = good ? 1.0 : 0.0;
+  if (good) {
+    for (int d = 0; d < 8 && okv > 0; ++d) {
+      if (nb8[d] < 0) continue;
+      // the same neighbour can appear in several directions only on degenerate layouts; map each once
+      bool mapped = false;
+      for (int q = 0; q < d; ++q) if (nb8[q] == nb8[d]) { peer_block[d] = peer_block[q]; mapped = true; }
+      if (mapped) continue;
+      void* pp = nullptr;
+      if (cudaIpcOpenMemHandle(&pp, cards[nb8[d]].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { okv = 0.0; cudaGetLastError(); break; }
+      peer_block[d] = (char*)pp;
+    }
+  }
+  double vmin = -okv;  // min over ranks via max of the negative
+  if (allreduce_host(&vmin, 1, 1)) { err = "p2p: allreduce failed"; return -5; }
+  p2p = (vmin == -1.0);
+  if (!p2p) {
+    for (int d = 0; d < 8; ++d) {
+      bool first = peer_block[d] != nullptr;
+      for (int q = 0; q < d; ++q) if (peer_block[q] == peer_block[d]) first = false;
+      if (first) cudaIpcCloseMemHandle(peer_block[d]);
+      peer_block[d] = nullptr;
+    }
+  }
+  return 0;
+}
+
+int Halo::exchange_p2p(const std::vector<HaloField>& fl, int width, int estore, const Fields* ff, cudaStream_t st) {
+  XList L{};
+  const int w = width;
+  if (estore) {
+    L.nf = 1;
+    L.f[0].p = ff->estore; L.f[0].si = g.esi; L.f[0].sk = 0; L.f[0].nk = 1; L.f[0].grid = 2;
+  } else {
+    if (fl.size() > 16) return -5;
+    L.nf = (int)fl.size();
+    for (int q = 0; q < L.nf; ++q) {
+      L.f[q].p = fl[q].p + g.sk; L.f[q].si = g.si; L.f[q].sk = g.sk; L.f[q].nk = fl[q].nk; L.f[q].grid = fl[q].dot ? 1 : 0;
+    }
+  }
+  const int J1[3] = {g.jce1, g.jde1, g.jci1}, J2[3] = {g.jce2, g.jde2, g.jci2};
+  const int I1[3] = {g.ice1, g.ide1, g.ici1}, I2[3] = {g.ice2, g.ide2, g.ici2};
+  long long maxn = 0;
+  ++seq;
+  const int par = (int)(seq & 1ULL);
+  for (int d = 0; d < 8; ++d) {
+    L.active[d] = nb8[d] >= 0;
+    long long msg = 0;
+    for (int t = 0; t < 3; ++t) {
+      const int j1 = J1[t], j2 = J2[t], i1 = I1[t], i2 = I2[t];
+      const int dj = kDj[d], di = kDi[d];
+      L.nj[d][t] = dj == 0 ? j2 - j1 + 1 : w;
+      L.ni[d][t] = di == 0 ? i2 - i1 + 1 : w;
+      L.s_ja[d][t] = dj < 0 ? j1 : (dj > 0 ? j2 - w + 1 : j1);
+      L.s_ia[d][t] = di < 0 ? i1 : (di > 0 ? i2 - w + 1 : i1);
+      L.r_ja[d][t] = dj < 0 ? j1 - w : (dj > 0 ? j2 + 1 : j1);
+      L.r_ia[d][t] = di < 0 ? i1 - w : (di > 0 ? i2 + 1 : i1);
+    }
+    if (!L.active[d]) continue;
+    for (int q = 0; q < L.nf; ++q) {
+      const long long n = (long long)L.nj[d][L.f[q].grid] * L.ni[d][L.f[q].grid] * L.f[q].nk;
+      msg += n; maxn = std::max(maxn, n);
+    }
+    if ((size_t)msg > pcap) return -5;
+    const int od = kOpp[d];
+    L.sendbuf[d] = (double*)(peer_block[d] + kFlagBytes) + ((size_t)par * 8 + od) * pcap;
+    L.recvbuf[d] = (double*)(pblock + kFlagBytes) + ((size_t)par * 8 + d) * pcap;
+    L.flag_peer[d] = (unsigned long long*)peer_block[d] + od;
+  }
+  L.flag_mine = (unsigned long long*)pblock;
+  L.seq = seq;
+  L.done = (unsigned int*)(errflag + 1);
+  L.err = errflag;
+  if (maxn == 0) return 0;
+  const unsigned gx = (unsigned)std::min<long long>((maxn + 255) / 256, 64);
+  dim3 b(256), gr(gx, (unsigned)L.nf, 8);
+  k_x_pack<<<gr, b, 0, st>>>(L);
+  k_x_unpack<<<gr, b, 0, st>>>(L);
+  launches += 2;
+  return cudaGetLastError() == cudaSuccess ? 0 : -5;
+}
+#endif
+
 // sides: 0 = west, 1 = east, 2 = south, 3 = north
 int Halo::exchange(const std::vector<HaloField>& fl, int width, cudaStream_t st) {
   if (nproc <= 1) return 0;
   if (!comm) return -5;
+#ifndef RCM_EMU
+  if (p2p) return exchange_p2p(fl, width, 0, nullptr, st);
+#endif
   const int nb[4] = {nb_w, nb_e, nb_s, nb_n};
   const int w = width;
   // ---- phase 1: west/east, own rows only ----
@@ -255,6 +510,9 @@ int Halo::exchange(const std::vector<HaloField>& fl, int width, cudaStream_t st)
 int Halo::exchange_estore(const Fields& f, cudaStream_t st) {
   if (nproc <= 1) return 0;
   if (!comm) return -5;
+#ifndef RCM_EMU
+  if (p2p) return exchange_p2p({}, RCM_EHALO, 1, &f, st);
+#endif
   const int nb[4] = {nb_w, nb_e, nb_s, nb_n};
   const int w = RCM_EHALO;
   // estore is addressed as p[j + esi*i]; present it to the generic copier as a

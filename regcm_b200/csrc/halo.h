@@ -27,6 +27,23 @@ struct Halo {
   double* red = nullptr;      // small device buffer for scalar reductions
   long long launches = 0;
 
+  // ---- NVLink peer-memory transport (one GPU per rank, all on one node) ----
+  // Each rank owns one device block: 2 parities x 8 directions of receive
+  // buffers + 8 arrival flags.  It is exported with CUDA IPC, so that the pack
+  // kernel of a neighbour stores its edge straight into this rank's receive
+  // buffer over NVLink and then raises the flag; the unpack kernel waits on the
+  // flags.  One phase, 8 neighbours, no NCCL call on the step path.
+  bool p2p = false;
+  char* pblock = nullptr;          // my block
+  char* peer_block[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // neighbour blocks (mapped)
+  int nb8[8] = {-1, -1, -1, -1, -1, -1, -1, -1};  // W, E, S, N, SW, SE, NW, NE
+  size_t pcap = 0;                 // doubles per (parity, direction) buffer
+  unsigned long long seq = 0;      // exchange sequence number (flag value)
+  int* errflag = nullptr;          // device: set when a wait timed out
+  int setup_p2p(std::string& err);
+  int take_error();                // 1 if a wait on a neighbour timed out since the last call
+  int exchange_p2p(const std::vector<HaloField>& fl, int width, int estore, const Fields* f, cudaStream_t st);
+
   void init(const Geom& g_, int nproc_, int myid_, int cj_, int ci_);
   int comm_init(const void* id, int id_bytes, std::string& err);
   static int unique_id(void* out, int out_bytes);
