@@ -30,7 +30,7 @@ ALG_BYTES_STEP = lambda istep: 352 + 192 * istep  # noqa: E731
 # read + written by that kernel), listed in DESIGN.md §Kernels
 ALG_BYTES_KERNEL = {
     "k_prep": 104, "k_xkc": 48, "k_uv": 80, "k_tq": 144, "k_ppw": 136, "k_snd_init": 88,
-    "k_snd_uv": 80, "k_snd_wfwd": 120, "k_snd_wback": 168, "k_snd_final": 160,
+    "k_snd_uv": 80, "k_snd_wfwd": 128, "k_snd_wback": 168, "k_snd_final": 160,
 }
 
 

@@ -40,7 +40,7 @@
 #define RCM_MB_UV 4
 #endif
 #ifndef RCM_MB_TQ
-#define RCM_MB_TQ 4
+#define RCM_MB_TQ 6
 #endif
 #ifndef RCM_MB_PPW
 #define RCM_MB_PPW 4

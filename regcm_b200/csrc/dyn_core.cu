@@ -278,7 +278,7 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   for (double** p : {&f.au, &f.av, &f.at, &f.aqv, &f.aqc, &f.app, &f.aw, &f.bu, &f.bv, &f.bt, &f.bqv, &f.bqc, &f.bpp,
                      &f.bw, &f.nat, &f.naqv, &f.naqc, &f.nbt, &f.nbqv, &f.nbqc, &f.xub0, &f.xubt, &f.xvb0, &f.xvbt,
                      &f.xtb0, &f.xtbt, &f.xqb0, &f.xqbt, &f.xpb0, &f.xpbt, &f.xwb0, &f.xwbt, &f.pr0, &f.t0, &f.rho0,
-                     &f.rhof0, &f.pr1, &f.rho1, &f.th, &f.qdot, &f.cr, &f.xkc, &f.dub, &f.dvb, &f.uten, &f.vten, &f.ppten, &f.wten,
+                     &f.rhof0, &f.pr1, &f.rho1, &f.th, &f.qdot, &f.cr, &f.xkc, &f.dub, &f.dvb, &f.scc, &f.scdd, &f.sca, &f.uten, &f.vten, &f.ppten, &f.wten,
                      &f.cu, &f.cv, &f.cpp, &f.cppd, &f.cw, &f.ct, &f.se, &f.sf})
     A3(*p);
   for (int q = 0; q < 6; ++q) { A3(h->b1[q]); A3(h->nx[q]); }

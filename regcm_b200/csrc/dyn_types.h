@@ -77,6 +77,7 @@ struct Fields {
   double *tau_c, *tau_d, *tau_f;  // same geometry, levels 1..rayndamp
   // slow-part work fields
   double *pr1, *rho1, *th, *qdot, *cr, *xkc;
+  double *scc, *scdd, *sca;  // per-step invariants of the implicit w solve (k_snd_wfwd, first sub-step)
   double *dub, *dvb;  // level-b winds decoupled and divided by the dot map factor (operands of diffu_d)
   double *uten, *vten, *ppten, *wten;
   // acoustic work fields

@@ -83,6 +83,10 @@ struct SndLevel {
   double tk, cc, cdd, cj, ptend, pp, wo;
 };
 
+// FIRST = first sub-step of a model step: the coefficients that do not change
+// during the step (cc, cdd and ca: 4 of the 10 divisions per level) are computed
+// and stored; the later sub-steps load them instead of pr1 and rho1.
+template <bool FIRST>
 __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_WFWD)
 k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
@@ -95,9 +99,11 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
 
   // request level kk of every streamed field into L2 (see PF3)
   auto prefetch = [&](int kk) {
-    PF3(f.cu, j, i, kk); PF3(f.cv, j, i, kk); PF3(f.pr1, j, i, kk); PF3(f.rho0, j, i, kk);
+    PF3(f.cu, j, i, kk); PF3(f.cv, j, i, kk); PF3(f.rho0, j, i, kk);
     PF3(f.pr0, j, i, kk); PF3(f.t0, j, i, kk); PF3(f.nbt, j, i, kk); PF3(f.ppten, j, i, kk);
-    PF3(f.cpp, j, i, kk); PF3(f.cw, j, i, kk); PF3(f.rho1, j, i, kk); PF3(f.wten, j, i, kk);
+    PF3(f.cpp, j, i, kk); PF3(f.cw, j, i, kk); PF3(f.wten, j, i, kk);
+    if (FIRST) { PF3(f.pr1, j, i, kk); PF3(f.rho1, j, i, kk); }
+    else { PF3(f.scc, j, i, kk); PF3(f.scdd, j, i, kk); PF3(f.sca, j, i, kk); }
   };
   const int pfd = g.pfd;
   if (pfd > 0)
@@ -117,11 +123,13 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
   // the divisions below carry slow-path branches that end the basic block, and a
   // load placed after one would cost its own memory round trip.
   struct Raw {
-    double pr1, rho0, rho1, t0, nbt, ppten, pp, wo, p0w, p0e, p0s, p0n, ds;
+    double pr1, rho0, rho1, t0, nbt, ppten, pp, wo, p0w, p0e, p0s, p0n, ds;  // pr1 = cc, rho1 = cdd when !FIRST
   };
   auto loadraw = [&](int m) {
     Raw r;
-    r.pr1 = L3(f.pr1, j, i, m); r.rho0 = L3(f.rho0, j, i, m); r.rho1 = L3(f.rho1, j, i, m);
+    r.rho0 = L3(f.rho0, j, i, m);
+    if (FIRST) { r.pr1 = L3(f.pr1, j, i, m); r.rho1 = L3(f.rho1, j, i, m); }
+    else { r.pr1 = L3(f.scc, j, i, m); r.rho1 = L3(f.scdd, j, i, m); }
     r.t0 = L3(f.t0, j, i, m); r.nbt = L3(f.nbt, j, i, m); r.ppten = L3(f.ppten, j, i, m);
     r.pp = L3(f.cpp, j, i, m); r.wo = L3(f.cw, j, i, m);
     r.p0w = L3(f.pr0, j - 1, i, m); r.p0e = L3(f.pr0, j + 1, i, m);
@@ -135,8 +143,15 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
   // build the k-local record of level m; needs u,v at m+1 (or kz), m, m-1 (or 1)
   auto build = [&](int m, const Raw& r, SndLevel& L) {
     L.tk = (0.5 * ps0 * r.t0) / (xgamma * p0_c * r.nbt * rpsb);
-    L.cc = xgamma * r.pr1 * dts / (dx * msfx);
-    L.cdd = xgamma * r.pr1 * r.rho0 * egrav * dts / (ps0 * r.ds);
+    if (FIRST) {
+      L.cc = xgamma * r.pr1 * dts / (dx * msfx);
+      L.cdd = xgamma * r.pr1 * r.rho0 * egrav * dts / (ps0 * r.ds);
+      P3(f.scc, j, i, m) = L.cc;
+      P3(f.scdd, j, i, m) = L.cdd;
+    } else {
+      L.cc = r.pr1;
+      L.cdd = r.rho1;
+    }
     L.cj = 0.5 * r.rho0 * egrav * dts;
     double pxup, pyvp;
     if (m == 1) {
@@ -195,6 +210,7 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
     const Raw rm = loadraw(km1);
     const double p0_n = (km1 >= 2) ? L3(f.pr0, j, i, k - 2) : 0.0;
     const double wten_k = L3(f.wten, j, i, k);
+    const double ca_ld = FIRST ? 0.0 : L3(f.sca, j, i, k);
     // shift the wind and p0 windows down one level and build the record of k-1
 #pragma unroll
     for (int q = 0; q < 4; ++q) { up_[q] = uc_[q]; vp_[q] = vc_[q]; uc_[q] = um_[q]; vc_[q] = vm_[q]; }
@@ -207,8 +223,14 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
     build(km1, rm, Lm);
     // ---- coefficients of level k (:373-401) ----
     const double rho0_m = rm.rho0, rho1_m = rm.rho1, dsm = rm.ds;
-    const double rofac = (dsm * rho0_k + dsk * rho0_m) / (dsm * rho1_k + dsk * rho1_m);
-    const double ca = egrav * dts / (p0_k - p0_c) * rofac;
+    double ca;
+    if (FIRST) {
+      const double rofac = (dsm * rho0_k + dsk * rho0_m) / (dsm * rho1_k + dsk * rho1_m);
+      ca = egrav * dts / (p0_k - p0_c) * rofac;
+      P3(f.sca, j, i, k) = ca;
+    } else {
+      ca = ca_ld;
+    }
     const double g1 = 1.0 - dsm * Lk.tk;
     const double g2 = 1.0 + dsk * Lm.tk;
     const double c = -ca * (Lm.cdd - Lm.cj) * g2 * bpxbp;
@@ -295,7 +317,7 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
     r.v0 = L3(f.cv, j, i, k); r.v1 = L3(f.cv, j, i + 1, k); r.v2 = L3(f.cv, j + 1, i, k); r.v3 = L3(f.cv, j + 1, i + 1, k);
     r.rhof0 = L3(f.rhof0, j, i, k);
     r.cpp = P3(f.cpp, j, i, k); r.cppd = P3(f.cppd, j, i, k);
-    r.pr1 = L3(f.pr1, j, i, k); r.rho0 = L3(f.rho0, j, i, k); r.rho1 = L3(f.rho1, j, i, k);
+    r.pr1 = L3(f.scdd, j, i, k); r.rho0 = L3(f.rho0, j, i, k); r.rho1 = L3(f.rho1, j, i, k);  // pr1 <- cdd (k_snd_wfwd)
     r.ppten = L3(f.ppten, j, i, k); r.nbqv = L3(f.nbqv, j, i, k);
     r.nbt = P3(f.nbt, j, i, k); r.nat = P3(f.nat, j, i, k);
     r.pr0 = L3(f.pr0, j, i, k);
@@ -306,7 +328,7 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
   // request level kk of every streamed field into L2
   auto prefetch = [&](int kk) {
     PF3(f.se, j, i, kk); PF3(f.sf, j, i, kk); PF3(f.cu, j, i, kk); PF3(f.cv, j, i, kk);
-    PF3(f.rhof0, j, i, kk); PF3(f.cpp, j, i, kk); PF3(f.cppd, j, i, kk); PF3(f.pr1, j, i, kk);
+    PF3(f.rhof0, j, i, kk); PF3(f.cpp, j, i, kk); PF3(f.cppd, j, i, kk); PF3(f.scdd, j, i, kk);
     PF3(f.rho0, j, i, kk); PF3(f.rho1, j, i, kk); PF3(f.ppten, j, i, kk); PF3(f.nbqv, j, i, kk);
     PF3(f.nbt, j, i, kk); PF3(f.nat, j, i, kk); PF3(f.pr0, j, i, kk);
   };
@@ -335,7 +357,7 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
     ucrs_m = ucrs; vcrs_m = vcrs;
     // ---- new pressure and temperature correction (:669-689) ----
     const double ppold = c.cpp;
-    const double cddtmp = xgamma * c.pr1 * c.rho0 * egrav * dts / (ps0 * c.ds);
+    const double cddtmp = c.pr1;  // xgamma*pr1*rho0*egrav*dts/(ps0*dsigma), stored by k_snd_wfwd
     const double cjtmp = c.rho0 * egrav * dts * 0.5;
     const double ppn = c.cppd + (cjtmp * (w_n + w_k) + cddtmp * (w_n - w_k)) * bp;
     const double pi = ppn - ppold - c.ppten;
@@ -434,7 +456,8 @@ void launch_snd_uv(const Geom& g, const Fields& f, const StepScalars& s, cudaStr
 void launch_snd_wfwd(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
   const dim3 b = rcm::col_block(); dim3 gr((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y);
-  RCM_LAUNCH(k_snd_wfwd, gr, b, st, g, f, s);
+  if (s.it == 1) RCM_LAUNCH(k_snd_wfwd<true>, gr, b, st, g, f, s);
+  else RCM_LAUNCH(k_snd_wfwd<false>, gr, b, st, g, f, s);
 }
 void launch_snd_wpval(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
