@@ -32,7 +32,6 @@ void launch_snd_init(const Geom&, const Fields&, const StepScalars&, cudaStream_
 void launch_snd_uv(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_xkc(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_wfwd(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
-void launch_snd_wpval(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_wback(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_final(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_couple(const Geom&, double*, const double*, int, int, int, int, int, cudaStream_t);
@@ -1002,7 +1001,6 @@ static int tend(rcm_dyn* h) {
       if (h->day_now == h->model_time && it == 1)
         if ((rc = update_tmask(h))) return rc;
     }
-    TIMED(KID_SND_WPVAL, 1, launch_snd_wpval(g, f, s, h->st));
     TIMED(KID_SND_WBACK, 1, launch_snd_wback(g, f, s, h->st));
     if (it < istep) {
       TIMED(KID_HALO, 0, rc = exch_sound_pp(h));

@@ -267,26 +267,6 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
 }
 
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-k_snd_wpval(const Geom g, const Fields f, const StepScalars s) {
-  const int si = g.si;
-  const int j = g.jci1 + blockIdx.x * 32 + threadIdx.x;
-  const int i = g.ici1 + blockIdx.y * 8 + threadIdx.y;
-  if (j > g.jci2 || i > g.ici2) return;
-  double wp = 0.0;
-  if (s.ifupr == 1) {
-    for (int nsi = -6; nsi <= 6; ++nsi) {
-      const int inn = min(max(g.icross1 + 1, i + nsi), g.icross2 - 1);
-      for (int nsj = -6; nsj <= 6; ++nsj) {
-        const int jnn = min(max(g.jcross1 + 1, j + nsj), g.jcross2 - 1);
-        wp = wp + f.estore[(long long)jnn + (long long)inn * g.esi] * LD1(&f.tmask[(nsj + 6) + 13 * (nsi + 6)]);
-      }
-    }
-  }
-  P2(f.wpval, j, i) = wp;
-}
-
-// ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_WBACK)
 k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
@@ -335,7 +315,21 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
   const int pfd = g.pfd;
   if (pfd > 0)
     for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
-  double w_k = L2(f.wpval, j, i);
+  // ---- upper radiative boundary condition (:497-523): w at the model top is
+  //      the 13x13 tmask convolution of estore (clamped at the domain edge) ----
+  double w_k = 0.0;
+  if (s.ifupr == 1) {
+    for (int nsi = -6; nsi <= 6; ++nsi) {
+      const int inn = min(max(g.icross1 + 1, i + nsi), g.icross2 - 1);
+      const double* erow = f.estore + (long long)inn * g.esi;
+      const double* trow = f.tmask + 13 * (nsi + 6) + 6;
+#pragma unroll
+      for (int nsj = -6; nsj <= 6; ++nsj) {
+        const int jnn = min(max(g.jcross1 + 1, j + nsj), g.jcross2 - 1);
+        w_k = w_k + erow[jnn] * LD1(trow + nsj);
+      }
+    }
+  }
   P3(f.cw, j, i, 1) = w_k;
   double ucrs_m = 0.0, vcrs_m = 0.0;
   double ppd_m2 = 0.0, ppd_m1 = 0.0;  // damped p' at k-2, k-1 (for ct of level k-1)
@@ -458,11 +452,6 @@ void launch_snd_wfwd(const Geom& g, const Fields& f, const StepScalars& s, cudaS
   const dim3 b = rcm::col_block(); dim3 gr((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y);
   if (s.it == 1) RCM_LAUNCH(k_snd_wfwd<true>, gr, b, st, g, f, s);
   else RCM_LAUNCH(k_snd_wfwd<false>, gr, b, st, g, f, s);
-}
-void launch_snd_wpval(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
-  const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
-  dim3 b2(32, 8), gr2((nj + 31) / 32, (ni + 7) / 8);
-  RCM_LAUNCH(k_snd_wpval, gr2, b2, st, g, f, s);
 }
 void launch_snd_wback(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
