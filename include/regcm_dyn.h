@@ -173,6 +173,15 @@ int rcm_dyn_set_static(rcm_dyn* h, int static_id, const double* a,
 int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a,
                     const int32_t lb[3], const int32_t ub[3]);
 
+/* Asynchronous variant of rcm_dyn_set_bdy(…, RCM_BDY_NEXT, …): what a driver
+ * does when it reads the next ICBC record ahead of time (the reference reads it
+ * synchronously inside bdyin, Main/mod_bdycod.F90:669-690).  The copy is queued on
+ * a private stream and overlaps rcm_dyn_step; the record change inside
+ * rcm_dyn_step waits for it on the device.  `a` must stay valid (and should be
+ * page-locked) until rcm_dyn_stage_wait returns or the record has been consumed. */
+int rcm_dyn_stage_bdy_async(rcm_dyn* h, int field, const double* a, const int32_t lb[3], const int32_t ub[3]);
+int rcm_dyn_stage_wait(rcm_dyn* h);
+
 /* replaces: the static part of `param` (map-factor inversion, xmsf/dmsf,
  * hsigma/dsigma/twt/qcon, init_advection, setup_bdycon,
  * make_reference_atmosphere, compute_full_coriolis_coefficients —

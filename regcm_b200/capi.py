@@ -151,6 +151,8 @@ class CoreLib:
             "profile_kernels": ([], C.c_int),
             "comm_unique_id": ([C.c_void_p, C.c_int], C.c_int),
             "comm_init": ([vp, C.c_void_p, C.c_int], C.c_int),
+            "stage_bdy_async": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
+            "stage_wait": ([vp], C.c_int),
         }.items():
             if hasattr(self.lib, p + opt):
                 fn = getattr(self.lib, p + opt)
@@ -205,6 +207,16 @@ class DynCore:
         a = self._f(a)
         ub = tuple(lb[d] + a.shape[d] - 1 for d in range(3))
         self._check(self.lib.set_bdy(self.h, field, slot, a.ctypes.data_as(_DP), *_bounds(lb, ub)))
+
+    def stage_bdy_async(self, field: int, a: np.ndarray, lb=(1, 1, 1)):
+        """Queue the H2D copy of one field of the NEXT record; `a` must be Fortran-ordered
+        float64 and stay alive until stage_wait() or the record change."""
+        assert a.dtype == np.float64 and a.flags.f_contiguous
+        ub = tuple(lb[d] + a.shape[d] - 1 for d in range(3))
+        self._check(self.lib.stage_bdy_async(self.h, field, a.ctypes.data_as(_DP), *_bounds(lb, ub)))
+
+    def stage_wait(self):
+        self._check(self.lib.stage_wait(self.h))
 
     def init(self):
         self._check(self.lib.init(self.h))

@@ -99,6 +99,9 @@ struct rcm_dyn {
   int nan_flag = 0;
   // stream / timing
   cudaStream_t st = nullptr;
+  cudaStream_t st_copy = nullptr;  // asynchronous staging of the next boundary record
+  cudaEvent_t ev_stage = nullptr;
+  bool stage_pending = false;
   cudaStream_t st_b = nullptr, st_c = nullptr;  // side streams: the three slow-tendency kernels are independent
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_jb = nullptr, ev_jc = nullptr;
   int64_t launches = 0;
@@ -259,6 +262,10 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   h->off3 = h->off2 - g.sk;
   g.esi = ((nj + 2 * RCM_EHALO + 15) / 16) * 16;
   g.pfd = 2;
+  g.kc_uv = g.kc_tq = g.kc_ppw = g.kz + 1;
+  if (const char* e = std::getenv("RCM_KC_UV")) g.kc_uv = std::max(1, std::atoi(e));
+  if (const char* e = std::getenv("RCM_KC_TQ")) g.kc_tq = std::max(1, std::atoi(e));
+  if (const char* e = std::getenv("RCM_KC_PPW")) g.kc_ppw = std::max(1, std::atoi(e));
   if (const char* e = std::getenv("RCM_OVERLAP")) h->overlap_slow = std::atoi(e) != 0;
   if (const char* e = std::getenv("RCM_PFD")) g.pfd = std::max(0, std::min(8, std::atoi(e)));
   h->eni = ni + 2 * RCM_EHALO;
@@ -384,7 +391,9 @@ static double** bdy_bt(rcm_dyn* h, int q) {
 #ifndef RCM_EMU
 // strided 3-D copy between a caller window (Fortran bounds lb/ub) and the
 // padded device geometry: one cudaMemcpy3DAsync, no host staging.
-static int copy3d(rcm_dyn* h, double* dev_shifted, const double* host, const int32_t* lb, const int32_t* ub, int nk, bool to_device) {
+static int copy3d(rcm_dyn* h, double* dev_shifted, const double* host, const int32_t* lb, const int32_t* ub, int nk, bool to_device,
+                  cudaStream_t st = nullptr, bool sync = true) {
+  if (!st) st = h->st;
   const Geom& g = h->g;
   const int jlo = std::max(lb[0], g.jde1 - RCM_HALO), jhi = std::min(ub[0], g.jde2 + RCM_HALO);
   const int ilo = std::max(lb[1], g.ide1 - RCM_HALO), ihi = std::min(ub[1], g.ide2 + RCM_HALO);
@@ -401,8 +410,8 @@ static int copy3d(rcm_dyn* h, double* dev_shifted, const double* host, const int
   p.dstPtr = to_device ? dp : hp; p.dstPos = to_device ? dpos : hpos;
   p.extent = make_cudaExtent((size_t)(jhi - jlo + 1) * sizeof(double), (size_t)(ihi - ilo + 1), (size_t)(khi - klo + 1));
   p.kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
-  CUDA_OK(cudaMemcpy3DAsync(&p, h->st));
-  CUDA_OK(cudaStreamSynchronize(h->st));
+  CUDA_OK(cudaMemcpy3DAsync(&p, st));
+  if (sync) CUDA_OK(cudaStreamSynchronize(st));
   return RCM_OK;
 }
 #endif
@@ -430,6 +439,39 @@ extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a,
   else return fail(h, RCM_ERR_ARG, "bad slot");
   const int nk = (field == RCM_F_W) ? h->g.kzp1 : h->g.kz;
   return upload3(h, dst, a, lb, ub, nk);
+}
+
+// Asynchronous staging of the NEXT boundary record: the copy runs on its own
+// stream while rcm_dyn_step keeps computing; bdyin waits for it on the device.
+extern "C" int rcm_dyn_stage_bdy_async(rcm_dyn* h, int field, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a) return RCM_ERR_ARG;
+  const int q = bdy_index(field);
+  if (q < 0) return fail(h, RCM_ERR_ARG, "no boundary data for this field");
+  cudaSetDevice(h->device);
+  const int nk = (field == RCM_F_W) ? h->g.kzp1 : h->g.kz;
+#ifndef RCM_EMU
+  if (!h->st_copy) {
+    CUDA_OK(cudaStreamCreateWithFlags(&h->st_copy, cudaStreamNonBlocking));
+    CUDA_OK(cudaEventCreateWithFlags(&h->ev_stage, cudaEventDisableTiming));
+  }
+  int rc = copy3d(h, h->nx[q], a, lb, ub, nk, true, h->st_copy, false);
+  if (rc) return rc;
+  CUDA_OK(cudaEventRecord(h->ev_stage, h->st_copy));
+  h->stage_pending = true;
+#else
+  int rc = upload3(h, h->nx[q], a, lb, ub, nk);
+  if (rc) return rc;
+#endif
+  h->have_next = true;
+  return RCM_OK;
+}
+
+extern "C" int rcm_dyn_stage_wait(rcm_dyn* h) {
+  if (!h) return RCM_ERR_ARG;
+#ifndef RCM_EMU
+  if (h->stage_pending) { cudaSetDevice(h->device); CUDA_OK(cudaStreamSynchronize(h->st_copy)); h->stage_pending = false; }
+#endif
+  return RCM_OK;
 }
 
 // ---------------------------------------------------------------------------
@@ -872,6 +914,9 @@ static int bdyin(rcm_dyn* h) {
   const int jclo = jdlo, jchi = std::min(g.jx - 1, g.jde2 + RCM_HALO);
   const int iclo = idlo, ichi = std::min(g.iy - 1, g.ide2 + RCM_HALO);
   h->xbctime = 0.0;
+#ifndef RCM_EMU
+  if (h->stage_pending) { CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_stage, 0)); h->stage_pending = false; }
+#endif
   for (int q = 0; q < 6; ++q) {
     // b0 <- b1 (pointer swap), b1 <- staged record
     std::swap(*bdy_b0(h, q), h->b1[q]);
@@ -1190,6 +1235,8 @@ extern "C" int rcm_dyn_destroy(rcm_dyn* h) {
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->st) cudaStreamDestroy(h->st);
+  if (h->st_copy) { cudaStreamSynchronize(h->st_copy); cudaStreamDestroy(h->st_copy); }
+  if (h->ev_stage) cudaEventDestroy(h->ev_stage);
   if (h->st_b) cudaStreamDestroy(h->st_b);
   if (h->st_c) cudaStreamDestroy(h->st_c);
   for (cudaEvent_t e : {h->ev_fork, h->ev_jb, h->ev_jc}) if (e) cudaEventDestroy(e);

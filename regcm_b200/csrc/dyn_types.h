@@ -29,6 +29,7 @@ struct Geom {
   int si;        // doubles per i-row
   long long sk;  // doubles per k-plane
   int esi;       // pitch of the wide-halo 2-D estore array
+  int kc_uv, kc_tq, kc_ppw;  // levels per thread of the slow-tendency kernels (>= kz: one thread marches the whole column)
   int pfd;       // L2 prefetch distance (levels ahead) of the column-marching kernels; 0 = off
 };
 

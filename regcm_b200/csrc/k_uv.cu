@@ -19,10 +19,14 @@ __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_UV)
 k_uv(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
-  const int j = g.jdi1 + blockIdx.x * blockDim.x + threadIdx.x;
+  // blockIdx.x = (tile column) * nchunk + (k chunk): the chunks of one tile are
+  // neighbours in launch order, so the level shared by two chunks is read from L2
+  const int nch = (g.kz + g.kc_uv - 1) / g.kc_uv;
+  const int j = g.jdi1 + (blockIdx.x / nch) * blockDim.x + threadIdx.x;
   const int i = g.idi1 + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jdi2 || i > g.idi2) return;
   const int kz = g.kz;
+  const int k0 = 1 + (blockIdx.x % nch) * g.kc_uv, k1 = min(kz, k0 + g.kc_uv - 1);
   const bool up = s.upstream_mode != 0;
   const double ul = s.ul;
 
@@ -43,7 +47,13 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
 
   // vertical-advection flux at the upper interface of level k (full level k)
   double uu_k = 0.0, vv_k = 0.0;  // uu(1) = 0: loop starts at k = 2
-  double wadot_k = 0.125 * (L3(f.aw, j - 1, i - 1, 1) + L3(f.aw, j - 1, i, 1) + L3(f.aw, j, i - 1, 1) + L3(f.aw, j, i, 1));
+  if (k0 >= 2) {  // this thread starts mid-column: flux through its upper interface
+    const double qq = 0.25 * (L3(f.qdot, j, i, k0) + L3(f.qdot, j, i - 1, k0) + L3(f.qdot, j - 1, i, k0) + L3(f.qdot, j - 1, i - 1, k0));
+    const double t1 = LD1(&f.twt1[k0]), t2 = LD1(&f.twt2[k0]);
+    uu_k = qq * (t1 * L3(f.au, j, i, k0) + t2 * L3(f.au, j, i, k0 - 1));
+    vv_k = qq * (t1 * L3(f.av, j, i, k0) + t2 * L3(f.av, j, i, k0 - 1));
+  }
+  double wadot_k = 0.125 * (L3(f.aw, j - 1, i - 1, k0) + L3(f.aw, j - 1, i, k0) + L3(f.aw, j, i - 1, k0) + L3(f.aw, j, i, k0));
 
   // request level kk of every streamed field into L2 (see PF3)
   auto prefetch = [&](int kk) {
@@ -51,9 +61,9 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
   };
   const int pfd = g.pfd;
   if (pfd > 0)
-    for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
-  for (int k = 1; k <= kz; ++k) {
-    if (pfd > 0 && k + pfd <= kz) prefetch(k + pfd);
+    for (int kk = k0; kk <= min(k0 + pfd - 1, k1); ++kk) prefetch(kk);
+  for (int k = k0; k <= k1; ++k) {
+    if (pfd > 0 && k + pfd <= k1) prefetch(k + pfd);
     // ---- level-a raw momentum on the 3x3 box ----
     double au[3][3], av[3][3];
 #pragma unroll
@@ -177,6 +187,7 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
 
 void launch_uv(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jdi2 - g.jdi1 + 1, ni = g.idi2 - g.idi1 + 1;
-  const dim3 b = rcm::col_block(); dim3 gr((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y);
+  const int nch = (g.kz + g.kc_uv - 1) / g.kc_uv;
+  const dim3 b = rcm::col_block(); dim3 gr(((nj + b.x - 1) / b.x) * nch, (ni + b.y - 1) / b.y);
   RCM_LAUNCH(k_uv, gr, b, st, g, f, s);
 }

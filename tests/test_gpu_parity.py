@@ -65,6 +65,23 @@ def test_boundary_record_change_and_long_run(cuda_lib):
     assert _worst(errs) <= 1e-9, errs
 
 
+def test_async_record_staging(cuda_lib):
+    """rcm_dyn_stage_bdy_async while steps run == synchronous rcm_dyn_set_bdy before them."""
+    case = synth.make_case("tiny", ibdyfrq=2)
+    a = capi.DynCore(cuda_lib, case.cfg); synth.load_case(a, case, stage_next=True)
+    b = capi.DynCore(cuda_lib, case.cfg); synth.load_case(b, case, stage_next=False)
+    b.step(20)
+    keep = {fid: np.asfortranarray(arr) for fid, arr in case.bdy[capi.BDY_NEXT].items()}
+    for fid, arr in keep.items():
+        b.stage_bdy_async(fid, arr)
+    b.step(90)          # crosses the record change at step 60 without an explicit wait
+    b.stage_wait()
+    a.step(110)
+    for f in range(7):
+        for lv in (0, 1):
+            assert np.array_equal(a.get_state(f, lv), b.get_state(f, lv)), (f, lv)
+
+
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "nh_*.npz"))))
 def test_golden_fixtures(cuda_lib, path):
     case, nsteps, fields = load_golden(path)
