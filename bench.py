@@ -34,6 +34,19 @@ ALG_BYTES_KERNEL = {
 }
 
 
+def measured_traffic(kernel, workload, world):
+    """dram bytes per launch of `kernel` from the committed ncu capture (profiles/r1_traffic.json);
+    only meaningful for the configuration it was captured on."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as fh:
+            t = json.load(fh)
+        if t["workload"] == workload and t["n_gpus"] == world:
+            return t["bytes_per_launch"].get(kernel)
+    except Exception:
+        pass
+    return None
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
@@ -262,7 +275,7 @@ def run_gpu(args):
     top_ms = kern[top][0] / kern[top][1]
     achieved = ALG_BYTES_KERNEL[top] * local_cells / (top_ms * 1e-3) / 1e9
     roofline = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "avg_launch_ms": top_ms,
+                "traffic": measured_traffic(top, args.workload, world), "peak_source": peak_src, "avg_launch_ms": top_ms,
                 "alg_bytes_per_launch": ALG_BYTES_KERNEL[top] * local_cells,
                 "share_of_step": kern[top][0] / max(sum(v[0] for v in prof.values()), 1e-30),
                 "per_kernel": {k: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps,
