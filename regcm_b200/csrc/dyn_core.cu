@@ -533,10 +533,14 @@ static int exch_sound_pp(rcm_dyn* h) {  // atmc%t, atmc%pp  (Main/mod_sound.F90:
   if (h->halo.exchange({{h->f.cppd, kz, 0}, {h->f.ct, kz, 0}}, 1, h->st)) return fail(h, RCM_ERR_NCCL, "halo exchange (pp) failed");
   return RCM_OK;
 }
-static int exch_sound_uv(rcm_dyn* h) {  // atmc%u, atmc%v  (Main/mod_sound.F90:300-301)
+// The reference exchanges atmc%u, atmc%v in every sub-step (Main/mod_sound.F90:300-301).
+// Here the acoustic u,v tendencies are exchanged ONCE per step instead and k_snd_uv
+// advances the first high-side ghost row itself (bit-identical to the owner's values).
+static int exch_uvten(rcm_dyn* h) {
   if (h->cfg.nproc <= 1) return RCM_OK;
   const int kz = h->g.kz;
-  if (h->halo.exchange({{h->f.cu, kz, 1}, {h->f.cv, kz, 1}}, 1, h->st)) return fail(h, RCM_ERR_NCCL, "halo exchange (uv) failed");
+  if (h->halo.exchange({{h->f.cppd, kz, 0}, {h->f.ct, kz, 0}, {h->f.uten, kz, 1}, {h->f.vten, kz, 1}}, 1, h->st))
+    return fail(h, RCM_ERR_NCCL, "halo exchange (uten, pp) failed");
   return RCM_OK;
 }
 static int exch_state(rcm_dyn* h) {  // atm1/atm2 all prognostics, width 2 (Main/mod_tendency.F90:866-869,1046-1083)
@@ -1032,13 +1036,11 @@ static int tend(rcm_dyn* h) {
     CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jc, 0));
   }
   TIMED(KID_SND_INIT, 1, launch_snd_init(g, f, s, h->st));
-  TIMED(KID_HALO, 0, rc = exch_sound_pp(h));
+  TIMED(KID_HALO, 0, rc = exch_uvten(h));  // + the first cppd, ct of the step
   if (rc) return rc;
   for (int it = 1; it <= istep; ++it) {
     s.it = it;
     TIMED(KID_SND_UV, 1, launch_snd_uv(g, f, s, h->st));
-    TIMED(KID_HALO, 0, rc = exch_sound_uv(h));
-    if (rc) return rc;
     TIMED(KID_SND_WFWD, 1, launch_snd_wfwd(g, f, s, h->st));
     if (h->cfg.ifupr == 1) {
       TIMED(KID_HALO, 0, rc = exch_estore(h));

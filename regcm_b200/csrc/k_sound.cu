@@ -60,7 +60,10 @@ k_snd_uv(const Geom g, const Fields f, const StepScalars s) {
   const int j = g.jdi1 + blockIdx.x * 32 + threadIdx.x;
   const int i = g.idi1 + blockIdx.y * 4 + threadIdx.y;
   const int k = 1 + blockIdx.z * 2 + threadIdx.z;
-  if (j > g.jdi2 || i > g.idi2 || k > g.kz) return;
+  // the first ghost row/column on the high side is advanced redundantly (same
+  // inputs, same arithmetic as the owning rank): k_snd_wfwd/k_snd_wback read
+  // u,v at (j..j+1, i..i+1), and this saves one halo exchange per sub-step
+  if (j > g.jdi2 + g.gr || i > g.idi2 + g.gt || k > g.kz) return;
   const double rho = 0.25 * (L3(f.rho1, j, i, k) + L3(f.rho1, j - 1, i, k) + L3(f.rho1, j, i - 1, k) + L3(f.rho1, j - 1, i - 1, k));
   const double dppdp0 = 0.25 * (L3(f.ct, j, i, k) + L3(f.ct, j - 1, i, k) + L3(f.ct, j, i - 1, k) + L3(f.ct, j - 1, i - 1, k));
   const double chh = 0.5 * s.dts / (rho * s.dx) / L2(f.msfd, j, i);
@@ -443,7 +446,7 @@ void launch_snd_init(const Geom& g, const Fields& f, const StepScalars& s, cudaS
   RCM_LAUNCH(k_snd_init, gr, b, st, g, f, s);
 }
 void launch_snd_uv(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
-  const int nj = g.jdi2 - g.jdi1 + 1, ni = g.idi2 - g.idi1 + 1;
+  const int nj = g.jdi2 + g.gr - g.jdi1 + 1, ni = g.idi2 + g.gt - g.idi1 + 1;
   dim3 b(32, 4, 2), gr((nj + 31) / 32, (ni + 3) / 4, (g.kz + 1) / 2);
   RCM_LAUNCH(k_snd_uv, gr, b, st, g, f, s);
 }
