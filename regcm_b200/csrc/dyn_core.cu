@@ -26,6 +26,9 @@ using namespace rcm;
 // kernel launchers (k_*.cu)
 void launch_prep(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_uv(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void* uv_tma_setup(const Geom&, const Fields&, long long off3, int ni_pad);
+void uv_tma_destroy(void*);
+void launch_uv_tma(const Geom&, const Fields&, const StepScalars&, cudaStream_t, const void* maps);
 void launch_tq(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_ppw(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_init(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
@@ -58,6 +61,7 @@ struct ProfRec { int kid; cudaEvent_t a, b; };
 
 struct rcm_dyn {
   bool prof_on = false;
+  void* uv_maps = nullptr;   // TMA tensor maps of k_uv_tma (nullptr: plain k_uv)
   bool overlap_slow = true;  // RCM_OVERLAP=0 serialises the slow-tendency kernels
   std::vector<ProfRec> prof_recs;
   std::vector<cudaEvent_t> prof_pool;
@@ -328,6 +332,10 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   cudaStreamCreateWithFlags(&h->st_c, cudaStreamNonBlocking);
   cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
   cudaEventCreate(&h->ev_fork); cudaEventCreate(&h->ev_jb); cudaEventCreate(&h->ev_jc);
+  {
+    const char* e = std::getenv("RCM_UV_TMA");
+    if (!e || std::atoi(e) != 0) h->uv_maps = uv_tma_setup(g, f, h->off3, h->ni_pad);
+  }
   h->halo.init(g, c.nproc, c.myid, cj, ci);
   *out = h;
   return RCM_OK;
@@ -1017,7 +1025,7 @@ static int tend(rcm_dyn* h) {
   TIMED(KID_PREP, 1, launch_prep(g, f, s, h->st));
   TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
   if (h->prof_on || !h->overlap_slow) {
-    TIMED(KID_UV, 1, launch_uv(g, f, s, h->st));
+    TIMED(KID_UV, 1, h->uv_maps ? launch_uv_tma(g, f, s, h->st, h->uv_maps) : launch_uv(g, f, s, h->st));
     TIMED(KID_TQ, 1, launch_tq(g, f, s, h->st));
     TIMED(KID_PPW, 1, launch_ppw(g, f, s, h->st));
   } else {
@@ -1028,7 +1036,7 @@ static int tend(rcm_dyn* h) {
     CUDA_OK(cudaStreamWaitEvent(h->st_c, h->ev_fork, 0));
     launch_tq(g, f, s, h->st);
     launch_ppw(g, f, s, h->st_b);
-    launch_uv(g, f, s, h->st_c);
+    if (h->uv_maps) launch_uv_tma(g, f, s, h->st_c, h->uv_maps); else launch_uv(g, f, s, h->st_c);
     h->launches += 3;
     CUDA_OK(cudaEventRecord(h->ev_jb, h->st_b));
     CUDA_OK(cudaEventRecord(h->ev_jc, h->st_c));
@@ -1237,6 +1245,7 @@ extern "C" int rcm_dyn_destroy(rcm_dyn* h) {
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->st) cudaStreamDestroy(h->st);
+  if (h->uv_maps) uv_tma_destroy(h->uv_maps);
   if (h->st_copy) { cudaStreamSynchronize(h->st_copy); cudaStreamDestroy(h->st_copy); }
   if (h->ev_stage) cudaEventDestroy(h->ev_stage);
   if (h->st_b) cudaStreamDestroy(h->st_b);
