@@ -26,6 +26,10 @@ using namespace rcm;
 // kernel launchers (k_*.cu)
 void launch_prep(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_uv(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+bool tq_tma_setup();
+bool ppw_tma_setup();
+void launch_ppw_tma(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_tq_tma(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void* uv_tma_setup(const Geom&, const Fields&, long long off3, int ni_pad);
 void uv_tma_destroy(void*);
 void launch_uv_tma(const Geom&, const Fields&, const StepScalars&, cudaStream_t, const void* maps);
@@ -61,6 +65,8 @@ struct ProfRec { int kid; cudaEvent_t a, b; };
 
 struct rcm_dyn {
   bool prof_on = false;
+  bool ppw_tma = false;      // k_ppw_tma instead of k_ppw
+  bool tq_tma = false;       // k_tq_tma instead of k_tq
   void* uv_maps = nullptr;   // TMA tensor maps of k_uv_tma (nullptr: plain k_uv)
   bool overlap_slow = true;  // RCM_OVERLAP=0 serialises the slow-tendency kernels
   std::vector<ProfRec> prof_recs;
@@ -335,6 +341,10 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   {
     const char* e = std::getenv("RCM_UV_TMA");
     if (!e || std::atoi(e) != 0) h->uv_maps = uv_tma_setup(g, f, h->off3, h->ni_pad);
+    e = std::getenv("RCM_TQ_TMA");
+    if (!e || std::atoi(e) != 0) h->tq_tma = tq_tma_setup();
+    e = std::getenv("RCM_PPW_TMA");  // measured slower than k_ppw on B200 (3.55 vs 3.33 ms on C4): opt-in
+    if (e && std::atoi(e) != 0) h->ppw_tma = ppw_tma_setup();
   }
   h->halo.init(g, c.nproc, c.myid, cj, ci);
   *out = h;
@@ -1026,16 +1036,16 @@ static int tend(rcm_dyn* h) {
   TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_UV, 1, h->uv_maps ? launch_uv_tma(g, f, s, h->st, h->uv_maps) : launch_uv(g, f, s, h->st));
-    TIMED(KID_TQ, 1, launch_tq(g, f, s, h->st));
-    TIMED(KID_PPW, 1, launch_ppw(g, f, s, h->st));
+    TIMED(KID_TQ, 1, h->tq_tma ? launch_tq_tma(g, f, s, h->st) : launch_tq(g, f, s, h->st));
+    TIMED(KID_PPW, 1, h->ppw_tma ? launch_ppw_tma(g, f, s, h->st) : launch_ppw(g, f, s, h->st));
   } else {
     // k_uv, k_tq, k_ppw read the same inputs and write disjoint outputs: run
     // them side by side so that one kernel's tail wave is filled by the others
     CUDA_OK(cudaEventRecord(h->ev_fork, h->st));
     CUDA_OK(cudaStreamWaitEvent(h->st_b, h->ev_fork, 0));
     CUDA_OK(cudaStreamWaitEvent(h->st_c, h->ev_fork, 0));
-    launch_tq(g, f, s, h->st);
-    launch_ppw(g, f, s, h->st_b);
+    if (h->tq_tma) launch_tq_tma(g, f, s, h->st); else launch_tq(g, f, s, h->st);
+    if (h->ppw_tma) launch_ppw_tma(g, f, s, h->st_b); else launch_ppw(g, f, s, h->st_b);
     if (h->uv_maps) launch_uv_tma(g, f, s, h->st_c, h->uv_maps); else launch_uv(g, f, s, h->st_c);
     h->launches += 3;
     CUDA_OK(cudaEventRecord(h->ev_jb, h->st_b));

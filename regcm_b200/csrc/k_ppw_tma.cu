@@ -1,0 +1,125 @@
+// k_ppw with its stencil operands staged through shared memory by the TMA engine
+// (see k_uv_tma.cu for the scheme).  Tiles per level: au, av, app, aw (1 ghost cell
+// used), bpp, bw (2 ghost cells, 4th-order diffusion); the 2-D 1/p* table of the
+// diffusion operands is staged once per block.  The loop runs to kz+1 (w lives on
+// full levels); level k+1 centre values of app and aw come from the next tile.
+#include "dev_common.cuh"
+#include "launch.h"
+#include "tma_stage.cuh"
+
+#ifndef RCM_EMU
+using namespace rcm;
+
+namespace {
+constexpr int kBY = 8, kTW = 40, kTH = kBY + 4, kTile = kTW * kTH, kNT = 6, kStages = 3;
+constexpr int kRowBytes = kTW * 8, kStageBytes = kNT * kTile * 8;
+enum { T_AU, T_AV, T_APP, T_AW, T_BPP, T_BW };
+
+__global__ void __launch_bounds__(256, 2)
+k_ppw_tma(const Geom g, const Fields f, const StepScalars s) {
+  extern __shared__ __align__(128) unsigned char smraw[];
+  double* tiles = reinterpret_cast<double*>(smraw);
+  double* rtile = tiles + (size_t)kStages * kNT * kTile;  // rpsb, 2-D
+  uint64_t* full = reinterpret_cast<uint64_t*>(rtile + kTile);  // kStages + 1 barriers
+  const int si = g.si;
+  const long long sk = g.sk;
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * 32 + tx;
+  const int j0 = g.jci1 + blockIdx.x * 32, i0 = g.ici1 + blockIdx.y * kBY;
+  const bool valid = (j0 + tx <= g.jci2) && (i0 + ty <= g.ici2);
+  const int j = min(j0 + tx, g.jci2), i = min(i0 + ty, g.ici2);
+  const int kz = g.kz, kzp1 = g.kzp1;
+  const int jlo = g.jde1 - RCM_HALO;
+  int jstart = (j0 - 2) - (((j0 - 2) - jlo) & 1);
+  jstart = min(jstart, jlo + si - kTW);
+  const int ihi = g.ide2 + RCM_HALO;
+  const int to = (i - (i0 - 2)) * kTW + (j - jstart);
+
+  if (tid == 0) {
+    for (int q = 0; q < kStages + 1; ++q) mbar_init(full + q, 1);
+    mbar_init_fence();
+  }
+  __syncthreads();
+  const int cq = tid / kTH, cr_ = tid % kTH;
+  const double* csrc = nullptr;
+  if (tid < kNT * kTH) {
+    const double* fld = cq == T_AU ? f.au : cq == T_AV ? f.av : cq == T_APP ? f.app : cq == T_AW ? f.aw : cq == T_BPP ? f.bpp : f.bw;
+    csrc = &P3(fld, jstart, min(i0 - 2 + cr_, ihi), 0);
+  }
+  auto issue = [&](int level) {  // level = 1..kz+1
+    const int st = (level - 1) % kStages;
+    if (tid == 0) mbar_expect_tx(full + st, kStageBytes);
+    if (tid < kNT * kTH)
+      bulk_load(tiles + (size_t)(st * kNT + cq) * kTile + cr_ * kTW, csrc + (long long)level * sk, kRowBytes, full + st);
+  };
+  if (tid == 0) mbar_expect_tx(full + kStages, kTile * 8);
+  if (tid < kTH) bulk_load(rtile + tid * kTW, &P2(f.rpsb, jstart, min(i0 - 2 + tid, ihi)), kRowBytes, full + kStages);
+  issue(1);
+  issue(2);
+
+  const bool up = s.upstream_mode != 0;
+  const double ul = s.ul, xt = s.xt;
+  const double psa = L2(f.psa, j, i), psb = L2(f.psb, j, i);
+  const double rpsa_c = L2(f.rpsa, j, i), rpsa_jm = L2(f.rpsa, j - 1, i), rpsa_jp = L2(f.rpsa, j + 1, i),
+               rpsa_im = L2(f.rpsa, j, i - 1), rpsa_ip = L2(f.rpsa, j, i + 1);
+  const double rpsb_c = L2(f.rpsb, j, i), rpsb_jm = L2(f.rpsb, j - 1, i), rpsb_jp = L2(f.rpsb, j + 1, i),
+               rpsb_im = L2(f.rpsb, j, i - 1), rpsb_ip = L2(f.rpsb, j, i + 1);
+  const double xmsf = L2(f.xmsf, j, i);
+  const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i), m11 = L2(f.msfd, j + 1, i + 1);
+  const double ex = L2(f.ex, j, i), crx = L2(f.crx, j, i), cry = L2(f.cry, j, i);
+  const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_c, j, i) : 0;
+  const bool dint = diff_interior(g, j, i, false);
+  const int nring = ring_count(g, j, i, false);
+
+  // ---- carried state (level k-1 values and interface fluxes) ----
+  double uavg1_m = 0, uavg2_m = 0, vavg1_m = 0, vavg2_m = 0;  // uavg at k-1
+  double ucc_m = 0, vcc_m = 0;                                // raw 4-dot sums at k-1
+  double axpr_m = 0, rho0_m = 0, rho1_m = 0, qc_m = 0, cr_m = 0;
+  double app_m = 0;        // atm1%pp(k-1)
+  double fx_pp_k = 0.0;    // vertical pp flux at full level k
+  double fxw_m = 0.0;      // vertical w flux of loop index k-1
+  double xkc_m = 0.0;      // raw xkc(k-1)
+  mbar_wait(full + kStages, 0);
+  mbar_wait(full + 0, 0);  // level 1
+  double aw_k = tiles[T_AW * kTile + to];
+  const double* rp = rtile + to;
+
+  for (int k = 1; k <= kzp1; ++k) {
+    __syncthreads();  // everyone is done with level k-1: its stage can take level k+2
+    if (k + 2 <= kzp1) issue(k + 2);
+    mbar_wait(full + (k - 1) % kStages, ((k - 1) / kStages) & 1);    // level k
+    if (k < kzp1) mbar_wait(full + k % kStages, (k / kStages) & 1);  // level k+1
+    const double* tk = tiles + (size_t)((k - 1) % kStages) * kNT * kTile + to;
+    const double* tn = tiles + (size_t)(k % kStages) * kNT * kTile + to;
+#define TK_AU(dj, di) tk[T_AU * kTile + (di) * kTW + (dj)]
+#define TK_AV(dj, di) tk[T_AV * kTile + (di) * kTW + (dj)]
+#define TK_APP(dj, di) tk[T_APP * kTile + (di) * kTW + (dj)]
+#define TK_AW(dj, di) tk[T_AW * kTile + (di) * kTW + (dj)]
+#define TK_BPP(dj, di) tk[T_BPP * kTile + (di) * kTW + (dj)]
+#define TK_BW(dj, di) tk[T_BW * kTile + (di) * kTW + (dj)]
+#define TN_APP(dj, di) tn[T_APP * kTile + (di) * kTW + (dj)]
+#define TN_AW(dj, di) tn[T_AW * kTile + (di) * kTW + (dj)]
+#define RPSB(dj, di) rp[(di) * kTW + (dj)]
+#define RCM_STORE_OK valid
+#include "k_ppw_level.inc"
+#undef RCM_STORE_OK
+#undef RPSB
+  }
+  (void)app_m;
+}
+constexpr int kSmem = kStages * kStageBytes + kTile * 8 + 64;
+}  // namespace
+
+bool ppw_tma_setup() {
+  if (cudaFuncSetAttribute(k_ppw_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem) != cudaSuccess) { cudaGetLastError(); return false; }
+  return true;
+}
+
+void launch_ppw_tma(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
+  const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
+  dim3 b(32, kBY), gr((nj + 31) / 32, (ni + kBY - 1) / kBY);
+  k_ppw_tma<<<gr, b, kSmem, st>>>(g, f, s);
+}
+#else
+bool ppw_tma_setup() { return false; }
+void launch_ppw_tma(const Geom&, const Fields&, const StepScalars&, cudaStream_t) {}
+#endif

@@ -12,6 +12,7 @@
 // scripts/tma_test.cu - so the rows are copied one by one.)
 #include "dev_common.cuh"
 #include "launch.h"
+#include "tma_stage.cuh"
 
 #ifndef RCM_EMU
 #include <cstdint>
@@ -23,32 +24,6 @@ namespace {
 constexpr int kBY = 8, kTW = 40, kTH = kBY + 4, kTile = kTW * kTH, kNT = 8, kStages = 3;
 constexpr int kRowBytes = kTW * 8, kStageBytes = kNT * kTile * 8;
 enum { T_AU, T_AV, T_CR, T_XKC, T_DUB, T_DVB, T_QDOT, T_AW };
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "W_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra D_%=;\n"
-      "bra W_%=;\n"
-      "D_%=:\n"
-      "}\n" ::"r"(smem_u32(b)),
-      "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src),
-               "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
-}
 
 __global__ void __launch_bounds__(256, 2)
 k_uv_tma(const Geom g, const Fields f, const StepScalars s) {
@@ -73,7 +48,7 @@ k_uv_tma(const Geom g, const Fields f, const StepScalars s) {
 
   if (tid == 0) {
     for (int q = 0; q < kStages; ++q) mbar_init(full + q, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_init_fence();
   }
   __syncthreads();
   // copy number tid (0..95) of a level: field q = tid / 12, tile row r = tid % 12

@@ -65,6 +65,25 @@ def test_boundary_record_change_and_long_run(cuda_lib):
     assert _worst(errs) <= 1e-9, errs
 
 
+@pytest.mark.parametrize("name", ["small", "C2"])
+def test_staged_kernels_equal_plain_kernels(cuda_lib, name, monkeypatch):
+    """The TMA/shared-memory staged variants of the slow-tendency kernels share their
+    arithmetic with the plain kernels (k_*_level.inc): results must be bit-identical."""
+    case = synth.make_case(name)
+    for v in ("RCM_UV_TMA", "RCM_TQ_TMA", "RCM_PPW_TMA"):
+        monkeypatch.setenv(v, "1")
+    a = capi.DynCore(cuda_lib, case.cfg); synth.load_case(a, case)
+    for v in ("RCM_UV_TMA", "RCM_TQ_TMA", "RCM_PPW_TMA"):
+        monkeypatch.setenv(v, "0")
+    b = capi.DynCore(cuda_lib, case.cfg); synth.load_case(b, case)
+    a.step(5); b.step(5)
+    for f in range(7):
+        for lv in (0, 1):
+            assert np.array_equal(a.get_state(f, lv), b.get_state(f, lv)), (f, lv)
+    for w in range(10):
+        assert np.array_equal(a.get_work(w), b.get_work(w)), w
+
+
 def test_async_record_staging(cuda_lib):
     """rcm_dyn_stage_bdy_async while steps run == synchronous rcm_dyn_set_bdy before them."""
     case = synth.make_case("tiny", ibdyfrq=2)
