@@ -343,8 +343,8 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
     if (!e || std::atoi(e) != 0) h->uv_maps = uv_tma_setup(g, f, h->off3, h->ni_pad);
     e = std::getenv("RCM_TQ_TMA");
     if (!e || std::atoi(e) != 0) h->tq_tma = tq_tma_setup();
-    e = std::getenv("RCM_PPW_TMA");  // measured slower than k_ppw on B200 (3.55 vs 3.33 ms on C4): opt-in
-    if (e && std::atoi(e) != 0) h->ppw_tma = ppw_tma_setup();
+    e = std::getenv("RCM_PPW_TMA");
+    if (!e || std::atoi(e) != 0) h->ppw_tma = ppw_tma_setup();
   }
   h->halo.init(g, c.nproc, c.myid, cj, ci);
   *out = h;

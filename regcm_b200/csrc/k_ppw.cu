@@ -66,6 +66,16 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
 #define TN_APP(dj, di) L3(f.app, j + (dj), i + (di), k + 1)
 #define TN_AW(dj, di) L3(f.aw, j + (dj), i + (di), k + 1)
 #define RPSB(dj, di) L2(f.rpsb, j + (dj), i + (di))
+#define CK_AT L3(f.at, j, i, k)
+#define CK_AQV L3(f.aqv, j, i, k)
+#define CK_AQC L3(f.aqc, j, i, k)
+#define CK_RHO0 L3(f.rho0, j, i, k)
+#define CK_RHO1 L3(f.rho1, j, i, k)
+#define CK_T0 L3(f.t0, j, i, k)
+#define CK_CR L3(f.cr, j, i, k)
+#define CK_XKC L3(f.xkc, j, i, k)
+#define CK_QDOT L3(f.qdot, j, i, k)
+#define CN_QDOT L3(f.qdot, j, i, k + 1)
 #define RCM_STORE_OK true
 #include "k_ppw_level.inc"
 #undef RCM_STORE_OK

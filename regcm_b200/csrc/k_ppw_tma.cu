@@ -1,8 +1,9 @@
-// k_ppw with its stencil operands staged through shared memory by the TMA engine
-// (see k_uv_tma.cu for the scheme).  Tiles per level: au, av, app, aw (1 ghost cell
-// used), bpp, bw (2 ghost cells, 4th-order diffusion); the 2-D 1/p* table of the
-// diffusion operands is staged once per block.  The loop runs to kz+1 (w lives on
-// full levels); level k+1 centre values of app and aw come from the next tile.
+// k_ppw with ALL its per-level operands staged through shared memory by the TMA
+// engine (see k_uv_tma.cu for the scheme).  Halo tiles (12 rows): au, av, app, aw,
+// bpp, bw; centre tiles (8 rows): at, aqv, aqc, rho0, rho1, t0, cr, xkc, qdot; the
+// 2-D 1/p* table is staged once.  Two stages (level k computed, k+1 in flight);
+// the three level-(k+1) centre values (app, aw, qdot) are plain global loads issued
+// at the top of the iteration.  The loop runs to kz+1 (w lives on full levels).
 #include "dev_common.cuh"
 #include "launch.h"
 #include "tma_stage.cuh"
@@ -11,16 +12,18 @@
 using namespace rcm;
 
 namespace {
-constexpr int kBY = 8, kTW = 40, kTH = kBY + 4, kTile = kTW * kTH, kNT = 6, kStages = 3;
-constexpr int kRowBytes = kTW * 8, kStageBytes = kNT * kTile * 8;
+constexpr int kBY = 8, kTW = 40, kTH = kBY + 4, kTileH = kTW * kTH, kTileC = kTW * kBY, kNH = 6, kNC = 9, kStages = 2;
+constexpr int kRowBytes = kTW * 8, kStageDbl = kNH * kTileH + kNC * kTileC, kStageBytes = kStageDbl * 8;
+constexpr int kCopies = kNH * kTH + kNC * kBY;  // 144 row copies per level
 enum { T_AU, T_AV, T_APP, T_AW, T_BPP, T_BW };
+enum { C_AT, C_AQV, C_AQC, C_RHO0, C_RHO1, C_T0, C_CR, C_XKC, C_QDOT };
 
 __global__ void __launch_bounds__(256, 2)
 k_ppw_tma(const Geom g, const Fields f, const StepScalars s) {
   extern __shared__ __align__(128) unsigned char smraw[];
   double* tiles = reinterpret_cast<double*>(smraw);
-  double* rtile = tiles + (size_t)kStages * kNT * kTile;  // rpsb, 2-D
-  uint64_t* full = reinterpret_cast<uint64_t*>(rtile + kTile);  // kStages + 1 barriers
+  double* rtile = tiles + (size_t)kStages * kStageDbl;  // rpsb, 2-D, halo rows
+  uint64_t* full = reinterpret_cast<uint64_t*>(rtile + kTileH);  // kStages + 1 barriers
   const int si = g.si;
   const long long sk = g.sk;
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * 32 + tx;
@@ -32,29 +35,37 @@ k_ppw_tma(const Geom g, const Fields f, const StepScalars s) {
   int jstart = (j0 - 2) - (((j0 - 2) - jlo) & 1);
   jstart = min(jstart, jlo + si - kTW);
   const int ihi = g.ide2 + RCM_HALO;
-  const int to = (i - (i0 - 2)) * kTW + (j - jstart);
+  const int to = (i - (i0 - 2)) * kTW + (j - jstart);  // own cell in a halo tile
+  const int tc = (i - i0) * kTW + (j - jstart);        // own cell in a centre tile
 
   if (tid == 0) {
     for (int q = 0; q < kStages + 1; ++q) mbar_init(full + q, 1);
     mbar_init_fence();
   }
   __syncthreads();
-  const int cq = tid / kTH, cr_ = tid % kTH;
+  // row copy number tid of a level
   const double* csrc = nullptr;
-  if (tid < kNT * kTH) {
-    const double* fld = cq == T_AU ? f.au : cq == T_AV ? f.av : cq == T_APP ? f.app : cq == T_AW ? f.aw : cq == T_BPP ? f.bpp : f.bw;
-    csrc = &P3(fld, jstart, min(i0 - 2 + cr_, ihi), 0);
+  int cdst = 0;
+  if (tid < kNH * kTH) {
+    const int q = tid / kTH, r = tid % kTH;
+    const double* fld = q == T_AU ? f.au : q == T_AV ? f.av : q == T_APP ? f.app : q == T_AW ? f.aw : q == T_BPP ? f.bpp : f.bw;
+    csrc = &P3(fld, jstart, min(i0 - 2 + r, ihi), 0);
+    cdst = q * kTileH + r * kTW;
+  } else if (tid < kCopies) {
+    const int c = tid - kNH * kTH, q = c / kBY, r = c % kBY;
+    const double* fld = q == C_AT ? f.at : q == C_AQV ? f.aqv : q == C_AQC ? f.aqc : q == C_RHO0 ? f.rho0 : q == C_RHO1 ? f.rho1
+                        : q == C_T0 ? f.t0 : q == C_CR ? f.cr : q == C_XKC ? f.xkc : f.qdot;
+    csrc = &P3(fld, jstart, min(i0 + r, ihi), 0);
+    cdst = kNH * kTileH + q * kTileC + r * kTW;
   }
   auto issue = [&](int level) {  // level = 1..kz+1
     const int st = (level - 1) % kStages;
     if (tid == 0) mbar_expect_tx(full + st, kStageBytes);
-    if (tid < kNT * kTH)
-      bulk_load(tiles + (size_t)(st * kNT + cq) * kTile + cr_ * kTW, csrc + (long long)level * sk, kRowBytes, full + st);
+    if (tid < kCopies) bulk_load(tiles + (size_t)st * kStageDbl + cdst, csrc + (long long)level * sk, kRowBytes, full + st);
   };
-  if (tid == 0) mbar_expect_tx(full + kStages, kTile * 8);
+  if (tid == 0) mbar_expect_tx(full + kStages, kTileH * 8);
   if (tid < kTH) bulk_load(rtile + tid * kTW, &P2(f.rpsb, jstart, min(i0 - 2 + tid, ihi)), kRowBytes, full + kStages);
   issue(1);
-  issue(2);
 
   const bool up = s.upstream_mode != 0;
   const double ul = s.ul, xt = s.xt;
@@ -78,26 +89,38 @@ k_ppw_tma(const Geom g, const Fields f, const StepScalars s) {
   double fx_pp_k = 0.0;    // vertical pp flux at full level k
   double fxw_m = 0.0;      // vertical w flux of loop index k-1
   double xkc_m = 0.0;      // raw xkc(k-1)
+  double aw_k = L3(f.aw, j, i, 1);
   mbar_wait(full + kStages, 0);
-  mbar_wait(full + 0, 0);  // level 1
-  double aw_k = tiles[T_AW * kTile + to];
   const double* rp = rtile + to;
 
   for (int k = 1; k <= kzp1; ++k) {
-    __syncthreads();  // everyone is done with level k-1: its stage can take level k+2
-    if (k + 2 <= kzp1) issue(k + 2);
-    mbar_wait(full + (k - 1) % kStages, ((k - 1) / kStages) & 1);    // level k
-    if (k < kzp1) mbar_wait(full + k % kStages, (k / kStages) & 1);  // level k+1
-    const double* tk = tiles + (size_t)((k - 1) % kStages) * kNT * kTile + to;
-    const double* tn = tiles + (size_t)(k % kStages) * kNT * kTile + to;
-#define TK_AU(dj, di) tk[T_AU * kTile + (di) * kTW + (dj)]
-#define TK_AV(dj, di) tk[T_AV * kTile + (di) * kTW + (dj)]
-#define TK_APP(dj, di) tk[T_APP * kTile + (di) * kTW + (dj)]
-#define TK_AW(dj, di) tk[T_AW * kTile + (di) * kTW + (dj)]
-#define TK_BPP(dj, di) tk[T_BPP * kTile + (di) * kTW + (dj)]
-#define TK_BW(dj, di) tk[T_BW * kTile + (di) * kTW + (dj)]
-#define TN_APP(dj, di) tn[T_APP * kTile + (di) * kTW + (dj)]
-#define TN_AW(dj, di) tn[T_AW * kTile + (di) * kTW + (dj)]
+    __syncthreads();  // everyone is done with level k-1: its stage can take level k+1
+    if (k + 1 <= kzp1) issue(k + 1);
+    // level k+1 centre values straight from global memory, ahead of the wait
+    const double n_app = (k < kz) ? L3(f.app, j, i, k + 1) : 0.0;
+    const double n_aw = (k <= kz) ? L3(f.aw, j, i, k + 1) : 0.0;
+    const double n_qdot = (k <= kz) ? L3(f.qdot, j, i, k + 1) : 0.0;
+    mbar_wait(full + (k - 1) % kStages, ((k - 1) / kStages) & 1);  // level k
+    const double* tk = tiles + (size_t)((k - 1) % kStages) * kStageDbl + to;
+    const double* ck = tiles + (size_t)((k - 1) % kStages) * kStageDbl + kNH * kTileH + tc;
+#define TK_AU(dj, di) tk[T_AU * kTileH + (di) * kTW + (dj)]
+#define TK_AV(dj, di) tk[T_AV * kTileH + (di) * kTW + (dj)]
+#define TK_APP(dj, di) tk[T_APP * kTileH + (di) * kTW + (dj)]
+#define TK_AW(dj, di) tk[T_AW * kTileH + (di) * kTW + (dj)]
+#define TK_BPP(dj, di) tk[T_BPP * kTileH + (di) * kTW + (dj)]
+#define TK_BW(dj, di) tk[T_BW * kTileH + (di) * kTW + (dj)]
+#define TN_APP(dj, di) n_app
+#define TN_AW(dj, di) n_aw
+#define CN_QDOT n_qdot
+#define CK_AT ck[C_AT * kTileC]
+#define CK_AQV ck[C_AQV * kTileC]
+#define CK_AQC ck[C_AQC * kTileC]
+#define CK_RHO0 ck[C_RHO0 * kTileC]
+#define CK_RHO1 ck[C_RHO1 * kTileC]
+#define CK_T0 ck[C_T0 * kTileC]
+#define CK_CR ck[C_CR * kTileC]
+#define CK_XKC ck[C_XKC * kTileC]
+#define CK_QDOT ck[C_QDOT * kTileC]
 #define RPSB(dj, di) rp[(di) * kTW + (dj)]
 #define RCM_STORE_OK valid
 #include "k_ppw_level.inc"
@@ -106,7 +129,7 @@ k_ppw_tma(const Geom g, const Fields f, const StepScalars s) {
   }
   (void)app_m;
 }
-constexpr int kSmem = kStages * kStageBytes + kTile * 8 + 64;
+constexpr int kSmem = kStages * kStageBytes + kTileH * 8 + 64;
 }  // namespace
 
 bool ppw_tma_setup() {

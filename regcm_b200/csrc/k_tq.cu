@@ -71,6 +71,10 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
 #define TN_AQC(dj, di) L3(f.aqc, j + (dj), i + (di), k + 1)
 #define RCM_STORE_OK true
 #define RPSB(dj, di) L2(f.rpsb, j + (dj), i + (di))
+#define CK_CR L3(f.cr, j, i, k)
+#define CK_XKC L3(f.xkc, j, i, k)
+#define CK_AT L3(f.at, j, i, k)
+#define CN_QDOT L3(f.qdot, j, i, k + 1)
 #include "k_tq_level.inc"
 #undef RCM_STORE_OK
 #undef RPSB

@@ -1,7 +1,9 @@
-// k_tq with its stencil operands staged through shared memory by the TMA engine
-// (see k_uv_tma.cu for the scheme).  Tiles per level: au, av, th, aqv, aqc (1 ghost
-// cell used), bt, bqv, bqc (2 ghost cells, 4th-order diffusion); the 2-D 1/p* table
-// the diffusion operands are scaled with is staged once per block.
+// k_tq with its per-level operands staged through shared memory by the TMA engine
+// (see k_uv_tma.cu for the scheme).  Halo tiles (12 rows): au, av, th, aqv, aqc
+// (1 ghost cell used), bt, bqv, bqc (2 ghost cells, 4th-order diffusion); centre
+// tiles (8 rows): cr, xkc, at; the 2-D 1/p* table is staged once.  Two stages
+// (level k computed, k+1 in flight); the four level-(k+1) centre values (th, aqv,
+// aqc, qdot) are plain global loads issued at the top of the iteration.
 #include "dev_common.cuh"
 #include "launch.h"
 #include "tma_stage.cuh"
@@ -10,20 +12,18 @@
 using namespace rcm;
 
 namespace {
-#ifndef RCM_TQ_STAGES
-#define RCM_TQ_STAGES 3  // 3: level k+1 operands from the next tile; 2: from global memory (more blocks per SM)
-#endif
-constexpr int kBY = 8, kTW = 40, kTH = kBY + 4, kTile = kTW * kTH, kNT = 8, kStages = RCM_TQ_STAGES;
-constexpr int kAhead = kStages - 1;  // levels in flight ahead of the one being computed
-constexpr int kRowBytes = kTW * 8, kStageBytes = kNT * kTile * 8;
+constexpr int kBY = 8, kTW = 40, kTH = kBY + 4, kTileH = kTW * kTH, kTileC = kTW * kBY, kNH = 8, kNC = 3, kStages = 2;
+constexpr int kRowBytes = kTW * 8, kStageDbl = kNH * kTileH + kNC * kTileC, kStageBytes = kStageDbl * 8;
+constexpr int kCopies = kNH * kTH + kNC * kBY;  // 120 row copies per level
 enum { T_AU, T_AV, T_TH, T_AQV, T_AQC, T_BT, T_BQV, T_BQC };
+enum { C_CR, C_XKC, C_AT };
 
-__global__ void __launch_bounds__(256, kStages == 2 ? 3 : 2)
+__global__ void __launch_bounds__(256, 2)
 k_tq_tma(const Geom g, const Fields f, const StepScalars s) {
   extern __shared__ __align__(128) unsigned char smraw[];
   double* tiles = reinterpret_cast<double*>(smraw);
-  double* rtile = tiles + (size_t)kStages * kNT * kTile;  // rpsb, 2-D
-  uint64_t* full = reinterpret_cast<uint64_t*>(rtile + kTile);  // kStages + 1 barriers
+  double* rtile = tiles + (size_t)kStages * kStageDbl;  // rpsb, 2-D, halo rows
+  uint64_t* full = reinterpret_cast<uint64_t*>(rtile + kTileH);  // kStages + 1 barriers
   const int si = g.si;
   const long long sk = g.sk;
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * 32 + tx;
@@ -35,31 +35,36 @@ k_tq_tma(const Geom g, const Fields f, const StepScalars s) {
   int jstart = (j0 - 2) - (((j0 - 2) - jlo) & 1);
   jstart = min(jstart, jlo + si - kTW);
   const int ihi = g.ide2 + RCM_HALO;
-  const int to = (i - (i0 - 2)) * kTW + (j - jstart);
+  const int to = (i - (i0 - 2)) * kTW + (j - jstart);  // own cell in a halo tile
+  const int tc = (i - i0) * kTW + (j - jstart);        // own cell in a centre tile
 
   if (tid == 0) {
     for (int q = 0; q < kStages + 1; ++q) mbar_init(full + q, 1);
     mbar_init_fence();
   }
   __syncthreads();
-  const int cq = tid / kTH, cr_ = tid % kTH;
   const double* csrc = nullptr;
-  if (tid < kNT * kTH) {
-    const double* fld = cq == T_AU ? f.au : cq == T_AV ? f.av : cq == T_TH ? f.th : cq == T_AQV ? f.aqv
-                        : cq == T_AQC ? f.aqc : cq == T_BT ? f.bt : cq == T_BQV ? f.bqv : f.bqc;
-    csrc = &P3(fld, jstart, min(i0 - 2 + cr_, ihi), 0);
+  int cdst = 0;
+  if (tid < kNH * kTH) {
+    const int q = tid / kTH, r = tid % kTH;
+    const double* fld = q == T_AU ? f.au : q == T_AV ? f.av : q == T_TH ? f.th : q == T_AQV ? f.aqv
+                        : q == T_AQC ? f.aqc : q == T_BT ? f.bt : q == T_BQV ? f.bqv : f.bqc;
+    csrc = &P3(fld, jstart, min(i0 - 2 + r, ihi), 0);
+    cdst = q * kTileH + r * kTW;
+  } else if (tid < kCopies) {
+    const int c = tid - kNH * kTH, q = c / kBY, r = c % kBY;
+    const double* fld = q == C_CR ? f.cr : q == C_XKC ? f.xkc : f.at;
+    csrc = &P3(fld, jstart, min(i0 + r, ihi), 0);
+    cdst = kNH * kTileH + q * kTileC + r * kTW;
   }
   auto issue = [&](int level) {  // level = 1..kz
     const int st = (level - 1) % kStages;
     if (tid == 0) mbar_expect_tx(full + st, kStageBytes);
-    if (tid < kNT * kTH)
-      bulk_load(tiles + (size_t)(st * kNT + cq) * kTile + cr_ * kTW, csrc + (long long)level * sk, kRowBytes, full + st);
+    if (tid < kCopies) bulk_load(tiles + (size_t)st * kStageDbl + cdst, csrc + (long long)level * sk, kRowBytes, full + st);
   };
-  // 2-D 1/p* tile
-  if (tid == 0) mbar_expect_tx(full + kStages, kTile * 8);
+  if (tid == 0) mbar_expect_tx(full + kStages, kTileH * 8);
   if (tid < kTH) bulk_load(rtile + tid * kTW, &P2(f.rpsb, jstart, min(i0 - 2 + tid, ihi)), kRowBytes, full + kStages);
   issue(1);
-  if (kAhead >= 2 && kz >= 2) issue(2);
 
   const bool up = s.upstream_mode != 0;
   const bool se = s.stability_enhance != 0;
@@ -77,36 +82,35 @@ k_tq_tma(const Geom g, const Fields f, const StepScalars s) {
   const double beta = 0.53;
 
   double fx_th_k = 0.0, fl_qv_k = 0.0, fl_qc_k = 0.0;
+  double tha_k = L3(f.th, j, i, 1) * psa;
   mbar_wait(full + kStages, 0);
-  mbar_wait(full + 0, 0);  // level 1
-  double tha_k = tiles[T_TH * kTile + to] * psa;
   const double* rp = rtile + to;
 
   for (int k = 1; k <= kz; ++k) {
-    __syncthreads();  // everyone is done with level k-1: its stage can take level k+kAhead
-    if (k + kAhead <= kz) issue(k + kAhead);
+    __syncthreads();  // everyone is done with level k-1: its stage can take level k+1
+    if (k + 1 <= kz) issue(k + 1);
+    // level k+1 centre values straight from global memory, ahead of the wait
+    const bool nx = k < kz;
+    const double n_th = nx ? L3(f.th, j, i, k + 1) : 0.0, n_aqv = nx ? L3(f.aqv, j, i, k + 1) : 0.0,
+                 n_aqc = nx ? L3(f.aqc, j, i, k + 1) : 0.0, n_qdot = nx ? L3(f.qdot, j, i, k + 1) : 0.0;
     mbar_wait(full + (k - 1) % kStages, ((k - 1) / kStages) & 1);  // level k
-    if (kStages >= 3 && k < kz) mbar_wait(full + k % kStages, (k / kStages) & 1);  // level k+1
-    const double* tk = tiles + (size_t)((k - 1) % kStages) * kNT * kTile + to;
-    const double* tn = tiles + (size_t)(k % kStages) * kNT * kTile + to;
-    (void)tn;
-#define TK_AU(dj, di) tk[T_AU * kTile + (di) * kTW + (dj)]
-#define TK_AV(dj, di) tk[T_AV * kTile + (di) * kTW + (dj)]
-#define TK_TH(dj, di) tk[T_TH * kTile + (di) * kTW + (dj)]
-#define TK_AQV(dj, di) tk[T_AQV * kTile + (di) * kTW + (dj)]
-#define TK_AQC(dj, di) tk[T_AQC * kTile + (di) * kTW + (dj)]
-#define TK_BT(dj, di) tk[T_BT * kTile + (di) * kTW + (dj)]
-#define TK_BQV(dj, di) tk[T_BQV * kTile + (di) * kTW + (dj)]
-#define TK_BQC(dj, di) tk[T_BQC * kTile + (di) * kTW + (dj)]
-#if RCM_TQ_STAGES >= 3
-#define TN_TH(dj, di) tn[T_TH * kTile + (di) * kTW + (dj)]
-#define TN_AQV(dj, di) tn[T_AQV * kTile + (di) * kTW + (dj)]
-#define TN_AQC(dj, di) tn[T_AQC * kTile + (di) * kTW + (dj)]
-#else
-#define TN_TH(dj, di) L3(f.th, j + (dj), i + (di), k + 1)
-#define TN_AQV(dj, di) L3(f.aqv, j + (dj), i + (di), k + 1)
-#define TN_AQC(dj, di) L3(f.aqc, j + (dj), i + (di), k + 1)
-#endif
+    const double* tk = tiles + (size_t)((k - 1) % kStages) * kStageDbl + to;
+    const double* ck = tiles + (size_t)((k - 1) % kStages) * kStageDbl + kNH * kTileH + tc;
+#define TK_AU(dj, di) tk[T_AU * kTileH + (di) * kTW + (dj)]
+#define TK_AV(dj, di) tk[T_AV * kTileH + (di) * kTW + (dj)]
+#define TK_TH(dj, di) tk[T_TH * kTileH + (di) * kTW + (dj)]
+#define TK_AQV(dj, di) tk[T_AQV * kTileH + (di) * kTW + (dj)]
+#define TK_AQC(dj, di) tk[T_AQC * kTileH + (di) * kTW + (dj)]
+#define TK_BT(dj, di) tk[T_BT * kTileH + (di) * kTW + (dj)]
+#define TK_BQV(dj, di) tk[T_BQV * kTileH + (di) * kTW + (dj)]
+#define TK_BQC(dj, di) tk[T_BQC * kTileH + (di) * kTW + (dj)]
+#define TN_TH(dj, di) n_th
+#define TN_AQV(dj, di) n_aqv
+#define TN_AQC(dj, di) n_aqc
+#define CN_QDOT n_qdot
+#define CK_CR ck[C_CR * kTileC]
+#define CK_XKC ck[C_XKC * kTileC]
+#define CK_AT ck[C_AT * kTileC]
 #define RPSB(dj, di) rp[(di) * kTW + (dj)]
 #define RCM_STORE_OK valid
 #include "k_tq_level.inc"
@@ -114,7 +118,7 @@ k_tq_tma(const Geom g, const Fields f, const StepScalars s) {
 #undef RPSB
   }
 }
-constexpr int kSmem = kStages * kStageBytes + kTile * 8 + 64;
+constexpr int kSmem = kStages * kStageBytes + kTileH * 8 + 64;
 }  // namespace
 
 bool tq_tma_setup() {

@@ -1,5 +1,4 @@
 mkdir -p gpurun_out
 timeout 300 python -m pytest tests/test_gpu_parity.py -x -q 2>&1 | tail -3
-for T in 0 1; do echo "== PPW_TMA $T"; RCM_PPW_TMA=$T RCM_OVERLAP=0 timeout 300 bash scripts/gq.sh | grep -E "^[0-9]|k_uv|k_tq|k_ppw"; done
-echo "== tq 2 stages"; RCM_DYN_LIB=$PWD/regcm_b200/csrc/variants/libregcm_dyn_tq2s.so RCM_OVERLAP=0 timeout 300 bash scripts/gq.sh | grep -E "^[0-9]|k_tq"
+for T in 0 1; do echo "== TQ_TMA $T"; RCM_TQ_TMA=$T RCM_OVERLAP=0 timeout 300 bash scripts/gq.sh | grep -E "^[0-9]|k_uv|k_tq|k_ppw"; done
 echo "== overlap on"; timeout 300 bash scripts/gq.sh | grep -E "^[0-9]"
