@@ -39,6 +39,8 @@ void launch_snd_init(const Geom&, const Fields&, const StepScalars&, cudaStream_
 void launch_snd_uv(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_xkc(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_wfwd(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+bool wfwd_tma_setup();
+void launch_snd_wfwd_tma(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_wback(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_final(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_couple(const Geom&, double*, const double*, int, int, int, int, int, cudaStream_t);
@@ -67,6 +69,7 @@ struct rcm_dyn {
   bool prof_on = false;
   bool ppw_tma = false;      // k_ppw_tma instead of k_ppw
   bool tq_tma = false;       // k_tq_tma instead of k_tq
+  bool wfwd_tma = false;     // k_snd_wfwd_tma instead of k_snd_wfwd<false>
   void* uv_maps = nullptr;   // TMA tensor maps of k_uv_tma (nullptr: plain k_uv)
   bool overlap_slow = true;  // RCM_OVERLAP=0 serialises the slow-tendency kernels
   std::vector<ProfRec> prof_recs;
@@ -345,6 +348,8 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
     if (!e || std::atoi(e) != 0) h->tq_tma = tq_tma_setup();
     e = std::getenv("RCM_PPW_TMA");
     if (!e || std::atoi(e) != 0) h->ppw_tma = ppw_tma_setup();
+    e = std::getenv("RCM_WFWD_TMA");  // opt-in: measured slower than the plain kernel
+    if (e && std::atoi(e) != 0) h->wfwd_tma = wfwd_tma_setup();
   }
   h->halo.init(g, c.nproc, c.myid, cj, ci);
   *out = h;
@@ -1059,7 +1064,7 @@ static int tend(rcm_dyn* h) {
   for (int it = 1; it <= istep; ++it) {
     s.it = it;
     TIMED(KID_SND_UV, 1, launch_snd_uv(g, f, s, h->st));
-    TIMED(KID_SND_WFWD, 1, launch_snd_wfwd(g, f, s, h->st));
+    TIMED(KID_SND_WFWD, 1, (h->wfwd_tma && s.it > 1) ? launch_snd_wfwd_tma(g, f, s, h->st) : launch_snd_wfwd(g, f, s, h->st));
     if (h->cfg.ifupr == 1) {
       TIMED(KID_HALO, 0, rc = exch_estore(h));
       if (rc) return rc;

@@ -82,10 +82,6 @@ k_snd_uv(const Geom g, const Fields f, const StepScalars s) {
 // ---------------------------------------------------------------------------
 // One level of per-column coefficients (mod_sound.F90:335-372 for k = 1,
 // :373-416 for k >= 2 — the k-local part).
-struct SndLevel {
-  double tk, cc, cdd, cj, ptend, pp, wo;
-};
-
 // FIRST = first sub-step of a model step: the coefficients that do not change
 // during the step (cc, cdd and ca: 4 of the 10 divisions per level) are computed
 // and stored; the later sub-steps load them instead of pr1 and rho1.
@@ -112,161 +108,21 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
   if (pfd > 0)
     for (int kk = kz; kk >= max(kz - pfd, 1); --kk) prefetch(kk);
 
-  const double ps0 = L2(f.ps0, j, i), msfx = L2(f.msfx, j, i);
-  const double rpsb = 1.0 / L2(f.psb, j, i);
-  const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i), m11 = L2(f.msfd, j + 1, i + 1);
-
-  // winds at the four surrounding dots: [0]=(j,i) [1]=(j+1,i) [2]=(j,i+1) [3]=(j+1,i+1)
-  double up_[4], uc_[4], um_[4], vp_[4], vc_[4], vm_[4];  // levels m+1, m, m-1 of the record being built
-#define LOADUV(U, V, kk)                                                            \
-  U[0] = L3(f.cu, j, i, kk); U[1] = L3(f.cu, j + 1, i, kk); U[2] = L3(f.cu, j, i + 1, kk); U[3] = L3(f.cu, j + 1, i + 1, kk); \
-  V[0] = L3(f.cv, j, i, kk); V[1] = L3(f.cv, j + 1, i, kk); V[2] = L3(f.cv, j, i + 1, kk); V[3] = L3(f.cv, j + 1, i + 1, kk);
-
-  // Everything one level contributes, loaded as ONE batch before any arithmetic:
-  // the divisions below carry slow-path branches that end the basic block, and a
-  // load placed after one would cost its own memory round trip.
-  struct Raw {
-    double pr1, rho0, rho1, t0, nbt, ppten, pp, wo, p0w, p0e, p0s, p0n, ds;  // pr1 = cc, rho1 = cdd when !FIRST
-  };
-  auto loadraw = [&](int m) {
-    Raw r;
-    r.rho0 = L3(f.rho0, j, i, m);
-    if (FIRST) { r.pr1 = L3(f.pr1, j, i, m); r.rho1 = L3(f.rho1, j, i, m); }
-    else { r.pr1 = L3(f.scc, j, i, m); r.rho1 = L3(f.scdd, j, i, m); }
-    r.t0 = L3(f.t0, j, i, m); r.nbt = L3(f.nbt, j, i, m); r.ppten = L3(f.ppten, j, i, m);
-    r.pp = L3(f.cpp, j, i, m); r.wo = L3(f.cw, j, i, m);
-    r.p0w = L3(f.pr0, j - 1, i, m); r.p0e = L3(f.pr0, j + 1, i, m);
-    r.p0s = L3(f.pr0, j, i - 1, m); r.p0n = L3(f.pr0, j, i + 1, m);
-    r.ds = LD1(&f.dsigma[m]);
-    return r;
-  };
-  // reference p0 at the levels m+1 (or kz), m, m-1 of the record being built
-  double p0_p, p0_c, p0_m;
-
-  // build the k-local record of level m; needs u,v at m+1 (or kz), m, m-1 (or 1)
-  auto build = [&](int m, const Raw& r, SndLevel& L) {
-    L.tk = (0.5 * ps0 * r.t0) / (xgamma * p0_c * r.nbt * rpsb);
-    if (FIRST) {
-      L.cc = xgamma * r.pr1 * dts / (dx * msfx);
-      L.cdd = xgamma * r.pr1 * r.rho0 * egrav * dts / (ps0 * r.ds);
-      P3(f.scc, j, i, m) = L.cc;
-      P3(f.scdd, j, i, m) = L.cdd;
-    } else {
-      L.cc = r.pr1;
-      L.cdd = r.rho1;
-    }
-    L.cj = 0.5 * r.rho0 * egrav * dts;
-    double pxup, pyvp;
-    if (m == 1) {
-      const double den = (p0_c - p0_p);
-      pxup = 0.0625 * (r.p0e - r.p0w) *
-             (uc_[0] + uc_[1] + uc_[2] + uc_[3] - up_[0] - up_[1] - up_[2] - up_[3]) / den;
-      pyvp = 0.0625 * (r.p0n - r.p0s) *
-             (vc_[0] + vc_[1] + vc_[2] + vc_[3] - vp_[0] - vp_[1] - vp_[2] - vp_[3]) / den;
-    } else {
-      const double den = (p0_m - p0_p);
-      // at m = kz the "kp1" level is kz itself: up_ then aliases uc_ (set by caller)
-      pyvp = 0.125 * (r.p0n - r.p0s) *
-             (vm_[0] + vm_[1] + vm_[2] + vm_[3] - vp_[0] - vp_[1] - vp_[2] - vp_[3]) / den;
-      pxup = 0.125 * (r.p0e - r.p0w) *
-             (um_[0] + um_[1] + um_[2] + um_[3] - up_[0] - up_[1] - up_[2] - up_[3]) / den;
-      if (m == kz) { pyvp = pyvp * 0.5; pxup = pxup * 0.5; }
-    }
-    L.ptend = r.ppten -
-              0.5 * L.cc * ((vc_[2] * m01 - vc_[0] * m00 + vc_[3] * m11 - vc_[1] * m10 +
-                             uc_[1] * m10 - uc_[0] * m00 + uc_[3] * m11 - uc_[2] * m01) / msfx -
-                            2.0 * (pyvp + pxup));
-    L.pp = r.pp;
-    L.wo = r.wo;
-  };
-
-  // ---- bottom boundary condition (:323-334) ----
-  LOADUV(uc_, vc_, kz);
-  if (kz >= 2) { LOADUV(um_, vm_, kz - 1); }
-  Raw rk = loadraw(kz);
-  p0_c = L3(f.pr0, j, i, kz);
-  p0_p = (kz == 1) ? L3(f.pr0, j, i, 2) : p0_c;
-  p0_m = (kz >= 2) ? L3(f.pr0, j, i, kz - 1) : p0_c;
-  const double wo_bot = L3(f.cw, j, i, kzp1);
-  const double w_bot = 0.5 * 0.25 * regrav *
-                       ((vc_[2] + vc_[0] + vc_[3] + vc_[1]) * (L2(f.ht, j, i + 1) - L2(f.ht, j, i - 1)) +
-                        (uc_[2] + uc_[0] + uc_[3] + uc_[1]) * (L2(f.ht, j + 1, i) - L2(f.ht, j - 1, i))) /
-                       (dx * msfx);
-  double e_k = 0.0, f_k = w_bot;
-  P3(f.se, j, i, kz) = e_k;
-  P3(f.sf, j, i, kz) = f_k;
-
-  // record of level kz: "m+1" level is kz itself
-#pragma unroll
-  for (int q = 0; q < 4; ++q) { up_[q] = uc_[q]; vp_[q] = vc_[q]; }
-  SndLevel Lk, Lm;
-  build(kz, rk, Lk);
-  double wo_kp1 = wo_bot;  // wo(k+1)
-  double rho0_k = rk.rho0, rho1_k = rk.rho1, dsk = rk.ds;
-
-  for (int k = kz; k >= 2; --k) {
-    const int km1 = k - 1;
-    if (pfd > 0 && km1 - pfd >= 1) prefetch(km1 - pfd);
-    // ---- all loads of this iteration ----
-    double un_[4], vn_[4];
-    if (km1 >= 2) { LOADUV(un_, vn_, k - 2); }
-    const Raw rm = loadraw(km1);
-    const double p0_n = (km1 >= 2) ? L3(f.pr0, j, i, k - 2) : 0.0;
-    const double wten_k = L3(f.wten, j, i, k);
-    const double ca_ld = FIRST ? 0.0 : L3(f.sca, j, i, k);
-    // shift the wind and p0 windows down one level and build the record of k-1
-#pragma unroll
-    for (int q = 0; q < 4; ++q) { up_[q] = uc_[q]; vp_[q] = vc_[q]; uc_[q] = um_[q]; vc_[q] = vm_[q]; }
-    if (km1 >= 2) {
-#pragma unroll
-      for (int q = 0; q < 4; ++q) { um_[q] = un_[q]; vm_[q] = vn_[q]; }
-    }
-    const double p0_k = p0_c;  // pr0(k)
-    p0_p = p0_c; p0_c = p0_m; p0_m = p0_n;
-    build(km1, rm, Lm);
-    // ---- coefficients of level k (:373-401) ----
-    const double rho0_m = rm.rho0, rho1_m = rm.rho1, dsm = rm.ds;
-    double ca;
-    if (FIRST) {
-      const double rofac = (dsm * rho0_k + dsk * rho0_m) / (dsm * rho1_k + dsk * rho1_m);
-      ca = egrav * dts / (p0_k - p0_c) * rofac;
-      P3(f.sca, j, i, k) = ca;
-    } else {
-      ca = ca_ld;
-    }
-    const double g1 = 1.0 - dsm * Lk.tk;
-    const double g2 = 1.0 + dsk * Lm.tk;
-    const double c = -ca * (Lm.cdd - Lm.cj) * g2 * bpxbp;
-    const double b = 1.0 + ca * (g1 * (Lk.cdd - Lk.cj) + g2 * (Lm.cdd + Lm.cj)) * bpxbp;
-    const double aa = -ca * (Lk.cdd + Lk.cj) * g1 * bpxbp;
-    // rhs (:440-453): atmc%w(k) still equals wo(k) for k <= kz
-    const double rhs = Lk.wo + wten_k +
-                       ca * (bpxbm * ((Lm.cdd - Lm.cj) * g2 * Lm.wo -
-                                      ((Lm.cdd + Lm.cj) * g2 + (Lk.cdd - Lk.cj) * g1) * Lk.wo +
-                                      (Lk.cdd + Lk.cj) * g1 * wo_kp1) +
-                             (Lk.pp * g1 - Lm.pp * g2) + (g1 * Lk.ptend - g2 * Lm.ptend) * bp);
-    // p' after the explicit part (:454-464)
-    P3(f.cppd, j, i, k) = Lk.pp + Lk.ptend + (Lk.cj * (wo_kp1 + Lk.wo) + Lk.cdd * (wo_kp1 - Lk.wo)) * bm;
-    // upward elimination (:468-476)
-    const double denom = aa * e_k + b;
-    const double e_m = -c / denom;
-    const double f_m = (rhs - f_k * aa) / denom;
-    P3(f.se, j, i, km1) = e_m;
-    P3(f.sf, j, i, km1) = f_m;
-    e_k = e_m; f_k = f_m;
-    wo_kp1 = Lk.wo;
-    Lk = Lm;
-    rho0_k = rho0_m; rho1_k = rho1_m; dsk = dsm;
-  }
-  // level 1
-  const double ppmid1 = Lk.pp + Lk.ptend + (Lk.cj * (wo_kp1 + Lk.wo) + Lk.cdd * (wo_kp1 - Lk.wo)) * bm;
-  P3(f.cppd, j, i, 1) = ppmid1;
-  if (s.ifupr == 1) {
-    const double denom = (Lk.cdd + Lk.cj) * bp;
-    f.estore[(long long)j + (long long)i * g.esi] = ppmid1 + f_k * denom;
-    P2(f.astore, j, i) = denom * e_k + (Lk.cj - Lk.cdd) * bp;
-  }
-#undef LOADUV
+#define WF_OK true
+#define WF_ITER_BEGIN(k) if (pfd > 0 && (k) - 1 - pfd >= 1) prefetch((k) - 1 - pfd)
+#define WF_LOADUV_ITER(U, V) LOADUV(U, V, k - 2)
+#define WF_LOADRAW_ITER(r) r = loadraw(km1)
+#define WF_P0N L3(f.pr0, j, i, k - 2)
+#define WF_WTEN L3(f.wten, j, i, k)
+#define WF_CA L3(f.sca, j, i, k)
+#include "k_snd_wfwd_body.inc"
+#undef WF_OK
+#undef WF_ITER_BEGIN
+#undef WF_LOADUV_ITER
+#undef WF_LOADRAW_ITER
+#undef WF_P0N
+#undef WF_WTEN
+#undef WF_CA
 }
 
 // ---------------------------------------------------------------------------

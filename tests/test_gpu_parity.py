@@ -67,13 +67,13 @@ def test_boundary_record_change_and_long_run(cuda_lib):
 
 @pytest.mark.parametrize("name", ["small", "C2"])
 def test_staged_kernels_equal_plain_kernels(cuda_lib, name, monkeypatch):
-    """The TMA/shared-memory staged variants of the slow-tendency kernels share their
+    """The TMA/shared-memory staged variants of the slow-tendency kernels and of the forward sweep share their
     arithmetic with the plain kernels (k_*_level.inc): results must be bit-identical."""
     case = synth.make_case(name)
-    for v in ("RCM_UV_TMA", "RCM_TQ_TMA", "RCM_PPW_TMA"):
+    for v in ("RCM_UV_TMA", "RCM_TQ_TMA", "RCM_PPW_TMA", "RCM_WFWD_TMA"):
         monkeypatch.setenv(v, "1")
     a = capi.DynCore(cuda_lib, case.cfg); synth.load_case(a, case)
-    for v in ("RCM_UV_TMA", "RCM_TQ_TMA", "RCM_PPW_TMA"):
+    for v in ("RCM_UV_TMA", "RCM_TQ_TMA", "RCM_PPW_TMA", "RCM_WFWD_TMA"):
         monkeypatch.setenv(v, "0")
     b = capi.DynCore(cuda_lib, case.cfg); synth.load_case(b, case)
     a.step(5); b.step(5)
