@@ -4,8 +4,8 @@
 //   k_snd_uv     :270-299  explicit u,v (pressure-gradient) step
 //   k_snd_wfwd   :317-476  w/p' coefficients, tridiagonal forward elimination
 //                          (bottom-up), estore/astore for the radiative BC
-//   k_snd_wpval  :551-561  13x13 upper-radiative-BC convolution
-//   k_snd_wback  :565-689  back substitution, CFL, new p', T correction,
+//   k_snd_wback  :551-561  13x13 upper-radiative-BC convolution (per column), then
+//                :565-689  back substitution, CFL, new p', T correction,
 //                          divergence damping + d p'/d p0 for the next sub-step
 //   k_snd_final  :696-712  recouple, Robert-Asselin filters, tiny-w flush
 //
