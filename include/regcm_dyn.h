@@ -52,7 +52,12 @@ enum rcm_field {
   RCM_F_QC = 4, /* cross                  p*·qc */
   RCM_F_PP = 5, /* cross                  p*·p' */
   RCM_F_W = 6,  /* cross (jx-1,iy-1,kz+1) p*·w  */
-  RCM_F_COUNT = 7
+  RCM_F_PS = 7, /* cross (jx-1,iy-1) 2-D: p* = ps - ptop [cb], sfs%psa/psb
+                 * (idynamic = 1 only; Main/mod_atm_interface.F90 `sfs`).  As a
+                 * boundary field (xpsb, rcm_dyn_set_bdy) the value passed is the
+                 * ICBC surface pressure in hPa; the library converts it like
+                 * Main/mod_bdycod.F90:394 (`ps*0.1 - ptop`). */
+  RCM_F_COUNT = 8
 };
 
 /* static domain fields: members of `mddom` read by read_domain_info
@@ -91,7 +96,26 @@ enum rcm_work {
   RCM_W_VTEN = 7,
   RCM_W_PPTEN = 8,
   RCM_W_WTEN = 9,  /* (kz+1) */
-  RCM_W_COUNT = 10
+  /* idynamic = 1 */
+  RCM_W_OMEGA = 10, /* omega      Main/mod_tendency.F90:1199-1215  [cb/s]   */
+  RCM_W_PHI = 11,   /* phi        Main/mod_tendency.F90:2069-2097           */
+  RCM_W_PTEN = 12,  /* pten (2-D) Main/mod_tendency.F90:1131-1148, before nudging */
+  RCM_W_COUNT = 13
+};
+
+/* vertical-mode tables of the split-explicit scheme (idynamic = 1), computed
+ * once by `spinit`/`vmodes` (Main/mod_split.F90:75-175, Main/mod_vmodes.F90:86-594).
+ * Column-major like the Fortran arrays. */
+enum rcm_table {
+  RCM_T_HBAR = 0,   /* hbar(kz)        equivalent depths, descending         */
+  RCM_T_ZMATX = 1,  /* zmatx(kz,kz)    after the `fac` scaling of spinit     */
+  RCM_T_ZMATXR = 2, /* zmatxr(kz,kz)                                         */
+  RCM_T_TAU = 3,    /* tau(kz,kz)      as left by spinit (rows 1..nsplit)    */
+  RCM_T_VARPA1 = 4, /* varpa1(kz,kz+1) as left by spinit                     */
+  RCM_T_AM = 5,     /* am(kz,nsplit)                                         */
+  RCM_T_AN = 6,     /* an(nsplit)                                            */
+  RCM_T_TAU0 = 7,   /* tau(kz,kz) of vmodes (the matrix whose eigenproblem is solved) */
+  RCM_T_COUNT = 8
 };
 
 /* Flat copy of the namelist scalars the dyn-core reads
@@ -122,7 +146,10 @@ typedef struct rcm_cfg {
   int32_t nproc, myid;
   int32_t cpus_j, cpus_i; /* 0,0 = choose like set_nproc                   */
   int32_t device;         /* CUDA device ordinal, -1 = myid % device count */
-  int32_t reserved_i[8];
+  /* &hydroparam (idynamic = 1; Main/mod_params.F90:113,283-284) */
+  int32_t nsplit;         /* number of split-explicit vertical modes (2)   */
+  int32_t lstand;         /* 1: linearise vmodes about the standard atmosphere */
+  int32_t reserved_i[6];
   /* &geoparam */
   double ds;    /* grid spacing [km]                                       */
   double ptop;  /* model top pressure [cb]                                 */
@@ -148,6 +175,10 @@ typedef struct rcm_diag {
   int32_t istep;      /* acoustic sub-steps of last step                   */
   int32_t nan_flag;
   int64_t neg_q_points; /* points repaired by the negative-q fix, last step */
+  /* idynamic = 1: Bleck (1977) noise parameters of the last step, summed over
+   * the interior (Main/mod_tendency.F90:1449-1459; the reference divides by
+   * the number of points when it prints them, :715-716) */
+  double ptntot, pt2tot;
 } rcm_diag;
 
 typedef struct rcm_dyn rcm_dyn; /* opaque */
@@ -207,6 +238,11 @@ int rcm_dyn_set_state(rcm_dyn* h, int field, int level, const double* a,
 /* debug tap, see enum rcm_work */
 int rcm_dyn_get_work(rcm_dyn* h, int work_id, double* a, const int32_t lb[3],
                      const int32_t ub[3]);
+
+/* replaces: the public tables of mod_vmodes / mod_split (Main/mod_vmodes.F90:39-52,
+ * Main/mod_split.F90:40-42).  Copies min(n, size) doubles, returns the table size
+ * (or a negative RCM_ERR_*). */
+int rcm_dyn_get_table(rcm_dyn* h, int table_id, double* out, int n);
 
 int rcm_dyn_diag(rcm_dyn* h, rcm_diag* out);
 int rcm_dyn_last_error(rcm_dyn* h, char* buf, int len);

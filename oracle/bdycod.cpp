@@ -270,6 +270,7 @@ void Oracle::bdyval() {
         a2_w(j, ice1, k) = a1_w(j, ice1, k); a2_w(j, ice2, k) = a1_w(j, ice2, k);
       }
   }
+  if (hydro) bdyval_ps();  // p* rim first (:1317-1342,1426-1451)
   // boundary values of p*u, p*v (:1393-1425 fixed, :1494-1525 time dependent)
   const double xtu = (iboudy == 0) ? d_zero : xt;
   auto bc = [&](const V3dBound& b, int j, int i, int k) {

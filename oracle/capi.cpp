@@ -42,6 +42,7 @@ int orc_diag(void* h, rcm_diag* d) {
   d->lcount = o->lcount; d->xbctime = o->xbctime; d->dt = o->dt;
   d->max_cfl = o->max_cfl_step; d->istep = o->last_istep;
   d->neg_q_points = o->neg_q_points;
+  d->ptntot = o->ptntot; d->pt2tot = o->pt2tot;
   return RCM_OK;
 }
 int orc_last_error(void* h, char* buf, int len) {
@@ -66,6 +67,7 @@ int orc_get_aux(void* h, const char* name, double* out, int n) {
   std::memcpy(out, v->data(), v->size() * sizeof(double));
   return (int)v->size();
 }
+int orc_get_table(void* h, int id, double* out, int n) { return ((Oracle*)h)->get_table(id, out, n); }
 int orc_get_zone(void* h, int dot, int32_t* out) {
   // packed zone map: bits 0..3 = south,north,west,east; bits 8.. = ibnd
   Oracle* o = (Oracle*)h;

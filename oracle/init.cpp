@@ -262,12 +262,17 @@ void Oracle::init_state() {
       }
 }
 
-// Main/mod_diffusion.F90:93-167 (idiffu < 3, idynamic == 2)
+// Main/mod_diffusion.F90:93-167 (idiffu < 3)
 void Oracle::initialize_diffusion() {
   xkhmax = dxsq / (64.0 * dtsec);
   dydc = cfg.adyndif * vonkar * vonkar * dx * d_rfour;
-  double xkhz = cfg.ckh * dx;
-  xkhmax = d_two * xkhmax;
+  double xkhz;
+  if (hydro) {
+    xkhz = cfg.ckh * 1.5e-3 * dxsq / dtsec;
+  } else {
+    xkhz = cfg.ckh * dx;
+    xkhmax = d_two * xkhmax;
+  }
   for (int i = ice1; i <= ice2; ++i)
     for (int j = jce1; j <= jce2; ++j) hgfact(j, i) = xkhz;
   if (cfg.diffu_hgtf == 1) {
@@ -311,6 +316,15 @@ int Oracle::init() {
   param_static();
   init_advection();
   setup_bdycon();
+  if (hydro) {
+    init_bdy_hydro();
+    init_state_hydro();
+    initialize_diffusion();
+    spinit();   // Main/mod_regcm_interface.F90:141
+    if (vm_numerr) { err = "vmodes: vertical mode problem reported errors"; return RCM_ERR_ARG; }
+    bdyval();   // :146
+    return RCM_OK;
+  }
   make_reference_atmosphere();
   compute_full_coriolis_coefficients();
   init_bdy();
@@ -341,7 +355,7 @@ int Oracle::step(int n) {
     if (cfl_error) { err = "CFL violation"; return RCM_ERR_CFL; }
     if (alarm_bdy_act()) {
       if (!have_next) { err = "boundary record needed but not staged"; return RCM_ERR_BDY; }
-      bdyin();
+      if (hydro) bdyin_hydro(); else bdyin();
     }
     bdyval();
   }
@@ -374,6 +388,14 @@ int Oracle::get_state(int field, int level, double* a, const int32_t lb[3], cons
     case RCM_F_QC: copy_out_4d(A ? a1_qx : a2_qx, iqc, a, lb, ub); return RCM_OK;
     case RCM_F_PP: copy_out_3d(A ? a1_pp : a2_pp, a, lb, ub); return RCM_OK;
     case RCM_F_W: copy_out_3d(A ? a1_w : a2_w, a, lb, ub); return RCM_OK;
+    case RCM_F_PS: {
+      const A2& src = A ? psa : psb;
+      const int n1 = ub[0] - lb[0] + 1;
+      for (int i = std::max(lb[1], src.l2); i <= std::min(ub[1], src.l2 + src.n2 - 1); ++i)
+        for (int j = std::max(lb[0], src.l1); j <= std::min(ub[0], src.l1 + src.n1 - 1); ++j)
+          a[(size_t)(j - lb[0]) + (size_t)n1 * (size_t)(i - lb[1])] = src(j, i);
+      return RCM_OK;
+    }
   }
   err = "bad field"; return RCM_ERR_ARG;
 }
@@ -390,6 +412,15 @@ int Oracle::get_work(int id, double* a, const int32_t lb[3], const int32_t ub[3]
     case RCM_W_PPTEN: copy_out_3d(ppten, a, lb, ub); return RCM_OK;
     case RCM_W_WTEN: copy_out_3d(wten, a, lb, ub); return RCM_OK;
     case RCM_W_XKC: copy_out_3d(xkc_raw, a, lb, ub); return RCM_OK;
+    case RCM_W_OMEGA: copy_out_3d(omega, a, lb, ub); return RCM_OK;
+    case RCM_W_PHI: copy_out_3d(phi, a, lb, ub); return RCM_OK;
+    case RCM_W_PTEN: {
+      const int n1 = ub[0] - lb[0] + 1;
+      for (int i = std::max(lb[1], pten.l2); i <= std::min(ub[1], pten.l2 + pten.n2 - 1); ++i)
+        for (int j = std::max(lb[0], pten.l1); j <= std::min(ub[0], pten.l1 + pten.n1 - 1); ++j)
+          a[(size_t)(j - lb[0]) + (size_t)n1 * (size_t)(i - lb[1])] = pten_raw(j, i);
+      return RCM_OK;
+    }
   }
   err = "bad work id"; return RCM_ERR_ARG;
 }

@@ -20,6 +20,10 @@ struct V3dBound {  // type v3dbound, Main/mpplib/mod_regcm_types.F90
   A3 b0, b1, bt;
 };
 
+struct V2dBound {  // type v2dbound
+  A2 b0, b1, bt;
+};
+
 struct BoundArea {  // type bound_area, Main/mod_atm_interface.F90:383-542
   int nsp = 0, ns = 0, nn = 0, nw = 0, ne = 0;
   bool havebound = false;
@@ -132,6 +136,47 @@ struct Oracle {
   int last_istep = 0;
   bool cfl_error = false;
   int64_t neg_q_points = 0;
+
+  // ---- hydrostatic core (idynamic = 1; oracle/hydro.cpp, oracle/split.cpp) ----
+  bool hydro = false;
+  A2 pten, pten_raw, rpsc, ptn2d, pt22d;          // mod_tendency.F90:63-66
+  A3 phi, td, tvfac, pf3d, pb3d;        // mod_tendency.F90:57-62, atms%pf3d/pb3d
+  V2dBound xpsb;                        // mod_atm_interface.F90 xpsb
+  A2 nx_ps;                             // staged next ps record [hPa]
+  double ptntot = 0, pt2tot = 0;
+  // mod_vmodes.F90:46-52
+  int nsplit = 2;
+  double xps = 0, pd = 0;
+  A2 vm_a0, zmatx, zmatxr, vm_tau, vm_tau0, varpa1, hydroc, hydros;
+  A1 sigmah, tbarh, hbar;
+  int vm_numerr = 0;
+  // mod_split.F90:40-51, mod_atm_interface dstor/hstor
+  A1 aam, an_, dtau;
+  A2 am_, map_, uu, vv, xdelh;
+  A3 uuu, vvv, ddsum, dhsum, work, dstor, hstor;
+  A4 deld, delh;
+  void allocate_hydro();
+  void init_bdy_hydro();
+  void init_state_hydro();
+  void bdyin_hydro();
+  void bdyval_ps();
+  void surface_pressures_hydro();
+  void decouple_hydro();
+  void compute_omega_hydro();
+  void mkslice_hydro();
+  void new_pressure();
+  void nudge2d(int ibdy, const A2& f, const V2dBound& bnd, A2& ften);
+  void calc_coeff_hydro();
+  void hadvuv_hydro(A3& ut, A3& vt, const A3& u, const A3& v);
+  void vadv3d_ind1_hydro(A3& ften, const A3& f);
+  void pressure_gradient_force();
+  void filter_ra_2d(A2& phin, A2& phinm1, const A2& phinp1, double alpha);
+  void tend_hydro();
+  void vmodes();
+  void spinit();
+  void splitf();
+  void spstep();
+  int get_table(int id, double* out, int n);
 
   // ---- life cycle (oracle/setup.cpp) ----
   int create(const rcm_cfg& c);

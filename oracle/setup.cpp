@@ -22,7 +22,10 @@ namespace orc {
 int Oracle::create(const rcm_cfg& c) {
   cfg = c;
   if (c.struct_size != (int)sizeof(rcm_cfg)) { err = "rcm_cfg size mismatch"; return RCM_ERR_ARG; }
-  if (c.idynamic != 2) { err = "oracle: only idynamic=2 restated so far"; return RCM_ERR_ARG; }
+  if (c.idynamic != 1 && c.idynamic != 2) { err = "oracle: idynamic must be 1 or 2 (MOLOCH not restated)"; return RCM_ERR_ARG; }
+  hydro = (c.idynamic == 1);
+  if (hydro && (c.nsplit < 1 || c.nsplit > c.kz)) { err = "oracle: nsplit out of range"; return RCM_ERR_ARG; }
+  nsplit = hydro ? c.nsplit : 0;
   if (c.idiffu != 1) { err = "oracle: only idiffu=1"; return RCM_ERR_ARG; }
   if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 5)) { err = "oracle: iboudy must be 0,1,5"; return RCM_ERR_ARG; }
   if (c.nqx != 2) { err = "oracle: nqx must be 2"; return RCM_ERR_ARG; }
@@ -42,6 +45,7 @@ int Oracle::create(const rcm_cfg& c) {
   xbctime = 0; have_next = false;
   setup_model_indexes();
   allocate_all();
+  if (hydro) allocate_hydro();
   setup_boundaries(false, false, ba_cr);   // mod_params.F90:1788-1793
   setup_boundaries(true, true, ba_dt);
   return RCM_OK;
@@ -261,6 +265,13 @@ int Oracle::set_static(int id, const double* a, const int32_t lb[3], const int32
 }
 
 int Oracle::set_bdy(int field, int slot, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (field == RCM_F_PS) {
+    if (!hydro) { err = "ps boundary data exist for idynamic = 1 only"; return RCM_ERR_ARG; }
+    if (slot == RCM_BDY_B0) return copy_in_2d(xpsb.b0, a, lb, ub);
+    if (slot == RCM_BDY_B1) return copy_in_2d(xpsb.b1, a, lb, ub);
+    if (slot == RCM_BDY_NEXT) { have_next = true; return copy_in_2d(nx_ps, a, lb, ub); }
+    err = "bad slot"; return RCM_ERR_ARG;
+  }
   V3dBound* b = nullptr; A3* nx = nullptr;
   switch (field) {
     case RCM_F_U: b = &xub; nx = &nx_u; break;
@@ -296,6 +307,7 @@ int Oracle::set_state(int field, int level, const double* a, const int32_t lb[3]
     case RCM_F_QC: return in4(A ? a1_qx : a2_qx, iqc);
     case RCM_F_PP: return copy_in_3d(A ? a1_pp : a2_pp, a, lb, ub);
     case RCM_F_W: return copy_in_3d(A ? a1_w : a2_w, a, lb, ub);
+    case RCM_F_PS: return copy_in_2d(A ? psa : psb, a, lb, ub);
   }
   err = "bad field"; return RCM_ERR_ARG;
 }

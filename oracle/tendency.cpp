@@ -145,6 +145,18 @@ void Oracle::decouple() {
     for (int i = ice1; i <= ice2; ++i)
       for (int j = jce1; j <= jce2; ++j)
         ax_tv(j, i, k) = ax_t(j, i, k) * (d_one + ep1 * ax_qx(j, i, k, iqv));
+  if (hydro) {  // idynamic == 1 (:1036-1040, :1093-1096)
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ice1; i <= ice2; ++i)
+        for (int j = jce1; j <= jce2; ++j) {
+          a1_pr(j, i, k) = (hsigma(k) * psa(j, i) + ptop) * d_1000;
+          a1_rho(j, i, k) = a1_pr(j, i, k) / (rgas * ax_tv(j, i, k));
+        }
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ice1; i <= ice2; ++i)
+        for (int j = jce1; j <= jce2; ++j) a2_pr(j, i, k) = (hsigma(k) * psb(j, i) + ptop) * d_1000;
+    return;
+  }
   // non-hydrostatic part (:1046-1065)
   for (int k = 1; k <= kz; ++k)
     for (int i = ice1; i <= ice2; ++i)
@@ -340,6 +352,7 @@ void Oracle::diffusion() {
 }
 
 void Oracle::tend() {
+  if (hydro) { tend_hydro(); return; }
   static const bool prof = std::getenv("ORC_PROF") != nullptr;
   auto t0 = std::chrono::steady_clock::now();
   auto lap = [&](const char* nm) {

@@ -17,13 +17,15 @@ from typing import Sequence
 import numpy as np
 
 # enum rcm_field / rcm_static / rcm_work (include/regcm_dyn.h)
-F_U, F_V, F_T, F_QV, F_QC, F_PP, F_W = range(7)
-FIELD_NAMES = ("u", "v", "t", "qv", "qc", "pp", "w")
+F_U, F_V, F_T, F_QV, F_QC, F_PP, F_W, F_PS = range(8)
+FIELD_NAMES = ("u", "v", "t", "qv", "qc", "pp", "w", "ps")
 S_HT, S_MSFX, S_MSFD, S_CORIOL, S_XLAT, S_XLON, S_DLAT, S_SIGMA = range(8)
 LEVEL_A, LEVEL_B = 0, 1
 BDY_B0, BDY_B1, BDY_NEXT = 0, 1, 2
-W_CR, W_QDOT, W_XKC, W_TH, W_RHO1, W_PR1, W_UTEN, W_VTEN, W_PPTEN, W_WTEN = range(10)
-WORK_NAMES = ("cr", "qdot", "xkc", "th", "rho1", "pr1", "uten", "vten", "ppten", "wten")
+W_CR, W_QDOT, W_XKC, W_TH, W_RHO1, W_PR1, W_UTEN, W_VTEN, W_PPTEN, W_WTEN, W_OMEGA, W_PHI, W_PTEN = range(13)
+WORK_NAMES = ("cr", "qdot", "xkc", "th", "rho1", "pr1", "uten", "vten", "ppten", "wten", "omega", "phi", "pten")
+# enum rcm_table: vertical-mode tables of the split-explicit scheme (idynamic = 1)
+T_HBAR, T_ZMATX, T_ZMATXR, T_TAU, T_VARPA1, T_AM, T_AN, T_TAU0 = range(8)
 
 ERRORS = {0: "RCM_OK", -1: "RCM_ERR_ARG", -2: "RCM_ERR_CUDA", -3: "RCM_ERR_CFL",
           -4: "RCM_ERR_NAN", -5: "RCM_ERR_NCCL", -6: "RCM_ERR_BDY", -7: "RCM_ERR_STATE"}
@@ -42,7 +44,8 @@ class RcmCfg(C.Structure):
         ("nproc", C.c_int32), ("myid", C.c_int32),
         ("cpus_j", C.c_int32), ("cpus_i", C.c_int32),
         ("device", C.c_int32),
-        ("reserved_i", C.c_int32 * 8),
+        ("nsplit", C.c_int32), ("lstand", C.c_int32),
+        ("reserved_i", C.c_int32 * 6),
         ("ds", C.c_double), ("ptop", C.c_double),
         ("dt", C.c_double),
         ("gnu1", C.c_double), ("gnu2", C.c_double), ("ckh", C.c_double), ("adyndif", C.c_double),
@@ -60,6 +63,7 @@ class RcmDiag(C.Structure):
         ("lcount", C.c_int64), ("xbctime", C.c_double), ("dt", C.c_double),
         ("max_cfl", C.c_double), ("istep", C.c_int32), ("nan_flag", C.c_int32),
         ("neg_q_points", C.c_int64),
+        ("ptntot", C.c_double), ("pt2tot", C.c_double),
     ]
 
 
@@ -77,6 +81,7 @@ def default_cfg(idynamic: int = 2, **kw) -> RcmCfg:
     c.upstream_mode = c.stability_enhance = 1
     c.nproc, c.myid, c.cpus_j, c.cpus_i, c.device = 1, 0, 0, 0, -1
     c.ptop = 5.0
+    c.nsplit, c.lstand = 2, 1   # Main/mod_params.F90:283-284
     if idynamic == 2:
         c.gnu1 = c.gnu2 = 0.1
         c.diffu_hgtf = 0
@@ -146,6 +151,7 @@ class CoreLib:
             "launch_count": ([vp], C.c_int64),
             "last_step_ms": ([vp], C.c_double),
             "get_tile": ([vp, C.POINTER(C.c_int32)], C.c_int),
+            "get_table": ([vp, C.c_int, _DP, C.c_int], C.c_int),
             "profile": ([vp, C.c_int], C.c_int),
             "profile_get": ([vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_char_p, C.c_int], C.c_int),
             "profile_kernels": ([], C.c_int),
@@ -191,6 +197,8 @@ class DynCore:
             return (jx, iy, kz)
         if field == F_W:
             return (jx - 1, iy - 1, kz + 1)
+        if field == F_PS:
+            return (jx - 1, iy - 1, 1)
         return (jx - 1, iy - 1, kz)
 
     # -- API ---------------------------------------------------------------
@@ -205,6 +213,8 @@ class DynCore:
 
     def set_bdy(self, field: int, slot: int, a: np.ndarray, lb=(1, 1, 1)):
         a = self._f(a)
+        if a.ndim == 2:
+            a = a.reshape(a.shape + (1,), order="F")
         ub = tuple(lb[d] + a.shape[d] - 1 for d in range(3))
         self._check(self.lib.set_bdy(self.h, field, slot, a.ctypes.data_as(_DP), *_bounds(lb, ub)))
 
@@ -236,6 +246,8 @@ class DynCore:
 
     def set_state(self, field: int, level: int, a: np.ndarray, lb=(1, 1, 1)):
         a = self._f(a)
+        if a.ndim == 2:
+            a = a.reshape(a.shape + (1,), order="F")
         ub = tuple(lb[d] + a.shape[d] - 1 for d in range(3))
         self._check(self.lib.set_state(self.h, field, level, a.ctypes.data_as(_DP), *_bounds(lb, ub)))
 
@@ -249,11 +261,28 @@ class DynCore:
             lb, ub = (2, 2, 1), (jx - 2, iy - 2, kz + 1)
         elif wid == W_QDOT:
             lb, ub = (1, 1, 1), (jx - 1, iy - 1, kz + 1)
+        elif wid == W_OMEGA:
+            lb, ub = (2, 2, 1), (jx - 2, iy - 2, kz)
+        elif wid == W_PTEN:
+            lb, ub = (1, 1, 1), (jx - 1, iy - 1, 1)
         else:
             lb, ub = (1, 1, 1), (jx - 1, iy - 1, kz)
         out = np.zeros(tuple(ub[d] - lb[d] + 1 for d in range(3)), dtype=np.float64, order="F")
         self._check(self.lib.get_work(self.h, wid, out.ctypes.data_as(_DP), *_bounds(lb, ub)))
         return out
+
+    def get_table(self, tid: int) -> np.ndarray:
+        """Vertical-mode table `tid` (enum rcm_table) as a Fortran-ordered array."""
+        kz, ns = self.kz, self.cfg.nsplit
+        shape = {T_HBAR: (kz,), T_ZMATX: (kz, kz), T_ZMATXR: (kz, kz), T_TAU: (kz, kz), T_VARPA1: (kz, kz + 1),
+                 T_AM: (kz, ns), T_AN: (ns,), T_TAU0: (kz, kz)}[tid]
+        n = int(np.prod(shape))
+        out = np.zeros(n, dtype=np.float64)
+        rc = self.lib.get_table(self.h, tid, out.ctypes.data_as(_DP), n)
+        if rc < 0:
+            self._check(rc)
+        assert rc == n, (rc, n)
+        return out.reshape(shape, order="F")
 
     def diag(self) -> RcmDiag:
         d = RcmDiag()

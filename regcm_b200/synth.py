@@ -49,6 +49,7 @@ CASES = {
     # name: jx, iy, kz, ds[km], dt[s], nspg
     "tiny": dict(jx=20, iy=16, kz=8, ds=60.0, dt=120.0, nspg=4),
     "small": dict(jx=40, iy=30, kz=14, ds=60.0, dt=120.0, nspg=6),
+    "C1": dict(jx=64, iy=34, kz=18, ds=60.0, dt=150.0, nspg=12, idynamic=1),  # Testing/test_001.in shape, hydrostatic
     "C2": dict(jx=64, iy=34, kz=18, ds=60.0, dt=120.0, nspg=8),
     "C3": dict(jx=250, iy=200, kz=23, ds=50.0, dt=120.0, nspg=12),
     "C4": dict(jx=1000, iy=1000, kz=41, ds=3.0, dt=6.0, nspg=12),
@@ -102,7 +103,9 @@ def make_case(name: str = "C2", *, flat: bool = False, unit_map: bool = False, n
         if k in cfg_over:
             p[k] = cfg_over.pop(k)
     jx, iy, kz = p["jx"], p["iy"], p["kz"]
-    cfg = capi.default_cfg(2, jx=jx, iy=iy, kz=kz, ds=p["ds"], dt=p["dt"],
+    idynamic = cfg_over.pop("idynamic", p.get("idynamic", 2))
+    hydro = idynamic == 1
+    cfg = capi.default_cfg(idynamic, jx=jx, iy=iy, kz=kz, ds=p["ds"], dt=p["dt"],
                            nspgx=p["nspg"], nspgd=p["nspg"], ibdyfrq=ibdyfrq)
     for k, v in cfg_over.items():
         setattr(cfg, k, v)
@@ -184,6 +187,11 @@ def make_case(name: str = "C2", *, flat: bool = False, unit_map: bool = False, n
         u = u + 2.0e-2 * nz_u
         v = v + 2.0e-2 * nz_v
         qv = np.maximum(0.012 * np.exp(-z / 2500.0) * (1.0 + 0.2 * np.sin(2 * np.pi * xs_c / Lx)), 1.0e-8)
+        if hydro:
+            # surface pressure [hPa] on the terrain (same closed form as the profile above) with a
+            # smooth travelling perturbation, so that the p* boundary tendency is non-zero
+            ps = (ps0 + ptop_pa) * 0.01 * (1.0 + 1.0e-3 * np.sin(2 * np.pi * (Xc - phase) / Lx) * np.cos(2 * np.pi * Yc / Ly))
+            return {capi.F_U: F(u), capi.F_V: F(v), capi.F_T: F(t), capi.F_QV: F(qv), capi.F_PS: F(ps)}
         pp = np.zeros(Xc.shape + (kz,))
         ww = np.zeros(Xc.shape + (kz + 1,))
         return {capi.F_U: F(u), capi.F_V: F(v), capi.F_T: F(t), capi.F_QV: F(qv),
