@@ -20,6 +20,7 @@
 #include "dyn_types.h"
 #include "halo.h"
 #include "launch.h"
+#include "split_host.h"
 
 using namespace rcm;
 
@@ -48,6 +49,21 @@ void launch_timeint(const Geom&, const double*, const double*, double*, double, 
 void launch_bdyval(const Geom&, const Fields&, const double*, const double*, const double*, const int2*, int,
                    const int2*, int, double, int, int, cudaStream_t);
 
+// hydrostatic core (k_hydro.cu, k_split.cu)
+void launch_psc2psd(const Geom&, const double*, double*, double*, cudaStream_t);
+void launch_ps_convert(const Geom&, double*, double, cudaStream_t);
+void launch_h_ps(const Geom&, const Fields&, cudaStream_t);
+void launch_h_rimcopy(const Geom&, const Fields&, const int2*, int, const int2*, int, cudaStream_t);
+void launch_h_prep(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_h_uv(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_h_tq(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_h_psfilt(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_bdyval_ps(const Geom&, const Fields&, const int2*, int, double, int, cudaStream_t);
+void launch_sp_init(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_sp_proj(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_sp_step(const Geom&, const Fields&, const StepScalars&, int, cudaStream_t);
+void launch_sp_corr(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+
 #define CUDA_OK(call)                                                                   \
   do {                                                                                  \
     cudaError_t e_ = (call);                                                            \
@@ -60,9 +76,10 @@ void launch_bdyval(const Geom&, const Fields&, const double*, const double*, con
 // per-kernel device timing (CUDA events on the library's stream), enabled by
 // rcm_dyn_profile(); used by bench.py for the per-kernel roofline
 enum { KID_PREP, KID_XKC, KID_UV, KID_TQ, KID_PPW, KID_SND_INIT, KID_SND_UV, KID_SND_WFWD, KID_SND_WPVAL, KID_SND_WBACK,
-       KID_SND_FINAL, KID_BDY, KID_HALO, KID_COUNT };
+       KID_SND_FINAL, KID_BDY, KID_HALO, KID_H_PS, KID_H_PREP, KID_H_UV, KID_H_TQ, KID_SP_PROJ, KID_SP_STEP, KID_SP_CORR, KID_COUNT };
 static const char* const kKernelNames[KID_COUNT] = {"k_prep", "k_xkc", "k_uv", "k_tq", "k_ppw", "k_snd_init", "k_snd_uv",
-                                                    "k_snd_wfwd", "k_snd_wpval", "k_snd_wback", "k_snd_final", "k_bdy", "halo"};
+                                                    "k_snd_wfwd", "k_snd_wpval", "k_snd_wback", "k_snd_final", "k_bdy", "halo",
+                                                    "k_h_ps", "k_h_prep", "k_h_uv", "k_h_tq", "k_sp_proj", "k_sp_step", "k_sp_corr"};
 struct ProfRec { int kid; cudaEvent_t a, b; };
 
 struct rcm_dyn {
@@ -95,6 +112,11 @@ struct rcm_dyn {
   double* nx[6] = {nullptr};   // staged next record (decoupled)
   double* psdot_bdy = nullptr; // bdycon psdot = atm0%psdot*1e-3 (Main/mod_bdycod.F90:425-431)
   double* xpsb = nullptr;      // xpsb%b0 = atm0%ps*1e-3
+  // hydrostatic core
+  bool hydro = false;
+  double *xps_b1 = nullptr, *xps_nx = nullptr;  // xpsb%b1 and the staged next record (2-D)
+  SplitTables sp;
+  double ptntot = 0, pt2tot = 0;
   int2 *rim_d = nullptr, *rim_c = nullptr;
   int nrim_d = 0, nrim_c = 0;
   std::vector<double> stage;   // host staging, one 3-D field
@@ -168,6 +190,7 @@ extern "C" int rcm_dyn_default_cfg(rcm_cfg* c, int idynamic) {
   c->upstream_mode = c->stability_enhance = 1;
   c->nproc = 1; c->myid = 0; c->cpus_j = c->cpus_i = 0; c->device = -1;
   c->ptop = 5.0;
+  c->nsplit = 2; c->lstand = 1;  // Main/mod_params.F90:283-284
   if (idynamic == 2) { c->gnu1 = c->gnu2 = 0.1; c->diffu_hgtf = 0; }
   else { c->gnu1 = c->gnu2 = 0.0625; c->diffu_hgtf = 1; }
   c->ckh = c->adyndif = 1.0;
@@ -231,7 +254,10 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   h->cfg = *cfg;
   const rcm_cfg& c = h->cfg;
   if (c.struct_size != (int)sizeof(rcm_cfg)) return bail(RCM_ERR_ARG, "rcm_cfg size mismatch");
-  if (c.idynamic != 2) return bail(RCM_ERR_ARG, "only idynamic=2 (non-hydrostatic core) is implemented");
+  if (c.idynamic != 1 && c.idynamic != 2) return bail(RCM_ERR_ARG, "idynamic must be 1 (hydrostatic) or 2 (non-hydrostatic); MOLOCH is not implemented");
+  h->hydro = (c.idynamic == 1);
+  if (h->hydro && c.nproc != 1) return bail(RCM_ERR_ARG, "idynamic=1 runs on one rank only (BASELINE configs[0] is a single-rank case)");
+  if (h->hydro && (c.nsplit < 1 || c.nsplit > RCM_MAXSPLIT || c.nsplit > c.kz)) return bail(RCM_ERR_ARG, "nsplit must be 1..4");
   if (c.idiffu != 1) return bail(RCM_ERR_ARG, "only idiffu=1 is implemented");
   if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 5)) return bail(RCM_ERR_ARG, "iboudy must be 0, 1 or 5");
   if (c.nqx != 2) return bail(RCM_ERR_ARG, "nqx must be 2 (qv,qc)");
@@ -305,7 +331,21 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
                      &f.ddy, &f.dmdx, &f.dmdy, &f.ex, &f.crx, &f.cry, &f.dpsdxm, &f.dpsdym, &f.ht, &f.ps0, &f.hgfact,
                      &f.astore, &f.wpval, &h->psdot_bdy, &h->xpsb})
     A2(*p);
-  f.psb = f.psa; f.rpsb = f.rpsa; f.psdotb = f.psdota;  // idynamic = 2: p* is the constant reference p*
+  if (!h->hydro) {
+    f.psb = f.psa; f.rpsb = f.rpsa; f.psdotb = f.psdota; f.rpsdb = f.rpsda;  // idynamic = 2: p* is the constant reference p*
+  } else {
+    for (double** p : {&f.psb, &f.rpsb, &f.psdotb, &f.rpsdb, &f.psc, &f.pten, &f.ptn2d, &f.pt22d, &f.xpsb0, &f.xpsbt, &f.map,
+                       &h->xps_b1, &h->xps_nx})
+      A2(*p);
+    for (double** p : {&f.phi, &f.nau, &f.nav, &f.nbu, &f.nbv}) A3(*p);
+    f.omega = f.th;  // tap only; th is not used by the hydrostatic core
+    const int ns = c.nsplit;
+    f.deld = dev_alloc3(h, 3 * ns); f.delh = dev_alloc3(h, 3 * ns);
+    f.ddsum = dev_alloc3(h, ns); f.dhsum = dev_alloc3(h, ns); f.dstor = dev_alloc3(h, ns); f.hstor = dev_alloc3(h, ns);
+    ok = ok && f.deld && f.delh && f.ddsum && f.dhsum && f.dstor && f.hstor;
+    const size_t nt = (size_t)ns * (kzp1 + 1) + 1;
+    for (double** p : {&f.sp_zr, &f.sp_tau, &f.sp_pdlog, &f.sp_eps1, &f.sp_am, &f.sp_zm}) { *p = dev_alloc_raw<double>(h, nt); ok = ok && *p; }
+  }
   {
     int* z = dev_alloc_raw<int>(h, (size_t)g.sk); ok = ok && z; f.zone_c = z ? z + h->off2 : nullptr;
     z = dev_alloc_raw<int>(h, (size_t)g.sk); ok = ok && z; f.zone_d = z ? z + h->off2 : nullptr;
@@ -450,8 +490,25 @@ static int upload3(rcm_dyn* h, double* dev_shifted, const double* a, const int32
 #endif
 }
 
+// 2-D p* records (idynamic = 1): a 2-D shifted pointer p is the 3-D shifted pointer p - sk with k = 1
+static double* ps_slot(rcm_dyn* h, int slot) {
+  if (slot == RCM_BDY_B0) return h->f.xpsb0;
+  if (slot == RCM_BDY_B1) return h->xps_b1;
+  if (slot == RCM_BDY_NEXT) return h->xps_nx;
+  return nullptr;
+}
+
 extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
+  if (field == RCM_F_PS) {
+    if (!h->hydro) return fail(h, RCM_ERR_ARG, "ps boundary data exist for idynamic = 1 only");
+    double* dst2 = ps_slot(h, slot);
+    if (!dst2) return fail(h, RCM_ERR_ARG, "bad slot");
+    cudaSetDevice(h->device);
+    if (slot == RCM_BDY_NEXT) h->have_next = true;
+    int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
+    return upload3(h, dst2 - h->g.sk, a, l3, u3, 1);
+  }
   const int q = bdy_index(field);
   if (q < 0) return fail(h, RCM_ERR_ARG, "no boundary data for this field");
   cudaSetDevice(h->device);
@@ -468,21 +525,25 @@ extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a,
 // stream while rcm_dyn_step keeps computing; bdyin waits for it on the device.
 extern "C" int rcm_dyn_stage_bdy_async(rcm_dyn* h, int field, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
-  const int q = bdy_index(field);
+  const bool is_ps = (field == RCM_F_PS && h->hydro);
+  const int q = is_ps ? 0 : bdy_index(field);
   if (q < 0) return fail(h, RCM_ERR_ARG, "no boundary data for this field");
   cudaSetDevice(h->device);
-  const int nk = (field == RCM_F_W) ? h->g.kzp1 : h->g.kz;
+  const int nk = is_ps ? 1 : ((field == RCM_F_W) ? h->g.kzp1 : h->g.kz);
+  double* const dst_async = is_ps ? h->xps_nx - h->g.sk : h->nx[q];
+  int32_t lb3[3] = {lb[0], lb[1], is_ps ? 1 : lb[2]}, ub3[3] = {ub[0], ub[1], is_ps ? 1 : ub[2]};
+  lb = lb3; ub = ub3;
 #ifndef RCM_EMU
   if (!h->st_copy) {
     CUDA_OK(cudaStreamCreateWithFlags(&h->st_copy, cudaStreamNonBlocking));
     CUDA_OK(cudaEventCreateWithFlags(&h->ev_stage, cudaEventDisableTiming));
   }
-  int rc = copy3d(h, h->nx[q], a, lb, ub, nk, true, h->st_copy, false);
+  int rc = copy3d(h, dst_async, a, lb, ub, nk, true, h->st_copy, false);
   if (rc) return rc;
   CUDA_OK(cudaEventRecord(h->ev_stage, h->st_copy));
   h->stage_pending = true;
 #else
-  int rc = upload3(h, h->nx[q], a, lb, ub, nk);
+  int rc = upload3(h, dst_async, a, lb, ub, nk);
   if (rc) return rc;
 #endif
   h->have_next = true;
@@ -548,6 +609,7 @@ static double tau_fn(const rcm_cfg& c, double z, double zmax) {  // Main/mod_bdy
 }
 
 static int bdyval(rcm_dyn* h, const double* oat, const double* oaqv, const double* oaqc);
+static int init_hydro(rcm_dyn* h);
 
 // exchange call sites (the reference's are listed in SURVEY.md §2.4)
 static int exch_sound_pp(rcm_dyn* h) {  // atmc%t, atmc%pp  (Main/mod_sound.F90:265-266)
@@ -634,7 +696,7 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
   std::vector<double> ps0(n2, 1.0), psdot0(n2, 1.0);
   std::vector<double> pr0((size_t)g.sk * kzp1, 1.0), t0((size_t)g.sk * kzp1, 1.0), rho0((size_t)g.sk * kzp1, 1.0),
       z0((size_t)g.sk * kzp1, 0.0), rhof0((size_t)g.sk * kzp1, 1.0), zf0((size_t)g.sk * kzp1, 0.0);
-  {
+  if (!h->hydro) {  // the hydrostatic core has no reference atmosphere
     const double p0 = c.base_state_pressure, tlp = c.logp_lrate, st0 = c.base_state_ts0, ptoppa = ptop * 1000.0;
     auto nhbase = [&](int kx, const std::vector<double>& sig, std::vector<double>& pr, std::vector<double>* tt,
                       std::vector<double>& rho, std::vector<double>& zz) {
@@ -664,8 +726,9 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
   // Note: the reference multiplies ht by regrav and back by egrav around
   // nhbase (:2621,2634); (ht*egrav)*regrav is what `ter` holds above, and
   // mddom%ht afterwards is ((ht*egrav)*regrav)*egrav.
-  for (int i = idlo; i <= idhi; ++i)
-    for (int j = jdlo; j <= jdhi; ++j) H2(ht, j, i) = (H2(ht, j, i) * regrav) * egrav;
+  if (!h->hydro)
+    for (int i = idlo; i <= idhi; ++i)
+      for (int j = jdlo; j <= jdhi; ++j) H2(ht, j, i) = (H2(ht, j, i) * regrav) * egrav;
 
   // psc2psd (Main/mpplib/mod_mppparam.F90:13811-13862) on global indices
   auto psc2psd = [&](const std::vector<double>& pc, std::vector<double>& pd) {
@@ -741,8 +804,13 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
   StepScalars& s = h->s;
   s.xkhmax = dxsq / (64.0 * h->dtsec);
   s.dydc = c.adyndif * vonkar * vonkar * dx * 0.25;
-  const double xkhz = c.ckh * dx;
-  s.xkhmax = 2.0 * s.xkhmax;
+  double xkhz;
+  if (h->hydro) {
+    xkhz = c.ckh * 1.5e-3 * dxsq / h->dtsec;  // RegCM3 formulation (mod_diffusion.F90:106-107)
+  } else {
+    xkhz = c.ckh * dx;  // Xu et al. 2001 (:108-113)
+    s.xkhmax = 2.0 * s.xkhmax;
+  }
   std::vector<double> hgfact(n2, xkhz);
   if (c.diffu_hgtf == 1)
     for (int i = std::max(2, iclo + 1); i <= std::min(g.iy - 2, ichi - 1); ++i)
@@ -848,6 +916,7 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
   s.iboudy = c.iboudy; s.ifrayd = c.ifrayd; s.ifupr = c.ifupr;
   s.kt_ray = std::min(kz, c.rayndamp); s.ktf_ray = std::min(kzp1, c.rayndamp);
   s.nspgx = c.nspgx; s.nspgd = c.nspgd;
+  s.hydro = h->hydro ? 1 : 0; s.nsplit = h->hydro ? c.nsplit : 0; s.integrating = 0;
 
   // ---- upload statics ----
   if ((rc = up2(h, f.ht, ht)) || (rc = up2(h, f.msfx, msfx)) || (rc = up2(h, f.msfd, msfd)) || (rc = up2(h, f.xmsf, xmsf)) ||
@@ -888,6 +957,7 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
     if (!rcx.empty()) CUDA_OK(cudaMemcpy(h->rim_c, rcx.data(), rcx.size() * sizeof(int2), cudaMemcpyHostToDevice));
   }
 
+  if (h->hydro) return init_hydro(h);
   // ---- boundary records: couple with p*, tendencies (init_bdy :393-435,522-559,625-640) ----
   h->xbctime = 0.0;
   for (int q = 0; q < 6; ++q) {
@@ -924,8 +994,134 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
 }
 
 // ---------------------------------------------------------------------------
+// hydrostatic core: tail of rcm_dyn_init
+static int upload_split_tables(rcm_dyn* h) {
+  const SplitTables& T = h->sp;
+  const int ns = T.nsplit, kz = T.kz, kzp1 = kz + 1;
+  const size_t nt = (size_t)ns * (kzp1 + 1) + 1;
+  std::vector<double> zr(nt, 0.0), tau(nt, 0.0), am(nt, 0.0), zm(nt, 0.0), pdlog(nt, 0.0), eps1(nt, 0.0);
+  for (int l = 1; l <= ns; ++l)
+    for (int k = 1; k <= kz; ++k) {
+      const size_t q = (size_t)l + (size_t)ns * (k - 1);
+      zr[q] = T.zmatxr[(size_t)(l - 1) + (size_t)kz * (k - 1)];   // zmatxr(l,k)
+      tau[q] = T.tau[(size_t)(l - 1) + (size_t)kz * (k - 1)];     // tau(l,k)
+      am[q] = T.am[(size_t)(k - 1) + (size_t)kz * (l - 1)];       // am(k,l)
+      zm[q] = T.zmatx[(size_t)(k - 1) + (size_t)kz * (l - 1)];    // zmatx(k,l)
+    }
+  for (size_t q = 0; q < T.pdlog.size() && q < nt; ++q) { pdlog[q] = T.pdlog[q]; eps1[q] = T.eps1[q]; }
+  int rc;
+  Fields& f = h->f;
+  if ((rc = up1(h, f.sp_zr, zr)) || (rc = up1(h, f.sp_tau, tau)) || (rc = up1(h, f.sp_am, am)) || (rc = up1(h, f.sp_zm, zm)) ||
+      (rc = up1(h, f.sp_pdlog, pdlog)) || (rc = up1(h, f.sp_eps1, eps1)))
+    return rc;
+  StepScalars& s = h->s;
+  s.sp_pd = T.pd;
+  for (int l = 1; l <= ns; ++l) {
+    s.sp_aam[l - 1] = T.aam[l]; s.sp_m2[l - 1] = (int)T.aam[l] * 2; s.sp_dtau[l - 1] = T.dtau[l];
+    s.sp_hbar[l - 1] = T.hbar[l]; s.sp_an[l - 1] = T.an[l];
+  }
+  return RCM_OK;
+}
+
+static int download2(rcm_dyn* h, const double* dev2, std::vector<double>& v) {
+  v.assign((size_t)h->g.sk, 0.0);
+  CUDA_OK(cudaMemcpy(v.data(), dev2 - h->off2, (size_t)h->g.sk * sizeof(double), cudaMemcpyDeviceToHost));
+  return RCM_OK;
+}
+
+static int init_hydro(rcm_dyn* h) {
+  const Geom& g = h->g;
+  const rcm_cfg& c = h->cfg;
+  Fields& f = h->f;
+  const int kz = g.kz;
+  int rc;
+  // ---- boundary records (init_bdy, Main/mod_bdycod.F90:393-396,408-423,522-552,625-637):
+  //      p* from the ICBC surface pressure, dot-point p*, coupling, tendencies ----
+  h->xbctime = 0.0;
+  double* ub[4] = {f.xub0, f.xvb0, f.xtb0, f.xqb0};
+  for (int rec = 0; rec < 2; ++rec) {
+    double* ps = rec ? h->xps_b1 : f.xpsb0;
+    launch_ps_convert(g, ps, c.ptop, h->st);
+    launch_psc2psd(g, ps, h->psdot_bdy, nullptr, h->st);
+    for (int q = 0; q < 4; ++q) {
+      const bool dot = (q < 2);
+      double* a = rec ? h->b1[q] : ub[q];
+      launch_couple(g, a, dot ? h->psdot_bdy : ps, kz, dot ? g.jde1 : g.jce1, dot ? g.jde2 : g.jce2, dot ? g.ide1 : g.ice1,
+                    dot ? g.ide2 : g.ice2, h->st);
+    }
+    h->launches += 6;
+  }
+  for (int q = 0; q < 4; ++q) {
+    const bool dot = (q < 2);
+    launch_timeint(g, h->b1[q], *bdy_b0(h, q), *bdy_bt(h, q), h->rdtbdy, kz, dot ? g.jde1 : g.jce1, dot ? g.jde2 : g.jce2,
+                   dot ? g.ide1 : g.ice1, dot ? g.ide2 : g.ice2, h->st);
+  }
+  launch_timeint(g, h->xps_b1 - g.sk, f.xpsb0 - g.sk, f.xpsbt - g.sk, h->rdtbdy, 1, g.jce1, g.jce2, g.ice1, g.ice2, h->st);
+  h->launches += 5;
+  // ---- initial state (init, Main/mod_init.F90:96-147,173-178) ----
+  {
+    const size_t nb = (size_t)g.sk * g.kzp1 * sizeof(double), nb2 = (size_t)g.sk * sizeof(double);
+    double* a[4] = {f.au, f.av, f.at, f.aqv};
+    double* b[4] = {f.bu, f.bv, f.bt, f.bqv};
+    for (int q = 0; q < 4; ++q) {
+      CUDA_OK(cudaMemcpyAsync(a[q] - h->off3, *bdy_b0(h, q) - h->off3, nb, cudaMemcpyDeviceToDevice, h->st));
+      CUDA_OK(cudaMemcpyAsync(b[q] - h->off3, *bdy_b0(h, q) - h->off3, nb, cudaMemcpyDeviceToDevice, h->st));
+    }
+    CUDA_OK(cudaMemsetAsync(f.aqc - h->off3, 0, nb, h->st));
+    CUDA_OK(cudaMemsetAsync(f.bqc - h->off3, 0, nb, h->st));
+    CUDA_OK(cudaMemcpyAsync(f.psa - h->off2, f.xpsb0 - h->off2, nb2, cudaMemcpyDeviceToDevice, h->st));
+    CUDA_OK(cudaMemcpyAsync(f.psb - h->off2, f.xpsb0 - h->off2, nb2, cudaMemcpyDeviceToDevice, h->st));
+  }
+  launch_h_ps(g, f, h->st);
+  h->launches += 1;
+  h->lcount = 0; h->model_time = 0;
+  h->day_lastact = 0; h->day_now = 0; h->bdy_lastact = 0; h->bdy_now = 0;
+  // ---- spinit (Main/mod_split.F90:75-239): vertical modes on the host, storage on the device ----
+  {
+    double xps = 0.0;
+    std::vector<double> tbarh((size_t)kz + 1, 0.0);
+    if (!c.lstand) {  // linearisation about the horizontal mean of the data (:103-129)
+      std::vector<double> psa, msfx, t;
+      CUDA_OK(cudaStreamSynchronize(h->st));
+      if ((rc = download2(h, f.psa, psa)) || (rc = download2(h, f.msfx, msfx))) return rc;
+      t.assign((size_t)g.sk * g.kzp1, 0.0);
+      CUDA_OK(cudaMemcpy(t.data(), f.at - h->off3, t.size() * sizeof(double), cudaMemcpyDeviceToHost));
+      const double rnpts = 1.0 / (double)((g.iy - 1) * (g.jx - 1));
+      double lxps = 0.0, lxms = 0.0;
+      for (int i = g.ice1; i <= g.ice2; ++i)
+        for (int j = g.jce1; j <= g.jce2; ++j) {
+          const double map = 1.0 / (H2(msfx, j, i) * H2(msfx, j, i));
+          lxms = lxms + rnpts * map;
+          lxps = lxps + rnpts * H2(psa, j, i) * map;
+        }
+      xps = lxps / lxms;
+      for (int k = 1; k <= kz; ++k) {
+        double ltbark = 0.0;
+        for (int i = g.ice1; i <= g.ice2; ++i)
+          for (int j = g.jce1; j <= g.jce2; ++j) {
+            const double map = 1.0 / (H2(msfx, j, i) * H2(msfx, j, i));
+            ltbark = ltbark + rnpts * map * H3(t, j, i, k) / H2(psa, j, i);
+          }
+        tbarh[k] = ltbark / lxms;
+      }
+    }
+    if (rcm_split_tables(kz, c.nsplit, c.lstand, c.ptop, h->dtsec, h->h_sigma, xps, tbarh, h->sp))
+      return fail(h, RCM_ERR_ARG, "vmodes: the vertical mode problem reported errors (Main/mod_vmodes.F90:435-436)");
+    if ((rc = upload_split_tables(h))) return rc;
+    launch_sp_init(g, f, h->s, h->st);
+    h->launches += 1;
+  }
+  h->inited = true;
+  // first bdyval (Main/mod_regcm_interface.F90:146)
+  if ((rc = bdyval(h, f.at, f.aqv, f.aqc))) return rc;
+  CUDA_OK(cudaStreamSynchronize(h->st));
+  return RCM_OK;
+}
+
+// ---------------------------------------------------------------------------
 static int bdyval(rcm_dyn* h, const double* oat, const double* oaqv, const double* oaqc) {
   const double xt = h->xbctime + h->dt;
+  if (h->hydro) TIMED(KID_BDY, 1, launch_bdyval_ps(h->g, h->f, h->rim_c, h->nrim_c, xt, h->cfg.iboudy, h->st));
   TIMED(KID_BDY, 2, launch_bdyval(h->g, h->f, oat, oaqv, oaqc, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, xt,
                                   h->lcount > 0 ? 1 : 0, h->cfg.iboudy, h->st));
   h->xbctime = h->xbctime + h->dtsec;
@@ -944,6 +1140,25 @@ static int bdyin(rcm_dyn* h) {
 #ifndef RCM_EMU
   if (h->stage_pending) { CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_stage, 0)); h->stage_pending = false; }
 #endif
+  if (h->hydro) {  // Main/mod_bdycod.F90:686,774-787,808-825
+    Fields& f = h->f;
+    std::swap(f.xpsb0, h->xps_b1);
+    std::swap(h->xps_b1, h->xps_nx);
+    launch_ps_convert(g, h->xps_b1, h->cfg.ptop, h->st);
+    launch_psc2psd(g, h->xps_b1, h->psdot_bdy, nullptr, h->st);
+    for (int q = 0; q < 4; ++q) {
+      std::swap(*bdy_b0(h, q), h->b1[q]);
+      std::swap(h->b1[q], h->nx[q]);
+      const bool dot = (q < 2);
+      const int j1 = dot ? g.jde1 : g.jce1, j2 = dot ? g.jde2 : g.jce2, i1 = dot ? g.ide1 : g.ice1, i2 = dot ? g.ide2 : g.ice2;
+      launch_couple(g, h->b1[q], dot ? h->psdot_bdy : h->xps_b1, kz, j1, j2, i1, i2, h->st);
+      launch_timeint(g, h->b1[q], *bdy_b0(h, q), *bdy_bt(h, q), h->rdtbdy, kz, j1, j2, i1, i2, h->st);
+    }
+    launch_timeint(g, h->xps_b1 - g.sk, f.xpsb0 - g.sk, f.xpsbt - g.sk, h->rdtbdy, 1, g.jce1, g.jce2, g.ice1, g.ice2, h->st);
+    h->launches += 11;
+    h->have_next = false;
+    return RCM_OK;
+  }
   for (int q = 0; q < 6; ++q) {
     // b0 <- b1 (pointer swap), b1 <- staged record
     std::swap(*bdy_b0(h, q), h->b1[q]);
@@ -1022,8 +1237,50 @@ static void timer_advance(rcm_dyn* h) {  // Main/mpplib/mod_timer.F90:152-177,30
   check(h->bdy_lastact, h->bdy_now, (int64_t)h->dtbdys);
 }
 
+// one call of `tend` for the hydrostatic core (Main/mod_tendency.F90:212-616), physics off
+static int tend_hydro(rcm_dyn* h) {
+  const Geom& g = h->g;
+  Fields& f = h->f;
+  StepScalars& s = h->s;
+  s.dt = h->dt;
+  s.xt = h->xbctime + h->dt;
+  s.integrating = h->lcount > 0 ? 1 : 0;
+  h->last_istep = 0;
+  CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
+  TIMED(KID_H_PS, 2, (launch_h_ps(g, f, h->st), launch_h_rimcopy(g, f, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, h->st)));
+  TIMED(KID_H_PREP, 1, launch_h_prep(g, f, s, h->st));
+  TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
+  if (h->prof_on || !h->overlap_slow) {
+    TIMED(KID_H_UV, 1, launch_h_uv(g, f, s, h->st));
+    TIMED(KID_H_TQ, 1, launch_h_tq(g, f, s, h->st));
+  } else {
+    // k_h_uv and k_h_tq read the same inputs and write disjoint outputs
+    CUDA_OK(cudaEventRecord(h->ev_fork, h->st));
+    CUDA_OK(cudaStreamWaitEvent(h->st_b, h->ev_fork, 0));
+    launch_h_tq(g, f, s, h->st);
+    launch_h_uv(g, f, s, h->st_b);
+    h->launches += 2;
+    CUDA_OK(cudaEventRecord(h->ev_jb, h->st_b));
+    CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jb, 0));
+  }
+  // time filter of p*, then p* on dot points as at the head of splitf (:259-260)
+  TIMED(KID_H_PS, 2, (launch_h_psfilt(g, f, s, h->st), launch_psc2psd(g, f.psa, f.psdota, nullptr, h->st)));
+  TIMED(KID_SP_PROJ, 1, launch_sp_proj(g, f, s, h->st));
+  int m2max = 0;
+  for (int l = 0; l < s.nsplit; ++l) m2max = std::max(m2max, s.sp_m2[l]);
+  for (int n = 1; n <= m2max; ++n) TIMED(KID_SP_STEP, 1, launch_sp_step(g, f, s, n, h->st));
+  TIMED(KID_SP_CORR, 2, launch_sp_corr(g, f, s, h->st));
+  std::swap(f.au, f.nau); std::swap(f.av, f.nav); std::swap(f.bu, f.nbu); std::swap(f.bv, f.nbv);
+  std::swap(f.at, f.nat); std::swap(f.aqv, f.naqv); std::swap(f.aqc, f.naqc);
+  std::swap(f.bt, f.nbt); std::swap(f.bqv, f.nbqv); std::swap(f.bqc, f.nbqc);
+  timer_advance(h);
+  if (h->lcount == 2) h->dt = h->dt2;
+  return RCM_OK;
+}
+
 // one call of `tend` (Main/mod_tendency.F90:212-616), physics off
 static int tend(rcm_dyn* h) {
+  if (h->hydro) return tend_hydro(h);
   const Geom& g = h->g;
   Fields& f = h->f;
   StepScalars& s = h->s;
@@ -1146,6 +1403,8 @@ static double* state_ptr(rcm_dyn* h, int field, int level) {
   return nullptr;
 }
 
+static double* ps_state(rcm_dyn* h, int level) { return (level == RCM_LEVEL_A) ? h->f.psa : h->f.psb; }
+
 static int download3(rcm_dyn* h, const double* dev_shifted, double* a, const int32_t* lb, const int32_t* ub, int nk) {
 #ifndef RCM_EMU
   return copy3d(h, const_cast<double*>(dev_shifted), a, lb, ub, nk, false);
@@ -1167,6 +1426,11 @@ static int download3(rcm_dyn* h, const double* dev_shifted, double* a, const int
 extern "C" int rcm_dyn_get_state(rcm_dyn* h, int field, int level, double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
   cudaSetDevice(h->device);
+  if (field == RCM_F_PS) {
+    if (!h->hydro) return fail(h, RCM_ERR_ARG, "p* is a state field for idynamic = 1 only");
+    int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
+    return download3(h, ps_state(h, level) - h->g.sk, a, l3, u3, 1);
+  }
   double* p = state_ptr(h, field, level);
   if (!p) return fail(h, RCM_ERR_ARG, "bad field");
   return download3(h, p, a, lb, ub, h->g.kzp1);
@@ -1175,6 +1439,11 @@ extern "C" int rcm_dyn_get_state(rcm_dyn* h, int field, int level, double* a, co
 extern "C" int rcm_dyn_set_state(rcm_dyn* h, int field, int level, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
   cudaSetDevice(h->device);
+  if (field == RCM_F_PS) {
+    if (!h->hydro) return fail(h, RCM_ERR_ARG, "p* is a state field for idynamic = 1 only");
+    int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
+    return upload3(h, ps_state(h, level) - h->g.sk, a, l3, u3, 1);
+  }
   double* p = state_ptr(h, field, level);
   if (!p) return fail(h, RCM_ERR_ARG, "bad field");
   return upload3(h, p, a, lb, ub, h->g.kzp1);
@@ -1196,8 +1465,16 @@ extern "C" int rcm_dyn_get_work(rcm_dyn* h, int id, double* a, const int32_t lb[
     case RCM_W_VTEN: p = f.vten; break;
     case RCM_W_PPTEN: p = f.ppten; break;
     case RCM_W_WTEN: p = f.wten; break;
+    case RCM_W_OMEGA: p = h->hydro ? f.omega : nullptr; break;
+    case RCM_W_PHI: p = h->hydro ? f.phi : nullptr; break;
+    case RCM_W_PTEN: {
+      if (!h->hydro) return fail(h, RCM_ERR_ARG, "pten exists for idynamic = 1 only");
+      int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
+      return download3(h, f.pten - h->g.sk, a, l3, u3, 1);
+    }
     default: return fail(h, RCM_ERR_ARG, "bad work id");
   }
+  if (!p) return fail(h, RCM_ERR_ARG, "work array not available for this core");
   return download3(h, p, a, lb, ub, h->g.kzp1);
 }
 
@@ -1207,6 +1484,18 @@ extern "C" int rcm_dyn_diag(rcm_dyn* h, rcm_diag* d) {
   d->lcount = h->lcount; d->xbctime = h->xbctime; d->dt = h->dt;
   d->max_cfl = h->max_cfl; d->istep = h->last_istep; d->nan_flag = h->nan_flag;
   d->neg_q_points = h->neg_q;
+  if (h->hydro && h->inited) {
+    // Bleck (1977) noise parameters: per-point terms summed on the host in the
+    // reference's loop order (i outer, j inner; Main/mod_tendency.F90:1452-1458)
+    cudaSetDevice(h->device);
+    std::vector<double> a, b;
+    int rc;
+    if ((rc = download2(h, h->f.ptn2d, a)) || (rc = download2(h, h->f.pt22d, b))) return rc;
+    double ptn = 0.0, pt2 = 0.0;
+    for (int i = h->g.ici1; i <= h->g.ici2; ++i)
+      for (int j = h->g.jci1; j <= h->g.jci2; ++j) { ptn = ptn + H2(a, j, i); pt2 = pt2 + H2(b, j, i); }
+    d->ptntot = ptn; d->pt2tot = pt2;
+  }
   return RCM_OK;
 }
 
@@ -1216,6 +1505,27 @@ extern "C" int rcm_dyn_last_error(rcm_dyn* h, char* buf, int len) {
   std::strncpy(buf, m.c_str(), (size_t)len - 1);
   buf[len - 1] = 0;
   return RCM_OK;
+}
+
+extern "C" int rcm_dyn_get_table(rcm_dyn* h, int id, double* out, int n) {
+  if (!h) return RCM_ERR_ARG;
+  if (!h->hydro || !h->inited) return fail(h, RCM_ERR_ARG, "vertical-mode tables exist for idynamic = 1 after rcm_dyn_init");
+  const SplitTables& T = h->sp;
+  std::vector<double> v;
+  switch (id) {
+    case RCM_T_HBAR: v.assign(T.hbar.begin() + 1, T.hbar.end()); break;
+    case RCM_T_ZMATX: v = T.zmatx; break;
+    case RCM_T_ZMATXR: v = T.zmatxr; break;
+    case RCM_T_TAU: v = T.tau; break;
+    case RCM_T_VARPA1: v = T.varpa1; break;
+    case RCM_T_AM: v = T.am; break;
+    case RCM_T_AN: v.assign(T.an.begin() + 1, T.an.end()); break;
+    case RCM_T_TAU0: v = T.tau0; break;
+    default: return fail(h, RCM_ERR_ARG, "bad table id");
+  }
+  const int m = std::min<int>(n, (int)v.size());
+  if (out && m > 0) std::memcpy(out, v.data(), (size_t)m * sizeof(double));
+  return (int)v.size();
 }
 
 extern "C" int rcm_dyn_get_tile(rcm_dyn* h, int32_t out[4]) {

@@ -15,6 +15,7 @@
 
 #define RCM_HALO 2
 #define RCM_EHALO 6 /* estore halo for the upper radiative BC, mod_sound.F90:551-561 */
+#define RCM_MAXSPLIT 4 /* upper bound on nsplit (split-explicit vertical modes, idynamic = 1) */
 
 struct Geom {
   int jx, iy, kz, kzp1;
@@ -51,6 +52,14 @@ struct StepScalars {
   int ktf_ray;  // min(kzp1, rayndamp)
   int nspgx, nspgd;
   int it, istep;
+  // ---- hydrostatic core (idynamic = 1) ----
+  int hydro;     // 1: idynamic = 1
+  int integrating;  // rcmtimer%integrating(): lcount > 0
+  // split-explicit scheme (Main/mod_split.F90): per mode l = 0..nsplit-1
+  int nsplit;
+  int sp_m2[RCM_MAXSPLIT];        // 2*int(aam)
+  double sp_aam[RCM_MAXSPLIT], sp_dtau[RCM_MAXSPLIT], sp_hbar[RCM_MAXSPLIT], sp_an[RCM_MAXSPLIT];
+  double sp_pd;                   // vmodes pd = xps - ptop
 };
 
 // Device pointers (origin-shifted).  Names follow the reference's structures:
@@ -84,6 +93,17 @@ struct Fields {
   // acoustic work fields
   double *cu, *cv, *cpp, *cppd, *cw, *ct, *se, *sf;
   double *estore, *astore, *wpval, *tmask;  // estore: wide-halo 2-D; tmask 13x13
+  // ---- hydrostatic core (idynamic = 1); null / aliases for idynamic = 2 ----
+  double *rpsdb;                 // 1/psdotb (alias of rpsda for idynamic = 2)
+  double *psc, *pten;            // forecast p*, p* tendency before the boundary relaxation (2-D)
+  double *ptn2d, *pt22d;         // per-point terms of the Bleck noise parameters (2-D)
+  double *xpsb0, *xpsbt;         // boundary record of p* (2-D): b0, bt
+  double *phi, *omega;           // geopotential (3-D); omega tap (3-D)
+  double *nau, *nav, *nbu, *nbv; // double-buffered next levels of p*u, p*v
+  // split-explicit work: planes are (slot-1)*nsplit + l for deld/delh (slot 1..3), l for the others
+  double *deld, *delh, *ddsum, *dhsum, *dstor, *hstor, *map;
+  // vertical-mode tables: [l + nsplit*(k-1)] for zr (zmatxr), tau, pdlog, eps1 (k = 1..kz+1), am, zm (zmatx)
+  double *sp_zr, *sp_tau, *sp_pdlog, *sp_eps1, *sp_am, *sp_zm;
   // diagnostics
   unsigned long long *cflbits;  // max CFL as ordered bits
   unsigned long long *negq;     // negative-q repairs

@@ -108,13 +108,13 @@ k_xkc(const Geom g, const Fields f, const StepScalars s) {
   const int k = 1 + blockIdx.z;
   if (j > g.jde2 + 2 * g.gr || i > g.ide2 + 2 * g.gt) return;
   // ubd3d = atm2%u * (1/psdotb), wb3d = atm2%w * (1/psb)  (Main/mod_slice.F90:169-263)
-  const double u00 = L3(f.bu, j, i, k) * L2(f.rpsda, j, i);
-  const double v00 = L3(f.bv, j, i, k) * L2(f.rpsda, j, i);
+  const double u00 = L3(f.bu, j, i, k) * L2(f.rpsdb, j, i);
+  const double v00 = L3(f.bv, j, i, k) * L2(f.rpsdb, j, i);
   const double md = L2(f.msfd, j, i);
   P3(f.dub, j, i, k) = u00 / md;
   P3(f.dvb, j, i, k) = v00 / md;
   if (j < g.jce1 - g.gl || j > g.jce2 + g.gr || i < g.ice1 - g.gb || i > g.ice2 + g.gt) return;
-  const double r01 = L2(f.rpsda, j, i + 1), r10 = L2(f.rpsda, j + 1, i), r11 = L2(f.rpsda, j + 1, i + 1);
+  const double r01 = L2(f.rpsdb, j, i + 1), r10 = L2(f.rpsdb, j + 1, i), r11 = L2(f.rpsdb, j + 1, i + 1);
   const double rpsb = L2(f.rpsb, j, i);
   const double u01 = L3(f.bu, j, i + 1, k) * r01, u10 = L3(f.bu, j + 1, i, k) * r10, u11 = L3(f.bu, j + 1, i + 1, k) * r11;
   const double v01 = L3(f.bv, j, i + 1, k) * r01, v10 = L3(f.bv, j + 1, i, k) * r10, v11 = L3(f.bv, j + 1, i + 1, k) * r11;
@@ -122,7 +122,8 @@ k_xkc(const Geom g, const Fields f, const StepScalars s) {
   const double dvdx = v10 + v11 - v00 - v01;
   const double dudy = u01 + u11 - u00 - u10;
   const double dvdy = v01 + v11 - v00 - v10;
-  const double dwdz = L3(f.bw, j, i, k) * rpsb - L3(f.bw, j, i, k + 1) * rpsb;
+  // hydrostatic core: no dw/dz term (Main/mod_diffusion.F90:193-211)
+  const double dwdz = s.hydro ? 0.0 : L3(f.bw, j, i, k) * rpsb - L3(f.bw, j, i, k + 1) * rpsb;
   const double duv = sqrt(fmax((dudx - dvdy) * (dudx - dvdy) + (dvdx + dudy) * (dvdx + dudy) - dwdz * dwdz, 0.0));
   P3(f.xkc, j, i, k) = fmin((L2(f.hgfact, j, i) + s.dydc * duv), s.xkhmax);
 }

@@ -49,8 +49,10 @@ inline int lu_factor(int n, std::vector<double>& a, std::vector<int>& piv) {
 
 // solve LU x = b (b overwritten)
 inline void lu_solve(int n, const std::vector<double>& lu, const std::vector<int>& piv, double* b) {
-  for (int k = 0; k < n; ++k) {
+  // rows were interchanged across the whole matrix (LAPACK style): permute b first
+  for (int k = 0; k < n; ++k)
     if (piv[k] != k) std::swap(b[k], b[piv[k]]);
+  for (int k = 0; k < n; ++k) {
     const double t = b[k];
     if (t != 0.0)
       for (int i = k + 1; i < n; ++i) b[i] -= lu[i + (size_t)n * k] * t;

@@ -3,10 +3,19 @@ import numpy as np
 from regcm_b200 import capi, synth
 
 
+HYDRO_FIELDS = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PS)
+HYDRO_WORK = (capi.W_QDOT, capi.W_XKC, capi.W_OMEGA, capi.W_PHI, capi.W_PTEN)
+
+
+def prognostics(core):
+    """Prognostic fields of the core in use (idynamic = 1 carries p*, no p', w)."""
+    return HYDRO_FIELDS if core.cfg.idynamic == 1 else tuple(range(7))
+
+
 def rel_errors(core, ref, levels=(capi.LEVEL_A, capi.LEVEL_B)):
     """Per prognostic field: L-inf and L2 error normalised by the reference."""
     out = {}
-    for f in range(7):
+    for f in prognostics(core):
         for lv in levels:
             a, b = core.get_state(f, lv), ref.get_state(f, lv)
             sc = max(float(np.abs(b).max()), 1e-300)
@@ -17,7 +26,7 @@ def rel_errors(core, ref, levels=(capi.LEVEL_A, capi.LEVEL_B)):
 
 def work_errors(core, ref):
     out = {}
-    for w in range(10):
+    for w in (HYDRO_WORK if core.cfg.idynamic == 1 else range(10)):
         a, b = core.get_work(w), ref.get_work(w)
         sc = max(float(np.abs(b).max()), 1e-300)
         out[capi.WORK_NAMES[w]] = float(np.abs(a - b).max()) / sc

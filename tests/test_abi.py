@@ -42,8 +42,19 @@ def test_create_rejects_bad_config(built):
     bad.struct_size = 4
     h = C.c_void_p()
     assert lib.create(C.byref(bad), C.byref(h)) == -1 and not h
-    hyd = capi.default_cfg(1, jx=64, iy=34, kz=18, ds=60.0, dt=120.0)
+    mol = capi.default_cfg(3, jx=64, iy=34, kz=18, ds=60.0, dt=120.0)   # MOLOCH: not implemented
+    assert lib.create(C.byref(mol), C.byref(h)) == -1 and not h
+    hyd = capi.default_cfg(1, jx=64, iy=34, kz=18, ds=60.0, dt=150.0, nproc=2)  # the hydrostatic core is single-rank
     assert lib.create(C.byref(hyd), C.byref(h)) == -1 and not h
+    hyd = capi.default_cfg(1, jx=64, iy=34, kz=18, ds=60.0, dt=150.0, nsplit=9)
+    assert lib.create(C.byref(hyd), C.byref(h)) == -1 and not h
+    # a valid hydrostatic configuration passes the argument checks: without a device the
+    # library refuses with RCM_ERR_CUDA (no CPU fallback), with one it creates a handle
+    hyd = capi.default_cfg(1, jx=64, iy=34, kz=18, ds=60.0, dt=150.0)
+    rc = lib.create(C.byref(hyd), C.byref(h))
+    assert rc in (0, -2)
+    if rc == 0:
+        lib.destroy(h)
 
 
 def test_product_has_no_cpu_fallback():
