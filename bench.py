@@ -26,11 +26,14 @@ METRIC = "dyn-core grid-point-steps/s"
 UNIT = "grid-point-steps/s"
 # compulsory HBM bytes per grid-point-step of the NH core, nqx = 2
 ALG_BYTES_STEP = lambda istep: 352 + 192 * istep  # noqa: E731
+ALG_BYTES_STEP_HYDRO = 312  # hydrostatic core, 39 passes (+ the 2-D sub-steps, not counted)
 # per-kernel algorithmic bytes per grid point and launch = 8 B x (distinct 3-D fields
 # read + written by that kernel), listed in DESIGN.md §Kernels
 ALG_BYTES_KERNEL = {
     "k_prep": 104, "k_xkc": 48, "k_uv": 80, "k_tq": 144, "k_ppw": 136, "k_snd_init": 88,
     "k_snd_uv": 80, "k_snd_wfwd": 128, "k_snd_wback": 168, "k_snd_final": 160,
+    # hydrostatic core
+    "k_h_prep": 64, "k_h_uv": 120, "k_h_tq": 136, "k_sp_proj": 48, "k_sp_corr": 96,
 }
 
 
@@ -184,7 +187,8 @@ def run_reference(args):
 
 def workload_desc(w):
     c = synth.CASES[w]
-    return (f"{w}: {c['jx']}x{c['iy']}x{c['kz']} non-hydrostatic (idynamic=2), ds={c['ds']} km, dt={c['dt']} s, "
+    core = "hydrostatic (idynamic=1, split-explicit nsplit=2)" if c.get("idynamic", 2) == 1 else "non-hydrostatic (idynamic=2)"
+    return (f"{w}: {c['jx']}x{c['iy']}x{c['kz']} {core}, ds={c['ds']} km, dt={c['dt']} s, "
             f"physics off, synthetic analytic ICBC")
 
 
@@ -208,7 +212,10 @@ def run_gpu(args):
     # the rank's tile (+ghost rows): ask the library for the decomposition by creating the handle first
     probe_cfg = synth.make_case("tiny").cfg  # only for struct defaults
     del probe_cfg
-    cfg = capi.default_cfg(2, jx=base["jx"], iy=base["iy"], kz=base["kz"], ds=base["ds"], dt=base["dt"],
+    hydro = base.get("idynamic", 2) == 1
+    if hydro and world > 1:
+        raise SystemExit("bench.py: the hydrostatic workload (BASELINE configs[0]) is a single-rank case")
+    cfg = capi.default_cfg(base.get("idynamic", 2), jx=base["jx"], iy=base["iy"], kz=base["kz"], ds=base["ds"], dt=base["dt"],
                            nspgx=base["nspg"], nspgd=base["nspg"], **cfgkw)
     core = capi.DynCore(lib, cfg)
     if world > 1:
@@ -281,7 +288,7 @@ def run_gpu(args):
                 "per_kernel": {k: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps,
                                    "GBs": (ALG_BYTES_KERNEL[k] * local_cells / (v[0] / v[1] * 1e-3) / 1e9 if k in ALG_BYTES_KERNEL and v[1] else None)}
                                for k, v in prof.items() if v[1] > 0}}
-    step_bytes = ALG_BYTES_STEP(istep)
+    step_bytes = ALG_BYTES_STEP_HYDRO if hydro else ALG_BYTES_STEP(istep)
     step_roof = {"alg_bytes_per_grid_point_step": step_bytes, "achieved_GBs": step_bytes * value / world / 1e9,
                  "frac_of_peak_per_gpu": step_bytes * value / world / 1e9 / peak}
 
@@ -301,11 +308,12 @@ def run_gpu(args):
             pinned_in[fid] = v
         j1, j2, i1, i2 = core.tile()
         out_lbub = {}
-        for fid in range(7):
+        prognostics = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PS) if hydro else tuple(range(7))
+        for fid in prognostics:
             dot = fid in (capi.F_U, capi.F_V)
             lbs = (j1, i1, 1)
             ubs = (j2 if dot else min(j2, base["jx"] - 1), i2 if dot else min(i2, base["iy"] - 1),
-                   base["kz"] + (1 if fid == capi.F_W else 0))
+                   1 if fid == capi.F_PS else base["kz"] + (1 if fid == capi.F_W else 0))
             shp = tuple(ubs[d] - lbs[d] + 1 for d in range(3))
             t = torch.empty(shp[::-1], dtype=torch.float64).pin_memory()
             pinned_out[fid] = t.numpy().T
@@ -326,8 +334,8 @@ def run_gpu(args):
         e2e_s = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": cells * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d / args.steps,
                "d2h_bytes_per_step": d2h / args.steps, "ms_per_step": e2e_s / args.steps * 1e3,
-               "what": "per rank: stage one ICBC record (6 fields) from pinned host memory (rcm_dyn_stage_bdy_async, overlapped with the "
-                       "steps), K x {rcm_dyn_step(1); rcm_dyn_diag}, rcm_dyn_stage_wait, download the 7 level-a prognostic fields to "
+               "what": f"per rank: stage one ICBC record ({len(pinned_in)} fields) from pinned host memory (rcm_dyn_stage_bdy_async, overlapped with the "
+                       f"steps), K x {{rcm_dyn_step(1); rcm_dyn_diag}}, rcm_dyn_stage_wait, download the {len(pinned_out)} level-a prognostic fields to "
                        "pinned host memory (synchronous); bytes amortised over the K steps"}
 
     # ---- CPU baseline (rank 0, N = 1 only): the oracle on a bounded sample ----

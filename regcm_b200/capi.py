@@ -222,7 +222,8 @@ class DynCore:
         """Queue the H2D copy of one field of the NEXT record; `a` must be Fortran-ordered
         float64 and stay alive until stage_wait() or the record change."""
         assert a.dtype == np.float64 and a.flags.f_contiguous
-        ub = tuple(lb[d] + a.shape[d] - 1 for d in range(3))
+        shp = a.shape if a.ndim == 3 else a.shape + (1,)
+        ub = tuple(lb[d] + shp[d] - 1 for d in range(3))
         self._check(self.lib.stage_bdy_async(self.h, field, a.ctypes.data_as(_DP), *_bounds(lb, ub)))
 
     def stage_wait(self):

@@ -17,6 +17,9 @@ from regcm_b200 import capi, synth  # noqa: E402
 from oracle import pyoracle  # noqa: E402
 
 CASES = [("tiny", 12, {}), ("tiny", 6, {"iboudy": 1, "ifupr": 0}), ("small", 4, {})]
+# hydrostatic core (idynamic = 1): files hy_*.npz carry u, v, t, qv, qc, ps and the noise parameters
+HYDRO_CASES = [("tiny", 12, {}), ("tiny", 6, {"iboudy": 1}), ("small", 4, {})]
+HYDRO_FIELDS = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PS)
 
 
 def main():
@@ -36,6 +39,22 @@ def main():
         tag = name + "".join(f"_{k}{v}" for k, v in sorted(kw.items()))
         np.savez_compressed(os.path.join(ROOT, "tests", "golden", f"nh_{tag}_{nsteps}.npz"), **out)
         print("wrote", tag, nsteps)
+    for name, nsteps, kw in HYDRO_CASES:
+        case = synth.make_case(name, idynamic=1, **kw)
+        o = pyoracle.make_oracle(case.cfg)
+        synth.load_case(o, case)
+        o.step(nsteps)
+        out = {"nsteps": nsteps}
+        for f in HYDRO_FIELDS:
+            for lv in (0, 1):
+                out[capi.FIELD_NAMES[f] + "_" + "ab"[lv]] = o.get_state(f, lv)
+        d = o.diag()
+        out["ptntot"] = d.ptntot
+        out["pt2tot"] = d.pt2tot
+        out["hbar"] = o.get_table(capi.T_HBAR)
+        tag = name + "".join(f"_{k}{v}" for k, v in sorted(kw.items()))
+        np.savez_compressed(os.path.join(ROOT, "tests", "golden", f"hy_{tag}_{nsteps}.npz"), **out)
+        print("wrote hydro", tag, nsteps)
 
 
 if __name__ == "__main__":
