@@ -38,15 +38,17 @@ ALG_BYTES_KERNEL = {
 
 
 def measured_traffic(kernel, workload, world):
-    """dram bytes per launch of `kernel` from the committed ncu capture (profiles/r1_traffic.json);
-    only meaningful for the configuration it was captured on."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as fh:
-            t = json.load(fh)
-        if t["workload"] == workload and t["n_gpus"] == world:
-            return t["bytes_per_launch"].get(kernel)
-    except Exception:
-        pass
+    """dram bytes per launch of `kernel` from the committed ncu captures (profiles/r1_traffic.json for the
+    non-hydrostatic C4, profiles/r1_hydro_traffic.json for the hydrostatic C4hq); only meaningful for the
+    configuration it was captured on."""
+    for fn in ("r1_traffic.json", "r1_hydro_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", fn)) as fh:
+                t = json.load(fh)
+            if t["workload"] == workload and t["n_gpus"] == world:
+                return t["bytes_per_launch"].get(kernel)
+        except Exception:
+            pass
     return None
 
 
