@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the RegCM non-hydrostatic dyn-core step on B200.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C4|C3|C2] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C4|C3|C2 | C1|C3h|C4h|C4hq (hydrostatic)] [--impl reference]
 
 One "step" = one full model step (`tend` + `bdyval`: slow tendencies, istep acoustic
 sub-steps, filters, boundary update) over the whole synthetic domain.  Prints ONE JSON
