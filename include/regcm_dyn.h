@@ -57,8 +57,18 @@ enum rcm_field {
                  * boundary field (xpsb, rcm_dyn_set_bdy) the value passed is the
                  * ICBC surface pressure in hPa; the library converts it like
                  * Main/mod_bdycod.F90:394 (`ps*0.1 - ptop`). */
-  RCM_F_COUNT = 8
+  RCM_F_PAI = 8, /* cross (jx-1,iy-1,kz): Exner function Pi of the MOLOCH core
+                  * (mo_atm%pai, Main/mod_atm_interface.F90:575-616); state only */
+  RCM_F_COUNT = 9
 };
+/* idynamic = 3 (MOLOCH, Arakawa C grid, Main/mod_atm_interface.F90:575-616):
+ * the state is single-level and uncoupled: RCM_F_U is mo_atm%u on
+ * (jx, iy-1, kz), RCM_F_V is mo_atm%v on (jx-1, iy, kz), RCM_F_W is mo_atm%w on
+ * (jx-1, iy-1, kz+1), RCM_F_T/QV/QC/PAI on (jx-1, iy-1, kz), RCM_F_PS is the
+ * diagnosed surface pressure sfs%psa [Pa]; the `level` argument is ignored.
+ * Boundary fields are U, V, T, QV as read from the ICBC file and RCM_F_PS in
+ * hPa (converted like Main/mod_bdycod.F90:529); Pi on the boundary is derived
+ * by `paicompute` (Main/mod_bdycod.F90:5125-5155). */
 
 /* static domain fields: members of `mddom` read by read_domain_info
  * (Main/mod_params.F90:1733) plus the sigma vector. */
@@ -71,7 +81,12 @@ enum rcm_static {
   RCM_S_XLON = 5,   /* longitude of cross points [deg]                    */
   RCM_S_DLAT = 6,   /* latitude  of dot points [deg]                      */
   RCM_S_SIGMA = 7,  /* full sigma levels, kz+1 values (k = 1 is the top)  */
-  RCM_S_COUNT = 8
+  /* idynamic = 3 (MOLOCH) */
+  RCM_S_MSFU = 8,   /* map factor at u points (jx,iy-1)                   */
+  RCM_S_MSFV = 9,   /* map factor at v points (jx-1,iy)                   */
+  RCM_S_ULAT = 10,  /* latitude of u points [deg]                         */
+  RCM_S_VLAT = 11,  /* latitude of v points [deg]                         */
+  RCM_S_COUNT = 12
 };
 
 /* time levels of the leapfrog state (atm1 = "a" = tau, atm2 = "b" = tau-1) */
@@ -100,7 +115,15 @@ enum rcm_work {
   RCM_W_OMEGA = 10, /* omega      Main/mod_tendency.F90:1199-1215  [cb/s]   */
   RCM_W_PHI = 11,   /* phi        Main/mod_tendency.F90:2069-2097           */
   RCM_W_PTEN = 12,  /* pten (2-D) Main/mod_tendency.F90:1131-1148, before nudging */
-  RCM_W_COUNT = 13
+  /* idynamic = 3 */
+  RCM_W_MO_P = 13,     /* mo_atm%p      Main/mod_moloch.F90:368-375 [Pa]      */
+  RCM_W_MO_TVIRT = 14, /* mo_atm%tvirt  Main/mod_moloch.F90:321-327            */
+  RCM_W_MO_FMZ = 15,   /* mo_atm%fmz    Main/mod_params.F90:2816-2824          */
+  RCM_W_MO_FMZF = 16,  /* mo_atm%fmzf   (kz+1) :2827-2837                      */
+  RCM_W_MO_ZETA = 17,  /* mo_atm%zeta   :2816-2824                             */
+  RCM_W_MO_S = 18,     /* s (kz+1), generalized vertical velocity left by the
+                        * last sound() of the step, Main/mod_moloch.F90:1022-1038 */
+  RCM_W_COUNT = 19
 };
 
 /* vertical-mode tables of the split-explicit scheme (idynamic = 1), computed
@@ -149,7 +172,12 @@ typedef struct rcm_cfg {
   /* &hydroparam (idynamic = 1; Main/mod_params.F90:113,283-284) */
   int32_t nsplit;         /* number of split-explicit vertical modes (2)   */
   int32_t lstand;         /* 1: linearise vmodes about the standard atmosphere */
-  int32_t reserved_i[6];
+  /* idynamic = 3, &dynparam / &molochparam (Main/mod_params.F90:296-300,
+   * Share/mod_dynparam.F90:189-190) */
+  int32_t mo_nadv;        /* advection sub-steps per step (3)              */
+  int32_t mo_nsound;      /* sound sub-steps per advection step (6)        */
+  int32_t mo_nzfilt;      /* levels of the top sponge in the w solve (3)   */
+  int32_t reserved_i[3];
   /* &geoparam */
   double ds;    /* grid spacing [km]                                       */
   double ptop;  /* model top pressure [cb]                                 */
@@ -163,7 +191,9 @@ typedef struct rcm_cfg {
   double high_nudge, medium_nudge, low_nudge, bdy_nm, bdy_dm;
   /* &referenceatm + DOMAIN-file base state surface temperature */
   double base_state_pressure, logp_lrate, base_state_ts0;
-  double reserved_d[8];
+  double mo_anu2;  /* divergence-damping coefficient of filt3d (0.6)      */
+  double mo_a0, mo_b0; /* decay / stretching of the zita coordinate (0, 0.5) */
+  double reserved_d[5];
 } rcm_cfg;
 
 /* health metrics the reference prints (Main/mod_sound.F90:634-646) */
@@ -179,6 +209,9 @@ typedef struct rcm_diag {
    * the interior (Main/mod_tendency.F90:1449-1459; the reference divides by
    * the number of points when it prints them, :715-716) */
   double ptntot, pt2tot;
+  /* idynamic = 3: extremes of ps over the interior [Pa], the reference's
+   * per-report print (Main/mod_moloch.F90:437-460) */
+  double ps_max, ps_min;
 } rcm_diag;
 
 typedef struct rcm_dyn rcm_dyn; /* opaque */

@@ -23,10 +23,13 @@ constexpr double rgasmol = navgdr * boltzk;   // :130
 constexpr double c287 = rgasmol / amd;        // :132
 constexpr double rgas = c287 * 1000.0;        // :134
 constexpr double cpd = 3.5 * rgas;            // :144
+constexpr double cvd = 2.5 * rgas;            // :145
 constexpr double regrav = d_one / egrav;      // :182
 constexpr double rcpd = d_one / cpd;          // :183
 constexpr double rovcp = rgas * rcpd;         // :184
 constexpr double rovg = rgas / egrav;         // :187
+constexpr double rdrcv = rgas / cvd;          // :185
+constexpr double cpovr = cpd / rgas;          // :186
 constexpr double govr = egrav / rgas;         // :188
 constexpr double tiso = 216.65;               // :198
 constexpr double p00 = 1.0e5;                 // :229
@@ -39,6 +42,9 @@ constexpr double eomeg = 7.2921159e-5;        // :286
 constexpr double eomeg2 = d_two * eomeg;      // :287
 constexpr double vonkar = 0.4;                // :296
 constexpr double ep1 = amd / amw - d_one;     // :303
+constexpr double ep2 = amw / amd;             // :304
+constexpr double minqc = 1.0e-10;             // :58
+constexpr double tzero = 273.15;
 
 // Share/cpmf.inc: heat capacity of moist air at constant pressure
 inline double cpmf(double qv) { return cpd * (d_one + 0.80 * qv); }

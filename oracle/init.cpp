@@ -91,6 +91,10 @@ void Oracle::setup_bdycon() {
   if (iboudy == 1 || iboudy == 5) {
     fnudge = (cfg.bdy_nm > d_zero) ? cfg.bdy_nm : 0.1 / dt;
     gnudge = (cfg.bdy_dm > d_zero) ? cfg.bdy_dm : d_one / (dt * 50.0);
+    if (moloch) {   // :216-219
+      fnudge = fnudge * (double)nadv * (double)nsound;
+      gnudge = gnudge * (double)nadv * (double)nsound;
+    }
   }
   // iboudy == 1 .or. idynamic == 2
   for (int n = 2; n <= nspgx - 1; ++n) {
@@ -313,6 +317,20 @@ void Oracle::init_sound() {
 }
 
 int Oracle::init() {
+  if (moloch) {
+    // Main/mod_params.F90:1981-1986,2005-2010 (ht -> geopotential, hsigma of the
+    // DOMAIN-file sigma: what setup_bdycon sees, :2070), :2077, then init_bdy,
+    // init, init_moloch and the first bdyval (Main/mod_regcm_interface.F90:146)
+    for (auto& x : ht.d) x = x * egrav;
+    for (int k = 1; k <= kz; ++k) hsigma(k) = (sigma(k + 1) + sigma(k)) * d_half;
+    setup_bdycon();
+    compute_moloch_static();
+    init_bdy_moloch();
+    init_state_moloch();
+    init_moloch();
+    bdyval_moloch();
+    return RCM_OK;
+  }
   param_static();
   init_advection();
   setup_bdycon();
@@ -351,6 +369,16 @@ void Oracle::timer_advance() {
 // Main/mod_regcm_interface.F90:172-228
 int Oracle::step(int n) {
   for (int s = 0; s < n; ++s) {
+    if (moloch) {
+      moloch_step();
+      if (!(ps_max == ps_max) || !(ps_min == ps_min)) { err = "CFL violation"; return RCM_ERR_CFL; }  // mod_moloch.F90:443-451
+      if (alarm_bdy_act()) {
+        if (!have_next) { err = "boundary record needed but not staged"; return RCM_ERR_BDY; }
+        bdyin_moloch();
+      }
+      bdyval_moloch();
+      continue;
+    }
     tend();
     if (cfl_error) { err = "CFL violation"; return RCM_ERR_CFL; }
     if (alarm_bdy_act()) {
@@ -379,6 +407,7 @@ static void copy_out_4d(const A4& src, int n, double* a, const int32_t lb[3], co
 }
 
 int Oracle::get_state(int field, int level, double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (moloch) return mo_get_state(field, a, lb, ub);
   const bool A = (level == RCM_LEVEL_A);
   switch (field) {
     case RCM_F_U: copy_out_3d(A ? a1_u : a2_u, a, lb, ub); return RCM_OK;
@@ -401,6 +430,7 @@ int Oracle::get_state(int field, int level, double* a, const int32_t lb[3], cons
 }
 
 int Oracle::get_work(int id, double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (moloch) return mo_get_work(id, a, lb, ub);
   switch (id) {
     case RCM_W_CR: copy_out_3d(cr, a, lb, ub); return RCM_OK;
     case RCM_W_QDOT: copy_out_3d(qdot, a, lb, ub); return RCM_OK;

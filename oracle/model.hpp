@@ -178,6 +178,56 @@ struct Oracle {
   void spstep();
   int get_table(int id, double* out, int n);
 
+  // ---- MOLOCH core (idynamic = 3; oracle/moloch.cpp) ----
+  // mo_atm (Main/mod_atm_interface.F90:575-616), mod_moloch module arrays
+  // (Main/mod_moloch.F90:52-91,115-157), mddom C-grid statics.
+  bool moloch = false;
+  int nadv = 3, nsound = 6;
+  double mo_dz = 0, hzita = 0, rayzd = 0;
+  double ps_max = 0, ps_min = 0;
+  A1 zita, zitah, gzitak, gzitakh, ffilt, ak, bk;
+  A2 msfu, msfv, ulat, vlat, coriou, coriov, hx, hy, mx2, rmu, rmv, p2d;
+  A3 m_u, m_v, m_w, m_ux, m_vx, m_wx, m_t, m_pai, m_tetav, m_tvirt, m_p, m_rho,
+      m_zeta, m_fmz, m_fmzf, m_deltaw, m_s, m_zdiv2, m_wwkw, m_wz, m_p0, m_ud,
+      m_vd, m_zetau, m_zetav;
+  A2 m_wfw, m_zpby, m_zpbw;
+  A4 m_qx;
+  V3dBound xpaib;
+  BoundArea ba_ut, ba_vt;
+  double gzita(double z) const;
+  double gzitap(double z) const;
+  double bzita(double z) const;
+  double bzitap(double z) const;
+  double md_fmz(double z, double geopot) const;
+  int create_moloch();
+  void compute_moloch_static();
+  void init_bdy_moloch();
+  void init_state_moloch();
+  void init_moloch();
+  void paicompute(const A2& ps, const A3& t, const A3& q, A3& pai);
+  void bdyin_moloch();
+  void bdyval_moloch();
+  void moloch_step();
+  void mo_sound(double dts);
+  void mo_filt3d();
+  void mo_advection(double dta);
+  void wafone(A3& pp, double dta);
+  void wafone4(A4& pp, int n, double dta);
+  void uvstagtox();
+  void xtouvstag();
+  void wstagtox(const A3& w, A3& wx);
+  void xtowstag(const A3& wx, A3& w);
+  void xtoustag(const A3& ux, A3& u);
+  void xtovstag(const A3& vx, A3& v);
+  void mo_boundary();
+  void monudge3d(int ibdy, A3& f, const V3dBound& bnd);
+  void monudge4d3d(int ibdy, A4& f, const V3dBound& bnd, int n);
+  void monudgeuv(int ibdy, A3& fu, A3& fv, const V3dBound& bu, const V3dBound& bv);
+  void moraydamp(const A3& z, A3& var, const V3dBound& bnd, int j1, int j2, int i1, int i2, int k1, int k2);
+  int mo_set_state(int field, const double* a, const int32_t lb[3], const int32_t ub[3]);
+  int mo_get_state(int field, double* a, const int32_t lb[3], const int32_t ub[3]);
+  int mo_get_work(int id, double* a, const int32_t lb[3], const int32_t ub[3]);
+
   // ---- life cycle (oracle/setup.cpp) ----
   int create(const rcm_cfg& c);
   int set_static(int id, const double* a, const int32_t lb[3],

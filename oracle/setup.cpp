@@ -22,8 +22,9 @@ namespace orc {
 int Oracle::create(const rcm_cfg& c) {
   cfg = c;
   if (c.struct_size != (int)sizeof(rcm_cfg)) { err = "rcm_cfg size mismatch"; return RCM_ERR_ARG; }
-  if (c.idynamic != 1 && c.idynamic != 2) { err = "oracle: idynamic must be 1 or 2 (MOLOCH not restated)"; return RCM_ERR_ARG; }
+  if (c.idynamic < 1 || c.idynamic > 3) { err = "oracle: idynamic must be 1, 2 or 3"; return RCM_ERR_ARG; }
   hydro = (c.idynamic == 1);
+  moloch = (c.idynamic == 3);
   if (hydro && (c.nsplit < 1 || c.nsplit > c.kz)) { err = "oracle: nsplit out of range"; return RCM_ERR_ARG; }
   nsplit = hydro ? c.nsplit : 0;
   if (c.idiffu != 1) { err = "oracle: only idiffu=1"; return RCM_ERR_ARG; }
@@ -44,6 +45,7 @@ int Oracle::create(const rcm_cfg& c) {
   day_lastact = 0; day_now = 0; bdy_lastact = 0; bdy_now = 0;
   xbctime = 0; have_next = false;
   setup_model_indexes();
+  if (moloch) return create_moloch();
   allocate_all();
   if (hydro) allocate_hydro();
   setup_boundaries(false, false, ba_cr);   // mod_params.F90:1788-1793
@@ -252,11 +254,15 @@ int Oracle::set_static(int id, const double* a, const int32_t lb[3], const int32
   switch (id) {
     case RCM_S_HT: return copy_in_2d(ht, a, lb, ub);
     case RCM_S_MSFX: return copy_in_2d(msfx, a, lb, ub);
-    case RCM_S_MSFD: return copy_in_2d(msfd, a, lb, ub);
-    case RCM_S_CORIOL: return copy_in_2d(coriol, a, lb, ub);
+    case RCM_S_MSFD: return moloch ? RCM_OK : copy_in_2d(msfd, a, lb, ub);
+    case RCM_S_CORIOL: return moloch ? RCM_OK : copy_in_2d(coriol, a, lb, ub);
     case RCM_S_XLAT: return copy_in_2d(xlat, a, lb, ub);
     case RCM_S_XLON: return copy_in_2d(xlon, a, lb, ub);
-    case RCM_S_DLAT: return copy_in_2d(dlat, a, lb, ub);
+    case RCM_S_DLAT: return moloch ? RCM_OK : copy_in_2d(dlat, a, lb, ub);
+    case RCM_S_MSFU: return copy_in_2d(msfu, a, lb, ub);
+    case RCM_S_MSFV: return copy_in_2d(msfv, a, lb, ub);
+    case RCM_S_ULAT: return copy_in_2d(ulat, a, lb, ub);
+    case RCM_S_VLAT: return copy_in_2d(vlat, a, lb, ub);
     case RCM_S_SIGMA:
       for (int k = lb[2]; k <= ub[2]; ++k) sigma(k) = a[k - lb[2]];
       return RCM_OK;
@@ -266,7 +272,7 @@ int Oracle::set_static(int id, const double* a, const int32_t lb[3], const int32
 
 int Oracle::set_bdy(int field, int slot, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (field == RCM_F_PS) {
-    if (!hydro) { err = "ps boundary data exist for idynamic = 1 only"; return RCM_ERR_ARG; }
+    if (!hydro && !moloch) { err = "ps boundary data exist for idynamic = 1 and 3 only"; return RCM_ERR_ARG; }
     if (slot == RCM_BDY_B0) return copy_in_2d(xpsb.b0, a, lb, ub);
     if (slot == RCM_BDY_B1) return copy_in_2d(xpsb.b1, a, lb, ub);
     if (slot == RCM_BDY_NEXT) { have_next = true; return copy_in_2d(nx_ps, a, lb, ub); }
@@ -278,10 +284,11 @@ int Oracle::set_bdy(int field, int slot, const double* a, const int32_t lb[3], c
     case RCM_F_V: b = &xvb; nx = &nx_v; break;
     case RCM_F_T: b = &xtb; nx = &nx_t; break;
     case RCM_F_QV: b = &xqb; nx = &nx_q; break;
-    case RCM_F_PP: b = &xppb; nx = &nx_pp; break;
-    case RCM_F_W: b = &xwwb; nx = &nx_ww; break;
-    default: err = "no boundary data for this field"; return RCM_ERR_ARG;
+    case RCM_F_PP: if (!moloch) { b = &xppb; nx = &nx_pp; } break;
+    case RCM_F_W: if (!moloch) { b = &xwwb; nx = &nx_ww; } break;
+    default: break;
   }
+  if (!b) { err = "no boundary data for this field"; return RCM_ERR_ARG; }
   if (slot == RCM_BDY_B0) return copy_in_3d(b->b0, a, lb, ub);
   if (slot == RCM_BDY_B1) return copy_in_3d(b->b1, a, lb, ub);
   if (slot == RCM_BDY_NEXT) { have_next = true; return copy_in_3d(*nx, a, lb, ub); }
@@ -290,6 +297,7 @@ int Oracle::set_bdy(int field, int slot, const double* a, const int32_t lb[3], c
 
 // state import (tests only): the coupled atm1/atm2 fields
 int Oracle::set_state(int field, int level, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (moloch) return mo_set_state(field, a, lb, ub);
   const bool A = (level == RCM_LEVEL_A);
   auto in4 = [&](A4& dst, int n) {
     const int n1 = ub[0] - lb[0] + 1, n2 = ub[1] - lb[1] + 1;

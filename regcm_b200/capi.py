@@ -17,13 +17,15 @@ from typing import Sequence
 import numpy as np
 
 # enum rcm_field / rcm_static / rcm_work (include/regcm_dyn.h)
-F_U, F_V, F_T, F_QV, F_QC, F_PP, F_W, F_PS = range(8)
-FIELD_NAMES = ("u", "v", "t", "qv", "qc", "pp", "w", "ps")
-S_HT, S_MSFX, S_MSFD, S_CORIOL, S_XLAT, S_XLON, S_DLAT, S_SIGMA = range(8)
+F_U, F_V, F_T, F_QV, F_QC, F_PP, F_W, F_PS, F_PAI = range(9)
+FIELD_NAMES = ("u", "v", "t", "qv", "qc", "pp", "w", "ps", "pai")
+S_HT, S_MSFX, S_MSFD, S_CORIOL, S_XLAT, S_XLON, S_DLAT, S_SIGMA, S_MSFU, S_MSFV, S_ULAT, S_VLAT = range(12)
 LEVEL_A, LEVEL_B = 0, 1
 BDY_B0, BDY_B1, BDY_NEXT = 0, 1, 2
-W_CR, W_QDOT, W_XKC, W_TH, W_RHO1, W_PR1, W_UTEN, W_VTEN, W_PPTEN, W_WTEN, W_OMEGA, W_PHI, W_PTEN = range(13)
-WORK_NAMES = ("cr", "qdot", "xkc", "th", "rho1", "pr1", "uten", "vten", "ppten", "wten", "omega", "phi", "pten")
+(W_CR, W_QDOT, W_XKC, W_TH, W_RHO1, W_PR1, W_UTEN, W_VTEN, W_PPTEN, W_WTEN, W_OMEGA, W_PHI, W_PTEN,
+ W_MO_P, W_MO_TVIRT, W_MO_FMZ, W_MO_FMZF, W_MO_ZETA, W_MO_S) = range(19)
+WORK_NAMES = ("cr", "qdot", "xkc", "th", "rho1", "pr1", "uten", "vten", "ppten", "wten", "omega", "phi", "pten",
+              "mo_p", "mo_tvirt", "mo_fmz", "mo_fmzf", "mo_zeta", "mo_s")
 # enum rcm_table: vertical-mode tables of the split-explicit scheme (idynamic = 1)
 T_HBAR, T_ZMATX, T_ZMATXR, T_TAU, T_VARPA1, T_AM, T_AN, T_TAU0 = range(8)
 
@@ -45,7 +47,8 @@ class RcmCfg(C.Structure):
         ("cpus_j", C.c_int32), ("cpus_i", C.c_int32),
         ("device", C.c_int32),
         ("nsplit", C.c_int32), ("lstand", C.c_int32),
-        ("reserved_i", C.c_int32 * 6),
+        ("mo_nadv", C.c_int32), ("mo_nsound", C.c_int32), ("mo_nzfilt", C.c_int32),
+        ("reserved_i", C.c_int32 * 3),
         ("ds", C.c_double), ("ptop", C.c_double),
         ("dt", C.c_double),
         ("gnu1", C.c_double), ("gnu2", C.c_double), ("ckh", C.c_double), ("adyndif", C.c_double),
@@ -54,7 +57,8 @@ class RcmCfg(C.Structure):
         ("high_nudge", C.c_double), ("medium_nudge", C.c_double), ("low_nudge", C.c_double),
         ("bdy_nm", C.c_double), ("bdy_dm", C.c_double),
         ("base_state_pressure", C.c_double), ("logp_lrate", C.c_double), ("base_state_ts0", C.c_double),
-        ("reserved_d", C.c_double * 8),
+        ("mo_anu2", C.c_double), ("mo_a0", C.c_double), ("mo_b0", C.c_double),
+        ("reserved_d", C.c_double * 5),
     ]
 
 
@@ -64,6 +68,7 @@ class RcmDiag(C.Structure):
         ("max_cfl", C.c_double), ("istep", C.c_int32), ("nan_flag", C.c_int32),
         ("neg_q_points", C.c_int64),
         ("ptntot", C.c_double), ("pt2tot", C.c_double),
+        ("ps_max", C.c_double), ("ps_min", C.c_double),
     ]
 
 
@@ -82,6 +87,8 @@ def default_cfg(idynamic: int = 2, **kw) -> RcmCfg:
     c.nproc, c.myid, c.cpus_j, c.cpus_i, c.device = 1, 0, 0, 0, -1
     c.ptop = 5.0
     c.nsplit, c.lstand = 2, 1   # Main/mod_params.F90:283-284
+    c.mo_nadv, c.mo_nsound, c.mo_nzfilt = 3, 6, 3      # Main/mod_params.F90:296-300
+    c.mo_anu2, c.mo_a0, c.mo_b0 = 0.6, 0.0, 0.5        # Share/mod_dynparam.F90:189-190
     if idynamic == 2:
         c.gnu1 = c.gnu2 = 0.1
         c.diffu_hgtf = 0
@@ -193,6 +200,8 @@ class DynCore:
 
     def field_shape(self, field: int):
         jx, iy, kz = self.jx, self.iy, self.kz
+        if self.cfg.idynamic == 3 and field in (F_U, F_V):   # Arakawa C grid
+            return (jx, iy - 1, kz) if field == F_U else (jx - 1, iy, kz)
         if field in (F_U, F_V):
             return (jx, iy, kz)
         if field == F_W:
@@ -260,7 +269,7 @@ class DynCore:
             lb, ub = (2, 2, 1), (jx - 2, iy - 2, kz)
         elif wid == W_WTEN:
             lb, ub = (2, 2, 1), (jx - 2, iy - 2, kz + 1)
-        elif wid == W_QDOT:
+        elif wid in (W_QDOT, W_MO_FMZF, W_MO_S):
             lb, ub = (1, 1, 1), (jx - 1, iy - 1, kz + 1)
         elif wid == W_OMEGA:
             lb, ub = (2, 2, 1), (jx - 2, iy - 2, kz)

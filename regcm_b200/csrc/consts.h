@@ -21,6 +21,11 @@ constexpr double rgasmol = navgdr * boltzk;
 constexpr double c287 = rgasmol / amd;
 constexpr double rgas = c287 * 1000.0;
 constexpr double cpd = 3.5 * rgas;
+constexpr double cvd = 2.5 * rgas;
+constexpr double rdrcv = rgas / cvd;
+constexpr double cpovr = cpd / rgas;
+constexpr double minqc = 1.0e-10;
+constexpr double tzero = 273.15;
 constexpr double regrav = 1.0 / egrav;
 constexpr double rcpd = 1.0 / cpd;
 constexpr double rovcp = rgas * rcpd;
@@ -37,6 +42,7 @@ constexpr double eomeg = 7.2921159e-5;
 constexpr double eomeg2 = 2.0 * eomeg;
 constexpr double vonkar = 0.4;
 constexpr double ep1 = amd / amw - 1.0;
+constexpr double ep2 = amw / amd;
 // Share/cpmf.inc
 RCM_HD inline double cpmf(double qv) { return cpd * (1.0 + 0.80 * qv); }
 }  // namespace rcm

@@ -191,6 +191,8 @@ extern "C" int rcm_dyn_default_cfg(rcm_cfg* c, int idynamic) {
   c->nproc = 1; c->myid = 0; c->cpus_j = c->cpus_i = 0; c->device = -1;
   c->ptop = 5.0;
   c->nsplit = 2; c->lstand = 1;  // Main/mod_params.F90:283-284
+  c->mo_nadv = 3; c->mo_nsound = 6; c->mo_nzfilt = 3; c->mo_anu2 = 0.6;  // :296-300
+  c->mo_a0 = 0.0; c->mo_b0 = 0.5;                                        // Share/mod_dynparam.F90:189-190
   if (idynamic == 2) { c->gnu1 = c->gnu2 = 0.1; c->diffu_hgtf = 0; }
   else { c->gnu1 = c->gnu2 = 0.0625; c->diffu_hgtf = 1; }
   c->ckh = c->adyndif = 1.0;

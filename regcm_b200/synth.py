@@ -58,6 +58,11 @@ CASES = {
     "C3h": dict(jx=250, iy=200, kz=23, ds=50.0, dt=120.0, nspg=12, idynamic=1),
     "C4h": dict(jx=1000, iy=1000, kz=41, ds=3.0, dt=6.0, nspg=12, idynamic=1),
     "C4hq": dict(jx=500, iy=500, kz=41, ds=3.0, dt=6.0, nspg=12, idynamic=1),
+    # MOLOCH core (idynamic = 3): C5 is BASELINE configs[4] (12 km, ~500x500x30, mo_nadv=3, mo_nsound=6)
+    "tinym": dict(jx=20, iy=16, kz=10, ds=12.0, dt=90.0, nspg=4, idynamic=3),
+    "smallm": dict(jx=40, iy=30, kz=14, ds=12.0, dt=90.0, nspg=6, idynamic=3),
+    "C5": dict(jx=500, iy=500, kz=30, ds=12.0, dt=90.0, nspg=12, idynamic=3),
+    "C5q": dict(jx=250, iy=250, kz=30, ds=12.0, dt=90.0, nspg=12, idynamic=3),
 }
 
 
@@ -113,6 +118,10 @@ def make_case(name: str = "C2", *, flat: bool = False, unit_map: bool = False, n
                            nspgx=p["nspg"], nspgd=p["nspg"], ibdyfrq=ibdyfrq)
     for k, v in cfg_over.items():
         setattr(cfg, k, v)
+    if idynamic == 3:
+        if window is not None:
+            raise ValueError("the MOLOCH cases are generated on the whole domain (single rank)")
+        return _make_moloch_case(name, cfg, flat=flat, unit_map=unit_map, noise=noise, ibdyfrq=ibdyfrq, records=records)
     j1, j2, i1, i2 = window or (1, jx, 1, iy)
     j1, i1, j2, i2 = max(1, j1), max(1, i1), min(jx, j2), min(iy, i2)
     jc2, ic2 = min(j2, jx - 1), min(i2, iy - 1)
@@ -202,6 +211,98 @@ def make_case(name: str = "C2", *, flat: bool = False, unit_map: bool = False, n
                 capi.F_PP: F(pp), capi.F_W: F(ww)}
 
     shift = 20.0 * 3600.0 * ibdyfrq * 0.25  # a quarter of the jet advection distance per record
+    phases = {capi.BDY_B0: 0.0, capi.BDY_B1: shift, capi.BDY_NEXT: 2 * shift}
+    case.bdy = {slot: record(phases[slot]) for slot in records}
+    return case
+
+
+def moloch_levels(cfg):
+    """zita coordinate of the MOLOCH core (Share/mod_zita.F90:30-92, Main/mod_params.F90:1169,2802-2813):
+    (hzita, dz, zita[kz+1], zitah[kz], ak[kz], bk[kz]), k = 1 at the top."""
+    rgas = 6.02214129e23 * 1.3806504e-23 / 28.96454 * 1000.0
+    kz = cfg.kz
+    hzita = rgas * 280.0 / 9.80665
+    dz = hzita / kz
+    zita = (kz - np.arange(0, kz + 1)) * dz
+    zitah = zita[:-1] - 0.5 * dz
+    r = zitah / hzita
+    gz = 1.0 - cfg.mo_a0 * r - (3.0 - 2.0 * cfg.mo_a0) * r ** 2 + (2.0 - cfg.mo_a0) * r ** 3
+    bz = cfg.mo_b0 + (1.0 - cfg.mo_b0) * r
+    ak = -hzita * bz * np.log(1.0 - r)
+    return hzita, dz, zita, zitah, ak, gz
+
+
+def _make_moloch_case(name, cfg, *, flat, unit_map, noise, ibdyfrq, records) -> Case:
+    """Synthetic DOMAIN + ICBC for idynamic = 3 on the Arakawa C grid: u on (jx, iy-1), v on (jx-1, iy),
+    T/qv on (jx-1, iy-1), ps [hPa] 2-D.  Temperature follows the standard lapse rate in the height of the
+    zita levels (as the reference's own analytic cases do, Main/mod_bdycod.F90:5157-5199) plus the same smooth
+    wave / bubble / jet perturbations and hashed noise as the sigma-coordinate cases."""
+    jx, iy, kz = cfg.jx, cfg.iy, cfg.kz
+    dx = cfg.ds * 1000.0
+    rearth = 6.371229e6
+    clat, clon = 45.0, 13.0
+    jd, idd = np.arange(1, jx + 1), np.arange(1, iy + 1)
+    jc, ic = np.arange(1, jx), np.arange(1, iy)
+    xd, yd = (jd - 0.5 * (jx + 1)) * dx, (idd - 0.5 * (iy + 1)) * dx
+    xc, yc = (jc - 0.5 * (jx + 1)) * dx + 0.5 * dx, (ic - 0.5 * (iy + 1)) * dx + 0.5 * dx
+    Xc, Yc = np.meshgrid(xc, yc, indexing="ij")
+    Xu, Yu = np.meshgrid(xd, yc, indexing="ij")      # u points: dot in x, cross in y
+    Xv, Yv = np.meshgrid(xc, yd, indexing="ij")      # v points
+    half_span = np.degrees(0.5 * iy * dx / rearth)
+    fac = min(1.0, 20.0 / half_span)
+    lat = lambda Y: clat + np.degrees(Y / rearth) * fac
+    xlat, ulat, vlat = lat(Yc), lat(Yu), lat(Yv)
+    xlon = clon + np.degrees(Xc / (rearth * np.cos(np.radians(xlat))))
+    if unit_map:
+        msfx, msfu, msfv = np.ones_like(Xc), np.ones_like(Xu), np.ones_like(Xv)
+        ulat, vlat = np.zeros_like(Xu), np.zeros_like(Xv)      # zero Coriolis (test2 of the reference)
+    else:
+        msfx, msfu, msfv = _lambert_msf(xlat), _lambert_msf(ulat), _lambert_msf(vlat)
+    if flat:
+        ht = np.zeros_like(Xc)
+    else:
+        L = 0.15 * min(jx, iy) * dx
+        ht = 1500.0 * np.exp(-(Xc ** 2 + Yc ** 2) / L ** 2)
+    hzita, dz, zita, zitah, ak, bk = moloch_levels(cfg)
+    sigma = 1.0 - zita / hzita
+    case = Case(name=name, cfg=cfg)
+    F = np.asfortranarray
+    case.statics = {capi.S_HT: F(ht), capi.S_MSFX: F(msfx), capi.S_MSFU: F(msfu), capi.S_MSFV: F(msfv),
+                    capi.S_XLAT: F(xlat), capi.S_XLON: F(xlon), capi.S_ULAT: F(ulat), capi.S_VLAT: F(vlat),
+                    capi.S_SIGMA: sigma}
+    rgas = 6.02214129e23 * 1.3806504e-23 / 28.96454 * 1000.0
+    g = 9.80665
+    zeta = ak[None, None, :] + (bk[None, None, :] - 1.0) * ht[:, :, None]      # height above the terrain
+    zmsl = zeta + ht[:, :, None]
+    t0 = np.maximum(288.15 - 0.00649 * zmsl, 210.0)
+    ps0 = 1013.25 * (1.0 - 0.00649 * ht / 288.15) ** (g / (rgas * 0.00649))    # hPa on the terrain
+    Lx, Ly = jx * dx, iy * dx
+    hs = np.clip(zitah / hzita, 0.0, 1.0)
+    sh = np.sin(np.pi * hs)[None, None, :]
+    kk = np.arange(1, kz + 1)
+    if noise:
+        def nz(fid, ja, ia):
+            J, I, K = np.meshgrid(ja, ia, kk, indexing="ij", sparse=True)
+            return _hash_noise(fid, J + 0 * I + 0 * K, I + 0 * J + 0 * K, K + 0 * J + 0 * I)
+        nz_t, nz_u, nz_v = nz(1, jc, ic), nz(2, jd, ic), nz(3, jc, idd)
+    else:
+        nz_t = nz_u = nz_v = 0.0
+
+    def record(phase: float):
+        xs_c = Xc[:, :, None] - phase
+        wave = 2.0 * np.sin(2 * np.pi * xs_c / Lx) * np.cos(2 * np.pi * Yc[:, :, None] / Ly) * sh
+        r2 = ((xs_c - 0.2 * Lx) ** 2 + (Yc[:, :, None] + 0.15 * Ly) ** 2) / (0.08 * min(Lx, Ly)) ** 2
+        t = (t0 + wave + 1.0 * np.exp(-r2) * sh) * (1.0 + 1.0e-5 * nz_t)
+        u = 15.0 * sh ** 2 * np.ones(Xu.shape + (1,)) + \
+            2.0 * np.sin(2 * np.pi * (Xu[:, :, None] - phase) / Lx + 0.7) * np.sin(2 * np.pi * Yu[:, :, None] / Ly + 0.3)
+        v = 4.0 * np.sin(2 * np.pi * (Xv[:, :, None] - phase) / Lx) * np.ones((1, 1, kz))
+        u = u + 2.0e-2 * nz_u
+        v = v + 2.0e-2 * nz_v
+        qv = np.maximum(0.010 * np.exp(-zmsl / 2500.0) * (1.0 + 0.2 * np.sin(2 * np.pi * xs_c / Lx)), 1.0e-8)
+        ps = ps0 * (1.0 + 1.0e-3 * np.sin(2 * np.pi * (Xc - phase) / Lx) * np.cos(2 * np.pi * Yc / Ly))
+        return {capi.F_U: F(u), capi.F_V: F(v), capi.F_T: F(t), capi.F_QV: F(qv), capi.F_PS: F(ps)}
+
+    shift = 15.0 * 3600.0 * ibdyfrq * 0.25
     phases = {capi.BDY_B0: 0.0, capi.BDY_B1: shift, capi.BDY_NEXT: 2 * shift}
     case.bdy = {slot: record(phases[slot]) for slot in records}
     return case
