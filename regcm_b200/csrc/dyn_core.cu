@@ -76,10 +76,12 @@ void launch_sp_corr(const Geom&, const Fields&, const StepScalars&, cudaStream_t
 // per-kernel device timing (CUDA events on the library's stream), enabled by
 // rcm_dyn_profile(); used by bench.py for the per-kernel roofline
 enum { KID_PREP, KID_XKC, KID_UV, KID_TQ, KID_PPW, KID_SND_INIT, KID_SND_UV, KID_SND_WFWD, KID_SND_WPVAL, KID_SND_WBACK,
-       KID_SND_FINAL, KID_BDY, KID_HALO, KID_H_PS, KID_H_PREP, KID_H_UV, KID_H_TQ, KID_SP_PROJ, KID_SP_STEP, KID_SP_CORR, KID_COUNT };
+       KID_SND_FINAL, KID_BDY, KID_HALO, KID_H_PS, KID_H_PREP, KID_H_UV, KID_H_TQ, KID_SP_PROJ, KID_SP_STEP, KID_SP_CORR,
+       KID_MO_PRE, KID_MO_DIV, KID_MO_W, KID_MO_UV, KID_MO_STAG, KID_MO_WAF, KID_COUNT };
 static const char* const kKernelNames[KID_COUNT] = {"k_prep", "k_xkc", "k_uv", "k_tq", "k_ppw", "k_snd_init", "k_snd_uv",
                                                     "k_snd_wfwd", "k_snd_wpval", "k_snd_wback", "k_snd_final", "k_bdy", "halo",
-                                                    "k_h_ps", "k_h_prep", "k_h_uv", "k_h_tq", "k_sp_proj", "k_sp_step", "k_sp_corr"};
+                                                    "k_h_ps", "k_h_prep", "k_h_uv", "k_h_tq", "k_sp_proj", "k_sp_step", "k_sp_corr",
+                                                    "k_mo_pre", "k_mo_div", "k_mo_w", "k_mo_uv", "k_mo_stag", "k_mo_waf"};
 struct ProfRec { int kid; cudaEvent_t a, b; };
 
 struct rcm_dyn {
@@ -117,6 +119,15 @@ struct rcm_dyn {
   double *xps_b1 = nullptr, *xps_nx = nullptr;  // xpsb%b1 and the staged next record (2-D)
   SplitTables sp;
   double ptntot = 0, pt2tot = 0;
+  // MOLOCH core (idynamic = 3), mo_core.inc
+  bool moloch = false;
+  MoFields mf{};
+  MoScalars ms{};
+  double* mo_zdf = nullptr;   // full divergence (the raw one is still read by the neighbours' filter)
+  int2 *mo_rim_u = nullptr, *mo_rim_v = nullptr, *mo_rim_c = nullptr, *mo_zl_c = nullptr, *mo_zl_u = nullptr, *mo_zl_v = nullptr;
+  int mo_nrim_u = 0, mo_nrim_v = 0, mo_nrim_c = 0, mo_nzl_c = 0, mo_nzl_u = 0, mo_nzl_v = 0;
+  std::vector<double> h_msfu, h_msfv, h_ulat, h_vlat;
+  double ps_max = 0, ps_min = 0;
   int2 *rim_d = nullptr, *rim_c = nullptr;
   int nrim_d = 0, nrim_c = 0;
   std::vector<double> stage;   // host staging, one 3-D field
@@ -170,6 +181,14 @@ static void prof_collect(rcm_dyn* h) {
   }
   h->prof_recs.clear();
 }
+
+static int mo_create(rcm_dyn* h);
+static int mo_init(rcm_dyn* h);
+static int mo_step_one(rcm_dyn* h);
+static int mo_bdyin(rcm_dyn* h);
+static int mo_bdyval(rcm_dyn* h);
+static double* mo_state_ptr(rcm_dyn* h, int field);
+static double* mo_work_ptr(rcm_dyn* h, int id);
 
 static int fail(rcm_dyn* h, int code, const std::string& msg) {
   if (h) h->err = msg;
@@ -256,8 +275,12 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   h->cfg = *cfg;
   const rcm_cfg& c = h->cfg;
   if (c.struct_size != (int)sizeof(rcm_cfg)) return bail(RCM_ERR_ARG, "rcm_cfg size mismatch");
-  if (c.idynamic != 1 && c.idynamic != 2) return bail(RCM_ERR_ARG, "idynamic must be 1 (hydrostatic) or 2 (non-hydrostatic); MOLOCH is not implemented");
+  if (c.idynamic < 1 || c.idynamic > 3) return bail(RCM_ERR_ARG, "idynamic must be 1 (hydrostatic), 2 (non-hydrostatic) or 3 (MOLOCH)");
   h->hydro = (c.idynamic == 1);
+  h->moloch = (c.idynamic == 3);
+  if (h->moloch && c.nproc != 1) return bail(RCM_ERR_ARG, "idynamic=3 runs on one rank only in this version");
+  if (h->moloch && (c.mo_nadv < 1 || c.mo_nsound < 1 || c.kz < 4 || c.ipptls < 0 || c.ipptls > 1))
+    return bail(RCM_ERR_ARG, "idynamic=3 needs mo_nadv >= 1, mo_nsound >= 1, kz >= 4, ipptls 0 or 1");
   if (h->hydro && c.nproc != 1) return bail(RCM_ERR_ARG, "idynamic=1 runs on one rank only (BASELINE configs[0] is a single-rank case)");
   if (h->hydro && (c.nsplit < 1 || c.nsplit > RCM_MAXSPLIT || c.nsplit > c.kz)) return bail(RCM_ERR_ARG, "nsplit must be 1..4");
   if (c.idiffu != 1) return bail(RCM_ERR_ARG, "only idiffu=1 is implemented");
@@ -316,6 +339,20 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   h->dtbdys = (double)c.ibdyfrq * 3600.0;
   h->rdtbdy = 1.0 / h->dtbdys;
 
+  if (h->moloch) {
+    if (mo_create(h) != RCM_OK) {
+      for (void* p : h->allocs) cudaFree(p);
+      return bail(RCM_ERR_CUDA, "device memory allocation failed");
+    }
+    cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&h->st_b, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&h->st_c, cudaStreamNonBlocking);
+    cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
+    cudaEventCreate(&h->ev_fork); cudaEventCreate(&h->ev_jb); cudaEventCreate(&h->ev_jc);
+    h->halo.init(g, c.nproc, c.myid, cj, ci);
+    *out = h;
+    return RCM_OK;
+  }
   // ---- device memory ----
   Fields& f = h->f;
   const int kzp1 = g.kzp1;
@@ -425,11 +462,16 @@ extern "C" int rcm_dyn_set_static(rcm_dyn* h, int id, const double* a, const int
     case RCM_S_XLAT: dst = &h->h_xlat; break;
     case RCM_S_XLON: dst = &h->h_xlon; break;
     case RCM_S_DLAT: dst = &h->h_dlat; break;
+    case RCM_S_MSFU: dst = &h->h_msfu; break;
+    case RCM_S_MSFV: dst = &h->h_msfv; break;
+    case RCM_S_ULAT: dst = &h->h_ulat; break;
+    case RCM_S_VLAT: dst = &h->h_vlat; break;
     case RCM_S_SIGMA:
       for (int k = lb[2]; k <= ub[2] && k <= h->g.kzp1; ++k) if (k >= 1) h->h_sigma[k] = a[k - lb[2]];
       return RCM_OK;
     default: return fail(h, RCM_ERR_ARG, "bad static id");
   }
+  if (dst->empty()) return RCM_OK;   // a static field the selected core does not use
   int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
   win_in(h, *dst, h->off2, 1, a, l3, u3, 1);
   return RCM_OK;
@@ -503,7 +545,7 @@ static double* ps_slot(rcm_dyn* h, int slot) {
 extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
   if (field == RCM_F_PS) {
-    if (!h->hydro) return fail(h, RCM_ERR_ARG, "ps boundary data exist for idynamic = 1 only");
+    if (!h->hydro && !h->moloch) return fail(h, RCM_ERR_ARG, "ps boundary data exist for idynamic = 1 and 3 only");
     double* dst2 = ps_slot(h, slot);
     if (!dst2) return fail(h, RCM_ERR_ARG, "bad slot");
     cudaSetDevice(h->device);
@@ -512,7 +554,7 @@ extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a,
     return upload3(h, dst2 - h->g.sk, a, l3, u3, 1);
   }
   const int q = bdy_index(field);
-  if (q < 0) return fail(h, RCM_ERR_ARG, "no boundary data for this field");
+  if (q < 0 || (h->moloch && q > 3)) return fail(h, RCM_ERR_ARG, "no boundary data for this field");
   cudaSetDevice(h->device);
   double* dst = nullptr;
   if (slot == RCM_BDY_B0) dst = *bdy_b0(h, q);
@@ -527,9 +569,9 @@ extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a,
 // stream while rcm_dyn_step keeps computing; bdyin waits for it on the device.
 extern "C" int rcm_dyn_stage_bdy_async(rcm_dyn* h, int field, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
-  const bool is_ps = (field == RCM_F_PS && h->hydro);
+  const bool is_ps = (field == RCM_F_PS && (h->hydro || h->moloch));
   const int q = is_ps ? 0 : bdy_index(field);
-  if (q < 0) return fail(h, RCM_ERR_ARG, "no boundary data for this field");
+  if (q < 0 || (h->moloch && q > 3)) return fail(h, RCM_ERR_ARG, "no boundary data for this field");
   cudaSetDevice(h->device);
   const int nk = is_ps ? 1 : ((field == RCM_F_W) ? h->g.kzp1 : h->g.kz);
   double* const dst_async = is_ps ? h->xps_nx - h->g.sk : h->nx[q];
@@ -649,6 +691,7 @@ static int exch_estore(rcm_dyn* h) {
 extern "C" int rcm_dyn_init(rcm_dyn* h) {
   if (!h) return RCM_ERR_ARG;
   cudaSetDevice(h->device);
+  if (h->moloch) return mo_init(h);
   const Geom& g = h->g;
   const rcm_cfg& c = h->cfg;
   Fields& f = h->f;
@@ -1350,6 +1393,32 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
   if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_step before rcm_dyn_init");
   cudaSetDevice(h->device);
   Fields& f = h->f;
+  if (h->moloch) {   // Main/mod_regcm_interface.F90:186-209: moloch; bdyin on the boundary alarm; bdyval
+    CUDA_OK(cudaMemsetAsync(f.nanflag, 0, sizeof(int), h->st));
+    CUDA_OK(cudaEventRecord(h->ev0, h->st));
+    int rc = RCM_OK;
+    for (int n = 0; n < nsteps; ++n) {
+      if ((rc = mo_step_one(h))) break;
+      if (h->bdy_now == h->model_time) {
+        if (!h->have_next) { rc = fail(h, RCM_ERR_BDY, "boundary record needed but not staged"); break; }
+        if ((rc = mo_bdyin(h))) break;
+      }
+      if ((rc = mo_bdyval(h))) break;
+    }
+    CUDA_OK(cudaEventRecord(h->ev1, h->st));
+    CUDA_OK(cudaStreamSynchronize(h->st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+    h->last_ms = ms;
+    prof_collect(h);
+    if (rc) return rc;
+    int nanf = 0;
+    CUDA_OK(cudaMemcpy(&nanf, f.nanflag, sizeof(nanf), cudaMemcpyDeviceToHost));
+    h->nan_flag = nanf;
+    CUDA_OK(cudaGetLastError());
+    if (nanf) return fail(h, RCM_ERR_CFL, "CFL violation: surface pressure is not a number (decrease dt)");   // Main/mod_moloch.F90:443-451
+    return RCM_OK;
+  }
   CUDA_OK(cudaMemsetAsync(f.cflbits, 0, 2 * sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.nanflag, 0, sizeof(int), h->st));
@@ -1429,11 +1498,11 @@ extern "C" int rcm_dyn_get_state(rcm_dyn* h, int field, int level, double* a, co
   if (!h || !a) return RCM_ERR_ARG;
   cudaSetDevice(h->device);
   if (field == RCM_F_PS) {
-    if (!h->hydro) return fail(h, RCM_ERR_ARG, "p* is a state field for idynamic = 1 only");
+    if (!h->hydro && !h->moloch) return fail(h, RCM_ERR_ARG, "p* is a state field for idynamic = 1 and 3 only");
     int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
-    return download3(h, ps_state(h, level) - h->g.sk, a, l3, u3, 1);
+    return download3(h, (h->moloch ? h->mf.ps : ps_state(h, level)) - h->g.sk, a, l3, u3, 1);
   }
-  double* p = state_ptr(h, field, level);
+  double* p = h->moloch ? mo_state_ptr(h, field) : state_ptr(h, field, level);
   if (!p) return fail(h, RCM_ERR_ARG, "bad field");
   return download3(h, p, a, lb, ub, h->g.kzp1);
 }
@@ -1446,7 +1515,7 @@ extern "C" int rcm_dyn_set_state(rcm_dyn* h, int field, int level, const double*
     int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
     return upload3(h, ps_state(h, level) - h->g.sk, a, l3, u3, 1);
   }
-  double* p = state_ptr(h, field, level);
+  double* p = h->moloch ? mo_state_ptr(h, field) : state_ptr(h, field, level);
   if (!p) return fail(h, RCM_ERR_ARG, "bad field");
   return upload3(h, p, a, lb, ub, h->g.kzp1);
 }
@@ -1456,6 +1525,11 @@ extern "C" int rcm_dyn_get_work(rcm_dyn* h, int id, double* a, const int32_t lb[
   cudaSetDevice(h->device);
   Fields& f = h->f;
   const double* p = nullptr;
+  if (h->moloch) {
+    p = mo_work_ptr(h, id);
+    if (!p) return fail(h, RCM_ERR_ARG, "work array not available for this core");
+    return download3(h, p, a, lb, ub, h->g.kzp1);
+  }
   switch (id) {
     case RCM_W_CR: p = f.cr; break;
     case RCM_W_QDOT: p = f.qdot; break;
@@ -1497,6 +1571,16 @@ extern "C" int rcm_dyn_diag(rcm_dyn* h, rcm_diag* d) {
     for (int i = h->g.ici1; i <= h->g.ici2; ++i)
       for (int j = h->g.jci1; j <= h->g.jci2; ++j) { ptn = ptn + H2(a, j, i); pt2 = pt2 + H2(b, j, i); }
     d->ptntot = ptn; d->pt2tot = pt2;
+  }
+  if (h->moloch && h->inited) {   // max, min of ps over the interior (Main/mod_moloch.F90:437-441)
+    cudaSetDevice(h->device);
+    std::vector<double> a;
+    int rc;
+    if ((rc = download2(h, h->mf.ps, a))) return rc;
+    double mx = -1e300, mn = 1e300;
+    for (int i = h->g.ici1; i <= h->g.ici2; ++i)
+      for (int j = h->g.jci1; j <= h->g.jci2; ++j) { mx = std::max(mx, H2(a, j, i)); mn = std::min(mn, H2(a, j, i)); }
+    d->ps_max = mx; d->ps_min = mn;
   }
   return RCM_OK;
 }
@@ -1581,3 +1665,5 @@ extern "C" int rcm_dyn_destroy(rcm_dyn* h) {
   delete h;
   return RCM_OK;
 }
+
+#include "mo_core.inc"

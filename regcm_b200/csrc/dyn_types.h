@@ -109,3 +109,32 @@ struct Fields {
   unsigned long long *negq;     // negative-q repairs
   int *nanflag;
 };
+
+// ---------------------------------------------------------------------------
+// MOLOCH core (idynamic = 3; Main/mod_moloch.F90, Arakawa C grid, zita levels).
+// Same padded (j,i,k) geometry and origin-shifted pointers as above: u lives on
+// (jx, iy-1), v on (jx-1, iy), everything else on cross points.
+#define RCM_MO_MAXF 7 /* fields advected by wafone: tetav, pai, ux, vx, wx, qv, qc */
+
+struct MoScalars {
+  double dtsec, dt, xt, dx, dz;
+  double dts, zdtrdx, zdtrdy, zdtrdz, zcs2, egdts;  // sound sub-step (Main/mod_moloch.F90:720-723)
+  double dta, adtrdx, adtrdy, adtrdz;               // advection step (:1109-1111)
+  double anu2;
+  double zz1, gzm1;                                 // surface-pressure closure (:377-383)
+  int ipptls, iboudy, ifrayd, kray, nspgx, nspgd, nf;
+};
+
+struct MoFields {
+  double *u, *v, *un, *vn, *w, *t, *pai, *tetav, *qv, *qc, *ux, *vx, *wx;
+  double *s, *zdiv, *deltaw, *wwkw, *p, *tvirt;
+  double *adv[RCM_MO_MAXF], *wz[RCM_MO_MAXF], *p0[RCM_MO_MAXF];
+  double *fmz, *fmzf, *zru, *zrv, *zeta, *tau_c, *tau_u, *tau_v;
+  double *ht, *hx, *hy, *mx2, *rmu, *rmv, *msfu, *msfv, *coriou, *coriov, *ps;
+  double *gzitak, *gzitakh, *ffilt;
+  double *xfc, *xgc, *xfd, *xgd;  // relaxation coefficients [ib + nspg*(k-1)]
+  double *xub0, *xubt, *xvb0, *xvbt, *xtb0, *xtbt, *xqb0, *xqbt, *xpb0, *xpbt;
+  int *zone_c, *zone_u, *zone_v;  // bits 0-3: south, north, west, east; bits 8..: ibnd
+  double* rimbuf;
+  int* nanflag;
+};

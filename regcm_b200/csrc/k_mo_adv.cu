@@ -1,0 +1,224 @@
+// MOLOCH core (idynamic = 3): advection step.
+//   k_mo_destag  uvstagtox + wstagtox                         Main/mod_moloch.F90:1739-1794,1574-1597
+//   k_mo_wafz / k_mo_wafy / k_mo_wafx   wafone (WAF/TVD, directional split z -> y -> x), non-ROTLLR branch
+//                                                             :1098-1181,1274-1358
+//   k_mo_restag  xtouvstag + xtowstag                         :1680-1737,1599-1618
+// The reference calls wafone once per advected field (tetav, pai, ux, vx, wx, qv[, qc]); the advecting
+// velocities, the metric ratios and the upwind selection do not depend on the field, so here one thread
+// computes them once per point and loops over the fields (RCM_MO_MAXF pointers in MoFields::adv).
+// Per field the arithmetic and its order are the reference's.
+#include "dev_common.cuh"
+#include "launch.h"
+
+using namespace rcm;
+
+__device__ __forceinline__ double mo_rdeno(const double t1, const double t2, const double t3, const double t4) {
+  const double zzden = (t3 - t4);
+  return (t1 - t2) / copysign(fmax(fabs(zzden), 1.0e-15), zzden);
+}
+__device__ __forceinline__ double mo_phi(const double r, const double is, const double zamu) {
+  const double b = fmax(0.0, fmin(2.0, fmax(r, fmin(2.0 * r, 1.0))));
+  return is + zamu * b - is * b;
+}
+
+__global__ void k_mo_destag(const Geom g, const MoFields f) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = 1 + blockIdx.z;
+  if (j > g.jce2 || i > g.ice2) return;
+  const int kz = g.kz;
+  double ux;
+  if (j >= g.jci1 && j <= g.jci2) ux = 0.5625 * (L3(f.u, j + 1, i, k) + L3(f.u, j, i, k)) - 0.0625 * (L3(f.u, j + 2, i, k) + L3(f.u, j - 1, i, k));
+  else if (j == g.jce1) ux = 0.5 * (L3(f.u, g.jde1, i, k) + L3(f.u, g.jdi1, i, k));
+  else ux = 0.5 * (L3(f.u, g.jde2, i, k) + L3(f.u, g.jdi2, i, k));
+  P3(f.ux, j, i, k) = ux;
+  double vx;
+  if (i >= g.ici1 && i <= g.ici2) vx = 0.5625 * (L3(f.v, j, i + 1, k) + L3(f.v, j, i, k)) - 0.0625 * (L3(f.v, j, i + 2, k) + L3(f.v, j, i - 1, k));
+  else if (i == g.ice1) vx = 0.5 * (L3(f.v, j, g.ide1, k) + L3(f.v, j, g.idi1, k));
+  else vx = 0.5 * (L3(f.v, j, g.ide2, k) + L3(f.v, j, g.idi2, k));
+  P3(f.vx, j, i, k) = vx;
+  double wx;
+  if (k >= 2 && k <= kz - 1) wx = 0.5625 * (L3(f.w, j, i, k + 1) + L3(f.w, j, i, k)) - 0.0625 * (L3(f.w, j, i, k + 2) + L3(f.w, j, i, k - 1));
+  else if (k == 1) wx = 0.5 * (L3(f.w, j, i, 2) + L3(f.w, j, i, 1));
+  else wx = 0.5 * (L3(f.w, j, i, kz + 1) + L3(f.w, j, i, kz));
+  P3(f.wx, j, i, k) = wx;
+}
+
+// vertical pass: one thread per interior column, all fields
+__global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_wafz(const Geom g, const MoFields f, const MoScalars s) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j > g.jci2 || i > g.ici2) return;
+  const int kz = g.kz, nf = s.nf;
+  const double zdtrdz = s.adtrdz;
+  const bool rs = (i == g.ici1), rn = (i == g.ici2);
+  for (int n = 0; n < nf; ++n) {
+    const double* pp = f.adv[n];
+    double* wz = f.wz[n];
+    double wfw_k = 0.0;                       // wfw(k), flux through the upper face of level k
+    double pkm1 = 0.0, pk = L3(pp, j, i, 1), pkp1 = L3(pp, j, i, 2), pkp2;
+    double s_k = 0.0;
+    for (int k = 1; k <= kz; ++k) {
+      pkp2 = (k + 2 <= kz) ? L3(pp, j, i, k + 2) : 0.0;
+      double wfw_kp1 = 0.0, s_kp1 = 0.0;
+      if (k <= kz - 1) {
+        s_kp1 = L3(f.s, j, i, k + 1);
+        const double zamu = s_kp1 * zdtrdz;
+        double is, p1, p1m1;
+        if (zamu >= 0.0) { is = 1.0; p1 = pkp1; p1m1 = (k + 2 > kz) ? pkp1 : pkp2; }   // k1 = k+1, k1m1 = min(k+2, kz)
+        else { is = -1.0; p1m1 = pk; p1 = (k - 1 < 1) ? pk : pkm1; }                    // k1m1 = k, k1 = max(k-1, 1)
+        const double r = mo_rdeno(p1, p1m1, pk, pkp1);
+        const double zphi = mo_phi(r, is, zamu);
+        wfw_kp1 = 0.5 * s_kp1 * ((1.0 + zphi) * pkp1 + (1.0 - zphi) * pk);
+      }
+      const double fmz = L3(f.fmz, j, i, k);
+      const double zrfmm = zdtrdz * fmz / L3(f.fmzf, j, i, k + 1);
+      double out;
+      if (k == 1) {
+        const double zdv = -s_kp1 * zrfmm * pk;
+        out = pk + wfw_kp1 * zrfmm + zdv;
+      } else {
+        const double zrfmp = zdtrdz * fmz / L3(f.fmzf, j, i, k);
+        const double zdv = (s_k * zrfmp - s_kp1 * zrfmm) * pk;
+        out = pk - wfw_k * zrfmp + wfw_kp1 * zrfmm + zdv;
+      }
+      P3(wz, j, i, k) = out;
+      if (rs) P3(wz, j, g.ice1, k) = out;
+      if (rn) P3(wz, j, g.ice2, k) = out;
+      wfw_k = wfw_kp1; s_k = s_kp1;
+      pkm1 = pk; pk = pkp1; pkp1 = pkp2;
+    }
+  }
+}
+
+// meridional pass
+__global__ void k_mo_wafy(const Geom g, const MoFields f, const MoScalars s) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = 1 + blockIdx.z;
+  if (j > g.jci2 || i > g.ici2) return;
+  const double zdtrdy = s.adtrdy;
+  const int nf = s.nf;
+  // the two faces i (south) and i+1 (north)
+  double vr[2], zamu[2], is[2];
+  int ih[2], ihm1[2];
+  for (int m = 0; m < 2; ++m) {
+    const int ii = i + m;
+    vr[m] = L3(f.v, j, ii, k) * L2(f.rmv, j, ii);
+    zamu[m] = vr[m] * zdtrdy;
+    if (zamu[m] > 0.0) { is[m] = 1.0; ih[m] = ii - 1; }
+    else { is[m] = -1.0; ih[m] = min(ii + 1, g.icross2); }
+    ihm1[m] = max(ih[m] - 1, g.icross1);
+  }
+  const double fmz = L3(f.fmz, j, i, k);
+  const double zrfmn = zdtrdy * 2.0 * fmz / (fmz + L3(f.fmz, j, i + 1, k));
+  const double zrfms = zdtrdy * 2.0 * fmz / (fmz + L3(f.fmz, j, i - 1, k));
+  const double mx2 = L2(f.mx2, j, i);
+  const double dvf = (vr[1] * zrfmn - vr[0] * zrfms);
+  const bool cw = (j == g.jci1), ce = (j == g.jci2);
+  for (int n = 0; n < nf; ++n) {
+    const double* wz = f.wz[n];
+    double zpby[2];
+    for (int m = 0; m < 2; ++m) {
+      const int ii = i + m;
+      const double wc = L3(wz, j, ii, k), wm = L3(wz, j, ii - 1, k);
+      const double r = mo_rdeno(L3(wz, j, ih[m], k), L3(wz, j, ihm1[m], k), wc, wm);
+      const double zphi = mo_phi(r, is[m], zamu[m]);
+      zpby[m] = 0.5 * vr[m] * ((1.0 + zphi) * wm + (1.0 - zphi) * wc);
+    }
+    const double zdv = dvf * L3(f.adv[n], j, i, k);
+    const double out = L3(wz, j, i, k) + mx2 * (zpby[0] * zrfms - zpby[1] * zrfmn + zdv);
+    double* p0 = f.p0[n];
+    P3(p0, j, i, k) = out;
+    if (cw) P3(p0, g.jce1, i, k) = out;
+    if (ce) P3(p0, g.jce2, i, k) = out;
+  }
+}
+
+// zonal pass; writes the advected field in place (each thread reads only its own point of it)
+__global__ void k_mo_wafx(const Geom g, const MoFields f, const MoScalars s) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = 1 + blockIdx.z;
+  if (j > g.jci2 || i > g.ici2) return;
+  const double zdtrdx = s.adtrdx;
+  const int nf = s.nf;
+  double ur[2], zamu[2], is[2];
+  int jh[2], jhm1[2];
+  for (int m = 0; m < 2; ++m) {
+    const int jj = j + m;
+    ur[m] = L3(f.u, jj, i, k) * L2(f.rmu, jj, i);
+    zamu[m] = ur[m] * zdtrdx;
+    if (zamu[m] > 0.0) { is[m] = 1.0; jh[m] = jj - 1; }
+    else { is[m] = -1.0; jh[m] = min(jj + 1, g.jcross2); }
+    jhm1[m] = max(jh[m] - 1, g.jcross1);
+  }
+  const double fmz = L3(f.fmz, j, i, k);
+  const double zrfme = zdtrdx * 2.0 * fmz / (fmz + L3(f.fmz, j + 1, i, k));
+  const double zrfmw = zdtrdx * 2.0 * fmz / (fmz + L3(f.fmz, j - 1, i, k));
+  const double mx2 = L2(f.mx2, j, i);
+  const double dvf = (ur[1] * zrfme - ur[0] * zrfmw);
+  for (int n = 0; n < nf; ++n) {
+    const double* p0 = f.p0[n];
+    double zpbw[2];
+    for (int m = 0; m < 2; ++m) {
+      const int jj = j + m;
+      const double pc = L3(p0, jj, i, k), pm = L3(p0, jj - 1, i, k);
+      const double r = mo_rdeno(L3(p0, jh[m], i, k), L3(p0, jhm1[m], i, k), pc, pm);
+      const double zphi = mo_phi(r, is[m], zamu[m]);
+      zpbw[m] = 0.5 * ur[m] * ((1.0 + zphi) * pm + (1.0 - zphi) * pc);
+    }
+    double* pp = f.adv[n];
+    const double zdv = dvf * P3(pp, j, i, k);
+    P3(pp, j, i, k) = L3(p0, j, i, k) + mx2 * (zpbw[0] * zrfmw - zpbw[1] * zrfme + zdv);
+  }
+}
+
+__global__ void k_mo_restag(const Geom g, const MoFields f) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jde1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ide1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = 1 + blockIdx.z;
+  if (j > g.jde2 || i > g.ide2) return;
+  const int kz = g.kz;
+  if (i >= g.ici1 && i <= g.ici2) {
+    if (j >= g.jdii1 && j <= g.jdii2)
+      P3(f.u, j, i, k) = 0.5625 * (L3(f.ux, j, i, k) + L3(f.ux, j - 1, i, k)) - 0.0625 * (L3(f.ux, j + 1, i, k) + L3(f.ux, j - 2, i, k));
+    else if (j == g.jdi2) P3(f.u, j, i, k) = 0.5 * (L3(f.ux, g.jci2, i, k) + L3(f.ux, g.jce2, i, k));
+    else if (j == g.jdi1) P3(f.u, j, i, k) = 0.5 * (L3(f.ux, g.jci1, i, k) + L3(f.ux, g.jce1, i, k));
+  }
+  if (j >= g.jci1 && j <= g.jci2) {
+    if (i >= g.idii1 && i <= g.idii2)
+      P3(f.v, j, i, k) = 0.5625 * (L3(f.vx, j, i, k) + L3(f.vx, j, i - 1, k)) - 0.0625 * (L3(f.vx, j, i + 1, k) + L3(f.vx, j, i - 2, k));
+    else if (i == g.idi2) P3(f.v, j, i, k) = 0.5 * (L3(f.vx, j, g.ici2, k) + L3(f.vx, j, g.ice2, k));
+    else if (i == g.idi1) P3(f.v, j, i, k) = 0.5 * (L3(f.vx, j, g.ici1, k) + L3(f.vx, j, g.ice1, k));
+  }
+  if (j <= g.jce2 && i <= g.ice2 && k >= 2) {
+    if (k >= 3 && k <= kz - 1)
+      P3(f.w, j, i, k) = 0.5625 * (L3(f.wx, j, i, k) + L3(f.wx, j, i, k - 1)) - 0.0625 * (L3(f.wx, j, i, k + 1) + L3(f.wx, j, i, k - 2));
+    else if (k == 2) P3(f.w, j, i, 2) = 0.5 * (L3(f.wx, j, i, 2) + L3(f.wx, j, i, 1));
+    else if (k == kz) P3(f.w, j, i, kz) = 0.5 * (L3(f.wx, j, i, kz) + L3(f.wx, j, i, kz - 1));
+  }
+}
+
+static dim3 grid3(int nj, int ni, int nk, dim3 b) { return dim3((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y, nk); }
+
+void launch_mo_destag(const Geom& g, const MoFields& f, cudaStream_t st) {
+  dim3 b(32, 4);
+  RCM_LAUNCH(k_mo_destag, grid3(g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, g.kz, b), b, st, g, f);
+}
+void launch_mo_waf(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
+  dim3 bc = col_block(), b(32, 4);
+  const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
+  RCM_LAUNCH(k_mo_wafz, grid3(nj, ni, 1, bc), bc, st, g, f, s);
+  RCM_LAUNCH(k_mo_wafy, grid3(nj, ni, g.kz, b), b, st, g, f, s);
+  RCM_LAUNCH(k_mo_wafx, grid3(nj, ni, g.kz, b), b, st, g, f, s);
+}
+void launch_mo_restag(const Geom& g, const MoFields& f, cudaStream_t st) {
+  dim3 b(32, 4);
+  RCM_LAUNCH(k_mo_restag, grid3(g.jde2 - g.jde1 + 1, g.ide2 - g.ide1 + 1, g.kz, b), b, st, g, f);
+}

@@ -1,0 +1,216 @@
+// MOLOCH core (idynamic = 3): sound sub-steps.
+//   k_mo_pre    tvirt, tetav at the head of `moloch`        Main/mod_moloch.F90:251-301
+//   k_mo_div    horizontal part of the divergence (Eq. 16)  :806-824 (non-ROTLLR)
+//   k_mo_w      filt3d + full divergence + implicit w (tridiagonal, Eq. 19) + new Exner function
+//                                                           :549-569,743-768,826-925,1022-1038
+//   k_mo_uv     horizontal momentum (Eq. 17, 18)            :975-1012
+//   k_mo_close  tvirt, t, p, ps at the end of the step      :321-383
+// One thread owns one (j,i) column in k_mo_w (the vertical recurrences); the other kernels are
+// elementwise over (j,i,k).  u and v are double-buffered (u,v -> un,vn) so that the Coriolis average
+// reads the pre-update winds, which is what the reference's ud/vd copies are for (:735-736).
+#include "dev_common.cuh"
+#include "launch.h"
+
+using namespace rcm;
+
+__global__ void k_mo_pre(const Geom g, const MoFields f, const MoScalars s) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = 1 + blockIdx.z;
+  if (j > g.jce2 || i > g.ice2) return;
+  double tv;
+  if (s.ipptls > 0) tv = P3(f.t, j, i, k) * (1.0 + ep1 * P3(f.qv, j, i, k) - P3(f.qc, j, i, k));
+  else tv = P3(f.t, j, i, k) * (1.0 + ep1 * P3(f.qv, j, i, k));
+  P3(f.tetav, j, i, k) = tv / P3(f.pai, j, i, k);
+}
+
+__global__ void k_mo_div(const Geom g, const MoFields f, const MoScalars s) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = 1 + blockIdx.z;
+  if (j > g.jce2 || i > g.ice2) return;
+  const double zum = L3(f.u, j, i, k) * L2(f.rmu, j, i) * L3(f.zru, j, i, k);
+  const double zup = L3(f.u, j + 1, i, k) * L2(f.rmu, j + 1, i) * L3(f.zru, j + 1, i, k);
+  const double zvm = L3(f.v, j, i, k) * L2(f.rmv, j, i) * L3(f.zrv, j, i, k);
+  const double zvp = L3(f.v, j, i + 1, k) * L2(f.rmv, j, i + 1) * L3(f.zrv, j, i + 1, k);
+  P3(f.zdiv, j, i, k) = (zup - zum) * s.zdtrdx + (zvp - zvm) * s.zdtrdy;
+}
+
+// filtered horizontal divergence of level k at (j,i): filt3d acts on interior points only
+__device__ __forceinline__ double mo_zd(const MoFields& f, const int si, const long long sk, const bool interior,
+                                        const double anu2, const int j, const int i, const int k) {
+  const double c = L3(f.zdiv, j, i, k);
+  if (!interior) return c;
+  const double p2d = 0.125 * (L3(f.zdiv, j - 1, i, k) + L3(f.zdiv, j + 1, i, k) + L3(f.zdiv, j, i - 1, k) + L3(f.zdiv, j, i + 1, k)) - 0.5 * c;
+  return c + anu2 * p2d;
+}
+
+// `zdf` receives the full divergence (a second array: the raw one is still being read by the
+// neighbours' filter); `jsound` is the 1-based sub-step index; `last`: write s (Eq. 10 completed).
+__global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_w(const Geom g, const MoFields f, const MoScalars s, double* zdf,
+                                                      const int jsound, const int last) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j > g.jce2 || i > g.ice2) return;
+  const int kz = g.kz, kzp1 = g.kzp1;
+  const bool interior = (j >= g.jci1 && j <= g.jci2 && i >= g.ici1 && i <= g.ici2);
+  const double hx0 = L2(f.hx, j, i), hx1 = L2(f.hx, j + 1, i), hy0 = L2(f.hy, j, i), hy1 = L2(f.hy, j, i + 1);
+  const double mx2 = L2(f.mx2, j, i);
+  const double zdtrdz = s.zdtrdz, zcs2 = s.zcs2, egdts = s.egdts, rjs = (double)jsound;
+  // winds of level k (carried) and k-1
+  double u0 = L3(f.u, j, i, kz), u1 = L3(f.u, j + 1, i, kz), v0 = L3(f.v, j, i, kz), v1 = L3(f.v, j, i + 1, kz);
+  double wkp1;  // w(k+1) of the downward sweep
+  {
+    const double zuh = u0 * hx0 + u1 * hx1, zvh = v0 * hy0 + v1 * hy1;
+    wkp1 = 0.5 * (zuh + zvh);
+    P3(f.w, j, i, kzp1) = wkp1;
+  }
+  double s_kp1 = -wkp1;
+  if (last) P3(f.s, j, i, kzp1) = interior ? 0.0 : s_kp1;
+  // s(kz), zdiv(kz)
+  double um0 = L3(f.u, j, i, kz - 1), um1 = L3(f.u, j + 1, i, kz - 1), vm0 = L3(f.v, j, i, kz - 1), vm1 = L3(f.v, j, i + 1, kz - 1);
+  double s_k;
+  {
+    const double zuh = (u0 + um0) * hx0 + (u1 + um1) * hx1, zvh = (v0 + vm0) * hy0 + (v1 + vm1) * hy1;
+    s_k = -0.25 * (zuh + zvh) * LD1(f.gzitak + kz);
+  }
+  double fmz_k = L3(f.fmz, j, i, kz);
+  double zdiv_k = fmz_k * (mx2 * mo_zd(f, si, sk, interior, s.anu2, j, i, kz) + zdtrdz * (s_k - s_kp1));
+  P3(zdf, j, i, kz) = zdiv_k;
+  double pai_k = P3(f.pai, j, i, kz), tet_k = L3(f.tetav, j, i, kz);
+  double wwkw_kp1 = 0.0;
+  for (int k = kz; k >= 2; --k) {
+    // level k-1 quantities: s(k-1) (0 for k-1 = 1), zdiv(k-1)
+    u0 = um0; u1 = um1; v0 = vm0; v1 = vm1;
+    double s_km1 = 0.0;
+    if (k - 1 >= 2) {
+      um0 = L3(f.u, j, i, k - 2); um1 = L3(f.u, j + 1, i, k - 2); vm0 = L3(f.v, j, i, k - 2); vm1 = L3(f.v, j, i + 1, k - 2);
+      const double zuh = (u0 + um0) * hx0 + (u1 + um1) * hx1, zvh = (v0 + vm0) * hy0 + (v1 + vm1) * hy1;
+      s_km1 = -0.25 * (zuh + zvh) * LD1(f.gzitak + k - 1);
+    }
+    const double fmz_km1 = L3(f.fmz, j, i, k - 1);
+    const double zdiv_km1 = fmz_km1 * (mx2 * mo_zd(f, si, sk, interior, s.anu2, j, i, k - 1) + zdtrdz * (s_km1 - s_k));
+    P3(zdf, j, i, k - 1) = zdiv_km1;
+    const double pai_km1 = P3(f.pai, j, i, k - 1), tet_km1 = L3(f.tetav, j, i, k - 1);
+    const double fmzf_k = L3(f.fmzf, j, i, k);
+    const double w_k = P3(f.w, j, i, k);
+    P3(f.deltaw, j, i, k) = -w_k;
+    double zrom1w = 0.5 * cpd * fmzf_k * (tet_km1 + tet_k);
+    zrom1w = zrom1w - cpd * w_k * (fmzf_k * fmzf_k) * rjs * zdtrdz * (tet_km1 - tet_k);
+    double zwexpl = w_k - zrom1w * zdtrdz * (pai_km1 - pai_k) - egdts;
+    zwexpl = zwexpl + rdrcv * zrom1w * zdtrdz * (pai_km1 * zdiv_km1 - pai_k * zdiv_k);
+    const double ff = LD1(f.ffilt + k);
+    const double zp = zcs2 * fmz_km1 * zrom1w * pai_km1 + ff;
+    const double zm = zcs2 * fmz_k * zrom1w * pai_k + ff;
+    const double zrapp = 1.0 / (1.0 + zm + zp - zm * wwkw_kp1);
+    const double wn = zrapp * (zwexpl + zm * wkp1);
+    wwkw_kp1 = zrapp * zp;
+    P3(f.w, j, i, k) = wn;
+    P3(f.wwkw, j, i, k) = wwkw_kp1;
+    if (last) P3(f.s, j, i, k) = s_k;
+    wkp1 = wn;
+    s_k = s_km1; zdiv_k = zdiv_km1; fmz_k = fmz_km1; pai_k = pai_km1; tet_k = tet_km1;
+  }
+  // 2nd loop of the tridiagonal inversion, new Exner function, completed s
+  double w_km1 = P3(f.w, j, i, 1);
+  for (int k = 2; k <= kz; ++k) {
+    const double wk = P3(f.w, j, i, k) + P3(f.wwkw, j, i, k) * w_km1;
+    P3(f.w, j, i, k) = wk;
+    P3(f.deltaw, j, i, k) = P3(f.deltaw, j, i, k) + wk;
+    if (interior) {
+      const double zd = P3(zdf, j, i, k - 1) + zdtrdz * L3(f.fmz, j, i, k - 1) * (w_km1 - wk);
+      P3(f.pai, j, i, k - 1) = P3(f.pai, j, i, k - 1) * (1.0 - rdrcv * zd);
+      if (last) P3(f.s, j, i, k) = (wk + P3(f.s, j, i, k)) * L3(f.fmzf, j, i, k);
+    }
+    w_km1 = wk;
+  }
+  if (interior) {
+    const double zd = P3(zdf, j, i, kz) + zdtrdz * L3(f.fmz, j, i, kz) * (w_km1 - P3(f.w, j, i, kzp1));
+    P3(f.pai, j, i, kz) = P3(f.pai, j, i, kz) * (1.0 - rdrcv * zd);
+    if (last) P3(f.s, j, i, 1) = 0.0;
+  }
+}
+
+__global__ void k_mo_uv(const Geom g, const MoFields f, const MoScalars s) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jde1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ide1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = 1 + blockIdx.z;
+  if (j > g.jde2 || i > g.ide2) return;
+  const double gk = LD1(f.gzitakh + k);
+  if (i <= g.ice2) {  // u point
+    double un = L3(f.u, j, i, k);
+    if (j >= g.jdii1 && j <= g.jdii2 && i >= g.ici1 && i <= g.ici2) {
+      const double zcx = s.zdtrdx * L2(f.msfu, j, i);
+      const double zfz = 0.25 * (L3(f.deltaw, j - 1, i, k) + L3(f.deltaw, j - 1, i, k + 1) + L3(f.deltaw, j, i, k) + L3(f.deltaw, j, i, k + 1)) + s.egdts;
+      const double zrom1u = 0.5 * cpd * (L3(f.tetav, j - 1, i, k) + L3(f.tetav, j, i, k));
+      const double zcor1u = L2(f.coriou, j, i) * 0.25 * (L3(f.v, j, i, k) + L3(f.v, j - 1, i, k) + L3(f.v, j, i + 1, k) + L3(f.v, j - 1, i + 1, k));
+      un = un + zcor1u * s.dts - zfz * L2(f.hx, j, i) * gk - zcx * zrom1u * (L3(f.pai, j, i, k) - L3(f.pai, j - 1, i, k));
+    }
+    P3(f.un, j, i, k) = un;
+  }
+  if (j <= g.jce2) {  // v point
+    double vn = L3(f.v, j, i, k);
+    if (i >= g.idii1 && i <= g.idii2 && j >= g.jci1 && j <= g.jci2) {
+      const double zcy = s.zdtrdy * L2(f.msfv, j, i);
+      const double zfz = 0.25 * (L3(f.deltaw, j, i - 1, k) + L3(f.deltaw, j, i - 1, k + 1) + L3(f.deltaw, j, i, k) + L3(f.deltaw, j, i, k + 1)) + s.egdts;
+      const double zrom1v = 0.5 * cpd * (L3(f.tetav, j, i - 1, k) + L3(f.tetav, j, i, k));
+      const double zcor1v = L2(f.coriov, j, i) * 0.25 * (L3(f.u, j, i, k) + L3(f.u, j + 1, i, k) + L3(f.u, j, i - 1, k) + L3(f.u, j + 1, i - 1, k));
+      vn = vn - zcor1v * s.dts - zfz * L2(f.hy, j, i) * gk - zcy * zrom1v * (L3(f.pai, j, i, k) - L3(f.pai, j, i - 1, k));
+    }
+    P3(f.vn, j, i, k) = vn;
+  }
+}
+
+__global__ void k_mo_close(const Geom g, const MoFields f, const MoScalars s) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j > g.jce2 || i > g.ice2) return;
+  const bool interior = (j >= g.jci1 && j <= g.jci2 && i >= g.ici1 && i <= g.ici2);
+  double tv = 0.0, pk = 0.0;
+  for (int k = 1; k <= g.kz; ++k) {
+    const double qv = P3(f.qv, j, i, k);
+    const double den = (s.ipptls > 0) ? (1.0 + ep1 * qv - P3(f.qc, j, i, k)) : (1.0 + ep1 * qv);
+    const double pai = P3(f.pai, j, i, k);
+    if (interior) {
+      tv = P3(f.tetav, j, i, k) * pai;
+      P3(f.t, j, i, k) = tv / den;
+    } else {
+      tv = P3(f.t, j, i, k) * den;
+    }
+    P3(f.tvirt, j, i, k) = tv;
+    pk = pow(pai, cpovr) * p00;
+    P3(f.p, j, i, k) = pk;
+  }
+  const double zdgz = L2(f.ht, j, i) * s.gzm1 + s.zz1;
+  const double ps = pk * exp(zdgz / (rgas * tv));
+  P2(f.ps, j, i) = ps;
+  if (!(ps == ps)) *f.nanflag = 1;
+}
+
+static dim3 grid3(const Geom& g, int nj, int ni, int nk, dim3 b) { return dim3((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y, nk); }
+
+void launch_mo_pre(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
+  dim3 b(32, 4);
+  RCM_LAUNCH(k_mo_pre, grid3(g, g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, g.kz, b), b, st, g, f, s);
+}
+void launch_mo_div(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
+  dim3 b(32, 4);
+  RCM_LAUNCH(k_mo_div, grid3(g, g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, g.kz, b), b, st, g, f, s);
+}
+void launch_mo_w(const Geom& g, const MoFields& f, const MoScalars& s, double* zdf, int jsound, int last, cudaStream_t st) {
+  dim3 b = col_block();
+  RCM_LAUNCH(k_mo_w, grid3(g, g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, 1, b), b, st, g, f, s, zdf, jsound, last);
+}
+void launch_mo_uv(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
+  dim3 b(32, 4);
+  RCM_LAUNCH(k_mo_uv, grid3(g, g.jde2 - g.jde1 + 1, g.ide2 - g.ide1 + 1, g.kz, b), b, st, g, f, s);
+}
+void launch_mo_close(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
+  dim3 b = col_block();
+  RCM_LAUNCH(k_mo_close, grid3(g, g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, 1, b), b, st, g, f, s);
+}
