@@ -27,6 +27,8 @@ UNIT = "grid-point-steps/s"
 # compulsory HBM bytes per grid-point-step of the NH core, nqx = 2
 ALG_BYTES_STEP = lambda istep: 352 + 192 * istep  # noqa: E731
 ALG_BYTES_STEP_HYDRO = 312  # hydrostatic core, 39 passes (+ the 2-D sub-steps, not counted)
+# MOLOCH, nqx = 2: B_MO = nadv*(nsound*112 + 424) + 64 (3352 B for nadv = 3, nsound = 6)
+ALG_BYTES_STEP_MOLOCH = lambda nadv, nsound: nadv * (nsound * 112 + 424) + 64  # noqa: E731
 # per-kernel algorithmic bytes per grid point and launch = 8 B x (distinct 3-D fields
 # read + written by that kernel), listed in DESIGN.md §Kernels
 ALG_BYTES_KERNEL = {
@@ -34,6 +36,9 @@ ALG_BYTES_KERNEL = {
     "k_snd_uv": 80, "k_snd_wfwd": 128, "k_snd_wback": 168, "k_snd_final": 160,
     # hydrostatic core
     "k_h_prep": 64, "k_h_uv": 120, "k_h_tq": 136, "k_sp_proj": 48, "k_sp_corr": 96,
+    # MOLOCH core; k_mo_waf = the three directional passes of all 7 fields (one timed group),
+    # k_mo_stag = destagger or restagger, k_mo_pre = head (tetav) or tail (t, p, ps) of the step
+    "k_mo_div": 40, "k_mo_w": 104, "k_mo_uv": 56, "k_mo_waf": 504, "k_mo_stag": 48, "k_mo_pre": 52,
 }
 
 
@@ -189,7 +194,8 @@ def run_reference(args):
 
 def workload_desc(w):
     c = synth.CASES[w]
-    core = "hydrostatic (idynamic=1, split-explicit nsplit=2)" if c.get("idynamic", 2) == 1 else "non-hydrostatic (idynamic=2)"
+    core = {1: "hydrostatic (idynamic=1, split-explicit nsplit=2)", 2: "non-hydrostatic (idynamic=2)",
+            3: "MOLOCH (idynamic=3, mo_nadv=3, mo_nsound=6)"}[c.get("idynamic", 2)]
     return (f"{w}: {c['jx']}x{c['iy']}x{c['kz']} {core}, ds={c['ds']} km, dt={c['dt']} s, "
             f"physics off, synthetic analytic ICBC")
 
@@ -215,8 +221,9 @@ def run_gpu(args):
     probe_cfg = synth.make_case("tiny").cfg  # only for struct defaults
     del probe_cfg
     hydro = base.get("idynamic", 2) == 1
-    if hydro and world > 1:
-        raise SystemExit("bench.py: the hydrostatic workload (BASELINE configs[0]) is a single-rank case")
+    moloch = base.get("idynamic", 2) == 3
+    if (hydro or moloch) and world > 1:
+        raise SystemExit("bench.py: the hydrostatic and MOLOCH workloads run on one rank in this version")
     cfg = capi.default_cfg(base.get("idynamic", 2), jx=base["jx"], iy=base["iy"], kz=base["kz"], ds=base["ds"], dt=base["dt"],
                            nspgx=base["nspg"], nspgd=base["nspg"], **cfgkw)
     core = capi.DynCore(lib, cfg)
@@ -290,7 +297,8 @@ def run_gpu(args):
                 "per_kernel": {k: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps,
                                    "GBs": (ALG_BYTES_KERNEL[k] * local_cells / (v[0] / v[1] * 1e-3) / 1e9 if k in ALG_BYTES_KERNEL and v[1] else None)}
                                for k, v in prof.items() if v[1] > 0}}
-    step_bytes = ALG_BYTES_STEP_HYDRO if hydro else ALG_BYTES_STEP(istep)
+    step_bytes = (ALG_BYTES_STEP_HYDRO if hydro else ALG_BYTES_STEP_MOLOCH(cfg.mo_nadv, cfg.mo_nsound) if moloch
+                  else ALG_BYTES_STEP(istep))
     step_roof = {"alg_bytes_per_grid_point_step": step_bytes, "achieved_GBs": step_bytes * value / world / 1e9,
                  "frac_of_peak_per_gpu": step_bytes * value / world / 1e9 / peak}
 
@@ -310,11 +318,13 @@ def run_gpu(args):
             pinned_in[fid] = v
         j1, j2, i1, i2 = core.tile()
         out_lbub = {}
-        prognostics = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PS) if hydro else tuple(range(7))
+        prognostics = ((capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PS) if hydro else
+                       (capi.F_U, capi.F_V, capi.F_W, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PAI, capi.F_PS) if moloch else tuple(range(7)))
         for fid in prognostics:
-            dot = fid in (capi.F_U, capi.F_V)
+            dotj = fid == capi.F_U or (fid == capi.F_V and not moloch)     # Arakawa C: u is staggered in j only, v in i only
+            doti = fid == capi.F_V or (fid == capi.F_U and not moloch)
             lbs = (j1, i1, 1)
-            ubs = (j2 if dot else min(j2, base["jx"] - 1), i2 if dot else min(i2, base["iy"] - 1),
+            ubs = (j2 if dotj else min(j2, base["jx"] - 1), i2 if doti else min(i2, base["iy"] - 1),
                    1 if fid == capi.F_PS else base["kz"] + (1 if fid == capi.F_W else 0))
             shp = tuple(ubs[d] - lbs[d] + 1 for d in range(3))
             t = torch.empty(shp[::-1], dtype=torch.float64).pin_memory()

@@ -20,6 +20,9 @@ CASES = [("tiny", 12, {}), ("tiny", 6, {"iboudy": 1, "ifupr": 0}), ("small", 4, 
 # hydrostatic core (idynamic = 1): files hy_*.npz carry u, v, t, qv, qc, ps and the noise parameters
 HYDRO_CASES = [("tiny", 12, {}), ("tiny", 6, {"iboudy": 1}), ("small", 4, {})]
 HYDRO_FIELDS = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PS)
+# MOLOCH core (idynamic = 3): files mo_*.npz carry the single-level C-grid state u, v, w, t, qv, qc, pai, ps
+MOLOCH_CASES = [("tinym", 10, {}), ("tinym", 6, {"iboudy": 1}), ("smallm", 3, {})]
+MOLOCH_FIELDS = (capi.F_U, capi.F_V, capi.F_W, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PAI, capi.F_PS)
 
 
 def main():
@@ -55,6 +58,19 @@ def main():
         tag = name + "".join(f"_{k}{v}" for k, v in sorted(kw.items()))
         np.savez_compressed(os.path.join(ROOT, "tests", "golden", f"hy_{tag}_{nsteps}.npz"), **out)
         print("wrote hydro", tag, nsteps)
+    for name, nsteps, kw in MOLOCH_CASES:
+        case = synth.make_case(name, **kw)
+        o = pyoracle.make_oracle(case.cfg)
+        synth.load_case(o, case)
+        o.step(nsteps)
+        out = {"nsteps": nsteps}
+        for f in MOLOCH_FIELDS:
+            out[capi.FIELD_NAMES[f] + "_a"] = o.get_state(f)
+        d = o.diag()
+        out["ps_max"], out["ps_min"] = d.ps_max, d.ps_min
+        tag = name + "".join(f"_{k}{v}" for k, v in sorted(kw.items()))
+        np.savez_compressed(os.path.join(ROOT, "tests", "golden", f"mo_{tag}_{nsteps}.npz"), **out)
+        print("wrote moloch", tag, nsteps)
 
 
 if __name__ == "__main__":

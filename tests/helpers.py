@@ -7,14 +7,23 @@ HYDRO_FIELDS = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PS)
 HYDRO_WORK = (capi.W_QDOT, capi.W_XKC, capi.W_OMEGA, capi.W_PHI, capi.W_PTEN)
 
 
+MOLOCH_FIELDS = (capi.F_U, capi.F_V, capi.F_W, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PAI, capi.F_PS)
+MOLOCH_WORK = (capi.W_MO_P, capi.W_MO_TVIRT, capi.W_MO_FMZ, capi.W_MO_FMZF, capi.W_MO_ZETA, capi.W_MO_S)
+
+
 def prognostics(core):
-    """Prognostic fields of the core in use (idynamic = 1 carries p*, no p', w)."""
+    """Prognostic fields of the core in use (idynamic = 1 carries p*, no p', w; idynamic = 3: the
+    single-level C-grid state of mo_atm)."""
+    if core.cfg.idynamic == 3:
+        return MOLOCH_FIELDS
     return HYDRO_FIELDS if core.cfg.idynamic == 1 else tuple(range(7))
 
 
 def rel_errors(core, ref, levels=(capi.LEVEL_A, capi.LEVEL_B)):
     """Per prognostic field: L-inf and L2 error normalised by the reference."""
     out = {}
+    if core.cfg.idynamic == 3:
+        levels = (capi.LEVEL_A,)
     for f in prognostics(core):
         for lv in levels:
             a, b = core.get_state(f, lv), ref.get_state(f, lv)
@@ -26,7 +35,7 @@ def rel_errors(core, ref, levels=(capi.LEVEL_A, capi.LEVEL_B)):
 
 def work_errors(core, ref):
     out = {}
-    for w in (HYDRO_WORK if core.cfg.idynamic == 1 else range(10)):
+    for w in (MOLOCH_WORK if core.cfg.idynamic == 3 else HYDRO_WORK if core.cfg.idynamic == 1 else range(10)):
         a, b = core.get_work(w), ref.get_work(w)
         sc = max(float(np.abs(b).max()), 1e-300)
         out[capi.WORK_NAMES[w]] = float(np.abs(a - b).max()) / sc

@@ -156,6 +156,7 @@ def test_hydro_rejects_unsupported(emu_lib):
     case.cfg.nproc = 2
     with pytest.raises(capi.RcmError):
         capi.DynCore(emu_lib, case.cfg)
-    case = synth.make_case("tiny", idynamic=3)
+    case = synth.make_case("tiny", idynamic=1)
+    case.cfg.idynamic = 4          # no such core
     with pytest.raises(capi.RcmError):
         capi.DynCore(emu_lib, case.cfg)

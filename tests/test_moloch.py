@@ -1,0 +1,176 @@
+"""MOLOCH core (idynamic = 3): pins of the CPU restatement and the kernel
+LOGIC check of the CUDA sources through the test-only host harness (tests/emu), bit for bit.
+
+The reference ships no golden vectors for this path.  The behavioural pins it does hold are its
+two built-in analytic cases (`moloch_do_test_1/2`, Main/mpplib/mod_runparams.F90:171-172,
+Main/mod_bdycod.F90:5157-5199, Main/mod_params.F90:1737-1756): a resting standard atmosphere over
+flat terrain must stay at rest, and a uniform 10 m/s flow with unit map factors, no Coriolis force and
+no top sponge must stay uniform.  Both are reproduced here with exactly those fields.  The
+coordinate functions are checked against their closed forms (Share/mod_zita.F90:46-120)."""
+import numpy as np
+import pytest
+
+from oracle import pyoracle
+from regcm_b200 import capi, synth
+from tests.helpers import MOLOCH_FIELDS, make_pair, rel_errors, work_errors
+
+RGAS = 6.02214129e23 * 1.3806504e-23 / 28.96454 * 1000.0
+G = 9.80665
+
+
+def _analytic_case(test: int, name="tinym", **kw):
+    """The reference's analytic ICBC: test 1 = rest, test 2 = uniform zonal flow."""
+    over = dict(flat=True, noise=False)
+    if test == 2:
+        over.update(unit_map=True, mo_nzfilt=0)
+    over.update(kw)
+    case = synth.make_case(name, **over)
+    _, _, _, _, ak, _ = synth.moloch_levels(case.cfg)      # zeta over flat terrain = ak
+    t = np.maximum(288.15 - 0.00649 * ak, 210.0)
+    for slot in case.bdy:
+        r = case.bdy[slot]
+        r[capi.F_U][...] = 0.0 if test == 1 else 10.0
+        r[capi.F_V][...] = 0.0
+        r[capi.F_QV][...] = 0.0
+        r[capi.F_T][...] = t[None, None, :]
+        r[capi.F_PS][...] = 1013.25 if test == 1 else 1013.25 * np.exp(-(G / RGAS) * ak[-1] / t[-1])
+    return case
+
+
+def _run(case, nsteps, checked=True):
+    o = pyoracle.make_oracle(case.cfg, checked=checked)
+    synth.load_case(o, case)
+    o.step(nsteps)
+    return o
+
+
+def test_oracle_moloch_static_test1_rest():
+    case = _analytic_case(1)
+    o = pyoracle.make_oracle(case.cfg, checked=True)
+    synth.load_case(o, case)
+    t0, p0 = o.get_state(capi.F_T), o.get_state(capi.F_PAI)
+    o.step(30)
+    assert np.abs(o.get_state(capi.F_U)).max() < 1e-7 and np.abs(o.get_state(capi.F_V)).max() < 1e-7
+    assert np.abs(o.get_state(capi.F_W)).max() < 1e-6
+    assert np.abs(o.get_state(capi.F_T) - t0).max() < 1e-6
+    assert np.abs(o.get_state(capi.F_PAI) - p0).max() < 1e-9
+    d = o.diag()
+    assert abs(d.ps_max - 101325.0) < 1e-3 and abs(d.ps_min - 101325.0) < 1e-3
+
+
+def test_oracle_moloch_static_test2_uniform_flow():
+    case = _analytic_case(2)
+    o = pyoracle.make_oracle(case.cfg, checked=True)
+    synth.load_case(o, case)
+    t0 = o.get_state(capi.F_T)
+    o.step(30)
+    assert np.abs(o.get_state(capi.F_U) - 10.0).max() < 1e-6
+    assert np.abs(o.get_state(capi.F_V)).max() < 1e-6 and np.abs(o.get_state(capi.F_W)).max() < 1e-5
+    assert np.abs(o.get_state(capi.F_T) - t0).max() < 1e-5
+
+
+def test_oracle_moloch_statics_closed_form():
+    """fmz, fmzf, zeta against Share/mod_zita.F90 (Eq. 7 and 9 of the MOLOCH description) in numpy."""
+    case = synth.make_case("tinym")
+    o = _run(case, 0)
+    cfg = case.cfg
+    hz, dz, zita, zitah, ak, bk = synth.moloch_levels(cfg)
+    ht = case.statics[capi.S_HT]
+    zeta = o.get_work(capi.W_MO_ZETA)
+    assert np.abs(zeta - (ak[None, None, :] + (bk[None, None, :] - 1.0) * ht[:, :, None])).max() < 1e-8
+    def fmz(z, orog):
+        zfz = 1.0 - z / hz
+        r = z / hz
+        gp = (-cfg.mo_a0 - (6.0 - 4.0 * cfg.mo_a0) * r + (6.0 - 3.0 * cfg.mo_a0) * r ** 2) / hz
+        b = cfg.mo_b0 + (1.0 - cfg.mo_b0) * r
+        return zfz / (b + orog * zfz * gp - hz * zfz * np.log(zfz) * (1.0 - cfg.mo_b0) / hz)
+    got = o.get_work(capi.W_MO_FMZ)
+    want = fmz(zitah[None, None, :], ht[:, :, None])
+    assert np.abs(got - want).max() / np.abs(want).max() < 1e-13
+    gotf = o.get_work(capi.W_MO_FMZF)
+    wantf = fmz(zita[None, None, 1:], ht[:, :, None])
+    assert np.abs(gotf[:, :, 1:] - wantf).max() / np.abs(wantf).max() < 1e-13
+    assert np.all(gotf[:, :, 0] == 0.0)
+    # the initial Exner function is in hydrostatic balance with the discrete w equation: a state at
+    # rest produces no vertical acceleration (checked dynamically by test 1); here: monotone and < 1 aloft
+    pai = o.get_state(capi.F_PAI)
+    assert np.all(np.diff(pai, axis=2) > 0) and pai.max() < 1.01 and pai.min() > 0.2
+
+
+def test_oracle_moloch_long_run_with_record_change():
+    case = synth.make_case("tinym", ibdyfrq=1)      # 40 steps per record
+    o = _run(case, 70, checked=False)
+    d = o.diag()
+    assert d.lcount == 70 and d.xbctime == 90.0 * 31
+    assert 8.0e4 < d.ps_min < d.ps_max < 1.06e5
+    assert np.abs(o.get_state(capi.F_W)).max() < 5.0 and np.abs(o.get_state(capi.F_U)).max() < 60.0
+    with pytest.raises(capi.RcmError) as ei:
+        o.step(40)           # third record not staged
+    assert ei.value.code == -6
+
+
+MOLOCH_VARIANTS = [{}, {"iboudy": 1}, {"iboudy": 0}, {"ipptls": 0}, {"ifrayd": 0}, {"mo_nzfilt": 0},
+                   {"mo_nadv": 2, "mo_nsound": 4}, {"mo_nadv": 1, "mo_nsound": 1}, {"mo_anu2": 0.0},
+                   {"flat": True, "unit_map": True}, {"noise": False}, {"mo_a0": 0.1, "mo_b0": 0.6}]
+
+
+@pytest.mark.parametrize("kw", MOLOCH_VARIANTS, ids=lambda k: "-".join(f"{a}{b}" for a, b in k.items()) or "default")
+def test_emu_moloch_bit_exact(emu_lib, kw):
+    """Same .cu sources executed thread by thread on the host: every prognostic field and work array
+    equals the oracle bit for bit (both sides use glibc for pow/exp/log)."""
+    case, core, ref = make_pair(emu_lib, "tinym", oracle_checked=True, **kw)
+    for f in MOLOCH_FIELDS:
+        np.testing.assert_array_equal(core.get_state(f), ref.get_state(f), err_msg="init " + capi.FIELD_NAMES[f])
+    core.step(3); ref.step(3)
+    for f in MOLOCH_FIELDS:
+        np.testing.assert_array_equal(core.get_state(f), ref.get_state(f), err_msg=capi.FIELD_NAMES[f])
+    assert max(work_errors(core, ref).values()) == 0.0
+    dc, dr = core.diag(), ref.diag()
+    assert (dc.lcount, dc.xbctime, dc.ps_max, dc.ps_min) == (dr.lcount, dr.xbctime, dr.ps_max, dr.ps_min)
+
+
+def test_emu_moloch_boundary_record_change(emu_lib):
+    case, core, ref = make_pair(emu_lib, "tinym", ibdyfrq=1)
+    core.step(45); ref.step(45)      # record change at step 40
+    assert core.diag().xbctime == ref.diag().xbctime == 90.0 * 6
+    assert max(e[0] for e in rel_errors(core, ref).values()) == 0.0
+
+
+def test_emu_moloch_small_shape_and_cloud_water(emu_lib):
+    case, core, ref = make_pair(emu_lib, "smallm")
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    J, I, K = np.meshgrid(np.arange(jx - 1), np.arange(iy - 1), np.arange(kz), indexing="ij")
+    qc = np.asfortranarray(1e-4 * (1.0 + 0.5 * np.sin(2 * np.pi * J / (jx - 1)) * np.cos(2 * np.pi * I / (iy - 1))) * np.sin(np.pi * (K + 0.5) / kz))
+    for c in (core, ref):
+        c.set_state(capi.F_QC, capi.LEVEL_A, qc)
+    np.testing.assert_array_equal(core.get_state(capi.F_QC), qc)
+    core.step(2); ref.step(2)
+    assert max(e[0] for e in rel_errors(core, ref).values()) == 0.0
+    # the inflow/outflow rule acted on the rim of qc
+    assert np.any(ref.get_state(capi.F_QC)[0, :, :] == 0.0) or np.any(ref.get_state(capi.F_QC)[-1, :, :] == 0.0)
+
+
+def test_emu_moloch_analytic_cases(emu_lib):
+    for test in (1, 2):
+        case = _analytic_case(test)
+        core = capi.DynCore(emu_lib, case.cfg)
+        synth.load_case(core, case)
+        core.step(10)
+        u = core.get_state(capi.F_U)
+        assert np.abs(u - (0.0 if test == 1 else 10.0)).max() < 1e-6
+        assert np.abs(core.get_state(capi.F_V)).max() < 1e-6
+
+
+def test_moloch_rejects_unsupported(emu_lib):
+    for kw in ({"nproc": 2}, {"mo_nadv": 0}, {"ipptls": 2}, {"kz": 3}):
+        case = synth.make_case("tinym")
+        cfg = case.cfg
+        for k, v in kw.items():
+            setattr(cfg, k, v)
+        with pytest.raises(capi.RcmError) as ei:
+            capi.DynCore(emu_lib, cfg)
+        assert ei.value.code == -1, kw
+    case = synth.make_case("tinym")
+    core = capi.DynCore(emu_lib, case.cfg)
+    with pytest.raises(capi.RcmError):
+        core.set_bdy(capi.F_PP, capi.BDY_B0, np.zeros((19, 15, 10)))     # no p' in this core

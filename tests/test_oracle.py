@@ -114,7 +114,8 @@ def test_checked_build_full_run(built):
 
 
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "nh_*.npz")) +
-                                        glob.glob(os.path.join(ROOT, "tests", "golden", "hy_*.npz"))))
+                                        glob.glob(os.path.join(ROOT, "tests", "golden", "hy_*.npz")) +
+                                        glob.glob(os.path.join(ROOT, "tests", "golden", "mo_*.npz"))))
 def test_oracle_matches_golden(built, path):
     """Regression pin: the oracle reproduces the committed fixtures exactly."""
     from tests.golden_util import load_golden
