@@ -1,10 +1,12 @@
 #!/usr/bin/env python
-"""Benchmark of the RegCM non-hydrostatic dyn-core step on B200.
+"""Benchmark of the RegCM dyn-core step on B200.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C4|C3|C2 | C1|C3h|C4h|C4hq (hydrostatic)] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+                  [--workload C4|C3|C2 (non-hydrostatic) | C1|C3h|C4h|C4hq (hydrostatic) | C5|C5q|smallm (MOLOCH)]
 
-One "step" = one full model step (`tend` + `bdyval`: slow tendencies, istep acoustic
-sub-steps, filters, boundary update) over the whole synthetic domain.  Prints ONE JSON
+One "step" = one full model step (`tend` or `moloch`, then `bdyval`: slow tendencies, acoustic
+sub-steps, advection, filters, boundary update) over the whole synthetic domain.  The default
+workload C4 is the non-hydrostatic convection-permitting configuration the metric is quoted on.  Prints ONE JSON
 line on rank 0.  With torchrun (N > 1) the domain is decomposed over the ranks like
 set_nproc does (strong scaling: the total work is fixed).
 """
@@ -46,7 +48,7 @@ def measured_traffic(kernel, workload, world):
     """dram bytes per launch of `kernel` from the committed ncu captures (profiles/r1_traffic.json for the
     non-hydrostatic C4, profiles/r1_hydro_traffic.json for the hydrostatic C4hq); only meaningful for the
     configuration it was captured on."""
-    for fn in ("r1_traffic.json", "r1_hydro_traffic.json"):
+    for fn in ("r1_traffic.json", "r1_hydro_traffic.json", "r1_moloch_traffic.json"):
         try:
             with open(os.path.join(ROOT, "profiles", fn)) as fh:
                 t = json.load(fh)
