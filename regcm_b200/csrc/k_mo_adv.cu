@@ -45,51 +45,65 @@ __global__ void k_mo_destag(const Geom g, const MoFields f) {
   P3(f.wx, j, i, k) = wx;
 }
 
-// vertical pass: one thread per interior column, all fields
-__global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_wafz(const Geom g, const MoFields f, const MoScalars s) {
+// vertical pass: one thread per interior column marches k once for all NF fields; the 4-level window
+// pp(k-1..k+2) of every field lives in registers, the interface velocity and the metric ratios are
+// evaluated once per level
+template <int NF>
+__global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_wafz(const Geom g, const MoFields f, const MoScalars s) {
   const int si = g.si; const long long sk = g.sk;
   const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jci2 || i > g.ici2) return;
-  const int kz = g.kz, nf = s.nf;
+  const int kz = g.kz;
   const double zdtrdz = s.adtrdz;
   const bool rs = (i == g.ici1), rn = (i == g.ici2);
-  for (int n = 0; n < nf; ++n) {
-    const double* pp = f.adv[n];
-    double* wz = f.wz[n];
-    double wfw_k = 0.0;                       // wfw(k), flux through the upper face of level k
-    double pkm1 = 0.0, pk = L3(pp, j, i, 1), pkp1 = L3(pp, j, i, 2), pkp2;
-    double s_k = 0.0;
-    for (int k = 1; k <= kz; ++k) {
-      pkp2 = (k + 2 <= kz) ? L3(pp, j, i, k + 2) : 0.0;
-      double wfw_kp1 = 0.0, s_kp1 = 0.0;
+  double pkm1[NF], pk[NF], pkp1[NF], wfw_k[NF];
+#pragma unroll
+  for (int n = 0; n < NF; ++n) {
+    pkm1[n] = 0.0; wfw_k[n] = 0.0;
+    pk[n] = L3(f.adv[n], j, i, 1); pkp1[n] = L3(f.adv[n], j, i, 2);
+  }
+  double s_k = 0.0;
+  double fmzf_k = 0.0;   // fmzf(k); not used for k = 1
+  for (int k = 1; k <= kz; ++k) {
+    double pkp2[NF];
+#pragma unroll
+    for (int n = 0; n < NF; ++n) pkp2[n] = (k + 2 <= kz) ? L3(f.adv[n], j, i, k + 2) : 0.0;
+    const double s_kp1 = (k <= kz - 1) ? L3(f.s, j, i, k + 1) : 0.0;
+    const double fmz = L3(f.fmz, j, i, k);
+    const double fmzf_kp1 = L3(f.fmzf, j, i, k + 1);
+    const double zamu = s_kp1 * zdtrdz;
+    const bool up = (zamu >= 0.0);
+    const double is = up ? 1.0 : -1.0;
+    const double zrfmm = zdtrdz * fmz / fmzf_kp1;
+    const double zrfmp = (k > 1) ? zdtrdz * fmz / fmzf_k : 0.0;
+#pragma unroll
+    for (int n = 0; n < NF; ++n) {
+      double wfw_kp1 = 0.0;
       if (k <= kz - 1) {
-        s_kp1 = L3(f.s, j, i, k + 1);
-        const double zamu = s_kp1 * zdtrdz;
-        double is, p1, p1m1;
-        if (zamu >= 0.0) { is = 1.0; p1 = pkp1; p1m1 = (k + 2 > kz) ? pkp1 : pkp2; }   // k1 = k+1, k1m1 = min(k+2, kz)
-        else { is = -1.0; p1m1 = pk; p1 = (k - 1 < 1) ? pk : pkm1; }                    // k1m1 = k, k1 = max(k-1, 1)
-        const double r = mo_rdeno(p1, p1m1, pk, pkp1);
+        double p1, p1m1;
+        if (up) { p1 = pkp1[n]; p1m1 = (k + 2 > kz) ? pkp1[n] : pkp2[n]; }   // k1 = k+1, k1m1 = min(k+2, kz)
+        else { p1m1 = pk[n]; p1 = (k - 1 < 1) ? pk[n] : pkm1[n]; }           // k1m1 = k, k1 = max(k-1, 1)
+        const double r = mo_rdeno(p1, p1m1, pk[n], pkp1[n]);
         const double zphi = mo_phi(r, is, zamu);
-        wfw_kp1 = 0.5 * s_kp1 * ((1.0 + zphi) * pkp1 + (1.0 - zphi) * pk);
+        wfw_kp1 = 0.5 * s_kp1 * ((1.0 + zphi) * pkp1[n] + (1.0 - zphi) * pk[n]);
       }
-      const double fmz = L3(f.fmz, j, i, k);
-      const double zrfmm = zdtrdz * fmz / L3(f.fmzf, j, i, k + 1);
       double out;
       if (k == 1) {
-        const double zdv = -s_kp1 * zrfmm * pk;
-        out = pk + wfw_kp1 * zrfmm + zdv;
+        const double zdv = -s_kp1 * zrfmm * pk[n];
+        out = pk[n] + wfw_kp1 * zrfmm + zdv;
       } else {
-        const double zrfmp = zdtrdz * fmz / L3(f.fmzf, j, i, k);
-        const double zdv = (s_k * zrfmp - s_kp1 * zrfmm) * pk;
-        out = pk - wfw_k * zrfmp + wfw_kp1 * zrfmm + zdv;
+        const double zdv = (s_k * zrfmp - s_kp1 * zrfmm) * pk[n];
+        out = pk[n] - wfw_k[n] * zrfmp + wfw_kp1 * zrfmm + zdv;
       }
+      double* wz = f.wz[n];
       P3(wz, j, i, k) = out;
       if (rs) P3(wz, j, g.ice1, k) = out;
       if (rn) P3(wz, j, g.ice2, k) = out;
-      wfw_k = wfw_kp1; s_k = s_kp1;
-      pkm1 = pk; pk = pkp1; pkp1 = pkp2;
+      wfw_k[n] = wfw_kp1;
+      pkm1[n] = pk[n]; pk[n] = pkp1[n]; pkp1[n] = pkp2[n];
     }
+    s_k = s_kp1; fmzf_k = fmzf_kp1;
   }
 }
 
@@ -178,6 +192,132 @@ __global__ void k_mo_wafx(const Geom g, const MoFields f, const MoScalars s) {
   }
 }
 
+// Variants of the horizontal passes in which one thread owns RCM_MO_NC consecutive cells along the
+// advection direction: the NC+1 face fluxes are evaluated once each (the one-cell kernels above evaluate
+// every face twice, once from either side), and the 4-point stencils of neighbouring cells share loads.
+#define RCM_MO_NC 4
+__global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_wafy4(const Geom g, const MoFields f, const MoScalars s) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i0 = g.ici1 + (blockIdx.y * blockDim.y + threadIdx.y) * RCM_MO_NC;
+  const int k = 1 + blockIdx.z;
+  if (j > g.jci2 || i0 > g.ici2) return;
+  const int nc = min(RCM_MO_NC, g.ici2 - i0 + 1);
+  const double zdtrdy = s.adtrdy;
+  const int nf = s.nf;
+  double vr[RCM_MO_NC + 1], zamu[RCM_MO_NC + 1], is[RCM_MO_NC + 1];
+  bool up[RCM_MO_NC + 1], cl[RCM_MO_NC + 1];     // upwind side; index clamp (ihm1 at icross1 / ih at icross2)
+#pragma unroll
+  for (int m = 0; m <= RCM_MO_NC; ++m) {
+    const int ii = min(i0 + m, g.ice2);          // faces beyond the last owned cell are not used
+    vr[m] = L3(f.v, j, ii, k) * L2(f.rmv, j, ii);
+    zamu[m] = vr[m] * zdtrdy;
+    up[m] = (zamu[m] > 0.0);                     // ih = ii-1, ihm1 = max(ii-2, icross1)  |  ih = min(ii+1, icross2), ihm1 = ih-1
+    is[m] = up[m] ? 1.0 : -1.0;
+    cl[m] = up[m] ? (ii - 2 < g.icross1) : (ii + 1 > g.icross2);
+  }
+  double fm[RCM_MO_NC + 2];                      // fmz(i0-1 .. i0+NC)
+#pragma unroll
+  for (int m = 0; m < RCM_MO_NC + 2; ++m) fm[m] = L3(f.fmz, j, min(i0 - 1 + m, g.ice2), k);
+  double zrfmn[RCM_MO_NC], zrfms[RCM_MO_NC], dvf[RCM_MO_NC], mx2[RCM_MO_NC];
+#pragma unroll
+  for (int c = 0; c < RCM_MO_NC; ++c) {
+    zrfmn[c] = zdtrdy * 2.0 * fm[c + 1] / (fm[c + 1] + fm[c + 2]);
+    zrfms[c] = zdtrdy * 2.0 * fm[c + 1] / (fm[c + 1] + fm[c]);
+    dvf[c] = (vr[c + 1] * zrfmn[c] - vr[c] * zrfms[c]);
+    mx2[c] = L2(f.mx2, j, min(i0 + c, g.ice2));
+  }
+  const bool cw = (j == g.jci1), ce = (j == g.jci2);
+  for (int n = 0; n < nf; ++n) {
+    const double* wz = f.wz[n];
+    double w[RCM_MO_NC + 4];                     // wz(i0-2 .. i0+NC+1), clamped to the rows that exist
+#pragma unroll
+    for (int m = 0; m < RCM_MO_NC + 4; ++m) w[m] = L3(wz, j, min(max(i0 - 2 + m, g.ice1), g.ice2), k);
+    double zpby[RCM_MO_NC + 1];
+#pragma unroll
+    for (int m = 0; m <= RCM_MO_NC; ++m) {
+      const double wc = w[m + 2], wm = w[m + 1];
+      // upstream pair from the register window: w[q] holds row i0-2+q, face m sits between q = m+1 and m+2
+      const double wh = up[m] ? wm : (cl[m] ? wc : w[m + 3]);
+      const double whm1 = up[m] ? (cl[m] ? wm : w[m]) : (cl[m] ? wm : wc);
+      const double r = mo_rdeno(wh, whm1, wc, wm);
+      const double zphi = mo_phi(r, is[m], zamu[m]);
+      zpby[m] = 0.5 * vr[m] * ((1.0 + zphi) * wm + (1.0 - zphi) * wc);
+    }
+    double* p0 = f.p0[n];
+    const double* pp = f.adv[n];
+#pragma unroll
+    for (int c = 0; c < RCM_MO_NC; ++c) {
+      if (c < nc) {
+        const int i = i0 + c;
+        const double zdv = dvf[c] * L3(pp, j, i, k);
+        const double out = w[c + 2] + mx2[c] * (zpby[c] * zrfms[c] - zpby[c + 1] * zrfmn[c] + zdv);
+        P3(p0, j, i, k) = out;
+        if (cw) P3(p0, g.jce1, i, k) = out;
+        if (ce) P3(p0, g.jce2, i, k) = out;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_wafx4(const Geom g, const MoFields f, const MoScalars s) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j0 = g.jci1 + (blockIdx.x * blockDim.x + threadIdx.x) * RCM_MO_NC;
+  const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = 1 + blockIdx.z;
+  if (j0 > g.jci2 || i > g.ici2) return;
+  const int nc = min(RCM_MO_NC, g.jci2 - j0 + 1);
+  const double zdtrdx = s.adtrdx;
+  const int nf = s.nf;
+  double ur[RCM_MO_NC + 1], zamu[RCM_MO_NC + 1], is[RCM_MO_NC + 1];
+  bool up[RCM_MO_NC + 1], cl[RCM_MO_NC + 1];
+#pragma unroll
+  for (int m = 0; m <= RCM_MO_NC; ++m) {
+    const int jj = min(j0 + m, g.jce2);
+    ur[m] = L3(f.u, jj, i, k) * L2(f.rmu, jj, i);
+    zamu[m] = ur[m] * zdtrdx;
+    up[m] = (zamu[m] > 0.0);
+    is[m] = up[m] ? 1.0 : -1.0;
+    cl[m] = up[m] ? (jj - 2 < g.jcross1) : (jj + 1 > g.jcross2);
+  }
+  double fm[RCM_MO_NC + 2];
+#pragma unroll
+  for (int m = 0; m < RCM_MO_NC + 2; ++m) fm[m] = L3(f.fmz, min(j0 - 1 + m, g.jce2), i, k);
+  double zrfme[RCM_MO_NC], zrfmw[RCM_MO_NC], dvf[RCM_MO_NC], mx2[RCM_MO_NC];
+#pragma unroll
+  for (int c = 0; c < RCM_MO_NC; ++c) {
+    zrfme[c] = zdtrdx * 2.0 * fm[c + 1] / (fm[c + 1] + fm[c + 2]);
+    zrfmw[c] = zdtrdx * 2.0 * fm[c + 1] / (fm[c + 1] + fm[c]);
+    dvf[c] = (ur[c + 1] * zrfme[c] - ur[c] * zrfmw[c]);
+    mx2[c] = L2(f.mx2, min(j0 + c, g.jce2), i);
+  }
+  for (int n = 0; n < nf; ++n) {
+    const double* p0 = f.p0[n];
+    double w[RCM_MO_NC + 4];
+#pragma unroll
+    for (int m = 0; m < RCM_MO_NC + 4; ++m) w[m] = L3(p0, min(max(j0 - 2 + m, g.jce1), g.jce2), i, k);
+    double zpbw[RCM_MO_NC + 1];
+#pragma unroll
+    for (int m = 0; m <= RCM_MO_NC; ++m) {
+      const double pc = w[m + 2], pm = w[m + 1];
+      const double ph = up[m] ? pm : (cl[m] ? pc : w[m + 3]);
+      const double phm1 = up[m] ? (cl[m] ? pm : w[m]) : (cl[m] ? pm : pc);
+      const double r = mo_rdeno(ph, phm1, pc, pm);
+      const double zphi = mo_phi(r, is[m], zamu[m]);
+      zpbw[m] = 0.5 * ur[m] * ((1.0 + zphi) * pm + (1.0 - zphi) * pc);
+    }
+    double* pp = f.adv[n];
+#pragma unroll
+    for (int c = 0; c < RCM_MO_NC; ++c) {
+      if (c < nc) {
+        const int j = j0 + c;
+        const double zdv = dvf[c] * P3(pp, j, i, k);
+        P3(pp, j, i, k) = w[c + 2] + mx2[c] * (zpbw[c] * zrfmw[c] - zpbw[c + 1] * zrfme[c] + zdv);
+      }
+    }
+  }
+}
+
 __global__ void k_mo_restag(const Geom g, const MoFields f) {
   const int si = g.si; const long long sk = g.sk;
   const int j = g.jde1 + blockIdx.x * blockDim.x + threadIdx.x;
@@ -214,9 +354,15 @@ void launch_mo_destag(const Geom& g, const MoFields& f, cudaStream_t st) {
 void launch_mo_waf(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
   dim3 bc = col_block(), b(32, 4);
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
-  RCM_LAUNCH(k_mo_wafz, grid3(nj, ni, 1, bc), bc, st, g, f, s);
-  RCM_LAUNCH(k_mo_wafy, grid3(nj, ni, g.kz, b), b, st, g, f, s);
-  RCM_LAUNCH(k_mo_wafx, grid3(nj, ni, g.kz, b), b, st, g, f, s);
+  if (s.nf == 7) RCM_LAUNCH(k_mo_wafz<7>, grid3(nj, ni, 1, bc), bc, st, g, f, s);
+  else RCM_LAUNCH(k_mo_wafz<6>, grid3(nj, ni, 1, bc), bc, st, g, f, s);
+  // RCM_MO_WAF: bit 0 = one-cell meridional kernel, bit 1 = one-cell zonal kernel (tuning switch; default: 4-cell kernels)
+  static int mode = -1;
+  if (mode < 0) { const char* e = std::getenv("RCM_MO_WAF"); mode = e ? std::atoi(e) : 2; }
+  if (mode & 1) RCM_LAUNCH(k_mo_wafy, grid3(nj, ni, g.kz, b), b, st, g, f, s);
+  else RCM_LAUNCH(k_mo_wafy4, grid3(nj, (ni + RCM_MO_NC - 1) / RCM_MO_NC, g.kz, b), b, st, g, f, s);
+  if (mode & 2) RCM_LAUNCH(k_mo_wafx, grid3(nj, ni, g.kz, b), b, st, g, f, s);
+  else RCM_LAUNCH(k_mo_wafx4, grid3((nj + RCM_MO_NC - 1) / RCM_MO_NC, ni, g.kz, b), b, st, g, f, s);
 }
 void launch_mo_restag(const Geom& g, const MoFields& f, cudaStream_t st) {
   dim3 b(32, 4);

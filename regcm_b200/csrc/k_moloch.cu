@@ -47,9 +47,36 @@ __device__ __forceinline__ double mo_zd(const MoFields& f, const int si, const l
   return c + anu2 * p2d;
 }
 
+// Inputs of one level of the downward sweep.  They do not depend on the recurrence, so the loads of
+// level k-1 are issued before the stores of level k (software pipelining by hand: the compiler cannot
+// move them across the stores itself because the arrays may alias).
+struct MoWIn {
+  double um0, um1, vm0, vm1;   // winds of level k-2 (for s(k-1))
+  double gz;                   // gzitak(k-1)
+  double fmz_km1, zd_km1, pai_km1, tet_km1, fmzf_k, w_k, ff;
+};
+__device__ __forceinline__ MoWIn mo_w_load(const Geom& g, const MoFields& f, const double anu2, const bool interior,
+                                           const int si, const long long sk, const int j, const int i, const int k) {
+  MoWIn r;
+  if (k - 1 >= 2) {
+    r.um0 = L3(f.u, j, i, k - 2); r.um1 = L3(f.u, j + 1, i, k - 2); r.vm0 = L3(f.v, j, i, k - 2); r.vm1 = L3(f.v, j, i + 1, k - 2);
+    r.gz = LD1(f.gzitak + k - 1);
+  } else {
+    r.um0 = r.um1 = r.vm0 = r.vm1 = 0.0; r.gz = 0.0;
+  }
+  r.fmz_km1 = L3(f.fmz, j, i, k - 1);
+  r.zd_km1 = mo_zd(f, si, sk, interior, anu2, j, i, k - 1);
+  r.pai_km1 = P3(f.pai, j, i, k - 1);
+  r.tet_km1 = L3(f.tetav, j, i, k - 1);
+  r.fmzf_k = L3(f.fmzf, j, i, k);
+  r.w_k = P3(f.w, j, i, k);
+  r.ff = LD1(f.ffilt + k);
+  return r;
+}
+
 // `zdf` receives the full divergence (a second array: the raw one is still being read by the
 // neighbours' filter); `jsound` is the 1-based sub-step index; `last`: write s (Eq. 10 completed).
-__global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_w(const Geom g, const MoFields f, const MoScalars s, double* zdf,
+__global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_w(const Geom g, const MoFields f, const MoScalars s, double* zdf,
                                                       const int jsound, const int last) {
   const int si = g.si; const long long sk = g.sk;
   const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
@@ -62,6 +89,11 @@ __global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_w(const Geom g, const MoFiel
   const double zdtrdz = s.zdtrdz, zcs2 = s.zcs2, egdts = s.egdts, rjs = (double)jsound;
   // winds of level k (carried) and k-1
   double u0 = L3(f.u, j, i, kz), u1 = L3(f.u, j + 1, i, kz), v0 = L3(f.v, j, i, kz), v1 = L3(f.v, j, i + 1, kz);
+  double um0 = L3(f.u, j, i, kz - 1), um1 = L3(f.u, j + 1, i, kz - 1), vm0 = L3(f.v, j, i, kz - 1), vm1 = L3(f.v, j, i + 1, kz - 1);
+  MoWIn cur = mo_w_load(g, f, s.anu2, interior, si, sk, j, i, kz);
+  double fmz_k = L3(f.fmz, j, i, kz);
+  const double zd_kz = mo_zd(f, si, sk, interior, s.anu2, j, i, kz);
+  double pai_k = P3(f.pai, j, i, kz), tet_k = L3(f.tetav, j, i, kz);
   double wkp1;  // w(k+1) of the downward sweep
   {
     const double zuh = u0 * hx0 + u1 * hx1, zvh = v0 * hy0 + v1 * hy1;
@@ -70,39 +102,37 @@ __global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_w(const Geom g, const MoFiel
   }
   double s_kp1 = -wkp1;
   if (last) P3(f.s, j, i, kzp1) = interior ? 0.0 : s_kp1;
-  // s(kz), zdiv(kz)
-  double um0 = L3(f.u, j, i, kz - 1), um1 = L3(f.u, j + 1, i, kz - 1), vm0 = L3(f.v, j, i, kz - 1), vm1 = L3(f.v, j, i + 1, kz - 1);
   double s_k;
   {
     const double zuh = (u0 + um0) * hx0 + (u1 + um1) * hx1, zvh = (v0 + vm0) * hy0 + (v1 + vm1) * hy1;
     s_k = -0.25 * (zuh + zvh) * LD1(f.gzitak + kz);
   }
-  double fmz_k = L3(f.fmz, j, i, kz);
-  double zdiv_k = fmz_k * (mx2 * mo_zd(f, si, sk, interior, s.anu2, j, i, kz) + zdtrdz * (s_k - s_kp1));
+  double zdiv_k = fmz_k * (mx2 * zd_kz + zdtrdz * (s_k - s_kp1));
   P3(zdf, j, i, kz) = zdiv_k;
-  double pai_k = P3(f.pai, j, i, kz), tet_k = L3(f.tetav, j, i, kz);
   double wwkw_kp1 = 0.0;
   for (int k = kz; k >= 2; --k) {
+    MoWIn nxt = cur;
+    if (k > 2) nxt = mo_w_load(g, f, s.anu2, interior, si, sk, j, i, k - 1);
     // level k-1 quantities: s(k-1) (0 for k-1 = 1), zdiv(k-1)
     u0 = um0; u1 = um1; v0 = vm0; v1 = vm1;
     double s_km1 = 0.0;
     if (k - 1 >= 2) {
-      um0 = L3(f.u, j, i, k - 2); um1 = L3(f.u, j + 1, i, k - 2); vm0 = L3(f.v, j, i, k - 2); vm1 = L3(f.v, j, i + 1, k - 2);
+      um0 = cur.um0; um1 = cur.um1; vm0 = cur.vm0; vm1 = cur.vm1;
       const double zuh = (u0 + um0) * hx0 + (u1 + um1) * hx1, zvh = (v0 + vm0) * hy0 + (v1 + vm1) * hy1;
-      s_km1 = -0.25 * (zuh + zvh) * LD1(f.gzitak + k - 1);
+      s_km1 = -0.25 * (zuh + zvh) * cur.gz;
     }
-    const double fmz_km1 = L3(f.fmz, j, i, k - 1);
-    const double zdiv_km1 = fmz_km1 * (mx2 * mo_zd(f, si, sk, interior, s.anu2, j, i, k - 1) + zdtrdz * (s_km1 - s_k));
+    const double fmz_km1 = cur.fmz_km1;
+    const double zdiv_km1 = fmz_km1 * (mx2 * cur.zd_km1 + zdtrdz * (s_km1 - s_k));
     P3(zdf, j, i, k - 1) = zdiv_km1;
-    const double pai_km1 = P3(f.pai, j, i, k - 1), tet_km1 = L3(f.tetav, j, i, k - 1);
-    const double fmzf_k = L3(f.fmzf, j, i, k);
-    const double w_k = P3(f.w, j, i, k);
+    const double pai_km1 = cur.pai_km1, tet_km1 = cur.tet_km1;
+    const double fmzf_k = cur.fmzf_k;
+    const double w_k = cur.w_k;
     P3(f.deltaw, j, i, k) = -w_k;
     double zrom1w = 0.5 * cpd * fmzf_k * (tet_km1 + tet_k);
     zrom1w = zrom1w - cpd * w_k * (fmzf_k * fmzf_k) * rjs * zdtrdz * (tet_km1 - tet_k);
     double zwexpl = w_k - zrom1w * zdtrdz * (pai_km1 - pai_k) - egdts;
     zwexpl = zwexpl + rdrcv * zrom1w * zdtrdz * (pai_km1 * zdiv_km1 - pai_k * zdiv_k);
-    const double ff = LD1(f.ffilt + k);
+    const double ff = cur.ff;
     const double zp = zcs2 * fmz_km1 * zrom1w * pai_km1 + ff;
     const double zm = zcs2 * fmz_k * zrom1w * pai_k + ff;
     const double zrapp = 1.0 / (1.0 + zm + zp - zm * wwkw_kp1);
@@ -113,23 +143,40 @@ __global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_w(const Geom g, const MoFiel
     if (last) P3(f.s, j, i, k) = s_k;
     wkp1 = wn;
     s_k = s_km1; zdiv_k = zdiv_km1; fmz_k = fmz_km1; pai_k = pai_km1; tet_k = tet_km1;
+    cur = nxt;
   }
-  // 2nd loop of the tridiagonal inversion, new Exner function, completed s
+  // 2nd loop of the tridiagonal inversion, new Exner function, completed s; the operands of level
+  // k+1 are loaded before the stores of level k
   double w_km1 = P3(f.w, j, i, 1);
+  double a_w = P3(f.w, j, i, 2), a_ww = P3(f.wwkw, j, i, 2), a_dw = P3(f.deltaw, j, i, 2);
+  double a_zd = 0.0, a_fmz = 0.0, a_pai = 0.0, a_s = 0.0, a_fzf = 0.0;
+  if (interior) {
+    a_zd = P3(zdf, j, i, 1); a_fmz = L3(f.fmz, j, i, 1); a_pai = P3(f.pai, j, i, 1);
+    if (last) { a_s = P3(f.s, j, i, 2); a_fzf = L3(f.fmzf, j, i, 2); }
+  }
   for (int k = 2; k <= kz; ++k) {
-    const double wk = P3(f.w, j, i, k) + P3(f.wwkw, j, i, k) * w_km1;
+    double b_w = 0.0, b_ww = 0.0, b_dw = 0.0, b_zd = 0.0, b_fmz = 0.0, b_pai = 0.0, b_s = 0.0, b_fzf = 0.0;
+    if (k < kz) {
+      b_w = P3(f.w, j, i, k + 1); b_ww = P3(f.wwkw, j, i, k + 1); b_dw = P3(f.deltaw, j, i, k + 1);
+    }
+    if (interior) {   // level k (the Exner function is updated one level behind w); for k = kz these feed the tail
+      b_zd = P3(zdf, j, i, k); b_fmz = L3(f.fmz, j, i, k); b_pai = P3(f.pai, j, i, k);
+      if (last && k < kz) { b_s = P3(f.s, j, i, k + 1); b_fzf = L3(f.fmzf, j, i, k + 1); }
+    }
+    const double wk = a_w + a_ww * w_km1;
     P3(f.w, j, i, k) = wk;
-    P3(f.deltaw, j, i, k) = P3(f.deltaw, j, i, k) + wk;
+    P3(f.deltaw, j, i, k) = a_dw + wk;
     if (interior) {
-      const double zd = P3(zdf, j, i, k - 1) + zdtrdz * L3(f.fmz, j, i, k - 1) * (w_km1 - wk);
-      P3(f.pai, j, i, k - 1) = P3(f.pai, j, i, k - 1) * (1.0 - rdrcv * zd);
-      if (last) P3(f.s, j, i, k) = (wk + P3(f.s, j, i, k)) * L3(f.fmzf, j, i, k);
+      const double zd = a_zd + zdtrdz * a_fmz * (w_km1 - wk);
+      P3(f.pai, j, i, k - 1) = a_pai * (1.0 - rdrcv * zd);
+      if (last) P3(f.s, j, i, k) = (wk + a_s) * a_fzf;
     }
     w_km1 = wk;
+    a_w = b_w; a_ww = b_ww; a_dw = b_dw; a_zd = b_zd; a_fmz = b_fmz; a_pai = b_pai; a_s = b_s; a_fzf = b_fzf;
   }
   if (interior) {
-    const double zd = P3(zdf, j, i, kz) + zdtrdz * L3(f.fmz, j, i, kz) * (w_km1 - P3(f.w, j, i, kzp1));
-    P3(f.pai, j, i, kz) = P3(f.pai, j, i, kz) * (1.0 - rdrcv * zd);
+    const double zd = a_zd + zdtrdz * a_fmz * (w_km1 - P3(f.w, j, i, kzp1));
+    P3(f.pai, j, i, kz) = a_pai * (1.0 - rdrcv * zd);
     if (last) P3(f.s, j, i, 1) = 0.0;
   }
 }
