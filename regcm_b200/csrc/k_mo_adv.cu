@@ -12,12 +12,16 @@
 
 using namespace rcm;
 
+// min/max with the selection rule of the reference's host compilers for ordinary numbers
+// ((a < b) ? b : a): a compare and two selects instead of the NaN-propagating fmin/fmax sequences
+__device__ __forceinline__ double mo_max(const double a, const double b) { return (a < b) ? b : a; }
+__device__ __forceinline__ double mo_min(const double a, const double b) { return (b < a) ? b : a; }
 __device__ __forceinline__ double mo_rdeno(const double t1, const double t2, const double t3, const double t4) {
   const double zzden = (t3 - t4);
-  return (t1 - t2) / copysign(fmax(fabs(zzden), 1.0e-15), zzden);
+  return (t1 - t2) / copysign(mo_max(fabs(zzden), 1.0e-15), zzden);
 }
 __device__ __forceinline__ double mo_phi(const double r, const double is, const double zamu) {
-  const double b = fmax(0.0, fmin(2.0, fmax(r, fmin(2.0 * r, 1.0))));
+  const double b = mo_max(0.0, mo_min(2.0, mo_max(r, mo_min(2.0 * r, 1.0))));
   return is + zamu * b - is * b;
 }
 
@@ -107,88 +111,68 @@ __global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_wafz(const Geom g, const MoF
   }
 }
 
-// meridional pass
-__global__ void k_mo_wafy(const Geom g, const MoFields f, const MoScalars s) {
+// One horizontal pass (DIR 0: meridional, wz -> p0; DIR 1: zonal, p0 -> the field itself, in place: each
+// thread reads only its own point of it).  The upwind choice, the face velocities, the metric ratios and
+// all element offsets are field-independent and computed once; the field loop is unrolled (NF is a
+// template parameter) so that the per-field work is loads at precomputed offsets plus the limiter.
+template <int NF, int DIR>
+__global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_wafh(const Geom g, const MoFields f, const MoScalars s) {
   const int si = g.si; const long long sk = g.sk;
   const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
   const int k = 1 + blockIdx.z;
   if (j > g.jci2 || i > g.ici2) return;
-  const double zdtrdy = s.adtrdy;
-  const int nf = s.nf;
-  // the two faces i (south) and i+1 (north)
+  const long long st = DIR ? 1 : (long long)si;              // element stride along the advection direction
+  const long long o = (long long)j + (long long)i * si + (long long)k * sk;
+  const int c = DIR ? j : i, c1 = DIR ? g.jcross1 : g.icross1, c2 = DIR ? g.jcross2 : g.icross2;
+  const double zdtrd = DIR ? s.adtrdx : s.adtrdy;
+  const double* vel = DIR ? f.u : f.v;
+  const double* rm = DIR ? f.rmu : f.rmv;
+  const long long o2 = (long long)j + (long long)i * si;
+  // the two faces c (low side) and c+1 (high side)
   double vr[2], zamu[2], is[2];
-  int ih[2], ihm1[2];
+  long long oh[2], ohm1[2];
+#pragma unroll
   for (int m = 0; m < 2; ++m) {
-    const int ii = i + m;
-    vr[m] = L3(f.v, j, ii, k) * L2(f.rmv, j, ii);
-    zamu[m] = vr[m] * zdtrdy;
-    if (zamu[m] > 0.0) { is[m] = 1.0; ih[m] = ii - 1; }
-    else { is[m] = -1.0; ih[m] = min(ii + 1, g.icross2); }
-    ihm1[m] = max(ih[m] - 1, g.icross1);
+    const int cc = c + m;
+    vr[m] = LD1(vel + o + m * st) * LD1(rm + o2 + m * st);
+    zamu[m] = vr[m] * zdtrd;
+    int ch;
+    if (zamu[m] > 0.0) { is[m] = 1.0; ch = cc - 1; }
+    else { is[m] = -1.0; ch = min(cc + 1, c2); }
+    const int chm1 = max(ch - 1, c1);
+    oh[m] = o + (long long)(ch - c) * st; ohm1[m] = o + (long long)(chm1 - c) * st;
   }
-  const double fmz = L3(f.fmz, j, i, k);
-  const double zrfmn = zdtrdy * 2.0 * fmz / (fmz + L3(f.fmz, j, i + 1, k));
-  const double zrfms = zdtrdy * 2.0 * fmz / (fmz + L3(f.fmz, j, i - 1, k));
-  const double mx2 = L2(f.mx2, j, i);
-  const double dvf = (vr[1] * zrfmn - vr[0] * zrfms);
-  const bool cw = (j == g.jci1), ce = (j == g.jci2);
-  for (int n = 0; n < nf; ++n) {
-    const double* wz = f.wz[n];
-    double zpby[2];
+  const double fmz = LD1(f.fmz + o);
+  const double zrfhi = zdtrd * 2.0 * fmz / (fmz + LD1(f.fmz + o + st));   // zrfmn / zrfme
+  const double zrflo = zdtrd * 2.0 * fmz / (fmz + LD1(f.fmz + o - st));   // zrfms / zrfmw
+  const double mx2 = LD1(f.mx2 + o2);
+  const double dvf = (vr[1] * zrfhi - vr[0] * zrflo);
+  const bool cw = (!DIR) && (j == g.jci1), ce = (!DIR) && (j == g.jci2);
+  const long long ow = (long long)g.jce1 + (long long)i * si + (long long)k * sk, oe = ow + (g.jce2 - g.jce1);
+#pragma unroll
+  for (int n = 0; n < NF; ++n) {
+    const double* src = DIR ? f.p0[n] : f.wz[n];
+    const double wm0 = LD1(src + o - st), wc0 = LD1(src + o), wc1 = LD1(src + o + st);
+    double flux[2];
+#pragma unroll
     for (int m = 0; m < 2; ++m) {
-      const int ii = i + m;
-      const double wc = L3(wz, j, ii, k), wm = L3(wz, j, ii - 1, k);
-      const double r = mo_rdeno(L3(wz, j, ih[m], k), L3(wz, j, ihm1[m], k), wc, wm);
+      const double wc = m ? wc1 : wc0, wm = m ? wc0 : wm0;
+      const double r = mo_rdeno(LD1(src + oh[m]), LD1(src + ohm1[m]), wc, wm);
       const double zphi = mo_phi(r, is[m], zamu[m]);
-      zpby[m] = 0.5 * vr[m] * ((1.0 + zphi) * wm + (1.0 - zphi) * wc);
-    }
-    const double zdv = dvf * L3(f.adv[n], j, i, k);
-    const double out = L3(wz, j, i, k) + mx2 * (zpby[0] * zrfms - zpby[1] * zrfmn + zdv);
-    double* p0 = f.p0[n];
-    P3(p0, j, i, k) = out;
-    if (cw) P3(p0, g.jce1, i, k) = out;
-    if (ce) P3(p0, g.jce2, i, k) = out;
-  }
-}
-
-// zonal pass; writes the advected field in place (each thread reads only its own point of it)
-__global__ void k_mo_wafx(const Geom g, const MoFields f, const MoScalars s) {
-  const int si = g.si; const long long sk = g.sk;
-  const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = 1 + blockIdx.z;
-  if (j > g.jci2 || i > g.ici2) return;
-  const double zdtrdx = s.adtrdx;
-  const int nf = s.nf;
-  double ur[2], zamu[2], is[2];
-  int jh[2], jhm1[2];
-  for (int m = 0; m < 2; ++m) {
-    const int jj = j + m;
-    ur[m] = L3(f.u, jj, i, k) * L2(f.rmu, jj, i);
-    zamu[m] = ur[m] * zdtrdx;
-    if (zamu[m] > 0.0) { is[m] = 1.0; jh[m] = jj - 1; }
-    else { is[m] = -1.0; jh[m] = min(jj + 1, g.jcross2); }
-    jhm1[m] = max(jh[m] - 1, g.jcross1);
-  }
-  const double fmz = L3(f.fmz, j, i, k);
-  const double zrfme = zdtrdx * 2.0 * fmz / (fmz + L3(f.fmz, j + 1, i, k));
-  const double zrfmw = zdtrdx * 2.0 * fmz / (fmz + L3(f.fmz, j - 1, i, k));
-  const double mx2 = L2(f.mx2, j, i);
-  const double dvf = (ur[1] * zrfme - ur[0] * zrfmw);
-  for (int n = 0; n < nf; ++n) {
-    const double* p0 = f.p0[n];
-    double zpbw[2];
-    for (int m = 0; m < 2; ++m) {
-      const int jj = j + m;
-      const double pc = L3(p0, jj, i, k), pm = L3(p0, jj - 1, i, k);
-      const double r = mo_rdeno(L3(p0, jh[m], i, k), L3(p0, jhm1[m], i, k), pc, pm);
-      const double zphi = mo_phi(r, is[m], zamu[m]);
-      zpbw[m] = 0.5 * ur[m] * ((1.0 + zphi) * pm + (1.0 - zphi) * pc);
+      flux[m] = 0.5 * vr[m] * ((1.0 + zphi) * wm + (1.0 - zphi) * wc);
     }
     double* pp = f.adv[n];
-    const double zdv = dvf * P3(pp, j, i, k);
-    P3(pp, j, i, k) = L3(p0, j, i, k) + mx2 * (zpbw[0] * zrfmw - zpbw[1] * zrfme + zdv);
+    const double zdv = dvf * pp[o];
+    const double out = wc0 + mx2 * (flux[0] * zrflo - flux[1] * zrfhi + zdv);
+    if (DIR) {
+      pp[o] = out;
+    } else {
+      double* p0 = f.p0[n];
+      p0[o] = out;
+      if (cw) p0[ow] = out;
+      if (ce) p0[oe] = out;
+    }
   }
 }
 
@@ -356,13 +340,17 @@ void launch_mo_waf(const Geom& g, const MoFields& f, const MoScalars& s, cudaStr
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
   if (s.nf == 7) RCM_LAUNCH(k_mo_wafz<7>, grid3(nj, ni, 1, bc), bc, st, g, f, s);
   else RCM_LAUNCH(k_mo_wafz<6>, grid3(nj, ni, 1, bc), bc, st, g, f, s);
-  // RCM_MO_WAF: bit 0 = one-cell meridional kernel, bit 1 = one-cell zonal kernel (tuning switch; default: 4-cell kernels)
+  // RCM_MO_WAF: bit 0 = one-cell meridional kernel, bit 1 = one-cell zonal kernel (default 3: measured faster on B200 than the 4-cell kernels, profiles/r1_moloch.md)
   static int mode = -1;
-  if (mode < 0) { const char* e = std::getenv("RCM_MO_WAF"); mode = e ? std::atoi(e) : 2; }
-  if (mode & 1) RCM_LAUNCH(k_mo_wafy, grid3(nj, ni, g.kz, b), b, st, g, f, s);
-  else RCM_LAUNCH(k_mo_wafy4, grid3(nj, (ni + RCM_MO_NC - 1) / RCM_MO_NC, g.kz, b), b, st, g, f, s);
-  if (mode & 2) RCM_LAUNCH(k_mo_wafx, grid3(nj, ni, g.kz, b), b, st, g, f, s);
-  else RCM_LAUNCH(k_mo_wafx4, grid3((nj + RCM_MO_NC - 1) / RCM_MO_NC, ni, g.kz, b), b, st, g, f, s);
+  if (mode < 0) { const char* e = std::getenv("RCM_MO_WAF"); mode = e ? std::atoi(e) : 3; }
+  if (mode & 1) {
+    if (s.nf == 7) RCM_LAUNCH((k_mo_wafh<7, 0>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+    else RCM_LAUNCH((k_mo_wafh<6, 0>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+  } else RCM_LAUNCH(k_mo_wafy4, grid3(nj, (ni + RCM_MO_NC - 1) / RCM_MO_NC, g.kz, b), b, st, g, f, s);
+  if (mode & 2) {
+    if (s.nf == 7) RCM_LAUNCH((k_mo_wafh<7, 1>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+    else RCM_LAUNCH((k_mo_wafh<6, 1>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+  } else RCM_LAUNCH(k_mo_wafx4, grid3((nj + RCM_MO_NC - 1) / RCM_MO_NC, ni, g.kz, b), b, st, g, f, s);
 }
 void launch_mo_restag(const Geom& g, const MoFields& f, cudaStream_t st) {
   dim3 b(32, 4);

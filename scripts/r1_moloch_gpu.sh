@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,driver_version --format=csv,noheader > gpurun_out/mo_gpu.txt 2>&1
 ( time timeout 420 python -m pytest tests/test_gpu_moloch.py -x -q ) > gpurun_out/mo_pytest.log 2>&1; echo "rc=$?" >> gpurun_out/mo_pytest.log; tail -6 gpurun_out/mo_pytest.log
-timeout 300 python bench.py --workload C5 --steps 10 --warmup 3 > gpurun_out/mo_bench_c5.json 2> gpurun_out/mo_bench_c5.err; echo "c5 rc=$?"; tail -3 gpurun_out/mo_bench_c5.err
+timeout 300 python bench.py --workload C5 --steps 20 --warmup 3 > gpurun_out/mo_bench_c5.json 2> gpurun_out/mo_bench_c5.err; echo "c5 rc=$?"; tail -3 gpurun_out/mo_bench_c5.err
 timeout 120 python bench.py --workload smallm --steps 50 --warmup 3 --no-cpu > gpurun_out/mo_bench_small.json 2> gpurun_out/mo_bench_small.err; echo "small rc=$?"
 timeout 150 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/mo_smoke.log 2>&1; tail -3 gpurun_out/mo_smoke.log
 timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/mo_launches_c5q.csv python bench.py --workload C5q --steps 1 --warmup 3 --no-e2e --no-cpu > gpurun_out/mo_ncu_c5q.log 2>&1; echo "ncu list rc=$?"
