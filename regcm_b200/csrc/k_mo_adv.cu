@@ -49,11 +49,11 @@ __global__ void k_mo_destag(const Geom g, const MoFields f) {
   P3(f.wx, j, i, k) = wx;
 }
 
-// vertical pass: one thread per interior column marches k once for all NF fields; the 4-level window
-// pp(k-1..k+2) of every field lives in registers, the interface velocity and the metric ratios are
-// evaluated once per level
+// vertical pass: one thread marches k once for a group of up to NF fields of one interior column
+// (blockIdx.z selects the group: fields z*NF .. z*NF+NF-1); the 4-level window pp(k-1..k+2) of every
+// field lives in registers, the interface velocity and the metric ratios are evaluated once per level
 template <int NF>
-__global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_wafz(const Geom g, const MoFields f, const MoScalars s) {
+__global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_wafz(const Geom g, const MoFields f, const MoScalars s) {
   const int si = g.si; const long long sk = g.sk;
   const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
@@ -61,18 +61,22 @@ __global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_wafz(const Geom g, const MoF
   const int kz = g.kz;
   const double zdtrdz = s.adtrdz;
   const bool rs = (i == g.ici1), rn = (i == g.ici2);
+  const int n0 = blockIdx.z * NF;
+  const double* adv[NF]; double* wzp[NF];
+#pragma unroll
+  for (int n = 0; n < NF; ++n) { const int q = min(n0 + n, s.nf - 1); adv[n] = f.adv[q]; wzp[n] = f.wz[q]; }   // a short last group repeats its last field
   double pkm1[NF], pk[NF], pkp1[NF], wfw_k[NF];
 #pragma unroll
   for (int n = 0; n < NF; ++n) {
     pkm1[n] = 0.0; wfw_k[n] = 0.0;
-    pk[n] = L3(f.adv[n], j, i, 1); pkp1[n] = L3(f.adv[n], j, i, 2);
+    pk[n] = L3(adv[n], j, i, 1); pkp1[n] = L3(adv[n], j, i, 2);
   }
   double s_k = 0.0;
   double fmzf_k = 0.0;   // fmzf(k); not used for k = 1
   for (int k = 1; k <= kz; ++k) {
     double pkp2[NF];
 #pragma unroll
-    for (int n = 0; n < NF; ++n) pkp2[n] = (k + 2 <= kz) ? L3(f.adv[n], j, i, k + 2) : 0.0;
+    for (int n = 0; n < NF; ++n) pkp2[n] = (k + 2 <= kz) ? L3(adv[n], j, i, k + 2) : 0.0;
     const double s_kp1 = (k <= kz - 1) ? L3(f.s, j, i, k + 1) : 0.0;
     const double fmz = L3(f.fmz, j, i, k);
     const double fmzf_kp1 = L3(f.fmzf, j, i, k + 1);
@@ -100,7 +104,7 @@ __global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_wafz(const Geom g, const MoF
         const double zdv = (s_k * zrfmp - s_kp1 * zrfmm) * pk[n];
         out = pk[n] - wfw_k[n] * zrfmp + wfw_kp1 * zrfmm + zdv;
       }
-      double* wz = f.wz[n];
+      double* wz = wzp[n];
       P3(wz, j, i, k) = out;
       if (rs) P3(wz, j, g.ice1, k) = out;
       if (rn) P3(wz, j, g.ice2, k) = out;
@@ -338,8 +342,13 @@ void launch_mo_destag(const Geom& g, const MoFields& f, cudaStream_t st) {
 void launch_mo_waf(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
   dim3 bc = col_block(), b(32, 4);
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
-  if (s.nf == 7) RCM_LAUNCH(k_mo_wafz<7>, grid3(nj, ni, 1, bc), bc, st, g, f, s);
-  else RCM_LAUNCH(k_mo_wafz<6>, grid3(nj, ni, 1, bc), bc, st, g, f, s);
+  // RCM_MO_WAFZ = fields per thread of the vertical pass (default 4: two thread groups per column)
+  static int zg = -1;
+  if (zg < 0) { const char* e = std::getenv("RCM_MO_WAFZ"); zg = e ? std::atoi(e) : 4; }
+  if (zg >= 7) RCM_LAUNCH(k_mo_wafz<7>, grid3(nj, ni, 1, bc), bc, st, g, f, s);
+  else if (zg == 2) RCM_LAUNCH(k_mo_wafz<2>, grid3(nj, ni, (s.nf + 1) / 2, bc), bc, st, g, f, s);
+  else if (zg == 3) RCM_LAUNCH(k_mo_wafz<3>, grid3(nj, ni, (s.nf + 2) / 3, bc), bc, st, g, f, s);
+  else RCM_LAUNCH(k_mo_wafz<4>, grid3(nj, ni, (s.nf + 3) / 4, bc), bc, st, g, f, s);
   // RCM_MO_WAF: bit 0 = one-cell meridional kernel, bit 1 = one-cell zonal kernel (default 3: measured faster on B200 than the 4-cell kernels, profiles/r1_moloch.md)
   static int mode = -1;
   if (mode < 0) { const char* e = std::getenv("RCM_MO_WAF"); mode = e ? std::atoi(e) : 3; }
