@@ -342,9 +342,9 @@ void launch_mo_destag(const Geom& g, const MoFields& f, cudaStream_t st) {
 void launch_mo_waf(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
   dim3 bc = col_block(), b(32, 4);
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
-  // RCM_MO_WAFZ = fields per thread of the vertical pass (default 4: two thread groups per column)
+  // RCM_MO_WAFZ = fields per thread of the vertical pass (default 7 = all fields in one thread: measured fastest on B200, gpurun_out/mo_abz_*.json)
   static int zg = -1;
-  if (zg < 0) { const char* e = std::getenv("RCM_MO_WAFZ"); zg = e ? std::atoi(e) : 4; }
+  if (zg < 0) { const char* e = std::getenv("RCM_MO_WAFZ"); zg = e ? std::atoi(e) : 7; }
   if (zg >= 7) RCM_LAUNCH(k_mo_wafz<7>, grid3(nj, ni, 1, bc), bc, st, g, f, s);
   else if (zg == 2) RCM_LAUNCH(k_mo_wafz<2>, grid3(nj, ni, (s.nf + 1) / 2, bc), bc, st, g, f, s);
   else if (zg == 3) RCM_LAUNCH(k_mo_wafz<3>, grid3(nj, ni, (s.nf + 2) / 3, bc), bc, st, g, f, s);
