@@ -1413,8 +1413,11 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
     prof_collect(h);
     if (rc) return rc;
     int nanf = 0;
+    unsigned long long pb[2] = {0, 0};
     CUDA_OK(cudaMemcpy(&nanf, f.nanflag, sizeof(nanf), cudaMemcpyDeviceToHost));
+    CUDA_OK(cudaMemcpy(pb, h->mf.psbits, sizeof(pb), cudaMemcpyDeviceToHost));
     h->nan_flag = nanf;
+    if (nsteps > 0 && pb[0]) { const unsigned long long mn = ~pb[1]; std::memcpy(&h->ps_max, &pb[0], 8); std::memcpy(&h->ps_min, &mn, 8); }
     CUDA_OK(cudaGetLastError());
     if (nanf) return fail(h, RCM_ERR_CFL, "CFL violation: surface pressure is not a number (decrease dt)");   // Main/mod_moloch.F90:443-451
     return RCM_OK;
@@ -1572,15 +1575,8 @@ extern "C" int rcm_dyn_diag(rcm_dyn* h, rcm_diag* d) {
       for (int j = h->g.jci1; j <= h->g.jci2; ++j) { ptn = ptn + H2(a, j, i); pt2 = pt2 + H2(b, j, i); }
     d->ptntot = ptn; d->pt2tot = pt2;
   }
-  if (h->moloch && h->inited) {   // max, min of ps over the interior (Main/mod_moloch.F90:437-441)
-    cudaSetDevice(h->device);
-    std::vector<double> a;
-    int rc;
-    if ((rc = download2(h, h->mf.ps, a))) return rc;
-    double mx = -1e300, mn = 1e300;
-    for (int i = h->g.ici1; i <= h->g.ici2; ++i)
-      for (int j = h->g.jci1; j <= h->g.jci2; ++j) { mx = std::max(mx, H2(a, j, i)); mn = std::min(mn, H2(a, j, i)); }
-    d->ps_max = mx; d->ps_min = mn;
+  if (h->moloch) {   // max, min of ps over the interior of the last step (Main/mod_moloch.F90:437-441), reduced on the device
+    d->ps_max = h->ps_max; d->ps_min = h->ps_min;
   }
   return RCM_OK;
 }

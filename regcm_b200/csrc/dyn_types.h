@@ -137,4 +137,5 @@ struct MoFields {
   int *zone_c, *zone_u, *zone_v;  // bits 0-3: south, north, west, east; bits 8..: ibnd
   double* rimbuf;
   int* nanflag;
+  unsigned long long* psbits;  // [0] max of ps over the interior as ordered bits, [1] complement of the min's bits
 };

@@ -216,27 +216,46 @@ __global__ void k_mo_close(const Geom g, const MoFields f, const MoScalars s) {
   const int si = g.si; const long long sk = g.sk;
   const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
-  if (j > g.jce2 || i > g.ice2) return;
+  const bool inrange = (j <= g.jce2 && i <= g.ice2);
   const bool interior = (j >= g.jci1 && j <= g.jci2 && i >= g.ici1 && i <= g.ici2);
-  double tv = 0.0, pk = 0.0;
-  for (int k = 1; k <= g.kz; ++k) {
-    const double qv = P3(f.qv, j, i, k);
-    const double den = (s.ipptls > 0) ? (1.0 + ep1 * qv - P3(f.qc, j, i, k)) : (1.0 + ep1 * qv);
-    const double pai = P3(f.pai, j, i, k);
-    if (interior) {
-      tv = P3(f.tetav, j, i, k) * pai;
-      P3(f.t, j, i, k) = tv / den;
-    } else {
-      tv = P3(f.t, j, i, k) * den;
+  unsigned long long bmax = 0ULL, bmin = 0ULL;
+  if (inrange) {
+    double tv = 0.0, pk = 0.0;
+    for (int k = 1; k <= g.kz; ++k) {
+      const double qv = P3(f.qv, j, i, k);
+      const double den = (s.ipptls > 0) ? (1.0 + ep1 * qv - P3(f.qc, j, i, k)) : (1.0 + ep1 * qv);
+      const double pai = P3(f.pai, j, i, k);
+      if (interior) {
+        tv = P3(f.tetav, j, i, k) * pai;
+        P3(f.t, j, i, k) = tv / den;
+      } else {
+        tv = P3(f.t, j, i, k) * den;
+      }
+      P3(f.tvirt, j, i, k) = tv;
+      pk = pow(pai, cpovr) * p00;
+      P3(f.p, j, i, k) = pk;
     }
-    P3(f.tvirt, j, i, k) = tv;
-    pk = pow(pai, cpovr) * p00;
-    P3(f.p, j, i, k) = pk;
+    const double zdgz = L2(f.ht, j, i) * s.gzm1 + s.zz1;
+    const double ps = pk * exp(zdgz / (rgas * tv));
+    P2(f.ps, j, i) = ps;
+    if (!(ps == ps)) *f.nanflag = 1;
+    else if (interior && ps > 0.0) {   // positive doubles order like their bit patterns
+      bmax = (unsigned long long)__double_as_longlong(ps);
+      bmin = ~bmax;
+    }
   }
-  const double zdgz = L2(f.ht, j, i) * s.gzm1 + s.zz1;
-  const double ps = pk * exp(zdgz / (rgas * tv));
-  P2(f.ps, j, i) = ps;
-  if (!(ps == ps)) *f.nanflag = 1;
+  // max / min of ps over the interior (Main/mod_moloch.F90:437-441): one atomic pair per warp
+#ifndef RCM_EMU
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long a = __shfl_xor_sync(0xffffffffu, bmax, o), b = __shfl_xor_sync(0xffffffffu, bmin, o);
+    bmax = a > bmax ? a : bmax; bmin = b > bmin ? b : bmin;
+  }
+  if (((threadIdx.x + blockDim.x * threadIdx.y) & 31) != 0) return;
+#endif
+  if (bmax == 0ULL) return;
+  atomicMax(f.psbits, bmax);
+  atomicMax(f.psbits + 1, bmin);
 }
 
 static dim3 grid3(const Geom& g, int nj, int ni, int nk, dim3 b) { return dim3((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y, nk); }
