@@ -76,8 +76,24 @@ __device__ __forceinline__ MoWIn mo_w_load(const Geom& g, const MoFields& f, con
 
 // `zdf` receives the full divergence (a second array: the raw one is still being read by the
 // neighbours' filter); `jsound` is the 1-based sub-step index; `last`: write s (Eq. 10 completed).
-__global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_w(const Geom g, const MoFields f, const MoScalars s, double* zdf,
+//
+// SM = true (GPU only): the three per-level scratch values of the column (intermediate w, elimination
+// coefficient, full divergence) stay in shared memory between the two sweeps instead of making a round
+// trip through HBM: slot (a*(kz+1) + k)*blockThreads + tid of the dynamic shared array, a = 0,1,2.
+#ifdef RCM_EMU
+#define MOW_LD(a, kk, gl) (gl)
+#define MOW_ST(a, kk, gl, v) (gl) = (v)
+#else
+#define MOW_LD(a, kk, gl) (SM ? smw[((a) * kzp1 + (kk)) * nt + tid] : (gl))
+#define MOW_ST(a, kk, gl, v) do { if (SM) smw[((a) * kzp1 + (kk)) * nt + tid] = (v); else (gl) = (v); } while (0)
+#endif
+template <bool SM>
+__global__ void __launch_bounds__(RCM_MAXT, 2) k_mo_w(const Geom g, const MoFields f, const MoScalars s, double* zdf,
                                                       const int jsound, const int last) {
+#ifndef RCM_EMU
+  extern __shared__ double smw[];
+  const int nt = blockDim.x * blockDim.y, tid = threadIdx.x + blockDim.x * threadIdx.y;
+#endif
   const int si = g.si; const long long sk = g.sk;
   const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
@@ -100,6 +116,7 @@ __global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_w(const Geom g, const MoFiel
     wkp1 = 0.5 * (zuh + zvh);
     P3(f.w, j, i, kzp1) = wkp1;
   }
+  const double w_bot = wkp1;
   double s_kp1 = -wkp1;
   if (last) P3(f.s, j, i, kzp1) = interior ? 0.0 : s_kp1;
   double s_k;
@@ -108,7 +125,7 @@ __global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_w(const Geom g, const MoFiel
     s_k = -0.25 * (zuh + zvh) * LD1(f.gzitak + kz);
   }
   double zdiv_k = fmz_k * (mx2 * zd_kz + zdtrdz * (s_k - s_kp1));
-  P3(zdf, j, i, kz) = zdiv_k;
+  MOW_ST(2, kz, P3(zdf, j, i, kz), zdiv_k);
   double wwkw_kp1 = 0.0;
   for (int k = kz; k >= 2; --k) {
     MoWIn nxt = cur;
@@ -123,7 +140,7 @@ __global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_w(const Geom g, const MoFiel
     }
     const double fmz_km1 = cur.fmz_km1;
     const double zdiv_km1 = fmz_km1 * (mx2 * cur.zd_km1 + zdtrdz * (s_km1 - s_k));
-    P3(zdf, j, i, k - 1) = zdiv_km1;
+    MOW_ST(2, k - 1, P3(zdf, j, i, k - 1), zdiv_km1);
     const double pai_km1 = cur.pai_km1, tet_km1 = cur.tet_km1;
     const double fmzf_k = cur.fmzf_k;
     const double w_k = cur.w_k;
@@ -138,8 +155,8 @@ __global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_w(const Geom g, const MoFiel
     const double zrapp = 1.0 / (1.0 + zm + zp - zm * wwkw_kp1);
     const double wn = zrapp * (zwexpl + zm * wkp1);
     wwkw_kp1 = zrapp * zp;
-    P3(f.w, j, i, k) = wn;
-    P3(f.wwkw, j, i, k) = wwkw_kp1;
+    MOW_ST(0, k, P3(f.w, j, i, k), wn);
+    MOW_ST(1, k, P3(f.wwkw, j, i, k), wwkw_kp1);
     if (last) P3(f.s, j, i, k) = s_k;
     wkp1 = wn;
     s_k = s_km1; zdiv_k = zdiv_km1; fmz_k = fmz_km1; pai_k = pai_km1; tet_k = tet_km1;
@@ -148,19 +165,19 @@ __global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_w(const Geom g, const MoFiel
   // 2nd loop of the tridiagonal inversion, new Exner function, completed s; the operands of level
   // k+1 are loaded before the stores of level k
   double w_km1 = P3(f.w, j, i, 1);
-  double a_w = P3(f.w, j, i, 2), a_ww = P3(f.wwkw, j, i, 2), a_dw = P3(f.deltaw, j, i, 2);
+  double a_w = MOW_LD(0, 2, P3(f.w, j, i, 2)), a_ww = MOW_LD(1, 2, P3(f.wwkw, j, i, 2)), a_dw = P3(f.deltaw, j, i, 2);
   double a_zd = 0.0, a_fmz = 0.0, a_pai = 0.0, a_s = 0.0, a_fzf = 0.0;
   if (interior) {
-    a_zd = P3(zdf, j, i, 1); a_fmz = L3(f.fmz, j, i, 1); a_pai = P3(f.pai, j, i, 1);
+    a_zd = MOW_LD(2, 1, P3(zdf, j, i, 1)); a_fmz = L3(f.fmz, j, i, 1); a_pai = P3(f.pai, j, i, 1);
     if (last) { a_s = P3(f.s, j, i, 2); a_fzf = L3(f.fmzf, j, i, 2); }
   }
   for (int k = 2; k <= kz; ++k) {
     double b_w = 0.0, b_ww = 0.0, b_dw = 0.0, b_zd = 0.0, b_fmz = 0.0, b_pai = 0.0, b_s = 0.0, b_fzf = 0.0;
     if (k < kz) {
-      b_w = P3(f.w, j, i, k + 1); b_ww = P3(f.wwkw, j, i, k + 1); b_dw = P3(f.deltaw, j, i, k + 1);
+      b_w = MOW_LD(0, k + 1, P3(f.w, j, i, k + 1)); b_ww = MOW_LD(1, k + 1, P3(f.wwkw, j, i, k + 1)); b_dw = P3(f.deltaw, j, i, k + 1);
     }
     if (interior) {   // level k (the Exner function is updated one level behind w); for k = kz these feed the tail
-      b_zd = P3(zdf, j, i, k); b_fmz = L3(f.fmz, j, i, k); b_pai = P3(f.pai, j, i, k);
+      b_zd = MOW_LD(2, k, P3(zdf, j, i, k)); b_fmz = L3(f.fmz, j, i, k); b_pai = P3(f.pai, j, i, k);
       if (last && k < kz) { b_s = P3(f.s, j, i, k + 1); b_fzf = L3(f.fmzf, j, i, k + 1); }
     }
     const double wk = a_w + a_ww * w_km1;
@@ -175,7 +192,7 @@ __global__ void __launch_bounds__(RCM_MAXT, 3) k_mo_w(const Geom g, const MoFiel
     a_w = b_w; a_ww = b_ww; a_dw = b_dw; a_zd = b_zd; a_fmz = b_fmz; a_pai = b_pai; a_s = b_s; a_fzf = b_fzf;
   }
   if (interior) {
-    const double zd = a_zd + zdtrdz * a_fmz * (w_km1 - P3(f.w, j, i, kzp1));
+    const double zd = a_zd + zdtrdz * a_fmz * (w_km1 - w_bot);
     P3(f.pai, j, i, kz) = a_pai * (1.0 - rdrcv * zd);
     if (last) P3(f.s, j, i, 1) = 0.0;
   }
@@ -270,7 +287,27 @@ void launch_mo_div(const Geom& g, const MoFields& f, const MoScalars& s, cudaStr
 }
 void launch_mo_w(const Geom& g, const MoFields& f, const MoScalars& s, double* zdf, int jsound, int last, cudaStream_t st) {
   dim3 b = col_block();
-  RCM_LAUNCH(k_mo_w, grid3(g, g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, 1, b), b, st, g, f, s, zdf, jsound, last);
+  const dim3 gr = grid3(g, g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, 1, b);
+#ifndef RCM_EMU
+  // RCM_MO_WSM=0 selects the global-memory scratch; the shared-memory variant needs 24 B x (kz+1) per thread
+  static int mode = -1;
+  static size_t maxsm = 0;
+  if (mode < 0) {
+    const char* e = std::getenv("RCM_MO_WSM");
+    mode = e ? std::atoi(e) : 1;
+    int dev = 0, v = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    maxsm = (size_t)v;
+    if (mode) cudaFuncSetAttribute(k_mo_w<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)maxsm);
+  }
+  const size_t need = (size_t)3 * g.kzp1 * b.x * b.y * sizeof(double);
+  if (mode && need <= maxsm) {
+    k_mo_w<true><<<gr, b, need, st>>>(g, f, s, zdf, jsound, last);
+    return;
+  }
+#endif
+  RCM_LAUNCH(k_mo_w<false>, gr, b, st, g, f, s, zdf, jsound, last);
 }
 void launch_mo_uv(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
   dim3 b(32, 4);
