@@ -52,8 +52,14 @@ __global__ void k_mo_destag(const Geom g, const MoFields f) {
 // vertical pass: one thread marches k once for a group of up to NF fields of one interior column
 // (blockIdx.z selects the group: fields z*NF .. z*NF+NF-1); the 4-level window pp(k-1..k+2) of every
 // field lives in registers, the interface velocity and the metric ratios are evaluated once per level
+#ifndef RCM_MB_WAFZ
+#define RCM_MB_WAFZ 3
+#endif
+#ifndef RCM_MB_WAFH
+#define RCM_MB_WAFH 4
+#endif
 template <int NF>
-__global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_wafz(const Geom g, const MoFields f, const MoScalars s) {
+__global__ void __launch_bounds__(RCM_MAXT, RCM_MB_WAFZ) k_mo_wafz(const Geom g, const MoFields f, const MoScalars s) {
   const int si = g.si; const long long sk = g.sk;
   const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
@@ -120,7 +126,7 @@ __global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_wafz(const Geom g, const MoF
 // all element offsets are field-independent and computed once; the field loop is unrolled (NF is a
 // template parameter) so that the per-field work is loads at precomputed offsets plus the limiter.
 template <int NF, int DIR>
-__global__ void __launch_bounds__(RCM_MAXT, 4) k_mo_wafh(const Geom g, const MoFields f, const MoScalars s) {
+__global__ void __launch_bounds__(RCM_MAXT, RCM_MB_WAFH) k_mo_wafh(const Geom g, const MoFields f, const MoScalars s) {
   const int si = g.si; const long long sk = g.sk;
   const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;

@@ -6,7 +6,7 @@ name=$1; shift
 root=$(cd "$(dirname "$0")/.." && pwd)
 tmp=$(mktemp -d /tmp/rcmvar.XXXX)
 mkdir -p $tmp/regcm_b200/csrc $tmp/include $root/regcm_b200/csrc/variants
-cp $root/regcm_b200/csrc/*.cu $root/regcm_b200/csrc/*.h $root/regcm_b200/csrc/*.cuh $root/regcm_b200/csrc/*.inc $root/regcm_b200/csrc/Makefile $tmp/regcm_b200/csrc/
+cp $root/regcm_b200/csrc/*.cu $root/regcm_b200/csrc/*.hpp $root/regcm_b200/csrc/*.h $root/regcm_b200/csrc/*.cuh $root/regcm_b200/csrc/*.inc $root/regcm_b200/csrc/Makefile $tmp/regcm_b200/csrc/
 cp $root/include/*.h $tmp/include/
 make -s -C $tmp/regcm_b200/csrc -j8 NVFLAGS="-O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=false -Xcompiler -fPIC,-ffp-contract=off,-fno-fast-math -Xptxas -v $*" >/dev/null
 python3 - $tmp/regcm_b200/csrc <<'PY'
