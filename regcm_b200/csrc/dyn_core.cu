@@ -278,7 +278,6 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   if (c.idynamic < 1 || c.idynamic > 3) return bail(RCM_ERR_ARG, "idynamic must be 1 (hydrostatic), 2 (non-hydrostatic) or 3 (MOLOCH)");
   h->hydro = (c.idynamic == 1);
   h->moloch = (c.idynamic == 3);
-  if (h->moloch && c.nproc != 1) return bail(RCM_ERR_ARG, "idynamic=3 runs on one rank only in this version");
   if (h->moloch && (c.mo_nadv < 1 || c.mo_nsound < 1 || c.kz < 4 || c.ipptls < 0 || c.ipptls > 1))
     return bail(RCM_ERR_ARG, "idynamic=3 needs mo_nadv >= 1, mo_nsound >= 1, kz >= 4, ipptls 0 or 1");
   if (h->hydro && c.nproc != 1) return bail(RCM_ERR_ARG, "idynamic=1 runs on one rank only (BASELINE configs[0] is a single-rank case)");
@@ -1418,6 +1417,11 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
     CUDA_OK(cudaMemcpy(pb, h->mf.psbits, sizeof(pb), cudaMemcpyDeviceToHost));
     h->nan_flag = nanf;
     if (nsteps > 0 && pb[0]) { const unsigned long long mn = ~pb[1]; std::memcpy(&h->ps_max, &pb[0], 8); std::memcpy(&h->ps_min, &mn, 8); }
+    if (h->cfg.nproc > 1 && nsteps > 0) {   // maxall / minall of the reference (Main/mod_moloch.F90:440-441)
+      double v[3] = {h->ps_max, -h->ps_min, (double)nanf};
+      if (h->halo.allreduce_host(v, 3, 1)) return fail(h, RCM_ERR_NCCL, "allreduce (ps extremes) failed");
+      h->ps_max = v[0]; h->ps_min = -v[1]; nanf = (int)v[2]; h->nan_flag = nanf;
+    }
     CUDA_OK(cudaGetLastError());
     if (nanf) return fail(h, RCM_ERR_CFL, "CFL violation: surface pressure is not a number (decrease dt)");   // Main/mod_moloch.F90:443-451
     return RCM_OK;

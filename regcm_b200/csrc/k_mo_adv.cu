@@ -345,24 +345,28 @@ void launch_mo_destag(const Geom& g, const MoFields& f, cudaStream_t st) {
   dim3 b(32, 4);
   RCM_LAUNCH(k_mo_destag, grid3(g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, g.kz, b), b, st, g, f);
 }
-void launch_mo_waf(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
+void launch_mo_waf(const Geom& g, const MoFields& f, const MoScalars& s, int passes, cudaStream_t st) {
   dim3 bc = col_block(), b(32, 4);
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
   // RCM_MO_WAFZ = fields per thread of the vertical pass (default 7 = all fields in one thread: measured fastest on B200, gpurun_out/mo_abz_*.json)
   static int zg = -1;
   if (zg < 0) { const char* e = std::getenv("RCM_MO_WAFZ"); zg = e ? std::atoi(e) : 7; }
-  if (zg >= 7) RCM_LAUNCH(k_mo_wafz<7>, grid3(nj, ni, 1, bc), bc, st, g, f, s);
+  if (!(passes & 1)) {}
+  else if (zg >= 7) RCM_LAUNCH(k_mo_wafz<7>, grid3(nj, ni, 1, bc), bc, st, g, f, s);
   else if (zg == 2) RCM_LAUNCH(k_mo_wafz<2>, grid3(nj, ni, (s.nf + 1) / 2, bc), bc, st, g, f, s);
   else if (zg == 3) RCM_LAUNCH(k_mo_wafz<3>, grid3(nj, ni, (s.nf + 2) / 3, bc), bc, st, g, f, s);
   else RCM_LAUNCH(k_mo_wafz<4>, grid3(nj, ni, (s.nf + 3) / 4, bc), bc, st, g, f, s);
   // RCM_MO_WAF: bit 0 = one-cell meridional kernel, bit 1 = one-cell zonal kernel (default 3: measured faster on B200 than the 4-cell kernels, profiles/r1_moloch.md)
   static int mode = -1;
   if (mode < 0) { const char* e = std::getenv("RCM_MO_WAF"); mode = e ? std::atoi(e) : 3; }
-  if (mode & 1) {
+  const int md = (g.gl | g.gr | g.gb | g.gt) ? 3 : mode;   // the 4-cell kernels clamp to the tile: single rank only
+  if (!(passes & 2)) {}
+  else if (md & 1) {
     if (s.nf == 7) RCM_LAUNCH((k_mo_wafh<7, 0>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
     else RCM_LAUNCH((k_mo_wafh<6, 0>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
   } else RCM_LAUNCH(k_mo_wafy4, grid3(nj, (ni + RCM_MO_NC - 1) / RCM_MO_NC, g.kz, b), b, st, g, f, s);
-  if (mode & 2) {
+  if (!(passes & 4)) {}
+  else if (md & 2) {
     if (s.nf == 7) RCM_LAUNCH((k_mo_wafh<7, 1>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
     else RCM_LAUNCH((k_mo_wafh<6, 1>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
   } else RCM_LAUNCH(k_mo_wafx4, grid3((nj + RCM_MO_NC - 1) / RCM_MO_NC, ni, g.kz, b), b, st, g, f, s);

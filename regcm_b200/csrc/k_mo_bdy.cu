@@ -124,7 +124,8 @@ __global__ void k_mo_bdyval_c(const Geom g, const MoFields f, const MoScalars s,
     P3(f.pai, j, i, k) = L3(f.xpb0, j, i, k) + s.xt * L3(f.xpbt, j, i, k);
   }
   if (s.ipptls > 0) {
-    const bool west = (j == g.jce1), east = (j == g.jce2), south = (i == g.ice1), north = (i == g.ice2);
+    const bool west = g.has_bdyleft && (j == g.jce1), east = g.has_bdyright && (j == g.jce2),
+               south = g.has_bdybottom && (i == g.ice1), north = g.has_bdytop && (i == g.ice2);
     double qxint, windavg; bool zero;
     if (west || east) {
       const int jin = west ? g.jci1 : g.jci2, jd = west ? g.jde1 : g.jde2, jdn = west ? g.jdi1 : g.jdi2;
@@ -149,11 +150,11 @@ __global__ void k_mo_bdyval_c(const Geom g, const MoFields f, const MoScalars s,
 
 // pai of one boundary record from ps [Pa], t, qv (column march upward)
 __global__ void k_mo_paicompute(const Geom g, const MoFields f, const MoScalars s, const double* ps, const double* t,
-                                const double* q, double* pai) {
+                                const double* q, double* pai, const int j1, const int j2, const int i1, const int i2) {
   const int si = g.si; const long long sk = g.sk;
-  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
-  if (j > g.jce2 || i > g.ice2) return;
+  const int j = j1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = i1 + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j > j2 || i > i2) return;
   const int kz = g.kz;
   const double zdelta0 = L2(f.ht, j, i) * s.gzm1 + s.zz1;
   double tv2 = L3(t, j, i, kz) * (1.0 + ep1 * L3(q, j, i, kz));
@@ -222,11 +223,11 @@ __global__ void k_mo_init_state(const Geom g, const MoFields f, const MoScalars 
   }
 }
 
-__global__ void k_mo_scale2d(const Geom g, double* a, const double c) {
+__global__ void k_mo_scale2d(const Geom g, double* a, const double c, const int j1, const int j2, const int i1, const int i2) {
   const int si = g.si;
-  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
-  if (j > g.jce2 || i > g.ice2) return;
+  const int j = j1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = i1 + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j > j2 || i > i2) return;
   P2(a, j, i) = P2(a, j, i) * c;
 }
 
@@ -246,20 +247,20 @@ void launch_mo_raydamp(const Geom& g, const MoFields& f, const MoScalars& s, cud
 void launch_mo_bdyval(const Geom& g, const MoFields& f, const MoScalars& s, const int2* rim_u, int nu, const int2* rim_v, int nv,
                       const int2* rim_c, int nc, cudaStream_t st) {
   dim3 b(128);
-  RCM_LAUNCH(k_mo_bdyval_uv, dim3((nu + 127) / 128, g.kz), b, st, g, f, s, rim_u, nu, 0);
-  RCM_LAUNCH(k_mo_bdyval_uv, dim3((nv + 127) / 128, g.kz), b, st, g, f, s, rim_v, nv, 1);
-  RCM_LAUNCH(k_mo_bdyval_c, dim3((nc + 127) / 128, g.kz), b, st, g, f, s, rim_c, nc);
+  if (nu > 0) RCM_LAUNCH(k_mo_bdyval_uv, dim3((nu + 127) / 128, g.kz), b, st, g, f, s, rim_u, nu, 0);
+  if (nv > 0) RCM_LAUNCH(k_mo_bdyval_uv, dim3((nv + 127) / 128, g.kz), b, st, g, f, s, rim_v, nv, 1);
+  if (nc > 0) RCM_LAUNCH(k_mo_bdyval_c, dim3((nc + 127) / 128, g.kz), b, st, g, f, s, rim_c, nc);
 }
 void launch_mo_paicompute(const Geom& g, const MoFields& f, const MoScalars& s, const double* ps, const double* t, const double* q,
-                          double* pai, cudaStream_t st) {
+                          double* pai, int j1, int j2, int i1, int i2, cudaStream_t st) {
   dim3 b = col_block();
-  RCM_LAUNCH(k_mo_paicompute, grid2(g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, b), b, st, g, f, s, ps, t, q, pai);
+  RCM_LAUNCH(k_mo_paicompute, grid2(j2 - j1 + 1, i2 - i1 + 1, b), b, st, g, f, s, ps, t, q, pai, j1, j2, i1, i2);
 }
 void launch_mo_init_state(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
   dim3 b = col_block();
   RCM_LAUNCH(k_mo_init_state, grid2(g.jde2 - g.jde1 + 1, g.ide2 - g.ide1 + 1, b), b, st, g, f, s);
 }
-void launch_mo_scale2d(const Geom& g, double* a, double c, cudaStream_t st) {
+void launch_mo_scale2d(const Geom& g, double* a, double c, int j1, int j2, int i1, int i2, cudaStream_t st) {
   dim3 b(32, 4);
-  RCM_LAUNCH(k_mo_scale2d, grid2(g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, b), b, st, g, a, c);
+  RCM_LAUNCH(k_mo_scale2d, grid2(j2 - j1 + 1, i2 - i1 + 1, b), b, st, g, a, c, j1, j2, i1, i2);
 }

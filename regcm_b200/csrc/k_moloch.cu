@@ -25,12 +25,15 @@ __global__ void k_mo_pre(const Geom g, const MoFields f, const MoScalars s) {
   P3(f.tetav, j, i, k) = tv / P3(f.pai, j, i, k);
 }
 
+// Evaluated on the owned cells plus one ghost ring towards neighbouring ranks (g.gl/gr/gb/gt), so that the
+// 5-point filter of k_mo_w finds its neighbours without a separate exchange of the divergence (the reference
+// exchanges zdiv2, Main/mod_moloch.F90:553; here u and v carry two ghost rows instead).
 __global__ void k_mo_div(const Geom g, const MoFields f, const MoScalars s) {
   const int si = g.si; const long long sk = g.sk;
-  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int j = g.jce1 - g.gl + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ice1 - g.gb + blockIdx.y * blockDim.y + threadIdx.y;
   const int k = 1 + blockIdx.z;
-  if (j > g.jce2 || i > g.ice2) return;
+  if (j > g.jce2 + g.gr || i > g.ice2 + g.gt) return;
   const double zum = L3(f.u, j, i, k) * L2(f.rmu, j, i) * L3(f.zru, j, i, k);
   const double zup = L3(f.u, j + 1, i, k) * L2(f.rmu, j + 1, i) * L3(f.zru, j + 1, i, k);
   const double zvm = L3(f.v, j, i, k) * L2(f.rmv, j, i) * L3(f.zrv, j, i, k);
@@ -286,7 +289,7 @@ void launch_mo_pre(const Geom& g, const MoFields& f, const MoScalars& s, cudaStr
 }
 void launch_mo_div(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
   dim3 b(32, 4);
-  RCM_LAUNCH(k_mo_div, grid3(g, g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, g.kz, b), b, st, g, f, s);
+  RCM_LAUNCH(k_mo_div, grid3(g, g.jce2 - g.jce1 + 1 + g.gl + g.gr, g.ice2 - g.ice1 + 1 + g.gb + g.gt, g.kz, b), b, st, g, f, s);
 }
 void launch_mo_w(const Geom& g, const MoFields& f, const MoScalars& s, double* zdf, int jsound, int last, cudaStream_t st) {
   dim3 b = col_block();

@@ -119,9 +119,8 @@ def make_case(name: str = "C2", *, flat: bool = False, unit_map: bool = False, n
     for k, v in cfg_over.items():
         setattr(cfg, k, v)
     if idynamic == 3:
-        if window is not None:
-            raise ValueError("the MOLOCH cases are generated on the whole domain (single rank)")
-        return _make_moloch_case(name, cfg, flat=flat, unit_map=unit_map, noise=noise, ibdyfrq=ibdyfrq, records=records)
+        case = _make_moloch_case(name, cfg, flat=flat, unit_map=unit_map, noise=noise, ibdyfrq=ibdyfrq, records=records)
+        return _window_moloch(case, window) if window is not None else case
     j1, j2, i1, i2 = window or (1, jx, 1, iy)
     j1, i1, j2, i2 = max(1, j1), max(1, i1), min(jx, j2), min(iy, i2)
     jc2, ic2 = min(j2, jx - 1), min(i2, iy - 1)
@@ -306,6 +305,23 @@ def _make_moloch_case(name, cfg, *, flat, unit_map, noise, ibdyfrq, records) -> 
     phases = {capi.BDY_B0: 0.0, capi.BDY_B1: shift, capi.BDY_NEXT: 2 * shift}
     case.bdy = {slot: record(phases[slot]) for slot in records}
     return case
+
+
+def _window_moloch(case: Case, window) -> Case:
+    """Cut the GLOBAL C-grid arrays of a MOLOCH case down to the inclusive dot-index window (j1, j2, i1, i2);
+    every array keeps its own grid's upper limit (u: iy-1 rows, v: jx-1 columns, cross: both)."""
+    jx, iy = case.cfg.jx, case.cfg.iy
+    j1, j2, i1, i2 = window
+    j1, i1, j2, i2 = max(1, j1), max(1, i1), min(jx, j2), min(iy, i2)
+
+    def cut(a):
+        nj, ni = a.shape[0], a.shape[1]          # the array's own global extent
+        return np.asfortranarray(a[j1 - 1:min(j2, nj), i1 - 1:min(i2, ni), ...])
+    out = Case(name=case.name, cfg=case.cfg)
+    out.lb = (j1, i1)
+    out.statics = {sid: (a if sid == capi.S_SIGMA else cut(a)) for sid, a in case.statics.items()}
+    out.bdy = {slot: {fid: cut(a) for fid, a in rec.items()} for slot, rec in case.bdy.items()}
+    return out
 
 
 def load_case(core: capi.DynCore, case: Case, stage_next: bool = True) -> None:

@@ -20,6 +20,7 @@ sys.path.insert(0, ROOT)
 from regcm_b200 import capi, synth  # noqa: E402
 
 FIELDS = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PP, capi.F_W)
+MOLOCH_FIELDS = (capi.F_U, capi.F_V, capi.F_W, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PAI, capi.F_PS)
 
 
 def tile_window(tile, jx, iy, pad=3):
@@ -31,6 +32,13 @@ def owned_bounds(core, field):
     """Global index range of the points of `field` this rank owns."""
     j1, j2, i1, i2 = core.tile()
     kz = core.kz
+    if core.cfg.idynamic == 3:   # Arakawa C grid: u (jx, iy-1), v (jx-1, iy), ps 2-D
+        if field == capi.F_U:
+            return (j1, i1, 1), (j2, min(i2, core.iy - 1), kz)
+        if field == capi.F_V:
+            return (j1, i1, 1), (min(j2, core.jx - 1), i2, kz)
+        if field == capi.F_PS:
+            return (j1, i1, 1), (min(j2, core.jx - 1), min(i2, core.iy - 1), 1)
     if field in (capi.F_U, capi.F_V):
         return (j1, i1, 1), (j2, i2, kz)
     nk = kz + 1 if field == capi.F_W else kz
@@ -45,6 +53,7 @@ def main():
     ap.add_argument("--cpus-j", type=int, default=0)
     ap.add_argument("--cpus-i", type=int, default=0)
     ap.add_argument("--ibdyfrq", type=int, default=6)
+    ap.add_argument("--iboudy", type=int, default=-1)
     ap.add_argument("--work", action="store_true", help="also dump the per-step work arrays")
     ap.add_argument("--out", required=True)
     args = ap.parse_args()
@@ -91,6 +100,8 @@ def main():
 
     base = synth.make_case(args.case, records=(), ibdyfrq=args.ibdyfrq)  # cfg only
     cfg = base.cfg
+    if args.iboudy >= 0:
+        cfg.iboudy = args.iboudy
     cfg.nproc, cfg.myid, cfg.cpus_j, cfg.cpus_i = world, rank, args.cpus_j, args.cpus_i
     if args.lib == "cuda":
         cfg.device = int(os.environ.get("LOCAL_RANK", rank))
@@ -102,8 +113,9 @@ def main():
     synth.load_case(core, case, stage_next=True)
     core.step(args.steps)
     out = {"tile": np.array(core.tile())}
-    for fld in FIELDS:
-        for lev, tag in ((capi.LEVEL_A, "a"), (capi.LEVEL_B, "b")):
+    moloch = cfg.idynamic == 3
+    for fld in (MOLOCH_FIELDS if moloch else FIELDS):
+        for lev, tag in (((capi.LEVEL_A, "a"),) if moloch else ((capi.LEVEL_A, "a"), (capi.LEVEL_B, "b"))):
             lb, ub = owned_bounds(core, fld)
             out[f"f{fld}{tag}"] = core.get_state(fld, lev, lb=lb, ub=ub)
             out[f"lb{fld}"] = np.array(lb)
@@ -130,6 +142,7 @@ def main():
             out[f"wlb{wid}"] = np.array(lb)
     d = core.diag()
     out["max_cfl"] = np.array(d.max_cfl)
+    out["ps_extremes"] = np.array([d.ps_max, d.ps_min])
     np.savez(os.path.join(args.out, f"rank{rank}.npz"), **out)
     core.close()
     dist.barrier()

@@ -44,8 +44,6 @@ def test_create_rejects_bad_config(built):
     assert lib.create(C.byref(bad), C.byref(h)) == -1 and not h
     bad = capi.default_cfg(4, jx=64, iy=34, kz=18, ds=60.0, dt=120.0)   # no such core
     assert lib.create(C.byref(bad), C.byref(h)) == -1 and not h
-    mol = capi.default_cfg(3, jx=64, iy=34, kz=18, ds=12.0, dt=90.0, nproc=2)   # MOLOCH is single-rank
-    assert lib.create(C.byref(mol), C.byref(h)) == -1 and not h
     mol = capi.default_cfg(3, jx=64, iy=34, kz=18, ds=12.0, dt=90.0, mo_nsound=0)
     assert lib.create(C.byref(mol), C.byref(h)) == -1 and not h
     hyd = capi.default_cfg(1, jx=64, iy=34, kz=18, ds=60.0, dt=150.0, nproc=2)  # the hydrostatic core is single-rank

@@ -162,7 +162,7 @@ def test_emu_moloch_analytic_cases(emu_lib):
 
 
 def test_moloch_rejects_unsupported(emu_lib):
-    for kw in ({"nproc": 2}, {"mo_nadv": 0}, {"ipptls": 2}, {"kz": 3}):
+    for kw in ({"mo_nadv": 0}, {"ipptls": 2}, {"kz": 3}):
         case = synth.make_case("tinym")
         cfg = case.cfg
         for k, v in kw.items():
