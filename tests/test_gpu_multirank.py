@@ -44,3 +44,38 @@ def test_nccl_halo_matches_single_gpu(cuda_lib, tmp_path, world, layout, case_na
     orc.step(steps)
     oref = {(f, "ab"[lv]): orc.get_state(f, lv) for f in range(7) for lv in (0, 1)}
     compare(glob, oref, 1e-10)
+
+
+@pytest.mark.parametrize("world,layout,case_name", [(2, (0, 0), "smallm"), (2, (1, 2), "smallm"), (4, (2, 2), "smallm"), (8, (0, 0), "C5q")])
+def test_moloch_halo_matches_single_gpu(cuda_lib, tmp_path, world, layout, case_name):
+    """MOLOCH core (idynamic = 3) on a 2-D decomposition: equal to the one-GPU result of the same library
+    (the exchange is exact) and within the single-GPU tolerance of the CPU oracle."""
+    if ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    from test_multirank_emu import MOLOCH_FIELDS, assemble_moloch
+    steps = 3
+    run_ranks(world, tmp_path, ["--case", case_name, "--steps", str(steps), "--cpus-j", str(layout[0]), "--cpus-i", str(layout[1])],
+              lib="cuda")
+    case = synth.make_case(case_name)
+    core = capi.DynCore(cuda_lib, case.cfg)
+    synth.load_case(core, case)
+    core.step(steps)
+    glob, exts = assemble_moloch(tmp_path, world, case.cfg)
+    for f in MOLOCH_FIELDS:
+        a, b = glob[f], core.get_state(f)
+        b = b if b.ndim == 3 else b[:, :, None]
+        assert not np.isnan(a).any(), capi.FIELD_NAMES[f]
+        assert float(np.abs(a - b).max()) <= 1e-12 * max(float(np.abs(b).max()), 1e-300), capi.FIELD_NAMES[f]
+    d = core.diag()
+    for e in exts:
+        assert abs(e[0] - d.ps_max) <= 1e-12 * d.ps_max and abs(e[1] - d.ps_min) <= 1e-12 * d.ps_min
+    core.close()
+    if case_name == "smallm":
+        from oracle import pyoracle
+        orc = pyoracle.make_oracle(case.cfg)
+        synth.load_case(orc, case)
+        orc.step(steps)
+        for f in MOLOCH_FIELDS:
+            a, b = glob[f], orc.get_state(f)
+            b = b if b.ndim == 3 else b[:, :, None]
+            assert float(np.abs(a - b).max()) <= 1e-10 * max(float(np.abs(b).max()), 1e-300), capi.FIELD_NAMES[f]
