@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY.
 // CPU (double precision) restatement of the reference's dyn-core state and
-// step for idynamic = 2 (non-hydrostatic MM5 core), single rank.
+// step for idynamic = 2 (non-hydrostatic MM5 core), 1 (hydrostatic split-explicit
+// core) and 3 (MOLOCH), single rank.  See oracle/README.md.
 // "parity unpinned": the reference ships no golden vectors for this path
 // (SURVEY.md §8c); this restatement IS the pin.
 //
