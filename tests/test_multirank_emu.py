@@ -150,7 +150,7 @@ def single_rank_moloch(emu_lib, case_name, steps, **kw):
     return case.cfg, ref, (d.ps_max, d.ps_min)
 
 
-@pytest.mark.parametrize("world,layout", [(2, (0, 0)), (2, (1, 2)), (4, (2, 2)), (3, (3, 1))])
+@pytest.mark.parametrize("world,layout", [(2, (0, 0)), (2, (1, 2)), (4, (2, 2)), (3, (3, 1)), (8, (0, 0))])
 def test_moloch_multirank_matches_single_rank(emu_lib, tmp_path, world, layout):
     """2-D decomposition of the MOLOCH core: ghost-ring divergence, per-sub-step exchanges of u, v and
     pai/deltaw, the exchanges between the directional advection passes, tile-aware relaxation zones and
