@@ -177,7 +177,9 @@ typedef struct rcm_cfg {
   int32_t mo_nadv;        /* advection sub-steps per step (3)              */
   int32_t mo_nsound;      /* sound sub-steps per advection step (6)        */
   int32_t mo_nzfilt;      /* levels of the top sponge in the w solve (3)   */
-  int32_t reserved_i[3];
+  int32_t mo_rotllr;      /* 1: iproj = 'ROTLLR' (rotated lat-lon) branches of sound / wafone /
+                           * compute_moloch_static (Main/mod_moloch.F90:773,932,1183; Main/mod_params.F90:2766) */
+  int32_t reserved_i[2];
   /* &geoparam */
   double ds;    /* grid spacing [km]                                       */
   double ptop;  /* model top pressure [cb]                                 */

@@ -1,6 +1,6 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY.
 // Restates the MOLOCH core (idynamic = 3) of the reference, single rank,
-// non-ROTLLR projection branch, physics off:
+// both projection branches (generic and iproj = 'ROTLLR'), physics off:
 //   Main/mod_moloch.F90       allocate_moloch:115 init_moloch:159 moloch:224
 //                             boundary:485 filt3d:549 sound:708 advection:1042
 //                             wafone:1098 stagger operators :1574-1794
@@ -103,7 +103,7 @@ int Oracle::create_moloch() {
   return RCM_OK;
 }
 
-// Main/mod_params.F90:2743-2847 (non-ROTLLR)
+// Main/mod_params.F90:2743-2847
 void Oracle::compute_moloch_static() {
   for (int i = ice1; i <= ice2; ++i)
     for (int j = jde1; j <= jde2; ++j) coriou(j, i) = eomeg2 * std::sin(ulat(j, i) * degrad);
@@ -112,7 +112,10 @@ void Oracle::compute_moloch_static() {
   for (int i = ice1; i <= ice2; ++i)
     for (int j = jdi1; j <= jdi2; ++j) hx(j, i) = (ht(j, i) - ht(j - 1, i)) * msfu(j, i) * rdx * regrav;
   for (int i = idi1; i <= idi2; ++i)
-    for (int j = jce1; j <= jce2; ++j) hy(j, i) = (ht(j, i) - ht(j, i - 1)) * msfv(j, i) * rdx * regrav;
+    for (int j = jce1; j <= jce2; ++j) {
+      if (cfg.mo_rotllr) hy(j, i) = (ht(j, i) - ht(j, i - 1)) * rdx * regrav;   // :2766-2771
+      else hy(j, i) = (ht(j, i) - ht(j, i - 1)) * msfv(j, i) * rdx * regrav;
+    }
   for (int i = ice1; i <= ice2; ++i) { hx(jde1, i) = hx(jdi1, i); hx(jde2, i) = hx(jdi2, i); }
   for (int j = jce1; j <= jce2; ++j) { hy(j, ide1) = hy(j, idi1); hy(j, ide2) = hy(j, idi2); }
   zita(kzp1) = d_zero;
@@ -373,12 +376,13 @@ void Oracle::mo_filt3d() {
   }
 }
 
-// ---- Main/mod_moloch.F90:708-1040 (do_fulleq = .false., non-ROTLLR) ----
+// ---- Main/mod_moloch.F90:708-1040 (do_fulleq = .false.; both projection branches) ----
 void Oracle::mo_sound(double dts) {
   A3 &u = m_u, &v = m_v, &w = m_w, &s = m_s, &zdiv2 = m_zdiv2, &deltaw = m_deltaw, &wwkw = m_wwkw, &pai = m_pai,
      &tetav = m_tetav, &fmz = m_fmz, &fmzf = m_fmzf, &ud = m_ud, &vd = m_vd;
   const double zdtrdx = dts / dx, zdtrdy = dts / dx, zdtrdz = dts / mo_dz;
   const double zcs2 = (zdtrdz * zdtrdz) * rdrcv;
+  const bool rot = cfg.mo_rotllr != 0;   // iproj == 'ROTLLR'
   for (int jsound = 1; jsound <= nsound; ++jsound) {
     ud.d = u.d; vd.d = v.d;
     for (int i = ice1; i <= ice2; ++i)
@@ -405,18 +409,26 @@ void Oracle::mo_sound(double dts) {
           double zrfmzvm = d_two / (fmz(j, i, k) + fmz(j, im1, k));
           double zrfmzup = d_two / (fmz(j, i, k) + fmz(jp1, i, k));
           double zrfmzvp = d_two / (fmz(j, i, k) + fmz(j, ip1, k));
-          double zum = u(j, i, k) * rmu(j, i) * zrfmzum;
-          double zup = u(j + 1, i, k) * rmu(j + 1, i) * zrfmzup;
-          double zvm = v(j, i, k) * rmv(j, i) * zrfmzvm;
-          double zvp = v(j, i + 1, k) * rmv(j, i + 1) * zrfmzvp;
-          zdiv2(j, i, k) = (zup - zum) * zdtrdx + (zvp - zvm) * zdtrdy;
+          if (rot) {   // :775-793
+            double zum = zdtrdx * u(j, i, k) * zrfmzum;
+            double zup = zdtrdx * u(j + 1, i, k) * zrfmzup;
+            double zvm = zdtrdy * v(j, i, k) * zrfmzvm * rmv(j, i);
+            double zvp = zdtrdy * v(j, i + 1, k) * zrfmzvp * rmv(j, i + 1);
+            zdiv2(j, i, k) = (zup - zum) + (zvp - zvm);
+          } else {
+            double zum = u(j, i, k) * rmu(j, i) * zrfmzum;
+            double zup = u(j + 1, i, k) * rmu(j + 1, i) * zrfmzup;
+            double zvm = v(j, i, k) * rmv(j, i) * zrfmzvm;
+            double zvp = v(j, i + 1, k) * rmv(j, i + 1) * zrfmzvp;
+            zdiv2(j, i, k) = (zup - zum) * zdtrdx + (zvp - zvm) * zdtrdy;
+          }
         }
       }
     mo_filt3d();
     for (int k = 1; k <= kz; ++k)
       for (int i = ice1; i <= ice2; ++i)
         for (int j = jce1; j <= jce2; ++j)
-          zdiv2(j, i, k) = fmz(j, i, k) * (mx2(j, i) * zdiv2(j, i, k) + zdtrdz * (s(j, i, k) - s(j, i, k + 1)));
+          zdiv2(j, i, k) = fmz(j, i, k) * ((rot ? msfx(j, i) : mx2(j, i)) * zdiv2(j, i, k) + zdtrdz * (s(j, i, k) - s(j, i, k + 1)));
     // new w (implicit scheme), Equation 19
     for (int k = kz; k >= 2; --k)
       for (int i = ice1; i <= ice2; ++i)
@@ -460,7 +472,7 @@ void Oracle::mo_sound(double dts) {
     for (int k = 1; k <= kz; ++k)
       for (int i = idii1; i <= idii2; ++i)
         for (int j = jci1; j <= jci2; ++j) {
-          double zcy = zdtrdy * msfv(j, i);
+          double zcy = rot ? zdtrdy : zdtrdy * msfv(j, i);   // :956 / :997
           double zfz = 0.25 * (deltaw(j, i - 1, k) + deltaw(j, i - 1, k + 1) + deltaw(j, i, k) + deltaw(j, i, k + 1)) + egrav * dts;
           double zrom1v = d_half * cpd * (tetav(j, i - 1, k) + tetav(j, i, k));
           double zcor1v = coriov(j, i) * 0.25 * (ud(j, i, k) + ud(j + 1, i, k) + ud(j, i - 1, k) + ud(j + 1, i - 1, k));
@@ -481,7 +493,7 @@ static inline double rdeno(double t1, double t2, double t3, double t4) {
   return (t1 - t2) / std::copysign(std::max(std::fabs(zzden), minden), zzden);
 }
 
-// ---- Main/mod_moloch.F90:1098-1361 (non-ROTLLR branch) ----
+// ---- Main/mod_moloch.F90:1098-1361 (ROTLLR branch :1183-1270, generic branch :1272-1358) ----
 void Oracle::wafone(A3& pp, double dta) {
   A3 &s = m_s, &fmz = m_fmz, &fmzf = m_fmzf, &wz = m_wz, &p0 = m_p0, &u = m_u, &v = m_v;
   A2 &wfw = m_wfw, &zpby = m_zpby, &zpbw = m_zpbw;
@@ -514,6 +526,57 @@ void Oracle::wafone(A3& pp, double dta) {
   }
   for (int k = 1; k <= kz; ++k)
     for (int j = jci1; j <= jci2; ++j) { wz(j, ice1, k) = wz(j, ici1, k); wz(j, ice2, k) = wz(j, ici2, k); }
+  if (cfg.mo_rotllr) {   // iproj == 'ROTLLR' (:1183-1270)
+    const A2& mu = msfu; const A2& mx = msfx;
+    for (int k = 1; k <= kz; ++k) {
+      for (int i = ici1; i <= ice2; ++i)
+        for (int j = jci1; j <= jci2; ++j) {
+          double zamu = v(j, i, k) * zdtrdy, is;
+          int ih;
+          if (zamu > d_zero) { is = d_one; ih = i - 1; }
+          else { is = -d_one; ih = std::min(i + 1, icross2); }
+          const int ihm1 = std::max(ih - 1, icross1);
+          double r = rdeno(wz(j, ih, k), wz(j, ihm1, k), wz(j, i, k), wz(j, i - 1, k));
+          double b = std::max(d_zero, std::min(d_two, std::max(r, std::min(d_two * r, d_one))));
+          double zphi = is + zamu * b - is * b;
+          zpby(j, i) = d_half * v(j, i, k) * ((d_one + zphi) * wz(j, i - 1, k) + (d_one - zphi) * wz(j, i, k));
+        }
+      for (int i = ici1; i <= ici2; ++i)
+        for (int j = jci1; j <= jci2; ++j) {
+          double zhxvtn = zdtrdy * rmv(j, i + 1) * mx(j, i);
+          double zhxvts = zdtrdy * rmv(j, i) * mx(j, i);
+          double zrfmn = zhxvtn * d_two * fmz(j, i, k) / (fmz(j, i, k) + fmz(j, i + 1, k));
+          double zrfms = zhxvts * d_two * fmz(j, i, k) / (fmz(j, i, k) + fmz(j, i - 1, k));
+          double zdv = (v(j, i + 1, k) * zrfmn - v(j, i, k) * zrfms) * pp(j, i, k);
+          p0(j, i, k) = wz(j, i, k) + zpby(j, i) * zrfms - zpby(j, i + 1) * zrfmn + zdv;
+        }
+    }
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ici1; i <= ici2; ++i) { p0(jce1, i, k) = p0(jci1, i, k); p0(jce2, i, k) = p0(jci2, i, k); }
+    for (int k = 1; k <= kz; ++k) {
+      for (int i = ici1; i <= ici2; ++i)
+        for (int j = jci1; j <= jce2; ++j) {
+          double zamu = u(j, i, k) * mu(j, i) * zdtrdx, is;
+          int jh;
+          if (zamu > d_zero) { is = d_one; jh = j - 1; }
+          else { is = -d_one; jh = std::min(j + 1, jcross2); }
+          const int jhm1 = std::max(jh - 1, jcross1);
+          double r = rdeno(p0(jh, i, k), p0(jhm1, i, k), p0(j, i, k), p0(j - 1, i, k));
+          double b = std::max(d_zero, std::min(d_two, std::max(r, std::min(d_two * r, d_one))));
+          double zphi = is + zamu * b - is * b;
+          zpbw(j, i) = d_half * u(j, i, k) * ((d_one + zphi) * p0(j - 1, i, k) + (d_one - zphi) * p0(j, i, k));
+        }
+      for (int i = ici1; i <= ici2; ++i)
+        for (int j = jci1; j <= jci2; ++j) {
+          double zcostx = zdtrdx * mu(j, i);
+          double zrfme = zcostx * d_two * fmz(j, i, k) / (fmz(j, i, k) + fmz(j + 1, i, k));
+          double zrfmw = zcostx * d_two * fmz(j, i, k) / (fmz(j, i, k) + fmz(j - 1, i, k));
+          double zdv = (u(j + 1, i, k) * zrfme - u(j, i, k) * zrfmw) * pp(j, i, k);
+          pp(j, i, k) = p0(j, i, k) + zpbw(j, i) * zrfmw - zpbw(j + 1, i) * zrfme + zdv;
+        }
+    }
+    return;
+  }
   // Meridional advection
   for (int k = 1; k <= kz; ++k) {
     for (int i = ici1; i <= ice2; ++i)

@@ -47,8 +47,8 @@ class RcmCfg(C.Structure):
         ("cpus_j", C.c_int32), ("cpus_i", C.c_int32),
         ("device", C.c_int32),
         ("nsplit", C.c_int32), ("lstand", C.c_int32),
-        ("mo_nadv", C.c_int32), ("mo_nsound", C.c_int32), ("mo_nzfilt", C.c_int32),
-        ("reserved_i", C.c_int32 * 3),
+        ("mo_nadv", C.c_int32), ("mo_nsound", C.c_int32), ("mo_nzfilt", C.c_int32), ("mo_rotllr", C.c_int32),
+        ("reserved_i", C.c_int32 * 2),
         ("ds", C.c_double), ("ptop", C.c_double),
         ("dt", C.c_double),
         ("gnu1", C.c_double), ("gnu2", C.c_double), ("ckh", C.c_double), ("adyndif", C.c_double),

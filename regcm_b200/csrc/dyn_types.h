@@ -123,6 +123,7 @@ struct MoScalars {
   double anu2;
   double zz1, gzm1;                                 // surface-pressure closure (:377-383)
   int ipptls, iboudy, ifrayd, kray, nspgx, nspgd, nf;
+  int rotllr;   // iproj == 'ROTLLR' branches (Main/mod_moloch.F90:773,932,1183)
 };
 
 struct MoFields {
@@ -130,7 +131,7 @@ struct MoFields {
   double *s, *zdiv, *deltaw, *wwkw, *p, *tvirt;
   double *adv[RCM_MO_MAXF], *wz[RCM_MO_MAXF], *p0[RCM_MO_MAXF];
   double *fmz, *fmzf, *zru, *zrv, *zeta, *tau_c, *tau_u, *tau_v;
-  double *ht, *hx, *hy, *mx2, *rmu, *rmv, *msfu, *msfv, *coriou, *coriov, *ps;
+  double *ht, *hx, *hy, *mx2, *mx, *rmu, *rmv, *msfu, *msfv, *coriou, *coriov, *ps;
   double *gzitak, *gzitakh, *ffilt;
   double *xfc, *xgc, *xfd, *xgd;  // relaxation coefficients [ib + nspg*(k-1)]
   double *xub0, *xubt, *xvb0, *xvbt, *xtb0, *xtbt, *xqb0, *xqbt, *xpb0, *xpbt;

@@ -1,6 +1,6 @@
 // MOLOCH core (idynamic = 3): advection step.
 //   k_mo_destag  uvstagtox + wstagtox                         Main/mod_moloch.F90:1739-1794,1574-1597
-//   k_mo_wafz / k_mo_wafy / k_mo_wafx   wafone (WAF/TVD, directional split z -> y -> x), non-ROTLLR branch
+//   k_mo_wafz / k_mo_wafy / k_mo_wafx   wafone (WAF/TVD, directional split z -> y -> x), both projection branches
 //                                                             :1098-1181,1274-1358
 //   k_mo_restag  xtouvstag + xtowstag                         :1680-1737,1599-1618
 // The reference calls wafone once per advected field (tetav, pai, ux, vx, wx, qv[, qc]); the advecting
@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_WAFZ) k_mo_wafz(const Geom g,
 // thread reads only its own point of it).  The upwind choice, the face velocities, the metric ratios and
 // all element offsets are field-independent and computed once; the field loop is unrolled (NF is a
 // template parameter) so that the per-field work is loads at precomputed offsets plus the limiter.
-template <int NF, int DIR>
+template <int NF, int DIR, bool ROT>
 __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_WAFH) k_mo_wafh(const Geom g, const MoFields f, const MoScalars s) {
   const int si = g.si; const long long sk = g.sk;
   const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
@@ -145,8 +145,13 @@ __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_WAFH) k_mo_wafh(const Geom g,
 #pragma unroll
   for (int m = 0; m < 2; ++m) {
     const int cc = c + m;
-    vr[m] = LD1(vel + o + m * st) * LD1(rm + o2 + m * st);
-    zamu[m] = vr[m] * zdtrd;
+    if (!ROT) {
+      vr[m] = LD1(vel + o + m * st) * LD1(rm + o2 + m * st);
+      zamu[m] = vr[m] * zdtrd;
+    } else {   // ROTLLR (:1190-1203, 1243-1256): the flux carries the wind itself; zonal Courant number with mu
+      vr[m] = LD1(vel + o + m * st);
+      zamu[m] = DIR ? vr[m] * LD1(f.msfu + o2 + m) * zdtrd : vr[m] * zdtrd;
+    }
     int ch;
     if (zamu[m] > 0.0) { is[m] = 1.0; ch = cc - 1; }
     else { is[m] = -1.0; ch = min(cc + 1, c2); }
@@ -154,9 +159,12 @@ __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_WAFH) k_mo_wafh(const Geom g,
     oh[m] = o + (long long)(ch - c) * st; ohm1[m] = o + (long long)(chm1 - c) * st;
   }
   const double fmz = LD1(f.fmz + o);
-  const double zrfhi = zdtrd * 2.0 * fmz / (fmz + LD1(f.fmz + o + st));   // zrfmn / zrfme
-  const double zrflo = zdtrd * 2.0 * fmz / (fmz + LD1(f.fmz + o - st));   // zrfms / zrfmw
-  const double mx2 = LD1(f.mx2 + o2);
+  // metric ratios: zdtrd (:1298-1299,1350-1351); ROTLLR: zhxvtn / zhxvts (:1209-1212), zcostx (:1262-1264)
+  const double chi = !ROT ? zdtrd : (DIR ? zdtrd * LD1(f.msfu + o2) : zdtrd * LD1(f.rmv + o2 + si) * LD1(f.mx + o2));
+  const double clo = !ROT ? zdtrd : (DIR ? zdtrd * LD1(f.msfu + o2) : zdtrd * LD1(f.rmv + o2) * LD1(f.mx + o2));
+  const double zrfhi = chi * 2.0 * fmz / (fmz + LD1(f.fmz + o + st));   // zrfmn / zrfme
+  const double zrflo = clo * 2.0 * fmz / (fmz + LD1(f.fmz + o - st));   // zrfms / zrfmw
+  const double mx2 = ROT ? 0.0 : LD1(f.mx2 + o2);
   const double dvf = (vr[1] * zrfhi - vr[0] * zrflo);
   const bool cw = (!DIR) && (j == g.jci1), ce = (!DIR) && (j == g.jci2);
   const long long ow = (long long)g.jce1 + (long long)i * si + (long long)k * sk, oe = ow + (g.jce2 - g.jce1);
@@ -174,7 +182,8 @@ __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_WAFH) k_mo_wafh(const Geom g,
     }
     double* pp = f.adv[n];
     const double zdv = dvf * pp[o];
-    const double out = wc0 + mx2 * (flux[0] * zrflo - flux[1] * zrfhi + zdv);
+    const double out = ROT ? (wc0 + flux[0] * zrflo - flux[1] * zrfhi + zdv)
+                           : (wc0 + mx2 * (flux[0] * zrflo - flux[1] * zrfhi + zdv));
     if (DIR) {
       pp[o] = out;
     } else {
@@ -359,16 +368,22 @@ void launch_mo_waf(const Geom& g, const MoFields& f, const MoScalars& s, int pas
   // RCM_MO_WAF: bit 0 = one-cell meridional kernel, bit 1 = one-cell zonal kernel (default 3: measured faster on B200 than the 4-cell kernels, profiles/r1_moloch.md)
   static int mode = -1;
   if (mode < 0) { const char* e = std::getenv("RCM_MO_WAF"); mode = e ? std::atoi(e) : 3; }
-  const int md = (g.gl | g.gr | g.gb | g.gt) ? 3 : mode;   // the 4-cell kernels clamp to the tile: single rank only
+  const int md = ((g.gl | g.gr | g.gb | g.gt) || s.rotllr) ? 3 : mode;   // the 4-cell kernels: single rank, non-ROTLLR only
   if (!(passes & 2)) {}
   else if (md & 1) {
-    if (s.nf == 7) RCM_LAUNCH((k_mo_wafh<7, 0>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
-    else RCM_LAUNCH((k_mo_wafh<6, 0>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+    if (s.rotllr) {
+      if (s.nf == 7) RCM_LAUNCH((k_mo_wafh<7, 0, true>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+      else RCM_LAUNCH((k_mo_wafh<6, 0, true>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+    } else if (s.nf == 7) RCM_LAUNCH((k_mo_wafh<7, 0, false>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+    else RCM_LAUNCH((k_mo_wafh<6, 0, false>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
   } else RCM_LAUNCH(k_mo_wafy4, grid3(nj, (ni + RCM_MO_NC - 1) / RCM_MO_NC, g.kz, b), b, st, g, f, s);
   if (!(passes & 4)) {}
   else if (md & 2) {
-    if (s.nf == 7) RCM_LAUNCH((k_mo_wafh<7, 1>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
-    else RCM_LAUNCH((k_mo_wafh<6, 1>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+    if (s.rotllr) {
+      if (s.nf == 7) RCM_LAUNCH((k_mo_wafh<7, 1, true>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+      else RCM_LAUNCH((k_mo_wafh<6, 1, true>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+    } else if (s.nf == 7) RCM_LAUNCH((k_mo_wafh<7, 1, false>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
+    else RCM_LAUNCH((k_mo_wafh<6, 1, false>), grid3(nj, ni, g.kz, b), b, st, g, f, s);
   } else RCM_LAUNCH(k_mo_wafx4, grid3((nj + RCM_MO_NC - 1) / RCM_MO_NC, ni, g.kz, b), b, st, g, f, s);
 }
 void launch_mo_restag(const Geom& g, const MoFields& f, cudaStream_t st) {

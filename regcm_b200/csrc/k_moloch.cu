@@ -1,6 +1,6 @@
 // MOLOCH core (idynamic = 3): sound sub-steps.
 //   k_mo_pre    tvirt, tetav at the head of `moloch`        Main/mod_moloch.F90:251-301
-//   k_mo_div    horizontal part of the divergence (Eq. 16)  :806-824 (non-ROTLLR)
+//   k_mo_div    horizontal part of the divergence (Eq. 16)  :775-793 (ROTLLR), :806-824
 //   k_mo_w      filt3d + full divergence + implicit w (tridiagonal, Eq. 19) + new Exner function
 //                                                           :549-569,743-768,826-925,1022-1038
 //   k_mo_uv     horizontal momentum (Eq. 17, 18)            :975-1012
@@ -34,6 +34,14 @@ __global__ void k_mo_div(const Geom g, const MoFields f, const MoScalars s) {
   const int i = g.ice1 - g.gb + blockIdx.y * blockDim.y + threadIdx.y;
   const int k = 1 + blockIdx.z;
   if (j > g.jce2 + g.gr || i > g.ice2 + g.gt) return;
+  if (s.rotllr) {   // :775-793
+    const double zum = s.zdtrdx * L3(f.u, j, i, k) * L3(f.zru, j, i, k);
+    const double zup = s.zdtrdx * L3(f.u, j + 1, i, k) * L3(f.zru, j + 1, i, k);
+    const double zvm = s.zdtrdy * L3(f.v, j, i, k) * L3(f.zrv, j, i, k) * L2(f.rmv, j, i);
+    const double zvp = s.zdtrdy * L3(f.v, j, i + 1, k) * L3(f.zrv, j, i + 1, k) * L2(f.rmv, j, i + 1);
+    P3(f.zdiv, j, i, k) = (zup - zum) + (zvp - zvm);
+    return;
+  }
   const double zum = L3(f.u, j, i, k) * L2(f.rmu, j, i) * L3(f.zru, j, i, k);
   const double zup = L3(f.u, j + 1, i, k) * L2(f.rmu, j + 1, i) * L3(f.zru, j + 1, i, k);
   const double zvm = L3(f.v, j, i, k) * L2(f.rmv, j, i) * L3(f.zrv, j, i, k);
@@ -107,7 +115,7 @@ __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_MOW) k_mo_w(const Geom g, con
   const int kz = g.kz, kzp1 = g.kzp1;
   const bool interior = (j >= g.jci1 && j <= g.jci2 && i >= g.ici1 && i <= g.ici2);
   const double hx0 = L2(f.hx, j, i), hx1 = L2(f.hx, j + 1, i), hy0 = L2(f.hy, j, i), hy1 = L2(f.hy, j, i + 1);
-  const double mx2 = L2(f.mx2, j, i);
+  const double mx2 = s.rotllr ? L2(f.mx, j, i) : L2(f.mx2, j, i);   // mx (ROTLLR, :798) or mx**2 (:829)
   const double zdtrdz = s.zdtrdz, zcs2 = s.zcs2, egdts = s.egdts, rjs = (double)jsound;
   // winds of level k (carried) and k-1
   double u0 = L3(f.u, j, i, kz), u1 = L3(f.u, j + 1, i, kz), v0 = L3(f.v, j, i, kz), v1 = L3(f.v, j, i + 1, kz);
@@ -225,7 +233,7 @@ __global__ void k_mo_uv(const Geom g, const MoFields f, const MoScalars s) {
   if (j <= g.jce2) {  // v point
     double vn = L3(f.v, j, i, k);
     if (i >= g.idii1 && i <= g.idii2 && j >= g.jci1 && j <= g.jci2) {
-      const double zcy = s.zdtrdy * L2(f.msfv, j, i);
+      const double zcy = s.rotllr ? s.zdtrdy : s.zdtrdy * L2(f.msfv, j, i);   // :956 / :997
       const double zfz = 0.25 * (L3(f.deltaw, j, i - 1, k) + L3(f.deltaw, j, i - 1, k + 1) + L3(f.deltaw, j, i, k) + L3(f.deltaw, j, i, k + 1)) + s.egdts;
       const double zrom1v = 0.5 * cpd * (L3(f.tetav, j, i - 1, k) + L3(f.tetav, j, i, k));
       const double zcor1v = L2(f.coriov, j, i) * 0.25 * (L3(f.u, j, i, k) + L3(f.u, j + 1, i, k) + L3(f.u, j, i - 1, k) + L3(f.u, j + 1, i - 1, k));

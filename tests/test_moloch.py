@@ -111,7 +111,8 @@ def test_oracle_moloch_long_run_with_record_change():
 
 MOLOCH_VARIANTS = [{}, {"iboudy": 1}, {"iboudy": 0}, {"ipptls": 0}, {"ifrayd": 0}, {"mo_nzfilt": 0},
                    {"mo_nadv": 2, "mo_nsound": 4}, {"mo_nadv": 1, "mo_nsound": 1}, {"mo_anu2": 0.0},
-                   {"flat": True, "unit_map": True}, {"noise": False}, {"mo_a0": 0.1, "mo_b0": 0.6}]
+                   {"flat": True, "unit_map": True}, {"noise": False}, {"mo_a0": 0.1, "mo_b0": 0.6},
+                   {"mo_rotllr": 1}, {"mo_rotllr": 1, "ipptls": 0, "iboudy": 1}]
 
 
 @pytest.mark.parametrize("kw", MOLOCH_VARIANTS, ids=lambda k: "-".join(f"{a}{b}" for a, b in k.items()) or "default")
@@ -151,8 +152,8 @@ def test_emu_moloch_small_shape_and_cloud_water(emu_lib):
 
 
 def test_emu_moloch_analytic_cases(emu_lib):
-    for test in (1, 2):
-        case = _analytic_case(test)
+    for test, rot in ((1, 0), (2, 0), (1, 1), (2, 1)):    # also through the ROTLLR branches
+        case = _analytic_case(test, mo_rotllr=rot)
         core = capi.DynCore(emu_lib, case.cfg)
         synth.load_case(core, case)
         core.step(10)
