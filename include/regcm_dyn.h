@@ -152,7 +152,8 @@ typedef struct rcm_cfg {
   /* &coreparam */
   int32_t idynamic; /* 1 hydrostatic, 2 non-hydrostatic, 3 MOLOCH          */
   /* &physicsparam (dynamics-relevant switches only) */
-  int32_t iboudy;   /* 0 fixed, 1 linear relax., 5 exponential relax.      */
+  int32_t iboudy;   /* 0 fixed, 1 linear relax., 5 exponential relax.;
+                     * 4 sponge (idynamic = 3 only)                         */
   int32_t idiffu;   /* 1 = 4th-order (only value implemented)              */
   int32_t ipptls;   /* >0: hydrometeors advected, water loading in w       */
   /* &nonhydroparam */

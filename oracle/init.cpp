@@ -105,6 +105,17 @@ void Oracle::setup_bdycon() {
     double xfun = (double)(nspgd - n) / (double)(nspgd - 2);
     fcd(n) = fnudge * xfun; gcd(n) = gnudge * xfun;
   }
+  if (iboudy == 4) {   // :237-250 (MOLOCH only in this restatement)
+    for (int k = 2; k <= nspgd - 1; ++k) wgtd(k) = d_one;
+    if (nspgd - 1 >= 2) wgtd(2) = 0.20;
+    if (nspgd - 1 >= 3) wgtd(3) = 0.55;
+    if (nspgd - 1 >= 4) wgtd(4) = 0.80;
+    if (nspgd - 1 >= 5) wgtd(5) = 0.95;
+    for (int k = 2; k <= nspgx - 1; ++k) wgtx(k) = d_one;
+    if (nspgx - 1 >= 2) wgtx(2) = 0.4;
+    if (nspgx - 1 >= 3) wgtx(3) = 0.7;
+    if (nspgx - 1 >= 4) wgtx(4) = 0.9;
+  }
   if (iboudy == 5) {
     std::vector<double> anudge(kz + 1);
     for (int k = 1; k <= kz; ++k) {

@@ -221,6 +221,10 @@ struct Oracle {
   void xtoustag(const A3& ux, A3& u);
   void xtovstag(const A3& vx, A3& v);
   void mo_boundary();
+  A1 wgtx, wgtd;   // sponge weights (Main/mod_bdycod.F90:237-250)
+  void mosponge3d(A3& f, const V3dBound& bnd);
+  void mosponge4d3d(A4& f, const V3dBound& bnd, int n);
+  void mospongeuv(A3& fu, A3& fv, const V3dBound& bu, const V3dBound& bv);
   void monudge3d(int ibdy, A3& f, const V3dBound& bnd);
   void monudge4d3d(int ibdy, A4& f, const V3dBound& bnd, int n);
   void monudgeuv(int ibdy, A3& fu, A3& fv, const V3dBound& bu, const V3dBound& bv);

@@ -97,6 +97,7 @@ int Oracle::create_moloch() {
   hefc.alloc(2, nspgx - 1, 1, kz); hegc.alloc(2, nspgx - 1, 1, kz);
   hefd.alloc(2, nspgd - 1, 1, kz); hegd.alloc(2, nspgd - 1, 1, kz);
   fg1.alloc(jde1, jde2, ide1, ide2, 1, kzp1); fg2.alloc(jde1, jde2, ide1, ide2, 1, kz);
+  wgtx.alloc(2, nspgx - 1); wgtd.alloc(2, nspgd - 1);
   setup_boundaries(false, false, ba_cr);   // Main/mod_params.F90:1788-1791
   setup_boundaries(true, false, ba_ut);
   setup_boundaries(false, true, ba_vt);
@@ -741,6 +742,55 @@ void Oracle::monudgeuv(int ibdy, A3& fu, A3& fv, const V3dBound& bu, const V3dBo
   }
 }
 
+// ---- sponge, iboudy = 4: mosponge3d (Main/mod_bdycod.F90:2996-3063), mosponge4d (:2665-2733),
+// mospongeuv (:2815-2925) ----
+void Oracle::mosponge3d(A3& f, const V3dBound& bnd) {
+  if (!ba_cr.havebound) return;
+  const int nk = f.n3;
+  const I2* masks[4] = {&ba_cr.bsouth, &ba_cr.bnorth, &ba_cr.bwest, &ba_cr.beast};
+  const int cnt[4] = {ba_cr.ns, ba_cr.nn, ba_cr.nw, ba_cr.ne};
+  for (int q = 0; q < 4; ++q) {
+    if (cnt[q] == 0) continue;
+    for (int k = 1; k <= nk; ++k)
+      for (int i = ici1; i <= ici2; ++i)
+        for (int j = jci1; j <= jci2; ++j) {
+          if (!(*masks[q])(j, i)) continue;
+          const int ib = ba_cr.ibnd(j, i);
+          f(j, i, k) = f(j, i, k) + (d_one - wgtx(ib)) * bnd.bt(j, i, k);
+        }
+  }
+}
+
+void Oracle::mosponge4d3d(A4& q, const V3dBound& bnd, int n) {
+  A3 tmp; tmp.alloc(q.l1, q.l1 + q.n1 - 1, q.l2, q.l2 + q.n2 - 1, q.l3, q.l3 + q.n3 - 1);
+  const size_t sz = tmp.d.size();
+  std::copy(q.d.begin() + (size_t)(n - q.l4) * sz, q.d.begin() + (size_t)(n - q.l4 + 1) * sz, tmp.d.begin());
+  mosponge3d(tmp, bnd);
+  std::copy(tmp.d.begin(), tmp.d.end(), q.d.begin() + (size_t)(n - q.l4) * sz);
+}
+
+void Oracle::mospongeuv(A3& fu, A3& fv, const V3dBound& bu, const V3dBound& bv) {
+  if (!ba_ut.havebound && !ba_vt.havebound) return;
+  struct Pass { bool isu; const I2* mask; int cnt; bool dw; };
+  const Pass P[8] = {{true, &ba_ut.bsouth, ba_ut.ns, false}, {false, &ba_vt.bsouth, ba_vt.ns, true},
+                     {true, &ba_ut.bnorth, ba_ut.nn, false}, {false, &ba_vt.bnorth, ba_vt.nn, true},
+                     {true, &ba_ut.bwest, ba_ut.nw, true},   {false, &ba_vt.bwest, ba_vt.nw, false},
+                     {true, &ba_ut.beast, ba_ut.ne, true},   {false, &ba_vt.beast, ba_vt.ne, false}};
+  for (const Pass& p : P) {
+    if (p.cnt == 0) continue;
+    A3& f = p.isu ? fu : fv;
+    const V3dBound& b = p.isu ? bu : bv;
+    const int i1 = p.isu ? ici1 : idi1, i2 = p.isu ? ici2 : idi2, j1 = p.isu ? jdi1 : jci1, j2 = p.isu ? jdi2 : jci2;
+    for (int k = 1; k <= kz; ++k)
+      for (int i = i1; i <= i2; ++i)
+        for (int j = j1; j <= j2; ++j) {
+          if (!(*p.mask)(j, i)) continue;
+          const int ib = (p.isu ? ba_ut : ba_vt).ibnd(j, i);
+          f(j, i, k) = f(j, i, k) + (d_one - (p.dw ? wgtd(ib) : wgtx(ib))) * b.bt(j, i, k);
+        }
+  }
+}
+
 // ---- Main/mod_bdycod.F90:5047-5065 ----
 void Oracle::moraydamp(const A3& z, A3& var, const V3dBound& bnd, int j1, int j2, int i1, int i2, int k1, int k2) {
   const double xt = xbctime + dt;
@@ -761,6 +811,11 @@ void Oracle::mo_boundary() {
     monudge3d(iboudy, m_t, xtb);
     monudge4d3d(iboudy, m_qx, xqb, iqv);
     monudgeuv(iboudy, m_u, m_v, xub, xvb);
+  } else if (iboudy == 4) {
+    mosponge3d(m_pai, xpaib);
+    mosponge3d(m_t, xtb);
+    mosponge4d3d(m_qx, xqb, iqv);
+    mospongeuv(m_u, m_v, xub, xvb);
   }
 }
 
@@ -857,6 +912,33 @@ void Oracle::bdyval_moloch() {
   for (int k = 1; k <= kz; ++k) for (int i = ici1; i <= ici2; ++i) cell(jce2, i, k);
   for (int k = 1; k <= kz; ++k) for (int j = jce1; j <= jce2; ++j) cell(j, ice1, k);
   for (int k = 1; k <= kz; ++k) for (int j = jce1; j <= jce2; ++j) cell(j, ice2, k);
+  if (cfg.iboudy == 3 || cfg.iboudy == 4) {   // qv by inflow/outflow (:1813-1890)
+    A3 &u = m_u, &v = m_v;
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ici1; i <= ici2; ++i) {
+        double qext = qx(jce1, i, k, iqv), qint = qx(jci1, i, k, iqv);
+        double windavg = u(jde1, i, k) + u(jdi1, i, k);
+        qx(jce1, i, k, iqv) = (windavg > d_zero) ? qext : qint;
+      }
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ici1; i <= ici2; ++i) {
+        double qext = qx(jce2, i, k, iqv), qint = qx(jci2, i, k, iqv);
+        double windavg = u(jde2, i, k) + u(jdi2, i, k);
+        qx(jce2, i, k, iqv) = (windavg < d_zero) ? qext : qint;
+      }
+    for (int k = 1; k <= kz; ++k)
+      for (int j = jce1; j <= jce2; ++j) {
+        double qext = qx(j, ice1, k, iqv), qint = qx(j, ici1, k, iqv);
+        double windavg = v(j, ide1, k) + v(j, idi1, k);
+        qx(j, ice1, k, iqv) = (windavg > d_zero) ? qext : qint;
+      }
+    for (int k = 1; k <= kz; ++k)
+      for (int j = jce1; j <= jce2; ++j) {
+        double qext = qx(j, ice2, k, iqv), qint = qx(j, ici2, k, iqv);
+        double windavg = v(j, ide2, k) + v(j, idi2, k);
+        qx(j, ice2, k, iqv) = (windavg < d_zero) ? qext : qint;
+      }
+  }
   if (cfg.ipptls > 0) {   // .not. present_qc, bdyflow (:1963-2100)
     A3 &u = m_u, &v = m_v;
     for (int n = iqfrst; n <= iqlst; ++n) {

@@ -28,7 +28,7 @@ int Oracle::create(const rcm_cfg& c) {
   if (hydro && (c.nsplit < 1 || c.nsplit > c.kz)) { err = "oracle: nsplit out of range"; return RCM_ERR_ARG; }
   nsplit = hydro ? c.nsplit : 0;
   if (c.idiffu != 1) { err = "oracle: only idiffu=1"; return RCM_ERR_ARG; }
-  if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 5)) { err = "oracle: iboudy must be 0,1,5"; return RCM_ERR_ARG; }
+  if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 5 || (c.idynamic == 3 && c.iboudy == 4))) { err = "oracle: iboudy must be 0,1,5 (4: MOLOCH only)"; return RCM_ERR_ARG; }
   if (c.nqx != 2) { err = "oracle: nqx must be 2"; return RCM_ERR_ARG; }
   jx = c.jx; iy = c.iy; kz = c.kz; kzp1 = kz + 1; nqx = c.nqx;
   iqv = 1; iqc = 2; iqfrst = 2; iqlst = nqx;

@@ -283,7 +283,8 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   if (h->hydro && c.nproc != 1) return bail(RCM_ERR_ARG, "idynamic=1 runs on one rank only (BASELINE configs[0] is a single-rank case)");
   if (h->hydro && (c.nsplit < 1 || c.nsplit > RCM_MAXSPLIT || c.nsplit > c.kz)) return bail(RCM_ERR_ARG, "nsplit must be 1..4");
   if (c.idiffu != 1) return bail(RCM_ERR_ARG, "only idiffu=1 is implemented");
-  if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 5)) return bail(RCM_ERR_ARG, "iboudy must be 0, 1 or 5");
+  if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 5 || (c.idynamic == 3 && c.iboudy == 4)))
+    return bail(RCM_ERR_ARG, "iboudy must be 0, 1 or 5 (4 = sponge: MOLOCH core only)");
   if (c.nqx != 2) return bail(RCM_ERR_ARG, "nqx must be 2 (qv,qc)");
   if (c.jx < 2 * c.nspgx || c.iy < 2 * c.nspgx || c.kz < 3) return bail(RCM_ERR_ARG, "domain too small for the relaxation zone");
   int ndev = 0;

@@ -43,6 +43,19 @@ __global__ void k_mo_nudge_a(const Geom g, const MoFields f, const MoScalars s, 
   const int nsp = dtab ? s.nspgd : s.nspgx;
   const double xf = LD1((dtab ? f.xfd : f.xfc) + ib + nsp * (k - 1)), xg = LD1((dtab ? f.xgd : f.xgc) + ib + nsp * (k - 1));
   const long long o = ((long long)(k - 1) * nrim + p) * 3;
+  if (s.iboudy == 4) {   // sponge: f + (1 - wgt(ib)) * bt, the tables hold wgt (mosponge*, Main/mod_bdycod.F90:2665-3063)
+    const double w1 = 1.0 - xf;
+    if (which == 0) {
+      f.rimbuf[o + 0] = P3(f.pai, j, i, k) + w1 * L3(f.xpbt, j, i, k);
+      f.rimbuf[o + 1] = P3(f.t, j, i, k) + w1 * L3(f.xtbt, j, i, k);
+      f.rimbuf[o + 2] = P3(f.qv, j, i, k) + w1 * L3(f.xqbt, j, i, k);
+    } else if (which == 1) {
+      f.rimbuf[o] = P3(f.u, j, i, k) + w1 * L3(f.xubt, j, i, k);
+    } else {
+      f.rimbuf[o] = P3(f.v, j, i, k) + w1 * L3(f.xvbt, j, i, k);
+    }
+    return;
+  }
   if (which == 0) {
     f.rimbuf[o + 0] = mo_nudged(f.xpb0, f.xpbt, f.pai, s.xt, xf, xg, si, sk, j, i, k);
     f.rimbuf[o + 1] = mo_nudged(f.xtb0, f.xtbt, f.t, s.xt, xf, xg, si, sk, j, i, k);
@@ -122,6 +135,27 @@ __global__ void k_mo_bdyval_c(const Geom g, const MoFields f, const MoScalars s,
     P3(f.t, j, i, k) = L3(f.xtb0, j, i, k) + s.xt * L3(f.xtbt, j, i, k);
     P3(f.qv, j, i, k) = L3(f.xqb0, j, i, k) + s.xt * L3(f.xqbt, j, i, k);
     P3(f.pai, j, i, k) = L3(f.xpb0, j, i, k) + s.xt * L3(f.xpbt, j, i, k);
+  }
+  if (s.iboudy == 3 || s.iboudy == 4) {   // qv by inflow/outflow (:1813-1890): west/east rows first, then the full south/north rows
+    const bool west = g.has_bdyleft && (j == g.jce1), east = g.has_bdyright && (j == g.jce2),
+               south = g.has_bdybottom && (i == g.ice1), north = g.has_bdytop && (i == g.ice2);
+    // value of a west/east rim point of row ii after the first pass (ii is an interior row)
+    auto we = [&](const int ii) {
+      const int jin = west ? g.jci1 : g.jci2, jd = west ? g.jde1 : g.jde2, jdn = west ? g.jdi1 : g.jdi2;
+      const double qext = (s.iboudy == 0) ? L3(f.xqb0, j, ii, k) : L3(f.xqb0, j, ii, k) + s.xt * L3(f.xqbt, j, ii, k);
+      const double qint = P3(f.qv, jin, ii, k);
+      const double windavg = P3(f.u, jd, ii, k) + P3(f.u, jdn, ii, k);
+      return (west ? (windavg > 0.0) : (windavg < 0.0)) ? qext : qint;
+    };
+    if (south || north) {
+      const int iin = south ? g.ici1 : g.ici2, idd = south ? g.ide1 : g.ide2, idn = south ? g.idi1 : g.idi2;
+      const double qext = P3(f.qv, j, i, k);                                    // just set from the record above
+      const double qint = (west || east) ? we(iin) : P3(f.qv, j, iin, k);       // corner: the west/east pass came first
+      const double windavg = P3(f.v, j, idd, k) + P3(f.v, j, idn, k);
+      P3(f.qv, j, i, k) = (south ? (windavg > 0.0) : (windavg < 0.0)) ? qext : qint;
+    } else {
+      P3(f.qv, j, i, k) = we(i);
+    }
   }
   if (s.ipptls > 0) {
     const bool west = g.has_bdyleft && (j == g.jce1), east = g.has_bdyright && (j == g.jce2),

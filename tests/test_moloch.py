@@ -112,7 +112,7 @@ def test_oracle_moloch_long_run_with_record_change():
 MOLOCH_VARIANTS = [{}, {"iboudy": 1}, {"iboudy": 0}, {"ipptls": 0}, {"ifrayd": 0}, {"mo_nzfilt": 0},
                    {"mo_nadv": 2, "mo_nsound": 4}, {"mo_nadv": 1, "mo_nsound": 1}, {"mo_anu2": 0.0},
                    {"flat": True, "unit_map": True}, {"noise": False}, {"mo_a0": 0.1, "mo_b0": 0.6},
-                   {"mo_rotllr": 1}, {"mo_rotllr": 1, "ipptls": 0, "iboudy": 1}]
+                   {"mo_rotllr": 1}, {"mo_rotllr": 1, "ipptls": 0, "iboudy": 1}, {"iboudy": 4}, {"iboudy": 4, "ipptls": 0}]
 
 
 @pytest.mark.parametrize("kw", MOLOCH_VARIANTS, ids=lambda k: "-".join(f"{a}{b}" for a, b in k.items()) or "default")
@@ -163,7 +163,7 @@ def test_emu_moloch_analytic_cases(emu_lib):
 
 
 def test_moloch_rejects_unsupported(emu_lib):
-    for kw in ({"mo_nadv": 0}, {"ipptls": 2}, {"kz": 3}):
+    for kw in ({"mo_nadv": 0}, {"ipptls": 2}, {"kz": 3}, {"iboudy": 3}):
         case = synth.make_case("tinym")
         cfg = case.cfg
         for k, v in kw.items():
