@@ -1,5 +1,6 @@
 """Parity tests of the MOLOCH core (idynamic = 3) on the GPU: the CUDA library through the C ABI
-against the CPU oracle on the same seeded synthetic inputs, against the committed golden fixtures
+against the CPU oracle on the same seeded synthetic inputs (all option variants of tests/test_moloch.py,
+including the ROTLLR projection branches and the sponge boundary option), against the committed golden fixtures
 tests/golden/mo_*.npz, and through the reference's own analytic cases at a size the oracle is not
 run at.  Tolerances (double precision, no FMA contraction on either side; the arithmetic differences
 are CUDA libm `pow`/`exp` vs glibc, <= 2 ulp, in paicompute and in the p / ps closure):
