@@ -3,15 +3,15 @@
 //   vmodes (+ vtlaps, vchekt, vcheke, vorder, vnorml, invmtrx)  Main/mod_vmodes.F90:86-647
 //   spinit   Main/mod_split.F90:75-239      splitf  :243-461      spstep  :463-669
 // The eigen-solver and the matrix inverse stand in for the reference's vendored
-// EISPACK `rg` and LINPACK `sgefa/sgedi` (Main/netlib): generic numerics shared
-// with the product through regcm_b200/csrc/linalg_small.hpp and pinned
-// independently against LAPACK in tests/test_oracle_hydro.py.
+// EISPACK `rg` and LINPACK `sgefa/sgedi` (Main/netlib): oracle/linalg_ref.hpp, a solver of
+// its own (NOT the product's regcm_b200/csrc/linalg_small.hpp), pinned against LAPACK in
+// tests/test_hydro.py::test_vmodes_against_lapack.
 #include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <limits>
 
-#include "../regcm_b200/csrc/linalg_small.hpp"
+#include "linalg_ref.hpp"
 #include "model.hpp"
 
 namespace orc {
@@ -183,7 +183,7 @@ void Oracle::vmodes() {
   vm_tau0.d = vm_tau.d;
   // eigenproblem (:358-363): rg -> vcheke -> vorder -> vnorml
   std::vector<double> wr, wi, z;
-  int ier = rcm_la::eig_real(kz, vm_tau.d, wr, wi, z);
+  int ier = orc_la::eig_real(kz, vm_tau.d, wr, wi, z);
   if (ier) vm_numerr++;
   {  // vcheke :571-593
     int numneg = 0, nimag = 0; double emax = d_zero;
@@ -217,10 +217,10 @@ void Oracle::vmodes() {
     }
   }
   std::vector<double> inv;
-  if (rcm_la::invert(kz, zmatx.d, inv)) vm_numerr++;
+  if (orc_la::invert(kz, zmatx.d, inv)) vm_numerr++;
   zmatxr.d = inv;
   std::vector<double> hydror;
-  if (rcm_la::invert(kz, hydros.d, hydror)) vm_numerr++;
+  if (orc_la::invert(kz, hydros.d, hydror)) vm_numerr++;
   auto HR = [&](int i, int j) { return hydror[(size_t)(i - 1) + (size_t)kz * (j - 1)]; };
   // daley's variational scheme arrays (:389-416): varpa1
   for (int k = 1; k <= kz; ++k) hweigh[k] = d_zero;

@@ -318,6 +318,23 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   g.jcross1 = 1; g.jcross2 = c.jx - 1; g.icross1 = 1; g.icross2 = c.iy - 1;
 
   const int nj = g.jde2 - g.jde1 + 1, ni = g.ide2 - g.ide1 + 1;
+  if (c.nproc > 1) {
+    // Every rank checks EVERY tile, so that all ranks reach the same verdict.  A tile with neighbours on both
+    // sides must hold the edge slab it sends: RCM_EHALO columns of estore for the upper radiative BC (a tile on
+    // a physical boundary may be narrower: the columns it cannot supply lie outside the clamped 13x13 window,
+    // Main/mod_sound.F90:551-561); the reference rejects tiles under 3x3 (Main/mpplib/mod_mppparam.F90:1365).
+    const int need = (c.idynamic == 2 && c.ifupr == 1) ? RCM_EHALO : RCM_HALO;
+    for (int q = 0; q < cj; ++q) {
+      int lo, hi; split_range(c.jx, cj, q, lo, hi);
+      const int n = hi - lo + 1;
+      if (n < 3 || (q > 0 && q < cj - 1 && n < need)) return bail(RCM_ERR_ARG, "tile too narrow along j for the halo width (interior tiles need >= 6 points with ifupr = 1; all tiles >= 3)");
+    }
+    for (int q = 0; q < ci; ++q) {
+      int lo, hi; split_range(c.iy, ci, q, lo, hi);
+      const int n = hi - lo + 1;
+      if (n < 3 || (q > 0 && q < ci - 1 && n < need)) return bail(RCM_ERR_ARG, "tile too narrow along i for the halo width (interior tiles need >= 6 points with ifupr = 1; all tiles >= 3)");
+    }
+  }
   h->nj_pad = ((nj + 2 * RCM_HALO + 15) / 16) * 16;
   h->ni_pad = ni + 2 * RCM_HALO;
   g.si = h->nj_pad;
@@ -1388,6 +1405,35 @@ static int tend(rcm_dyn* h) {
   return RCM_OK;
 }
 
+// One collective for the per-rank verdicts of a call: vmax[] is max-reduced, vsum[] sum-reduced, so that every
+// rank takes the same return path (the reference aborts all ranks together, Share/mod_message.F90:90-103).
+// Small worlds use ONE all-gather written as a sum of one-hot slots; NaN survives both reductions.
+static int reduce_verdicts(rcm_dyn* h, double* vmax, int nmax, double* vsum, int nsum) {
+  const int np = h->cfg.nproc, n = nmax + nsum;
+  if (np <= 1) return 0;
+  if (np * n <= 64) {
+    double buf[64];
+    for (double& x : buf) x = 0.0;
+    for (int q = 0; q < nmax; ++q) buf[h->cfg.myid * n + q] = vmax[q];
+    for (int q = 0; q < nsum; ++q) buf[h->cfg.myid * n + nmax + q] = vsum[q];
+    if (h->halo.allreduce_host(buf, np * n, 0)) return -5;
+    for (int q = 0; q < nmax; ++q) {
+      double m = buf[q];
+      for (int r = 1; r < np; ++r) { const double v = buf[r * n + q]; if (v != v || (m == m && v > m)) m = v; }
+      vmax[q] = m;
+    }
+    for (int q = 0; q < nsum; ++q) {
+      double t = 0.0;
+      for (int r = 0; r < np; ++r) t += buf[r * n + nmax + q];
+      vsum[q] = t;
+    }
+    return 0;
+  }
+  if (nmax > 0 && h->halo.allreduce_host(vmax, nmax, 1)) return -5;
+  if (nsum > 0 && h->halo.allreduce_host(vsum, nsum, 0)) return -5;
+  return 0;
+}
+
 extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
   if (!h) return RCM_ERR_ARG;
   if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_step before rcm_dyn_init");
@@ -1418,12 +1464,14 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
     CUDA_OK(cudaMemcpy(pb, h->mf.psbits, sizeof(pb), cudaMemcpyDeviceToHost));
     h->nan_flag = nanf;
     if (nsteps > 0 && pb[0]) { const unsigned long long mn = ~pb[1]; std::memcpy(&h->ps_max, &pb[0], 8); std::memcpy(&h->ps_min, &mn, 8); }
+    int halo_err = h->halo.take_error();
     if (h->cfg.nproc > 1 && nsteps > 0) {   // maxall / minall of the reference (Main/mod_moloch.F90:440-441)
-      double v[3] = {h->ps_max, -h->ps_min, (double)nanf};
-      if (h->halo.allreduce_host(v, 3, 1)) return fail(h, RCM_ERR_NCCL, "allreduce (ps extremes) failed");
-      h->ps_max = v[0]; h->ps_min = -v[1]; nanf = (int)v[2]; h->nan_flag = nanf;
+      double v[4] = {h->ps_max, -h->ps_min, (double)nanf, (double)halo_err};
+      if (reduce_verdicts(h, v, 4, nullptr, 0)) return fail(h, RCM_ERR_NCCL, "allreduce (ps extremes) failed");
+      h->ps_max = v[0]; h->ps_min = -v[1]; nanf = (v[2] != 0.0); h->nan_flag = nanf; halo_err = (v[3] != 0.0);
     }
     CUDA_OK(cudaGetLastError());
+    if (halo_err) return fail(h, RCM_ERR_NCCL, "halo exchange: timed out waiting for a neighbour's edge data");
     if (nanf) return fail(h, RCM_ERR_CFL, "CFL violation: surface pressure is not a number (decrease dt)");   // Main/mod_moloch.F90:443-451
     return RCM_OK;
   }
@@ -1450,14 +1498,20 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
   h->last_ms = ms;
   prof_collect(h);
   if (rc) return rc;
-  if (h->halo.take_error()) return fail(h, RCM_ERR_NCCL, "halo exchange: timed out waiting for a neighbour's edge data");
+  int halo_err = h->halo.take_error();
   unsigned long long bits2[2] = {0, 0}, nq = 0; int nanf = 0;
   CUDA_OK(cudaMemcpy(bits2, f.cflbits, sizeof(bits2), cudaMemcpyDeviceToHost));
   CUDA_OK(cudaMemcpy(&nq, f.negq, sizeof(nq), cudaMemcpyDeviceToHost));
   CUDA_OK(cudaMemcpy(&nanf, f.nanflag, sizeof(nanf), cudaMemcpyDeviceToHost));
   double cfl, cfl_last; std::memcpy(&cfl, &bits2[1], sizeof(cfl)); std::memcpy(&cfl_last, &bits2[0], sizeof(cfl_last));
+  if (h->cfg.nproc > 1 && nsteps > 0) {   // every rank must reach the same verdict (the reference's fatal() aborts all of them)
+    double vm[4] = {cfl, cfl_last, (double)nanf, (double)halo_err}, vs[1] = {(double)nq};
+    if (reduce_verdicts(h, vm, 4, vs, 1)) return fail(h, RCM_ERR_NCCL, "allreduce (step verdicts) failed");
+    cfl = vm[0]; cfl_last = vm[1]; nanf = (vm[2] != 0.0); halo_err = (vm[3] != 0.0); nq = (unsigned long long)vs[0];
+  }
   h->max_cfl = cfl_last; h->neg_q = (int64_t)nq; h->nan_flag = nanf;
   CUDA_OK(cudaGetLastError());
+  if (halo_err) return fail(h, RCM_ERR_NCCL, "halo exchange: timed out waiting for a neighbour's edge data");
   if (nanf || cfl != cfl) return fail(h, RCM_ERR_NAN, "NaN in the acoustic solver");
   if (cfl > 1.0) {
     char buf[128]; std::snprintf(buf, sizeof(buf), "CFL violation: max sigma-dot CFL = %g", cfl);

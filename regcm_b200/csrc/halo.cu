@@ -144,7 +144,7 @@ int Halo::comm_init(const void* id, int id_bytes, std::string& err) {
       err = "halo buffer allocation failed"; return -5;
     }
   }
-  if (cudaMalloc(&red, 16 * sizeof(double)) != cudaSuccess) { err = "halo buffer allocation failed"; return -5; }
+  if (cudaMalloc(&red, 64 * sizeof(double)) != cudaSuccess) { err = "halo buffer allocation failed"; return -5; }
 #ifndef RCM_EMU
   if (setup_p2p(err)) return -5;
 #endif
@@ -184,7 +184,7 @@ int Halo::take_error() {
 
 int Halo::allreduce_host(double* v, int n, int op) {
   if (nproc <= 1) return 0;
-  if (!comm || n > 16) return -5;
+  if (!comm || n > 64) return -5;
 #ifdef RCM_EMU
   return g_emu_allreduce(v, n, op) ? -5 : 0;
 #else
@@ -308,13 +308,16 @@ __global__ void __launch_bounds__(256) k_x_pack(const XList L) {
 __global__ void __launch_bounds__(256) k_x_unpack(const XList L) {
   const int d = blockIdx.z, fi = blockIdx.y;
   if (!L.active[d]) return;
+  __shared__ int arrived;
   if (threadIdx.x == 0) {
+    arrived = 1;
     const long long t0 = clock64();
     while (ld_acquire_sys(L.flag_mine + d) < L.seq) {
-      if (clock64() - t0 > 20000000000LL) { atomicExch(L.err, 1); break; }  // ~10 s: report instead of hanging
+      if (clock64() - t0 > 20000000000LL) { atomicExch(L.err, 1); arrived = 0; break; }  // ~10 s: report instead of hanging
     }
   }
   __syncthreads();
+  if (!arrived) return;  // never scatter a stale receive buffer into the ghost cells; rcm_dyn_step returns RCM_ERR_NCCL
   const XField F = L.f[fi];
   const int nj = L.nj[d][F.grid], ni = L.ni[d][F.grid];
   const long long n = (long long)nj * ni * F.nk;

@@ -5,7 +5,7 @@ Tolerances (double precision, no FMA contraction on either side; the arithmetic
 differences are CUDA libm `pow`/`log` vs glibc, <= 2 ulp, in the vertical
 T advection, the log-linear qv flux, the geopotential and the log-p pressure
 gradient):
-  * vertical-mode tables (host code on both sides)  <= 1e-13 relative
+  * vertical-mode tables (two independent host solvers: oracle/linalg_ref.hpp vs csrc/linalg_small.hpp)  <= 1e-11 relative
   * work arrays after one step                       <= 1e-12 relative L-inf
   * prognostic fields after N <= 12 steps            <= 1e-10 relative L-inf
   * after 110 steps with a boundary-record change    <= 1e-8  relative L-inf
@@ -43,7 +43,7 @@ def test_hydro_tables_and_one_step(cuda_lib):
     case, core, ref = make_pair(cuda_lib, "small", idynamic=1)
     for t in (capi.T_HBAR, capi.T_ZMATX, capi.T_ZMATXR, capi.T_TAU, capi.T_VARPA1, capi.T_AM, capi.T_AN):
         a, b = core.get_table(t), ref.get_table(t)
-        assert np.abs(a - b).max() <= 1e-13 * np.abs(b).max(), t
+        assert np.abs(a - b).max() <= 1e-11 * np.abs(b).max(), t
     core.step(1); ref.step(1)
     w = work_errors(core, ref)
     _record("one_step_work", w)

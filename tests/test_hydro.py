@@ -1,6 +1,10 @@
 """Hydrostatic core (idynamic = 1, SURVEY.md §8 a3, a20-a22 and the hydrostatic
 branches of a4-a18): pins of the CPU restatement, and the kernel LOGIC check of
-the CUDA sources through the test-only host harness (tests/emu), bit for bit.
+the CUDA sources through the test-only host harness (tests/emu).  The oracle and the
+product solve the init-time vertical-mode eigenproblem with DIFFERENT solvers
+(oracle/linalg_ref.hpp vs regcm_b200/csrc/linalg_small.hpp), so the tables agree
+to round-off (<= 1e-11 relative) and the hydrostatic state is compared at 1e-11 instead
+of bit for bit; everything that does not depend on the tables still is bit-exact.
 
 The reference ships no golden vectors for this path; the in-tree behavioural
 pins it does hold are the `vmodes` self-tests (Main/mod_vmodes.F90:314-334:
@@ -106,6 +110,9 @@ def test_oracle_hydro_noise_parameters_decay():
     assert vals[-1][1] < vals[0][1]
 
 
+TOL_TABLE = 1e-11   # two independent eigen-solvers / inverses
+TOL_STATE = 1e-11   # relative L-inf per prognostic after 8 steps
+
 HYDRO_VARIANTS = [
     {}, {"iboudy": 1}, {"iboudy": 0}, {"ipptls": 0}, {"diffu_hgtf": 0}, {"upstream_mode": 0},
     {"stability_enhance": 0}, {"flat": True, "unit_map": True}, {"noise": False}, {"lstand": 0}, {"nsplit": 1}, {"nsplit": 3},
@@ -113,31 +120,34 @@ HYDRO_VARIANTS = [
 
 
 @pytest.mark.parametrize("kw", HYDRO_VARIANTS, ids=lambda k: "-".join(f"{a}{b}" for a, b in k.items()) or "default")
-def test_emu_hydro_bit_exact(emu_lib, kw):
+def test_emu_hydro_parity(emu_lib, kw):
     case, core, ref = make_pair(emu_lib, "tiny", oracle_checked=True, idynamic=1, **kw)
+    assert np.array_equal(core.get_table(capi.T_TAU0), ref.get_table(capi.T_TAU0))   # the matrix both solvers start from
     for t in (capi.T_HBAR, capi.T_ZMATX, capi.T_ZMATXR, capi.T_TAU, capi.T_VARPA1, capi.T_AM, capi.T_AN):
-        assert np.array_equal(core.get_table(t), ref.get_table(t))
+        a, b = core.get_table(t), ref.get_table(t)
+        assert np.abs(a - b).max() <= TOL_TABLE * np.abs(b).max(), t
     core.step(1); ref.step(1)
-    assert max(work_errors(core, ref).values()) == 0.0
+    assert max(work_errors(core, ref).values()) == 0.0   # the slow tendencies do not read the tables: bit for bit
     core.step(7); ref.step(7)
     errs = rel_errors(core, ref)
-    assert max(e[0] for e in errs.values()) == 0.0, errs
+    assert max(e[0] for e in errs.values()) <= TOL_STATE, errs
     dc, dr = core.diag(), ref.diag()
-    assert dc.ptntot == dr.ptntot and dc.pt2tot == dr.pt2tot and dc.lcount == dr.lcount == 8
+    assert abs(dc.ptntot - dr.ptntot) <= 1e-9 * abs(dr.ptntot) and abs(dc.pt2tot - dr.pt2tot) <= 1e-9 * abs(dr.pt2tot)
+    assert dc.lcount == dr.lcount == 8
 
 
 def test_emu_hydro_boundary_record_change(emu_lib):
     case, core, ref = make_pair(emu_lib, "tiny", idynamic=1, ibdyfrq=1)
     core.step(35); ref.step(35)   # record change at step 30 (dt = 120 s)
     assert core.diag().xbctime == ref.diag().xbctime == 6 * 120.0
-    assert max(e[0] for e in rel_errors(core, ref).values()) == 0.0
+    assert max(e[0] for e in rel_errors(core, ref).values()) <= 1e-10
 
 
 def test_emu_hydro_c1_shape(emu_lib):
     case, core, ref = make_pair(emu_lib, "C1")
     assert case.cfg.idynamic == 1 and (case.cfg.jx, case.cfg.iy, case.cfg.kz) == (64, 34, 18)
     core.step(3); ref.step(3)
-    assert max(e[0] for e in rel_errors(core, ref).values()) == 0.0
+    assert max(e[0] for e in rel_errors(core, ref).values()) <= TOL_STATE
 
 
 def test_emu_hydro_cloud_water_path(emu_lib):
@@ -147,7 +157,7 @@ def test_emu_hydro_cloud_water_path(emu_lib):
         c.set_state(capi.F_QC, capi.LEVEL_A, qc)
         c.set_state(capi.F_QC, capi.LEVEL_B, qc)
     core.step(8); ref.step(8)
-    assert max(e[0] for e in rel_errors(core, ref).values()) == 0.0
+    assert max(e[0] for e in rel_errors(core, ref).values()) <= TOL_STATE
     assert np.abs(ref.get_state(capi.F_QC)).max() > 0 and ref.diag().neg_q_points == 0
 
 

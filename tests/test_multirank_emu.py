@@ -175,3 +175,19 @@ def test_moloch_multirank_record_change_linear_relaxation(emu_lib, tmp_path):
     glob, _ = assemble_moloch(tmp_path, 4, cfg)
     for f in MOLOCH_FIELDS:
         np.testing.assert_array_equal(glob[f], ref[f] if ref[f].ndim == 3 else ref[f][:, :, None], err_msg=capi.FIELD_NAMES[f])
+
+
+def test_create_rejects_tiles_narrower_than_the_halo(emu_lib):
+    """a tile between two neighbours must hold the RCM_EHALO = 6 estore columns it sends for the upper
+    radiative BC (width-6 exchange, Main/mod_sound.F90:551-561); every rank checks every tile."""
+    cfg = synth.make_case("tiny", records=()).cfg          # 20 x 16
+    cfg.nproc, cfg.cpus_j, cfg.cpus_i = 4, 4, 1            # tiles of 5 columns: the two inner ones are too narrow
+    for myid in range(4):
+        cfg.myid = myid
+        with pytest.raises(capi.RcmError):
+            capi.DynCore(emu_lib, cfg)
+    cfg.ifupr, cfg.myid = 0, 1                              # without the radiative BC the width-2 halo fits
+    capi.DynCore(emu_lib, cfg).close()
+    cfg.nproc, cfg.cpus_j, cfg.cpus_i = 8, 8, 1            # 20 / 8: tiles of 2 columns are below the reference's 3 x 3 minimum
+    with pytest.raises(capi.RcmError):
+        capi.DynCore(emu_lib, cfg)
