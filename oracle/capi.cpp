@@ -81,6 +81,13 @@ int orc_get_zone(void* h, int dot, int32_t* out) {
     }
   return RCM_OK;
 }
+// test hook: make the negative-moisture sweep behave as on a decomposed domain (see repair_negative_qx)
+int orc_set_repair_tiles(void* h, int ncj, const int32_t* jstart, int nci, const int32_t* istart) {
+  Oracle* o = (Oracle*)h;
+  o->rt_j.assign(jstart, jstart + ncj);
+  o->rt_i.assign(istart, istart + nci);
+  return RCM_OK;
+}
 int orc_destroy(void* h) { delete (Oracle*)h; return RCM_OK; }
 
 }  // extern "C"

@@ -480,18 +480,7 @@ void Oracle::tend_hydro() {
     for (int k = 1; k <= kz; ++k)
       for (int i = ici1; i <= ici2; ++i)
         for (int j = jci1; j <= jci2; ++j) ac_qx(j, i, k, n) = ac_qx(j, i, k, n) + dt * qxten(j, i, k, n);
-  neg_q_points = 0;
-  for (int n = 1; n <= nqx; ++n)
-    for (int k = 1; k <= kz; ++k)
-      for (int i = ici1; i <= ici2; ++i)
-        for (int j = jci1; j <= jci2; ++j)
-          if (ac_qx(j, i, k, n) < d_zero) {
-            double s = 0.0;
-            for (int ii = i - 1; ii <= i + 1; ++ii)
-              for (int jj = j - 1; jj <= j + 1; ++jj) s += std::fabs(ac_qx(jj, ii, k, n));
-            ac_qx(j, i, k, n) = 0.01 * s / 9.0;
-            neg_q_points++;
-          }
+  repair_negative_qx();  // :381-393 (tendency.cpp)
   pressure_gradient_force();
   for (int k = 1; k <= kz; ++k)
     for (int i = idi1; i <= idi2; ++i)

@@ -137,6 +137,8 @@ struct Oracle {
   int last_istep = 0;
   bool cfl_error = false;
   int64_t neg_q_points = 0;
+  std::vector<int> rt_j, rt_i;  // first dot index of every tile along j / i (set_repair_tiles; empty = one domain)
+  void repair_negative_qx();
 
   // ---- hydrostatic core (idynamic = 1; oracle/hydro.cpp, oracle/split.cpp) ----
   bool hydro = false;

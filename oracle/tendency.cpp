@@ -409,19 +409,7 @@ void Oracle::tend() {
     for (int k = 1; k <= kz; ++k)
       for (int i = ici1; i <= ici2; ++i)
         for (int j = jci1; j <= jci2; ++j) ac_qx(j, i, k, n) = ac_qx(j, i, k, n) + dt * qxten(j, i, k, n);
-  neg_q_points = 0;
-  for (int n = 1; n <= nqx; ++n)
-    for (int k = 1; k <= kz; ++k)
-      for (int i = ici1; i <= ici2; ++i)
-        for (int j = jci1; j <= jci2; ++j)
-          if (ac_qx(j, i, k, n) < d_zero) {
-            // sum(abs(atmc%qx(j-1:j+1,i-1:i+1,k,n))): array-section order
-            double s = 0.0;
-            for (int ii = i - 1; ii <= i + 1; ++ii)
-              for (int jj = j - 1; jj <= j + 1; ++jj) s += std::fabs(ac_qx(jj, ii, k, n));
-            ac_qx(j, i, k, n) = 0.01 * s / 9.0;
-            neg_q_points++;
-          }
+  repair_negative_qx();  // :381-393
   // (:404-411)
   for (int k = 1; k <= kz; ++k)
     for (int i = idi1; i <= idi2; ++i)
@@ -458,6 +446,36 @@ void Oracle::tend() {
   // next timestep ready (:608-616)
   timer_advance();
   if (lcount == 2) dt = dt2;
+}
+
+// Negative-moisture repair, Main/mod_tendency.F90:381-393: sequential sweep, a point
+// sees the already repaired values of the neighbours that precede it in loop order.
+//   call exchange(atmc%qx,1,...) ; do n ; do k ; do i ; do j
+//     if ( atmc%qx(j,i,k,n) < d_zero ) atmc%qx(j,i,k,n) = 0.01 * sum(abs(atmc%qx(j-1:j+1,i-1:i+1,k,n)))/9
+// On a decomposed domain every rank sweeps its own tile and its ghost cells keep the values exchanged BEFORE
+// the sweep.  set_repair_tiles() lets this single-domain restatement reproduce that: neighbours that belong
+// to another tile are read from a copy taken before the sweep.
+void Oracle::repair_negative_qx() {
+  neg_q_points = 0;
+  const bool tiled = rt_j.size() > 1 || rt_i.size() > 1;
+  A4 raw;
+  if (tiled) raw = ac_qx;
+  auto tile_of = [](const std::vector<int>& st, int x) { int q = 0; while (q + 1 < (int)st.size() && st[q + 1] <= x) ++q; return q; };
+  for (int n = 1; n <= nqx; ++n)
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ici1; i <= ici2; ++i)
+        for (int j = jci1; j <= jci2; ++j)
+          if (ac_qx(j, i, k, n) < d_zero) {
+            // sum(abs(atmc%qx(j-1:j+1,i-1:i+1,k,n))): array-section order
+            double s = 0.0;
+            for (int ii = i - 1; ii <= i + 1; ++ii)
+              for (int jj = j - 1; jj <= j + 1; ++jj) {
+                const bool other = tiled && (tile_of(rt_j, jj) != tile_of(rt_j, j) || tile_of(rt_i, ii) != tile_of(rt_i, i));
+                s += std::fabs(other ? raw(jj, ii, k, n) : ac_qx(jj, ii, k, n));
+              }
+            ac_qx(j, i, k, n) = 0.01 * s / 9.0;
+            neg_q_points++;
+          }
 }
 
 }  // namespace orc

@@ -142,6 +142,28 @@ __device__ __forceinline__ void commit_cfl(const Fields& f, const double cfl, co
   atomicMax(f.cflbits + 1, bits);
 }
 
+// Forecast of one moisture species at one point (Main/mod_tendency.F90:368-380), before the negative-value
+// repair of :381-393: store it where k_negq_repair or a neighbour rank will need it, count / list negatives.
+// n = 0 (qv) or 1 (qc); edge = the point lies on the tile perimeter next to a neighbour rank.
+__device__ __forceinline__ void negq_note(const Geom& g, const Fields& f, const StepScalars& s, const double cq, const int j,
+                                          const int i, const int k, const int n, const bool edge) {
+  const int si = g.si;
+  const long long sk = g.sk;
+  double* cqf = n == 0 ? f.cqv : f.cqc;
+  if (s.cq_mode != 0 || edge) P3(cqf, j, i, k) = cq;
+  if (cq < 0.0) {
+    if (s.cq_mode != 1) atomicAdd(f.negq, 1ULL);
+    if (s.cq_mode != 0) {
+      const int plane = n * g.kz + (k - 1);
+      const int slot = atomicAdd(f.nq_cnt + plane, 1);
+      f.nq_list[(long long)plane * sk + slot] = (j - (g.jde1 - RCM_HALO)) + (i - (g.ide1 - RCM_HALO)) * si;
+    }
+  }
+}
+__device__ __forceinline__ bool tile_edge(const Geom& g, const int j, const int i) {
+  return (g.gl && j == g.jci1) || (g.gr && j == g.jci2) || (g.gb && i == g.ici1) || (g.gt && i == g.ici2);
+}
+
 __device__ __forceinline__ bool diff_interior(const Geom& g, int j, int i, bool dot) {
   if (dot) return j >= g.jdii1 && j <= g.jdii2 && i >= g.idii1 && i <= g.idii2;
   return j >= g.jcii1 && j <= g.jcii2 && i >= g.icii1 && i <= g.icii2;

@@ -44,6 +44,7 @@ bool wfwd_tma_setup();
 void launch_snd_wfwd_tma(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_wback(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_final(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_negq_repair(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_couple(const Geom&, double*, const double*, int, int, int, int, int, cudaStream_t);
 void launch_timeint(const Geom&, const double*, const double*, double*, double, int, int, int, int, int, cudaStream_t);
 void launch_bdyval(const Geom&, const Fields&, const double*, const double*, const double*, const int2*, int,
@@ -77,11 +78,11 @@ void launch_sp_corr(const Geom&, const Fields&, const StepScalars&, cudaStream_t
 // rcm_dyn_profile(); used by bench.py for the per-kernel roofline
 enum { KID_PREP, KID_XKC, KID_UV, KID_TQ, KID_PPW, KID_SND_INIT, KID_SND_UV, KID_SND_WFWD, KID_SND_WPVAL, KID_SND_WBACK,
        KID_SND_FINAL, KID_BDY, KID_HALO, KID_H_PS, KID_H_PREP, KID_H_UV, KID_H_TQ, KID_SP_PROJ, KID_SP_STEP, KID_SP_CORR,
-       KID_MO_PRE, KID_MO_DIV, KID_MO_W, KID_MO_UV, KID_MO_STAG, KID_MO_WAF, KID_COUNT };
+       KID_MO_PRE, KID_MO_DIV, KID_MO_W, KID_MO_UV, KID_MO_STAG, KID_MO_WAF, KID_NEGQ, KID_COUNT };
 static const char* const kKernelNames[KID_COUNT] = {"k_prep", "k_xkc", "k_uv", "k_tq", "k_ppw", "k_snd_init", "k_snd_uv",
                                                     "k_snd_wfwd", "k_snd_wpval", "k_snd_wback", "k_snd_final", "k_bdy", "halo",
                                                     "k_h_ps", "k_h_prep", "k_h_uv", "k_h_tq", "k_sp_proj", "k_sp_step", "k_sp_corr",
-                                                    "k_mo_pre", "k_mo_div", "k_mo_w", "k_mo_uv", "k_mo_stag", "k_mo_waf"};
+                                                    "k_mo_pre", "k_mo_div", "k_mo_w", "k_mo_uv", "k_mo_stag", "k_mo_waf", "k_negq"};
 struct ProfRec { int kid; cudaEvent_t a, b; };
 
 struct rcm_dyn {
@@ -142,6 +143,7 @@ struct rcm_dyn {
   int last_istep = 0;
   double max_cfl = 0;
   int64_t neg_q = 0;
+  int cq_mode = 0;   // StepScalars::cq_mode of the next call: 2 after a call that repaired negative moisture, else 0
   int nan_flag = 0;
   // stream / timing
   cudaStream_t st = nullptr;
@@ -380,7 +382,7 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
                      &f.bw, &f.nat, &f.naqv, &f.naqc, &f.nbt, &f.nbqv, &f.nbqc, &f.xub0, &f.xubt, &f.xvb0, &f.xvbt,
                      &f.xtb0, &f.xtbt, &f.xqb0, &f.xqbt, &f.xpb0, &f.xpbt, &f.xwb0, &f.xwbt, &f.pr0, &f.t0, &f.rho0,
                      &f.rhof0, &f.pr1, &f.rho1, &f.th, &f.qdot, &f.cr, &f.xkc, &f.dub, &f.dvb, &f.scc, &f.scdd, &f.sca, &f.uten, &f.vten, &f.ppten, &f.wten,
-                     &f.cu, &f.cv, &f.cpp, &f.cppd, &f.cw, &f.ct, &f.se, &f.sf})
+                     &f.cu, &f.cv, &f.cpp, &f.cppd, &f.cw, &f.ct, &f.se, &f.sf, &f.cqv, &f.cqc})
     A3(*p);
   for (int q = 0; q < 6; ++q) { A3(h->b1[q]); A3(h->nx[q]); }
   for (double** p : {&f.psa, &f.rpsa, &f.psdota, &f.rpsda, &f.msfx, &f.msfd, &f.xmsf, &f.dmsf, &f.coriol, &f.ef, &f.ddx,
@@ -420,7 +422,9 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   f.cflbits = dev_alloc_raw<unsigned long long>(h, 2);
   f.negq = dev_alloc_raw<unsigned long long>(h, 1);
   f.nanflag = dev_alloc_raw<int>(h, 1);
-  ok = ok && f.hefc && f.hegc && f.hefd && f.hegd && f.tmask && f.cflbits && f.negq && f.nanflag;
+  f.nq_list = dev_alloc_raw<int>(h, (size_t)2 * g.kz * (size_t)g.sk);
+  f.nq_cnt = dev_alloc_raw<int>(h, (size_t)2 * g.kz);
+  ok = ok && f.hefc && f.hegc && f.hefd && f.hegd && f.tmask && f.cflbits && f.negq && f.nanflag && f.nq_list && f.nq_cnt;
   if (!ok) {
     for (void* p : h->allocs) cudaFree(p);
     return bail(RCM_ERR_CUDA, "device memory allocation failed");
@@ -685,8 +689,9 @@ static int exch_sound_pp(rcm_dyn* h) {  // atmc%t, atmc%pp  (Main/mod_sound.F90:
 static int exch_uvten(rcm_dyn* h) {
   if (h->cfg.nproc <= 1) return RCM_OK;
   const int kz = h->g.kz;
-  if (h->halo.exchange({{h->f.cppd, kz, 0}, {h->f.ct, kz, 0}, {h->f.uten, kz, 1}, {h->f.vten, kz, 1}}, 1, h->st))
-    return fail(h, RCM_ERR_NCCL, "halo exchange (uten, pp) failed");
+  // + the unfiltered moisture forecast atmc%qx for the negative-value repair (Main/mod_tendency.F90:381)
+  if (h->halo.exchange({{h->f.cppd, kz, 0}, {h->f.ct, kz, 0}, {h->f.uten, kz, 1}, {h->f.vten, kz, 1}, {h->f.cqv, kz, 0}, {h->f.cqc, kz, 0}}, 1, h->st))
+    return fail(h, RCM_ERR_NCCL, "halo exchange (uten, pp, qx forecast) failed");
   return RCM_OK;
 }
 static int exch_state(rcm_dyn* h) {  // atm1/atm2 all prognostics, width 2 (Main/mod_tendency.F90:866-869,1046-1083)
@@ -1308,18 +1313,23 @@ static int tend_hydro(rcm_dyn* h) {
   s.xt = h->xbctime + h->dt;
   s.integrating = h->lcount > 0 ? 1 : 0;
   h->last_istep = 0;
+  s.cq_mode = h->cq_mode;
+  StepScalars s2 = s; s2.cq_mode = 1;   // second pass of k_h_tq: exits at once unless the first one found negative moisture
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
+  CUDA_OK(cudaMemsetAsync(f.nq_cnt, 0, (size_t)2 * g.kz * sizeof(int), h->st));
   TIMED(KID_H_PS, 2, (launch_h_ps(g, f, h->st), launch_h_rimcopy(g, f, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, h->st)));
   TIMED(KID_H_PREP, 1, launch_h_prep(g, f, s, h->st));
   TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_H_UV, 1, launch_h_uv(g, f, s, h->st));
     TIMED(KID_H_TQ, 1, launch_h_tq(g, f, s, h->st));
+    if (s.cq_mode == 0) TIMED(KID_NEGQ, 1, launch_h_tq(g, f, s2, h->st));
   } else {
     // k_h_uv and k_h_tq read the same inputs and write disjoint outputs
     CUDA_OK(cudaEventRecord(h->ev_fork, h->st));
     CUDA_OK(cudaStreamWaitEvent(h->st_b, h->ev_fork, 0));
     launch_h_tq(g, f, s, h->st);
+    if (s.cq_mode == 0) { launch_h_tq(g, f, s2, h->st); h->launches += 1; }
     launch_h_uv(g, f, s, h->st_b);
     h->launches += 2;
     CUDA_OK(cudaEventRecord(h->ev_jb, h->st_b));
@@ -1327,6 +1337,8 @@ static int tend_hydro(rcm_dyn* h) {
   }
   // time filter of p*, then p* on dot points as at the head of splitf (:259-260)
   TIMED(KID_H_PS, 2, (launch_h_psfilt(g, f, s, h->st), launch_psc2psd(g, f.psa, f.psdota, nullptr, h->st)));
+  // negative-moisture repair (Main/mod_tendency.F90:381-393), after the p* filter whose result floors the qv filter (:420-425)
+  TIMED(KID_NEGQ, 1, launch_negq_repair(g, f, s, h->st));
   TIMED(KID_SP_PROJ, 1, launch_sp_proj(g, f, s, h->st));
   int m2max = 0;
   for (int l = 0; l < s.nsplit; ++l) m2max = std::max(m2max, s.sp_m2[l]);
@@ -1354,13 +1366,17 @@ static int tend(rcm_dyn* h) {
   s.istep = istep; s.it = 0;
   h->last_istep = istep;
   int rc;
+  s.cq_mode = h->cq_mode;
+  StepScalars s2 = s; s2.cq_mode = 1;   // second pass of k_tq: exits at once unless the first one found negative moisture
   CUDA_OK(cudaMemsetAsync(f.cflbits, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
+  CUDA_OK(cudaMemsetAsync(f.nq_cnt, 0, (size_t)2 * g.kz * sizeof(int), h->st));
   TIMED(KID_PREP, 1, launch_prep(g, f, s, h->st));
   TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_UV, 1, h->uv_maps ? launch_uv_tma(g, f, s, h->st, h->uv_maps) : launch_uv(g, f, s, h->st));
     TIMED(KID_TQ, 1, h->tq_tma ? launch_tq_tma(g, f, s, h->st) : launch_tq(g, f, s, h->st));
+    if (s.cq_mode == 0) TIMED(KID_NEGQ, 1, h->tq_tma ? launch_tq_tma(g, f, s2, h->st) : launch_tq(g, f, s2, h->st));
     TIMED(KID_PPW, 1, h->ppw_tma ? launch_ppw_tma(g, f, s, h->st) : launch_ppw(g, f, s, h->st));
   } else {
     // k_uv, k_tq, k_ppw read the same inputs and write disjoint outputs: run
@@ -1369,6 +1385,7 @@ static int tend(rcm_dyn* h) {
     CUDA_OK(cudaStreamWaitEvent(h->st_b, h->ev_fork, 0));
     CUDA_OK(cudaStreamWaitEvent(h->st_c, h->ev_fork, 0));
     if (h->tq_tma) launch_tq_tma(g, f, s, h->st); else launch_tq(g, f, s, h->st);
+    if (s.cq_mode == 0) { if (h->tq_tma) launch_tq_tma(g, f, s2, h->st); else launch_tq(g, f, s2, h->st); h->launches += 1; }
     if (h->ppw_tma) launch_ppw_tma(g, f, s, h->st_b); else launch_ppw(g, f, s, h->st_b);
     if (h->uv_maps) launch_uv_tma(g, f, s, h->st_c, h->uv_maps); else launch_uv(g, f, s, h->st_c);
     h->launches += 3;
@@ -1378,8 +1395,10 @@ static int tend(rcm_dyn* h) {
     CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jc, 0));
   }
   TIMED(KID_SND_INIT, 1, launch_snd_init(g, f, s, h->st));
-  TIMED(KID_HALO, 0, rc = exch_uvten(h));  // + the first cppd, ct of the step
+  TIMED(KID_HALO, 0, rc = exch_uvten(h));  // + the first cppd, ct of the step and the moisture forecast
   if (rc) return rc;
+  // negative-moisture repair (Main/mod_tendency.F90:381-393): before k_snd_wback first reads the filtered qv
+  TIMED(KID_NEGQ, 1, launch_negq_repair(g, f, s, h->st));
   for (int it = 1; it <= istep; ++it) {
     s.it = it;
     TIMED(KID_SND_UV, 1, launch_snd_uv(g, f, s, h->st));
@@ -1510,6 +1529,7 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
     cfl = vm[0]; cfl_last = vm[1]; nanf = (vm[2] != 0.0); halo_err = (vm[3] != 0.0); nq = (unsigned long long)vs[0];
   }
   h->max_cfl = cfl_last; h->neg_q = (int64_t)nq; h->nan_flag = nanf;
+  h->cq_mode = nq > 0 ? 2 : 0;   // moisture went negative: the next call stores the forecast in its first pass
   CUDA_OK(cudaGetLastError());
   if (halo_err) return fail(h, RCM_ERR_NCCL, "halo exchange: timed out waiting for a neighbour's edge data");
   if (nanf || cfl != cfl) return fail(h, RCM_ERR_NAN, "NaN in the acoustic solver");

@@ -52,6 +52,11 @@ struct StepScalars {
   int ktf_ray;  // min(kzp1, rayndamp)
   int nspgx, nspgd;
   int it, istep;
+  // negative-moisture repair: 0 = fused pass (count negatives; store the forecast on the tile perimeter only),
+  // 1 = second pass after negatives were found (store the forecast everywhere, list the negative points, no
+  // other output; exits at once when the count is zero), 2 = single pass that stores and lists everything
+  // (chosen when the previous call saw negatives)
+  int cq_mode;
   // ---- hydrostatic core (idynamic = 1) ----
   int hydro;     // 1: idynamic = 1
   int integrating;  // rcmtimer%integrating(): lcount > 0
@@ -107,6 +112,11 @@ struct Fields {
   // diagnostics
   unsigned long long *cflbits;  // max CFL as ordered bits
   unsigned long long *negq;     // negative-q repairs
+  // negative-moisture repair (Main/mod_tendency.F90:381-393; k_negq.cu): unfiltered forecast atmc%qx of qv and
+  // qc, the list of negative points per (species, level) plane and its fill counts
+  double *cqv, *cqc;
+  int *nq_list;                 // [plane * sk + slot] = local offset jl + il*si, plane = n*kz + (k-1)
+  int *nq_cnt;                  // [plane]
   int *nanflag;
 };
 

@@ -330,6 +330,9 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
   const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jci2 || i > g.ici2) return;
+  if (s.cq_mode == 1 && *f.negq == 0ULL) return;  // second pass of the negative-moisture repair: nothing went negative
+  const bool cq_edge = tile_edge(g, j, i);
+  const bool out = (s.cq_mode != 1);              // the second pass only stores the forecast moisture
   const int kz = g.kz;
   const bool up = s.upstream_mode != 0;
   const bool se = s.stability_enhance != 0;
@@ -403,7 +406,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         const double omega = 0.5 * (svv_n + qdot_k) * psa +
                              hs * (pten + ((au00 * r00 + au01 * r01 + au11 * r11 + au10 * r10) * dpsx +
                                            (av00 * r00 + av01 * r01 + av11 * r11 + av10 * r10) * dpsy) * dummy8);
-        P3(f.omega, j, i, k) = omega;
+        if (out) P3(f.omega, j, i, k) = omega;
         const double rovcpm = rgas / cpmf(qv_c);
         ten = ten + (omega * rovcpm * tv) / (s.ptop * rpsa_c + hs);
       }
@@ -427,8 +430,8 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
       }
       const double ct = bt_c + dt * ten;
       const double d = s.gnu1 * (ct + bt_c - 2.0 * at);
-      P3(f.nbt, j, i, k) = at + d;
-      P3(f.nat, j, i, k) = ct;
+      if (out) P3(f.nbt, j, i, k) = at + d;
+      if (out) P3(f.nat, j, i, k) = ct;
       dq_k = dq_n;
     }
 
@@ -470,10 +473,13 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         for (int r = 0; r < nring; ++r) ten = ten + 1.0 * xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * d_c);
       }
       double cq = b_c + dt * ten;
-      if (cq < 0.0) { atomicAdd(f.negq, 1ULL); cq = 0.0; }  // Main/mod_tendency.F90:382-393 (clipped, counted)
+      // Main/mod_tendency.F90:381-393: a negative forecast is replaced by 1 % of the 3x3 mean of |q|; the value
+      // filtered here for such a point is provisional and is redone by k_negq_repair (k_negq.cu)
+      negq_note(g, f, s, cq, j, i, k, 0, cq_edge);
+      if (cq < 0.0) cq = 0.0;
       const double d = s.gnu1 * (cq + b_c - 2.0 * aq_c);
-      P3(f.nbqv, j, i, k) = fmax(aq_c + beta * d, minqq * npsa);
-      P3(f.naqv, j, i, k) = fmax(cq + (beta - 1.0) * d, minqq * npsb);
+      if (out) P3(f.nbqv, j, i, k) = fmax(aq_c + beta * d, minqq * npsa);
+      if (out) P3(f.naqv, j, i, k) = fmax(cq + (beta - 1.0) * d, minqq * npsb);
       fl_qv_k = fl_n;
     }
 
@@ -513,14 +519,15 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
       }
       if (s.ipptls <= 0) ten = 0.0;  // Main/mod_tendency.F90:331-335
       double cq = b_c + dt * ten;
-      if (cq < 0.0) { atomicAdd(f.negq, 1ULL); cq = 0.0; }
+      negq_note(g, f, s, cq, j, i, k, 1, cq_edge);
+      if (cq < 0.0) cq = 0.0;
       const double d = s.gnu2 * (cq + b_c - 2.0 * ac_c);
       double nb = ac_c + beta * d;
       double na = cq + (beta - 1.0) * d;
       if (nb < 0.0) nb = 0.0;
       if (na < 0.0) na = 0.0;
-      P3(f.nbqc, j, i, k) = nb;
-      P3(f.naqc, j, i, k) = na;
+      if (out) P3(f.nbqc, j, i, k) = nb;
+      if (out) P3(f.naqc, j, i, k) = na;
       fl_qc_k = fl_n;
     }
     qdot_k = svv_n;

@@ -28,6 +28,8 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
   const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jci2 || i > g.ici2) return;
+  if (s.cq_mode == 1 && *f.negq == 0ULL) return;  // second pass of the negative-moisture repair: nothing went negative
+  const bool cq_edge = tile_edge(g, j, i);
   const int kz = g.kz;
   const bool up = s.upstream_mode != 0;
   const bool se = s.stability_enhance != 0;

@@ -20,6 +20,7 @@ enum { C_CR, C_XKC, C_AT };
 
 __global__ void __launch_bounds__(256, 2)
 k_tq_tma(const Geom g, const Fields f, const StepScalars s) {
+  if (s.cq_mode == 1 && *f.negq == 0ULL) return;  // second pass of the negative-moisture repair: nothing went negative
   extern __shared__ __align__(128) unsigned char smraw[];
   double* tiles = reinterpret_cast<double*>(smraw);
   double* rtile = tiles + (size_t)kStages * kStageDbl;  // rpsb, 2-D, halo rows
@@ -37,6 +38,7 @@ k_tq_tma(const Geom g, const Fields f, const StepScalars s) {
   const int ihi = g.ide2 + RCM_HALO;
   const int to = (i - (i0 - 2)) * kTW + (j - jstart);  // own cell in a halo tile
   const int tc = (i - i0) * kTW + (j - jstart);        // own cell in a centre tile
+  const bool cq_edge = tile_edge(g, j, i);
 
   if (tid == 0) {
     for (int q = 0; q < kStages + 1; ++q) mbar_init(full + q, 1);

@@ -58,3 +58,26 @@ def smooth_qc(case):
     J, I, K = np.meshgrid(np.arange(jx - 1), np.arange(iy - 1), np.arange(kz), indexing="ij")
     return np.asfortranarray(96.0 * 1e-4 * (1.0 + 0.5 * np.sin(2 * np.pi * J / (jx - 1)) * np.cos(2 * np.pi * I / (iy - 1)))
                              * np.sin(np.pi * (K + 0.5) / kz))
+
+
+def sharp_moisture(case, seed=7):
+    """Coupled qv and qc with sharp fronts: top-hat patches, single-cell spikes and checkerboard patches next to
+    dry air.  Advection and the 4th-order diffusion undershoot around them, so the leapfrog forecast goes negative
+    at isolated points AND in adjacent groups — the sequential case of Main/mod_tendency.F90:381-393."""
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    rng = np.random.default_rng(seed)
+    ps = 96.0
+    qv = np.full((jx - 1, iy - 1, kz), ps * 2.0e-6)
+    qc = np.zeros((jx - 1, iy - 1, kz))
+    for _ in range(max(3, (jx * iy) // 120)):
+        j0, i0 = int(rng.integers(2, jx - 6)), int(rng.integers(2, iy - 6))
+        w, h = int(rng.integers(1, 4)), int(rng.integers(1, 4))
+        k0 = int(rng.integers(0, kz - 2))
+        qv[j0:j0 + w, i0:i0 + h, k0:k0 + 3] = ps * 8.0e-3 * rng.uniform(0.5, 1.0)
+        qc[j0:j0 + w, i0:i0 + h, k0:k0 + 2] = ps * 1.0e-3 * rng.uniform(0.5, 1.0)
+    # checkerboard patch: neighbouring cells alternate between moist and dry
+    J, I = np.meshgrid(np.arange(jx - 1), np.arange(iy - 1), indexing="ij")
+    cb = ((J + I) % 2 == 0) & (J > jx // 2) & (I > iy // 3) & (J < jx - 4) & (I < iy - 4)
+    qc[cb, kz // 2] = ps * 2.0e-3
+    qv[cb, kz // 2 + 1] = ps * 6.0e-3
+    return np.asfortranarray(qv), np.asfortranarray(qc)

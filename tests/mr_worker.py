@@ -55,6 +55,7 @@ def main():
     ap.add_argument("--ibdyfrq", type=int, default=6)
     ap.add_argument("--iboudy", type=int, default=-1)
     ap.add_argument("--work", action="store_true", help="also dump the per-step work arrays")
+    ap.add_argument("--sharp-q", action="store_true", help="moisture with sharp fronts (drives the negative-q repair)")
     ap.add_argument("--out", required=True)
     args = ap.parse_args()
 
@@ -111,6 +112,12 @@ def main():
     case = synth.make_case(args.case, window=win, ibdyfrq=args.ibdyfrq)
     case.cfg = cfg
     synth.load_case(core, case, stage_next=True)
+    if args.sharp_q:
+        from tests.helpers import sharp_moisture
+        qv, qc = sharp_moisture(base)          # global arrays; the library keeps this rank's window
+        for lv in (capi.LEVEL_A, capi.LEVEL_B):
+            core.set_state(capi.F_QV, lv, qv)
+            core.set_state(capi.F_QC, lv, qc)
     core.step(args.steps)
     out = {"tile": np.array(core.tile())}
     moloch = cfg.idynamic == 3
@@ -142,6 +149,7 @@ def main():
             out[f"wlb{wid}"] = np.array(lb)
     d = core.diag()
     out["max_cfl"] = np.array(d.max_cfl)
+    out["neg_q"] = np.array(d.neg_q_points)
     out["ps_extremes"] = np.array([d.ps_max, d.ps_min])
     np.savez(os.path.join(args.out, f"rank{rank}.npz"), **out)
     core.close()
