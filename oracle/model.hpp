@@ -136,6 +136,7 @@ struct Oracle {
   double max_cfl_step = 0;
   int last_istep = 0;
   bool cfl_error = false;
+  bool break_before_sound = false;  // test hook (oracle/taps.cpp)
   int64_t neg_q_points = 0;
   std::vector<int> rt_j, rt_i;  // first dot index of every tile along j / i (set_repair_tiles; empty = one domain)
   void repair_negative_qx();
