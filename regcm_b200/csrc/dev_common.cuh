@@ -145,15 +145,18 @@ __device__ __forceinline__ void commit_cfl(const Fields& f, const double cfl, co
 // Forecast of one moisture species at one point (Main/mod_tendency.F90:368-380), before the negative-value
 // repair of :381-393: store it where k_negq_repair or a neighbour rank will need it, count / list negatives.
 // n = 0 (qv) or 1 (qc); edge = the point lies on the tile perimeter next to a neighbour rank.
-__device__ __forceinline__ void negq_note(const Geom& g, const Fields& f, const StepScalars& s, const double cq, const int j,
+// MODE = StepScalars::cq_mode as a compile-time constant (the kernels are instantiated per mode, so that the
+// common mode 0 carries no list code).
+template <int MODE>
+__device__ __forceinline__ void negq_note(const Geom& g, const Fields& f, const double cq, const int j,
                                           const int i, const int k, const int n, const bool edge) {
   const int si = g.si;
   const long long sk = g.sk;
   double* cqf = n == 0 ? f.cqv : f.cqc;
-  if (s.cq_mode != 0 || edge) P3(cqf, j, i, k) = cq;
+  if (MODE != 0 || edge) P3(cqf, j, i, k) = cq;
   if (cq < 0.0) {
-    if (s.cq_mode != 1) atomicAdd(f.negq, 1ULL);
-    if (s.cq_mode != 0) {
+    if (MODE != 1) atomicAdd(f.negq, 1ULL);
+    if (MODE != 0) {
       const int plane = n * g.kz + (k - 1);
       const int slot = atomicAdd(f.nq_cnt + plane, 1);
       f.nq_list[(long long)plane * sk + slot] = (j - (g.jde1 - RCM_HALO)) + (i - (g.ide1 - RCM_HALO)) * si;

@@ -323,6 +323,7 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
 }
 
 // ---------------------------------------------------------------------------
+template <int CQ_MODE>   // StepScalars::cq_mode (negative-moisture repair), compile-time
 __global__ void __launch_bounds__(RCM_MAXT, 3)  // 168 registers: no spills (80 spilled 300 B)
 k_h_tq(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
@@ -330,9 +331,9 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
   const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jci2 || i > g.ici2) return;
-  if (s.cq_mode == 1 && *f.negq == 0ULL) return;  // second pass of the negative-moisture repair: nothing went negative
+  if (CQ_MODE == 1 && *f.negq == 0ULL) return;  // second pass of the negative-moisture repair: nothing went negative
   const bool cq_edge = tile_edge(g, j, i);
-  const bool out = (s.cq_mode != 1);              // the second pass only stores the forecast moisture
+  const bool out = (CQ_MODE != 1);              // the second pass only stores the forecast moisture
   const int kz = g.kz;
   const bool up = s.upstream_mode != 0;
   const bool se = s.stability_enhance != 0;
@@ -475,7 +476,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
       double cq = b_c + dt * ten;
       // Main/mod_tendency.F90:381-393: a negative forecast is replaced by 1 % of the 3x3 mean of |q|; the value
       // filtered here for such a point is provisional and is redone by k_negq_repair (k_negq.cu)
-      negq_note(g, f, s, cq, j, i, k, 0, cq_edge);
+      negq_note<CQ_MODE>(g, f, cq, j, i, k, 0, cq_edge);
       if (cq < 0.0) cq = 0.0;
       const double d = s.gnu1 * (cq + b_c - 2.0 * aq_c);
       if (out) P3(f.nbqv, j, i, k) = fmax(aq_c + beta * d, minqq * npsa);
@@ -519,7 +520,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
       }
       if (s.ipptls <= 0) ten = 0.0;  // Main/mod_tendency.F90:331-335
       double cq = b_c + dt * ten;
-      negq_note(g, f, s, cq, j, i, k, 1, cq_edge);
+      negq_note<CQ_MODE>(g, f, cq, j, i, k, 1, cq_edge);
       if (cq < 0.0) cq = 0.0;
       const double d = s.gnu2 * (cq + b_c - 2.0 * ac_c);
       double nb = ac_c + beta * d;
@@ -589,7 +590,10 @@ void launch_h_uv(const Geom& g, const Fields& f, const StepScalars& s, cudaStrea
 }
 void launch_h_tq(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const dim3 b = rcm::col_block();
-  RCM_LAUNCH(k_h_tq, grid2(g.jci2 - g.jci1 + 1, g.ici2 - g.ici1 + 1, b), b, st, g, f, s);
+  const dim3 gr = grid2(g.jci2 - g.jci1 + 1, g.ici2 - g.ici1 + 1, b);
+  if (s.cq_mode == 0) RCM_LAUNCH(k_h_tq<0>, gr, b, st, g, f, s);
+  else if (s.cq_mode == 1) RCM_LAUNCH(k_h_tq<1>, gr, b, st, g, f, s);
+  else RCM_LAUNCH(k_h_tq<2>, gr, b, st, g, f, s);
 }
 void launch_h_psfilt(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   dim3 b(32, 8);

@@ -21,6 +21,7 @@
 
 using namespace rcm;
 
+template <int CQ_MODE>   // StepScalars::cq_mode (negative-moisture repair), compile-time
 __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_TQ)
 k_tq(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
@@ -28,7 +29,7 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
   const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jci2 || i > g.ici2) return;
-  if (s.cq_mode == 1 && *f.negq == 0ULL) return;  // second pass of the negative-moisture repair: nothing went negative
+  if (CQ_MODE == 1 && *f.negq == 0ULL) return;  // second pass of the negative-moisture repair: nothing went negative
   const bool cq_edge = tile_edge(g, j, i);
   const int kz = g.kz;
   const bool up = s.upstream_mode != 0;
@@ -86,5 +87,7 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
 void launch_tq(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
   const dim3 b = rcm::col_block(); dim3 gr((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y);
-  RCM_LAUNCH(k_tq, gr, b, st, g, f, s);
+  if (s.cq_mode == 0) RCM_LAUNCH(k_tq<0>, gr, b, st, g, f, s);
+  else if (s.cq_mode == 1) RCM_LAUNCH(k_tq<1>, gr, b, st, g, f, s);
+  else RCM_LAUNCH(k_tq<2>, gr, b, st, g, f, s);
 }

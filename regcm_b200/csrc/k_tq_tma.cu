@@ -18,9 +18,10 @@ constexpr int kCopies = kNH * kTH + kNC * kBY;  // 120 row copies per level
 enum { T_AU, T_AV, T_TH, T_AQV, T_AQC, T_BT, T_BQV, T_BQC };
 enum { C_CR, C_XKC, C_AT };
 
+template <int CQ_MODE>   // StepScalars::cq_mode (negative-moisture repair), compile-time
 __global__ void __launch_bounds__(256, 2)
 k_tq_tma(const Geom g, const Fields f, const StepScalars s) {
-  if (s.cq_mode == 1 && *f.negq == 0ULL) return;  // second pass of the negative-moisture repair: nothing went negative
+  if (CQ_MODE == 1 && *f.negq == 0ULL) return;  // second pass of the negative-moisture repair: nothing went negative
   extern __shared__ __align__(128) unsigned char smraw[];
   double* tiles = reinterpret_cast<double*>(smraw);
   double* rtile = tiles + (size_t)kStages * kStageDbl;  // rpsb, 2-D, halo rows
@@ -124,14 +125,18 @@ constexpr int kSmem = kStages * kStageBytes + kTileH * 8 + 64;
 }  // namespace
 
 bool tq_tma_setup() {
-  if (cudaFuncSetAttribute(k_tq_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem) != cudaSuccess) { cudaGetLastError(); return false; }
+  if (cudaFuncSetAttribute(k_tq_tma<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem) != cudaSuccess ||
+      cudaFuncSetAttribute(k_tq_tma<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem) != cudaSuccess ||
+      cudaFuncSetAttribute(k_tq_tma<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem) != cudaSuccess) { cudaGetLastError(); return false; }
   return true;
 }
 
 void launch_tq_tma(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const int nj = g.jci2 - g.jci1 + 1, ni = g.ici2 - g.ici1 + 1;
   dim3 b(32, kBY), gr((nj + 31) / 32, (ni + kBY - 1) / kBY);
-  k_tq_tma<<<gr, b, kSmem, st>>>(g, f, s);
+  if (s.cq_mode == 0) k_tq_tma<0><<<gr, b, kSmem, st>>>(g, f, s);
+  else if (s.cq_mode == 1) k_tq_tma<1><<<gr, b, kSmem, st>>>(g, f, s);
+  else k_tq_tma<2><<<gr, b, kSmem, st>>>(g, f, s);
 }
 #else
 bool tq_tma_setup() { return false; }
