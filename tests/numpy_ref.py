@@ -114,7 +114,7 @@ DLOWVAL = 1.0e-20                     # :68
 def sound(t, p):
     """Main/mod_sound.F90:163-718 (`sound`, single rank, alarm_day not active), all `istep` sub-steps and the
     epilogue.  t: dict of F arrays (modified in place: ac_u, ac_v, ac_pp, ac_w, ac_t, a1_t, a2_t, a1_u ... a2_w,
-    uten, vten, ppten, wten, s_estore, s_astore); p: scalars.  Returns (istep, max cfl of the last sub-step)."""
+    uten, vten, ppten, wten, s_estore, s_astore); p: scalars.  Returns (istep, max CFL number over the sub-steps)."""
     jx, iy, kz = p["jx"], p["iy"], p["kz"]
     kzp1 = kz + 1
     Jd, Id, Jdi, Idi = (1, jx), (1, iy), (2, jx - 1), (2, iy - 1)
@@ -193,7 +193,7 @@ def sound(t, p):
         f[:, :, kz - 1] = wbot
         t["_work"] = dict(wo=wo, e=e, f=f, pi=pi, it=it, dts=dts, rpsb=rpsb, qv=qv)
         _sound_column(t, p, t["_work"], ci, ci2, m, mx, ps0c, bp, bm, bpxbp, bpxbm)
-        cfl = t["_work"]["cfl"]
+        cfl = max(cfl, t["_work"]["cfl"])
     # ---- epilogue: recouple and Robert-Asselin filters (:693-712, Main/mod_timefilter.F90:92-110,132-156) ----
     u.s(Jdi, Idi, K)[...] *= psdotb.s(Jdi, Idi)[:, :, None]
     v.s(Jdi, Idi, K)[...] *= psdotb.s(Jdi, Idi)[:, :, None]
@@ -212,3 +212,127 @@ def sound(t, p):
     for nm in ("a2_w", "a1_w"):
         t[nm].a[np.abs(t[nm].a) < DLOWVAL] = 0.0
     return istep, cfl
+
+
+def _sound_column(t, p, wk, ci, ci2, m, mx, ps0c, bp, bm, bpxbp, bpxbm):
+    """Main/mod_sound.F90:335-444: the k-local coefficients cc, cdd, cj, tk, ca, g1, g2, the tridiagonal aa, b, c,
+    the terrain terms pxup, pyvp and ptend — one sub-step, whole (j,i) planes at a time."""
+    kz = p["kz"]
+    dts, dx, xgamma = wk["dts"], p["dx"], p["xgamma"]
+    u, v = t["ac_u"], t["ac_v"]
+    pr0, rho0, t0 = t["a0_pr"], t["a0_rho"], t["a0_t"]
+    pr1, rho1, a2t, dsig = t["a1_pr"], t["a1_rho"], t["a2_t"], t["dsigma"]
+    rpsb = wk["rpsb"]
+    ds = np.array([dsig.s(k) for k in range(1, kz + 1)])          # dsigma(1:kz)
+
+    def four(a, k):     # a(j,i) + a(j+1,i) + a(j,i+1) + a(j+1,i+1) at level k
+        return ci(a, 0, 0, k) + ci(a, 1, 0, k) + ci(a, 0, 1, k) + ci(a, 1, 1, k)
+
+    def four_diff(a, ka, kb):   # the eight-term bracket of pxup/pyvp: + four at ka, - four at kb, in the reference's order
+        return (ci(a, 0, 0, ka) + ci(a, 1, 0, ka) + ci(a, 0, 1, ka) + ci(a, 1, 1, ka) -
+                ci(a, 0, 0, kb) - ci(a, 1, 0, kb) - ci(a, 0, 1, kb) - ci(a, 1, 1, kb))
+
+    cc = xgamma * ci(pr1) * dts / (dx * mx)                                             # :336, :386
+    cdd = xgamma * ci(pr1) * ci(rho0) * EGRAV * dts / (ps0c * ds[None, None, :])        # :337-338, :387-388
+    cj = 0.5 * ci(rho0) * EGRAV * dts                                                   # :339, :389
+    tk = (0.5 * ps0c * ci(t0)) / (xgamma * ci(pr0) * ci(a2t) * rpsb[:, :, None])        # :370-371, :377-378
+    nj, ni = cc.shape[:2]
+    z = lambda: np.zeros((nj, ni, kz))   # noqa: E731
+    pxup, pyvp, ca, g1, g2, aa, b, c = z(), z(), z(), z(), z(), z(), z(), z()
+    den1 = ci(pr0, k=1) - ci(pr0, k=2)                                                  # :340-352
+    pxup[:, :, 0] = 0.0625 * (ci(pr0, 1, 0, 1) - ci(pr0, -1, 0, 1)) * four_diff(u, 1, 2) / den1
+    pyvp[:, :, 0] = 0.0625 * (ci(pr0, 0, 1, 1) - ci(pr0, 0, -1, 1)) * four_diff(v, 1, 2) / den1
+    for k in range(2, kz + 1):                                                          # :373-416
+        kp1, km1 = min(k + 1, kz), k - 1
+        q, qm = k - 1, km1 - 1                                                          # 0-based positions of k, km1
+        rofac = (ds[qm] * ci(rho0, k=k) + ds[q] * ci(rho0, k=km1)) / (ds[qm] * ci(rho1, k=k) + ds[q] * ci(rho1, k=km1))
+        ca[:, :, q] = EGRAV * dts / (ci(pr0, k=k) - ci(pr0, k=km1)) * rofac
+        g1[:, :, q] = 1.0 - ds[qm] * tk[:, :, q]
+        g2[:, :, q] = 1.0 + ds[q] * tk[:, :, qm]
+        c[:, :, q] = -ca[:, :, q] * (cdd[:, :, qm] - cj[:, :, qm]) * g2[:, :, q] * bpxbp
+        b[:, :, q] = 1.0 + ca[:, :, q] * (g1[:, :, q] * (cdd[:, :, q] - cj[:, :, q]) + g2[:, :, q] * (cdd[:, :, qm] + cj[:, :, qm])) * bpxbp
+        aa[:, :, q] = -ca[:, :, q] * (cdd[:, :, q] + cj[:, :, q]) * g1[:, :, q] * bpxbp
+        den = ci(pr0, k=km1) - ci(pr0, k=kp1)
+        pyvp[:, :, q] = 0.125 * (ci(pr0, 0, 1, k) - ci(pr0, 0, -1, k)) * four_diff(v, km1, kp1) / den
+        pxup[:, :, q] = 0.125 * (ci(pr0, 1, 0, k) - ci(pr0, -1, 0, k)) * four_diff(u, km1, kp1) / den
+    pyvp[:, :, kz - 1] = pyvp[:, :, kz - 1] * 0.5                                       # :424-427
+    pxup[:, :, kz - 1] = pxup[:, :, kz - 1] * 0.5
+    # ptend (:359-369 for k = 1, :433-444 for k >= 2: the same expression)
+    div = (ci(v, 0, 1) * m["01"] - ci(v, 0, 0) * m["00"] + ci(v, 1, 1) * m["11"] - ci(v, 1, 0) * m["10"] +
+           ci(u, 1, 0) * m["10"] - ci(u, 0, 0) * m["00"] + ci(u, 1, 1) * m["11"] - ci(u, 0, 1) * m["01"])
+    ptend = ci(t["ppten"]) - 0.5 * cc * (div / mx - 2.0 * (pyvp + pxup))
+    wk.update(cc=cc, cdd=cdd, cj=cj, tk=tk, ca=ca, g1=g1, g2=g2, aa=aa, b=b, c=c, ptend=ptend)
+    _sound_solve(t, p, wk, ci, ci2, ps0c, bp, bm, bpxbm)
+
+
+def _sound_solve(t, p, wk, ci, ci2, ps0c, bp, bm, bpxbm):
+    """Main/mod_sound.F90:445-689: rhs, explicit p' update, upward elimination, radiative upper BC (13x13
+    convolution of estore with tmask, clamped indices), downward sweep, CFL, new p', temperature correction."""
+    jx, iy, kz = p["jx"], p["iy"], p["kz"]
+    kzp1 = kz + 1
+    dts, dt, gnu1, cpd, xgamma = wk["dts"], p["dt"], p["gnu1"], p["cpd"], p["xgamma"]
+    u, v, pp, w = t["ac_u"], t["ac_v"], t["ac_pp"], t["ac_w"]
+    rho0, rhof0, pr1, rho1 = t["a0_rho"], t["a0_rhof"], t["a1_pr"], t["a1_rho"]
+    dsig, sigma, twt, wten, ppten = t["dsigma"], t["sigma"], t["twt"], t["wten"], t["ppten"]
+    wo, e, f, pi, qv = wk["wo"], wk["e"], wk["f"], wk["pi"], wk["qv"]
+    cdd, cj, ca, g1, g2, aa, b, c, ptend = (wk[n] for n in ("cdd", "cj", "ca", "g1", "g2", "aa", "b", "c", "ptend"))
+    nj, ni = cdd.shape[:2]
+    rhs = np.zeros((nj, ni, kz))
+    ppc = ci(pp)                      # view of atmc%pp on the interior
+    wc = ci(w, k=(1, kzp1))           # view of atmc%w on the interior (w(kzp1) already holds the bottom BC)
+    for k in range(2, kz + 1):        # :445-456 (atmc%w(k) still equals wo(k) for k <= kz)
+        q, qm = k - 1, k - 2
+        rhs[:, :, q] = wc[:, :, q] + ci(wten, k=k) + ca[:, :, q] * (
+            bpxbm * ((cdd[:, :, qm] - cj[:, :, qm]) * g2[:, :, q] * wo[:, :, qm] -
+                     ((cdd[:, :, qm] + cj[:, :, qm]) * g2[:, :, q] + (cdd[:, :, q] - cj[:, :, q]) * g1[:, :, q]) * wo[:, :, q] +
+                     (cdd[:, :, q] + cj[:, :, q]) * g1[:, :, q] * wo[:, :, q + 1]) +
+            (ppc[:, :, q] * g1[:, :, q] - ppc[:, :, qm] * g2[:, :, q]) +
+            (g1[:, :, q] * ptend[:, :, q] - g2[:, :, q] * ptend[:, :, qm]) * bp)
+    pi[...] = ppc                                                                      # :458-459
+    ppc[...] = ppc + ptend + (cj * (wo[:, :, 1:] + wo[:, :, :-1]) + cdd * (wo[:, :, 1:] - wo[:, :, :-1])) * bm   # :465-467
+    for k in range(kz, 1, -1):                                                         # :472-480
+        q = k - 1
+        denom = aa[:, :, q] * e[:, :, q] + b[:, :, q]
+        e[:, :, q - 1] = -c[:, :, q] / denom
+        f[:, :, q - 1] = (rhs[:, :, q] - f[:, :, q] * aa[:, :, q]) / denom
+    wpval = np.zeros((nj, ni))
+    if p["ifupr"] == 1:                                                                # :489-561
+        denom = (cdd[:, :, 0] + cj[:, :, 0]) * bp
+        est, ast = t["s_estore"], t["s_astore"]
+        ci2(est)[...] = ppc[:, :, 0] + f[:, :, 0] * denom
+        ci2(ast)[...] = denom * e[:, :, 0] + (cj[:, :, 0] - cdd[:, :, 0]) * bp
+        tmask = t["tmask"]
+        icross1, icross2, jcross1, jcross2 = 1, iy - 1, 1, jx - 1
+        jj = np.arange(2, jx - 2 + 1); ii = np.arange(2, iy - 2 + 1)
+        for nsi in range(-6, 7):          # summation order of the reference: nsi outer, nsj inner
+            inn = np.clip(ii + nsi, icross1 + 1, icross2 - 1)
+            for nsj in range(-6, 7):
+                jnn = np.clip(jj + nsj, jcross1 + 1, jcross2 - 1)
+                wpval = wpval + est.a[np.ix_(jnn - est.lb[0], inn - est.lb[1])] * tmask.s(nsj, nsi)
+    wc[:, :, 0] = wpval                                                                # :566-568
+    for k in range(1, kz + 1):                                                         # :572-574
+        wc[:, :, k] = e[:, :, k - 1] * wc[:, :, k - 1] + f[:, :, k - 1]
+    # ---- CFL (:611-633) ----
+    ucrs = ci(u, 0, 0) + ci(u, 0, 1) + ci(u, 1, 0) + ci(u, 1, 1)
+    vcrs = ci(v, 0, 0) + ci(v, 0, 1) + ci(v, 1, 0) + ci(v, 1, 1)
+    cfl = 0.0
+    dpx, dpy = ci2(t["dpsdxm"]), ci2(t["dpsdym"])
+    for k in range(kz, 1, -1):
+        q = k - 1
+        sigdot = -ci(rhof0, k=k) * EGRAV * wc[:, :, q] / ps0c[:, :, 0] - sigma.s(k) * (
+            dpx * (twt.s(k, 1) * ucrs[:, :, q] + twt.s(k, 2) * ucrs[:, :, q - 1]) +
+            dpy * (twt.s(k, 1) * vcrs[:, :, q] + twt.s(k, 2) * vcrs[:, :, q - 1]))
+        check = np.abs(sigdot) * dt / (dsig.s(k) + dsig.s(k - 1))
+        cfl = max(cfl, float(check.max()))
+    wk["cfl"] = cfl
+    # ---- new pressure and temperature correction (:669-689) ----
+    ds = np.array([dsig.s(k) for k in range(1, kz + 1)])
+    ppold = pi.copy()
+    cddtmp = xgamma * ci(pr1) * ci(rho0) * EGRAV * dts / (ps0c * ds[None, None, :])
+    cjtmp = ci(rho0) * EGRAV * dts * 0.5
+    ppc[...] = ppc + (cjtmp * (wc[:, :, 1:] + wc[:, :, :-1]) + cddtmp * (wc[:, :, 1:] - wc[:, :, :-1])) * bp
+    pi[...] = ppc - ppold - ci(ppten)
+    cpm = cpd * (1.0 + 0.80 * qv)                                                      # Share/cpmf.inc
+    dpterm = ci2(t["psb"])[:, :, None] * (ppc - ppold) / (cpm * ci(rho1))
+    ci(t["a2_t"])[...] = ci(t["a2_t"]) + gnu1 * dpterm
+    ci(t["a1_t"])[...] = ci(t["a1_t"]) + dpterm

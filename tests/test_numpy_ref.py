@@ -32,3 +32,39 @@ def test_hadvuv_vadvuv_numpy_vs_oracle(kw):
     want_v = t["vdyn"].s((idx[0], idx[1]), (idx[2], idx[3]), (1, kz))
     assert np.abs(want_u).max() > 0 and np.abs(want_v).max() > 0
     assert _rel(ut, want_u) <= TOL and _rel(vt, want_v) <= TOL
+
+
+SOUND_IN = ("psb", "psdotb", "ac_u", "ac_v", "ac_pp", "ac_w", "ac_t", "a2_u", "a2_v", "a2_pp", "a2_w", "a2_t", "a2_qx",
+            "a1_u", "a1_v", "a1_pp", "a1_w", "a1_t", "a1_pr", "a1_rho", "uten", "vten", "ppten", "wten",
+            "a0_pr", "a0_rho", "a0_t", "a0_ps", "a0_rhof", "a0_dprddx", "a0_dprddy", "msfd", "msfx", "ht",
+            "dsigma", "sigma", "twt", "dpsdxm", "dpsdym", "s_estore", "s_astore", "tmask")
+SOUND_OUT = ("a1_u", "a2_u", "a1_v", "a2_v", "a1_pp", "a2_pp", "a1_w", "a2_w", "a1_t", "a2_t", "s_estore", "s_astore")
+
+
+@pytest.mark.parametrize("kw", [{}, {"ifupr": 0}], ids=["ifupr1", "ifupr0"])
+def test_sound_numpy_vs_oracle(kw):
+    """The whole of `sound` (Main/mod_sound.F90:163-718: istep sub-steps of explicit u,v, the column-implicit w/p'
+    solve with the 13x13 radiative upper BC, CFL, temperature correction, epilogue filters) on the inputs the
+    oracle's 4th step hands it."""
+    case = synth.make_case("small", **kw)
+    o = pyoracle.make_oracle(case.cfg)
+    synth.load_case(o, case)
+    o.step(3)
+    o.lib.lib.orc_break_before_sound(o.h, 1)
+    o.step(1)                                   # tend() up to `call sound`
+    o.lib.lib.orc_break_before_sound(o.h, 0)
+    assert nr.scalar(o, "alarm_day") == 0.0     # the daily tmask update is not part of this restatement
+    t = {n: nr.F(nr.tap(o, n).a.copy(), nr.tap(o, n).lb) for n in SOUND_IN}
+    rgas = (6.02214129e23 * 1.3806504e-23 / 28.96454) * 1000.0       # Share/mod_constants.F90:92-134
+    p = dict(jx=case.cfg.jx, iy=case.cfg.iy, kz=case.cfg.kz, dt=nr.scalar(o, "dt"), dx=nr.scalar(o, "dx"),
+             xkd=nr.scalar(o, "xkd"), bet=nr.scalar(o, "bet"), xgamma=nr.scalar(o, "xgamma"), dtsmax=nr.scalar(o, "dtsmax"),
+             lcount=nr.scalar(o, "lcount"), gnu1=case.cfg.gnu1, gnu2=case.cfg.gnu2, cpd=3.5 * rgas, ifupr=case.cfg.ifupr)
+    istep, cfl = nr.sound(t, p)
+    nr.call(o, "sound")
+    d = o.diag()
+    assert istep == d.istep and istep >= 4
+    assert abs(cfl - d.max_cfl) <= 1e-12 * d.max_cfl      # diag reports the maximum over the sub-steps
+    for n in SOUND_OUT:
+        want = nr.tap(o, n).a
+        assert np.abs(want).max() > 0 or n.startswith("s_"), n
+        assert _rel(t[n].a, want) <= TOL, (n, _rel(t[n].a, want))
