@@ -123,7 +123,11 @@ enum rcm_work {
   RCM_W_MO_ZETA = 17,  /* mo_atm%zeta   :2816-2824                             */
   RCM_W_MO_S = 18,     /* s (kz+1), generalized vertical velocity left by the
                         * last sound() of the step, Main/mod_moloch.F90:1022-1038 */
-  RCM_W_COUNT = 19
+  /* idynamic = 1, 2: atmc%qx(:,:,:,iqv|iqc), the unfiltered leapfrog forecast AFTER the negative-value repair of
+   * Main/mod_tendency.F90:381-393; defined on a step that repaired at least one point (or follows one) */
+  RCM_W_CQV = 19,
+  RCM_W_CQC = 20,
+  RCM_W_COUNT = 21
 };
 
 /* vertical-mode tables of the split-explicit scheme (idynamic = 1), computed
@@ -314,6 +318,27 @@ int rcm_dyn_profile_kernels(void);
  * rcm_dyn_init / rcm_dyn_step as NCCL send/recv on packed edge buffers. */
 int rcm_dyn_comm_unique_id(void* out128, int out_bytes);
 int rcm_dyn_comm_init(rcm_dyn* h, const void* nccl_unique_id, int id_bytes);
+
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The negative-moisture repair of Main/mod_tendency.F90:381-393 (the sweep rcm_dyn_step applies to atmc%qx,
+ * csrc/k_negq.cu) as a stand-alone, handle-less operator that allocates nothing: its scratch (lists of negative
+ * points, fill counts) is a file-scope static __device__ array (csrc/k_negq_static.cu) of RCM_NQS_MAX_CELLS list
+ * entries + RCM_NQS_MAX_PLANES counters = 4 MiB + 4 KiB, held by every GPU that loads the library until exit.
+ *   q_in, q_out : DEVICE pointers (distinct), nk planes of (nj, ni) doubles, j fastest, no padding.  q_out = q_in
+ *                 with every negative point of the plane interiors (j = 2..nj-1, i = 2..ni-1, 1-based) replaced by
+ *                 0.01 * sum|q(j-1:j+1,i-1:i+1)| / 9 in the reference's sequential sweep order (j, then i, ascending);
+ *                 the outermost ring is copied unchanged (boundary / ghost values as the sweep should see them).
+ *   n_repaired  : DEVICE pointer or NULL; receives the number of repaired points.
+ *   stream      : a cudaStream_t (NULL = the default stream); the call is asynchronous on it.
+ * Returns RCM_ERR_ARG when nj*ni*nk > RCM_NQS_MAX_CELLS or nk > RCM_NQS_MAX_PLANES (or nj, ni < 3, nk < 1, NULL or
+ * aliased arrays), RCM_ERR_CUDA on a runtime failure.  Calls no cudaMalloc / cudaFree / allocating library routine.
+ * The first call on a device looks up the scratch address (cudaGetSymbolAddress): make it outside graph capture.
+ * All calls share the scratch: calls that overlap on the GPU (other streams, concurrent graph launches) race. */
+#define RCM_NQS_MAX_CELLS 1048576
+#define RCM_NQS_MAX_PLANES 1024
+int rcm_dyn_negq_repair_static(const double* q_in, double* q_out, int32_t nj, int32_t ni, int32_t nk,
+                               unsigned long long* n_repaired, void* stream);
 
 /* replaces: memory_destroy (Main/mod_regcm_interface.F90:264). */
 int rcm_dyn_destroy(rcm_dyn* h);

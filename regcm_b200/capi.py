@@ -23,9 +23,9 @@ S_HT, S_MSFX, S_MSFD, S_CORIOL, S_XLAT, S_XLON, S_DLAT, S_SIGMA, S_MSFU, S_MSFV,
 LEVEL_A, LEVEL_B = 0, 1
 BDY_B0, BDY_B1, BDY_NEXT = 0, 1, 2
 (W_CR, W_QDOT, W_XKC, W_TH, W_RHO1, W_PR1, W_UTEN, W_VTEN, W_PPTEN, W_WTEN, W_OMEGA, W_PHI, W_PTEN,
- W_MO_P, W_MO_TVIRT, W_MO_FMZ, W_MO_FMZF, W_MO_ZETA, W_MO_S) = range(19)
+ W_MO_P, W_MO_TVIRT, W_MO_FMZ, W_MO_FMZF, W_MO_ZETA, W_MO_S, W_CQV, W_CQC) = range(21)
 WORK_NAMES = ("cr", "qdot", "xkc", "th", "rho1", "pr1", "uten", "vten", "ppten", "wten", "omega", "phi", "pten",
-              "mo_p", "mo_tvirt", "mo_fmz", "mo_fmzf", "mo_zeta", "mo_s")
+              "mo_p", "mo_tvirt", "mo_fmz", "mo_fmzf", "mo_zeta", "mo_s", "cqv", "cqc")
 # enum rcm_table: vertical-mode tables of the split-explicit scheme (idynamic = 1)
 T_HBAR, T_ZMATX, T_ZMATXR, T_TAU, T_VARPA1, T_AM, T_AN, T_TAU0 = range(8)
 
@@ -166,6 +166,8 @@ class CoreLib:
             "comm_init": ([vp, C.c_void_p, C.c_int], C.c_int),
             "stage_bdy_async": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
             "stage_wait": ([vp], C.c_int),
+            # handle-less, allocation-free operator (device pointers): include/regcm_dyn.h
+            "negq_repair_static": ([C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p], C.c_int),
         }.items():
             if hasattr(self.lib, p + opt):
                 fn = getattr(self.lib, p + opt)

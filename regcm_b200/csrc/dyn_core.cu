@@ -1623,6 +1623,8 @@ extern "C" int rcm_dyn_get_work(rcm_dyn* h, int id, double* a, const int32_t lb[
     case RCM_W_VTEN: p = f.vten; break;
     case RCM_W_PPTEN: p = f.ppten; break;
     case RCM_W_WTEN: p = f.wten; break;
+    case RCM_W_CQV: p = f.cqv; break;
+    case RCM_W_CQC: p = f.cqc; break;
     case RCM_W_OMEGA: p = h->hydro ? f.omega : nullptr; break;
     case RCM_W_PHI: p = h->hydro ? f.phi : nullptr; break;
     case RCM_W_PTEN: {
