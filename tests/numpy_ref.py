@@ -336,3 +336,115 @@ def _sound_solve(t, p, wk, ci, ci2, ps0c, bp, bm, bpxbm):
     dpterm = ci2(t["psb"])[:, :, None] * (ppc - ppold) / (cpm * ci(rho1))
     ci(t["a2_t"])[...] = ci(t["a2_t"]) + gnu1 * dpterm
     ci(t["a1_t"])[...] = ci(t["a1_t"]) + dpterm
+
+
+# ---------------------------------------------------------------------------------------------------------
+MINDEN = 1.0e-15                      # Main/mod_moloch.F90:96
+
+
+def _rdeno(t1, t2, t3, t4):
+    """Main/mod_moloch.F90:1090-1096."""
+    zzden = t3 - t4
+    return (t1 - t2) / np.copysign(np.maximum(np.abs(zzden), MINDEN), zzden)
+
+
+def _waf_phi(r, zamu, isgn):
+    """limiter and weight, :1135-1137."""
+    b = np.maximum(0.0, np.minimum(2.0, np.maximum(r, np.minimum(2.0 * r, 1.0))))
+    return isgn + zamu * b - isgn * b
+
+
+def wafone(pp, s, fmz, fmzf, u, v, rmu, rmv, mx2, dta, dx, dz, jx, iy, kz):
+    """Main/mod_moloch.F90:1098-1361, generic projection branch (iproj /= 'ROTLLR'), single rank: WAF advection of
+    one cross-point field, directional split z -> y -> x.  pp: F array, modified in place on the interior."""
+    Jci, Ici = (2, jx - 2), (2, iy - 2)
+    jcross1, jcross2, icross1, icross2 = 1, jx - 1, 1, iy - 1
+    zdtrdx, zdtrdy, zdtrdz = dta / dx, dta / dx, dta / dz
+    A = pp.a                                    # (jx-1, iy-1, kz), lower bounds 1
+    assert pp.lb == (1, 1, 1) or tuple(pp.lb) == (1, 1, 1)
+    jj = slice(Jci[0] - 1, Jci[1])              # 0-based interior slices
+    ii = slice(Ici[0] - 1, Ici[1])
+    P = A[jj, ii, :]
+    S = s.s(Jci, Ici, (1, kz + 1))
+    FZ, FZF = fmz.s(Jci, Ici, (1, kz)), fmzf.s(Jci, Ici, (1, kz + 1))
+    nj, ni = P.shape[:2]
+    # ---- vertical advection (:1118-1160) ----
+    wfw = np.zeros((nj, ni, kz + 1))            # wfw(j,1) = wfw(j,kzp1) = 0
+    for k in range(1, kz):                      # face k+1 between levels k and k+1
+        zamu = S[:, :, k] * zdtrdz              # s(j,i,k+1)
+        up = zamu >= 0.0
+        isgn = np.where(up, 1.0, -1.0)
+        k1_u, k1m1_u = k + 1, min(k + 2, kz)    # zamu >= 0
+        k1m1_d, k1_d = k, max(k - 1, 1)         # zamu < 0
+        p_k1 = np.where(up, P[:, :, k1_u - 1], P[:, :, k1_d - 1])
+        p_k1m1 = np.where(up, P[:, :, k1m1_u - 1], P[:, :, k1m1_d - 1])
+        r = _rdeno(p_k1, p_k1m1, P[:, :, k - 1], P[:, :, k])
+        zphi = _waf_phi(r, zamu, isgn)
+        wfw[:, :, k] = 0.5 * S[:, :, k] * ((1.0 + zphi) * P[:, :, k] + (1.0 - zphi) * P[:, :, k - 1])
+    wz = np.zeros((jx - 1, iy - 1, kz))         # full cross extent; only interior j columns are used
+    zrfmm = zdtrdz * FZ[:, :, 0] / FZF[:, :, 1]
+    zdv = -S[:, :, 1] * zrfmm * P[:, :, 0]
+    wz[jj, ii, 0] = P[:, :, 0] + wfw[:, :, 1] * zrfmm + zdv
+    for k in range(2, kz + 1):
+        zrfmm = zdtrdz * FZ[:, :, k - 1] / FZF[:, :, k]
+        zrfmp = zdtrdz * FZ[:, :, k - 1] / FZF[:, :, k - 1]
+        zdv = (S[:, :, k - 1] * zrfmp - S[:, :, k] * zrfmm) * P[:, :, k - 1]
+        wz[jj, ii, k - 1] = P[:, :, k - 1] - wfw[:, :, k - 1] * zrfmp + wfw[:, :, k] * zrfmm + zdv
+    wz[jj, 0, :] = wz[jj, Ici[0] - 1, :]        # has_bdybottom: wz(j,ice1,k) = wz(j,ici1,k)  (:1170-1184)
+    wz[jj, iy - 2, :] = wz[jj, Ici[1] - 1, :]   # has_bdytop:    wz(j,ice2,k) = wz(j,ici2,k)
+    return _wafone_horizontal(pp, wz, fmz, u, v, rmu, rmv, mx2, zdtrdx, zdtrdy, jx, iy, kz)
+
+
+def _wafone_horizontal(pp, wz, fmz, u, v, rmu, rmv, mx2, zdtrdx, zdtrdy, jx, iy, kz):
+    """Main/mod_moloch.F90:1271-1357: meridional then zonal pass of the generic branch."""
+    Jci, Ici, K = (2, jx - 2), (2, iy - 2), (1, kz)
+    jcross1, jcross2, icross1, icross2 = 1, jx - 1, 1, iy - 1
+    A = pp.a
+    jj = slice(Jci[0] - 1, Jci[1])
+    ii = slice(Ici[0] - 1, Ici[1])
+    P = A[jj, ii, :].copy()                     # pp of the divergence terms: the values before this call's update
+    # ---- meridional advection: faces i = ici1 .. ice2 (= iy-1) ----
+    If = np.arange(Ici[0], iy - 1 + 1)          # 1-based face index i
+    vf = v.s(Jci, (If[0], If[-1]), K) * rmv.s(Jci, (If[0], If[-1]))[:, :, None]     # v(j,i,k)*rmv(j,i)
+    zamu = vf * zdtrdy
+    pos = zamu > 0.0
+    isgn = np.where(pos, 1.0, -1.0)
+    ih = np.where(pos, If[None, :, None] - 1, np.minimum(If[None, :, None] + 1, icross2))
+    ihm1 = np.maximum(ih - 1, icross1)
+    W = wz[jj, :, :]                            # (nj, iy-1, kz), second axis = i-1
+    w_ih = np.take_along_axis(W, ih - 1, axis=1)
+    w_ihm1 = np.take_along_axis(W, ihm1 - 1, axis=1)
+    w_i = W[:, If - 1, :]
+    w_im1 = W[:, If - 2, :]
+    zphi = _waf_phi(_rdeno(w_ih, w_ihm1, w_i, w_im1), zamu, isgn)
+    zpby = 0.5 * vf * ((1.0 + zphi) * w_im1 + (1.0 - zphi) * w_i)                  # zpby(j, i), i = If
+    FZ = fmz.s(Jci, Ici, K)
+    zrfmn = zdtrdy * 2.0 * FZ / (FZ + fmz.s(Jci, (Ici[0] + 1, Ici[1] + 1), K))
+    zrfms = zdtrdy * 2.0 * FZ / (FZ + fmz.s(Jci, (Ici[0] - 1, Ici[1] - 1), K))
+    ni = Ici[1] - Ici[0] + 1
+    zdv = (vf[:, 1:ni + 1, :] * zrfmn - vf[:, 0:ni, :] * zrfms) * P
+    p0 = np.zeros((jx - 1, iy - 1, kz))
+    p0[jj, ii, :] = wz[jj, ii, :] + mx2.s(Jci, Ici)[:, :, None] * (zpby[:, 0:ni, :] * zrfms - zpby[:, 1:ni + 1, :] * zrfmn + zdv)
+    p0[0, ii, :] = p0[Jci[0] - 1, ii, :]        # has_bdyleft : p0(jce1,i,k) = p0(jci1,i,k)
+    p0[jx - 2, ii, :] = p0[Jci[1] - 1, ii, :]   # has_bdyright: p0(jce2,i,k) = p0(jci2,i,k)
+    # ---- zonal advection: faces j = jci1 .. jce2 (= jx-1) ----
+    Jf = np.arange(Jci[0], jx - 1 + 1)
+    uf = u.s((Jf[0], Jf[-1]), Ici, K) * rmu.s((Jf[0], Jf[-1]), Ici)[:, :, None]     # u(j,i,k)*rmu(j,i)
+    zamu = uf * zdtrdx
+    pos = zamu > 0.0
+    isgn = np.where(pos, 1.0, -1.0)
+    jh = np.where(pos, Jf[:, None, None] - 1, np.minimum(Jf[:, None, None] + 1, jcross2))
+    jhm1 = np.maximum(jh - 1, jcross1)
+    Q = p0[:, ii, :]                            # (jx-1, ni, kz), first axis = j-1
+    q_jh = np.take_along_axis(Q, jh - 1, axis=0)
+    q_jhm1 = np.take_along_axis(Q, jhm1 - 1, axis=0)
+    q_j = Q[Jf - 1, :, :]
+    q_jm1 = Q[Jf - 2, :, :]
+    zphi = _waf_phi(_rdeno(q_jh, q_jhm1, q_j, q_jm1), zamu, isgn)
+    zpbw = 0.5 * uf * ((1.0 + zphi) * q_jm1 + (1.0 - zphi) * q_j)                  # zpbw(j, i), j = Jf
+    zrfme = zdtrdx * 2.0 * FZ / (FZ + fmz.s((Jci[0] + 1, Jci[1] + 1), Ici, K))
+    zrfmw = zdtrdx * 2.0 * FZ / (FZ + fmz.s((Jci[0] - 1, Jci[1] - 1), Ici, K))
+    nj = Jci[1] - Jci[0] + 1
+    zdv = (uf[1:nj + 1, :, :] * zrfme - uf[0:nj, :, :] * zrfmw) * P
+    A[jj, ii, :] = p0[jj, ii, :] + mx2.s(Jci, Ici)[:, :, None] * (zpbw[0:nj, :, :] * zrfmw - zpbw[1:nj + 1, :, :] * zrfme + zdv)
+    return pp

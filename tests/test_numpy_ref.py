@@ -68,3 +68,26 @@ def test_sound_numpy_vs_oracle(kw):
         want = nr.tap(o, n).a
         assert np.abs(want).max() > 0 or n.startswith("s_"), n
         assert _rel(t[n].a, want) <= TOL, (n, _rel(t[n].a, want))
+
+
+def test_wafone_numpy_vs_oracle():
+    """One `wafone` call of the MOLOCH core (Main/mod_moloch.F90:1098-1361, generic projection branch) on theta_v with
+    the velocities, metric factors and generalized vertical velocity `s` the oracle holds after 2 steps."""
+    case = synth.make_case("smallm")
+    o = pyoracle.make_oracle(case.cfg)
+    synth.load_case(o, case)
+    o.step(2)
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    t = {n: nr.tap(o, n) for n in ("m_tetav", "m_s", "m_fmz", "m_fmzf", "m_u", "m_v", "rmu", "rmv", "mx2")}
+    assert np.abs(t["m_s"].a).max() > 0 and np.abs(t["m_u"].a).max() > 1.0
+    pp = nr.F(t["m_tetav"].a.copy(), t["m_tetav"].lb)
+    before = pp.a.copy()
+    dta = case.cfg.dt / case.cfg.mo_nadv
+    nr.wafone(pp, t["m_s"], t["m_fmz"], t["m_fmzf"], t["m_u"], t["m_v"], t["rmu"], t["rmv"], t["mx2"], dta,
+              case.cfg.ds * 1000.0, nr.scalar(o, "mo_dz"), jx, iy, kz)
+    nr.call(o, "wafone_tetav", dta)
+    want = nr.tap(o, "m_tetav").a
+    change = np.abs(want - before).max()
+    assert change > 1e-3                         # the pass does something
+    assert np.abs(pp.a - want).max() <= 1e-12 * np.abs(want).max()
+    assert np.abs(pp.a - want).max() <= 1e-9 * change   # and agrees on the increment, not just on the 300 K background
