@@ -334,23 +334,33 @@ def run_gpu(args):
             out_lbub[fid] = (lbs, ubs)
         h2d = sum(v.nbytes for v in pinned_in.values())
         d2h = sum(v.nbytes for v in pinned_out.values())
+        # warm the export path once outside the timed region (first use allocates the device snapshots)
+        for fid, v in pinned_out.items():
+            core.get_state_async(fid, capi.LEVEL_A, v, out_lbub[fid][0], out_lbub[fid][1])
+        core.get_state_wait()
         barrier()
         t0 = time.perf_counter()
-        for fid, v in pinned_in.items():   # queued on the library's copy stream, overlaps the steps
+        for fid, v in pinned_in.items():   # H2D of the next ICBC record, queued on the library's copy stream
             core.stage_bdy_async(fid, v, lb=(lb[0], lb[1], 1))
+        for fid, v in pinned_out.items():  # D2H of the state the previous interval produced (device snapshot first)
+            core.get_state_async(fid, capi.LEVEL_A, v, out_lbub[fid][0], out_lbub[fid][1])
+        last = None
         for _ in range(args.steps):
-            core.step(1)
-            core.diag()
+            core.step_async(1)
+            last = core.diag()             # non-blocking: newest completed step's scalars from pinned host memory
+        core.sync()                        # verdict of the K steps (CFL / NaN / halo), reduced over the ranks
         core.stage_wait()
-        for fid, v in pinned_out.items():
-            core.get_state(fid, capi.LEVEL_A, lb=out_lbub[fid][0], ub=out_lbub[fid][1], out=v)
+        core.get_state_wait()
         torch.cuda.synchronize()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": cells * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d / args.steps,
-               "d2h_bytes_per_step": d2h / args.steps, "ms_per_step": e2e_s / args.steps * 1e3,
-               "what": f"per rank: stage one ICBC record ({len(pinned_in)} fields) from pinned host memory (rcm_dyn_stage_bdy_async, overlapped with the "
-                       f"steps), K x {{rcm_dyn_step(1); rcm_dyn_diag}}, rcm_dyn_stage_wait, download the {len(pinned_out)} level-a prognostic fields to "
-                       "pinned host memory (synchronous); bytes amortised over the K steps"}
+               "d2h_bytes_per_step": (d2h + 32 * args.steps) / args.steps, "ms_per_step": e2e_s / args.steps * 1e3,
+               "what": f"per rank, one coupling/output interval as a driver would run it, everything inside the timed region: "
+                       f"rcm_dyn_stage_bdy_async of one ICBC record ({len(pinned_in)} fields, pinned host -> device), "
+                       f"rcm_dyn_get_state_async of the {len(pinned_out)} level-a prognostic fields (device snapshot, then D2H into "
+                       f"pinned host memory on a private stream), K x {{rcm_dyn_step_async(1); rcm_dyn_diag (32-byte per-step verdict "
+                       f"D2H, read without blocking)}}, rcm_dyn_sync, rcm_dyn_stage_wait, rcm_dyn_get_state_wait; both transfers "
+                       "overlap the steps; bytes amortised over the K steps"}
 
     # ---- CPU baseline (rank 0, N = 1 only): the oracle on a bounded sample ----
     cpu = None

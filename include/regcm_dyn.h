@@ -130,6 +130,32 @@ enum rcm_work {
   RCM_W_COUNT = 21
 };
 
+/* the slices `mkslice` prepares for the physical parametrizations (type `slice`, Main/mpplib/mod_regcm_types.F90;
+ * Main/mod_slice.F90:167-308, idynamic = 1, 2), cross grid, level-b (tau-1) state decoupled from p*.  3-D with kz
+ * levels unless noted. */
+enum rcm_slice {
+  RCM_SL_TB3D = 0,   /* atms%tb3d    T [K]                                        :190 */
+  RCM_SL_QVB3D = 1,  /* atms%qxb3d(iqv), floored at minqq                         :191 */
+  RCM_SL_QCB3D = 2,  /* atms%qxb3d(iqc), floored at 0                             :194 */
+  RCM_SL_UBX3D = 3,  /* atms%ubx3d   u on cross points [m/s]                      :180-183 */
+  RCM_SL_VBX3D = 4,  /* atms%vbx3d                                                :184-187 */
+  RCM_SL_PB3D = 5,   /* atms%pb3d    pressure at half levels [Pa]                 :211-217,233-235 */
+  RCM_SL_PF3D = 6,   /* atms%pf3d    pressure at full levels [Pa], kz+1 levels    :221-231,239-241 */
+  RCM_SL_PS2D = 7,   /* atms%ps2d    surface pressure [Pa], 2-D                   :218-220,236-238 */
+  RCM_SL_RHOB3D = 8, /* atms%rhob3d  density [kg/m3]                              :253 */
+  RCM_SL_TH3D = 9,   /* atms%th3d    potential temperature                        :248-251 */
+  RCM_SL_TV3D = 10,  /* atms%tv3d    virtual temperature                          :202-205 */
+  RCM_SL_TP3D = 11,  /* atms%tp3d    T brought to the surface pressure            :254-255 */
+  RCM_SL_WPX3D = 12, /* atms%wpx3d   omega [Pa/s], interior cross points          :258-261,267-269 */
+  RCM_SL_WB3D = 13,  /* atms%wb3d    w [m/s], kz+1 levels                         :262-264,270-276 */
+  RCM_SL_ZQ = 14,    /* atms%zq      height of full levels [m], kz+1 levels (idynamic = 2: atm0%zf)  :283-292 */
+  RCM_SL_ZA = 15,    /* atms%za      height of half levels (idynamic = 2: atm0%z) :293-295 */
+  RCM_SL_DZQ = 16,   /* atms%dzq     layer thickness (idynamic = 2: atm0%dzf)     :296-298 */
+  RCM_SL_QSB3D = 17, /* atms%qsb3d   saturation mixing ratio (pfwsat)             :301-303 */
+  RCM_SL_RHB3D = 18, /* atms%rhb3d   relative humidity, clamped to [rhmin, rhmax] :304-307 */
+  RCM_SL_COUNT = 19
+};
+
 /* vertical-mode tables of the split-explicit scheme (idynamic = 1), computed
  * once by `spinit`/`vmodes` (Main/mod_split.F90:75-175, Main/mod_vmodes.F90:86-594).
  * Column-major like the Fortran arrays. */
@@ -267,6 +293,47 @@ int rcm_dyn_init(rcm_dyn* h);
  * Main/mod_bdycod.F90:654,1109).  Synchronous: the state is observable with
  * rcm_dyn_get_state on return. */
 int rcm_dyn_step(rcm_dyn* h, int nsteps);
+
+/* Physics coupling boundary (idynamic = 1, 2).  replaces: the place where `tend` hands over to the physical
+ * parametrizations and takes their tendencies back (Main/mod_tendency.F90:271 `call physical_parametrizations`,
+ * :1682-1820; slices: Main/mod_slice.F90:167-308; sums: Main/mod_tendency.F90:285-314,331-335,404-411).
+ *   rcm_dyn_step_pre_physics   everything of `tend` the parametrizations depend on (surface_pressures, decouple,
+ *                              compute_omega, the inputs of mkslice, calc_coeff); synchronous.
+ *   rcm_dyn_get_slice          one member of `atms` (enum rcm_slice), computed on request from the level-b state,
+ *                              on the cross grid with the usual lb/ub window.  Valid at any time between steps; omega
+ *                              (WPX3D, WB3D) of the hydrostatic core only between the pre- and post-physics calls.
+ *   rcm_dyn_set_phys_tend      aten(:,:,:,pc_physic) of one prognostic (RCM_F_U, V: dot grid; T, QV, QC, PP, W: cross
+ *                              grid; coupled with p* like the reference's).  Stays in effect — also for
+ *                              rcm_dyn_step — until replaced or cleared; zero until first set.
+ *   rcm_dyn_step_post_physics  the rest of `tend` (advection ... diffusion, the sums, forecast, time filters,
+ *                              sound / splitf), then bdyin / bdyval as in rcm_dyn_step.
+ * pre_physics; post_physics with no tendencies set equals rcm_dyn_step(h, 1) bit for bit. */
+int rcm_dyn_step_pre_physics(rcm_dyn* h);
+int rcm_dyn_get_slice(rcm_dyn* h, int slice_id, double* a, const int32_t lb[3], const int32_t ub[3]);
+int rcm_dyn_set_phys_tend(rcm_dyn* h, int field, const double* a, const int32_t lb[3], const int32_t ub[3]);
+int rcm_dyn_clear_phys_tend(rcm_dyn* h);
+int rcm_dyn_step_post_physics(rcm_dyn* h);
+
+/* Asynchronous form of rcm_dyn_step for drivers that overlap the time loop with their own work (the reference's
+ * RCM_run is synchronous: Main/mod_regcm_interface.F90:172-228; its output and boundary input block the loop).
+ * rcm_dyn_step_async enqueues nsteps steps on the library's stream and returns without waiting for them (it still
+ * waits once per simulated day for the tmask update of Main/mod_sound.F90:500-547); rcm_dyn_sync waits for
+ * everything enqueued and returns the verdict of the batch, identical on all ranks (RCM_ERR_CFL / RCM_ERR_NAN /
+ * RCM_ERR_NCCL).  rcm_dyn_step(h, n) == rcm_dyn_step_async(h, n); rcm_dyn_sync(h).  While steps are in flight
+ * rcm_dyn_diag does not block: it reports the newest step whose scalars have already arrived in page-locked host
+ * memory (one 32-byte D2H copy follows every step; this rank's values).  Every other accessor (get/set_state,
+ * get_work, set_bdy) synchronises first. */
+int rcm_dyn_step_async(rcm_dyn* h, int nsteps);
+int rcm_dyn_sync(rcm_dyn* h);
+
+/* Asynchronous state export — what `output` / write_savefile do between steps (Main/mod_regcm_interface.F90:211-222),
+ * without stopping the time loop: a device-side snapshot of the field is taken in stream order (after the steps
+ * already enqueued) and copied into `a` on a private stream while later steps run.  `a` should be page-locked and
+ * must stay valid until rcm_dyn_get_state_wait returns.  Same field / level / bounds conventions as
+ * rcm_dyn_get_state.  The first export of a field allocates its snapshot buffer (one 3-D field). */
+int rcm_dyn_get_state_async(rcm_dyn* h, int field, int level, double* a,
+                            const int32_t lb[3], const int32_t ub[3]);
+int rcm_dyn_get_state_wait(rcm_dyn* h);
 
 /* state export/import = what write_savefile/read_savefile carry for the
  * dynamics (Main/mod_savefile.F90:564-1264): COUPLED atm1/atm2 fields. */

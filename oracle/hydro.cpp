@@ -459,15 +459,15 @@ void Oracle::tend_hydro() {
   // tendency sums (:285-294,331-335)
   for (int k = 1; k <= kz; ++k)
     for (int i = ici1; i <= ici2; ++i)
-      for (int j = jci1; j <= jci2; ++j) tten(j, i, k) = tten(j, i, k) + tdyn(j, i, k) + d_zero;
+      for (int j = jci1; j <= jci2; ++j) tten(j, i, k) = tten(j, i, k) + tdyn(j, i, k) + phy3(tphy, j, i, k);
   for (int k = 1; k <= kz; ++k)
     for (int i = ici1; i <= ici2; ++i)
-      for (int j = jci1; j <= jci2; ++j) qxten(j, i, k, iqv) = qxten(j, i, k, iqv) + qxdyn(j, i, k, iqv) + d_zero;
+      for (int j = jci1; j <= jci2; ++j) qxten(j, i, k, iqv) = qxten(j, i, k, iqv) + qxdyn(j, i, k, iqv) + phy4(j, i, k, iqv);
   if (cfg.ipptls > 0)
     for (int n = iqfrst; n <= iqlst; ++n)
       for (int k = 1; k <= kz; ++k)
         for (int i = ici1; i <= ici2; ++i)
-          for (int j = jci1; j <= jci2; ++j) qxten(j, i, k, n) = qxten(j, i, k, n) + qxdyn(j, i, k, n) + d_zero;
+          for (int j = jci1; j <= jci2; ++j) qxten(j, i, k, n) = qxten(j, i, k, n) + qxdyn(j, i, k, n) + phy4(j, i, k, n);
   // forecast t, qv, qc at tau+1 (:368-393)
   for (int k = 1; k <= kz; ++k)
     for (int i = ici1; i <= ici2; ++i)
@@ -485,8 +485,8 @@ void Oracle::tend_hydro() {
   for (int k = 1; k <= kz; ++k)
     for (int i = idi1; i <= idi2; ++i)
       for (int j = jdi1; j <= jdi2; ++j) {
-        uten(j, i, k) = uten(j, i, k) + udyn(j, i, k) + d_zero;
-        vten(j, i, k) = vten(j, i, k) + vdyn(j, i, k) + d_zero;
+        uten(j, i, k) = uten(j, i, k) + udyn(j, i, k) + phy3(uphy, j, i, k);
+        vten(j, i, k) = vten(j, i, k) + vdyn(j, i, k) + phy3(vphy, j, i, k);
       }
   // time filters (:419-427)
   filter_ra_2d(psa, psb, psc, cfg.gnu1);

@@ -141,6 +141,18 @@ struct Oracle {
   std::vector<int> rt_j, rt_i;  // first dot index of every tile along j / i (set_repair_tiles; empty = one domain)
   void repair_negative_qx();
 
+  // ---- physics coupling boundary (oracle/physics.cpp) ----
+  bool phys_on = false;
+  A3 uphy, vphy, tphy, ppphy, wphy;     // aten(:,:,:,pc_physic)
+  A4 qxphy;
+  void pre_physics();
+  void ensure_phys();
+  void clear_phys();
+  int set_phys(int field, const double* a, const int32_t lb[3], const int32_t ub[3]);
+  int get_slice(int id, double* a, const int32_t lb[3], const int32_t ub[3]);
+  inline double phy3(const A3& p, int j, int i, int k) const { return phys_on ? p(j, i, k) : d_zero; }
+  inline double phy4(int j, int i, int k, int n) const { return phys_on ? qxphy(j, i, k, n) : d_zero; }
+
   // ---- hydrostatic core (idynamic = 1; oracle/hydro.cpp, oracle/split.cpp) ----
   bool hydro = false;
   A2 pten, pten_raw, rpsc, ptn2d, pt22d;          // mod_tendency.F90:63-66

@@ -373,26 +373,26 @@ void Oracle::tend() {
   boundary(); lap("boundary");
   // physical_parametrizations: OFF
   diffusion(); lap("diffusion");
-  // tendency sums (:285-314,331-335); the physics component is identically 0
+  // tendency sums (:285-314,331-335): ten = ten + dyn + phy (aten(pc_physic), zero until set: oracle/physics.cpp)
   for (int k = 1; k <= kz; ++k)
     for (int i = ici1; i <= ici2; ++i)
-      for (int j = jci1; j <= jci2; ++j) tten(j, i, k) = tten(j, i, k) + tdyn(j, i, k) + d_zero;
+      for (int j = jci1; j <= jci2; ++j) tten(j, i, k) = tten(j, i, k) + tdyn(j, i, k) + phy3(tphy, j, i, k);
   for (int k = 1; k <= kz; ++k)
     for (int i = ici1; i <= ici2; ++i)
       for (int j = jci1; j <= jci2; ++j)
-        qxten(j, i, k, iqv) = qxten(j, i, k, iqv) + qxdyn(j, i, k, iqv) + d_zero;
+        qxten(j, i, k, iqv) = qxten(j, i, k, iqv) + qxdyn(j, i, k, iqv) + phy4(j, i, k, iqv);
   for (int k = 1; k <= kzp1; ++k)
     for (int i = ici1; i <= ici2; ++i)
-      for (int j = jci1; j <= jci2; ++j) wten(j, i, k) = wten(j, i, k) + wdyn(j, i, k) + d_zero;
+      for (int j = jci1; j <= jci2; ++j) wten(j, i, k) = wten(j, i, k) + wdyn(j, i, k) + phy3(wphy, j, i, k);
   for (int k = 1; k <= kz; ++k)
     for (int i = ici1; i <= ici2; ++i)
-      for (int j = jci1; j <= jci2; ++j) ppten(j, i, k) = ppten(j, i, k) + ppdyn(j, i, k) + d_zero;
+      for (int j = jci1; j <= jci2; ++j) ppten(j, i, k) = ppten(j, i, k) + ppdyn(j, i, k) + phy3(ppphy, j, i, k);
   if (cfg.ipptls > 0)
     for (int n = iqfrst; n <= iqlst; ++n)
       for (int k = 1; k <= kz; ++k)
         for (int i = ici1; i <= ici2; ++i)
           for (int j = jci1; j <= jci2; ++j)
-            qxten(j, i, k, n) = qxten(j, i, k, n) + qxdyn(j, i, k, n) + d_zero;
+            qxten(j, i, k, n) = qxten(j, i, k, n) + qxdyn(j, i, k, n) + phy4(j, i, k, n);
   if (cfg.ifrayd == 1) {  // i_crm /= 1 (:356-364)
     raydamp3(a0_z, a2_t, tten, xtb);
     raydampqv(a0_z, a2_qx, qxten, xqb);
@@ -414,8 +414,8 @@ void Oracle::tend() {
   for (int k = 1; k <= kz; ++k)
     for (int i = idi1; i <= idi2; ++i)
       for (int j = jdi1; j <= jdi2; ++j) {
-        uten(j, i, k) = uten(j, i, k) + udyn(j, i, k) + d_zero;
-        vten(j, i, k) = vten(j, i, k) + vdyn(j, i, k) + d_zero;
+        uten(j, i, k) = uten(j, i, k) + udyn(j, i, k) + phy3(uphy, j, i, k);
+        vten(j, i, k) = vten(j, i, k) + vdyn(j, i, k) + phy3(vphy, j, i, k);
       }
   // time filters (:422-427)
   filter_ra_3d(a1_t, a2_t, ac_t, cfg.gnu1);

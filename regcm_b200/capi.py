@@ -26,6 +26,11 @@ BDY_B0, BDY_B1, BDY_NEXT = 0, 1, 2
  W_MO_P, W_MO_TVIRT, W_MO_FMZ, W_MO_FMZF, W_MO_ZETA, W_MO_S, W_CQV, W_CQC) = range(21)
 WORK_NAMES = ("cr", "qdot", "xkc", "th", "rho1", "pr1", "uten", "vten", "ppten", "wten", "omega", "phi", "pten",
               "mo_p", "mo_tvirt", "mo_fmz", "mo_fmzf", "mo_zeta", "mo_s", "cqv", "cqc")
+# enum rcm_slice: what mkslice hands to the physical parametrizations (Main/mod_slice.F90:167-308)
+(SL_TB3D, SL_QVB3D, SL_QCB3D, SL_UBX3D, SL_VBX3D, SL_PB3D, SL_PF3D, SL_PS2D, SL_RHOB3D, SL_TH3D, SL_TV3D, SL_TP3D,
+ SL_WPX3D, SL_WB3D, SL_ZQ, SL_ZA, SL_DZQ, SL_QSB3D, SL_RHB3D) = range(19)
+SLICE_NAMES = ("tb3d", "qvb3d", "qcb3d", "ubx3d", "vbx3d", "pb3d", "pf3d", "ps2d", "rhob3d", "th3d", "tv3d", "tp3d",
+               "wpx3d", "wb3d", "zq", "za", "dzq", "qsb3d", "rhb3d")
 # enum rcm_table: vertical-mode tables of the split-explicit scheme (idynamic = 1)
 T_HBAR, T_ZMATX, T_ZMATXR, T_TAU, T_VARPA1, T_AM, T_AN, T_TAU0 = range(8)
 
@@ -166,6 +171,16 @@ class CoreLib:
             "comm_init": ([vp, C.c_void_p, C.c_int], C.c_int),
             "stage_bdy_async": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
             "stage_wait": ([vp], C.c_int),
+            "step_async": ([vp, C.c_int], C.c_int),
+            "sync": ([vp], C.c_int),
+            "get_state_async": ([vp, C.c_int, C.c_int, _DP, _I3, _I3], C.c_int),
+            "get_state_wait": ([vp], C.c_int),
+            # physics coupling boundary
+            "step_pre_physics": ([vp], C.c_int),
+            "step_post_physics": ([vp], C.c_int),
+            "set_phys_tend": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
+            "clear_phys_tend": ([vp], C.c_int),
+            "get_slice": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
             # handle-less, allocation-free operator (device pointers): include/regcm_dyn.h
             "negq_repair_static": ([C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p], C.c_int),
         }.items():
@@ -245,6 +260,46 @@ class DynCore:
 
     def step(self, n: int = 1):
         self._check(self.lib.step(self.h, n))
+
+    # -- physics coupling boundary: the step splits where `tend` calls physical_parametrizations -----------------
+    def step_pre_physics(self):
+        self._check(self.lib.step_pre_physics(self.h))
+
+    def step_post_physics(self):
+        self._check(self.lib.step_post_physics(self.h))
+
+    def set_phys_tend(self, field: int, a: np.ndarray, lb=(1, 1, 1)):
+        """aten(:,:,:,pc_physic) of one prognostic (coupled with p*), in effect until replaced or cleared."""
+        a = self._f(a)
+        ub = tuple(lb[d] + a.shape[d] - 1 for d in range(3))
+        self._check(self.lib.set_phys_tend(self.h, field, a.ctypes.data_as(_DP), *_bounds(lb, ub)))
+
+    def clear_phys_tend(self):
+        self._check(self.lib.clear_phys_tend(self.h))
+
+    def get_slice(self, sid: int) -> np.ndarray:
+        """One slice of `atms` on the whole cross grid (jx-1, iy-1, nk)."""
+        nk = self.kz + 1 if sid in (SL_PF3D, SL_WB3D, SL_ZQ) else 1 if sid == SL_PS2D else self.kz
+        ub = (self.jx - 1, self.iy - 1, nk)
+        out = np.zeros(ub, dtype=np.float64, order="F")
+        self._check(self.lib.get_slice(self.h, sid, out.ctypes.data_as(_DP), *_bounds((1, 1, 1), ub)))
+        return out
+
+    def step_async(self, n: int = 1):
+        """Enqueue n steps without waiting (rcm_dyn_step_async); sync() returns the verdict of the batch."""
+        self._check(self.lib.step_async(self.h, n))
+
+    def sync(self):
+        self._check(self.lib.sync(self.h))
+
+    def get_state_async(self, field: int, level: int, out: np.ndarray, lb, ub):
+        """Queue the export of one field into `out` (Fortran-ordered float64, ideally page-locked); it is complete
+        after get_state_wait()."""
+        assert out.dtype == np.float64 and out.flags.f_contiguous and out.shape == tuple(ub[d] - lb[d] + 1 for d in range(3))
+        self._check(self.lib.get_state_async(self.h, field, level, out.ctypes.data_as(_DP), *_bounds(lb, ub)))
+
+    def get_state_wait(self):
+        self._check(self.lib.get_state_wait(self.h))
 
     def get_state(self, field: int, level: int = LEVEL_A, lb=None, ub=None, out=None) -> np.ndarray:
         shp = self.field_shape(field)

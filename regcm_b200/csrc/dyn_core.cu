@@ -45,6 +45,8 @@ void launch_snd_wfwd_tma(const Geom&, const Fields&, const StepScalars&, cudaStr
 void launch_snd_wback(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_snd_final(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_negq_repair(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
+void launch_slice(const Geom&, const Fields&, int id, int hydro, double ptop, double p0, double tlp, double ts0, double dx8, double* out, cudaStream_t);
+void launch_window(bool pack, double* buf, double* p_shifted, int j0, int i0, int k0, int n1, int n2, int nk, int si, long long sk, cudaStream_t st);
 void launch_couple(const Geom&, double*, const double*, int, int, int, int, int, cudaStream_t);
 void launch_timeint(const Geom&, const double*, const double*, double*, double, int, int, int, int, int, cudaStream_t);
 void launch_bdyval(const Geom&, const Fields&, const double*, const double*, const double*, const int2*, int,
@@ -155,6 +157,26 @@ struct rcm_dyn {
   int64_t launches = 0;
   double last_ms = 0;
   Halo halo;
+  // asynchronous stepping (rcm_dyn_step_async / rcm_dyn_sync): steps enqueued and not yet finished
+  bool pending = false;
+  int pending_steps = 0;
+  // per-step verdicts, copied D2H on the compute stream after every step into a pinned ring (read without blocking by rcm_dyn_diag)
+  struct VSlot { unsigned long long cfl[2], negq, nanf, ps[2]; };
+  enum { kVRing = 64 };
+  VSlot* vring = nullptr;                 // pinned host memory
+  cudaEvent_t vev[kVRing] = {nullptr};
+  int64_t vlcount[kVRing] = {0};
+  int64_t vhead = 0;                      // slots written so far
+  int64_t vdone = -1;                     // newest slot known to be complete
+  // asynchronous state export (rcm_dyn_get_state_async): device snapshots + D2H on a private stream
+  cudaStream_t st_out = nullptr;
+  double* snap[2 * RCM_F_COUNT] = {nullptr};
+  cudaEvent_t ev_snap[2 * RCM_F_COUNT] = {nullptr}, ev_out[2 * RCM_F_COUNT] = {nullptr};
+  bool out_pending = false;
+  // physics coupling boundary: rcm_dyn_step_pre_physics ran the head of `tend` and the tail is owed
+  bool mid_step = false, head_only = false;
+  double* slice_buf = nullptr;   // one 3-D field: the slice rcm_dyn_get_slice asked for
+  double* stage_dev = nullptr;   // contiguous landing buffer of rcm_dyn_stage_bdy_async (one 3-D field)
 };
 
 // host accessors in the padded geometry
@@ -196,6 +218,9 @@ static int fail(rcm_dyn* h, int code, const std::string& msg) {
   if (h) h->err = msg;
   return code;
 }
+static int finish_steps(rcm_dyn* h);   // waits for steps enqueued by rcm_dyn_step_async; every accessor calls it first
+static int tend(rcm_dyn* h);
+static int download3(rcm_dyn* h, const double* dev_shifted, double* a, const int32_t* lb, const int32_t* ub, int nk);
 
 // ---------------------------------------------------------------------------
 extern "C" int rcm_dyn_default_cfg(rcm_cfg* c, int idynamic) {
@@ -419,9 +444,10 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
     double* e = dev_alloc_raw<double>(h, (size_t)g.esi * h->eni); ok = ok && e; f.estore = e ? e + h->eoff : nullptr;
   }
   f.tmask = dev_alloc_raw<double>(h, 169);
-  f.cflbits = dev_alloc_raw<unsigned long long>(h, 2);
-  f.negq = dev_alloc_raw<unsigned long long>(h, 1);
-  f.nanflag = dev_alloc_raw<int>(h, 1);
+  {  // one contiguous verdict block: [0..1] CFL maxima, [2] negative-q count, [3] NaN flag (one D2H copy per step)
+    unsigned long long* blk = dev_alloc_raw<unsigned long long>(h, 4);
+    f.cflbits = blk; f.negq = blk ? blk + 2 : nullptr; f.nanflag = blk ? (int*)(blk + 3) : nullptr;
+  }
   f.nq_list = dev_alloc_raw<int>(h, (size_t)2 * g.kz * (size_t)g.sk);
   f.nq_cnt = dev_alloc_raw<int>(h, (size_t)2 * g.kz);
   ok = ok && f.hefc && f.hegc && f.hefd && f.hegd && f.tmask && f.cflbits && f.negq && f.nanflag && f.nq_list && f.nq_cnt;
@@ -565,6 +591,7 @@ static double* ps_slot(rcm_dyn* h, int slot) {
 
 extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
   if (field == RCM_F_PS) {
     if (!h->hydro && !h->moloch) return fail(h, RCM_ERR_ARG, "ps boundary data exist for idynamic = 1 and 3 only");
     double* dst2 = ps_slot(h, slot);
@@ -603,8 +630,28 @@ extern "C" int rcm_dyn_stage_bdy_async(rcm_dyn* h, int field, const double* a, c
     CUDA_OK(cudaStreamCreateWithFlags(&h->st_copy, cudaStreamNonBlocking));
     CUDA_OK(cudaEventCreateWithFlags(&h->ev_stage, cudaEventDisableTiming));
   }
-  int rc = copy3d(h, dst_async, a, lb, ub, nk, true, h->st_copy, false);
-  if (rc) return rc;
+  if (h->pending) {   // steps enqueued by rcm_dyn_step_async may still read the buffer this copy overwrites
+    CUDA_OK(cudaEventRecord(h->ev_fork, h->st));
+    CUDA_OK(cudaStreamWaitEvent(h->st_copy, h->ev_fork, 0));
+  }
+  {
+    const Geom& g = h->g;
+    const int jlo = std::max(lb[0], g.jde1 - RCM_HALO), jhi = std::min(ub[0], g.jde2 + RCM_HALO);
+    const int ilo = std::max(lb[1], g.ide1 - RCM_HALO), ihi = std::min(ub[1], g.ide2 + RCM_HALO);
+    const int klo = std::max(lb[2], 1), khi = std::min(ub[2], nk);
+    if (jhi >= jlo && ihi >= ilo && khi >= klo && jlo == lb[0] && jhi == ub[0] && ilo == lb[1] && ihi == ub[1]) {
+      // whole (j,i) planes of the caller's array: ONE contiguous H2D copy into a landing buffer, unpacked on the device
+      if (!h->stage_dev) CUDA_OK(cudaMalloc((void**)&h->stage_dev, (size_t)g.sk * (size_t)g.kzp1 * sizeof(double)));
+      const int n1 = jhi - jlo + 1, n2 = ihi - ilo + 1, nkk = khi - klo + 1;
+      CUDA_OK(cudaMemcpyAsync(h->stage_dev, a + (size_t)n1 * n2 * (size_t)(klo - lb[2]), (size_t)n1 * n2 * nkk * sizeof(double),
+                              cudaMemcpyHostToDevice, h->st_copy));
+      launch_window(false, h->stage_dev, dst_async, jlo, ilo, klo, n1, n2, nkk, g.si, g.sk, h->st_copy);
+      h->launches += 1;
+    } else {
+      int rc = copy3d(h, dst_async, a, lb, ub, nk, true, h->st_copy, false);
+      if (rc) return rc;
+    }
+  }
   CUDA_OK(cudaEventRecord(h->ev_stage, h->st_copy));
   h->stage_pending = true;
 #else
@@ -1317,9 +1364,13 @@ static int tend_hydro(rcm_dyn* h) {
   StepScalars s2 = s; s2.cq_mode = 1;   // second pass of k_h_tq: exits at once unless the first one found negative moisture
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.nq_cnt, 0, (size_t)2 * g.kz * sizeof(int), h->st));
-  TIMED(KID_H_PS, 2, (launch_h_ps(g, f, h->st), launch_h_rimcopy(g, f, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, h->st)));
-  TIMED(KID_H_PREP, 1, launch_h_prep(g, f, s, h->st));
-  TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
+  if (!h->mid_step) {   // head of `tend`: everything physical_parametrizations depends on (Main/mod_tendency.F90:230-270)
+    TIMED(KID_H_PS, 2, (launch_h_ps(g, f, h->st), launch_h_rimcopy(g, f, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, h->st)));
+    TIMED(KID_H_PREP, 1, launch_h_prep(g, f, s, h->st));
+    TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
+  }
+  if (h->head_only) { h->mid_step = true; return RCM_OK; }
+  h->mid_step = false;
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_H_UV, 1, launch_h_uv(g, f, s, h->st));
     TIMED(KID_H_TQ, 1, launch_h_tq(g, f, s, h->st));
@@ -1371,8 +1422,12 @@ static int tend(rcm_dyn* h) {
   CUDA_OK(cudaMemsetAsync(f.cflbits, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.nq_cnt, 0, (size_t)2 * g.kz * sizeof(int), h->st));
-  TIMED(KID_PREP, 1, launch_prep(g, f, s, h->st));
-  TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
+  if (!h->mid_step) {   // head of `tend`: everything physical_parametrizations depends on (Main/mod_tendency.F90:230-270)
+    TIMED(KID_PREP, 1, launch_prep(g, f, s, h->st));
+    TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
+  }
+  if (h->head_only) { h->mid_step = true; return RCM_OK; }
+  h->mid_step = false;
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_UV, 1, h->uv_maps ? launch_uv_tma(g, f, s, h->st, h->uv_maps) : launch_uv(g, f, s, h->st));
     TIMED(KID_TQ, 1, h->tq_tma ? launch_tq_tma(g, f, s, h->st) : launch_tq(g, f, s, h->st));
@@ -1453,30 +1508,84 @@ static int reduce_verdicts(rcm_dyn* h, double* vmax, int nmax, double* vsum, int
   return 0;
 }
 
-extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
-  if (!h) return RCM_ERR_ARG;
-  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_step before rcm_dyn_init");
-  cudaSetDevice(h->device);
+// copy the verdict scalars of the step just enqueued into the next slot of the pinned ring (stream-ordered)
+static int record_verdict(rcm_dyn* h) {
+  if (!h->vring) {
+    CUDA_OK(cudaMallocHost((void**)&h->vring, sizeof(rcm_dyn::VSlot) * rcm_dyn::kVRing));
+    std::memset(h->vring, 0, sizeof(rcm_dyn::VSlot) * rcm_dyn::kVRing);
+    for (int q = 0; q < rcm_dyn::kVRing; ++q) CUDA_OK(cudaEventCreate(&h->vev[q]));
+  }
+  const int q = (int)(h->vhead % rcm_dyn::kVRing);
+  if (h->vhead >= rcm_dyn::kVRing) CUDA_OK(cudaEventSynchronize(h->vev[q]));   // 64 steps old: complete long ago
+  rcm_dyn::VSlot* v = h->vring + q;
+  if (h->moloch) {
+    CUDA_OK(cudaMemcpyAsync(&v->nanf, h->f.nanflag, sizeof(int), cudaMemcpyDeviceToHost, h->st));
+    CUDA_OK(cudaMemcpyAsync(v->ps, h->mf.psbits, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->st));
+  } else {
+    CUDA_OK(cudaMemcpyAsync(v, h->f.cflbits, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->st));
+  }
+  CUDA_OK(cudaEventRecord(h->vev[q], h->st));
+  h->vlcount[q] = h->lcount;
+  h->vhead += 1;
+  return RCM_OK;
+}
+
+// enqueue nsteps x { tend | moloch ; [bdyin] ; bdyval } on the library's stream; no host synchronisation except the
+// daily tmask update (Main/mod_sound.F90:500-547) and what a record change needs
+static int enqueue_steps(rcm_dyn* h, int nsteps) {
   Fields& f = h->f;
-  if (h->moloch) {   // Main/mod_regcm_interface.F90:186-209: moloch; bdyin on the boundary alarm; bdyval
-    CUDA_OK(cudaMemsetAsync(f.nanflag, 0, sizeof(int), h->st));
+  if (!h->pending) {   // head of a batch: call-level maxima and flags start at zero
+    if (h->moloch) {
+      CUDA_OK(cudaMemsetAsync(f.nanflag, 0, sizeof(int), h->st));
+    } else {
+      CUDA_OK(cudaMemsetAsync(f.cflbits, 0, 2 * sizeof(unsigned long long), h->st));
+      CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
+      CUDA_OK(cudaMemsetAsync(f.nanflag, 0, sizeof(int), h->st));
+    }
     CUDA_OK(cudaEventRecord(h->ev0, h->st));
-    int rc = RCM_OK;
-    for (int n = 0; n < nsteps; ++n) {
+    h->pending = true;
+    h->pending_steps = 0;
+  }
+  int rc = RCM_OK;
+  for (int n = 0; n < nsteps; ++n) {
+    if (h->moloch) {   // Main/mod_regcm_interface.F90:186-209: moloch; bdyin on the boundary alarm; bdyval
       if ((rc = mo_step_one(h))) break;
       if (h->bdy_now == h->model_time) {
         if (!h->have_next) { rc = fail(h, RCM_ERR_BDY, "boundary record needed but not staged"); break; }
         if ((rc = mo_bdyin(h))) break;
       }
       if ((rc = mo_bdyval(h))) break;
+    } else {
+      if ((rc = tend(h))) break;
+      if (h->bdy_now == h->model_time) {
+        if (!h->have_next) { rc = fail(h, RCM_ERR_BDY, "boundary record needed but not staged"); break; }
+        if ((rc = bdyin(h))) break;
+      }
+      // after the swap in tend(): n?? hold the previous level-a buffers
+      TIMED(KID_HALO, 0, rc = exch_state(h));
+      if (rc) break;
+      if ((rc = bdyval(h, f.nat, f.naqv, f.naqc))) break;
     }
-    CUDA_OK(cudaEventRecord(h->ev1, h->st));
-    CUDA_OK(cudaStreamSynchronize(h->st));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
-    h->last_ms = ms;
-    prof_collect(h);
-    if (rc) return rc;
+    h->pending_steps += 1;
+    if ((rc = record_verdict(h))) break;
+  }
+  return rc;
+}
+
+// wait for the enqueued steps and reach the verdict of the batch (the same on every rank)
+static int finish_steps(rcm_dyn* h) {
+  if (!h->pending) return RCM_OK;
+  Fields& f = h->f;
+  const int nsteps = h->pending_steps;
+  h->pending = false;
+  CUDA_OK(cudaEventRecord(h->ev1, h->st));
+  CUDA_OK(cudaStreamSynchronize(h->st));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+  h->last_ms = ms;
+  prof_collect(h);
+  h->vdone = h->vhead - 1;
+  if (h->moloch) {
     int nanf = 0;
     unsigned long long pb[2] = {0, 0};
     CUDA_OK(cudaMemcpy(&nanf, f.nanflag, sizeof(nanf), cudaMemcpyDeviceToHost));
@@ -1494,42 +1603,19 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
     if (nanf) return fail(h, RCM_ERR_CFL, "CFL violation: surface pressure is not a number (decrease dt)");   // Main/mod_moloch.F90:443-451
     return RCM_OK;
   }
-  CUDA_OK(cudaMemsetAsync(f.cflbits, 0, 2 * sizeof(unsigned long long), h->st));
-  CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
-  CUDA_OK(cudaMemsetAsync(f.nanflag, 0, sizeof(int), h->st));
-  CUDA_OK(cudaEventRecord(h->ev0, h->st));
-  int rc = RCM_OK;
-  for (int n = 0; n < nsteps; ++n) {
-    if ((rc = tend(h))) break;
-    if (h->bdy_now == h->model_time) {
-      if (!h->have_next) { rc = fail(h, RCM_ERR_BDY, "boundary record needed but not staged"); break; }
-      if ((rc = bdyin(h))) break;
-    }
-    // after the swap in tend(): n?? hold the previous level-a buffers
-    TIMED(KID_HALO, 0, rc = exch_state(h));
-    if (rc) break;
-    if ((rc = bdyval(h, f.nat, f.naqv, f.naqc))) break;
-  }
-  CUDA_OK(cudaEventRecord(h->ev1, h->st));
-  CUDA_OK(cudaStreamSynchronize(h->st));
-  float ms = 0.f;
-  cudaEventElapsedTime(&ms, h->ev0, h->ev1);
-  h->last_ms = ms;
-  prof_collect(h);
-  if (rc) return rc;
   int halo_err = h->halo.take_error();
-  unsigned long long bits2[2] = {0, 0}, nq = 0; int nanf = 0;
-  CUDA_OK(cudaMemcpy(bits2, f.cflbits, sizeof(bits2), cudaMemcpyDeviceToHost));
-  CUDA_OK(cudaMemcpy(&nq, f.negq, sizeof(nq), cudaMemcpyDeviceToHost));
-  CUDA_OK(cudaMemcpy(&nanf, f.nanflag, sizeof(nanf), cudaMemcpyDeviceToHost));
-  double cfl, cfl_last; std::memcpy(&cfl, &bits2[1], sizeof(cfl)); std::memcpy(&cfl_last, &bits2[0], sizeof(cfl_last));
+  unsigned long long blk[4] = {0, 0, 0, 0};
+  CUDA_OK(cudaMemcpy(blk, f.cflbits, sizeof(blk), cudaMemcpyDeviceToHost));
+  unsigned long long nq = blk[2];
+  int nanf = 0; std::memcpy(&nanf, &blk[3], sizeof(nanf));
+  double cfl, cfl_last; std::memcpy(&cfl, &blk[1], sizeof(cfl)); std::memcpy(&cfl_last, &blk[0], sizeof(cfl_last));
   if (h->cfg.nproc > 1 && nsteps > 0) {   // every rank must reach the same verdict (the reference's fatal() aborts all of them)
     double vm[4] = {cfl, cfl_last, (double)nanf, (double)halo_err}, vs[1] = {(double)nq};
     if (reduce_verdicts(h, vm, 4, vs, 1)) return fail(h, RCM_ERR_NCCL, "allreduce (step verdicts) failed");
     cfl = vm[0]; cfl_last = vm[1]; nanf = (vm[2] != 0.0); halo_err = (vm[3] != 0.0); nq = (unsigned long long)vs[0];
   }
   h->max_cfl = cfl_last; h->neg_q = (int64_t)nq; h->nan_flag = nanf;
-  h->cq_mode = nq > 0 ? 2 : 0;   // moisture went negative: the next call stores the forecast in its first pass
+  h->cq_mode = nq > 0 ? 2 : 0;   // moisture went negative: the next batch stores the forecast in its first pass
   CUDA_OK(cudaGetLastError());
   if (halo_err) return fail(h, RCM_ERR_NCCL, "halo exchange: timed out waiting for a neighbour's edge data");
   if (nanf || cfl != cfl) return fail(h, RCM_ERR_NAN, "NaN in the acoustic solver");
@@ -1538,6 +1624,115 @@ extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
     return fail(h, RCM_ERR_CFL, buf);
   }
   return RCM_OK;
+}
+
+extern "C" int rcm_dyn_step(rcm_dyn* h, int nsteps) {
+  if (!h) return RCM_ERR_ARG;
+  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_step before rcm_dyn_init");
+  cudaSetDevice(h->device);
+  const int rc = enqueue_steps(h, nsteps);
+  const std::string msg = h->err;
+  const int rc2 = finish_steps(h);
+  if (rc) { h->err = msg; return rc; }
+  return rc2;
+}
+
+// ---------------------------------------------------------------------------
+// Physics coupling boundary.  The reference calls physical_parametrizations in the middle of
+// `tend` (Main/mod_tendency.F90:271): they read the `atms` slices built by mkslice and return aten(:,:,:,pc_physic),
+// which the tendency sums add (:285-314,331-335,404-411).  Here the step splits at the same place.
+static double** phys_ptr(rcm_dyn* h, int field) {
+  Fields& f = h->f;
+  switch (field) {
+    case RCM_F_U: return &f.phy_u; case RCM_F_V: return &f.phy_v; case RCM_F_T: return &f.phy_t;
+    case RCM_F_QV: return &f.phy_qv; case RCM_F_QC: return &f.phy_qc; case RCM_F_PP: return &f.phy_pp; case RCM_F_W: return &f.phy_w;
+  }
+  return nullptr;
+}
+
+extern "C" int rcm_dyn_set_phys_tend(rcm_dyn* h, int field, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a) return RCM_ERR_ARG;
+  if (h->moloch) return fail(h, RCM_ERR_ARG, "physics tendencies are coupled for idynamic = 1, 2");
+  double** pp = phys_ptr(h, field);
+  if (!pp || (h->hydro && (field == RCM_F_PP || field == RCM_F_W))) return fail(h, RCM_ERR_ARG, "no physics tendency for this field");
+  cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  if (!h->f.phy_t) {   // first use: all of them, zero-filled (u and v are added as a pair)
+    for (int q : {RCM_F_U, RCM_F_V, RCM_F_T, RCM_F_QV, RCM_F_QC, RCM_F_PP, RCM_F_W}) {
+      if (h->hydro && (q == RCM_F_PP || q == RCM_F_W)) continue;
+      double* p = dev_alloc3(h, h->g.kzp1);
+      if (!p) return fail(h, RCM_ERR_CUDA, "device memory allocation failed (physics tendencies)");
+      *phys_ptr(h, q) = p;
+    }
+  }
+  const int nk = (field == RCM_F_W) ? h->g.kzp1 : h->g.kz;
+  return upload3(h, *pp, a, lb, ub, nk);
+}
+
+extern "C" int rcm_dyn_clear_phys_tend(rcm_dyn* h) {
+  if (!h) return RCM_ERR_ARG;
+  cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  for (int q : {RCM_F_U, RCM_F_V, RCM_F_T, RCM_F_QV, RCM_F_QC, RCM_F_PP, RCM_F_W}) {
+    double** pp = phys_ptr(h, q);
+    if (pp && *pp) CUDA_OK(cudaMemset(*pp - h->off3, 0, (size_t)h->g.sk * h->g.kzp1 * sizeof(double)));
+  }
+  return RCM_OK;
+}
+
+extern "C" int rcm_dyn_step_pre_physics(rcm_dyn* h) {
+  if (!h) return RCM_ERR_ARG;
+  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_step_pre_physics before rcm_dyn_init");
+  if (h->moloch) return fail(h, RCM_ERR_ARG, "the pre-/post-physics split is built for idynamic = 1, 2");
+  cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  if (h->mid_step) return RCM_OK;   // already there
+  h->head_only = true;
+  const int rc = tend(h);
+  h->head_only = false;
+  if (rc) return rc;
+  CUDA_OK(cudaStreamSynchronize(h->st));
+  return RCM_OK;
+}
+
+extern "C" int rcm_dyn_step_post_physics(rcm_dyn* h) {
+  if (!h) return RCM_ERR_ARG;
+  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_step_post_physics before rcm_dyn_init");
+  if (!h->mid_step) return fail(h, RCM_ERR_STATE, "rcm_dyn_step_post_physics without rcm_dyn_step_pre_physics");
+  return rcm_dyn_step(h, 1);   // tend() skips the head it has already run
+}
+
+extern "C" int rcm_dyn_get_slice(rcm_dyn* h, int id, double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a) return RCM_ERR_ARG;
+  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_get_slice before rcm_dyn_init");
+  if (h->moloch) return fail(h, RCM_ERR_ARG, "slices are built for idynamic = 1, 2");
+  if (id < 0 || id >= RCM_SL_COUNT) return fail(h, RCM_ERR_ARG, "bad slice id");
+  cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  if (h->hydro && !h->mid_step && (id == RCM_SL_WPX3D || id == RCM_SL_WB3D))
+    return fail(h, RCM_ERR_STATE, "omega of the hydrostatic core exists between rcm_dyn_step_pre_physics and rcm_dyn_step_post_physics");
+  if (!h->slice_buf) { h->slice_buf = dev_alloc3(h, h->g.kzp1); if (!h->slice_buf) return fail(h, RCM_ERR_CUDA, "device memory allocation failed (slice)"); }
+  const rcm_cfg& c = h->cfg;
+  launch_slice(h->g, h->f, id, h->hydro ? 1 : 0, c.ptop, c.base_state_pressure, c.logp_lrate, c.base_state_ts0, h->s.dx8, h->slice_buf, h->st);
+  h->launches += 1;
+  int nk = h->g.kz;
+  if (id == RCM_SL_PF3D || id == RCM_SL_WB3D || id == RCM_SL_ZQ) nk = h->g.kzp1;
+  int32_t l3[3] = {lb[0], lb[1], lb[2]}, u3[3] = {ub[0], ub[1], ub[2]};
+  if (id == RCM_SL_PS2D) { nk = 1; l3[2] = u3[2] = 1; }
+  return download3(h, h->slice_buf, a, l3, u3, nk);
+}
+
+extern "C" int rcm_dyn_step_async(rcm_dyn* h, int nsteps) {
+  if (!h) return RCM_ERR_ARG;
+  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_step_async before rcm_dyn_init");
+  cudaSetDevice(h->device);
+  return enqueue_steps(h, nsteps);
+}
+
+extern "C" int rcm_dyn_sync(rcm_dyn* h) {
+  if (!h) return RCM_ERR_ARG;
+  cudaSetDevice(h->device);
+  return finish_steps(h);
 }
 
 // ---------------------------------------------------------------------------
@@ -1579,6 +1774,7 @@ static int download3(rcm_dyn* h, const double* dev_shifted, double* a, const int
 extern "C" int rcm_dyn_get_state(rcm_dyn* h, int field, int level, double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
   cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
   if (field == RCM_F_PS) {
     if (!h->hydro && !h->moloch) return fail(h, RCM_ERR_ARG, "p* is a state field for idynamic = 1 and 3 only");
     int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
@@ -1592,6 +1788,7 @@ extern "C" int rcm_dyn_get_state(rcm_dyn* h, int field, int level, double* a, co
 extern "C" int rcm_dyn_set_state(rcm_dyn* h, int field, int level, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
   cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
   if (field == RCM_F_PS) {
     if (!h->hydro) return fail(h, RCM_ERR_ARG, "p* is a state field for idynamic = 1 only");
     int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
@@ -1602,9 +1799,76 @@ extern "C" int rcm_dyn_set_state(rcm_dyn* h, int field, int level, const double*
   return upload3(h, p, a, lb, ub, h->g.kzp1);
 }
 
+// Asynchronous export of one prognostic field: a device-side snapshot is taken in stream order (after the steps
+// already enqueued), then copied to the caller's (page-locked) array on a private stream, so that the D2H transfer
+// overlaps the steps enqueued afterwards.  rcm_dyn_get_state_wait returns when every queued export has landed.
+extern "C" int rcm_dyn_get_state_async(rcm_dyn* h, int field, int level, double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a) return RCM_ERR_ARG;
+  cudaSetDevice(h->device);
+#ifdef RCM_EMU
+  return rcm_dyn_get_state(h, field, level, a, lb, ub);
+#else
+  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_get_state_async before rcm_dyn_init");
+  double* p = nullptr;
+  int nk = h->g.kzp1;
+  int32_t l3[3] = {lb[0], lb[1], lb[2]}, u3[3] = {ub[0], ub[1], ub[2]};
+  if (field == RCM_F_PS) {
+    if (!h->hydro && !h->moloch) return fail(h, RCM_ERR_ARG, "p* is a state field for idynamic = 1 and 3 only");
+    p = (h->moloch ? h->mf.ps : ps_state(h, level)) - h->g.sk; nk = 1; l3[2] = u3[2] = 1;
+  } else {
+    p = h->moloch ? mo_state_ptr(h, field) : state_ptr(h, field, level);
+  }
+  if (!p || field < 0 || field >= RCM_F_COUNT) return fail(h, RCM_ERR_ARG, "bad field");
+  const int q = 2 * field + (level == RCM_LEVEL_B ? 1 : 0);
+  const size_t bytes = (size_t)h->g.sk * (size_t)nk * sizeof(double);
+  if (!h->st_out) CUDA_OK(cudaStreamCreateWithFlags(&h->st_out, cudaStreamNonBlocking));
+  if (!h->snap[q]) {   // first export of this field: the only allocation, outside the stepping path
+    CUDA_OK(cudaMalloc((void**)&h->snap[q], (size_t)h->g.sk * (size_t)h->g.kzp1 * sizeof(double)));
+    CUDA_OK(cudaEventCreateWithFlags(&h->ev_snap[q], cudaEventDisableTiming));
+    CUDA_OK(cudaEventCreateWithFlags(&h->ev_out[q], cudaEventDisableTiming));
+  } else {
+    CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_out[q], 0));   // the previous export of this field must have left the snapshot
+  }
+  const Geom& g = h->g;
+  const int jlo = std::max(l3[0], g.jde1 - RCM_HALO), jhi = std::min(u3[0], g.jde2 + RCM_HALO);
+  const int ilo = std::max(l3[1], g.ide1 - RCM_HALO), ihi = std::min(u3[1], g.ide2 + RCM_HALO);
+  const int klo = std::max(l3[2], 1), khi = std::min(u3[2], nk);
+  if (jhi < jlo || ihi < ilo || khi < klo) return RCM_OK;
+  if (jlo == l3[0] && jhi == u3[0] && ilo == l3[1] && ihi == u3[1]) {
+    // the window covers whole (j,i) planes of the caller's array: pack it on the device (this IS the snapshot), then
+    // ONE contiguous D2H copy
+    const int n1 = jhi - jlo + 1, n2 = ihi - ilo + 1, nkk = khi - klo + 1;
+    launch_window(true, h->snap[q], p, jlo, ilo, klo, n1, n2, nkk, g.si, g.sk, h->st);
+    h->launches += 1;
+    CUDA_OK(cudaEventRecord(h->ev_snap[q], h->st));
+    CUDA_OK(cudaStreamWaitEvent(h->st_out, h->ev_snap[q], 0));
+    CUDA_OK(cudaMemcpyAsync(a + (size_t)n1 * n2 * (size_t)(klo - l3[2]), h->snap[q], (size_t)n1 * n2 * nkk * sizeof(double),
+                            cudaMemcpyDeviceToHost, h->st_out));
+  } else {
+    CUDA_OK(cudaMemcpyAsync(h->snap[q], p - h->off3, bytes, cudaMemcpyDeviceToDevice, h->st));
+    CUDA_OK(cudaEventRecord(h->ev_snap[q], h->st));
+    CUDA_OK(cudaStreamWaitEvent(h->st_out, h->ev_snap[q], 0));
+    const int rc = copy3d(h, h->snap[q] + h->off3, a, l3, u3, nk, false, h->st_out, false);
+    if (rc) return rc;
+  }
+  CUDA_OK(cudaEventRecord(h->ev_out[q], h->st_out));
+  h->out_pending = true;
+  return RCM_OK;
+#endif
+}
+
+extern "C" int rcm_dyn_get_state_wait(rcm_dyn* h) {
+  if (!h) return RCM_ERR_ARG;
+#ifndef RCM_EMU
+  if (h->out_pending) { cudaSetDevice(h->device); CUDA_OK(cudaStreamSynchronize(h->st_out)); h->out_pending = false; }
+#endif
+  return RCM_OK;
+}
+
 extern "C" int rcm_dyn_get_work(rcm_dyn* h, int id, double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
   cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
   Fields& f = h->f;
   const double* p = nullptr;
   if (h->moloch) {
@@ -1644,6 +1908,27 @@ extern "C" int rcm_dyn_diag(rcm_dyn* h, rcm_diag* d) {
   d->lcount = h->lcount; d->xbctime = h->xbctime; d->dt = h->dt;
   d->max_cfl = h->max_cfl; d->istep = h->last_istep; d->nan_flag = h->nan_flag;
   d->neg_q_points = h->neg_q;
+  if (h->pending && h->hydro) { cudaSetDevice(h->device); const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  if (h->pending) {
+    // Steps are in flight (rcm_dyn_step_async): report, WITHOUT blocking, the newest step whose verdict copy has
+    // arrived in the pinned ring (this rank's values; rcm_dyn_sync gives the rank-reduced verdict of the batch).
+    for (int64_t q = h->vhead - 1; q > h->vdone && q >= h->vhead - rcm_dyn::kVRing; --q)
+      if (cudaEventQuery(h->vev[q % rcm_dyn::kVRing]) == cudaSuccess) { h->vdone = q; break; }
+    cudaGetLastError();   // cudaErrorNotReady is not an error
+    d->lcount = h->lcount - h->pending_steps;   // nothing of this batch has landed yet: the last finished step
+    if (h->vdone >= 0 && h->vdone >= h->vhead - rcm_dyn::kVRing) {
+      const rcm_dyn::VSlot& v = h->vring[h->vdone % rcm_dyn::kVRing];
+      d->lcount = h->vlcount[h->vdone % rcm_dyn::kVRing];
+      d->nan_flag = (int)(v.nanf & 0xffffffffULL);
+      if (h->moloch) {
+        if (v.ps[0]) { const unsigned long long mn = ~v.ps[1]; std::memcpy(&d->ps_max, &v.ps[0], 8); std::memcpy(&d->ps_min, &mn, 8); }
+        return RCM_OK;
+      }
+      std::memcpy(&d->max_cfl, &v.cfl[0], 8);
+      d->neg_q_points = (int64_t)v.negq;
+    }
+    return RCM_OK;
+  }
   if (h->hydro && h->inited) {
     // Bleck (1977) noise parameters: per-point terms summed on the host in the
     // reference's loop order (i outer, j inner; Main/mod_tendency.F90:1452-1458)
@@ -1699,6 +1984,7 @@ extern "C" int rcm_dyn_get_tile(rcm_dyn* h, int32_t out[4]) {
 
 extern "C" int rcm_dyn_profile(rcm_dyn* h, int enable) {
   if (!h) return RCM_ERR_ARG;
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
   h->prof_on = enable != 0;
   for (int q = 0; q < KID_COUNT; ++q) { h->prof_ms[q] = 0; h->prof_n[q] = 0; }
   return RCM_OK;
@@ -1726,7 +2012,16 @@ extern "C" int rcm_dyn_comm_unique_id(void* out, int out_bytes) { return Halo::u
 extern "C" int rcm_dyn_destroy(rcm_dyn* h) {
   if (!h) return RCM_OK;
   cudaSetDevice(h->device);
+  h->pending = false;
   cudaDeviceSynchronize();
+  if (h->vring) { cudaFreeHost(h->vring); for (cudaEvent_t e : h->vev) if (e) cudaEventDestroy(e); }
+  for (int q = 0; q < 2 * RCM_F_COUNT; ++q) {
+    if (h->snap[q]) cudaFree(h->snap[q]);
+    if (h->ev_snap[q]) cudaEventDestroy(h->ev_snap[q]);
+    if (h->ev_out[q]) cudaEventDestroy(h->ev_out[q]);
+  }
+  if (h->st_out) cudaStreamDestroy(h->st_out);
+  if (h->stage_dev) cudaFree(h->stage_dev);
   h->halo.destroy();
   for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
   for (void* p : h->allocs) cudaFree(p);

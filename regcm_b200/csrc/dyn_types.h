@@ -109,6 +109,9 @@ struct Fields {
   double *deld, *delh, *ddsum, *dhsum, *dstor, *hstor, *map;
   // vertical-mode tables: [l + nsplit*(k-1)] for zr (zmatxr), tau, pdlog, eps1 (k = 1..kz+1), am, zm (zmatx)
   double *sp_zr, *sp_tau, *sp_pdlog, *sp_eps1, *sp_am, *sp_zm;
+  // aten(:,:,:,pc_physic): tendencies handed in by the physical parametrizations (rcm_dyn_set_phys_tend), coupled
+  // with p* like the reference's; null until first set (physics off), added at Main/mod_tendency.F90:285-314,331-335,404-411
+  double *phy_u, *phy_v, *phy_t, *phy_qv, *phy_qc, *phy_pp, *phy_w;
   // diagnostics
   unsigned long long *cflbits;  // max CFL as ordered bits
   unsigned long long *negq;     // negative-q repairs

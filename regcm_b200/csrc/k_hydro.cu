@@ -311,6 +311,7 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
     }
     // ---- forecast p*u, p*v and Robert-Asselin filter (:433-445) ----
     const double bu_c = L3(f.bu, j, i, k), bv_c = L3(f.bv, j, i, k);
+    if (f.phy_u) { ut = ut + L3(f.phy_u, j, i, k); vt = vt + L3(f.phy_v, j, i, k); }   // Main/mod_tendency.F90:404-411
     const double cu = bu_c + s.dt * ut, cv = bv_c + s.dt * vt;
     double d = s.gnu1 * (cu + bu_c - 2.0 * uc);
     P3(f.nbu, j, i, k) = uc + d;
@@ -429,6 +430,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         }
         for (int r = 0; r < nring; ++r) ten = ten + xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * (d_c));
       }
+      if (f.phy_t) ten = ten + L3(f.phy_t, j, i, k);   // Main/mod_tendency.F90:285-287
       const double ct = bt_c + dt * ten;
       const double d = s.gnu1 * (ct + bt_c - 2.0 * at);
       if (out) P3(f.nbt, j, i, k) = at + d;
@@ -473,6 +475,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         }
         for (int r = 0; r < nring; ++r) ten = ten + 1.0 * xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * d_c);
       }
+      if (f.phy_qv) ten = ten + L3(f.phy_qv, j, i, k);   // :292-294
       double cq = b_c + dt * ten;
       // Main/mod_tendency.F90:381-393: a negative forecast is replaced by 1 % of the 3x3 mean of |q|; the value
       // filtered here for such a point is provisional and is redone by k_negq_repair (k_negq.cu)
@@ -518,6 +521,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         }
         for (int r = 0; r < nring; ++r) ten = ten + 1.0 * xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * d_c);
       }
+      if (f.phy_qc) ten = ten + L3(f.phy_qc, j, i, k);
       if (s.ipptls <= 0) ten = 0.0;  // Main/mod_tendency.F90:331-335
       double cq = b_c + dt * ten;
       negq_note<CQ_MODE>(g, f, cq, j, i, k, 1, cq_edge);

@@ -80,3 +80,7 @@ static inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return 0;
 static inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned) { return 0; }
 static inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0.f; return 0; }
 static inline cudaError_t cudaEventDestroy(cudaEvent_t) { return 0; }
+static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return 0; }
+static inline cudaError_t cudaEventQuery(cudaEvent_t) { return 0; }
+static inline cudaError_t cudaMallocHost(void** p, size_t n) { *p = std::malloc(n); return *p ? 0 : 2; }
+static inline cudaError_t cudaFreeHost(void* p) { std::free(p); return 0; }
