@@ -182,8 +182,9 @@ typedef struct rcm_cfg {
   /* &coreparam */
   int32_t idynamic; /* 1 hydrostatic, 2 non-hydrostatic, 3 MOLOCH          */
   /* &physicsparam (dynamics-relevant switches only) */
-  int32_t iboudy;   /* 0 fixed, 1 linear relax., 5 exponential relax.;
-                     * 4 sponge (idynamic = 3 only)                         */
+  int32_t iboudy;   /* 0 fixed, 1 linear relax., 5 exponential relax., 4 sponge + inflow/outflow;
+                     * idynamic 1, 2 also: 2 time-dependent without relaxation, 3 = 2 + inflow/outflow
+                     * (Main/mod_tendency.F90:909-983,1462-1500; Main/mod_bdycod.F90:237-250,1809-1947,2591-3122) */
   int32_t idiffu;   /* 1 = 4th-order (only value implemented)              */
   int32_t ipptls;   /* >0: hydrometeors advected, water loading in w       */
   /* &nonhydroparam */

@@ -316,6 +316,34 @@ void Oracle::bdyval() {
     if (iboudy != 0)
       for (int j = jce1; j <= jce2; ++j) a1_w(j, ib_, 1) = a1_w(j, iin, 1);
   }
+  // iboudy 3, 4: water vapour on the boundary cells by inflow / outflow (Main/mod_bdycod.F90:1879-1947):
+  // inflow keeps the boundary value, outflow takes the interior neighbour; both pass through (q/p*)*p*
+  if (iboudy == 3 || iboudy == 4) {
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ici1; i <= ici2; ++i) {
+        double qext = a1_qx(jce1, i, k, iqv) / psa(jce1, i), qint = a1_qx(jci1, i, k, iqv) / psa(jci1, i);
+        double windavg = wue(i, k) + wue(i + 1, k) + wui(i, k) + wui(i + 1, k);
+        a1_qx(jce1, i, k, iqv) = (windavg > d_zero ? qext : qint) * psa(jce1, i);
+      }
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ici1; i <= ici2; ++i) {
+        double qext = a1_qx(jce2, i, k, iqv) / psa(jce2, i), qint = a1_qx(jci2, i, k, iqv) / psa(jci2, i);
+        double windavg = eue(i, k) + eue(i + 1, k) + eui(i, k) + eui(i + 1, k);
+        a1_qx(jce2, i, k, iqv) = (windavg < d_zero ? qext : qint) * psa(jce2, i);
+      }
+    for (int k = 1; k <= kz; ++k)
+      for (int j = jce1; j <= jce2; ++j) {
+        double qext = a1_qx(j, ice1, k, iqv) / psa(j, ice1), qint = a1_qx(j, ici1, k, iqv) / psa(j, ici1);
+        double windavg = sve(j, k) + sve(j + 1, k) + svi(j, k) + svi(j + 1, k);
+        a1_qx(j, ice1, k, iqv) = (windavg > d_zero ? qext : qint) * psa(j, ice1);
+      }
+    for (int k = 1; k <= kz; ++k)
+      for (int j = jce1; j <= jce2; ++j) {
+        double qext = a1_qx(j, ice2, k, iqv) / psa(j, ice2), qint = a1_qx(j, ici2, k, iqv) / psa(j, ici2);
+        double windavg = nve(j, k) + nve(j + 1, k) + nvi(j, k) + nvi(j + 1, k);
+        a1_qx(j, ice2, k, iqv) = (windavg < d_zero ? qext : qint) * psa(j, ice2);
+      }
+  }
   // hydrometeors: no boundary data (.not. present_qc), bdyflow = .true.
   // inflow -> 0, outflow -> interior value (:2153-2221)
   for (int n = iqfrst; n <= iqlst; ++n) {
@@ -349,6 +377,47 @@ void Oracle::bdyval() {
       }
   }
   xbctime = xbctime + dtsec;
+}
+
+// ---- sponge, iboudy = 4, sigma-coordinate cores: sponge3d (Main/mod_bdycod.F90:2919-2994), sponge4d (:2591-2663),
+//      spongeuv (:2735-2813), sponge2d (:3065-3122).  ften = wgt(ib)*ften + (1-wgt(ib))*bt in the four zones
+//      (the zones are disjoint: every point is visited at most once). ----
+void Oracle::sponge3d(const V3dBound& bnd, A3& ften) {
+  const int nk = ften.n3;
+  for (int k = 1; k <= nk; ++k)
+    for (int i = ici1; i <= ici2; ++i)
+      for (int j = jci1; j <= jci2; ++j) {
+        if (!(ba_cr.bsouth(j, i) || ba_cr.bnorth(j, i) || ba_cr.bwest(j, i) || ba_cr.beast(j, i))) continue;
+        const int ib = ba_cr.ibnd(j, i);
+        ften(j, i, k) = wgtx(ib) * ften(j, i, k) + (d_one - wgtx(ib)) * bnd.bt(j, i, k);
+      }
+}
+void Oracle::sponge4d(const V3dBound& bnd, A4& ften, int m) {
+  for (int k = 1; k <= kz; ++k)
+    for (int i = ici1; i <= ici2; ++i)
+      for (int j = jci1; j <= jci2; ++j) {
+        if (!(ba_cr.bsouth(j, i) || ba_cr.bnorth(j, i) || ba_cr.bwest(j, i) || ba_cr.beast(j, i))) continue;
+        const int ib = ba_cr.ibnd(j, i);
+        ften(j, i, k, m) = wgtx(ib) * ften(j, i, k, m) + (d_one - wgtx(ib)) * bnd.bt(j, i, k);
+      }
+}
+void Oracle::spongeuv(const V3dBound& bu, const V3dBound& bv, A3& ftu, A3& ftv) {
+  for (int k = 1; k <= kz; ++k)
+    for (int i = idi1; i <= idi2; ++i)
+      for (int j = jdi1; j <= jdi2; ++j) {
+        if (!(ba_dt.bsouth(j, i) || ba_dt.bnorth(j, i) || ba_dt.bwest(j, i) || ba_dt.beast(j, i))) continue;
+        const int ib = ba_dt.ibnd(j, i);
+        ftu(j, i, k) = wgtd(ib) * ftu(j, i, k) + (d_one - wgtd(ib)) * bu.bt(j, i, k);
+        ftv(j, i, k) = wgtd(ib) * ftv(j, i, k) + (d_one - wgtd(ib)) * bv.bt(j, i, k);
+      }
+}
+void Oracle::sponge2d(const V2dBound& bnd, A2& ften) {
+  for (int i = ici1; i <= ici2; ++i)
+    for (int j = jci1; j <= jci2; ++j) {
+      if (!(ba_cr.bsouth(j, i) || ba_cr.bnorth(j, i) || ba_cr.bwest(j, i) || ba_cr.beast(j, i))) continue;
+      const int ib = ba_cr.ibnd(j, i);
+      ften(j, i) = wgtx(ib) * ften(j, i) + (d_one - wgtx(ib)) * bnd.bt(j, i);
+    }
 }
 
 }  // namespace orc

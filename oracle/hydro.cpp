@@ -238,7 +238,8 @@ void Oracle::nudge2d(int ibdy, const A2& f, const V2dBound& bnd, A2& ften) {
 
 // Main/mod_tendency.F90:1428-1460
 void Oracle::new_pressure() {
-  if (cfg.iboudy == 1 || cfg.iboudy == 5) nudge2d(cfg.iboudy, psb, xpsb, pten);
+  if (cfg.iboudy == 4) sponge2d(xpsb, pten);   // Main/mod_tendency.F90:1434
+  else if (cfg.iboudy == 1 || cfg.iboudy == 5) nudge2d(cfg.iboudy, psb, xpsb, pten);
   for (int i = ice1; i <= ice2; ++i)
     for (int j = jce1; j <= jce2; ++j) {
       psc(j, i) = psb(j, i) + pten(j, i) * dt;
@@ -451,6 +452,10 @@ void Oracle::tend_hydro() {
     nudge3d(cfg.iboudy, a2_t, xtb, tdyn);
     nudge4d3d(cfg.iboudy, a2_qx, xqb, qxdyn, iqv);
     nudgeuv(cfg.iboudy, a2_u, a2_v, xub, xvb, udyn, vdyn);
+  } else if (cfg.iboudy == 4) {   // Main/mod_tendency.F90:1480-1483
+    sponge3d(xtb, tten);
+    sponge4d(xqb, qxten, iqv);
+    spongeuv(xub, xvb, uten, vten);
   }
   // diffusion (:1515-1530)
   diffu_d(udyn, vdyn, ubd3d, vbd3d);

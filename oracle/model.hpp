@@ -316,6 +316,10 @@ struct Oracle {
   void nudge4d3d(int ibdy, const A4& f, const V3dBound& bnd, A4& ften, int n);
   void nudgeuv(int ibdy, const A3& fu, const A3& fv, const V3dBound& bu,
                const V3dBound& bv, A3& ftu, A3& ftv);
+  void sponge3d(const V3dBound& bnd, A3& ften);
+  void sponge4d(const V3dBound& bnd, A4& ften, int m);
+  void spongeuv(const V3dBound& bu, const V3dBound& bv, A3& ftu, A3& ftv);
+  void sponge2d(const V2dBound& bnd, A2& ften);
   void raydamp3(const A3& z, const A3& var, A3& vten, const V3dBound& bnd);
   void raydamp3f(const A3& z, const A3& var, A3& vten, double sval);
   void raydampuv(const A3& z, const A3& u, const A3& v, A3& ut, A3& vt,

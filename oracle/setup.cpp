@@ -28,7 +28,8 @@ int Oracle::create(const rcm_cfg& c) {
   if (hydro && (c.nsplit < 1 || c.nsplit > c.kz)) { err = "oracle: nsplit out of range"; return RCM_ERR_ARG; }
   nsplit = hydro ? c.nsplit : 0;
   if (c.idiffu != 1) { err = "oracle: only idiffu=1"; return RCM_ERR_ARG; }
-  if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 5 || (c.idynamic == 3 && c.iboudy == 4))) { err = "oracle: iboudy must be 0,1,5 (4: MOLOCH only)"; return RCM_ERR_ARG; }
+  // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)
+  if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 4 || c.iboudy == 5 || (c.idynamic != 3 && (c.iboudy == 2 || c.iboudy == 3)))) { err = "oracle: iboudy must be 0..5 (2, 3: idynamic 1, 2 only)"; return RCM_ERR_ARG; }
   if (c.nqx != 2) { err = "oracle: nqx must be 2"; return RCM_ERR_ARG; }
   jx = c.jx; iy = c.iy; kz = c.kz; kzp1 = kz + 1; nqx = c.nqx;
   iqv = 1; iqc = 2; iqfrst = 2; iqlst = nqx;
@@ -214,6 +215,7 @@ void Oracle::allocate_all() {
   for (A2* a : {&sue, &sui, &nue, &nui, &sve, &svi, &nve, &nvi}) a->alloc(jde1, jde2, 1, kz);
   fcx.alloc(2, nspgx - 1); gcx.alloc(2, nspgx - 1);
   fcd.alloc(2, nspgd - 1); gcd.alloc(2, nspgd - 1);
+  wgtx.alloc(2, nspgx - 1); wgtd.alloc(2, nspgd - 1);   // sponge weights (iboudy = 4, Main/mod_bdycod.F90:237-250)
   hefc.alloc(2, nspgx - 1, 1, kz); hegc.alloc(2, nspgx - 1, 1, kz);
   hefd.alloc(2, nspgd - 1, 1, kz); hegd.alloc(2, nspgd - 1, 1, kz);
   fg1.alloc(jde1, jde2, ide1, ide2, 1, kzp1);

@@ -340,6 +340,12 @@ void Oracle::boundary() {
     nudgeuv(ib, a2_u, a2_v, xub, xvb, udyn, vdyn);
     nudge3d(ib, a2_pp, xppb, ppdyn);
     nudge3d(ib, a2_w, xwwb, wdyn);
+  } else if (ib == 4) {   // sponge on the TOTAL tendencies (Main/mod_tendency.F90:1480-1483,1497-1499)
+    sponge3d(xtb, tten);
+    sponge4d(xqb, qxten, iqv);
+    spongeuv(xub, xvb, uten, vten);
+    sponge3d(xppb, ppten);
+    sponge3d(xwwb, wten);
   }
 }
 

@@ -163,6 +163,23 @@ __device__ __forceinline__ void negq_note(const Geom& g, const Fields& f, const 
     }
   }
 }
+// Decoupled wind component `a` (au or av) at dot (j,i,k) as `decouple` leaves it for iboudy = 3, 4
+// (Main/mod_tendency.F90:887-994): on outflow the outermost dot row takes the value of the row next to it — west/east
+// on rows idi1..idi2 first, then south/north over the whole row, which may pick up a west/east-modified corner value.
+// Identity (a * rpsda) everywhere else.  Global index tests, so it is valid on any tile.
+__device__ __forceinline__ double dwind_io(const Geom& g, const Fields& f, const double* a, const int j, const int i, const int k) {
+  const int si = g.si;
+  const long long sk = g.sk;
+  int ii = i, jj = j;
+  if (i == 1 && L3(f.av, j, 1, k) >= 0.0) ii = 2;
+  else if (i == g.iy && L3(f.av, j, g.iy, k) <= 0.0) ii = g.iy - 1;
+  if (ii >= 2 && ii <= g.iy - 1) {
+    if (j == 1 && L3(f.au, 1, ii, k) <= 0.0) jj = 2;
+    else if (j == g.jx && L3(f.au, g.jx, ii, k) >= 0.0) jj = g.jx - 1;
+  }
+  return L3(a, jj, ii, k) * L2(f.rpsda, jj, ii);
+}
+
 __device__ __forceinline__ bool tile_edge(const Geom& g, const int j, const int i) {
   return (g.gl && j == g.jci1) || (g.gr && j == g.jci2) || (g.gb && i == g.ici1) || (g.gt && i == g.ici2);
 }

@@ -310,8 +310,9 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   if (h->hydro && c.nproc != 1) return bail(RCM_ERR_ARG, "idynamic=1 runs on one rank only (BASELINE configs[0] is a single-rank case)");
   if (h->hydro && (c.nsplit < 1 || c.nsplit > RCM_MAXSPLIT || c.nsplit > c.kz)) return bail(RCM_ERR_ARG, "nsplit must be 1..4");
   if (c.idiffu != 1) return bail(RCM_ERR_ARG, "only idiffu=1 is implemented");
-  if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 5 || (c.idynamic == 3 && c.iboudy == 4)))
-    return bail(RCM_ERR_ARG, "iboudy must be 0, 1 or 5 (4 = sponge: MOLOCH core only)");
+  // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)
+  if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 4 || c.iboudy == 5 || (c.idynamic != 3 && (c.iboudy == 2 || c.iboudy == 3))))
+    return bail(RCM_ERR_ARG, "iboudy must be 0, 1, 4 or 5 (idynamic 1, 2: also 2, 3)");
   if (c.nqx != 2) return bail(RCM_ERR_ARG, "nqx must be 2 (qv,qc)");
   if (c.jx < 2 * c.nspgx || c.iy < 2 * c.nspgx || c.kz < 3) return bail(RCM_ERR_ARG, "domain too small for the relaxation zone");
   int ndev = 0;
@@ -942,7 +943,7 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
       fnudge = (c.bdy_nm > 0.0) ? c.bdy_nm : 0.1 / h->dt;
       gnudge = (c.bdy_dm > 0.0) ? c.bdy_dm : 1.0 / (h->dt * 50.0);
     }
-    auto table = [&](int nsp, std::vector<double>& F, std::vector<double>& G) {
+    auto table = [&](int nsp, bool dot, std::vector<double>& F, std::vector<double>& G) {
       F.assign((size_t)nsp * kz + 1, 0.0); G.assign((size_t)nsp * kz + 1, 0.0);
       for (int k = 1; k <= kz; ++k) {
         double an = (hsigma[k] < 0.4) ? c.high_nudge : ((hsigma[k] < 0.8) ? c.medium_nudge : c.low_nudge);
@@ -952,14 +953,20 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
           else xfun = (double)(nsp - n) / (double)(nsp - 2);
           F[n + (size_t)nsp * (k - 1)] = fnudge * xfun;
           G[n + (size_t)nsp * (k - 1)] = gnudge * xfun;
+          if (c.iboudy == 4) {   // sponge weights (Main/mod_bdycod.F90:237-250): F = 1 - wgt(n), G = wgt(n)
+            static const double wx[3] = {0.4, 0.7, 0.9}, wd[4] = {0.20, 0.55, 0.80, 0.95};
+            const double w = dot ? (n - 2 < 4 ? wd[n - 2] : 1.0) : (n - 2 < 3 ? wx[n - 2] : 1.0);
+            F[n + (size_t)nsp * (k - 1)] = 1.0 - w;
+            G[n + (size_t)nsp * (k - 1)] = w;
+          }
         }
       }
     };
     std::vector<double> F, G;
-    table(c.nspgx, F, G);
+    table(c.nspgx, false, F, G);
     if ((rc = up1(h, f.hefc, F))) return rc;
     if ((rc = up1(h, f.hegc, G))) return rc;
-    table(c.nspgd, F, G);
+    table(c.nspgd, true, F, G);
     if ((rc = up1(h, f.hefd, F))) return rc;
     if ((rc = up1(h, f.hegd, G))) return rc;
   }

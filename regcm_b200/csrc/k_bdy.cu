@@ -101,6 +101,35 @@ __global__ void k_bdyval_crs(const Geom g, const Fields f, const double* oat, co
   P3(f.aw, j, i, k) = w;
 #undef BC
   if (!half) return;
+  // iboudy 3, 4: water vapour on the rim by inflow/outflow (Main/mod_bdycod.F90:1879-1947): inflow keeps the boundary
+  // value, outflow takes the interior neighbour, both through (q/p*)*p*.  West/east rows ici1..ici2 first, then the
+  // whole south/north rows, whose corner cells read the west/east result of the cell next to them.
+  if (iboudy == 3 || iboudy == 4) {
+    auto bcq = [&](int jj, int ii) { return P3(f.xqb0, jj, ii, k) + xt * P3(f.xqbt, jj, ii, k); };
+    // result of the west/east rule at rim cell (jr, ii), ii in ici1..ici2
+    auto qv_we = [&](int jr, int ii) {
+      const bool west = (jr == gjce1);
+      const int jin = west ? gjci1 : gjci2, jde = west ? 1 : g.jx, jdi = west ? 2 : g.jx - 1;
+      const double qext = bcq(jr, ii) / P2(f.psa, jr, ii), qint = P3(f.aqv, jin, ii, k) / P2(f.psa, jin, ii);
+      const double windavg = P3(f.au, jde, ii, k) + P3(f.au, jde, ii + 1, k) + P3(f.au, jdi, ii, k) + P3(f.au, jdi, ii + 1, k);
+      const bool keep = west ? (windavg > 0.0) : (windavg < 0.0);
+      return (keep ? qext : qint) * P2(f.psa, jr, ii);
+    };
+    double qn;
+    if (i == gice1 || i == gice2) {
+      const bool south = (i == gice1);
+      const int iin = south ? gici1 : gici2, ide = south ? 1 : g.iy, idi = south ? 2 : g.iy - 1;
+      const double qext = bcq(j, i) / P2(f.psa, j, i);
+      const double qin_v = (j == gjce1 || j == gjce2) ? qv_we(j, iin) : P3(f.aqv, j, iin, k);
+      const double qint = qin_v / P2(f.psa, j, iin);
+      const double windavg = P3(f.av, j, ide, k) + P3(f.av, j + 1, ide, k) + P3(f.av, j, idi, k) + P3(f.av, j + 1, idi, k);
+      const bool keep = south ? (windavg > 0.0) : (windavg < 0.0);
+      qn = (keep ? qext : qint) * P2(f.psa, j, i);
+    } else {
+      qn = qv_we(j, i);
+    }
+    P3(f.aqv, j, i, k) = qn;
+  }
   // hydrometeors without boundary data: zero on inflow, interior value on
   // outflow (Main/mod_bdycod.F90:2153-2221); strips as left by bdyuv.
   const bool tdep = (iboudy != 0);

@@ -162,6 +162,10 @@ k_h_prep(const Geom g, const Fields f, const StepScalars s) {
       ptn = ptn + xf * fls0 - xg * (fls1 + fls2 + fls3 + fls4 - 4.0 * fls0);
     }
   }
+  if (interior && s.iboudy == 4) {   // sponge2d (Main/mod_tendency.F90:1434, mod_bdycod.F90:3065-3122)
+    const int ib = L2(f.zone_c, j, i);
+    if (ib > 0) ptn = LD1(&f.hegc[ib]) * ptn + LD1(&f.hefc[ib]) * L2(f.xpsbt, j, i);
+  }
   const double psc = psb + ptn * s.dt;
   P2(f.psc, j, i) = psc;
   if (interior) {
@@ -192,6 +196,7 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
   const double dmsf = L2(f.dmsf, j, i), coriol = L2(f.coriol, j, i);
   const double psdota = L2(f.psdota, j, i), psdotb = L2(f.psdotb, j, i);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_d, j, i) : 0;
+  const int ibs = (s.iboudy == 4) ? L2(f.zone_d, j, i) : 0;   // sponge zone (iboudy = 4)
   const bool dint = diff_interior(g, j, i, true);
   const int nring = ring_count(g, j, i, true);
   // cross points around the dot: 11=(j,i) 10=(j,i-1) 01=(j-1,i) 00=(j-1,i-1)
@@ -219,10 +224,15 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
     double vcmonc = VA(2, 0) + 2.0 * VA(1, 0) + VA(0, 0);
 #undef UA
 #undef VA
-    const double u_c = au[1][1] * rp_c, u_jp = au[2][1] * rp_jp, u_jm = au[0][1] * rp_jm, u_ip = au[1][2] * rp_ip,
-                 u_im = au[1][0] * rp_im;
-    const double v_c = av[1][1] * rp_c, v_jp = av[2][1] * rp_jp, v_jm = av[0][1] * rp_jm, v_ip = av[1][2] * rp_ip,
-                 v_im = av[1][0] * rp_im;
+    const double u_c = au[1][1] * rp_c, v_c = av[1][1] * rp_c;
+    double u_jp = au[2][1] * rp_jp, u_jm = au[0][1] * rp_jm, u_ip = au[1][2] * rp_ip, u_im = au[1][0] * rp_im;
+    double v_jp = av[2][1] * rp_jp, v_jm = av[0][1] * rp_jm, v_ip = av[1][2] * rp_ip, v_im = av[1][0] * rp_im;
+    if (s.iboudy == 3 || s.iboudy == 4) {   // inflow/outflow rule of `decouple` (Main/mod_tendency.F90:909-983), see k_uv_level.inc
+      if (j == 2 && au[0][1] <= 0.0) { u_jm = u_c; v_jm = v_c; }
+      if (j == g.jx - 1 && au[2][1] >= 0.0) { u_jp = u_c; v_jp = v_c; }
+      if (i == 2 && av[1][0] >= 0.0) { u_im = u_c; v_im = v_c; }
+      if (i == g.iy - 1 && av[1][2] <= 0.0) { u_ip = u_c; v_ip = v_c; }
+    }
     if (up) {
       const double ff1 = ul * (u_jp + u_c);
       const double ff2 = ul * (u_jm + u_c);
@@ -311,6 +321,10 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
     }
     // ---- forecast p*u, p*v and Robert-Asselin filter (:433-445) ----
     const double bu_c = L3(f.bu, j, i, k), bv_c = L3(f.bv, j, i, k);
+    if (ibs > 0) {   // sponge (iboudy = 4): (1 - wgtd(ib)) * bt added to the still-zero total tendency (spongeuv)
+      const double xs = LD1(&f.hefd[ibs]);
+      ut = ut + xs * L3(f.xubt, j, i, k); vt = vt + xs * L3(f.xvbt, j, i, k);
+    }
     if (f.phy_u) { ut = ut + L3(f.phy_u, j, i, k); vt = vt + L3(f.phy_v, j, i, k); }   // Main/mod_tendency.F90:404-411
     const double cu = bu_c + s.dt * ut, cv = bv_c + s.dt * vt;
     double d = s.gnu1 * (cu + bu_c - 2.0 * uc);
@@ -347,6 +361,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
   const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i), m11 = L2(f.msfd, j + 1, i + 1);
   const double r00 = L2(f.rpsda, j, i), r01 = L2(f.rpsda, j, i + 1), r10 = L2(f.rpsda, j + 1, i), r11 = L2(f.rpsda, j + 1, i + 1);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_c, j, i) : 0;
+  const int ibs = (s.iboudy == 4) ? L2(f.zone_c, j, i) : 0;   // sponge zone (iboudy = 4)
   const bool dint = diff_interior(g, j, i, false);
   const int nring = ring_count(g, j, i, false);
   const double beta = 0.53;
@@ -430,6 +445,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         }
         for (int r = 0; r < nring; ++r) ten = ten + xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * (d_c));
       }
+      if (ibs > 0) ten = ten + LD1(&f.hefc[ibs]) * L3(f.xtbt, j, i, k);   // sponge3d on tten (iboudy = 4)
       if (f.phy_t) ten = ten + L3(f.phy_t, j, i, k);   // Main/mod_tendency.F90:285-287
       const double ct = bt_c + dt * ten;
       const double d = s.gnu1 * (ct + bt_c - 2.0 * at);
@@ -475,6 +491,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         }
         for (int r = 0; r < nring; ++r) ten = ten + 1.0 * xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * d_c);
       }
+      if (ibs > 0) ten = ten + LD1(&f.hefc[ibs]) * L3(f.xqbt, j, i, k);   // sponge4d on qxten(iqv)
       if (f.phy_qv) ten = ten + L3(f.phy_qv, j, i, k);   // :292-294
       double cq = b_c + dt * ten;
       // Main/mod_tendency.F90:381-393: a negative forecast is replaced by 1 % of the 3x3 mean of |q|; the value

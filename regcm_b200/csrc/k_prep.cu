@@ -44,9 +44,17 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
          u11 = L3(f.au, j + 1, i + 1, 1);
   double v00 = L3(f.av, j, i, 1), v01 = L3(f.av, j, i + 1, 1), v10 = L3(f.av, j + 1, i, 1),
          v11 = L3(f.av, j + 1, i + 1, 1);
-  // ucc = sum of umd = (u*rpsda)*msfd over the 4 dots, reference order
-  double ucc_k = (u00 * r00) * m00 + (u01 * r01) * m01 + (u10 * r10) * m10 + (u11 * r11) * m11;
-  double vcc_k = (v00 * r00) * m00 + (v01 * r01) * m01 + (v10 * r10) * m10 + (v11 * r11) * m11;
+  // iboudy 3, 4: cells that touch the outermost dot ring see the inflow/outflow-adjusted decoupled winds (dwind_io)
+  const bool io_ring = (s.iboudy == 3 || s.iboudy == 4) && (j == 1 || j + 1 == g.jx || i == 1 || i + 1 == g.iy);
+  auto ucc_of = [&](const double* a, int kk, double a00, double a01, double a10, double a11) {
+    // sum of umd = (u*rpsda)*msfd over the 4 dots, reference order
+    if (io_ring)
+      return dwind_io(g, f, a, j, i, kk) * m00 + dwind_io(g, f, a, j, i + 1, kk) * m01 + dwind_io(g, f, a, j + 1, i, kk) * m10 +
+             dwind_io(g, f, a, j + 1, i + 1, kk) * m11;
+    return (a00 * r00) * m00 + (a01 * r01) * m01 + (a10 * r10) * m10 + (a11 * r11) * m11;
+  };
+  double ucc_k = ucc_of(f.au, 1, u00, u01, u10, u11);
+  double vcc_k = ucc_of(f.av, 1, v00, v01, v10, v11);
   double qd_k = 0.0;
   P3(f.qdot, j, i, 1) = 0.0;
 
@@ -75,8 +83,8 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
       const int kn = k + 1;
       n00 = L3(f.au, j, i, kn); n01 = L3(f.au, j, i + 1, kn); n10 = L3(f.au, j + 1, i, kn); n11 = L3(f.au, j + 1, i + 1, kn);
       w00 = L3(f.av, j, i, kn); w01 = L3(f.av, j, i + 1, kn); w10 = L3(f.av, j + 1, i, kn); w11 = L3(f.av, j + 1, i + 1, kn);
-      ucc_n = (n00 * r00) * m00 + (n01 * r01) * m01 + (n10 * r10) * m10 + (n11 * r11) * m11;
-      vcc_n = (w00 * r00) * m00 + (w01 * r01) * m01 + (w10 * r10) * m10 + (w11 * r11) * m11;
+      ucc_n = ucc_of(f.au, kn, n00, n01, n10, n11);
+      vcc_n = ucc_of(f.av, kn, w00, w01, w10, w11);
       const double w = L3(f.aw, j, i, kn) * rpsa;
       const double t1 = LD1(&f.twt1[kn]), t2 = LD1(&f.twt2[kn]);
       qd_n = -L3(f.rhof0, j, i, kn) * egrav * w / ps0 -

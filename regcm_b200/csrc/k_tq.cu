@@ -42,6 +42,7 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
   const double xmsf = L2(f.xmsf, j, i);
   const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i), m11 = L2(f.msfd, j + 1, i + 1);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_c, j, i) : 0;
+  const int ibs = (s.iboudy == 4) ? L2(f.zone_c, j, i) : 0;   // sponge zone (iboudy = 4)
   const bool dint = diff_interior(g, j, i, false);
   const int nring = ring_count(g, j, i, false);
   const double qthr = minqq * psa;           // vadvqv threshold

@@ -82,6 +82,7 @@ k_uv_tma(const Geom g, const Fields f, const StepScalars s) {
   const double ddx = L2(f.ddx, j, i), ddy = L2(f.ddy, j, i), dmdx = L2(f.dmdx, j, i), dmdy = L2(f.dmdy, j, i);
   const double psdotb = L2(f.psdotb, j, i);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_d, j, i) : 0;
+  const int ibs = (s.iboudy == 4) ? L2(f.zone_d, j, i) : 0;   // sponge zone (iboudy = 4)
   const bool dint = diff_interior(g, j, i, true);
   const int nring = ring_count(g, j, i, true);
 

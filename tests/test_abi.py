@@ -42,7 +42,9 @@ def test_create_rejects_bad_config(built):
     bad.struct_size = 4
     h = C.c_void_p()
     assert lib.create(C.byref(bad), C.byref(h)) == -1 and not h
-    bad = capi.default_cfg(2, jx=64, iy=34, kz=18, ds=60.0, dt=120.0, iboudy=4)   # sponge: MOLOCH core only
+    bad = capi.default_cfg(2, jx=64, iy=34, kz=18, ds=60.0, dt=120.0, iboudy=7)   # no such boundary option
+    assert lib.create(C.byref(bad), C.byref(h)) == -1 and not h
+    bad = capi.default_cfg(3, jx=64, iy=34, kz=18, ds=12.0, dt=90.0, iboudy=3)    # inflow/outflow without sponge: sigma cores only
     assert lib.create(C.byref(bad), C.byref(h)) == -1 and not h
     bad = capi.default_cfg(4, jx=64, iy=34, kz=18, ds=60.0, dt=120.0)   # no such core
     assert lib.create(C.byref(bad), C.byref(h)) == -1 and not h

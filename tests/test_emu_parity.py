@@ -9,7 +9,7 @@ from regcm_b200 import capi
 from tests.helpers import make_pair, rel_errors, smooth_qc, work_errors
 
 VARIANTS = [
-    {}, {"iboudy": 1}, {"iboudy": 0}, {"ifupr": 0}, {"ifrayd": 0}, {"ipptls": 0}, {"diffu_hgtf": 1},
+    {}, {"iboudy": 1}, {"iboudy": 0}, {"iboudy": 2}, {"iboudy": 3}, {"iboudy": 4}, {"ifupr": 0}, {"ifrayd": 0}, {"ipptls": 0}, {"diffu_hgtf": 1},
     {"upstream_mode": 0}, {"stability_enhance": 0}, {"flat": True, "unit_map": True}, {"noise": False},
 ]
 

@@ -66,7 +66,7 @@ def test_hydro_parity_vs_oracle(cuda_lib, name, nsteps):
     assert abs(dc.ptntot - dr.ptntot) <= 1e-9 * dr.ptntot and abs(dc.pt2tot - dr.pt2tot) <= 1e-7 * dr.pt2tot
 
 
-HYDRO_VARIANTS = [{"iboudy": 1}, {"iboudy": 0}, {"ipptls": 0}, {"diffu_hgtf": 0}, {"upstream_mode": 0},
+HYDRO_VARIANTS = [{"iboudy": 1}, {"iboudy": 0}, {"iboudy": 2}, {"iboudy": 3}, {"iboudy": 4}, {"ipptls": 0}, {"diffu_hgtf": 0}, {"upstream_mode": 0},
                   {"stability_enhance": 0}, {"flat": True, "unit_map": True}, {"lstand": 0}, {"nsplit": 1}, {"nsplit": 3}]
 
 

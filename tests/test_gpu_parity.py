@@ -45,7 +45,7 @@ def test_parity_vs_oracle(cuda_lib, name, nsteps):
     assert abs(dc.max_cfl - dr.max_cfl) <= 1e-11 * dr.max_cfl
 
 
-VARIANTS = [{"iboudy": 1}, {"iboudy": 0}, {"ifupr": 0}, {"ifrayd": 0}, {"ipptls": 0}, {"diffu_hgtf": 1},
+VARIANTS = [{"iboudy": 1}, {"iboudy": 0}, {"iboudy": 2}, {"iboudy": 3}, {"iboudy": 4}, {"ifupr": 0}, {"ifrayd": 0}, {"ipptls": 0}, {"diffu_hgtf": 1},
             {"upstream_mode": 0}, {"stability_enhance": 0}, {"flat": True, "unit_map": True}]
 
 

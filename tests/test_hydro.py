@@ -114,7 +114,7 @@ TOL_TABLE = 1e-11   # two independent eigen-solvers / inverses
 TOL_STATE = 1e-11   # relative L-inf per prognostic after 8 steps
 
 HYDRO_VARIANTS = [
-    {}, {"iboudy": 1}, {"iboudy": 0}, {"ipptls": 0}, {"diffu_hgtf": 0}, {"upstream_mode": 0},
+    {}, {"iboudy": 1}, {"iboudy": 0}, {"iboudy": 2}, {"iboudy": 3}, {"iboudy": 4}, {"ipptls": 0}, {"diffu_hgtf": 0}, {"upstream_mode": 0},
     {"stability_enhance": 0}, {"flat": True, "unit_map": True}, {"noise": False}, {"lstand": 0}, {"nsplit": 1}, {"nsplit": 3},
 ]
 

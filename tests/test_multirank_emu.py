@@ -72,8 +72,8 @@ def assemble(outdir, world, cfg):
     return glob
 
 
-def single_rank(emu_lib, case_name, steps, ibdyfrq=6):
-    case = synth.make_case(case_name, ibdyfrq=ibdyfrq)
+def single_rank(emu_lib, case_name, steps, ibdyfrq=6, **kw):
+    case = synth.make_case(case_name, ibdyfrq=ibdyfrq, **kw)
     core = capi.DynCore(emu_lib, case.cfg)
     synth.load_case(core, case)
     core.step(steps)
@@ -100,6 +100,17 @@ def test_multirank_matches_single_rank(emu_lib, tmp_path, world, layout):
     run_ranks(world, tmp_path, ["--case", "tiny", "--steps", str(steps), "--cpus-j", str(layout[0]), "--cpus-i", str(layout[1])])
     cfg, ref = single_rank(emu_lib, "tiny", steps)
     glob = assemble(tmp_path, world, cfg)
+    compare(glob, ref, 1e-12)
+
+
+@pytest.mark.parametrize("iboudy", [3, 4])
+def test_multirank_sponge_and_inflow_outflow(emu_lib, tmp_path, iboudy):
+    """iboudy 3 / 4 on a 2x2 decomposition: the inflow/outflow rule of `decouple` on the outermost dot ring (global
+    index tests on every tile), the qv rim rule in the ghost-extended rim lists, the sponge zones."""
+    steps = 5
+    run_ranks(4, tmp_path, ["--case", "tiny", "--steps", str(steps), "--cpus-j", "2", "--cpus-i", "2", "--iboudy", str(iboudy)])
+    cfg, ref = single_rank(emu_lib, "tiny", steps, iboudy=iboudy)
+    glob = assemble(tmp_path, 4, cfg)
     compare(glob, ref, 1e-12)
 
 
