@@ -5,8 +5,24 @@
 #include "launch.h"
 
 // origin-shifted addressing with the reference's global 1-based indices
-#define P3(p, j, i, k) (p)[(long long)(j) + (long long)(i) * si + (long long)(k) * sk]
-#define P2(p, j, i) (p)[(long long)(j) + (long long)(i) * si]
+// The element index is computed in 32-bit arithmetic: one IMAD.WIDE per access and an index shared by every field
+// read at the same point, instead of a 64-bit multiply-add chain per access (which was HALF of the issue slots of the
+// column kernels: 230 integer instructions for 40 memory operations per level in k_snd_wfwd).  rcm_dyn_create
+// rejects geometries whose largest index would not fit in 31 bits.
+// Measured per kernel on B200 (profiles/r2_measurements.md): most kernels gain (k_ppw -10 %, k_xkc -10 %, k_snd_init -8 %,
+// the other acoustic kernels -1..3 %), a few lose (k_prep +10 %, k_mo_uv +15 %, k_h_tq +4 %, k_snd_wfwd +4 %): those define RCM_IDX64
+// before including this header (or switch with RCM_USE_IDX64 / RCM_USE_IDX32 around one kernel).
+#define P3_32(p, j, i, k) (p)[(int)(j) + (int)(i) * (int)si + (int)(k) * (int)sk]
+#define P2_32(p, j, i) (p)[(int)(j) + (int)(i) * (int)si]
+#define P3_64(p, j, i, k) (p)[(long long)(j) + (long long)(i) * si + (long long)(k) * sk]
+#define P2_64(p, j, i) (p)[(long long)(j) + (long long)(i) * si]
+#ifdef RCM_IDX64
+#define P3(p, j, i, k) P3_64(p, j, i, k)
+#define P2(p, j, i) P2_64(p, j, i)
+#else
+#define P3(p, j, i, k) P3_32(p, j, i, k)
+#define P2(p, j, i) P2_32(p, j, i)
+#endif
 // read-only loads (ld.global.nc): the array is not written by the running
 // kernel, so the compiler may hoist these above stores and pipeline them
 // across the k loop

@@ -46,6 +46,7 @@ void launch_snd_wback(const Geom&, const Fields&, const StepScalars&, cudaStream
 void launch_snd_final(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_negq_repair(const Geom&, const Fields&, const StepScalars&, cudaStream_t);
 void launch_slice(const Geom&, const Fields&, int id, int hydro, double ptop, double p0, double tlp, double ts0, double dx8, double* out, cudaStream_t);
+void launch_window_strided(bool pack, double* buf, double* p_shifted, int j0, int i0, int k0, int n1, int n2, int nk, long long b1, long long b2, int si, long long sk, cudaStream_t st);
 void launch_window(bool pack, double* buf, double* p_shifted, int j0, int i0, int k0, int n1, int n2, int nk, int si, long long sk, cudaStream_t st);
 void launch_couple(const Geom&, double*, const double*, int, int, int, int, int, cudaStream_t);
 void launch_timeint(const Geom&, const double*, const double*, double*, double, int, int, int, int, int, cudaStream_t);
@@ -177,6 +178,7 @@ struct rcm_dyn {
   bool mid_step = false, head_only = false;
   double* slice_buf = nullptr;   // one 3-D field: the slice rcm_dyn_get_slice asked for
   double* stage_dev = nullptr;   // contiguous landing buffer of rcm_dyn_stage_bdy_async (one 3-D field)
+  size_t stage_cap = 0;          // its capacity in doubles
 };
 
 // host accessors in the padded geometry
@@ -367,6 +369,9 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   h->ni_pad = ni + 2 * RCM_HALO;
   g.si = h->nj_pad;
   g.sk = (long long)h->nj_pad * h->ni_pad;
+  // the kernels index with 32-bit arithmetic (dev_common.cuh): the largest element index of a field must fit
+  if ((long long)(g.jde2 + RCM_EHALO + 16) + (long long)std::max(g.si, g.esi) * (g.ide2 + RCM_EHALO + 2) + g.sk * (long long)(g.kzp1 + 2) >= (1LL << 31))
+    return bail(RCM_ERR_ARG, "tile too large for 32-bit element indices (more than 2^31 elements per field incl. the origin shift)");
   h->off2 = -((long long)(g.jde1 - RCM_HALO) + (long long)g.si * (g.ide1 - RCM_HALO));
   h->off3 = h->off2 - g.sk;
   g.esi = ((nj + 2 * RCM_EHALO + 15) / 16) * 16;
@@ -640,13 +645,22 @@ extern "C" int rcm_dyn_stage_bdy_async(rcm_dyn* h, int field, const double* a, c
     const int jlo = std::max(lb[0], g.jde1 - RCM_HALO), jhi = std::min(ub[0], g.jde2 + RCM_HALO);
     const int ilo = std::max(lb[1], g.ide1 - RCM_HALO), ihi = std::min(ub[1], g.ide2 + RCM_HALO);
     const int klo = std::max(lb[2], 1), khi = std::min(ub[2], nk);
-    if (jhi >= jlo && ihi >= ilo && khi >= klo && jlo == lb[0] && jhi == ub[0] && ilo == lb[1] && ihi == ub[1]) {
-      // whole (j,i) planes of the caller's array: ONE contiguous H2D copy into a landing buffer, unpacked on the device
-      if (!h->stage_dev) CUDA_OK(cudaMalloc((void**)&h->stage_dev, (size_t)g.sk * (size_t)g.kzp1 * sizeof(double)));
-      const int n1 = jhi - jlo + 1, n2 = ihi - ilo + 1, nkk = khi - klo + 1;
-      CUDA_OK(cudaMemcpyAsync(h->stage_dev, a + (size_t)n1 * n2 * (size_t)(klo - lb[2]), (size_t)n1 * n2 * nkk * sizeof(double),
-                              cudaMemcpyHostToDevice, h->st_copy));
-      launch_window(false, h->stage_dev, dst_async, jlo, ilo, klo, n1, n2, nkk, g.si, g.sk, h->st_copy);
+    if (jhi >= jlo && ihi >= ilo && khi >= klo) {
+      // ONE contiguous H2D copy of the planes klo..khi of the caller's array (whatever its window) into a landing
+      // buffer; the unpack kernel scatters the part that falls on this rank's padded tile
+      const size_t n1 = (size_t)(ub[0] - lb[0] + 1), n2 = (size_t)(ub[1] - lb[1] + 1), nkk = (size_t)(khi - klo + 1);
+      const size_t need = n1 * n2 * nkk;
+      if (need > h->stage_cap) {
+        if (h->stage_dev) { CUDA_OK(cudaStreamSynchronize(h->st_copy)); CUDA_OK(cudaFree(h->stage_dev)); h->stage_dev = nullptr; }
+        const size_t cap = std::max(need, (size_t)g.sk * (size_t)g.kzp1);
+        CUDA_OK(cudaMalloc((void**)&h->stage_dev, cap * sizeof(double)));
+        h->stage_cap = cap;
+      }
+      CUDA_OK(cudaMemcpyAsync(h->stage_dev, a + n1 * n2 * (size_t)(klo - lb[2]), need * sizeof(double), cudaMemcpyHostToDevice, h->st_copy));
+      // element (j,i,k) of the window sits at (j-lb0) + n1*((i-lb1) + n2*(k-klo)): shift the buffer so that the
+      // kernel's own origin (jlo,ilo,klo) with row pitch n1 lands there
+      launch_window_strided(false, h->stage_dev + (size_t)(jlo - lb[0]) + n1 * (size_t)(ilo - lb[1]), dst_async, jlo, ilo, klo,
+                            jhi - jlo + 1, ihi - ilo + 1, (int)nkk, (long long)n1, (long long)(n1 * n2), g.si, g.sk, h->st_copy);
       h->launches += 1;
     } else {
       int rc = copy3d(h, dst_async, a, lb, ub, nk, true, h->st_copy, false);

@@ -18,6 +18,9 @@
 //               diffu_x3d/x4d, forecast, negative-q guard, filters RA(t) RAW(qv) RAW(qc)
 //   k_h_psfilt  filter_ra_2d(psa,psb,psc) Main/mod_timefilter.F90:58-73, then psc2psd(psa)
 //               as at the head of splitf (Main/mod_split.F90:259-260)
+#ifndef RCM_IDX32_ALL   // (tuning builds only)
+#define RCM_IDX64   // 64-bit element indices measured faster for the kernels of this file (dev_common.cuh)
+#endif
 #include "dev_common.cuh"
 #include "launch.h"
 

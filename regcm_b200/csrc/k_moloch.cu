@@ -8,6 +8,9 @@
 // One thread owns one (j,i) column in k_mo_w (the vertical recurrences); the other kernels are
 // elementwise over (j,i,k).  u and v are double-buffered (u,v -> un,vn) so that the Coriolis average
 // reads the pre-update winds, which is what the reference's ud/vd copies are for (:735-736).
+#ifndef RCM_IDX32_ALL   // (tuning builds only)
+#define RCM_IDX64   // 64-bit element indices measured faster for the kernels of this file (dev_common.cuh)
+#endif
 #include "dev_common.cuh"
 #include "launch.h"
 

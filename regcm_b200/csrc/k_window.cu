@@ -20,7 +20,36 @@ __global__ void __launch_bounds__(256) k_window(double* __restrict__ buf, double
     if (PACK) buf[t] = *q; else *q = buf[t];
   }
 }
+// same with a strided buffer: buf[jj + b1*ii + b2*kk] (b1 = row pitch, b2 = plane pitch of the caller's array)
+template <bool PACK>
+__global__ void __launch_bounds__(256) k_window_strided(double* __restrict__ buf, double* __restrict__ p, const int j0, const int i0,
+                                                        const int k0, const int n1, const int n2, const int nk, const long long b1,
+                                                        const long long b2, const int si, const long long sk) {
+  const long long n = (long long)n1 * n2 * nk;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+    const int jj = (int)(t % n1);
+    const long long r = t / n1;
+    const int ii = (int)(r % n2), kk = (int)(r / n2);
+    double* q = p + (long long)(j0 + jj) + (long long)(i0 + ii) * si + (long long)(k0 + kk) * sk;
+    double* b = buf + jj + b1 * ii + b2 * kk;
+    if (PACK) *b = *q; else *q = *b;
+  }
+}
 }  // namespace
+
+void launch_window_strided(bool pack, double* buf, double* p_shifted, int j0, int i0, int k0, int n1, int n2, int nk, long long b1,
+                           long long b2, int si, long long sk, cudaStream_t st) {
+  const long long n = (long long)n1 * n2 * nk;
+  if (n <= 0) return;
+  const unsigned blocks = (unsigned)std::min<long long>((n + 255) / 256, 148LL * 16);
+#ifdef RCM_EMU
+  if (pack) RCM_LAUNCH(k_window_strided<true>, dim3(blocks), dim3(256), st, buf, p_shifted, j0, i0, k0, n1, n2, nk, b1, b2, si, sk);
+  else RCM_LAUNCH(k_window_strided<false>, dim3(blocks), dim3(256), st, buf, p_shifted, j0, i0, k0, n1, n2, nk, b1, b2, si, sk);
+#else
+  if (pack) k_window_strided<true><<<blocks, 256, 0, st>>>(buf, p_shifted, j0, i0, k0, n1, n2, nk, b1, b2, si, sk);
+  else k_window_strided<false><<<blocks, 256, 0, st>>>(buf, p_shifted, j0, i0, k0, n1, n2, nk, b1, b2, si, sk);
+#endif
+}
 
 void launch_window(bool pack, double* buf, double* p_shifted, int j0, int i0, int k0, int n1, int n2, int nk, int si, long long sk,
                    cudaStream_t st) {

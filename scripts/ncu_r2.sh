@@ -1,0 +1,14 @@
+# round 2 profiling evidence, ONE ncu pass per gpurun call (each only after the same command exited 0 without ncu):
+#   MODE=list : launch list (gpu__time_duration.sum) of 2 timed steps            -> gpurun_out/launches_r2.csv
+#   MODE=full : ncu --set full of the kernels of ONE step, slow kernels serialised -> gpurun_out/prof_r2.ncu-rep
+mkdir -p gpurun_out
+CMD="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu"
+$CMD > gpurun_out/plain_r2.json 2> gpurun_out/plain_r2.err || { echo "plain run failed"; tail -5 gpurun_out/plain_r2.err; exit 1; }
+if [ "$MODE" = full ]; then
+RCM_OVERLAP=0 ncu --set full --clock-control none --import-source on --kernel-name 'regex:k_' --launch-skip ${SKIP:-92} --launch-count ${COUNT:-27} \
+  -f -o gpurun_out/prof_r2 $CMD > gpurun_out/ncu_r2_full.log 2>&1
+tail -2 gpurun_out/ncu_r2_full.log | cut -c1-200; ls -la gpurun_out/prof_r2.ncu-rep
+else
+ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip ${SKIP:-60} --launch-count 200 --csv --log-file gpurun_out/launches_r2.csv $CMD > gpurun_out/ncu_r2_list.log 2>&1
+wc -l gpurun_out/launches_r2.csv
+fi
