@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 CMD="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu"
 $CMD > gpurun_out/plain_r2.json 2> gpurun_out/plain_r2.err || { echo "plain run failed"; tail -5 gpurun_out/plain_r2.err; exit 1; }
 if [ "$MODE" = full ]; then
-RCM_OVERLAP=0 ncu --set full --clock-control none --import-source on --kernel-name 'regex:k_' --launch-skip ${SKIP:-92} --launch-count ${COUNT:-27} \
+RCM_OVERLAP=0 ncu --set full --metrics smsp__inst_executed_pipe_fp64.sum,smsp__inst_executed.sum --clock-control none --import-source on --kernel-name 'regex:k_' --launch-skip ${SKIP:-92} --launch-count ${COUNT:-27} \
   -f -o gpurun_out/prof_r2 $CMD > gpurun_out/ncu_r2_full.log 2>&1
 tail -2 gpurun_out/ncu_r2_full.log | cut -c1-200; ls -la gpurun_out/prof_r2.ncu-rep
 else
