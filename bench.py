@@ -224,8 +224,6 @@ def run_gpu(args):
     del probe_cfg
     hydro = base.get("idynamic", 2) == 1
     moloch = base.get("idynamic", 2) == 3
-    if hydro and world > 1:
-        raise SystemExit("bench.py: the hydrostatic workload (BASELINE configs[0]) is a single-rank case")
     cfg = capi.default_cfg(base.get("idynamic", 2), jx=base["jx"], iy=base["iy"], kz=base["kz"], ds=base["ds"], dt=base["dt"],
                            nspgx=base["nspg"], nspgd=base["nspg"], **cfgkw)
     core = capi.DynCore(lib, cfg)

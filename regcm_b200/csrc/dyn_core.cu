@@ -54,7 +54,7 @@ void launch_bdyval(const Geom&, const Fields&, const double*, const double*, con
                    const int2*, int, double, int, int, cudaStream_t);
 
 // hydrostatic core (k_hydro.cu, k_split.cu)
-void launch_psc2psd(const Geom&, const double*, double*, double*, cudaStream_t);
+void launch_psc2psd(const Geom&, const double*, double*, double*, int gw, cudaStream_t);
 void launch_ps_convert(const Geom&, double*, double, cudaStream_t);
 void launch_h_ps(const Geom&, const Fields&, cudaStream_t);
 void launch_h_rimcopy(const Geom&, const Fields&, const int2*, int, const int2*, int, cudaStream_t);
@@ -309,7 +309,6 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   h->moloch = (c.idynamic == 3);
   if (h->moloch && (c.mo_nadv < 1 || c.mo_nsound < 1 || c.kz < 4 || c.ipptls < 0 || c.ipptls > 1))
     return bail(RCM_ERR_ARG, "idynamic=3 needs mo_nadv >= 1, mo_nsound >= 1, kz >= 4, ipptls 0 or 1");
-  if (h->hydro && c.nproc != 1) return bail(RCM_ERR_ARG, "idynamic=1 runs on one rank only (BASELINE configs[0] is a single-rank case)");
   if (h->hydro && (c.nsplit < 1 || c.nsplit > RCM_MAXSPLIT || c.nsplit > c.kz)) return bail(RCM_ERR_ARG, "nsplit must be 1..4");
   if (c.idiffu != 1) return bail(RCM_ERR_ARG, "only idiffu=1 is implemented");
   // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)
@@ -711,9 +710,10 @@ static void build_zone(rcm_dyn* h, bool dot, std::vector<int>& z) {
   const int igbb1 = 2, igbb2 = nsp - 1, jgbl1 = 2, jgbl2 = nsp - 1;
   const int igbt1 = iy - icy - nsp + 2, igbt2 = iy - icy - 1;
   const int jgbr1 = jx - icx - nsp + 2, jgbr2 = jx - icx - 1;
-  // the zones are computed on this rank's dot extent (jde1:jde2,ide1:ide2)
-  for (int i = g.ide1; i <= g.ide2; ++i)
-    for (int j = g.jde1; j <= g.jde2; ++j) {
+  // the zones are computed on this rank's dot extent (jde1:jde2,ide1:ide2) and, being a function of the global
+  // indices only, on its ghost rows (k_h_prep relaxes the p* tendency on the first ghost ring)
+  for (int i = std::max(1, g.ide1 - RCM_HALO); i <= std::min(iy, g.ide2 + RCM_HALO); ++i)
+    for (int j = std::max(1, g.jde1 - RCM_HALO); j <= std::min(jx, g.jde2 + RCM_HALO); ++j) {
       int v = 0;
       if (i >= igbb1 && i <= igbb2 && j >= jgbl1 && j <= jgbr2 && !(j <= jgbl2 && i >= j) && !(j >= jgbr1 && i >= (jgbr2 - j + 2)))
         v = i - igbb1 + 2;  // south
@@ -762,6 +762,37 @@ static int exch_state(rcm_dyn* h) {  // atm1/atm2 all prognostics, width 2 (Main
   Fields& f = h->f;
   if (h->halo.exchange({{f.au, kz, 1}, {f.av, kz, 1}, {f.at, kz, 0}, {f.aqv, kz, 0}, {f.aqc, kz, 0}, {f.app, kz, 0}, {f.aw, kzp1, 0},
                         {f.bu, kz, 1}, {f.bv, kz, 1}, {f.bt, kz, 0}, {f.bqv, kz, 0}, {f.bqc, kz, 0}, {f.bpp, kz, 0}, {f.bw, kzp1, 0}},
+                       RCM_HALO, h->st))
+    return fail(h, RCM_ERR_NCCL, "halo exchange (state) failed");
+  return RCM_OK;
+}
+// ---- hydrostatic core (the reference's call sites: Main/mod_tendency.F90:866-869, Main/mod_split.F90:197-198,
+//      276-277,312-313,438,499,527-528,583) ----
+static int exch_h_psdot(rcm_dyn* h) {   // dot-point p* tables of both time levels after psc2psd
+  if (h->cfg.nproc <= 1) return RCM_OK;
+  const Geom& g = h->g; Fields& f = h->f;
+  if (h->halo.exchange({{f.psdota - g.sk, 1, 1}, {f.rpsda - g.sk, 1, 1}, {f.psdotb - g.sk, 1, 1}, {f.rpsdb - g.sk, 1, 1}}, RCM_HALO, h->st))
+    return fail(h, RCM_ERR_NCCL, "halo exchange (psdot) failed");
+  return RCM_OK;
+}
+static int exch_h_new(rcm_dyn* h) {   // forecast and filtered winds for splitf's divergences + the moisture forecast for the repair
+  if (h->cfg.nproc <= 1) return RCM_OK;
+  const int kz = h->g.kz; Fields& f = h->f;
+  if (h->halo.exchange({{f.nau, kz, 1}, {f.nav, kz, 1}, {f.nbu, kz, 1}, {f.nbv, kz, 1}, {f.cqv, kz, 0}, {f.cqc, kz, 0}}, 1, h->st))
+    return fail(h, RCM_ERR_NCCL, "halo exchange (new winds, qx forecast) failed");
+  return RCM_OK;
+}
+static int exch_h_modal(rcm_dyn* h, double* p, int nplanes) {   // delh of one time slot / dhsum: nsplit planes, one row
+  if (h->cfg.nproc <= 1) return RCM_OK;
+  if (h->halo.exchange({{p, nplanes, 0}}, 1, h->st)) return fail(h, RCM_ERR_NCCL, "halo exchange (split-explicit modes) failed");
+  return RCM_OK;
+}
+static int exch_h_state(rcm_dyn* h) {   // atm1/atm2 prognostics and p* of both time levels, width RCM_HALO
+  if (h->cfg.nproc <= 1) return RCM_OK;
+  const Geom& g = h->g; Fields& f = h->f;
+  const int kz = g.kz;
+  if (h->halo.exchange({{f.au, kz, 1}, {f.av, kz, 1}, {f.at, kz, 0}, {f.aqv, kz, 0}, {f.aqc, kz, 0}, {f.psa - g.sk, 1, 0},
+                        {f.bu, kz, 1}, {f.bv, kz, 1}, {f.bt, kz, 0}, {f.bqv, kz, 0}, {f.bqc, kz, 0}, {f.psb - g.sk, 1, 0}},
                        RCM_HALO, h->st))
     return fail(h, RCM_ERR_NCCL, "halo exchange (state) failed");
   return RCM_OK;
@@ -1164,12 +1195,24 @@ static int download2(rcm_dyn* h, const double* dev2, std::vector<double>& v) {
   return RCM_OK;
 }
 
+// dot-point p* of a boundary record on the ghost rows (its outermost row needs cross-point p* beyond the host window)
+static int exch_h_bdy_psdot(rcm_dyn* h) {
+  if (h->cfg.nproc <= 1) return RCM_OK;
+  if (h->halo.exchange({{h->psdot_bdy - h->g.sk, 1, 1}}, RCM_HALO, h->st)) return fail(h, RCM_ERR_NCCL, "halo exchange (boundary psdot) failed");
+  return RCM_OK;
+}
+
 static int init_hydro(rcm_dyn* h) {
   const Geom& g = h->g;
   const rcm_cfg& c = h->cfg;
   Fields& f = h->f;
   const int kz = g.kz;
   int rc;
+  // tile + ghost rows inside the global domain (the host window)
+  const int jdlo = std::max(1, g.jde1 - RCM_HALO), jdhi = std::min(g.jx, g.jde2 + RCM_HALO);
+  const int idlo = std::max(1, g.ide1 - RCM_HALO), idhi = std::min(g.iy, g.ide2 + RCM_HALO);
+  const int jclo = jdlo, jchi = std::min(g.jx - 1, g.jde2 + RCM_HALO);
+  const int iclo = idlo, ichi = std::min(g.iy - 1, g.ide2 + RCM_HALO);
   // ---- boundary records (init_bdy, Main/mod_bdycod.F90:393-396,408-423,522-552,625-637):
   //      p* from the ICBC surface pressure, dot-point p*, coupling, tendencies ----
   h->xbctime = 0.0;
@@ -1177,21 +1220,21 @@ static int init_hydro(rcm_dyn* h) {
   for (int rec = 0; rec < 2; ++rec) {
     double* ps = rec ? h->xps_b1 : f.xpsb0;
     launch_ps_convert(g, ps, c.ptop, h->st);
-    launch_psc2psd(g, ps, h->psdot_bdy, nullptr, h->st);
+    launch_psc2psd(g, ps, h->psdot_bdy, nullptr, 0, h->st);
+    if ((rc = exch_h_bdy_psdot(h))) return rc;
     for (int q = 0; q < 4; ++q) {
       const bool dot = (q < 2);
       double* a = rec ? h->b1[q] : ub[q];
-      launch_couple(g, a, dot ? h->psdot_bdy : ps, kz, dot ? g.jde1 : g.jce1, dot ? g.jde2 : g.jce2, dot ? g.ide1 : g.ice1,
-                    dot ? g.ide2 : g.ice2, h->st);
+      launch_couple(g, a, dot ? h->psdot_bdy : ps, kz, dot ? jdlo : jclo, dot ? jdhi : jchi, dot ? idlo : iclo, dot ? idhi : ichi, h->st);
     }
     h->launches += 6;
   }
   for (int q = 0; q < 4; ++q) {
     const bool dot = (q < 2);
-    launch_timeint(g, h->b1[q], *bdy_b0(h, q), *bdy_bt(h, q), h->rdtbdy, kz, dot ? g.jde1 : g.jce1, dot ? g.jde2 : g.jce2,
-                   dot ? g.ide1 : g.ice1, dot ? g.ide2 : g.ice2, h->st);
+    launch_timeint(g, h->b1[q], *bdy_b0(h, q), *bdy_bt(h, q), h->rdtbdy, kz, dot ? jdlo : jclo, dot ? jdhi : jchi, dot ? idlo : iclo,
+                   dot ? idhi : ichi, h->st);
   }
-  launch_timeint(g, h->xps_b1 - g.sk, f.xpsb0 - g.sk, f.xpsbt - g.sk, h->rdtbdy, 1, g.jce1, g.jce2, g.ice1, g.ice2, h->st);
+  launch_timeint(g, h->xps_b1 - g.sk, f.xpsb0 - g.sk, f.xpsbt - g.sk, h->rdtbdy, 1, jclo, jchi, iclo, ichi, h->st);
   h->launches += 5;
   // ---- initial state (init, Main/mod_init.F90:96-147,173-178) ----
   {
@@ -1209,6 +1252,7 @@ static int init_hydro(rcm_dyn* h) {
   }
   launch_h_ps(g, f, h->st);
   h->launches += 1;
+  if ((rc = exch_h_psdot(h))) return rc;
   h->lcount = 0; h->model_time = 0;
   h->day_lastact = 0; h->day_now = 0; h->bdy_lastact = 0; h->bdy_now = 0;
   // ---- spinit (Main/mod_split.F90:75-239): vertical modes on the host, storage on the device ----
@@ -1229,7 +1273,8 @@ static int init_hydro(rcm_dyn* h) {
           lxms = lxms + rnpts * map;
           lxps = lxps + rnpts * H2(psa, j, i) * map;
         }
-      xps = lxps / lxms;
+      std::vector<double> sums((size_t)kz + 2, 0.0);   // sumall of the reference (Main/mod_split.F90:112-127)
+      sums[0] = lxms; sums[1] = lxps;
       for (int k = 1; k <= kz; ++k) {
         double ltbark = 0.0;
         for (int i = g.ice1; i <= g.ice2; ++i)
@@ -1237,8 +1282,12 @@ static int init_hydro(rcm_dyn* h) {
             const double map = 1.0 / (H2(msfx, j, i) * H2(msfx, j, i));
             ltbark = ltbark + rnpts * map * H3(t, j, i, k) / H2(psa, j, i);
           }
-        tbarh[k] = ltbark / lxms;
+        sums[(size_t)k + 1] = ltbark;
       }
+      if (c.nproc > 1 && h->halo.allreduce_host(sums.data(), kz + 2, 0)) return fail(h, RCM_ERR_NCCL, "allreduce failed (spinit means)");
+      lxms = sums[0]; lxps = sums[1];
+      xps = lxps / lxms;
+      for (int k = 1; k <= kz; ++k) tbarh[k] = sums[(size_t)k + 1] / lxms;
     }
     if (rcm_split_tables(kz, c.nsplit, c.lstand, c.ptop, h->dtsec, h->h_sigma, xps, tbarh, h->sp))
       return fail(h, RCM_ERR_ARG, "vmodes: the vertical mode problem reported errors (Main/mod_vmodes.F90:435-436)");
@@ -1280,16 +1329,17 @@ static int bdyin(rcm_dyn* h) {
     std::swap(f.xpsb0, h->xps_b1);
     std::swap(h->xps_b1, h->xps_nx);
     launch_ps_convert(g, h->xps_b1, h->cfg.ptop, h->st);
-    launch_psc2psd(g, h->xps_b1, h->psdot_bdy, nullptr, h->st);
+    launch_psc2psd(g, h->xps_b1, h->psdot_bdy, nullptr, 0, h->st);
+    { const int rcx = exch_h_bdy_psdot(h); if (rcx) return rcx; }
     for (int q = 0; q < 4; ++q) {
       std::swap(*bdy_b0(h, q), h->b1[q]);
       std::swap(h->b1[q], h->nx[q]);
       const bool dot = (q < 2);
-      const int j1 = dot ? g.jde1 : g.jce1, j2 = dot ? g.jde2 : g.jce2, i1 = dot ? g.ide1 : g.ice1, i2 = dot ? g.ide2 : g.ice2;
+      const int j1 = dot ? jdlo : jclo, j2 = dot ? jdhi : jchi, i1 = dot ? idlo : iclo, i2 = dot ? idhi : ichi;
       launch_couple(g, h->b1[q], dot ? h->psdot_bdy : h->xps_b1, kz, j1, j2, i1, i2, h->st);
       launch_timeint(g, h->b1[q], *bdy_b0(h, q), *bdy_bt(h, q), h->rdtbdy, kz, j1, j2, i1, i2, h->st);
     }
-    launch_timeint(g, h->xps_b1 - g.sk, f.xpsb0 - g.sk, f.xpsbt - g.sk, h->rdtbdy, 1, g.jce1, g.jce2, g.ice1, g.ice2, h->st);
+    launch_timeint(g, h->xps_b1 - g.sk, f.xpsb0 - g.sk, f.xpsbt - g.sk, h->rdtbdy, 1, jclo, jchi, iclo, ichi, h->st);
     h->launches += 11;
     h->have_next = false;
     return RCM_OK;
@@ -1381,12 +1431,15 @@ static int tend_hydro(rcm_dyn* h) {
   s.xt = h->xbctime + h->dt;
   s.integrating = h->lcount > 0 ? 1 : 0;
   h->last_istep = 0;
+  int rc = RCM_OK;
   s.cq_mode = h->cq_mode;
   StepScalars s2 = s; s2.cq_mode = 1;   // second pass of k_h_tq: exits at once unless the first one found negative moisture
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.nq_cnt, 0, (size_t)2 * g.kz * sizeof(int), h->st));
   if (!h->mid_step) {   // head of `tend`: everything physical_parametrizations depends on (Main/mod_tendency.F90:230-270)
     TIMED(KID_H_PS, 2, (launch_h_ps(g, f, h->st), launch_h_rimcopy(g, f, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, h->st)));
+    TIMED(KID_HALO, 0, rc = exch_h_psdot(h));
+    if (rc) return rc;
     TIMED(KID_H_PREP, 1, launch_h_prep(g, f, s, h->st));
     TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
   }
@@ -1407,14 +1460,26 @@ static int tend_hydro(rcm_dyn* h) {
     CUDA_OK(cudaEventRecord(h->ev_jb, h->st_b));
     CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jb, 0));
   }
-  // time filter of p*, then p* on dot points as at the head of splitf (:259-260)
-  TIMED(KID_H_PS, 2, (launch_h_psfilt(g, f, s, h->st), launch_psc2psd(g, f.psa, f.psdota, nullptr, h->st)));
+  // splitf reads the new winds one dot row out (Main/mod_split.F90:276-277,312-313); the repair reads the forecast moisture
+  TIMED(KID_HALO, 0, rc = exch_h_new(h));
+  if (rc) return rc;
+  // time filter of p*, then p* on dot points as at the head of splitf (:259-260); both also on the ghost ring
+  // spstep reads (the reference exchanges psdot there, :197-198)
+  TIMED(KID_H_PS, 2, (launch_h_psfilt(g, f, s, h->st), launch_psc2psd(g, f.psa, f.psdota, nullptr, 1, h->st)));
   // negative-moisture repair (Main/mod_tendency.F90:381-393), after the p* filter whose result floors the qv filter (:420-425)
   TIMED(KID_NEGQ, 1, launch_negq_repair(g, f, s, h->st));
   TIMED(KID_SP_PROJ, 1, launch_sp_proj(g, f, s, h->st));
   int m2max = 0;
   for (int l = 0; l < s.nsplit; ++l) m2max = std::max(m2max, s.sp_m2[l]);
-  for (int n = 1; n <= m2max; ++n) TIMED(KID_SP_STEP, 1, launch_sp_step(g, f, s, n, h->st));
+  for (int n = 1; n <= m2max; ++n) {
+    // the gradient of delh of the source time slot is taken on the 3x3 neighbourhood (:499,527-528,583)
+    const int src = (n == 1) ? 1 : ((n & 1) ? 1 : 2);
+    TIMED(KID_HALO, 0, rc = exch_h_modal(h, f.delh + (long long)(src - 1) * s.nsplit * g.sk, s.nsplit));
+    if (rc) return rc;
+    TIMED(KID_SP_STEP, 1, launch_sp_step(g, f, s, n, h->st));
+  }
+  TIMED(KID_HALO, 0, rc = exch_h_modal(h, f.dhsum, s.nsplit));   // :438
+  if (rc) return rc;
   TIMED(KID_SP_CORR, 2, launch_sp_corr(g, f, s, h->st));
   std::swap(f.au, f.nau); std::swap(f.av, f.nav); std::swap(f.bu, f.nbu); std::swap(f.bv, f.nbv);
   std::swap(f.at, f.nat); std::swap(f.aqv, f.naqv); std::swap(f.aqc, f.naqc);
@@ -1583,7 +1648,7 @@ static int enqueue_steps(rcm_dyn* h, int nsteps) {
         if ((rc = bdyin(h))) break;
       }
       // after the swap in tend(): n?? hold the previous level-a buffers
-      TIMED(KID_HALO, 0, rc = exch_state(h));
+      TIMED(KID_HALO, 0, rc = h->hydro ? exch_h_state(h) : exch_state(h));
       if (rc) break;
       if ((rc = bdyval(h, f.nat, f.naqv, f.naqc))) break;
     }

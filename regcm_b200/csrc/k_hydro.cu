@@ -26,7 +26,8 @@
 
 using namespace rcm;
 
-// psc2psd on global indices (single-rank tile: every side is a physical boundary)
+// psc2psd on global indices: the physical-boundary rules key on the global row/column, so the same code serves
+// every tile of a decomposition (the cross-point p* it reads lies in the exchanged ghost rows)
 __device__ __forceinline__ double psd_at(const Geom& g, const double* pc, int j, int i) {
   const int si = g.si;
   const bool jl = (j == 1), jr = (j == g.jx), ib = (i == 1), it = (i == g.iy);
@@ -39,34 +40,41 @@ __device__ __forceinline__ double psd_at(const Geom& g, const double* pc, int j,
 }
 
 // generic: pd = psc2psd(pc) on the dot extent; optional reciprocals
-__global__ void k_psc2psd(const Geom g, const double* pc, double* pd, double* rpd) {
+// gw = ghost rows computed on the HIGH sides that have a neighbour rank (0: the tile's own dot points)
+__global__ void k_psc2psd(const Geom g, const double* pc, double* pd, double* rpd, const int gw) {
   const int si = g.si;
   const int j = g.jde1 + blockIdx.x * blockDim.x + threadIdx.x;
   const int i = g.ide1 + blockIdx.y * blockDim.y + threadIdx.y;
-  if (j > g.jde2 || i > g.ide2) return;
+  if (j > g.jde2 + gw * g.gr || i > g.ide2 + gw * g.gt) return;
   const double v = psd_at(g, pc, j, i);
   P2(pd, j, i) = v;
   if (rpd) P2(rpd, j, i) = 1.0 / v;
 }
 
 // xpsb record: surface pressure [hPa] -> p* [cb] (Main/mod_bdycod.F90:394)
-__global__ void k_ps_convert(const Geom g, double* ps, double ptop) {
+__global__ void k_ps_convert(const Geom g, double* ps, double ptop) {   // whole host window: tile + RCM_HALO ghost rows
   const int si = g.si;
-  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
-  if (j > g.jce2 || i > g.ice2) return;
+  const int j = (g.jce1 - RCM_HALO * g.gl) + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (g.ice1 - RCM_HALO * g.gb) + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j > g.jce2 + RCM_HALO * g.gr || i > g.ice2 + RCM_HALO * g.gt) return;
   P2(ps, j, i) = (P2(ps, j, i) * 0.1) - ptop;
 }
 
+// On a decomposed domain 1/p* on cross points is also computed on the RCM_HALO ghost rows (p* was exchanged that
+// wide at the end of the previous step); the dot-point tables need cross-point p* one row further out than the
+// ghost rows reach, so they are computed on the tile's own points and exchanged (the reference does the same:
+// psc2psd, then exchange; Main/mod_tendency.F90:858-869).
 __global__ void k_h_ps(const Geom g, const Fields f) {
   const int si = g.si;
-  const int j = g.jde1 + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = g.ide1 + blockIdx.y * blockDim.y + threadIdx.y;
-  if (j > g.jde2 || i > g.ide2) return;
-  const double pa = psd_at(g, f.psa, j, i), pb = psd_at(g, f.psb, j, i);
-  P2(f.psdota, j, i) = pa; P2(f.rpsda, j, i) = 1.0 / pa;
-  P2(f.psdotb, j, i) = pb; P2(f.rpsdb, j, i) = 1.0 / pb;
-  if (j <= g.jce2 && i <= g.ice2) {
+  const int j = (g.jde1 - 2 * g.gl) + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (g.ide1 - 2 * g.gb) + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j > g.jde2 + 2 * g.gr || i > g.ide2 + 2 * g.gt) return;
+  if (j >= g.jde1 && j <= g.jde2 && i >= g.ide1 && i <= g.ide2) {
+    const double pa = psd_at(g, f.psa, j, i), pb = psd_at(g, f.psb, j, i);
+    P2(f.psdota, j, i) = pa; P2(f.rpsda, j, i) = 1.0 / pa;
+    P2(f.psdotb, j, i) = pb; P2(f.rpsdb, j, i) = 1.0 / pb;
+  }
+  if (j <= g.jce2 + 2 * g.gr && i <= g.ice2 + 2 * g.gt) {
     P2(f.rpsa, j, i) = 1.0 / P2(f.psa, j, i);
     P2(f.rpsb, j, i) = 1.0 / P2(f.psb, j, i);
   }
@@ -98,9 +106,11 @@ __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_PREP)
 k_h_prep(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
-  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
-  if (j > g.jce2 || i > g.ice2) return;
+  // tile + one ghost ring towards neighbour ranks: qdot, phi and the forecast p* are read one row out by k_h_uv,
+  // k_h_psfilt and psc2psd; recomputing that ring (bit-identical to the owner's values) replaces three exchanges
+  const int j = (g.jce1 - g.gl) + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (g.ice1 - g.gb) + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j > g.jce2 + g.gr || i > g.ice2 + g.gt) return;
   const int kz = g.kz;
   const double rpsa = L2(f.rpsa, j, i), psa = L2(f.psa, j, i), psb = L2(f.psb, j, i);
   const double msfx = L2(f.msfx, j, i);
@@ -152,7 +162,8 @@ k_h_prep(const Geom g, const Fields f, const StepScalars s) {
     }
   }
   // ---- new_pressure (:1428-1460): relaxation of pten, forecast p* ----
-  const bool interior = (j >= g.jci1 && j <= g.jci2 && i >= g.ici1 && i <= g.ici2);
+  const bool own = (j >= g.jci1 && j <= g.jci2 && i >= g.ici1 && i <= g.ici2);        // this rank's interior points
+  const bool interior = (j >= 2 && j <= g.jx - 2 && i >= 2 && i <= g.iy - 2);         // interior of the global domain
   double ptn = pten;
   if (interior && (s.iboudy == 1 || s.iboudy == 5)) {
     const int ib = L2(f.zone_c, j, i);
@@ -171,7 +182,7 @@ k_h_prep(const Geom g, const Fields f, const StepScalars s) {
   }
   const double psc = psb + ptn * s.dt;
   P2(f.psc, j, i) = psc;
-  if (interior) {
+  if (own) {
     P2(f.ptn2d, j, i) = s.integrating ? fabs(ptn) : 0.0;
     P2(f.pt22d, j, i) = s.integrating ? fabs((psc + psb - 2.0 * psa) / (s.dt * s.dt * 0.25)) : 0.0;
   }
@@ -564,9 +575,10 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
 // filter_ra_2d(psa, psb, psc) on the interior (Main/mod_timefilter.F90:58-73)
 __global__ void k_h_psfilt(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
-  const int j = g.jci1 + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = g.ici1 + blockIdx.y * blockDim.y + threadIdx.y;
-  if (j > g.jci2 || i > g.ici2) return;
+  // + one ghost ring towards neighbour ranks (psc2psd of the filtered p* reads it; see k_h_prep)
+  const int j = (g.jci1 - g.gl) + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (g.ici1 - g.gb) + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j > g.jci2 + g.gr || i > g.ici2 + g.gt) return;
   const double psa = P2(f.psa, j, i), psb = P2(f.psb, j, i), psc = P2(f.psc, j, i);
   const double d = s.gnu1 * (psc + psb - 2.0 * psa);
   P2(f.psb, j, i) = psa + d;
@@ -586,17 +598,17 @@ __global__ void k_bdyval_ps(const Geom g, const Fields f, const int2* rim, int n
 // ---------------------------------------------------------------------------
 static dim3 grid2(int nj, int ni, dim3 b) { return dim3((nj + b.x - 1) / b.x, (ni + b.y - 1) / b.y); }
 
-void launch_psc2psd(const Geom& g, const double* pc, double* pd, double* rpd, cudaStream_t st) {
+void launch_psc2psd(const Geom& g, const double* pc, double* pd, double* rpd, int gw, cudaStream_t st) {
   dim3 b(32, 8);
-  RCM_LAUNCH(k_psc2psd, grid2(g.jde2 - g.jde1 + 1, g.ide2 - g.ide1 + 1, b), b, st, g, pc, pd, rpd);
+  RCM_LAUNCH(k_psc2psd, grid2(g.jde2 - g.jde1 + 1 + gw * g.gr, g.ide2 - g.ide1 + 1 + gw * g.gt, b), b, st, g, pc, pd, rpd, gw);
 }
 void launch_ps_convert(const Geom& g, double* ps, double ptop, cudaStream_t st) {
   dim3 b(32, 8);
-  RCM_LAUNCH(k_ps_convert, grid2(g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, b), b, st, g, ps, ptop);
+  RCM_LAUNCH(k_ps_convert, grid2(g.jce2 - g.jce1 + 1 + RCM_HALO * (g.gl + g.gr), g.ice2 - g.ice1 + 1 + RCM_HALO * (g.gb + g.gt), b), b, st, g, ps, ptop);
 }
 void launch_h_ps(const Geom& g, const Fields& f, cudaStream_t st) {
   dim3 b(32, 8);
-  RCM_LAUNCH(k_h_ps, grid2(g.jde2 - g.jde1 + 1, g.ide2 - g.ide1 + 1, b), b, st, g, f);
+  RCM_LAUNCH(k_h_ps, grid2(g.jde2 - g.jde1 + 1 + 2 * (g.gl + g.gr), g.ide2 - g.ide1 + 1 + 2 * (g.gb + g.gt), b), b, st, g, f);
 }
 void launch_h_rimcopy(const Geom& g, const Fields& f, const int2* rim_d, int nrim_d, const int2* rim_c, int nrim_c, cudaStream_t st) {
   const int n = nrim_d > nrim_c ? nrim_d : nrim_c;
@@ -606,7 +618,7 @@ void launch_h_rimcopy(const Geom& g, const Fields& f, const int2* rim_d, int nri
 }
 void launch_h_prep(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const dim3 b = rcm::col_block();
-  RCM_LAUNCH(k_h_prep, grid2(g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, b), b, st, g, f, s);
+  RCM_LAUNCH(k_h_prep, grid2(g.jce2 - g.jce1 + 1 + g.gl + g.gr, g.ice2 - g.ice1 + 1 + g.gb + g.gt, b), b, st, g, f, s);
 }
 void launch_h_uv(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   const dim3 b = rcm::col_block();
@@ -621,7 +633,7 @@ void launch_h_tq(const Geom& g, const Fields& f, const StepScalars& s, cudaStrea
 }
 void launch_h_psfilt(const Geom& g, const Fields& f, const StepScalars& s, cudaStream_t st) {
   dim3 b(32, 8);
-  RCM_LAUNCH(k_h_psfilt, grid2(g.jci2 - g.jci1 + 1, g.ici2 - g.ici1 + 1, b), b, st, g, f, s);
+  RCM_LAUNCH(k_h_psfilt, grid2(g.jci2 - g.jci1 + 1 + g.gl + g.gr, g.ici2 - g.ici1 + 1 + g.gb + g.gt, b), b, st, g, f, s);
 }
 void launch_bdyval_ps(const Geom& g, const Fields& f, const int2* rim_c, int nrim_c, double xt, int iboudy, cudaStream_t st) {
   if (nrim_c <= 0) return;

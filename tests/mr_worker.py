@@ -20,6 +20,7 @@ sys.path.insert(0, ROOT)
 from regcm_b200 import capi, synth  # noqa: E402
 
 FIELDS = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PP, capi.F_W)
+HYDRO_FIELDS = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PS)
 MOLOCH_FIELDS = (capi.F_U, capi.F_V, capi.F_W, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PAI, capi.F_PS)
 
 
@@ -41,6 +42,8 @@ def owned_bounds(core, field):
             return (j1, i1, 1), (min(j2, core.jx - 1), min(i2, core.iy - 1), 1)
     if field in (capi.F_U, capi.F_V):
         return (j1, i1, 1), (j2, i2, kz)
+    if field == capi.F_PS:
+        return (j1, i1, 1), (min(j2, core.jx - 1), min(i2, core.iy - 1), 1)
     nk = kz + 1 if field == capi.F_W else kz
     return (j1, i1, 1), (min(j2, core.jx - 1), min(i2, core.iy - 1), nk)
 
@@ -54,6 +57,8 @@ def main():
     ap.add_argument("--cpus-i", type=int, default=0)
     ap.add_argument("--ibdyfrq", type=int, default=6)
     ap.add_argument("--iboudy", type=int, default=-1)
+    ap.add_argument("--idynamic", type=int, default=0, help="override the case's core (1 = hydrostatic)")
+    ap.add_argument("--cfg", action="append", default=[], help="name=value override of an rcm_cfg member")
     ap.add_argument("--work", action="store_true", help="also dump the per-step work arrays")
     ap.add_argument("--sharp-q", action="store_true", help="moisture with sharp fronts (drives the negative-q repair)")
     ap.add_argument("--out", required=True)
@@ -99,7 +104,13 @@ def main():
         dist.broadcast_object_list(box, src=0)
         uid = box[0]
 
-    base = synth.make_case(args.case, records=(), ibdyfrq=args.ibdyfrq)  # cfg only
+    over = {}
+    if args.idynamic:
+        over["idynamic"] = args.idynamic
+    for kv in args.cfg:
+        k, v = kv.split("=")
+        over[k] = float(v) if "." in v else int(v)
+    base = synth.make_case(args.case, records=(), ibdyfrq=args.ibdyfrq, **over)  # cfg only
     cfg = base.cfg
     if args.iboudy >= 0:
         cfg.iboudy = args.iboudy
@@ -109,7 +120,7 @@ def main():
     core = capi.DynCore(lib, cfg)
     core.comm_init(uid)
     win = tile_window(core.tile(), cfg.jx, cfg.iy)
-    case = synth.make_case(args.case, window=win, ibdyfrq=args.ibdyfrq)
+    case = synth.make_case(args.case, window=win, ibdyfrq=args.ibdyfrq, **over)
     case.cfg = cfg
     synth.load_case(core, case, stage_next=True)
     if args.sharp_q:
@@ -121,7 +132,7 @@ def main():
     core.step(args.steps)
     out = {"tile": np.array(core.tile())}
     moloch = cfg.idynamic == 3
-    for fld in (MOLOCH_FIELDS if moloch else FIELDS):
+    for fld in (MOLOCH_FIELDS if moloch else HYDRO_FIELDS if cfg.idynamic == 1 else FIELDS):
         for lev, tag in (((capi.LEVEL_A, "a"),) if moloch else ((capi.LEVEL_A, "a"), (capi.LEVEL_B, "b"))):
             lb, ub = owned_bounds(core, fld)
             out[f"f{fld}{tag}"] = core.get_state(fld, lev, lb=lb, ub=ub)
@@ -150,6 +161,7 @@ def main():
     d = core.diag()
     out["max_cfl"] = np.array(d.max_cfl)
     out["neg_q"] = np.array(d.neg_q_points)
+    out["ptn"] = np.array([d.ptntot, d.pt2tot])
     out["ps_extremes"] = np.array([d.ps_max, d.ps_min])
     np.savez(os.path.join(args.out, f"rank{rank}.npz"), **out)
     core.close()

@@ -50,8 +50,6 @@ def test_create_rejects_bad_config(built):
     assert lib.create(C.byref(bad), C.byref(h)) == -1 and not h
     mol = capi.default_cfg(3, jx=64, iy=34, kz=18, ds=12.0, dt=90.0, mo_nsound=0)
     assert lib.create(C.byref(mol), C.byref(h)) == -1 and not h
-    hyd = capi.default_cfg(1, jx=64, iy=34, kz=18, ds=60.0, dt=150.0, nproc=2)  # the hydrostatic core is single-rank
-    assert lib.create(C.byref(hyd), C.byref(h)) == -1 and not h
     hyd = capi.default_cfg(1, jx=64, iy=34, kz=18, ds=60.0, dt=150.0, nsplit=9)
     assert lib.create(C.byref(hyd), C.byref(h)) == -1 and not h
     # a valid hydrostatic configuration passes the argument checks: without a device the

@@ -79,3 +79,37 @@ def test_moloch_halo_matches_single_gpu(cuda_lib, tmp_path, world, layout, case_
             a, b = glob[f], orc.get_state(f)
             b = b if b.ndim == 3 else b[:, :, None]
             assert float(np.abs(a - b).max()) <= 1e-10 * max(float(np.abs(b).max()), 1e-300), capi.FIELD_NAMES[f]
+
+
+@pytest.mark.parametrize("world,layout,case_name", [(2, (0, 0), "small"), (2, (1, 2), "small"), (4, (2, 2), "C1"), (8, (0, 0), "C3h")])
+def test_hydro_halo_matches_single_gpu(cuda_lib, tmp_path, world, layout, case_name):
+    """Hydrostatic core (idynamic = 1) on a 2-D decomposition: equal to the one-GPU result of the same library
+    (lstand = 1: nothing is summed over ranks, the exchange is exact) and within the single-GPU tolerance of the
+    CPU oracle (tests/test_gpu_hydro.py)."""
+    if ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    from test_multirank_emu import HYDRO_FIELDS, assemble_hydro
+    steps = 6
+    run_ranks(world, tmp_path, ["--case", case_name, "--idynamic", "1", "--steps", str(steps), "--cpus-j", str(layout[0]),
+                                "--cpus-i", str(layout[1])], lib="cuda")
+    case = synth.make_case(case_name, idynamic=1)
+    core = capi.DynCore(cuda_lib, case.cfg)
+    synth.load_case(core, case)
+    core.step(steps)
+    glob, _ = assemble_hydro(tmp_path, world, case.cfg)
+    for f in HYDRO_FIELDS:
+        for lv, tag in ((0, "a"), (1, "b")):
+            a, b = glob[(f, tag)], core.get_state(f, lv)
+            b = b if b.ndim == 3 else b[:, :, None]
+            assert not np.isnan(a).any(), capi.FIELD_NAMES[f]
+            assert float(np.abs(a - b).max()) <= 1e-12 * max(float(np.abs(b).max()), 1e-300), capi.FIELD_NAMES[f] + tag
+    core.close()
+    if case_name != "C3h":
+        from oracle import pyoracle
+        orc = pyoracle.make_oracle(case.cfg)
+        synth.load_case(orc, case)
+        orc.step(steps)
+        for f in HYDRO_FIELDS:
+            a, b = glob[(f, "a")], orc.get_state(f, 0)
+            b = b if b.ndim == 3 else b[:, :, None]
+            assert float(np.abs(a - b).max()) <= 1e-11 * max(float(np.abs(b).max()), 1e-300), capi.FIELD_NAMES[f]

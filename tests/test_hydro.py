@@ -163,7 +163,11 @@ def test_emu_hydro_cloud_water_path(emu_lib):
 
 def test_hydro_rejects_unsupported(emu_lib):
     case = synth.make_case("tiny", idynamic=1)
-    case.cfg.nproc = 2
+    case.cfg.nproc, case.cfg.cpus_j, case.cfg.cpus_i = 2, 3, 1   # layout does not match nproc
+    with pytest.raises(capi.RcmError):
+        capi.DynCore(emu_lib, case.cfg)
+    case = synth.make_case("tiny", idynamic=1)
+    case.cfg.nsplit = 9             # beyond RCM_MAXSPLIT
     with pytest.raises(capi.RcmError):
         capi.DynCore(emu_lib, case.cfg)
     case = synth.make_case("tiny", idynamic=1)

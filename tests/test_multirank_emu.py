@@ -125,6 +125,84 @@ def test_multirank_record_change(emu_lib, tmp_path):
     compare(glob, ref, 1e-11)
 
 
+# ---------------------------------------------------------------------------- hydrostatic core (idynamic = 1)
+HYDRO_FIELDS = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PS)
+
+
+def assemble_hydro(outdir, world, cfg):
+    jx, iy, kz = cfg.jx, cfg.iy, cfg.kz
+    glob, cover, ptn = {}, {}, np.zeros(2)
+    for r in range(world):
+        d = np.load(os.path.join(outdir, f"rank{r}.npz"))
+        ptn += d["ptn"]
+        for fld in HYDRO_FIELDS:
+            lb = d[f"lb{fld}"]
+            for tag in "ab":
+                a = d[f"f{fld}{tag}"]
+                a = a if a.ndim == 3 else a[:, :, None]
+                key = (fld, tag)
+                if key not in glob:
+                    shp = (jx, iy, kz) if fld in (capi.F_U, capi.F_V) else (jx - 1, iy - 1, 1 if fld == capi.F_PS else kz)
+                    glob[key] = np.full(shp, np.nan)
+                    cover[key] = np.zeros(shp[:2], dtype=int)
+                sl = (slice(lb[0] - 1, lb[0] - 1 + a.shape[0]), slice(lb[1] - 1, lb[1] - 1 + a.shape[1]))
+                glob[key][sl[0], sl[1], :] = a
+                cover[key][sl] += 1
+    for key, c in cover.items():
+        assert (c == 1).all(), f"tiles do not partition the domain for {key}"
+    return glob, ptn
+
+
+def single_rank_hydro(emu_lib, case_name, steps, ibdyfrq=6, **kw):
+    case = synth.make_case(case_name, idynamic=1, ibdyfrq=ibdyfrq, **kw)
+    core = capi.DynCore(emu_lib, case.cfg)
+    synth.load_case(core, case)
+    core.step(steps)
+    ref = {}
+    for f in HYDRO_FIELDS:
+        for lv in (0, 1):
+            a = core.get_state(f, lv)
+            ref[(f, "ab"[lv])] = a if a.ndim == 3 else a[:, :, None]
+    d = core.diag()
+    core.close()
+    return case.cfg, ref, np.array([d.ptntot, d.pt2tot])
+
+
+@pytest.mark.parametrize("world,layout,extra", [(2, (0, 0), {}), (2, (1, 2), {}), (4, (2, 2), {}), (3, (3, 1), {}),
+                                                 (4, (2, 2), {"nsplit": 3}), (4, (2, 2), {"iboudy": 4}), (4, (2, 2), {"iboudy": 1})])
+def test_hydro_multirank_matches_single_rank(emu_lib, tmp_path, world, layout, extra):
+    """2-D decomposition of the hydrostatic core (SURVEY §8 a24 for idynamic = 1): psc2psd + exchange, the ghost-ring
+    recomputation of compute_omega / phi / new_pressure, the exchanges of splitf and of every spstep sub-step
+    (Main/mod_split.F90:197-198,276-277,312-313,438,499,527-528,583).  With lstand = 1 (the default) nothing is
+    summed over ranks, so the assembled result equals the single-rank one bit for bit."""
+    steps = 5
+    args = ["--case", "tiny", "--idynamic", "1", "--steps", str(steps), "--cpus-j", str(layout[0]), "--cpus-i", str(layout[1])]
+    for k, v in extra.items():
+        args += ["--cfg", f"{k}={v}"]
+    run_ranks(world, tmp_path, args)
+    cfg, ref, ptn = single_rank_hydro(emu_lib, "tiny", steps, **extra)
+    assert cfg.lstand == 1
+    glob, ptn_mr = assemble_hydro(tmp_path, world, cfg)
+    for key, a in glob.items():
+        assert not np.isnan(a).any(), key
+        np.testing.assert_array_equal(a, ref[key], err_msg=f"{capi.FIELD_NAMES[key[0]]}{key[1]}")
+    # Bleck noise sums: each rank reports its own part (the reference's sumall is left to the caller)
+    np.testing.assert_allclose(ptn_mr, ptn, rtol=1e-12)
+
+
+def test_hydro_multirank_record_change_and_data_means(emu_lib, tmp_path):
+    """lstand = 0 (vertical modes linearised about horizontal means that are summed over the ranks: additions
+    reorder, hence 1e-11) through a boundary-record change (bdyin: psc2psd of the new record + exchange, couple on
+    the ghost rows) on a 2x2 decomposition."""
+    case = synth.make_case("tiny", idynamic=1, records=(), ibdyfrq=1)
+    steps = int(round(3600.0 / case.cfg.dt)) + 3
+    run_ranks(4, tmp_path, ["--case", "tiny", "--idynamic", "1", "--steps", str(steps), "--cpus-j", "2", "--cpus-i", "2",
+                            "--ibdyfrq", "1", "--cfg", "lstand=0"], timeout=1200)
+    cfg, ref, _ = single_rank_hydro(emu_lib, "tiny", steps, ibdyfrq=1, lstand=0)
+    glob, _ = assemble_hydro(tmp_path, 4, cfg)
+    compare(glob, ref, 1e-11)
+
+
 # ---------------------------------------------------------------------------- MOLOCH core (idynamic = 3)
 MOLOCH_FIELDS = (capi.F_U, capi.F_V, capi.F_W, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PAI, capi.F_PS)
 
