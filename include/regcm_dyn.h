@@ -59,8 +59,17 @@ enum rcm_field {
                  * Main/mod_bdycod.F90:394 (`ps*0.1 - ptop`). */
   RCM_F_PAI = 8, /* cross (jx-1,iy-1,kz): Exner function Pi of the MOLOCH core
                   * (mo_atm%pai, Main/mod_atm_interface.F90:575-616); state only */
-  RCM_F_COUNT = 9
+  RCM_F_COUNT = 9,
+  /* Tracers (atm1%chi / atm2%chi, ichem = 1; idynamic 1, 2): tracer n = 0..ntr-1 is field
+   * RCM_F_CHI + n, cross (jx-1,iy-1,kz), p*·chi.  As a boundary field (chib0/chib1, che_init_bdy and chem_bdyin,
+   * Main/chemlib/mod_che_bdyco.F90:118-420) the value passed is the mixing ratio of the CHBC record on model
+   * levels; the library couples it with the boundary p* and forms chibt = (chib1 - chib0)/dtbdys as the reference
+   * does.  The initial tracer state is the first record.  Transport = hadvtr, vadv4d(ind = 2), nudge_chi with the
+   * time-dependent boundary values (ichebdy = 1), diffu_x4d, the negative fix with factor 0.1 and the RAW filter
+   * (Main/mod_tendency.F90:548-586,1393-1411,1502-1511,1539-1543). */
+  RCM_F_CHI = 16
 };
+#define RCM_MAXTR 8
 /* idynamic = 3 (MOLOCH, Arakawa C grid, Main/mod_atm_interface.F90:575-616):
  * the state is single-level and uncoupled: RCM_F_U is mo_atm%u on
  * (jx, iy-1, kz), RCM_F_V is mo_atm%v on (jx-1, iy, kz), RCM_F_W is mo_atm%w on
@@ -211,7 +220,8 @@ typedef struct rcm_cfg {
   int32_t mo_nzfilt;      /* levels of the top sponge in the w solve (3)   */
   int32_t mo_rotllr;      /* 1: iproj = 'ROTLLR' (rotated lat-lon) branches of sound / wafone /
                            * compute_moloch_static (Main/mod_moloch.F90:773,932,1183; Main/mod_params.F90:2766) */
-  int32_t reserved_i[2];
+  int32_t ntr;            /* number of transported tracers, 0..RCM_MAXTR (ichem = 1 with ntr species; 0 = ichem 0) */
+  int32_t reserved_i[1];
   /* &geoparam */
   double ds;    /* grid spacing [km]                                       */
   double ptop;  /* model top pressure [cb]                                 */
@@ -246,6 +256,8 @@ typedef struct rcm_diag {
   /* idynamic = 3: extremes of ps over the interior [Pa], the reference's
    * per-report print (Main/mod_moloch.F90:437-460) */
   double ps_max, ps_min;
+  int64_t neg_chi_points; /* tracer values repaired by the negative fix of Main/mod_tendency.F90:570-582, last step,
+                           * this rank */
 } rcm_diag;
 
 typedef struct rcm_dyn rcm_dyn; /* opaque */

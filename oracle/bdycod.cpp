@@ -376,6 +376,7 @@ void Oracle::bdyval() {
         else a1_qx(j, ice2, k, n) = qxint * psa(j, ice2);
       }
   }
+  if (ntr > 0) bdyval_tracers(xbctime + dt);   // chem_bdyval (Main/mod_bdycod.F90:2558-2564)
   xbctime = xbctime + dtsec;
 }
 

@@ -42,6 +42,7 @@ int orc_diag(void* h, rcm_diag* d) {
   d->lcount = o->lcount; d->xbctime = o->xbctime; d->dt = o->dt;
   d->max_cfl = o->max_cfl_step; d->istep = o->last_istep;
   d->neg_q_points = o->neg_q_points;
+  d->neg_chi_points = o->neg_chi_points;
   d->ptntot = o->ptntot; d->pt2tot = o->pt2tot;
   d->ps_max = o->ps_max; d->ps_min = o->ps_min;
   return RCM_OK;

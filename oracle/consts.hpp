@@ -11,6 +11,7 @@ constexpr double d_zero = 0.0, d_one = 1.0, d_two = 2.0, d_four = 4.0;
 constexpr double d_half = 0.5, d_rfour = 0.25;
 constexpr double d_1000 = 1000.0, d_r1000 = 0.001;
 
+constexpr double mintr = 1.0e-30;    // mod_constants.F90:63 (double precision)
 constexpr double minqq = 1.0e-8;    // mod_constants.F90:57
 constexpr double dlowval = 1.0e-20; // :68
 

@@ -461,6 +461,7 @@ void Oracle::tend_hydro() {
   diffu_d(udyn, vdyn, ubd3d, vbd3d);
   diffu_x3d(tdyn, tb3d);
   diffu_x4d(qxdyn, qxb3d, 1, nqx, d_one);
+  tracer_tendency();   // ichem = 1 (oracle/tracers.cpp)
   // tendency sums (:285-294,331-335)
   for (int k = 1; k <= kz; ++k)
     for (int i = ici1; i <= ici2; ++i)

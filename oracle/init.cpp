@@ -348,6 +348,7 @@ int Oracle::init() {
   if (hydro) {
     init_bdy_hydro();
     init_state_hydro();
+    init_bdy_tracers(); init_state_tracers();
     initialize_diffusion();
     spinit();   // Main/mod_regcm_interface.F90:141
     if (vm_numerr) { err = "vmodes: vertical mode problem reported errors"; return RCM_ERR_ARG; }
@@ -358,6 +359,7 @@ int Oracle::init() {
   compute_full_coriolis_coefficients();
   init_bdy();
   init_state();
+  init_bdy_tracers(); init_state_tracers();
   initialize_diffusion();
   init_sound();
   bdyval();   // Main/mod_regcm_interface.F90:146
@@ -395,6 +397,7 @@ int Oracle::step(int n) {
     if (alarm_bdy_act()) {
       if (!have_next) { err = "boundary record needed but not staged"; return RCM_ERR_BDY; }
       if (hydro) bdyin_hydro(); else bdyin();
+      if (ntr > 0) bdyin_tracers();
     }
     bdyval();
   }
@@ -419,6 +422,7 @@ static void copy_out_4d(const A4& src, int n, double* a, const int32_t lb[3], co
 
 int Oracle::get_state(int field, int level, double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (moloch) return mo_get_state(field, a, lb, ub);
+  if (field >= RCM_F_CHI) return tracer_state(field - RCM_F_CHI, level, a, lb, ub, false);
   const bool A = (level == RCM_LEVEL_A);
   switch (field) {
     case RCM_F_U: copy_out_3d(A ? a1_u : a2_u, a, lb, ub); return RCM_OK;

@@ -10,6 +10,7 @@
 #pragma once
 #include <cstdint>
 #include <string>
+#include <vector>
 
 #include "../include/regcm_dyn.h"
 #include "arr.hpp"
@@ -154,6 +155,21 @@ struct Oracle {
   inline double phy4(int j, int i, int k, int n) const { return phys_on ? qxphy(j, i, k, n) : d_zero; }
 
   // ---- hydrostatic core (idynamic = 1; oracle/hydro.cpp, oracle/split.cpp) ----
+  // ---- tracers (oracle/tracers.cpp) ----
+  int ntr = 0;
+  std::vector<A3> chia, chib, chic, chix, chib3d, chidyn, chiten, nx_chi;   // atm1%chi, atm2%chi, atmc%chi, atmx%chi, ...
+  std::vector<V3dBound> xchib;                                               // chib0, chib1, chibt (coupled)
+  A2 cefc, cegc;                                                             // setup_che_bdycon
+  int64_t neg_chi_points = 0;
+  void allocate_tracers();
+  void init_bdy_tracers();
+  void init_state_tracers();
+  void bdyin_tracers();
+  void bdyval_tracers(double xt);
+  void tracer_tendency();
+  int tracer_state(int n, int level, double* a, const int32_t lb[3], const int32_t ub[3], bool in);
+  int tracer_bdy(int n, int slot, const double* a, const int32_t lb[3], const int32_t ub[3]);
+
   bool hydro = false;
   A2 pten, pten_raw, rpsc, ptn2d, pt22d;          // mod_tendency.F90:63-66
   A3 phi, td, tvfac, pf3d, pb3d;        // mod_tendency.F90:57-62, atms%pf3d/pb3d

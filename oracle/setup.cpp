@@ -31,6 +31,7 @@ int Oracle::create(const rcm_cfg& c) {
   // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)
   if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 4 || c.iboudy == 5 || (c.idynamic != 3 && (c.iboudy == 2 || c.iboudy == 3)))) { err = "oracle: iboudy must be 0..5 (2, 3: idynamic 1, 2 only)"; return RCM_ERR_ARG; }
   if (c.nqx != 2) { err = "oracle: nqx must be 2"; return RCM_ERR_ARG; }
+  if (c.ntr < 0 || c.ntr > RCM_MAXTR || (c.ntr > 0 && c.idynamic == 3)) { err = "oracle: ntr must be 0..8 (idynamic 1, 2)"; return RCM_ERR_ARG; }
   jx = c.jx; iy = c.iy; kz = c.kz; kzp1 = kz + 1; nqx = c.nqx;
   iqv = 1; iqc = 2; iqfrst = 2; iqlst = nqx;
   ptop = c.ptop;
@@ -49,6 +50,7 @@ int Oracle::create(const rcm_cfg& c) {
   if (moloch) return create_moloch();
   allocate_all();
   if (hydro) allocate_hydro();
+  allocate_tracers();
   setup_boundaries(false, false, ba_cr);   // mod_params.F90:1788-1793
   setup_boundaries(true, true, ba_dt);
   return RCM_OK;
@@ -273,6 +275,7 @@ int Oracle::set_static(int id, const double* a, const int32_t lb[3], const int32
 }
 
 int Oracle::set_bdy(int field, int slot, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (field >= RCM_F_CHI) { if (slot == RCM_BDY_NEXT) have_next = true; return tracer_bdy(field - RCM_F_CHI, slot, a, lb, ub); }
   if (field == RCM_F_PS) {
     if (!hydro && !moloch) { err = "ps boundary data exist for idynamic = 1 and 3 only"; return RCM_ERR_ARG; }
     if (slot == RCM_BDY_B0) return copy_in_2d(xpsb.b0, a, lb, ub);
@@ -300,6 +303,7 @@ int Oracle::set_bdy(int field, int slot, const double* a, const int32_t lb[3], c
 // state import (tests only): the coupled atm1/atm2 fields
 int Oracle::set_state(int field, int level, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (moloch) return mo_set_state(field, a, lb, ub);
+  if (field >= RCM_F_CHI) return tracer_state(field - RCM_F_CHI, level, const_cast<double*>(a), lb, ub, true);
   const bool A = (level == RCM_LEVEL_A);
   auto in4 = [&](A4& dst, int n) {
     const int n1 = ub[0] - lb[0] + 1, n2 = ub[1] - lb[1] + 1;

@@ -38,7 +38,9 @@ int orc_array(void* h, const char* name, double** data, int32_t lb[4], int32_t n
   T3(uten) T3(vten) T3(ppten) T3(wten) T3(udyn) T3(vdyn) T3(qdot) T3(cr)
   T2(s_estore) T2(s_astore) T2(s_wpval) T2(tmask)
   T3(m_u) T3(m_v) T3(m_w) T3(m_s) T3(m_fmz) T3(m_fmzf) T3(m_tetav) T3(m_pai) T3(m_t) T4(m_qx) T3(m_ux) T3(m_vx) T3(m_wx)
-  T2(mx2) T2(rmu) T2(rmv) T2(msfu) T2(msfv)
+  T2(mx2) T2(rmu) T2(rmv) T2(msfu) T2(msfv) T3(xkc)
+  if (s == "chia0" && o->ntr > 0) v3(v, o->chia[0]); else if (s == "chib0" && o->ntr > 0) v3(v, o->chib[0]); else
+  if (s == "chic0" && o->ntr > 0) v3(v, o->chic[0]); else
   return RCM_ERR_ARG;
 #undef T1
 #undef T2

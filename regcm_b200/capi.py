@@ -18,6 +18,8 @@ import numpy as np
 
 # enum rcm_field / rcm_static / rcm_work (include/regcm_dyn.h)
 F_U, F_V, F_T, F_QV, F_QC, F_PP, F_W, F_PS, F_PAI = range(9)
+F_CHI = 16       # tracer n is field F_CHI + n
+MAXTR = 8
 FIELD_NAMES = ("u", "v", "t", "qv", "qc", "pp", "w", "ps", "pai")
 S_HT, S_MSFX, S_MSFD, S_CORIOL, S_XLAT, S_XLON, S_DLAT, S_SIGMA, S_MSFU, S_MSFV, S_ULAT, S_VLAT = range(12)
 LEVEL_A, LEVEL_B = 0, 1
@@ -53,7 +55,8 @@ class RcmCfg(C.Structure):
         ("device", C.c_int32),
         ("nsplit", C.c_int32), ("lstand", C.c_int32),
         ("mo_nadv", C.c_int32), ("mo_nsound", C.c_int32), ("mo_nzfilt", C.c_int32), ("mo_rotllr", C.c_int32),
-        ("reserved_i", C.c_int32 * 2),
+        ("ntr", C.c_int32),
+        ("reserved_i", C.c_int32 * 1),
         ("ds", C.c_double), ("ptop", C.c_double),
         ("dt", C.c_double),
         ("gnu1", C.c_double), ("gnu2", C.c_double), ("ckh", C.c_double), ("adyndif", C.c_double),
@@ -74,6 +77,7 @@ class RcmDiag(C.Structure):
         ("neg_q_points", C.c_int64),
         ("ptntot", C.c_double), ("pt2tot", C.c_double),
         ("ps_max", C.c_double), ("ps_min", C.c_double),
+        ("neg_chi_points", C.c_int64),
     ]
 
 

@@ -11,6 +11,7 @@
 
 namespace rcm {
 constexpr double minqq = 1.0e-8;      // mod_constants.F90:57
+constexpr double mintr = 1.0e-30;     // mod_constants.F90:63 (double precision)
 constexpr double dlowval = 1.0e-20;   // :68
 constexpr double egrav = 9.80665;     // :85
 constexpr double boltzk = 1.3806504e-23;

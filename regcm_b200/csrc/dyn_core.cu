@@ -48,6 +48,10 @@ void launch_negq_repair(const Geom&, const Fields&, const StepScalars&, cudaStre
 void launch_slice(const Geom&, const Fields&, int id, int hydro, double ptop, double p0, double tlp, double ts0, double dx8, double* out, cudaStream_t);
 void launch_window_strided(bool pack, double* buf, double* p_shifted, int j0, int i0, int k0, int n1, int n2, int nk, long long b1, long long b2, int si, long long sk, cudaStream_t st);
 void launch_window(bool pack, double* buf, double* p_shifted, int j0, int i0, int k0, int n1, int n2, int nk, int si, long long sk, cudaStream_t st);
+void launch_tr(const Geom&, const Fields&, const TrFields&, const StepScalars&, cudaStream_t);
+void launch_tr_repair(const Geom&, const TrFields&, const StepScalars&, cudaStream_t);
+void launch_tr_bdyval(const Geom&, const TrFields&, const int2*, int, double, int, int, cudaStream_t);
+void launch_tr_timeint(const Geom&, const double*, const double*, double*, double, int, int, int, int, int, cudaStream_t);
 void launch_couple(const Geom&, double*, const double*, int, int, int, int, int, cudaStream_t);
 void launch_timeint(const Geom&, const double*, const double*, double*, double, int, int, int, int, int, cudaStream_t);
 void launch_bdyval(const Geom&, const Fields&, const double*, const double*, const double*, const int2*, int,
@@ -81,11 +85,11 @@ void launch_sp_corr(const Geom&, const Fields&, const StepScalars&, cudaStream_t
 // rcm_dyn_profile(); used by bench.py for the per-kernel roofline
 enum { KID_PREP, KID_XKC, KID_UV, KID_TQ, KID_PPW, KID_SND_INIT, KID_SND_UV, KID_SND_WFWD, KID_SND_WPVAL, KID_SND_WBACK,
        KID_SND_FINAL, KID_BDY, KID_HALO, KID_H_PS, KID_H_PREP, KID_H_UV, KID_H_TQ, KID_SP_PROJ, KID_SP_STEP, KID_SP_CORR,
-       KID_MO_PRE, KID_MO_DIV, KID_MO_W, KID_MO_UV, KID_MO_STAG, KID_MO_WAF, KID_NEGQ, KID_COUNT };
+       KID_MO_PRE, KID_MO_DIV, KID_MO_W, KID_MO_UV, KID_MO_STAG, KID_MO_WAF, KID_NEGQ, KID_TR, KID_COUNT };
 static const char* const kKernelNames[KID_COUNT] = {"k_prep", "k_xkc", "k_uv", "k_tq", "k_ppw", "k_snd_init", "k_snd_uv",
                                                     "k_snd_wfwd", "k_snd_wpval", "k_snd_wback", "k_snd_final", "k_bdy", "halo",
                                                     "k_h_ps", "k_h_prep", "k_h_uv", "k_h_tq", "k_sp_proj", "k_sp_step", "k_sp_corr",
-                                                    "k_mo_pre", "k_mo_div", "k_mo_w", "k_mo_uv", "k_mo_stag", "k_mo_waf", "k_negq"};
+                                                    "k_mo_pre", "k_mo_div", "k_mo_w", "k_mo_uv", "k_mo_stag", "k_mo_waf", "k_negq", "k_tr"};
 struct ProfRec { int kid; cudaEvent_t a, b; };
 
 struct rcm_dyn {
@@ -116,6 +120,11 @@ struct rcm_dyn {
   std::vector<void*> allocs;
   double* b1[6] = {nullptr};   // boundary record b1 per bdy field (u v t qv pp w)
   double* nx[6] = {nullptr};   // staged next record (decoupled)
+  // tracers
+  TrFields tr{};
+  double* tr_b1[RCM_MAXTR] = {nullptr};   // chib1
+  double* tr_nx[RCM_MAXTR] = {nullptr};   // staged next record (mixing ratio)
+  int64_t neg_chi = 0;
   double* psdot_bdy = nullptr; // bdycon psdot = atm0%psdot*1e-3 (Main/mod_bdycod.F90:425-431)
   double* xpsb = nullptr;      // xpsb%b0 = atm0%ps*1e-3
   // hydrostatic core
@@ -171,8 +180,9 @@ struct rcm_dyn {
   int64_t vdone = -1;                     // newest slot known to be complete
   // asynchronous state export (rcm_dyn_get_state_async): device snapshots + D2H on a private stream
   cudaStream_t st_out = nullptr;
-  double* snap[2 * RCM_F_COUNT] = {nullptr};
-  cudaEvent_t ev_snap[2 * RCM_F_COUNT] = {nullptr}, ev_out[2 * RCM_F_COUNT] = {nullptr};
+  enum { kSnap = 2 * (RCM_F_CHI + RCM_MAXTR) };
+  double* snap[kSnap] = {nullptr};
+  cudaEvent_t ev_snap[kSnap] = {nullptr}, ev_out[kSnap] = {nullptr};
   bool out_pending = false;
   // physics coupling boundary: rcm_dyn_step_pre_physics ran the head of `tend` and the tail is owed
   bool mid_step = false, head_only = false;
@@ -315,6 +325,7 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 4 || c.iboudy == 5 || (c.idynamic != 3 && (c.iboudy == 2 || c.iboudy == 3))))
     return bail(RCM_ERR_ARG, "iboudy must be 0, 1, 4 or 5 (idynamic 1, 2: also 2, 3)");
   if (c.nqx != 2) return bail(RCM_ERR_ARG, "nqx must be 2 (qv,qc)");
+  if (c.ntr < 0 || c.ntr > RCM_MAXTR || (c.ntr > 0 && c.idynamic == 3)) return bail(RCM_ERR_ARG, "ntr must be 0..8 (tracers: idynamic 1, 2)");
   if (c.jx < 2 * c.nspgx || c.iy < 2 * c.nspgx || c.kz < 3) return bail(RCM_ERR_ARG, "domain too small for the relaxation zone");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return bail(RCM_ERR_CUDA, "no CUDA device (this library has no CPU fallback)");
@@ -456,6 +467,18 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   f.nq_list = dev_alloc_raw<int>(h, (size_t)2 * g.kz * (size_t)g.sk);
   f.nq_cnt = dev_alloc_raw<int>(h, (size_t)2 * g.kz);
   ok = ok && f.hefc && f.hegc && f.hefd && f.hegd && f.tmask && f.cflbits && f.negq && f.nanflag && f.nq_list && f.nq_cnt;
+  if (c.ntr > 0) {   // tracers
+    TrFields& tr = h->tr;
+    tr.ntr = c.ntr;
+    for (int n = 0; n < c.ntr; ++n)
+      for (double** p : {&tr.a[n], &tr.b[n], &tr.na[n], &tr.nb[n], &tr.c[n], &tr.b0[n], &tr.bt[n], &h->tr_b1[n], &h->tr_nx[n]}) A3(*p);
+    tr.cefc = dev_alloc_raw<double>(h, (size_t)c.nspgx * g.kz + 1); tr.cegc = dev_alloc_raw<double>(h, (size_t)c.nspgx * g.kz + 1);
+    int* z = dev_alloc_raw<int>(h, (size_t)g.sk); tr.ztype = z ? z + h->off2 : nullptr;
+    tr.nq_list = dev_alloc_raw<int>(h, (size_t)c.ntr * g.kz * (size_t)g.sk);
+    tr.nq_cnt = dev_alloc_raw<int>(h, (size_t)c.ntr * g.kz);
+    tr.negcnt = dev_alloc_raw<unsigned long long>(h, 1);
+    ok = ok && tr.cefc && tr.cegc && z && tr.nq_list && tr.nq_cnt && tr.negcnt;
+  }
   if (!ok) {
     for (void* p : h->allocs) cudaFree(p);
     return bail(RCM_ERR_CUDA, "device memory allocation failed");
@@ -606,6 +629,15 @@ extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a,
     int32_t l3[3] = {lb[0], lb[1], 1}, u3[3] = {ub[0], ub[1], 1};
     return upload3(h, dst2 - h->g.sk, a, l3, u3, 1);
   }
+  if (field >= RCM_F_CHI) {   // tracer record (mixing ratio; coupled at init / bdyin)
+    const int n = field - RCM_F_CHI;
+    if (n >= h->tr.ntr) return fail(h, RCM_ERR_ARG, "no such tracer");
+    cudaSetDevice(h->device);
+    double* dstc = slot == RCM_BDY_B0 ? h->tr.b0[n] : slot == RCM_BDY_B1 ? h->tr_b1[n] : slot == RCM_BDY_NEXT ? h->tr_nx[n] : nullptr;
+    if (!dstc) return fail(h, RCM_ERR_ARG, "bad slot");
+    if (slot == RCM_BDY_NEXT) h->have_next = true;
+    return upload3(h, dstc, a, lb, ub, h->g.kz);
+  }
   const int q = bdy_index(field);
   if (q < 0 || (h->moloch && q > 3)) return fail(h, RCM_ERR_ARG, "no boundary data for this field");
   cudaSetDevice(h->device);
@@ -623,11 +655,12 @@ extern "C" int rcm_dyn_set_bdy(rcm_dyn* h, int field, int slot, const double* a,
 extern "C" int rcm_dyn_stage_bdy_async(rcm_dyn* h, int field, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
   const bool is_ps = (field == RCM_F_PS && (h->hydro || h->moloch));
-  const int q = is_ps ? 0 : bdy_index(field);
+  const bool is_tr = (field >= RCM_F_CHI && field - RCM_F_CHI < h->tr.ntr);
+  const int q = (is_ps || is_tr) ? 0 : bdy_index(field);
   if (q < 0 || (h->moloch && q > 3)) return fail(h, RCM_ERR_ARG, "no boundary data for this field");
   cudaSetDevice(h->device);
   const int nk = is_ps ? 1 : ((field == RCM_F_W) ? h->g.kzp1 : h->g.kz);
-  double* const dst_async = is_ps ? h->xps_nx - h->g.sk : h->nx[q];
+  double* const dst_async = is_ps ? h->xps_nx - h->g.sk : is_tr ? h->tr_nx[field - RCM_F_CHI] : h->nx[q];
   int32_t lb3[3] = {lb[0], lb[1], is_ps ? 1 : lb[2]}, ub3[3] = {ub[0], ub[1], is_ps ? 1 : ub[2]};
   lb = lb3; ub = ub3;
 #ifndef RCM_EMU
@@ -700,10 +733,11 @@ static int up1(rcm_dyn* h, double* dev, const std::vector<double>& v) {
 }
 
 // relaxation-zone distance index (setup_boundaries, Main/mod_atm_interface.F90:383-542)
-static void build_zone(rcm_dyn* h, bool dot, std::vector<int>& z) {
+static void build_zone(rcm_dyn* h, bool dot, std::vector<int>& z, std::vector<int>* we = nullptr) {
   const Geom& g = h->g;
   const rcm_cfg& c = h->cfg;
   z.assign((size_t)g.sk, 0);
+  if (we) we->assign((size_t)g.sk, 0);   // 1 where the point belongs to the west / east zone
   const int jx = g.jx, iy = g.iy;
   const int icx = dot ? 0 : 1, icy = dot ? 0 : 1;
   const int nsp = dot ? c.nspgd : c.nspgx;
@@ -714,16 +748,17 @@ static void build_zone(rcm_dyn* h, bool dot, std::vector<int>& z) {
   // indices only, on its ghost rows (k_h_prep relaxes the p* tendency on the first ghost ring)
   for (int i = std::max(1, g.ide1 - RCM_HALO); i <= std::min(iy, g.ide2 + RCM_HALO); ++i)
     for (int j = std::max(1, g.jde1 - RCM_HALO); j <= std::min(jx, g.jde2 + RCM_HALO); ++j) {
-      int v = 0;
+      int v = 0, t = 0;
       if (i >= igbb1 && i <= igbb2 && j >= jgbl1 && j <= jgbr2 && !(j <= jgbl2 && i >= j) && !(j >= jgbr1 && i >= (jgbr2 - j + 2)))
         v = i - igbb1 + 2;  // south
       if (i >= igbt1 && i <= igbt2 && j >= jgbl1 && j <= jgbr2 && !(j <= jgbl2 && (igbt2 - i + 2) >= j) && !(j >= jgbr1 && (igbt2 - i) >= (jgbr2 - j)))
         v = igbt2 - i + 2;  // north
       if (i >= igbb1 && i <= igbt2 && j >= jgbl1 && j <= jgbl2 && !(i < igbb2 && j > i) && !(i > igbt1 && j > (igbt2 - i + 2)))
-        v = j - jgbl1 + 2;  // west
+        { v = j - jgbl1 + 2; t = 1; }  // west
       if (i >= igbb1 && i <= igbt2 && j >= jgbr1 && j <= jgbr2 && !(i < igbb2 && (jgbr2 - j + 2) > i) && !(i > igbt1 && (jgbr2 - j) > (igbt2 - i)))
-        v = jgbr2 - j + 2;  // east
+        { v = jgbr2 - j + 2; t = 1; }  // east
       z[h->off2 + j + (long long)i * g.si] = v;
+      if (we) (*we)[h->off2 + j + (long long)i * g.si] = t;
     }
 }
 
@@ -738,6 +773,14 @@ static double tau_fn(const rcm_cfg& c, double z, double zmax) {  // Main/mod_bdy
 static int bdyval(rcm_dyn* h, const double* oat, const double* oaqv, const double* oaqc);
 static int init_hydro(rcm_dyn* h);
 
+// tracers ride along in the exchanges of the moisture species (Main/mod_tendency.F90:570,873-874,1085-1090)
+static void tr_add(rcm_dyn* h, std::vector<HaloField>& fl, bool state) {
+  const TrFields& tr = h->tr;
+  for (int n = 0; n < tr.ntr; ++n) {
+    if (state) { fl.push_back({tr.a[n], h->g.kz, 0}); fl.push_back({tr.b[n], h->g.kz, 0}); }
+    else fl.push_back({tr.c[n], h->g.kz, 0});
+  }
+}
 // exchange call sites (the reference's are listed in SURVEY.md §2.4)
 static int exch_sound_pp(rcm_dyn* h) {  // atmc%t, atmc%pp  (Main/mod_sound.F90:265-266)
   if (h->cfg.nproc <= 1) return RCM_OK;
@@ -752,7 +795,9 @@ static int exch_uvten(rcm_dyn* h) {
   if (h->cfg.nproc <= 1) return RCM_OK;
   const int kz = h->g.kz;
   // + the unfiltered moisture forecast atmc%qx for the negative-value repair (Main/mod_tendency.F90:381)
-  if (h->halo.exchange({{h->f.cppd, kz, 0}, {h->f.ct, kz, 0}, {h->f.uten, kz, 1}, {h->f.vten, kz, 1}, {h->f.cqv, kz, 0}, {h->f.cqc, kz, 0}}, 1, h->st))
+  std::vector<HaloField> fl = {{h->f.cppd, kz, 0}, {h->f.ct, kz, 0}, {h->f.uten, kz, 1}, {h->f.vten, kz, 1}, {h->f.cqv, kz, 0}, {h->f.cqc, kz, 0}};
+  tr_add(h, fl, false);
+  if (h->halo.exchange(fl, 1, h->st))
     return fail(h, RCM_ERR_NCCL, "halo exchange (uten, pp, qx forecast) failed");
   return RCM_OK;
 }
@@ -760,9 +805,10 @@ static int exch_state(rcm_dyn* h) {  // atm1/atm2 all prognostics, width 2 (Main
   if (h->cfg.nproc <= 1) return RCM_OK;
   const int kz = h->g.kz, kzp1 = h->g.kzp1;
   Fields& f = h->f;
-  if (h->halo.exchange({{f.au, kz, 1}, {f.av, kz, 1}, {f.at, kz, 0}, {f.aqv, kz, 0}, {f.aqc, kz, 0}, {f.app, kz, 0}, {f.aw, kzp1, 0},
-                        {f.bu, kz, 1}, {f.bv, kz, 1}, {f.bt, kz, 0}, {f.bqv, kz, 0}, {f.bqc, kz, 0}, {f.bpp, kz, 0}, {f.bw, kzp1, 0}},
-                       RCM_HALO, h->st))
+  std::vector<HaloField> fl = {{f.au, kz, 1}, {f.av, kz, 1}, {f.at, kz, 0}, {f.aqv, kz, 0}, {f.aqc, kz, 0}, {f.app, kz, 0}, {f.aw, kzp1, 0},
+                               {f.bu, kz, 1}, {f.bv, kz, 1}, {f.bt, kz, 0}, {f.bqv, kz, 0}, {f.bqc, kz, 0}, {f.bpp, kz, 0}, {f.bw, kzp1, 0}};
+  tr_add(h, fl, true);
+  if (h->halo.exchange(fl, RCM_HALO, h->st))
     return fail(h, RCM_ERR_NCCL, "halo exchange (state) failed");
   return RCM_OK;
 }
@@ -778,7 +824,9 @@ static int exch_h_psdot(rcm_dyn* h) {   // dot-point p* tables of both time leve
 static int exch_h_new(rcm_dyn* h) {   // forecast and filtered winds for splitf's divergences + the moisture forecast for the repair
   if (h->cfg.nproc <= 1) return RCM_OK;
   const int kz = h->g.kz; Fields& f = h->f;
-  if (h->halo.exchange({{f.nau, kz, 1}, {f.nav, kz, 1}, {f.nbu, kz, 1}, {f.nbv, kz, 1}, {f.cqv, kz, 0}, {f.cqc, kz, 0}}, 1, h->st))
+  std::vector<HaloField> fl = {{f.nau, kz, 1}, {f.nav, kz, 1}, {f.nbu, kz, 1}, {f.nbv, kz, 1}, {f.cqv, kz, 0}, {f.cqc, kz, 0}};
+  tr_add(h, fl, false);
+  if (h->halo.exchange(fl, 1, h->st))
     return fail(h, RCM_ERR_NCCL, "halo exchange (new winds, qx forecast) failed");
   return RCM_OK;
 }
@@ -791,15 +839,82 @@ static int exch_h_state(rcm_dyn* h) {   // atm1/atm2 prognostics and p* of both 
   if (h->cfg.nproc <= 1) return RCM_OK;
   const Geom& g = h->g; Fields& f = h->f;
   const int kz = g.kz;
-  if (h->halo.exchange({{f.au, kz, 1}, {f.av, kz, 1}, {f.at, kz, 0}, {f.aqv, kz, 0}, {f.aqc, kz, 0}, {f.psa - g.sk, 1, 0},
-                        {f.bu, kz, 1}, {f.bv, kz, 1}, {f.bt, kz, 0}, {f.bqv, kz, 0}, {f.bqc, kz, 0}, {f.psb - g.sk, 1, 0}},
-                       RCM_HALO, h->st))
+  std::vector<HaloField> fl = {{f.au, kz, 1}, {f.av, kz, 1}, {f.at, kz, 0}, {f.aqv, kz, 0}, {f.aqc, kz, 0}, {f.psa - g.sk, 1, 0},
+                               {f.bu, kz, 1}, {f.bv, kz, 1}, {f.bt, kz, 0}, {f.bqv, kz, 0}, {f.bqc, kz, 0}, {f.psb - g.sk, 1, 0}};
+  tr_add(h, fl, true);
+  if (h->halo.exchange(fl, RCM_HALO, h->st))
     return fail(h, RCM_ERR_NCCL, "halo exchange (state) failed");
   return RCM_OK;
 }
 static int exch_estore(rcm_dyn* h) {
   if (h->cfg.nproc <= 1) return RCM_OK;
   if (h->halo.exchange_estore(h->f, h->st)) return fail(h, RCM_ERR_NCCL, "halo exchange (estore) failed");
+  return RCM_OK;
+}
+
+// ---- tracers: tables, boundary records, initial state; called by rcm_dyn_init before the first bdyval ----
+static void tr_extents(rcm_dyn* h, int& jclo, int& jchi, int& iclo, int& ichi) {
+  const Geom& g = h->g;
+  jclo = std::max(1, g.jde1 - RCM_HALO); jchi = std::min(g.jx - 1, g.jde2 + RCM_HALO);
+  iclo = std::max(1, g.ide1 - RCM_HALO); ichi = std::min(g.iy - 1, g.ide2 + RCM_HALO);
+}
+static int init_tracers(rcm_dyn* h) {
+  TrFields& tr = h->tr;
+  if (tr.ntr <= 0) return RCM_OK;
+  const Geom& g = h->g;
+  const rcm_cfg& c = h->cfg;
+  const int kz = g.kz;
+  // setup_che_bdycon (Main/chemlib/mod_che_bdyco.F90:1177-1217): exponential profile, dt2 = 2*dtsec
+  {
+    const double chdt2 = 2.0 * h->dtsec;
+    const double fn = (c.bdy_nm > 0.0) ? c.bdy_nm : 0.1 / chdt2;
+    const double gn = (c.bdy_dm > 0.0) ? c.bdy_dm : 1.0 / (50.0 * chdt2);
+    std::vector<double> ef((size_t)c.nspgx * kz + 1, 0.0), eg((size_t)c.nspgx * kz + 1, 0.0);
+    for (int k = 1; k <= kz; ++k) {
+      const double hs = (h->h_sigma[k + 1] + h->h_sigma[k]) * 0.5;
+      const double an = hs < 0.4 ? c.high_nudge : (hs < 0.8 ? c.medium_nudge : c.low_nudge);
+      for (int n = 2; n <= c.nspgx - 1; ++n) {
+        const double xfune = std::exp(-(double)(n - 2) / an);
+        ef[(size_t)n + (size_t)c.nspgx * (k - 1)] = fn * xfune; eg[(size_t)n + (size_t)c.nspgx * (k - 1)] = gn * xfune;
+      }
+    }
+    CUDA_OK(cudaMemcpy((void*)tr.cefc, ef.data(), ef.size() * sizeof(double), cudaMemcpyHostToDevice));
+    CUDA_OK(cudaMemcpy((void*)tr.cegc, eg.data(), eg.size() * sizeof(double), cudaMemcpyHostToDevice));
+    std::vector<int> z, we;
+    build_zone(h, false, z, &we);
+    CUDA_OK(cudaMemcpy((void*)(tr.ztype - h->off2), we.data(), we.size() * sizeof(int), cudaMemcpyHostToDevice));
+  }
+  // che_init_bdy (:257-290): couple with xpsb%b0 / xpsb%b1, chibt = (chib1 - chib0)/dtbdys
+  int jclo, jchi, iclo, ichi;
+  tr_extents(h, jclo, jchi, iclo, ichi);
+  const double* p0 = h->hydro ? h->f.xpsb0 : h->xpsb;
+  const double* p1 = h->hydro ? h->xps_b1 : h->xpsb;
+  const size_t nb = (size_t)g.sk * g.kzp1 * sizeof(double);
+  for (int n = 0; n < tr.ntr; ++n) {
+    launch_couple(g, tr.b0[n], p0, kz, jclo, jchi, iclo, ichi, h->st);
+    launch_couple(g, h->tr_b1[n], p1, kz, jclo, jchi, iclo, ichi, h->st);
+    launch_tr_timeint(g, h->tr_b1[n], tr.b0[n], tr.bt[n], h->dtbdys, kz, jclo, jchi, iclo, ichi, h->st);
+    CUDA_OK(cudaMemcpyAsync(tr.a[n] - h->off3, tr.b0[n] - h->off3, nb, cudaMemcpyDeviceToDevice, h->st));
+    CUDA_OK(cudaMemcpyAsync(tr.b[n] - h->off3, tr.b0[n] - h->off3, nb, cudaMemcpyDeviceToDevice, h->st));
+    h->launches += 3;
+  }
+  return RCM_OK;
+}
+// chem_bdyin (Main/chemlib/mod_che_bdyco.F90:326-413), after the meteorological bdyin
+static int bdyin_tracers(rcm_dyn* h) {
+  TrFields& tr = h->tr;
+  if (tr.ntr <= 0) return RCM_OK;
+  const Geom& g = h->g;
+  int jclo, jchi, iclo, ichi;
+  tr_extents(h, jclo, jchi, iclo, ichi);
+  const double* p1 = h->hydro ? h->xps_b1 : h->xpsb;
+  for (int n = 0; n < tr.ntr; ++n) {
+    std::swap(tr.b0[n], h->tr_b1[n]);
+    std::swap(h->tr_b1[n], h->tr_nx[n]);
+    launch_couple(g, h->tr_b1[n], p1, g.kz, jclo, jchi, iclo, ichi, h->st);
+    launch_tr_timeint(g, h->tr_b1[n], tr.b0[n], tr.bt[n], h->dtbdys, g.kz, jclo, jchi, iclo, ichi, h->st);
+    h->launches += 2;
+  }
   return RCM_OK;
 }
 
@@ -1153,6 +1268,7 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
   h->lcount = 0; h->model_time = 0;
   h->day_lastact = 0; h->day_now = 0; h->bdy_lastact = 0; h->bdy_now = 0;
   h->inited = true;
+  if ((rc = init_tracers(h))) return rc;
   // first bdyval (Main/mod_regcm_interface.F90:146)
   if ((rc = bdyval(h, f.at, f.aqv, f.aqc))) return rc;
   CUDA_OK(cudaStreamSynchronize(h->st));
@@ -1296,6 +1412,7 @@ static int init_hydro(rcm_dyn* h) {
     h->launches += 1;
   }
   h->inited = true;
+  if ((rc = init_tracers(h))) return rc;
   // first bdyval (Main/mod_regcm_interface.F90:146)
   if ((rc = bdyval(h, f.at, f.aqv, f.aqc))) return rc;
   CUDA_OK(cudaStreamSynchronize(h->st));
@@ -1308,6 +1425,8 @@ static int bdyval(rcm_dyn* h, const double* oat, const double* oaqv, const doubl
   if (h->hydro) TIMED(KID_BDY, 1, launch_bdyval_ps(h->g, h->f, h->rim_c, h->nrim_c, xt, h->cfg.iboudy, h->st));
   TIMED(KID_BDY, 2, launch_bdyval(h->g, h->f, oat, oaqv, oaqc, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, xt,
                                   h->lcount > 0 ? 1 : 0, h->cfg.iboudy, h->st));
+  if (h->tr.ntr > 0)   // chem_bdyval (Main/mod_bdycod.F90:2558-2564)
+    TIMED(KID_BDY, 1, launch_tr_bdyval(h->g, h->tr, h->rim_c, h->nrim_c, xt, h->lcount > 0 ? 1 : 0, h->lcount > 0 ? 1 : 0, h->st));
   h->xbctime = h->xbctime + h->dtsec;
   return RCM_OK;
 }
@@ -1436,6 +1555,10 @@ static int tend_hydro(rcm_dyn* h) {
   StepScalars s2 = s; s2.cq_mode = 1;   // second pass of k_h_tq: exits at once unless the first one found negative moisture
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.nq_cnt, 0, (size_t)2 * g.kz * sizeof(int), h->st));
+  if (h->tr.ntr > 0) {
+    CUDA_OK(cudaMemsetAsync(h->tr.nq_cnt, 0, (size_t)h->tr.ntr * g.kz * sizeof(int), h->st));
+    CUDA_OK(cudaMemsetAsync(h->tr.negcnt, 0, sizeof(unsigned long long), h->st));
+  }
   if (!h->mid_step) {   // head of `tend`: everything physical_parametrizations depends on (Main/mod_tendency.F90:230-270)
     TIMED(KID_H_PS, 2, (launch_h_ps(g, f, h->st), launch_h_rimcopy(g, f, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, h->st)));
     TIMED(KID_HALO, 0, rc = exch_h_psdot(h));
@@ -1460,6 +1583,7 @@ static int tend_hydro(rcm_dyn* h) {
     CUDA_OK(cudaEventRecord(h->ev_jb, h->st_b));
     CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jb, 0));
   }
+  if (h->tr.ntr > 0) TIMED(KID_TR, 1, launch_tr(g, f, h->tr, s, h->st));
   // splitf reads the new winds one dot row out (Main/mod_split.F90:276-277,312-313); the repair reads the forecast moisture
   TIMED(KID_HALO, 0, rc = exch_h_new(h));
   if (rc) return rc;
@@ -1468,6 +1592,7 @@ static int tend_hydro(rcm_dyn* h) {
   TIMED(KID_H_PS, 2, (launch_h_psfilt(g, f, s, h->st), launch_psc2psd(g, f.psa, f.psdota, nullptr, 1, h->st)));
   // negative-moisture repair (Main/mod_tendency.F90:381-393), after the p* filter whose result floors the qv filter (:420-425)
   TIMED(KID_NEGQ, 1, launch_negq_repair(g, f, s, h->st));
+  if (h->tr.ntr > 0) TIMED(KID_NEGQ, 1, launch_tr_repair(g, h->tr, s, h->st));
   TIMED(KID_SP_PROJ, 1, launch_sp_proj(g, f, s, h->st));
   int m2max = 0;
   for (int l = 0; l < s.nsplit; ++l) m2max = std::max(m2max, s.sp_m2[l]);
@@ -1484,6 +1609,7 @@ static int tend_hydro(rcm_dyn* h) {
   std::swap(f.au, f.nau); std::swap(f.av, f.nav); std::swap(f.bu, f.nbu); std::swap(f.bv, f.nbv);
   std::swap(f.at, f.nat); std::swap(f.aqv, f.naqv); std::swap(f.aqc, f.naqc);
   std::swap(f.bt, f.nbt); std::swap(f.bqv, f.nbqv); std::swap(f.bqc, f.nbqc);
+  for (int n = 0; n < h->tr.ntr; ++n) { std::swap(h->tr.a[n], h->tr.na[n]); std::swap(h->tr.b[n], h->tr.nb[n]); }
   timer_advance(h);
   if (h->lcount == 2) h->dt = h->dt2;
   return RCM_OK;
@@ -1508,6 +1634,10 @@ static int tend(rcm_dyn* h) {
   CUDA_OK(cudaMemsetAsync(f.cflbits, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.negq, 0, sizeof(unsigned long long), h->st));
   CUDA_OK(cudaMemsetAsync(f.nq_cnt, 0, (size_t)2 * g.kz * sizeof(int), h->st));
+  if (h->tr.ntr > 0) {
+    CUDA_OK(cudaMemsetAsync(h->tr.nq_cnt, 0, (size_t)h->tr.ntr * g.kz * sizeof(int), h->st));
+    CUDA_OK(cudaMemsetAsync(h->tr.negcnt, 0, sizeof(unsigned long long), h->st));
+  }
   if (!h->mid_step) {   // head of `tend`: everything physical_parametrizations depends on (Main/mod_tendency.F90:230-270)
     TIMED(KID_PREP, 1, launch_prep(g, f, s, h->st));
     TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
@@ -1535,11 +1665,13 @@ static int tend(rcm_dyn* h) {
     CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jb, 0));
     CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jc, 0));
   }
+  if (h->tr.ntr > 0) TIMED(KID_TR, 1, launch_tr(g, f, h->tr, s, h->st));
   TIMED(KID_SND_INIT, 1, launch_snd_init(g, f, s, h->st));
   TIMED(KID_HALO, 0, rc = exch_uvten(h));  // + the first cppd, ct of the step and the moisture forecast
   if (rc) return rc;
   // negative-moisture repair (Main/mod_tendency.F90:381-393): before k_snd_wback first reads the filtered qv
   TIMED(KID_NEGQ, 1, launch_negq_repair(g, f, s, h->st));
+  if (h->tr.ntr > 0) TIMED(KID_NEGQ, 1, launch_tr_repair(g, h->tr, s, h->st));
   for (int it = 1; it <= istep; ++it) {
     s.it = it;
     TIMED(KID_SND_UV, 1, launch_snd_uv(g, f, s, h->st));
@@ -1560,6 +1692,7 @@ static int tend(rcm_dyn* h) {
   // swap in the filtered t, qv, qc (the old buffers keep the previous rim)
   std::swap(f.at, f.nat); std::swap(f.aqv, f.naqv); std::swap(f.aqc, f.naqc);
   std::swap(f.bt, f.nbt); std::swap(f.bqv, f.nbqv); std::swap(f.bqc, f.nbqc);
+  for (int n = 0; n < h->tr.ntr; ++n) { std::swap(h->tr.a[n], h->tr.na[n]); std::swap(h->tr.b[n], h->tr.nb[n]); }
   timer_advance(h);
   if (h->lcount == 2) h->dt = h->dt2;
   return RCM_OK;
@@ -1646,6 +1779,7 @@ static int enqueue_steps(rcm_dyn* h, int nsteps) {
       if (h->bdy_now == h->model_time) {
         if (!h->have_next) { rc = fail(h, RCM_ERR_BDY, "boundary record needed but not staged"); break; }
         if ((rc = bdyin(h))) break;
+        if ((rc = bdyin_tracers(h))) break;
       }
       // after the swap in tend(): n?? hold the previous level-a buffers
       TIMED(KID_HALO, 0, rc = h->hydro ? exch_h_state(h) : exch_state(h));
@@ -1699,6 +1833,11 @@ static int finish_steps(rcm_dyn* h) {
     double vm[4] = {cfl, cfl_last, (double)nanf, (double)halo_err}, vs[1] = {(double)nq};
     if (reduce_verdicts(h, vm, 4, vs, 1)) return fail(h, RCM_ERR_NCCL, "allreduce (step verdicts) failed");
     cfl = vm[0]; cfl_last = vm[1]; nanf = (vm[2] != 0.0); halo_err = (vm[3] != 0.0); nq = (unsigned long long)vs[0];
+  }
+  if (h->tr.ntr > 0) {   // negative tracer forecasts of the last step (this rank's)
+    unsigned long long nc = 0;
+    CUDA_OK(cudaMemcpy(&nc, h->tr.negcnt, sizeof(nc), cudaMemcpyDeviceToHost));
+    h->neg_chi = (int64_t)nc;
   }
   h->max_cfl = cfl_last; h->neg_q = (int64_t)nq; h->nan_flag = nanf;
   h->cq_mode = nq > 0 ? 2 : 0;   // moisture went negative: the next batch stores the forecast in its first pass
@@ -1834,6 +1973,7 @@ static double* state_ptr(rcm_dyn* h, int field, int level) {
     case RCM_F_PP: return A ? f.app : f.bpp;
     case RCM_F_W: return A ? f.aw : f.bw;
   }
+  if (field >= RCM_F_CHI && field - RCM_F_CHI < h->tr.ntr) return A ? h->tr.a[field - RCM_F_CHI] : h->tr.b[field - RCM_F_CHI];
   return nullptr;
 }
 
@@ -1904,7 +2044,7 @@ extern "C" int rcm_dyn_get_state_async(rcm_dyn* h, int field, int level, double*
   } else {
     p = h->moloch ? mo_state_ptr(h, field) : state_ptr(h, field, level);
   }
-  if (!p || field < 0 || field >= RCM_F_COUNT) return fail(h, RCM_ERR_ARG, "bad field");
+  if (!p || field < 0 || 2 * field + 1 >= rcm_dyn::kSnap) return fail(h, RCM_ERR_ARG, "bad field");
   const int q = 2 * field + (level == RCM_LEVEL_B ? 1 : 0);
   const size_t bytes = (size_t)h->g.sk * (size_t)nk * sizeof(double);
   if (!h->st_out) CUDA_OK(cudaStreamCreateWithFlags(&h->st_out, cudaStreamNonBlocking));
@@ -1994,6 +2134,7 @@ extern "C" int rcm_dyn_diag(rcm_dyn* h, rcm_diag* d) {
   d->lcount = h->lcount; d->xbctime = h->xbctime; d->dt = h->dt;
   d->max_cfl = h->max_cfl; d->istep = h->last_istep; d->nan_flag = h->nan_flag;
   d->neg_q_points = h->neg_q;
+  d->neg_chi_points = h->neg_chi;
   if (h->pending && h->hydro) { cudaSetDevice(h->device); const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
   if (h->pending) {
     // Steps are in flight (rcm_dyn_step_async): report, WITHOUT blocking, the newest step whose verdict copy has

@@ -71,6 +71,23 @@ struct StepScalars {
 // a* = atm1 (time level a), b* = atm2 (level b), c* = atmc, n?* = the
 // double-buffered "next" a/b copies of t,qv,qc written by the fused slow
 // kernels and swapped in at the end of the step.
+// Tracers (atm1%chi / atm2%chi): one padded 3-D block per species, handed to the tracer kernels only
+#ifndef RCM_MAXTR
+#define RCM_MAXTR 8
+#endif
+struct TrFields {
+  int ntr;
+  double *a[RCM_MAXTR], *b[RCM_MAXTR];      // atm1%chi, atm2%chi (p*-coupled)
+  double *na[RCM_MAXTR], *nb[RCM_MAXTR];    // the filtered time levels of the step being computed (swapped in at its end)
+  double *c[RCM_MAXTR];                     // atmc%chi: unfiltered forecast (negative fix)
+  double *b0[RCM_MAXTR], *bt[RCM_MAXTR];    // chib0, chibt (coupled)
+  const double *cefc, *cegc;                // setup_che_bdycon tables [ib + nspgx*(k-1)]
+  const int* ztype;                         // 1 where the relaxation zone is the west/east one (neighbour order of nudge_chiten)
+  int* nq_list;                             // negative forecasts per (species, level) plane, as in Fields::nq_list
+  int* nq_cnt;
+  unsigned long long* negcnt;               // number of negative forecasts of the step
+};
+
 struct Fields {
   // prognostic state
   double *au, *av, *at, *aqv, *aqc, *app, *aw;

@@ -199,15 +199,23 @@ def make_case(name: str = "C2", *, flat: bool = False, unit_map: bool = False, n
         u = u + 2.0e-2 * nz_u
         v = v + 2.0e-2 * nz_v
         qv = np.maximum(0.012 * np.exp(-z / 2500.0) * (1.0 + 0.2 * np.sin(2 * np.pi * xs_c / Lx)), 1.0e-8)
+        tr = {}
+        for n in range(cfg.ntr):
+            # tracer n: a plume travelling with the record phase over a weak background that decays with height
+            # (mixing ratio, kg/kg); plumes of different tracers sit at different places and heights
+            cx, cy = (0.25 - 0.15 * n) * Lx, (-0.2 + 0.13 * n) * Ly
+            rr = ((xs_c - cx) ** 2 + (Yc[:, :, None] - cy) ** 2) / (0.10 * min(Lx, Ly)) ** 2
+            zc = 1500.0 + 1200.0 * n
+            tr[capi.F_CHI + n] = F(1.0e-9 * np.exp(-z / 4000.0) + 2.0e-7 * (n + 1) * np.exp(-rr) * np.exp(-((z - zc) / 1500.0) ** 2))
         if hydro:
             # surface pressure [hPa] on the terrain (same closed form as the profile above) with a
             # smooth travelling perturbation, so that the p* boundary tendency is non-zero
             ps = (ps0 + ptop_pa) * 0.01 * (1.0 + 1.0e-3 * np.sin(2 * np.pi * (Xc - phase) / Lx) * np.cos(2 * np.pi * Yc / Ly))
-            return {capi.F_U: F(u), capi.F_V: F(v), capi.F_T: F(t), capi.F_QV: F(qv), capi.F_PS: F(ps)}
+            return {capi.F_U: F(u), capi.F_V: F(v), capi.F_T: F(t), capi.F_QV: F(qv), capi.F_PS: F(ps), **tr}
         pp = np.zeros(Xc.shape + (kz,))
         ww = np.zeros(Xc.shape + (kz + 1,))
         return {capi.F_U: F(u), capi.F_V: F(v), capi.F_T: F(t), capi.F_QV: F(qv),
-                capi.F_PP: F(pp), capi.F_W: F(ww)}
+                capi.F_PP: F(pp), capi.F_W: F(ww), **tr}
 
     shift = 20.0 * 3600.0 * ibdyfrq * 0.25  # a quarter of the jet advection distance per record
     phases = {capi.BDY_B0: 0.0, capi.BDY_B1: shift, capi.BDY_NEXT: 2 * shift}

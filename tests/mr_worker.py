@@ -60,6 +60,7 @@ def main():
     ap.add_argument("--idynamic", type=int, default=0, help="override the case's core (1 = hydrostatic)")
     ap.add_argument("--cfg", action="append", default=[], help="name=value override of an rcm_cfg member")
     ap.add_argument("--work", action="store_true", help="also dump the per-step work arrays")
+    ap.add_argument("--spiky-tracers", action="store_true", help="tracers with sharp edges (drives their negative fix)")
     ap.add_argument("--sharp-q", action="store_true", help="moisture with sharp fronts (drives the negative-q repair)")
     ap.add_argument("--out", required=True)
     args = ap.parse_args()
@@ -123,6 +124,12 @@ def main():
     case = synth.make_case(args.case, window=win, ibdyfrq=args.ibdyfrq, **over)
     case.cfg = cfg
     synth.load_case(core, case, stage_next=True)
+    if args.spiky_tracers:
+        from tests.test_tracers import _spiky
+        for n in range(cfg.ntr):
+            q = _spiky(base, n)                    # global array; the library keeps this rank's window
+            for lv in (capi.LEVEL_A, capi.LEVEL_B):
+                core.set_state(capi.F_CHI + n, lv, q)
     if args.sharp_q:
         from tests.helpers import sharp_moisture
         qv, qc = sharp_moisture(base)          # global arrays; the library keeps this rank's window
@@ -132,7 +139,8 @@ def main():
     core.step(args.steps)
     out = {"tile": np.array(core.tile())}
     moloch = cfg.idynamic == 3
-    for fld in (MOLOCH_FIELDS if moloch else HYDRO_FIELDS if cfg.idynamic == 1 else FIELDS):
+    tracers = tuple(capi.F_CHI + n for n in range(cfg.ntr))
+    for fld in (MOLOCH_FIELDS if moloch else HYDRO_FIELDS if cfg.idynamic == 1 else FIELDS) + tracers:
         for lev, tag in (((capi.LEVEL_A, "a"),) if moloch else ((capi.LEVEL_A, "a"), (capi.LEVEL_B, "b"))):
             lb, ub = owned_bounds(core, fld)
             out[f"f{fld}{tag}"] = core.get_state(fld, lev, lb=lb, ub=ub)
@@ -161,6 +169,7 @@ def main():
     d = core.diag()
     out["max_cfl"] = np.array(d.max_cfl)
     out["neg_q"] = np.array(d.neg_q_points)
+    out["neg_chi"] = np.array(d.neg_chi_points)
     out["ptn"] = np.array([d.ptntot, d.pt2tot])
     out["ps_extremes"] = np.array([d.ps_max, d.ps_min])
     np.savez(os.path.join(args.out, f"rank{rank}.npz"), **out)

@@ -448,3 +448,57 @@ def _wafone_horizontal(pp, wz, fmz, u, v, rmu, rmv, mx2, zdtrdx, zdtrdy, jx, iy,
     zdv = (uf[1:nj + 1, :, :] * zrfme - uf[0:nj, :, :] * zrfmw) * P
     A[jj, ii, :] = p0[jj, ii, :] + mx2.s(Jci, Ici)[:, :, None] * (zpbw[0:nj, :, :] * zrfmw - zpbw[1:nj + 1, :, :] * zrfme + zdv)
     return pp
+
+
+# ---------------------------------------------------------------------------------------------------------
+def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc, ul, dt, gnu2, box, kz, upstream=True):
+    """One leapfrog step of ONE tracer away from the lateral zones, written from the Fortran text:
+    decouple (Main/mod_tendency.F90:1029-1034), start_advect (Main/mod_advection.F90:109-122: uavg/vavg from the
+    p*.u.m fluxes), hadvtr (:666-720), vadv4d ind = 2 (:895-914,946-950), diffu_x4d interior stencil
+    (Main/mod_diffusion.F90:658-725 with chib3d = max(atm2%chi*rpsb, 0), Main/mod_slice.F90:198), the sums and the
+    forecast (Main/mod_tendency.F90:548-569) and the RAW filter (Main/mod_timefilter.F90:231-278, alpha = gnu2,
+    beta = 0.53, floor 0).  `box` = (j1, j2, i1, i2): interior points at least three rows away from the zones.
+    Returns (forecast atmc%chi, filtered atm1%chi, filtered atm2%chi) on the box."""
+    j1, j2, i1, i2 = box
+    K = (1, kz)
+
+    def c(a, dj=0, di=0, k=K):
+        return a.s((j1 + dj, j2 + dj), (i1 + di, i2 + di), k) if len(a.lb) == 3 else a.s((j1 + dj, j2 + dj), (i1 + di, i2 + di))[:, :, None]
+
+    # start_advect: averages of the coupled, map-scaled winds on the cell faces
+    uavg1 = c(umc, 0, 1) + c(umc, 0, 0)
+    uavg2 = c(umc, 1, 1) + c(umc, 1, 0)
+    vavg1 = c(vmc, 1, 0) + c(vmc, 0, 0)
+    vavg2 = c(vmc, 1, 1) + c(vmc, 0, 1)
+    x = lambda dj=0, di=0: c(chia, dj, di) * c(rpsa, dj, di)          # atmx%chi
+    if upstream:
+        f1 = 0.5 * ul * (uavg2 + uavg1) / c(psa)
+        f2 = 0.5 * ul * (vavg2 + vavg1) / c(psa)
+        fx1 = (1.0 + f1) * x(-1, 0) + (1.0 - f1) * x()
+        fx2 = (1.0 + f1) * x() + (1.0 - f1) * x(1, 0)
+        fy1 = (1.0 + f2) * x(0, -1) + (1.0 - f2) * x()
+        fy2 = (1.0 + f2) * x() + (1.0 - f2) * x(0, 1)
+    else:
+        fx1, fx2, fy1, fy2 = x(-1, 0) + x(), x() + x(1, 0), x(0, -1) + x(), x() + x(0, 1)
+    ten = -c(xmsf) * (uavg2 * fx2 - uavg1 * fx1 + vavg2 * fy2 - vavg1 * fy1)
+    # vadv4d, ind = 2: flux through interface k = 2..kz, zero unless the upwind coupled value exceeds mintr*ps
+    fk = c(chia, k=(2, kz))
+    fkm1 = c(chia, k=(1, kz - 1))
+    sv = c(svv, k=(2, kz))
+    thr = 1.0e-30 * c(psa)
+    ok = np.where(sv > 0.0, fkm1 > thr, fk > thr)
+    tw1 = twt.s((2, kz), 1)[None, None, :]
+    tw2 = twt.s((2, kz), 2)[None, None, :]
+    fg = np.where(ok, sv * (tw1 * fk + tw2 * fkm1), 0.0)
+    xd = xds.s((1, kz))[None, None, :]
+    ten[:, :, :-1] -= fg * xd[:, :, :-1]
+    ten[:, :, 1:] += fg * xd[:, :, 1:]
+    # diffu_x4d on chib3d
+    b = lambda dj=0, di=0: np.maximum(c(chib, dj, di) * c(rpsb, dj, di), 0.0)
+    ten -= c(xkc) * ((b(2, 0) + b(-2, 0) + b(0, 2) + b(0, -2)) - 4.0 * (b(1, 0) + b(-1, 0) + b(0, 1) + b(0, -1)) + 12.0 * b())
+    fc = c(chib) + dt * ten
+    fcp = np.where(fc < 0.0, np.nan, fc)        # the negative fix is not part of this restatement
+    d = gnu2 * (fcp + c(chib) - 2.0 * c(chia))
+    nb = np.maximum(c(chia) + 0.53 * d, 0.0)
+    na = np.maximum(fcp + (0.53 - 1.0) * d, 0.0)
+    return fc, na, nb

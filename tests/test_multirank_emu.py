@@ -203,6 +203,49 @@ def test_hydro_multirank_record_change_and_data_means(emu_lib, tmp_path):
     compare(glob, ref, 1e-11)
 
 
+# ---------------------------------------------------------------------------- tracers
+@pytest.mark.parametrize("idynamic", [2, 1])
+def test_tracers_multirank_match_single_rank(emu_lib, tmp_path, idynamic):
+    """Tracers on a 2x2 decomposition: they ride along in the state exchange and in the exchange of the moisture
+    forecast; the sequential negative fix stops at the tile seams exactly as for moisture (every rank sweeps its own
+    tile, ghost values are the neighbour's unrepaired forecast)."""
+    from tests.test_tracers import _spiky
+    steps, ntr = 4, 2
+    run_ranks(4, tmp_path, ["--case", "tiny", "--idynamic", str(idynamic), "--steps", str(steps), "--cpus-j", "2", "--cpus-i", "2",
+                            "--cfg", f"ntr={ntr}", "--spiky-tracers"])
+    # single rank: the same library with the repair's tile seams of the 2x2 layout is not expressible there, so the
+    # reference is the oracle with set_repair_tiles (tests/test_negq.py does the same for moisture)
+    from oracle import pyoracle
+    case = synth.make_case("tiny", idynamic=idynamic, ntr=ntr)
+    ref = pyoracle.make_oracle(case.cfg)
+    synth.load_case(ref, case)
+    for n in range(ntr):
+        q = _spiky(case, n)
+        ref.set_state(capi.F_CHI + n, capi.LEVEL_A, q)
+        ref.set_state(capi.F_CHI + n, capi.LEVEL_B, q)
+    tiles = [np.load(os.path.join(tmp_path, f"rank{r}.npz"))["tile"] for r in range(4)]
+    import ctypes as C
+    js, is_ = sorted({int(t[0]) for t in tiles}), sorted({int(t[2]) for t in tiles})
+    assert ref.lib.lib.orc_set_repair_tiles(ref.h, len(js), (C.c_int32 * len(js))(*js), len(is_), (C.c_int32 * len(is_))(*is_)) == 0
+    ref.step(steps)
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    negs = 0
+    for n in range(ntr):
+        for lv, tag in ((0, "a"), (1, "b")):
+            glob = np.full((jx - 1, iy - 1, kz), np.nan)
+            for r in range(4):
+                d = np.load(os.path.join(tmp_path, f"rank{r}.npz"))
+                lb, a = d[f"lb{capi.F_CHI + n}"], d[f"f{capi.F_CHI + n}{tag}"]
+                glob[lb[0] - 1:lb[0] - 1 + a.shape[0], lb[1] - 1:lb[1] - 1 + a.shape[1], :] = a
+            want = ref.get_state(capi.F_CHI + n, lv)
+            assert not np.isnan(glob).any()
+            tol = 1e-11 if idynamic == 1 else 0.0
+            assert np.abs(glob - want).max() <= tol * want.max(), (n, tag)
+    for r in range(4):
+        negs += int(np.load(os.path.join(tmp_path, f"rank{r}.npz"))["neg_chi"])
+    assert negs == ref.diag().neg_chi_points and negs > 0
+
+
 # ---------------------------------------------------------------------------- MOLOCH core (idynamic = 3)
 MOLOCH_FIELDS = (capi.F_U, capi.F_V, capi.F_W, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PAI, capi.F_PS)
 
