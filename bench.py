@@ -48,7 +48,7 @@ def measured_traffic(kernel, workload, world):
     """dram bytes per launch of `kernel` from the committed ncu captures (profiles/r1_traffic.json for the
     non-hydrostatic C4, profiles/r1_hydro_traffic.json for the hydrostatic C4hq); only meaningful for the
     configuration it was captured on."""
-    for fn in ("r1_traffic.json", "r1_hydro_traffic.json", "r1_moloch_traffic.json"):
+    for fn in ("r2_traffic.json", "r1_traffic.json", "r1_hydro_traffic.json", "r1_moloch_traffic.json"):
         try:
             with open(os.path.join(ROOT, "profiles", fn)) as fh:
                 t = json.load(fh)
@@ -56,6 +56,24 @@ def measured_traffic(kernel, workload, world):
                 return t["bytes_per_launch"].get(kernel)
         except Exception:
             pass
+    return None
+
+
+# FP64 issue rate measured on this pool's B200 with register-resident DFMA/DADD/DMUL chains (scripts/fp64_peak.cu,
+# profiles/r2_measurements.md call A): one FP64 instruction per lane and clock whether FMA, add or multiply
+FP64_THREAD_INST_PER_S = 18.57e12
+
+
+def measured_fp64(kernel, workload, world):
+    """FP64 warp instructions per launch of `kernel` from the committed ncu capture (smsp__inst_executed_pipe_fp64.sum,
+    profiles/r2_fp64.json); only meaningful for the configuration it was captured on."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2_fp64.json")) as fh:
+            t = json.load(fh)
+        if t["workload"] == workload and t["n_gpus"] == world:
+            return t["fp64_warp_inst_per_launch"].get(kernel)
+    except Exception:
+        pass
     return None
 
 
@@ -178,7 +196,8 @@ def run_reference(args):
         pass
     side = int(max(40, min(256, np.sqrt(budget_cells / kz))))
     value, ms, case = oracle_throughput(args.workload, side, nthreads, args.steps, args.warmup)
-    sample = (f"{nthreads} independent oracle instances (1 host thread each, no halo exchange), each a "
+    ncpu = os.cpu_count() or nthreads
+    sample = (f"{nthreads} of {ncpu} host cores: {nthreads} independent oracle instances (1 host thread each, no halo exchange), each a "
               f"{case.cfg.jx}x{case.cfg.iy}x{case.cfg.kz} sub-domain of workload {args.workload} (same ds, dt, options)")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
@@ -290,13 +309,31 @@ def run_gpu(args):
     top = max(kern, key=lambda k: kern[k][0])
     top_ms = kern[top][0] / kern[top][1]
     achieved = ALG_BYTES_KERNEL[top] * local_cells / (top_ms * 1e-3) / 1e9
+    def floors(k, launch_ms):
+        """HBM floor (algorithmic bytes / measured copy bandwidth) and FP64-issue floor (FP64 instructions of the ncu
+        capture / measured FP64 issue rate) of one launch; the larger one is the roof that binds."""
+        hbm_ms = ALG_BYTES_KERNEL[k] * local_cells / (peak * 1e9) * 1e3 if k in ALG_BYTES_KERNEL else None
+        w = measured_fp64(k, args.workload, world)
+        f64_ms = w * 32.0 / FP64_THREAD_INST_PER_S * 1e3 if w else None
+        roof = max(x for x in (hbm_ms, f64_ms, 0.0) if x is not None)
+        return {"hbm_floor_ms": hbm_ms, "fp64_floor_ms": f64_ms, "bound": "fp64" if (f64_ms or 0.0) > (hbm_ms or 0.0) else "hbm",
+                "frac_of_binding_roof": (roof / launch_ms if roof > 0 else None)}
+
     roofline = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": measured_traffic(top, args.workload, world), "peak_source": peak_src, "avg_launch_ms": top_ms,
                 "alg_bytes_per_launch": ALG_BYTES_KERNEL[top] * local_cells,
                 "share_of_step": kern[top][0] / max(sum(v[0] for v in prof.values()), 1e-30),
+                "fp64_peak_thread_inst_per_s": FP64_THREAD_INST_PER_S,
+                "fp64_peak_source": "measured: scripts/fp64_peak.cu, profiles/r2_measurements.md (DFMA = DADD = DMUL issue rate)",
                 "per_kernel": {k: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps,
-                                   "GBs": (ALG_BYTES_KERNEL[k] * local_cells / (v[0] / v[1] * 1e-3) / 1e9 if k in ALG_BYTES_KERNEL and v[1] else None)}
+                                   "GBs": (ALG_BYTES_KERNEL[k] * local_cells / (v[0] / v[1] * 1e-3) / 1e9 if k in ALG_BYTES_KERNEL and v[1] else None),
+                                   **(floors(k, v[0] / v[1]) if k in ALG_BYTES_KERNEL else {})}
                                for k, v in prof.items() if v[1] > 0}}
+    # contract: bound is "hbm"|"tensor" (achieved/peak/frac above are the HBM figures); which of the HBM and FP64-issue
+    # floors is the larger one for the dominant kernel is reported beside it
+    ft = floors(top, top_ms)
+    roofline.update({"hbm_floor_ms": ft["hbm_floor_ms"], "fp64_floor_ms": ft["fp64_floor_ms"], "binding_roof": ft["bound"],
+                     "frac_of_binding_roof": ft["frac_of_binding_roof"]})
     step_bytes = (ALG_BYTES_STEP_HYDRO if hydro else ALG_BYTES_STEP_MOLOCH(cfg.mo_nadv, cfg.mo_nsound) if moloch
                   else ALG_BYTES_STEP(istep))
     step_roof = {"alg_bytes_per_grid_point_step": step_bytes, "achieved_GBs": step_bytes * value / world / 1e9,

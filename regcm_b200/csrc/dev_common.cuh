@@ -61,8 +61,11 @@
 #ifndef RCM_MB_PPW
 #define RCM_MB_PPW 4
 #endif
-#ifndef RCM_MB_WFWD
-#define RCM_MB_WFWD 3
+#ifndef RCM_MB_WFWD   // 2: ptxas then takes 160 registers (174 in the first sub-step) without spilling and 3 blocks still fit;
+#define RCM_MB_WFWD 2   // under the 170-register cap of 3 it spilled and ran 5.6 % slower (profiles/r2_measurements.md, call N)
+#endif
+#ifndef RCM_MB_STAGED   // the TMA-staged slow-tendency kernels (256 threads per block)
+#define RCM_MB_STAGED 2
 #endif
 #ifndef RCM_MB_WBACK
 #define RCM_MB_WBACK 4

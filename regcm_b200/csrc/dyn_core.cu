@@ -391,7 +391,10 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   if (const char* e = std::getenv("RCM_KC_TQ")) g.kc_tq = std::max(1, std::atoi(e));
   if (const char* e = std::getenv("RCM_KC_PPW")) g.kc_ppw = std::max(1, std::atoi(e));
   if (const char* e = std::getenv("RCM_OVERLAP")) h->overlap_slow = std::atoi(e) != 0;
-  if (const char* e = std::getenv("RCM_PFD")) g.pfd = std::max(0, std::min(8, std::atoi(e)));
+  g.pfd_wfwd = 4; g.pfd_wback = 1;   // measured on C4: wfwd 5.50 / 5.28 / 5.05 / 4.98 ms at distance 1 / 2 / 3 / 4, wback 4.86 / 4.96 / 5.19 / 5.57
+  if (const char* e = std::getenv("RCM_PFD")) g.pfd = g.pfd_wfwd = g.pfd_wback = std::max(0, std::min(8, std::atoi(e)));
+  if (const char* e = std::getenv("RCM_PFD_WFWD")) g.pfd_wfwd = std::max(0, std::min(12, std::atoi(e)));
+  if (const char* e = std::getenv("RCM_PFD_WBACK")) g.pfd_wback = std::max(0, std::min(12, std::atoi(e)));
   h->eni = ni + 2 * RCM_EHALO;
   h->eoff = -((long long)(g.jde1 - RCM_EHALO) + (long long)g.esi * (g.ide1 - RCM_EHALO));
 

@@ -32,6 +32,7 @@ struct Geom {
   int esi;       // pitch of the wide-halo 2-D estore array
   int kc_uv, kc_tq, kc_ppw;  // levels per thread of the slow-tendency kernels (>= kz: one thread marches the whole column)
   int pfd;       // L2 prefetch distance (levels ahead) of the column-marching kernels; 0 = off
+  int pfd_wfwd, pfd_wback;   // the same for the two acoustic sweeps, which want different distances (profiles/r2_measurements.md, call O)
 };
 
 // per-step scalars

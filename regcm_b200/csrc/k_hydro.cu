@@ -118,8 +118,17 @@ k_h_prep(const Geom g, const Fields f, const StepScalars s) {
   const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i),
                m11 = L2(f.msfd, j + 1, i + 1);
   // ---- mass divergence and p* tendency (compute_omega :1131-1148) ----
+  // request the next levels of the streamed fields into L2 (see PF3 in dev_common.cuh)
+  const int pfd = g.pfd;
+  auto pf_uv = [&](int kk) { PF3(f.au, j, i, kk); PF3(f.av, j, i, kk); PF3(f.au, j, i + 1, kk); PF3(f.av, j, i + 1, kk); };
+  auto pf_t = [&](int kk) { PF3(f.at, j, i, kk); PF3(f.aqv, j, i, kk); PF3(f.aqc, j, i, kk); };
+  if (pfd > 0) {
+    for (int kk = 1; kk <= min(pfd, kz); ++kk) pf_uv(kk);
+    for (int kk = kz; kk >= max(kz - pfd + 1, 1); --kk) pf_t(kk);
+  }
   double pten = 0.0;
   for (int k = 1; k <= kz; ++k) {
+    if (pfd > 0 && k + pfd <= kz) pf_uv(k + pfd);
     const double u00 = L3(f.au, j, i, k) * m00, u01 = L3(f.au, j, i + 1, k) * m01, u10 = L3(f.au, j + 1, i, k) * m10,
                  u11 = L3(f.au, j + 1, i + 1, k) * m11;
     const double v00 = L3(f.av, j, i, k) * m00, v01 = L3(f.av, j, i + 1, k) * m01, v10 = L3(f.av, j + 1, i, k) * m10,
@@ -143,6 +152,7 @@ k_h_prep(const Geom g, const Fields f, const StepScalars s) {
     const double ptr = s.ptop * rpsa;
     double td_n = 0.0, phi_n = 0.0, hs_n = 0.0, ds_n = 0.0;
     for (int k = kz; k >= 1; --k) {
+      if (pfd > 0 && k - pfd >= 1) pf_t(k - pfd);
       const double qvd = fmax(L3(f.aqv, j, i, k) * rpsa, minqq);
       const double qcd = fmax(L3(f.aqc, j, i, k) * rpsa, 0.0);
       const double td = L3(f.at, j, i, k) * (1.0 + ep1 * qvd);
@@ -219,7 +229,15 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
   const double dxm = s.dx * md[1][1], dx2m = s.dx2 * md[1][1];
 
   double uu_k = 0.0, vv_k = 0.0;  // vertical-advection flux at the upper interface of level k
+  const int pfd = g.pfd;
+  auto prefetch = [&](int kk) {   // the rows above and below this thread's are requested by the neighbouring threads
+    PF3(f.au, j, i, kk); PF3(f.av, j, i, kk); PF3(f.bu, j, i, kk); PF3(f.bv, j, i, kk); PF3(f.dub, j, i, kk); PF3(f.dvb, j, i, kk);
+    PF3(f.qdot, j, i, kk); PF3(f.xkc, j, i, kk); PF3(f.at, j, i, kk); PF3(f.aqv, j, i, kk); PF3(f.phi, j, i, kk);
+  };
+  if (pfd > 0)
+    for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
   for (int k = 1; k <= kz; ++k) {
+    if (pfd > 0 && k + pfd <= kz) prefetch(k + pfd);
     double au[3][3], av[3][3];
 #pragma unroll
     for (int a = 0; a < 3; ++a)
@@ -392,7 +410,15 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
 
   double dq_k = 0.0, fl_qv_k = 0.0, fl_qc_k = 0.0;  // vertical fluxes at full level k (zero at k = 1)
   double qdot_k = 0.0;
+  const int pfd = g.pfd;
+  auto prefetch = [&](int kk) {
+    PF3(f.au, j, i, kk); PF3(f.av, j, i, kk); PF3(f.au, j, i + 1, kk); PF3(f.av, j, i + 1, kk); PF3(f.qdot, j, i, kk); PF3(f.xkc, j, i, kk);
+    PF3(f.at, j, i, kk); PF3(f.bt, j, i, kk); PF3(f.aqv, j, i, kk); PF3(f.bqv, j, i, kk); PF3(f.aqc, j, i, kk); PF3(f.bqc, j, i, kk);
+  };
+  if (pfd > 0)
+    for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
   for (int k = 1; k <= kz; ++k) {
+    if (pfd > 0 && k + pfd <= kz) prefetch(k + pfd);
     const double au00 = L3(f.au, j, i, k), au01 = L3(f.au, j, i + 1, k), au10 = L3(f.au, j + 1, i, k), au11 = L3(f.au, j + 1, i + 1, k);
     const double av00 = L3(f.av, j, i, k), av01 = L3(f.av, j, i + 1, k), av10 = L3(f.av, j + 1, i, k), av11 = L3(f.av, j + 1, i + 1, k);
     const double ua00 = au00 * m00, ua01 = au01 * m01, ua10 = au10 * m10, ua11 = au11 * m11;

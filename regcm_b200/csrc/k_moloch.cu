@@ -144,7 +144,16 @@ __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_MOW) k_mo_w(const Geom g, con
   double zdiv_k = fmz_k * (mx2 * zd_kz + zdtrdz * (s_k - s_kp1));
   MOW_ST(2, kz, P3(zdf, j, i, kz), zdiv_k);
   double wwkw_kp1 = 0.0;
+  // request the operands of level k-1-pfd into L2 while level k is worked on (see PF3 in dev_common.cuh)
+  const int pfd = g.pfd;
+  auto prefetch = [&](int kk) {
+    PF3(f.u, j, i, kk - 1); PF3(f.v, j, i, kk - 1); PF3(f.v, j, i + 1, kk - 1); PF3(f.fmz, j, i, kk); PF3(f.zdiv, j, i, kk);
+    PF3(f.pai, j, i, kk); PF3(f.tetav, j, i, kk); PF3(f.fmzf, j, i, kk + 1); PF3(f.w, j, i, kk + 1);
+  };
+  if (pfd > 0)
+    for (int kk = kz - 1; kk >= max(kz - 1 - pfd, 2); --kk) prefetch(kk);
   for (int k = kz; k >= 2; --k) {
+    if (pfd > 0 && k - 2 - pfd >= 2) prefetch(k - 2 - pfd);
     MoWIn nxt = cur;
     if (k > 2) nxt = mo_w_load(g, f, s.anu2, interior, si, sk, j, i, k - 1);
     // level k-1 quantities: s(k-1) (0 for k-1 = 1), zdiv(k-1)

@@ -18,7 +18,7 @@ constexpr int kCopies = kNH * kTH + kNC * kBY;  // 144 row copies per level
 enum { T_AU, T_AV, T_APP, T_AW, T_BPP, T_BW };
 enum { C_AT, C_AQV, C_AQC, C_RHO0, C_RHO1, C_T0, C_CR, C_XKC, C_QDOT };
 
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, RCM_MB_STAGED)
 k_ppw_tma(const Geom g, const Fields f, const StepScalars s) {
   extern __shared__ __align__(128) unsigned char smraw[];
   double* tiles = reinterpret_cast<double*>(smraw);

@@ -111,10 +111,13 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
     if (FIRST) { PF3(f.pr1, j, i, kk); PF3(f.rho1, j, i, kk); }
     else { PF3(f.scc, j, i, kk); PF3(f.scdd, j, i, kk); PF3(f.sca, j, i, kk); }
   };
-  const int pfd = g.pfd;
+  const int pfd = g.pfd_wfwd;
   if (pfd > 0)
     for (int kk = kz; kk >= max(kz - pfd, 1); --kk) prefetch(kk);
 
+#if defined(RCM_WF_PIPE) && RCM_WF_PIPE
+#define WF_PIPELINED
+#endif
 #define WF_OK true
 #define WF_ITER_BEGIN(k) if (pfd > 0 && (k) - 1 - pfd >= 1) prefetch((k) - 1 - pfd)
 #define WF_LOADUV_ITER(U, V) LOADUV(U, V, k - 2)
@@ -130,6 +133,7 @@ k_snd_wfwd(const Geom g, const Fields f, const StepScalars s) {
 #undef WF_P0N
 #undef WF_WTEN
 #undef WF_CA
+#undef WF_PIPELINED
 }
 #undef P3
 #undef P2
@@ -182,7 +186,7 @@ k_snd_wback(const Geom g, const Fields f, const StepScalars s) {
     PF3(f.rho0, j, i, kk); PF3(f.rho1, j, i, kk); PF3(f.ppten, j, i, kk); PF3(f.nbqv, j, i, kk);
     PF3(f.nbt, j, i, kk); PF3(f.nat, j, i, kk); PF3(f.pr0, j, i, kk);
   };
-  const int pfd = g.pfd;
+  const int pfd = g.pfd_wback;
   if (pfd > 0)
     for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
   // ---- upper radiative boundary condition (:497-523): w at the model top is

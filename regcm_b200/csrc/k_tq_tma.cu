@@ -19,7 +19,7 @@ enum { T_AU, T_AV, T_TH, T_AQV, T_AQC, T_BT, T_BQV, T_BQC };
 enum { C_CR, C_XKC, C_AT };
 
 template <int CQ_MODE>   // StepScalars::cq_mode (negative-moisture repair), compile-time
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, RCM_MB_STAGED)
 k_tq_tma(const Geom g, const Fields f, const StepScalars s) {
   if (CQ_MODE == 1 && *f.negq == 0ULL) return;  // second pass of the negative-moisture repair: nothing went negative
   extern __shared__ __align__(128) unsigned char smraw[];

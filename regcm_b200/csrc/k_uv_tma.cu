@@ -25,7 +25,7 @@ constexpr int kBY = 8, kTW = 40, kTH = kBY + 4, kTile = kTW * kTH, kNT = 8, kSta
 constexpr int kRowBytes = kTW * 8, kStageBytes = kNT * kTile * 8;
 enum { T_AU, T_AV, T_CR, T_XKC, T_DUB, T_DVB, T_QDOT, T_AW };
 
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, RCM_MB_STAGED)
 k_uv_tma(const Geom g, const Fields f, const StepScalars s) {
   extern __shared__ __align__(128) unsigned char smraw[];
   double* tiles = reinterpret_cast<double*>(smraw);

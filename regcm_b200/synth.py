@@ -54,6 +54,7 @@ CASES = {
     "C3": dict(jx=250, iy=200, kz=23, ds=50.0, dt=120.0, nspg=12),
     "C4": dict(jx=1000, iy=1000, kz=41, ds=3.0, dt=6.0, nspg=12),
     "C4q": dict(jx=500, iy=500, kz=41, ds=3.0, dt=6.0, nspg=12),
+    "C4e": dict(jx=500, iy=250, kz=41, ds=3.0, dt=6.0, nspg=12),   # one tile of C4 on 8 ranks (4 x 2): tuning the N = 8 tile size on one GPU
     # hydrostatic core at sizes where the kernels are HBM-bound (kernel roofline; not BASELINE configs)
     "C3h": dict(jx=250, iy=200, kz=23, ds=50.0, dt=120.0, nspg=12, idynamic=1),
     "C4h": dict(jx=1000, iy=1000, kz=41, ds=3.0, dt=6.0, nspg=12, idynamic=1),
