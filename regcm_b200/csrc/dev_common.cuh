@@ -88,6 +88,19 @@ inline dim3 col_block() {
 
 namespace rcm {
 
+// x**c for x > 0 in the hot kernels.  The device library's pow() handles every special case of the C standard and
+// costs several hundred instructions per call — a third of k_h_tq's and k_prep's issue slots (profiles/r2_measurements.md);
+// every base here is a ratio of positive pressures or mixing ratios, for which exp(c*log(x)) is accurate to ~2 ulp
+// (|c*log(x)| < 3 at all call sites).  The host harness keeps the host's pow so that it stays bit-comparable with
+// the oracle.
+__device__ __forceinline__ double pow_pos(const double x, const double c) {
+#ifdef RCM_EMU
+  return pow(x, c);
+#else
+  return exp(c * log(x));
+#endif
+}
+
 // flux-form horizontal advection of a cross-point scalar
 // (Main/mod_advection.F90:336-351 upstream branch, :352-357 centred branch).
 // f1,f2 are the upstream weights 0.5*ul*(uavg2+uavg1)/ps and the v analogue.

@@ -453,8 +453,8 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         const double pfs = (LD1(&f.sigma[kn]) * psb + s.ptop) * 1000.0;
         const double hs_n = (LD1(&f.sigma[kn + 1]) + LD1(&f.sigma[kn])) * 0.5;
         const double phs_n = (hs_n * psb + s.ptop) * 1000.0, phs_k = (hs * psb + s.ptop) * 1000.0;
-        dq_n = svv_n * (LD1(&f.twt1[kn]) * L3(f.at, j, i, kn) * pow(pfs / phs_n, c287) +
-                        LD1(&f.twt2[kn]) * at * pow(pfs / phs_k, c287));
+        dq_n = svv_n * (LD1(&f.twt1[kn]) * L3(f.at, j, i, kn) * pow_pos(pfs / phs_n, c287) +
+                        LD1(&f.twt2[kn]) * at * pow_pos(pfs / phs_k, c287));
         ten = ten - dq_n * xdsk;
       }
       // adiabatic term with omega evaluated in place
@@ -507,7 +507,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
       if (k < kz) {
         const double aqv_n = L3(f.aqv, j, i, k + 1);
         double fgv = 0.0;
-        if (aqv_n > qthr && aq_c > qthr) fgv = aqv_n * pow(aq_c / aqv_n, LD1(&f.qcon[k + 1]));
+        if (aqv_n > qthr && aq_c > qthr) fgv = aqv_n * pow_pos(aq_c / aqv_n, LD1(&f.qcon[k + 1]));
         fl_n = svv_n * fgv;
         ten = ten - fl_n * xdsk;
       }

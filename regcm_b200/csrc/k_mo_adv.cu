@@ -79,7 +79,16 @@ __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_WAFZ) k_mo_wafz(const Geom g,
   }
   double s_k = 0.0;
   double fmzf_k = 0.0;   // fmzf(k); not used for k = 1
+  const int pfd = g.pfd;   // L2 prefetch distance beyond the two levels already held in registers (PF3, dev_common.cuh)
+  auto prefetch = [&](int kk) {
+#pragma unroll
+    for (int n = 0; n < NF; ++n) PF3(adv[n], j, i, kk + 2);
+    PF3(f.s, j, i, kk + 1); PF3(f.fmz, j, i, kk); PF3(f.fmzf, j, i, kk + 1);
+  };
+  if (pfd > 0)
+    for (int kk = 1; kk <= min(pfd, kz - 2); ++kk) prefetch(kk);
   for (int k = 1; k <= kz; ++k) {
+    if (pfd > 0 && k + pfd <= kz - 2) prefetch(k + pfd);
     double pkp2[NF];
 #pragma unroll
     for (int n = 0; n < NF; ++n) pkp2[n] = (k + 2 <= kz) ? L3(adv[n], j, i, k + 2) : 0.0;

@@ -275,7 +275,7 @@ __global__ void k_mo_close(const Geom g, const MoFields f, const MoScalars s) {
         tv = P3(f.t, j, i, k) * den;
       }
       P3(f.tvirt, j, i, k) = tv;
-      pk = pow(pai, cpovr) * p00;
+      pk = pow_pos(pai, cpovr) * p00;
       P3(f.p, j, i, k) = pk;
     }
     const double zdgz = L2(f.ht, j, i) * s.gzm1 + s.zz1;

@@ -82,7 +82,7 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
     const double pr1 = L3(f.pr0, j, i, k) + pp;
     P3(f.pr1, j, i, k) = pr1;
     P3(f.rho1, j, i, k) = pr1 / (rgas * tv);
-    P3(f.th, j, i, k) = t * pow(p00 / pr1, rovcp);
+    P3(f.th, j, i, k) = t * pow_pos(p00 / pr1, rovcp);
     // ---- sigma-dot at the next full level, divergence at this half level ----
     double qd_n = 0.0, ucc_n = 0.0, vcc_n = 0.0;
     double n00 = 0, n01 = 0, n10 = 0, n11 = 0, w00 = 0, w01 = 0, w10 = 0, w11 = 0;
