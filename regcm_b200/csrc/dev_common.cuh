@@ -92,12 +92,39 @@ namespace rcm {
 // costs several hundred instructions per call — a third of k_h_tq's and k_prep's issue slots (profiles/r2_measurements.md);
 // every base here is a ratio of positive pressures or mixing ratios, for which exp(c*log(x)) is accurate to ~2 ulp
 // (|c*log(x)| < 3 at all call sites).  The host harness keeps the host's pow so that it stays bit-comparable with
-// the oracle.
+// the CPU restatement used by the tests.
 __device__ __forceinline__ double pow_pos(const double x, const double c) {
 #ifdef RCM_EMU
   return pow(x, c);
 #else
   return exp(c * log(x));
+#endif
+}
+
+// n / d when several numerators share one denominator: r = 1/d is computed once (one IEEE division) and every
+// quotient costs three fused operations, q0 = n*r; rem = n - d*q0 (exact); q = q0 + rem*r — Markstein's division step,
+// which returns the correctly rounded quotient when r is the correctly rounded reciprocal and q0 is within one ulp.
+// Device only (RCM_NO_DIVS switches it off for A/B runs): the host harness divides, so that it stays bit-comparable with
+// the CPU restatement used by the tests.
+#ifndef RCM_NO_DIVS
+#define RCM_DIVS 1
+#endif
+__device__ __forceinline__ double div_r(const double n, const double d, const double r) {
+#if defined(RCM_EMU) || !defined(RCM_DIVS)
+  (void)r;
+  return n / d;
+#else
+  const double q0 = n * r;
+  const double rem = fma(-d, q0, n);
+  return fma(rem, r, q0);
+#endif
+}
+__device__ __forceinline__ double recip_for_div(const double d) {
+#if defined(RCM_EMU) || !defined(RCM_DIVS)
+  (void)d;
+  return 0.0;
+#else
+  return 1.0 / d;
 #endif
 }
 

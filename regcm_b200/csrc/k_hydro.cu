@@ -227,6 +227,7 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
   const double pa11 = L2(f.psa, j, i), pa10 = L2(f.psa, j, i - 1), pa01 = L2(f.psa, j - 1, i), pa00 = L2(f.psa, j - 1, i - 1);
   const double ra11 = L2(f.rpsa, j, i), ra10 = L2(f.rpsa, j, i - 1), ra01 = L2(f.rpsa, j - 1, i), ra00 = L2(f.rpsa, j - 1, i - 1);
   const double dxm = s.dx * md[1][1], dx2m = s.dx2 * md[1][1];
+  const double rdxm = recip_for_div(dxm), rdx2m = recip_for_div(dx2m);   // shared-denominator divisions (div_r)
 
   double uu_k = 0.0, vv_k = 0.0;  // vertical-advection flux at the upper interface of level k
   const int pfd = g.pfd;
@@ -345,11 +346,11 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
       double rtbar = 0.25 * (TV(j - 1, i - 1, ra00) + TV(j - 1, i, ra01) + TV(j, i - 1, ra10) + TV(j, i, ra11));
 #undef TV
       rtbar = rgas * rtbar * psdota;
-      ut = ut - rtbar * (log(0.5 * (pa11 + pa10) * hs + s.ptop) - log(0.5 * (pa01 + pa00) * hs + s.ptop)) / dxm;
-      vt = vt - rtbar * (log(0.5 * (pa11 + pa01) * hs + s.ptop) - log(0.5 * (pa00 + pa10) * hs + s.ptop)) / dxm;
+      ut = ut - div_r(rtbar * (log(0.5 * (pa11 + pa10) * hs + s.ptop) - log(0.5 * (pa01 + pa00) * hs + s.ptop)), dxm, rdxm);
+      vt = vt - div_r(rtbar * (log(0.5 * (pa11 + pa01) * hs + s.ptop) - log(0.5 * (pa00 + pa10) * hs + s.ptop)), dxm, rdxm);
       const double p11 = L3(f.phi, j, i, k), p10 = L3(f.phi, j, i - 1, k), p01 = L3(f.phi, j - 1, i, k), p00 = L3(f.phi, j - 1, i - 1, k);
-      ut = ut - psdota * (p11 + p10 - p01 - p00) / dx2m;
-      vt = vt - psdota * (p11 + p01 - p10 - p00) / dx2m;
+      ut = ut - div_r(psdota * (p11 + p10 - p01 - p00), dx2m, rdx2m);
+      vt = vt - div_r(psdota * (p11 + p01 - p10 - p00), dx2m, rdx2m);
     }
     // ---- forecast p*u, p*v and Robert-Asselin filter (:433-445) ----
     const double bu_c = L3(f.bu, j, i, k), bv_c = L3(f.bv, j, i, k);
@@ -387,6 +388,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
   const double ul = s.ul, xt = s.xt, dt = s.dt;
 
   const double psa = L2(f.psa, j, i), psb = L2(f.psb, j, i), psc = L2(f.psc, j, i);
+  const double rdiv_psa = recip_for_div(psa);
   const double rpsa_c = L2(f.rpsa, j, i), rpsa_jm = L2(f.rpsa, j - 1, i), rpsa_jp = L2(f.rpsa, j + 1, i),
                rpsa_im = L2(f.rpsa, j, i - 1), rpsa_ip = L2(f.rpsa, j, i + 1);
   const double xmsf = L2(f.xmsf, j, i);
@@ -425,8 +427,8 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
     const double va00 = av00 * m00, va01 = av01 * m01, va10 = av10 * m10, va11 = av11 * m11;
     const double uavg1 = ua01 + ua00, uavg2 = ua11 + ua10;
     const double vavg1 = va10 + va00, vavg2 = va11 + va01;
-    const double f1 = 0.5 * ul * (uavg2 + uavg1) / psa;
-    const double f2 = 0.5 * ul * (vavg2 + vavg1) / psa;
+    const double f1 = div_r(0.5 * ul * (uavg2 + uavg1), psa, rdiv_psa);
+    const double f2 = div_r(0.5 * ul * (vavg2 + vavg1), psa, rdiv_psa);
     const double xdsk = LD1(&f.xds[k]);
     const double svv_n = (k < kz) ? L3(f.qdot, j, i, k + 1) : 0.0;
     const double hs = (LD1(&f.sigma[k + 1]) + LD1(&f.sigma[k])) * 0.5;

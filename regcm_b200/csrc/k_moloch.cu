@@ -28,13 +28,14 @@ __global__ void k_mo_pre(const Geom g, const MoFields f, const MoScalars s) {
   P3(f.tetav, j, i, k) = tv / P3(f.pai, j, i, k);
 }
 
-// Evaluated on the owned cells plus one ghost ring towards neighbouring ranks (g.gl/gr/gb/gt), so that the
-// 5-point filter of k_mo_w finds its neighbours without a separate exchange of the divergence (the reference
-// exchanges zdiv2, Main/mod_moloch.F90:553; here u and v carry two ghost rows instead).
+// Evaluated on the owned cells plus one ghost ring towards neighbouring ranks (g.gl/gr/gb/gt) — two rings on the
+// low sides — so that the 5-point filter of k_mo_w finds its neighbours without a separate exchange of the
+// divergence (the reference exchanges zdiv2, Main/mod_moloch.F90:553; here u and v carry two ghost rows instead),
+// also on the low-side ghost ring that k_mo_w advances itself.
 __global__ void k_mo_div(const Geom g, const MoFields f, const MoScalars s) {
   const int si = g.si; const long long sk = g.sk;
-  const int j = g.jce1 - g.gl + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = g.ice1 - g.gb + blockIdx.y * blockDim.y + threadIdx.y;
+  const int j = g.jce1 - 2 * g.gl + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ice1 - 2 * g.gb + blockIdx.y * blockDim.y + threadIdx.y;
   const int k = 1 + blockIdx.z;
   if (j > g.jce2 + g.gr || i > g.ice2 + g.gt) return;
   if (s.rotllr) {   // :775-793
@@ -112,11 +113,14 @@ __global__ void __launch_bounds__(RCM_MAXT, RCM_MB_MOW) k_mo_w(const Geom g, con
   const int nt = blockDim.x * blockDim.y, tid = threadIdx.x + blockDim.x * threadIdx.y;
 #endif
   const int si = g.si; const long long sk = g.sk;
-  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
+  // owned columns plus the first ghost row / column on the LOW sides that have a neighbour rank: k_mo_uv reads pai and
+  // deltaw at (j-1, i) and (j, i-1), and advancing those columns here (bit-identical to their owner's values)
+  // replaces the exchange of pai and deltaw in every sound sub-step (the reference: Main/mod_moloch.F90:929-930)
+  const int j = g.jce1 - g.gl + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ice1 - g.gb + blockIdx.y * blockDim.y + threadIdx.y;
   if (j > g.jce2 || i > g.ice2) return;
   const int kz = g.kz, kzp1 = g.kzp1;
-  const bool interior = (j >= g.jci1 && j <= g.jci2 && i >= g.ici1 && i <= g.ici2);
+  const bool interior = (j >= 2 && j <= g.jx - 2 && i >= 2 && i <= g.iy - 2);   // interior of the global domain
   const double hx0 = L2(f.hx, j, i), hx1 = L2(f.hx, j + 1, i), hy0 = L2(f.hy, j, i), hy1 = L2(f.hy, j, i + 1);
   const double mx2 = s.rotllr ? L2(f.mx, j, i) : L2(f.mx2, j, i);   // mx (ROTLLR, :798) or mx**2 (:829)
   const double zdtrdz = s.zdtrdz, zcs2 = s.zcs2, egdts = s.egdts, rjs = (double)jsound;
@@ -309,11 +313,11 @@ void launch_mo_pre(const Geom& g, const MoFields& f, const MoScalars& s, cudaStr
 }
 void launch_mo_div(const Geom& g, const MoFields& f, const MoScalars& s, cudaStream_t st) {
   dim3 b(32, 4);
-  RCM_LAUNCH(k_mo_div, grid3(g, g.jce2 - g.jce1 + 1 + g.gl + g.gr, g.ice2 - g.ice1 + 1 + g.gb + g.gt, g.kz, b), b, st, g, f, s);
+  RCM_LAUNCH(k_mo_div, grid3(g, g.jce2 - g.jce1 + 1 + 2 * g.gl + g.gr, g.ice2 - g.ice1 + 1 + 2 * g.gb + g.gt, g.kz, b), b, st, g, f, s);
 }
 void launch_mo_w(const Geom& g, const MoFields& f, const MoScalars& s, double* zdf, int jsound, int last, cudaStream_t st) {
   dim3 b = col_block();
-  const dim3 gr = grid3(g, g.jce2 - g.jce1 + 1, g.ice2 - g.ice1 + 1, 1, b);
+  const dim3 gr = grid3(g, g.jce2 - g.jce1 + 1 + g.gl, g.ice2 - g.ice1 + 1 + g.gb, 1, b);
 #ifndef RCM_EMU
   // RCM_MO_WSM=1 selects the shared-memory scratch (24 B x (kz+1) per thread); default: global-memory scratch
   static int mode = -1;

@@ -27,6 +27,7 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
   const double ul = s.ul, xt = s.xt;
 
   const double psa = L2(f.psa, j, i), psb = L2(f.psb, j, i);
+  const double rdiv_psa = recip_for_div(psa);
   const double rpsa_c = L2(f.rpsa, j, i), rpsa_jm = L2(f.rpsa, j - 1, i), rpsa_jp = L2(f.rpsa, j + 1, i),
                rpsa_im = L2(f.rpsa, j, i - 1), rpsa_ip = L2(f.rpsa, j, i + 1);
   const double rpsb_c = L2(f.rpsb, j, i), rpsb_jm = L2(f.rpsb, j - 1, i), rpsb_jp = L2(f.rpsb, j + 1, i),

@@ -38,6 +38,7 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
   const int kz = g.kz;
 
   const double rpsa = L2(f.rpsa, j, i), psa = L2(f.psa, j, i), ps0 = L2(f.ps0, j, i);
+  const double rdiv_ps0 = recip_for_div(ps0);   // shared-denominator divisions (div_r)
   const double msfx = L2(f.msfx, j, i);
   const double dummy = 1.0 / (s.dx2 * msfx * msfx);
   const double dpsdxm = L2(f.dpsdxm, j, i), dpsdym = L2(f.dpsdym, j, i);
@@ -94,7 +95,7 @@ k_prep(const Geom g, const Fields f, const StepScalars s) {
       vcc_n = ucc_of(f.av, kn, w00, w01, w10, w11);
       const double w = L3(f.aw, j, i, kn) * rpsa;
       const double t1 = LD1(&f.twt1[kn]), t2 = LD1(&f.twt2[kn]);
-      qd_n = -L3(f.rhof0, j, i, kn) * egrav * w / ps0 -
+      qd_n = -div_r(L3(f.rhof0, j, i, kn) * egrav * w, ps0, rdiv_ps0) -
              LD1(&f.sigma[kn]) * (dpsdxm * (t1 * ucc_n + t2 * ucc_k) + dpsdym * (t1 * vcc_n + t2 * vcc_k));
     }
     P3(f.qdot, j, i, k + 1) = qd_n;
@@ -131,8 +132,9 @@ k_xkc(const Geom g, const Fields f, const StepScalars s) {
   const double u00 = L3(f.bu, j, i, k) * L2(f.rpsdb, j, i);
   const double v00 = L3(f.bv, j, i, k) * L2(f.rpsdb, j, i);
   const double md = L2(f.msfd, j, i);
-  P3(f.dub, j, i, k) = u00 / md;
-  P3(f.dvb, j, i, k) = v00 / md;
+  const double rmd = recip_for_div(md);
+  P3(f.dub, j, i, k) = div_r(u00, md, rmd);
+  P3(f.dvb, j, i, k) = div_r(v00, md, rmd);
   if (j < g.jce1 - g.gl || j > g.jce2 + g.gr || i < g.ice1 - g.gb || i > g.ice2 + g.gt) return;
   const double r01 = L2(f.rpsdb, j, i + 1), r10 = L2(f.rpsdb, j + 1, i), r11 = L2(f.rpsdb, j + 1, i + 1);
   const double rpsb = L2(f.rpsb, j, i);

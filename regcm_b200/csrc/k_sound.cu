@@ -32,8 +32,9 @@ k_snd_init(const Geom g, const Fields f, const StepScalars s) {
   const int kz = g.kz;
   const double psdotb = L2(f.psdotb, j, i);
   for (int k = 1; k <= kz; ++k) {
-    P3(f.cu, j, i, k) = L3(f.bu, j, i, k) / psdotb;
-    P3(f.cv, j, i, k) = L3(f.bv, j, i, k) / psdotb;
+    const double rpsd = recip_for_div(psdotb);
+    P3(f.cu, j, i, k) = div_r(L3(f.bu, j, i, k), psdotb, rpsd);
+    P3(f.cv, j, i, k) = div_r(L3(f.bv, j, i, k), psdotb, rpsd);
   }
   if (j <= g.jce2 + g.gr && i <= g.ice2 + g.gt) {
     const double rpsb = 1.0 / L2(f.psb, j, i);

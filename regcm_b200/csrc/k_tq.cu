@@ -37,6 +37,7 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
   const double ul = s.ul, xt = s.xt, dt = s.dt;
 
   const double psa = L2(f.psa, j, i), psb = L2(f.psb, j, i);
+  const double rdiv_psa = recip_for_div(psa);
   const double rpsa_c = L2(f.rpsa, j, i), rpsa_jm = L2(f.rpsa, j - 1, i), rpsa_jp = L2(f.rpsa, j + 1, i),
                rpsa_im = L2(f.rpsa, j, i - 1), rpsa_ip = L2(f.rpsa, j, i + 1);
   const double xmsf = L2(f.xmsf, j, i);

@@ -37,6 +37,7 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
   const double* __restrict__ bt = tr.bt[n];
 
   const double psa = L2(f.psa, j, i), psb = L2(f.psb, j, i);
+  const double rdiv_psa = recip_for_div(psa);
   const double rpsa_c = L2(f.rpsa, j, i), rpsa_jm = L2(f.rpsa, j - 1, i), rpsa_jp = L2(f.rpsa, j + 1, i),
                rpsa_im = L2(f.rpsa, j, i - 1), rpsa_ip = L2(f.rpsa, j, i + 1);
   const double xmsf = L2(f.xmsf, j, i);
@@ -57,8 +58,8 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
                  va11 = L3(f.av, j + 1, i + 1, k) * m11;
     const double uavg1 = ua01 + ua00, uavg2 = ua11 + ua10;
     const double vavg1 = va10 + va00, vavg2 = va11 + va01;
-    const double f1 = 0.5 * ul * (uavg2 + uavg1) / psa;
-    const double f2 = 0.5 * ul * (vavg2 + vavg1) / psa;
+    const double f1 = div_r(0.5 * ul * (uavg2 + uavg1), psa, rdiv_psa);
+    const double f2 = div_r(0.5 * ul * (vavg2 + vavg1), psa, rdiv_psa);
     const double xdsk = LD1(&f.xds[k]);
     const double svv_n = (k < kz) ? L3(f.qdot, j, i, k + 1) : 0.0;
     const double ac_c = L3(a1, j, i, k);
