@@ -372,7 +372,10 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
 
 // ---------------------------------------------------------------------------
 template <int CQ_MODE>   // StepScalars::cq_mode (negative-moisture repair), compile-time
-__global__ void __launch_bounds__(RCM_MAXT, 3)  // 168 registers: no spills (80 spilled 300 B)
+#ifndef RCM_MB_HTQ
+#define RCM_MB_HTQ 3
+#endif
+__global__ void __launch_bounds__(RCM_MAXT, RCM_MB_HTQ)  // 3: 168 registers, no spills (80 spilled 300 B)
 k_h_tq(const Geom g, const Fields f, const StepScalars s) {
   const int si = g.si;
   const long long sk = g.sk;
