@@ -373,6 +373,10 @@ def run_gpu(args):
         for fid, v in pinned_out.items():
             core.get_state_async(fid, capi.LEVEL_A, v, out_lbub[fid][0], out_lbub[fid][1])
         core.get_state_wait()
+        # ... and the staging path (first use creates the copy stream and the device landing buffer)
+        for fid, v in pinned_in.items():
+            core.stage_bdy_async(fid, v, lb=(lb[0], lb[1], 1))
+        core.stage_wait()
         barrier()
         t0 = time.perf_counter()
         for fid, v in pinned_in.items():   # H2D of the next ICBC record, queued on the library's copy stream
