@@ -38,7 +38,7 @@ int orc_array(void* h, const char* name, double** data, int32_t lb[4], int32_t n
   T3(uten) T3(vten) T3(ppten) T3(wten) T3(udyn) T3(vdyn) T3(qdot) T3(cr)
   T2(s_estore) T2(s_astore) T2(s_wpval) T2(tmask)
   T3(m_u) T3(m_v) T3(m_w) T3(m_s) T3(m_fmz) T3(m_fmzf) T3(m_tetav) T3(m_pai) T3(m_t) T4(m_qx) T3(m_ux) T3(m_vx) T3(m_wx)
-  T2(mx2) T2(rmu) T2(rmv) T2(msfu) T2(msfv) T3(xkc)
+  T2(mx2) T2(rmu) T2(rmv) T2(msfu) T2(msfv) T3(xkc) T3(th) T3(tha) T3(thten)
   if (s == "chia0" && o->ntr > 0) v3(v, o->chia[0]); else if (s == "chib0" && o->ntr > 0) v3(v, o->chib[0]); else
   if (s == "chic0" && o->ntr > 0) v3(v, o->chic[0]); else
   return RCM_ERR_ARG;
@@ -76,6 +76,11 @@ int orc_call(void* h, const char* routine, double arg) {
     o->start_advect();
     o->hadvuv(o->udyn, o->vdyn, o->ax_ud, o->ax_vd);
     o->vadvuv(o->udyn, o->vdyn, o->ax_uc, o->ax_vc);
+  } else if (s == "advect_theta") {   // ithadv = 1 (Main/mod_tendency.F90:1348-1357): hadvt + vadv3d on theta of the last tend()
+    o->thten.fill(0.0);
+    o->start_advect();
+    o->hadvt(o->thten, o->th);
+    o->vadv3d(o->thten, o->tha, o->kz, 0);
   } else if (s == "sound") {
     o->sound();
   } else if (s == "wafone_tetav") {   // one wafone call on mo_atm%tetav with time step arg (Main/mod_moloch.F90:1098-1361)

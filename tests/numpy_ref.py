@@ -502,3 +502,42 @@ def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc,
     nb = np.maximum(c(chia) + 0.53 * d, 0.0)
     na = np.maximum(fcp + (0.53 - 1.0) * d, 0.0)
     return fc, na, nb
+
+
+# ---------------------------------------------------------------------------------------------------------
+def advect_theta(th, tha, umc, vmc, psa, xmsf, svv, twt, xds, ul, t_extrema, idx, kz, upstream=True, stability_enhance=True):
+    """hadvt (Main/mod_advection.F90:311-394) of the uncoupled potential temperature `th` with its local-extrema
+    limiter — the i-direction test first, then the j-direction test, both on the flux left by the previous test —
+    followed by vadv3d(ind = 0, nk = kz) (:743-753) of the coupled `tha`, as `advection` calls them with ithadv = 1
+    (Main/mod_tendency.F90:1348-1357).  idx = (jci1, jci2, ici1, ici2).  Returns thten on that box."""
+    j1, j2, i1, i2 = idx
+    K = (1, kz)
+
+    def c(a, dj=0, di=0, k=K):
+        return a.s((j1 + dj, j2 + dj), (i1 + di, i2 + di), k) if len(a.lb) == 3 else a.s((j1 + dj, j2 + dj), (i1 + di, i2 + di))[:, :, None]
+
+    uavg1 = c(umc, 0, 1) + c(umc, 0, 0)      # start_advect (:109-122)
+    uavg2 = c(umc, 1, 1) + c(umc, 1, 0)
+    vavg1 = c(vmc, 1, 0) + c(vmc, 0, 0)
+    vavg2 = c(vmc, 1, 1) + c(vmc, 0, 1)
+    f, fjm, fjp, fim, fip = c(th), c(th, -1, 0), c(th, 1, 0), c(th, 0, -1), c(th, 0, 1)
+    ps = c(psa)
+    if upstream:
+        f1 = 0.5 * ul * (uavg2 + uavg1) / ps
+        f2 = 0.5 * ul * (vavg2 + vavg1) / ps
+        fx1, fx2 = (1.0 + f1) * fjm + (1.0 - f1) * f, (1.0 + f1) * f + (1.0 - f1) * fjp
+        fy1, fy2 = (1.0 + f2) * fim + (1.0 - f2) * f, (1.0 + f2) * f + (1.0 - f2) * fip
+    else:
+        fx1, fx2, fy1, fy2 = fjm + f, f + fjp, fim + f, f + fip
+    fg = -c(xmsf) * (uavg2 * fx2 - uavg1 * fx1 + vavg2 * fy2 - vavg1 * fy1)
+    if stability_enhance:
+        for lo, hi in ((fim, fip), (fjm, fjp)):        # i-direction first (SURVEY B13)
+            big = np.abs(hi + lo - 2.0 * f) / ps > t_extrema
+            fg = np.where(big & (f > hi) & (f > lo), np.minimum(fg, 0.0), fg)
+            fg = np.where(big & (f < hi) & (f < lo), np.maximum(fg, 0.0), fg)
+    ten = fg.copy()
+    fx = c(svv, k=(2, kz)) * (twt.s((2, kz), 1)[None, None, :] * c(tha, k=(2, kz)) + twt.s((2, kz), 2)[None, None, :] * c(tha, k=(1, kz - 1)))
+    xd = xds.s((1, kz))[None, None, :]
+    ten[:, :, :-1] -= fx * xd[:, :, :-1]
+    ten[:, :, 1:] += fx * xd[:, :, 1:]
+    return ten

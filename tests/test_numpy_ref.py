@@ -117,3 +117,27 @@ def test_tracer_step_numpy_vs_oracle(kw):
     sc = np.abs(want_c).max()
     assert np.abs(fc - want_c).max() <= 1e-12 * sc
     assert np.abs(na - want_a).max() <= 1e-12 * sc and np.abs(nb - want_b).max() <= 1e-12 * sc
+
+
+@pytest.mark.parametrize("kw", [{}, {"upstream_mode": 0}, {"stability_enhance": 0}, {"t_extrema": 1.0e-3}], ids=["default", "centred", "nolimiter", "limiter-active"])
+def test_advect_theta_numpy_vs_oracle(kw):
+    """hadvt with the local-extrema limiter (Main/mod_advection.F90:311-394) + vadv3d (:743-753) on potential temperature,
+    whole interior, on the flow of the oracle's 4th step.  `limiter-active` lowers t_extrema so that the limiter fires."""
+    case = synth.make_case("small", **kw)
+    o = pyoracle.make_oracle(case.cfg)
+    synth.load_case(o, case)
+    o.step(4)
+    nr.call(o, "advect_theta")
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    idx = (2, jx - 2, 2, iy - 2)    # jci1, jci2, ici1, ici2
+    t = {n: nr.tap(o, n) for n in ("th", "tha", "ax_umc", "ax_vmc", "psa", "xmsf", "qdot", "twt", "xds", "thten")}
+    got = nr.advect_theta(t["th"], t["tha"], t["ax_umc"], t["ax_vmc"], t["psa"], t["xmsf"], t["qdot"], t["twt"], t["xds"], nr.scalar(o, "ul"),
+                          case.cfg.t_extrema, idx, kz, upstream=case.cfg.upstream_mode != 0, stability_enhance=case.cfg.stability_enhance != 0)
+    want = t["thten"].s((idx[0], idx[1]), (idx[2], idx[3]), (1, kz))
+    sc = np.abs(want).max()
+    assert sc > 0 and np.abs(got - want).max() <= 1e-12 * sc
+    if kw.get("t_extrema"):
+        # the limiter did act: without it the result differs
+        free = nr.advect_theta(t["th"], t["tha"], t["ax_umc"], t["ax_vmc"], t["psa"], t["xmsf"], t["qdot"], t["twt"], t["xds"], nr.scalar(o, "ul"),
+                               case.cfg.t_extrema, idx, kz, upstream=True, stability_enhance=False)
+        assert np.abs(free - want).max() > 1e-6 * sc
