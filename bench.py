@@ -378,11 +378,14 @@ def run_gpu(args):
             core.stage_bdy_async(fid, v, lb=(lb[0], lb[1], 1))
         core.stage_wait()
         barrier()
+        probe = os.environ.get("RCM_E2E_PROBE", "")   # diagnostic runs only: "nostage" / "noexport" drop one transfer
         t0 = time.perf_counter()
         for fid, v in pinned_in.items():   # H2D of the next ICBC record, queued on the library's copy stream
-            core.stage_bdy_async(fid, v, lb=(lb[0], lb[1], 1))
+            if "nostage" not in probe:
+                core.stage_bdy_async(fid, v, lb=(lb[0], lb[1], 1))
         for fid, v in pinned_out.items():  # D2H of the state the previous interval produced (device snapshot first)
-            core.get_state_async(fid, capi.LEVEL_A, v, out_lbub[fid][0], out_lbub[fid][1])
+            if "noexport" not in probe:
+                core.get_state_async(fid, capi.LEVEL_A, v, out_lbub[fid][0], out_lbub[fid][1])
         last = None
         for _ in range(args.steps):
             core.step_async(1)
