@@ -364,6 +364,25 @@ int rcm_dyn_get_work(rcm_dyn* h, int work_id, double* a, const int32_t lb[3],
  * (or a negative RCM_ERR_*). */
 int rcm_dyn_get_table(rcm_dyn* h, int table_id, double* out, int n);
 
+/* Restart (the SAV path): `write_savefile` / `read_savefile` (Main/mod_savefile.F90:564-1264) keep their
+ * NetCDF layer on the host and obtain / hand back the dynamical state through rcm_dyn_get_state / rcm_dyn_set_state
+ * (atm1_u ... atm2_qx, atm1_w/pp, psa, psb; atm_u ... atm_pai, ps for idynamic = 3; the tracers as RCM_F_CHI + n).
+ * What the SAV file holds beside the prognostics and this library owns:
+ *   RCM_R_DSTOR, RCM_R_HSTOR  dstor, hstor of the split-explicit scheme (idynamic = 1; cross points, nsplit planes;
+ *                             dstor_io / hstor_io, mod_savefile.F90:326-327)
+ *   RCM_R_TMASK               the 13 x 13 mask of the upper radiative boundary condition (idynamic = 2, ifupr = 1;
+ *                             `tmask`, mod_savefile.F90:30), passed as a (13,13,1) array
+ * A restart is: rcm_dyn_create; rcm_dyn_set_static; rcm_dyn_set_bdy with the boundary records that bracket the restart
+ * date (as init_bdy reads them again, Main/mod_bdycod.F90:283-330); rcm_dyn_init; rcm_dyn_set_state of every
+ * prognostic at both levels; rcm_dyn_set_restart of the arrays above; rcm_dyn_set_clock with the step count and the
+ * seconds since boundary record b0 that rcm_dyn_diag reported when the state was saved (ktau / xbctime of the SAV
+ * file).  rcm_dyn_set_clock also refreshes the ghost rows of the restored state on a decomposed domain (collective).
+ * The continued run equals the uninterrupted one bit for bit (tests/test_restart.py). */
+enum rcm_restart { RCM_R_DSTOR = 0, RCM_R_HSTOR = 1, RCM_R_TMASK = 2 };
+int rcm_dyn_get_restart(rcm_dyn* h, int id, double* a, const int32_t lb[3], const int32_t ub[3]);
+int rcm_dyn_set_restart(rcm_dyn* h, int id, const double* a, const int32_t lb[3], const int32_t ub[3]);
+int rcm_dyn_set_clock(rcm_dyn* h, int64_t lcount, double xbctime);
+
 int rcm_dyn_diag(rcm_dyn* h, rcm_diag* out);
 int rcm_dyn_last_error(rcm_dyn* h, char* buf, int len);
 

@@ -19,6 +19,7 @@ import numpy as np
 # enum rcm_field / rcm_static / rcm_work (include/regcm_dyn.h)
 F_U, F_V, F_T, F_QV, F_QC, F_PP, F_W, F_PS, F_PAI = range(9)
 F_CHI = 16       # tracer n is field F_CHI + n
+R_DSTOR, R_HSTOR, R_TMASK = range(3)
 MAXTR = 8
 FIELD_NAMES = ("u", "v", "t", "qv", "qc", "pp", "w", "ps", "pai")
 S_HT, S_MSFX, S_MSFD, S_CORIOL, S_XLAT, S_XLON, S_DLAT, S_SIGMA, S_MSFU, S_MSFV, S_ULAT, S_VLAT = range(12)
@@ -185,6 +186,10 @@ class CoreLib:
             "set_phys_tend": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
             "clear_phys_tend": ([vp], C.c_int),
             "get_slice": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
+            # restart
+            "get_restart": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
+            "set_restart": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
+            "set_clock": ([vp, C.c_int64, C.c_double], C.c_int),
             # handle-less, allocation-free operator (device pointers): include/regcm_dyn.h
             "negq_repair_static": ([C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p], C.c_int),
         }.items():
@@ -341,6 +346,24 @@ class DynCore:
         out = np.zeros(tuple(ub[d] - lb[d] + 1 for d in range(3)), dtype=np.float64, order="F")
         self._check(self.lib.get_work(self.h, wid, out.ctypes.data_as(_DP), *_bounds(lb, ub)))
         return out
+
+    # -- restart: what the SAV file holds beside the prognostics (include/regcm_dyn.h) ------------------------------
+    def _restart_shape(self, rid: int):
+        return (13, 13, 1) if rid == R_TMASK else (self.jx - 1, self.iy - 1, self.cfg.nsplit)
+
+    def get_restart(self, rid: int) -> np.ndarray:
+        shp = self._restart_shape(rid)
+        out = np.zeros(shp, dtype=np.float64, order="F")
+        self._check(self.lib.get_restart(self.h, rid, out.ctypes.data_as(_DP), *_bounds((1, 1, 1), shp)))
+        return out
+
+    def set_restart(self, rid: int, a: np.ndarray, lb=(1, 1, 1)):
+        a = self._f(a)
+        ub = tuple(lb[d] + a.shape[d] - 1 for d in range(3))
+        self._check(self.lib.set_restart(self.h, rid, a.ctypes.data_as(_DP), *_bounds(lb, ub)))
+
+    def set_clock(self, lcount: int, xbctime: float):
+        self._check(self.lib.set_clock(self.h, int(lcount), float(xbctime)))
 
     def get_table(self, tid: int) -> np.ndarray:
         """Vertical-mode table `tid` (enum rcm_table) as a Fortran-ordered array."""

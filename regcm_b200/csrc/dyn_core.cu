@@ -225,6 +225,7 @@ static int mo_bdyin(rcm_dyn* h);
 static int mo_bdyval(rcm_dyn* h);
 static double* mo_state_ptr(rcm_dyn* h, int field);
 static double* mo_work_ptr(rcm_dyn* h, int id);
+static int mo_exch(rcm_dyn* h, const std::vector<HaloField>& fl, int width);
 
 static int fail(rcm_dyn* h, int code, const std::string& msg) {
   if (h) h->err = msg;
@@ -2174,6 +2175,77 @@ extern "C" int rcm_dyn_diag(rcm_dyn* h, rcm_diag* d) {
   if (h->moloch) {   // max, min of ps over the interior of the last step (Main/mod_moloch.F90:437-441), reduced on the device
     d->ps_max = h->ps_max; d->ps_min = h->ps_min;
   }
+  return RCM_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Restart support (what write_savefile / read_savefile need beside the prognostic state)
+static int restart_array(rcm_dyn* h, int id, double** p, int* nk) {
+  *p = nullptr; *nk = 0;
+  if (id == RCM_R_DSTOR || id == RCM_R_HSTOR) {
+    if (!h->hydro) return fail(h, RCM_ERR_ARG, "dstor / hstor exist for idynamic = 1 only");
+    *p = (id == RCM_R_DSTOR) ? h->f.dstor : h->f.hstor; *nk = h->cfg.nsplit;
+    return RCM_OK;
+  }
+  return fail(h, RCM_ERR_ARG, "bad restart array id");
+}
+extern "C" int rcm_dyn_get_restart(rcm_dyn* h, int id, double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a) return RCM_ERR_ARG;
+  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_get_restart before rcm_dyn_init");
+  cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  if (id == RCM_R_TMASK) {
+    if (h->hydro || h->moloch) return fail(h, RCM_ERR_ARG, "tmask exists for idynamic = 2 only");
+    CUDA_OK(cudaStreamSynchronize(h->st));
+    CUDA_OK(cudaMemcpy(a, h->f.tmask, 169 * sizeof(double), cudaMemcpyDeviceToHost));
+    return RCM_OK;
+  }
+  double* p; int nk;
+  const int rc = restart_array(h, id, &p, &nk);
+  if (rc) return rc;
+  return download3(h, p, a, lb, ub, nk);
+}
+extern "C" int rcm_dyn_set_restart(rcm_dyn* h, int id, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!h || !a) return RCM_ERR_ARG;
+  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_set_restart before rcm_dyn_init");
+  cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  if (id == RCM_R_TMASK) {
+    if (h->hydro || h->moloch) return fail(h, RCM_ERR_ARG, "tmask exists for idynamic = 2 only");
+    CUDA_OK(cudaStreamSynchronize(h->st));
+    CUDA_OK(cudaMemcpy(h->f.tmask, a, 169 * sizeof(double), cudaMemcpyHostToDevice));
+    return RCM_OK;
+  }
+  double* p; int nk;
+  const int rc = restart_array(h, id, &p, &nk);
+  if (rc) return rc;
+  return upload3(h, p, a, lb, ub, nk);
+}
+// ktau and xbctime of the saved run; alarms as the timer would have left them; halo of the restored state
+extern "C" int rcm_dyn_set_clock(rcm_dyn* h, int64_t lcount, double xbctime) {
+  if (!h || lcount < 0) return RCM_ERR_ARG;
+  if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_set_clock before rcm_dyn_init");
+  cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  h->lcount = lcount;
+  h->model_time = lcount * (int64_t)h->dtsec;
+  h->xbctime = xbctime;
+  if (!h->moloch) h->dt = (lcount >= 2) ? h->dt2 : h->dtsec;   // leapfrog start-up, Main/mod_tendency.F90:611-616 (MOLOCH: dt = dtsec)
+  h->day_lastact = (h->model_time / 86400) * 86400; h->day_now = h->day_lastact;
+  const int64_t nb = (int64_t)h->dtbdys;
+  h->bdy_lastact = (h->model_time / nb) * nb; h->bdy_now = h->bdy_lastact;
+  int rc = RCM_OK;
+  if (h->cfg.nproc > 1) {
+    if (h->moloch) {
+      MoFields& m = h->mf;
+      const int kz = h->g.kz;
+      rc = mo_exch(h, {{m.u, kz, 1}, {m.v, kz, 1}, {m.w, h->g.kzp1, 0}, {m.t, kz, 0}, {m.qv, kz, 0}, {m.qc, kz, 0}, {m.pai, kz, 0}}, RCM_HALO);
+    } else {
+      rc = h->hydro ? exch_h_state(h) : exch_state(h);
+    }
+    if (rc) return rc;
+  }
+  CUDA_OK(cudaStreamSynchronize(h->st));
   return RCM_OK;
 }
 

@@ -59,6 +59,8 @@ def main():
     ap.add_argument("--iboudy", type=int, default=-1)
     ap.add_argument("--idynamic", type=int, default=0, help="override the case's core (1 = hydrostatic)")
     ap.add_argument("--cfg", action="append", default=[], help="name=value override of an rcm_cfg member")
+    ap.add_argument("--restart-at", type=int, default=0, help="stop after this many steps, carry the OWNED points of the state into "
+                    "a new handle through the restart entry points, continue there")
     ap.add_argument("--work", action="store_true", help="also dump the per-step work arrays")
     ap.add_argument("--spiky-tracers", action="store_true", help="tracers with sharp edges (drives their negative fix)")
     ap.add_argument("--sharp-q", action="store_true", help="moisture with sharp fronts (drives the negative-q repair)")
@@ -136,7 +138,45 @@ def main():
         for lv in (capi.LEVEL_A, capi.LEVEL_B):
             core.set_state(capi.F_QV, lv, qv)
             core.set_state(capi.F_QC, lv, qc)
-    core.step(args.steps)
+    if args.restart_at > 0:
+        # what write_savefile / read_savefile would do on every rank (tests/test_restart.py), owned points only:
+        # rcm_dyn_set_clock refreshes the ghost rows of the restored state
+        from tests.test_restart import fields_of
+        core.step(args.restart_at)
+        flds, levels = fields_of(cfg)
+        d = core.diag()
+        sav = {}
+        for f in flds:
+            lb, ub = owned_bounds(core, f)
+            for lv in levels:
+                sav[(f, lv)] = (lb, core.get_state(f, lv, lb=lb, ub=ub))
+        aux = {}
+        j1, j2, i1, i2 = core.tile()
+        clb = (j1, i1, 1)
+        cub = lambda nk: (min(j2, cfg.jx - 1), min(i2, cfg.iy - 1), nk)
+        if cfg.idynamic == 1:
+            for rid in (capi.R_DSTOR, capi.R_HSTOR):
+                a = np.zeros(tuple(cub(cfg.nsplit)[q] - clb[q] + 1 for q in range(3)), order="F")
+                assert lib.get_restart(core.h, rid, a.ctypes.data_as(C.POINTER(C.c_double)), *capi._bounds(clb, cub(cfg.nsplit))) == 0
+                aux[rid] = a
+        if cfg.idynamic == 2:
+            aux[capi.R_TMASK] = core.get_restart(capi.R_TMASK)
+        core.close()
+        if args.lib == "cuda":
+            box = [capi.nccl_unique_id(lib) if rank == 0 else None]
+            dist.broadcast_object_list(box, src=0)
+            uid = box[0]
+        core = capi.DynCore(lib, cfg)
+        core.comm_init(uid)
+        synth.load_case(core, case, stage_next=True)
+        for (f, lv), (lb, a) in sav.items():
+            core.set_state(f, lv, a, lb=lb)
+        for rid, a in aux.items():
+            core.set_restart(rid, a, lb=(1, 1, 1) if rid == capi.R_TMASK else clb)
+        core.set_clock(d.lcount, d.xbctime)
+        core.step(args.steps - args.restart_at)
+    else:
+        core.step(args.steps)
     out = {"tile": np.array(core.tile())}
     moloch = cfg.idynamic == 3
     tracers = tuple(capi.F_CHI + n for n in range(cfg.ntr))

@@ -203,6 +203,32 @@ def test_hydro_multirank_record_change_and_data_means(emu_lib, tmp_path):
     compare(glob, ref, 1e-11)
 
 
+# ---------------------------------------------------------------------------- restart
+def test_multirank_restart_nh(emu_lib, tmp_path):
+    """Every rank saves the points it owns, a new set of handles restores them (rcm_dyn_set_clock refreshes the ghost
+    rows) and continues: equal to the uninterrupted single-rank run as in the plain multi-rank test."""
+    steps = 7
+    run_ranks(4, tmp_path, ["--case", "tiny", "--steps", str(steps), "--cpus-j", "2", "--cpus-i", "2", "--restart-at", "3"])
+    cfg, ref = single_rank(emu_lib, "tiny", steps)
+    compare(assemble(tmp_path, 4, cfg), ref, 1e-12)
+
+
+def test_multirank_restart_hydro_and_moloch(emu_lib, tmp_path):
+    steps = 6
+    d1 = tmp_path / "hy"; d1.mkdir()
+    run_ranks(4, d1, ["--case", "tiny", "--idynamic", "1", "--steps", str(steps), "--cpus-j", "2", "--cpus-i", "2", "--restart-at", "3"])
+    cfg, ref, _ = single_rank_hydro(emu_lib, "tiny", steps)
+    glob, _ = assemble_hydro(d1, 4, cfg)
+    for key, a in glob.items():
+        np.testing.assert_array_equal(a, ref[key], err_msg=str(key))
+    d2 = tmp_path / "mo"; d2.mkdir()
+    run_ranks(4, d2, ["--case", "tinym", "--steps", "4", "--cpus-j", "2", "--cpus-i", "2", "--restart-at", "2"])
+    cfg, ref, _ = single_rank_moloch(emu_lib, "tinym", 4)
+    glob, _ = assemble_moloch(d2, 4, cfg)
+    for f in MOLOCH_FIELDS:
+        np.testing.assert_array_equal(glob[f], ref[f] if ref[f].ndim == 3 else ref[f][:, :, None], err_msg=capi.FIELD_NAMES[f])
+
+
 # ---------------------------------------------------------------------------- tracers (SURVEY §8 f3)
 @pytest.mark.parametrize("idynamic", [2, 1])
 def test_tracers_multirank_match_single_rank(emu_lib, tmp_path, idynamic):
