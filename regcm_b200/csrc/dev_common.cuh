@@ -154,12 +154,12 @@ __device__ __forceinline__ double hflux(const bool up, const double f1, const do
 // 566-596): i-direction first, then j-direction (order matters).
 __device__ __forceinline__ double extrema_limit(double fg, const double fc, const double fjm, const double fjp,
                                                 const double fim, const double fip, const double scale,
-                                                const double thr) {
-  if (fabs(fip + fim - 2.0 * fc) / scale > thr) {
+                                                const double rscale /* recip_for_div(scale) */, const double thr) {
+  if (div_r(fabs(fip + fim - 2.0 * fc), scale, rscale) > thr) {
     if ((fc > fip) && (fc > fim)) fg = fmin(fg, 0.0);
     else if ((fc < fip) && (fc < fim)) fg = fmax(fg, 0.0);
   }
-  if (fabs(fjp + fjm - 2.0 * fc) / scale > thr) {
+  if (div_r(fabs(fjp + fjm - 2.0 * fc), scale, rscale) > thr) {
     if ((fc > fjp) && (fc > fjm)) fg = fmin(fg, 0.0);
     else if ((fc < fjp) && (fc < fjm)) fg = fmax(fg, 0.0);
   }

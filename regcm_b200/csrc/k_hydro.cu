@@ -448,7 +448,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
       const double t_c = at * rpsa_c, t_jm = L3(f.at, j - 1, i, k) * rpsa_jm, t_jp = L3(f.at, j + 1, i, k) * rpsa_jp,
                    t_im = L3(f.at, j, i - 1, k) * rpsa_im, t_ip = L3(f.at, j, i + 1, k) * rpsa_ip;
       double fg = hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, t_c, t_jm, t_jp, t_im, t_ip);
-      if (se) fg = extrema_limit(fg, t_c, t_jm, t_jp, t_im, t_ip, psa, s.t_extrema);
+      if (se) fg = extrema_limit(fg, t_c, t_jm, t_jp, t_im, t_ip, psa, rdiv_psa, s.t_extrema);
       double ten = 0.0 + fg;
       // vadv3d ind = 1: potential-temperature-like interpolation to full levels, level-b pressures
       if (k >= 2) ten = ten + dq_k * xdsk;
@@ -505,7 +505,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
                    q_jp = fmax(L3(f.aqv, j + 1, i, k) * rpsa_jp, minqq), q_im = fmax(L3(f.aqv, j, i - 1, k) * rpsa_im, minqq),
                    q_ip = fmax(L3(f.aqv, j, i + 1, k) * rpsa_ip, minqq);
       double fg = hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, q_c, q_jm, q_jp, q_im, q_ip);
-      if (se) fg = extrema_limit(fg, q_c, q_jm, q_jp, q_im, q_ip, fmax(q_c, dlowval), s.q_rel_extrema);
+      if (se) { const double qs = fmax(q_c, dlowval); fg = extrema_limit(fg, q_c, q_jm, q_jp, q_im, q_ip, qs, recip_for_div(qs), s.q_rel_extrema); }
       double ten = fg;
       if (k >= 2) ten = ten + fl_qv_k * xdsk;
       double fl_n = 0.0;
