@@ -163,7 +163,8 @@ struct rcm_dyn {
   cudaEvent_t ev_stage = nullptr;
   bool stage_pending = false;
   cudaStream_t st_b = nullptr, st_c = nullptr;  // side streams: the three slow-tendency kernels are independent
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_jb = nullptr, ev_jc = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_jb = nullptr, ev_jc = nullptr, ev_prep = nullptr;
+  bool overlap_head = true;  // RCM_OVERLAP2=0: k_xkc after k_prep and k_snd_init after the slow kernels instead of beside them
   int64_t launches = 0;
   double last_ms = 0;
   Halo halo;
@@ -392,6 +393,7 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   if (const char* e = std::getenv("RCM_KC_TQ")) g.kc_tq = std::max(1, std::atoi(e));
   if (const char* e = std::getenv("RCM_KC_PPW")) g.kc_ppw = std::max(1, std::atoi(e));
   if (const char* e = std::getenv("RCM_OVERLAP")) h->overlap_slow = std::atoi(e) != 0;
+  if (const char* e = std::getenv("RCM_OVERLAP2")) h->overlap_head = std::atoi(e) != 0;
   g.pfd_wfwd = 4; g.pfd_wback = 1;   // measured on C4: wfwd 5.50 / 5.28 / 5.05 / 4.98 ms at distance 1 / 2 / 3 / 4, wback 4.86 / 4.96 / 5.19 / 5.57
   if (const char* e = std::getenv("RCM_PFD")) g.pfd = g.pfd_wfwd = g.pfd_wback = std::max(0, std::min(8, std::atoi(e)));
   if (const char* e = std::getenv("RCM_PFD_WFWD")) g.pfd_wfwd = std::max(0, std::min(12, std::atoi(e)));
@@ -412,7 +414,7 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
     cudaStreamCreateWithFlags(&h->st_b, cudaStreamNonBlocking);
     cudaStreamCreateWithFlags(&h->st_c, cudaStreamNonBlocking);
     cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
-    cudaEventCreate(&h->ev_fork); cudaEventCreate(&h->ev_jb); cudaEventCreate(&h->ev_jc);
+    cudaEventCreate(&h->ev_fork); cudaEventCreate(&h->ev_jb); cudaEventCreate(&h->ev_jc); cudaEventCreate(&h->ev_prep);
     h->halo.init(g, c.nproc, c.myid, cj, ci);
     *out = h;
     return RCM_OK;
@@ -498,7 +500,7 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   cudaStreamCreateWithFlags(&h->st_b, cudaStreamNonBlocking);
   cudaStreamCreateWithFlags(&h->st_c, cudaStreamNonBlocking);
   cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
-  cudaEventCreate(&h->ev_fork); cudaEventCreate(&h->ev_jb); cudaEventCreate(&h->ev_jc);
+  cudaEventCreate(&h->ev_fork); cudaEventCreate(&h->ev_jb); cudaEventCreate(&h->ev_jc); cudaEventCreate(&h->ev_prep);
   {
     const char* e = std::getenv("RCM_UV_TMA");
     if (!e || std::atoi(e) != 0) h->uv_maps = uv_tma_setup(g, f, h->off3, h->ni_pad);
@@ -1567,8 +1569,18 @@ static int tend_hydro(rcm_dyn* h) {
     TIMED(KID_H_PS, 2, (launch_h_ps(g, f, h->st), launch_h_rimcopy(g, f, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, h->st)));
     TIMED(KID_HALO, 0, rc = exch_h_psdot(h));
     if (rc) return rc;
-    TIMED(KID_H_PREP, 1, launch_h_prep(g, f, s, h->st));
-    TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
+    if (!h->prof_on && h->overlap_slow && h->overlap_head) {   // as in tend(): k_xkc (level b) beside k_h_prep (level a)
+      CUDA_OK(cudaEventRecord(h->ev_fork, h->st));
+      CUDA_OK(cudaStreamWaitEvent(h->st_b, h->ev_fork, 0));
+      launch_xkc(g, f, s, h->st_b);
+      CUDA_OK(cudaEventRecord(h->ev_jb, h->st_b));
+      launch_h_prep(g, f, s, h->st);
+      CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jb, 0));
+      h->launches += 2;
+    } else {
+      TIMED(KID_H_PREP, 1, launch_h_prep(g, f, s, h->st));
+      TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
+    }
   }
   if (h->head_only) { h->mid_step = true; return RCM_OK; }
   h->mid_step = false;
@@ -1642,9 +1654,21 @@ static int tend(rcm_dyn* h) {
     CUDA_OK(cudaMemsetAsync(h->tr.nq_cnt, 0, (size_t)h->tr.ntr * g.kz * sizeof(int), h->st));
     CUDA_OK(cudaMemsetAsync(h->tr.negcnt, 0, sizeof(unsigned long long), h->st));
   }
+  const bool side = !h->prof_on && h->overlap_slow && h->overlap_head;
   if (!h->mid_step) {   // head of `tend`: everything physical_parametrizations depends on (Main/mod_tendency.F90:230-270)
-    TIMED(KID_PREP, 1, launch_prep(g, f, s, h->st));
-    TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
+    if (side) {
+      // k_xkc reads level b only, k_prep level a only, disjoint outputs: side by side (k_xkc is memory-bound, k_prep issue-bound)
+      CUDA_OK(cudaEventRecord(h->ev_fork, h->st));
+      CUDA_OK(cudaStreamWaitEvent(h->st_b, h->ev_fork, 0));
+      launch_xkc(g, f, s, h->st_b);
+      CUDA_OK(cudaEventRecord(h->ev_jb, h->st_b));
+      launch_prep(g, f, s, h->st);
+      CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jb, 0));
+      h->launches += 2;
+    } else {
+      TIMED(KID_PREP, 1, launch_prep(g, f, s, h->st));
+      TIMED(KID_XKC, 1, launch_xkc(g, f, s, h->st));
+    }
   }
   if (h->head_only) { h->mid_step = true; return RCM_OK; }
   h->mid_step = false;
@@ -1664,13 +1688,16 @@ static int tend(rcm_dyn* h) {
     if (h->ppw_tma) launch_ppw_tma(g, f, s, h->st_b); else launch_ppw(g, f, s, h->st_b);
     if (h->uv_maps) launch_uv_tma(g, f, s, h->st_c, h->uv_maps); else launch_uv(g, f, s, h->st_c);
     h->launches += 3;
+    // k_snd_init reads level b and the reference state only and writes the acoustic work arrays: behind k_uv (the
+    // shortest of the three) it fills memory bandwidth the issue-bound slow kernels leave idle
+    if (side) { launch_snd_init(g, f, s, h->st_c); h->launches += 1; }
     CUDA_OK(cudaEventRecord(h->ev_jb, h->st_b));
     CUDA_OK(cudaEventRecord(h->ev_jc, h->st_c));
     CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jb, 0));
     CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jc, 0));
   }
   if (h->tr.ntr > 0) TIMED(KID_TR, 1, launch_tr(g, f, h->tr, s, h->st));
-  TIMED(KID_SND_INIT, 1, launch_snd_init(g, f, s, h->st));
+  if (!side) TIMED(KID_SND_INIT, 1, launch_snd_init(g, f, s, h->st));
   TIMED(KID_HALO, 0, rc = exch_uvten(h));  // + the first cppd, ct of the step and the moisture forecast
   if (rc) return rc;
   // negative-moisture repair (Main/mod_tendency.F90:381-393): before k_snd_wback first reads the filtered qv
@@ -2335,7 +2362,7 @@ extern "C" int rcm_dyn_destroy(rcm_dyn* h) {
   if (h->ev_stage) cudaEventDestroy(h->ev_stage);
   if (h->st_b) cudaStreamDestroy(h->st_b);
   if (h->st_c) cudaStreamDestroy(h->st_c);
-  for (cudaEvent_t e : {h->ev_fork, h->ev_jb, h->ev_jc}) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : {h->ev_fork, h->ev_jb, h->ev_jc, h->ev_prep}) if (e) cudaEventDestroy(e);
   delete h;
   return RCM_OK;
 }
