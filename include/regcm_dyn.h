@@ -194,7 +194,8 @@ typedef struct rcm_cfg {
   int32_t iboudy;   /* 0 fixed, 1 linear relax., 5 exponential relax., 4 sponge + inflow/outflow;
                      * idynamic 1, 2 also: 2 time-dependent without relaxation, 3 = 2 + inflow/outflow
                      * (Main/mod_tendency.F90:909-983,1462-1500; Main/mod_bdycod.F90:237-250,1809-1947,2591-3122) */
-  int32_t idiffu;   /* 1 = 4th-order (only value implemented)              */
+  int32_t idiffu;   /* 1 = 4th order with the 2nd-order boundary ring, 2 = nine-point operator on every interior point
+                     * (Main/mod_diffusion.F90:266-411,523-601,658-735,792-894); 3 is rejected */
   int32_t ipptls;   /* >0: hydrometeors advected, water loading in w       */
   /* &nonhydroparam */
   int32_t ifupr;    /* upper radiative boundary condition                  */

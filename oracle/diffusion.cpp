@@ -1,7 +1,8 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY.
-// Restates Main/mod_diffusion.F90 for idiffu = 1, idynamic = 2:
-// calc_coeff :169-251, diffu_d :266-385, diffu_x3df :523-591,
-// diffu_x3d :658-725, diffu_x4d/diffu_x4d3d :792-880.
+// Restates Main/mod_diffusion.F90 for idiffu = 1 (4th order, 2nd order on the boundary ring) and
+// idiffu = 2 (the nine-point "LeVeque" operator on every interior point):
+// calc_coeff :169-251, diffu_d :266-411, diffu_x3df :523-601,
+// diffu_x3d :658-735, diffu_x4d/diffu_x4d3d :792-894.
 // Module aliases (:161-166): mpd = mddom%msfd, pc = sfs%psb, pd = sfs%psdotb,
 // ud = atms%ubd3d, vd = atms%vbd3d, wx = atms%wb3d.
 #include <algorithm>
@@ -12,6 +13,7 @@
 namespace orc {
 
 static constexpr double z4_c1 = 1.0, z4_c2 = -4.0, z4_c3 = 12.0;  // :69-71
+static constexpr double o4_c1 = 4.0 / 6.0, o4_c2 = 1.0 / 6.0, o4_c3 = -20.0 / 6.0;  // :63-65
 
 void Oracle::calc_coeff() {
   const A3& ud = ubd3d; const A3& vd = vbd3d; const A3& wx = wb3d;
@@ -51,6 +53,25 @@ void Oracle::calc_coeff() {
 
 void Oracle::diffu_d(A3& ut, A3& vt, const A3& u, const A3& v) {
   const A2& mpd = msfd;
+  if (cfg.idiffu == 2) {   // :386-411
+    for (int k = 1; k <= kz; ++k)
+      for (int i = idi1; i <= idi2; ++i)
+        for (int j = jdi1; j <= jdi2; ++j) {
+          ut(j, i, k) = ut(j, i, k) + xkd(j, i, k) *
+              (o4_c1 * (u(j + 1, i, k) / mpd(j + 1, i) + u(j - 1, i, k) / mpd(j - 1, i) +
+                        u(j, i + 1, k) / mpd(j, i + 1) + u(j, i - 1, k) / mpd(j, i - 1)) +
+               o4_c2 * (u(j + 1, i + 1, k) / mpd(j + 1, i + 1) + u(j - 1, i - 1, k) / mpd(j - 1, i - 1) +
+                        u(j - 1, i + 1, k) / mpd(j - 1, i + 1) + u(j + 1, i - 1, k) / mpd(j + 1, i - 1)) +
+               o4_c3 * (u(j, i, k) / mpd(j, i)));
+          vt(j, i, k) = vt(j, i, k) + xkd(j, i, k) *
+              (o4_c1 * (v(j + 1, i, k) / mpd(j + 1, i) + v(j - 1, i, k) / mpd(j - 1, i) +
+                        v(j, i + 1, k) / mpd(j, i + 1) + v(j, i - 1, k) / mpd(j, i - 1)) +
+               o4_c2 * (v(j + 1, i + 1, k) / mpd(j + 1, i + 1) + v(j - 1, i - 1, k) / mpd(j - 1, i - 1) +
+                        v(j - 1, i + 1, k) / mpd(j - 1, i + 1) + v(j + 1, i - 1, k) / mpd(j + 1, i - 1)) +
+               o4_c3 * (v(j, i, k) / mpd(j, i)));
+        }
+    return;
+  }
   for (int k = 1; k <= kz; ++k)
     for (int i = idii1; i <= idii2; ++i)
       for (int j = jdii1; j <= jdii2; ++j) {
@@ -88,6 +109,16 @@ void Oracle::diffu_d(A3& ut, A3& vt, const A3& u, const A3& v) {
 }
 
 void Oracle::diffu_x3d(A3& ften, const A3& f) {
+  if (cfg.idiffu == 2) {   // :726-735
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ici1; i <= ici2; ++i)
+        for (int j = jci1; j <= jci2; ++j)
+          ften(j, i, k) = ften(j, i, k) + xkc(j, i, k) *
+              (o4_c1 * (f(j + 1, i, k) + f(j - 1, i, k) + f(j, i + 1, k) + f(j, i - 1, k)) +
+               o4_c2 * (f(j + 1, i + 1, k) + f(j - 1, i - 1, k) + f(j - 1, i + 1, k) + f(j + 1, i - 1, k)) +
+               o4_c3 * (f(j, i, k)));
+    return;
+  }
   for (int k = 1; k <= kz; ++k)
     for (int i = icii1; i <= icii2; ++i)
       for (int j = jcii1; j <= jcii2; ++j)
@@ -111,6 +142,16 @@ void Oracle::diffu_x3d(A3& ften, const A3& f) {
 }
 
 void Oracle::diffu_x3df(A3& ften, const A3& f, double fac) {
+  if (cfg.idiffu == 2) {   // :592-601
+    for (int k = 1; k <= kzp1; ++k)
+      for (int i = ici1; i <= ici2; ++i)
+        for (int j = jci1; j <= jci2; ++j)
+          ften(j, i, k) = ften(j, i, k) + fac * xkcf(j, i, k) *
+              (o4_c1 * (f(j + 1, i, k) + f(j - 1, i, k) + f(j, i + 1, k) + f(j, i - 1, k)) +
+               o4_c2 * (f(j + 1, i + 1, k) + f(j - 1, i - 1, k) + f(j - 1, i + 1, k) + f(j + 1, i - 1, k)) +
+               o4_c3 * (f(j, i, k)));
+    return;
+  }
   for (int k = 1; k <= kzp1; ++k)
     for (int i = icii1; i <= icii2; ++i)
       for (int j = jcii1; j <= jcii2; ++j)
@@ -135,6 +176,16 @@ void Oracle::diffu_x3df(A3& ften, const A3& f, double fac) {
 
 void Oracle::diffu_x4d(A4& ften, const A4& f, int n1, int n2, double fac) {
   for (int n = n1; n <= n2; ++n) {
+    if (cfg.idiffu == 2) {   // :881-894
+      for (int k = 1; k <= kz; ++k)
+        for (int i = ici1; i <= ici2; ++i)
+          for (int j = jci1; j <= jci2; ++j)
+            ften(j, i, k, n) = ften(j, i, k, n) + fac * xkc(j, i, k) *
+                (o4_c1 * (f(j + 1, i, k, n) + f(j - 1, i, k, n) + f(j, i + 1, k, n) + f(j, i - 1, k, n)) +
+                 o4_c2 * (f(j + 1, i + 1, k, n) + f(j - 1, i - 1, k, n) + f(j - 1, i + 1, k, n) + f(j + 1, i - 1, k, n)) +
+                 o4_c3 * f(j, i, k, n));
+      continue;
+    }
     for (int k = 1; k <= kz; ++k)
       for (int i = icii1; i <= icii2; ++i)
         for (int j = jcii1; j <= jcii2; ++j)

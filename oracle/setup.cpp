@@ -27,7 +27,7 @@ int Oracle::create(const rcm_cfg& c) {
   moloch = (c.idynamic == 3);
   if (hydro && (c.nsplit < 1 || c.nsplit > c.kz)) { err = "oracle: nsplit out of range"; return RCM_ERR_ARG; }
   nsplit = hydro ? c.nsplit : 0;
-  if (c.idiffu != 1) { err = "oracle: only idiffu=1"; return RCM_ERR_ARG; }
+  if (c.idiffu != 1 && c.idiffu != 2) { err = "oracle: idiffu must be 1 or 2 (3, the flux-limited 6th-order operator, is not restated)"; return RCM_ERR_ARG; }
   // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)
   if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 4 || c.iboudy == 5 || (c.idynamic != 3 && (c.iboudy == 2 || c.iboudy == 3)))) { err = "oracle: iboudy must be 0..5 (2, 3: idynamic 1, 2 only)"; return RCM_ERR_ARG; }
   if (c.nqx != 2) { err = "oracle: nqx must be 2"; return RCM_ERR_ARG; }
@@ -37,7 +37,7 @@ int Oracle::create(const rcm_cfg& c) {
   ptop = c.ptop;
   dtsec = c.dt; dt = c.dt; dt2 = d_two * dt;   // mod_params.F90:1628,1708
   dtbdys = (double)c.ibdyfrq * 3600.0;          // :1631
-  idif = 2;                                     // idiffu == 1, :1967
+  idif = (c.idiffu == 2) ? 1 : 2;               // :1968-1971
   // mod_params.F90:1763-1770
   dx = c.ds * d_1000;
   dx2 = d_two * dx; dx4 = d_four * dx; dx8 = 8.0 * dx; dx16 = 16.0 * dx;

@@ -177,6 +177,16 @@ void Oracle::tracer_tendency() {
       }
     }
     // diffu_x4d(chidyn, chib3d, 1, ntr, 1.0)
+    if (cfg.idiffu == 2) {   // Main/mod_diffusion.F90:881-894
+      const double o4_c1 = 4.0 / 6.0, o4_c2 = 1.0 / 6.0, o4_c3 = -20.0 / 6.0;
+      for (int k = 1; k <= kz; ++k)
+        for (int i = ici1; i <= ici2; ++i)
+          for (int j = jci1; j <= jci2; ++j)
+            dyn(j, i, k) = dyn(j, i, k) + d_one * xkc(j, i, k) *
+                (o4_c1 * (b3(j + 1, i, k) + b3(j - 1, i, k) + b3(j, i + 1, k) + b3(j, i - 1, k)) +
+                 o4_c2 * (b3(j + 1, i + 1, k) + b3(j - 1, i - 1, k) + b3(j - 1, i + 1, k) + b3(j + 1, i - 1, k)) +
+                 o4_c3 * b3(j, i, k));
+    } else {
     for (int k = 1; k <= kz; ++k)
       for (int i = icii1; i <= icii2; ++i)
         for (int j = jcii1; j <= jcii2; ++j)
@@ -191,6 +201,7 @@ void Oracle::tracer_tendency() {
     if (has_bdyright) for (int k = 1; k <= kz; ++k) for (int i = ici1; i <= ici2; ++i) ring(jci2, i, k);
     if (has_bdybottom) for (int k = 1; k <= kz; ++k) for (int j = jci1; j <= jci2; ++j) ring(j, ici1, k);
     if (has_bdytop) for (int k = 1; k <= kz; ++k) for (int j = jci1; j <= jci2; ++j) ring(j, ici2, k);
+    }
     // chiten = chiten + chidyn + chiphy (physics off); forecast (:548-569)
     for (int k = 1; k <= kz; ++k)
       for (int i = ici1; i <= ici2; ++i)

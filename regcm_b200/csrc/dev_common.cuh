@@ -243,6 +243,14 @@ __device__ __forceinline__ bool tile_edge(const Geom& g, const int j, const int 
   return (g.gl && j == g.jci1) || (g.gr && j == g.jci2) || (g.gb && i == g.ici1) || (g.gt && i == g.ici2);
 }
 
+// idiffu = 2: the nine-point operator o4_c1*(sides) + o4_c2*(corners) + o4_c3*centre with the reference's order of
+// the sums (Main/mod_diffusion.F90:63-65,386-411,592-601,726-735,881-894); pp = (j+1,i+1), mm = (j-1,i-1),
+// mp = (j-1,i+1), pm = (j+1,i-1)
+__device__ __forceinline__ double lap9(double c, double jm, double jp, double im, double ip, double pp, double mm,
+                                       double mp, double pm) {
+  return (4.0 / 6.0) * (jp + jm + ip + im) + (1.0 / 6.0) * (pp + mm + mp + pm) + (-20.0 / 6.0) * (c);
+}
+
 __device__ __forceinline__ bool diff_interior(const Geom& g, int j, int i, bool dot) {
   if (dot) return j >= g.jdii1 && j <= g.jdii2 && i >= g.idii1 && i <= g.idii2;
   return j >= g.jcii1 && j <= g.jcii2 && i >= g.icii1 && i <= g.icii2;

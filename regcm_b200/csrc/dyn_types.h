@@ -49,6 +49,7 @@ struct StepScalars {
   double xgamma, bp, bm, bpxbp, bpxbm, xkd_snd;
   double ptop;
   int upstream_mode, stability_enhance, ipptls, iboudy, ifrayd, ifupr;
+  int idiffu;   // 1: 4th order with the 2nd-order boundary ring; 2: nine-point operator (Main/mod_diffusion.F90)
   int kt_ray;   // min(kz, rayndamp)
   int ktf_ray;  // min(kzp1, rayndamp)
   int nspgx, nspgd;

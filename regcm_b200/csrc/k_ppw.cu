@@ -37,8 +37,9 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
   const double ex = L2(f.ex, j, i), crx = L2(f.crx, j, i), cry = L2(f.cry, j, i);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_c, j, i) : 0;
   const int ibs = (s.iboudy == 4) ? L2(f.zone_c, j, i) : 0;   // sponge zone (iboudy = 4)
-  const bool dint = diff_interior(g, j, i, false);
-  const int nring = ring_count(g, j, i, false);
+  const bool d9 = (s.idiffu == 2);   // nine-point operator on every interior point, no boundary ring
+  const bool dint = !d9 && diff_interior(g, j, i, false);
+  const int nring = d9 ? 0 : ring_count(g, j, i, false);
 
   // ---- carried state (level k-1 values and interface fluxes) ----
   double uavg1_m = 0, uavg2_m = 0, vavg1_m = 0, vavg2_m = 0;  // uavg at k-1

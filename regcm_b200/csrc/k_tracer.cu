@@ -44,8 +44,9 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
   const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i), m11 = L2(f.msfd, j + 1, i + 1);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_c, j, i) : 0;
   const bool we = ib > 0 && L2(tr.ztype, j, i) != 0;
-  const bool dint = diff_interior(g, j, i, false);
-  const int nring = ring_count(g, j, i, false);
+  const bool d9 = (s.idiffu == 2);   // nine-point operator on every interior point, no boundary ring
+  const bool dint = !d9 && diff_interior(g, j, i, false);
+  const int nring = d9 ? 0 : ring_count(g, j, i, false);
   const double beta = 0.53;
   const double thr = mintr * psa;
 #define RPSB(dj, di) L2(f.rpsb, j + (dj), i + (di))
@@ -99,6 +100,8 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
         ten = ten - 1.0 * xkc * (1.0 * (d_jp2 + d_jm2 + d_ip2 + d_im2) + (-4.0) * (d_jp + d_jm + d_ip + d_im) + 12.0 * d_c);
       }
       for (int r = 0; r < nring; ++r) ten = ten + 1.0 * xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * d_c);
+      if (d9) ten = ten + 1.0 * xkc * lap9(d_c, d_jm, d_jp, d_im, d_ip, fmax(L3(a2, j + 1, i + 1, k) * RPSB(1, 1), 0.0), fmax(L3(a2, j - 1, i - 1, k) * RPSB(-1, -1), 0.0),
+                                           fmax(L3(a2, j - 1, i + 1, k) * RPSB(-1, 1), 0.0), fmax(L3(a2, j + 1, i - 1, k) * RPSB(1, -1), 0.0));
     }
     // chiten = chiten + chidyn + chiphy; forecast; the value filtered for a negative forecast is provisional
     // (k_tr_repair redoes it)

@@ -6,7 +6,7 @@
 //   vadvuv                   Main/mod_advection.F90:271-303
 //   curvature NH branch      Main/mod_tendency.F90:1840-1879
 //   nudgeuv (iboudy 1|5)     Main/mod_bdycod.F90:3581-3823
-//   diffu_d (idiffu = 1)     Main/mod_diffusion.F90:266-385
+//   diffu_d (idiffu = 1, 2)  Main/mod_diffusion.F90:266-411
 //   raydampuv                Main/mod_bdycod.F90:4990-5026
 //   uten*rpsda, *dts         Main/mod_tendency.F90:478-487, mod_sound.F90:228-231
 // Output: uten, vten (the acoustic tendencies), one write each.
@@ -43,8 +43,9 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
   const double psdotb = L2(f.psdotb, j, i);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_d, j, i) : 0;
   const int ibs = (s.iboudy == 4) ? L2(f.zone_d, j, i) : 0;   // sponge zone (iboudy = 4)
-  const bool dint = diff_interior(g, j, i, true);
-  const int nring = ring_count(g, j, i, true);
+  const bool d9 = (s.idiffu == 2);   // nine-point operator on every interior point, no boundary ring
+  const bool dint = !d9 && diff_interior(g, j, i, true);
+  const int nring = d9 ? 0 : ring_count(g, j, i, true);
 
   // vertical-advection flux at the upper interface of level k (full level k)
   double uu_k = 0.0, vv_k = 0.0;  // uu(1) = 0: loop starts at k = 2

@@ -18,8 +18,11 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def built():
     """Build the product library and the oracle once per session."""
+    import fcntl
     import __graft_entry__ as ge
-    ge.build()
+    with open(os.path.join(ROOT, "tests", ".build.lock"), "w") as lock:   # one pytest-xdist worker builds, the others wait
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        ge.build()
     return True
 
 
@@ -29,7 +32,10 @@ def emu_lib(built):
     compiled with g++ and executed thread by thread."""
     from regcm_b200 import capi
     d = os.path.join(ROOT, "tests", "emu")
-    subprocess.check_call(["make", "-s", "-C", d])
+    import fcntl
+    with open(os.path.join(d, ".build.lock"), "w") as lock:   # pytest-xdist workers would otherwise rebuild it at once
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        subprocess.check_call(["make", "-s", "-C", d])
     return capi.CoreLib(os.path.join(d, "libregcm_dyn_emu.so"), "rcm_dyn_")
 
 

@@ -451,11 +451,12 @@ def _wafone_horizontal(pp, wz, fmz, u, v, rmu, rmv, mx2, zdtrdx, zdtrdy, jx, iy,
 
 
 # ---------------------------------------------------------------------------------------------------------
-def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc, ul, dt, gnu2, box, kz, upstream=True):
+def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc, ul, dt, gnu2, box, kz, upstream=True, idiffu=1):
     """One leapfrog step of ONE tracer away from the lateral zones, written from the Fortran text:
     decouple (Main/mod_tendency.F90:1029-1034), start_advect (Main/mod_advection.F90:109-122: uavg/vavg from the
     p*.u.m fluxes), hadvtr (:666-720), vadv4d ind = 2 (:895-914,946-950), diffu_x4d interior stencil
-    (Main/mod_diffusion.F90:658-725 with chib3d = max(atm2%chi*rpsb, 0), Main/mod_slice.F90:198), the sums and the
+    (Main/mod_diffusion.F90:658-725 with chib3d = max(atm2%chi*rpsb, 0), Main/mod_slice.F90:198; idiffu = 2: the
+    nine-point operator of :881-894 with the weights 4/6, 1/6, -20/6 of :63-65), the sums and the
     forecast (Main/mod_tendency.F90:548-569) and the RAW filter (Main/mod_timefilter.F90:231-278, alpha = gnu2,
     beta = 0.53, floor 0).  `box` = (j1, j2, i1, i2): interior points at least three rows away from the zones.
     Returns (forecast atmc%chi, filtered atm1%chi, filtered atm2%chi) on the box."""
@@ -495,7 +496,11 @@ def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc,
     ten[:, :, 1:] += fg * xd[:, :, 1:]
     # diffu_x4d on chib3d
     b = lambda dj=0, di=0: np.maximum(c(chib, dj, di) * c(rpsb, dj, di), 0.0)
-    ten -= c(xkc) * ((b(2, 0) + b(-2, 0) + b(0, 2) + b(0, -2)) - 4.0 * (b(1, 0) + b(-1, 0) + b(0, 1) + b(0, -1)) + 12.0 * b())
+    if idiffu == 2:
+        ten += c(xkc) * (4.0 / 6.0 * (b(1, 0) + b(-1, 0) + b(0, 1) + b(0, -1)) + 1.0 / 6.0 * (b(1, 1) + b(-1, -1) + b(-1, 1) + b(1, -1))
+                         - 20.0 / 6.0 * b())
+    else:
+        ten -= c(xkc) * ((b(2, 0) + b(-2, 0) + b(0, 2) + b(0, -2)) - 4.0 * (b(1, 0) + b(-1, 0) + b(0, 1) + b(0, -1)) + 12.0 * b())
     fc = c(chib) + dt * ten
     fcp = np.where(fc < 0.0, np.nan, fc)        # the negative fix is not part of this restatement
     d = gnu2 * (fcp + c(chib) - 2.0 * c(chia))

@@ -103,6 +103,15 @@ def test_multirank_matches_single_rank(emu_lib, tmp_path, world, layout):
     compare(glob, ref, 1e-12)
 
 
+def test_multirank_idiffu2(emu_lib, tmp_path):
+    """idiffu = 2 on a 2x2 decomposition: the nine-point operator reads the corner ghost points of the level-b
+    fields (Main/mod_diffusion.F90:386-411,726-735; exchange width idif = 1, Main/mod_tendency.F90:1070-1083)."""
+    steps = 5
+    run_ranks(4, tmp_path, ["--case", "tiny", "--steps", str(steps), "--cpus-j", "2", "--cpus-i", "2", "--cfg", "idiffu=2"])
+    cfg, ref = single_rank(emu_lib, "tiny", steps, idiffu=2)
+    compare(assemble(tmp_path, 4, cfg), ref, 1e-12)
+
+
 @pytest.mark.parametrize("iboudy", [3, 4])
 def test_multirank_sponge_and_inflow_outflow(emu_lib, tmp_path, iboudy):
     """iboudy 3 / 4 on a 2x2 decomposition: the inflow/outflow rule of `decouple` on the outermost dot ring (global
@@ -169,7 +178,8 @@ def single_rank_hydro(emu_lib, case_name, steps, ibdyfrq=6, **kw):
 
 
 @pytest.mark.parametrize("world,layout,extra", [(2, (0, 0), {}), (2, (1, 2), {}), (4, (2, 2), {}), (3, (3, 1), {}),
-                                                 (4, (2, 2), {"nsplit": 3}), (4, (2, 2), {"iboudy": 4}), (4, (2, 2), {"iboudy": 1})])
+                                                 (4, (2, 2), {"nsplit": 3}), (4, (2, 2), {"iboudy": 4}), (4, (2, 2), {"iboudy": 1}),
+                                                 (4, (2, 2), {"idiffu": 2})])
 def test_hydro_multirank_matches_single_rank(emu_lib, tmp_path, world, layout, extra):
     """2-D decomposition of the hydrostatic core (SURVEY §8 a24 for idynamic = 1): psc2psd + exchange, the ghost-ring
     recomputation of compute_omega / phi / new_pressure, the exchanges of splitf and of every spstep sub-step

@@ -93,7 +93,7 @@ def test_wafone_numpy_vs_oracle():
     assert np.abs(pp.a - want).max() <= 1e-9 * change   # and agrees on the increment, not just on the 300 K background
 
 
-@pytest.mark.parametrize("kw", [{}, {"upstream_mode": 0}], ids=["default", "centred"])
+@pytest.mark.parametrize("kw", [{}, {"upstream_mode": 0}, {"idiffu": 2}], ids=["default", "centred", "idiffu2"])
 def test_tracer_step_numpy_vs_oracle(kw):
     """hadvtr + vadv4d(ind = 2) + diffu_x4d + forecast + RAW filter of one tracer, away from the lateral
     zones, on the flow of the oracle's 4th step."""
@@ -110,7 +110,8 @@ def test_tracer_step_numpy_vs_oracle(kw):
     t = {n: nr.tap(o, n) for n in ("ax_umc", "ax_vmc", "psa", "rpsa", "rpsb", "xmsf", "qdot", "twt", "xds", "xkc", "chic0", "chia0", "chib0")}
     box = (nsp + 2, jx - 1 - nsp - 2, nsp + 2, iy - 1 - nsp - 2)
     fc, na, nb = nr.tracer_step(chia, chib, t["ax_umc"], t["ax_vmc"], t["psa"], t["rpsa"], t["rpsb"], t["xmsf"], t["qdot"], t["twt"],
-                                t["xds"], t["xkc"], nr.scalar(o, "ul"), dt, case.cfg.gnu2, box, kz, upstream=case.cfg.upstream_mode != 0)
+                                t["xds"], t["xkc"], nr.scalar(o, "ul"), dt, case.cfg.gnu2, box, kz, upstream=case.cfg.upstream_mode != 0,
+                                idiffu=case.cfg.idiffu)
     sl = ((box[0], box[1]), (box[2], box[3]), (1, kz))
     want_c, want_a, want_b = t["chic0"].s(*sl), t["chia0"].s(*sl), t["chib0"].s(*sl)
     assert fc.min() > 0.0 and np.abs(want_c - chib.s(*sl)).max() > 1e-3 * np.abs(want_c).max()   # the step did move the tracer
