@@ -60,6 +60,12 @@ enum rcm_field {
   RCM_F_PAI = 8, /* cross (jx-1,iy-1,kz): Exner function Pi of the MOLOCH core
                   * (mo_atm%pai, Main/mod_atm_interface.F90:575-616); state only */
   RCM_F_COUNT = 9,
+  /* Turbulent kinetic energy of the UW PBL (atm1%tke / atm2%tke, ibltyp = 2; idynamic 1, 2): cross
+   * (jx-1,iy-1,kz+1), NOT coupled with p* [m2 s-2].  State and physics tendency only (no boundary record: the rim follows
+   * the inflow/outflow rule of Main/mod_bdycod.F90:2412-2538).  Transport = hadv3d(ind = 1) on atm1%tke,
+   * vadv3d(kz+1) on tke*psa, diffu_x3df(nuk) on atm2%tke, tketen = tkedyn*rpsa + tkephy, floor tkemin, RA filter
+   * (Main/mod_tendency.F90:518-544,1414-1425,1544-1548). */
+  RCM_F_TKE = 9,
   /* Tracers (atm1%chi / atm2%chi, ichem = 1; idynamic 1, 2): tracer n = 0..ntr-1 is field
    * RCM_F_CHI + n, cross (jx-1,iy-1,kz), p*·chi.  As a boundary field (chib0/chib1, che_init_bdy and chem_bdyin,
    * Main/chemlib/mod_che_bdyco.F90:118-420) the value passed is the mixing ratio of the CHBC record on model
@@ -222,6 +228,10 @@ typedef struct rcm_cfg {
   int32_t mo_rotllr;      /* 1: iproj = 'ROTLLR' (rotated lat-lon) branches of sound / wafone /
                            * compute_moloch_static (Main/mod_moloch.F90:773,932,1183; Main/mod_params.F90:2766) */
   int32_t ntr;            /* number of transported tracers, 0..RCM_MAXTR (ichem = 1 with ntr species; 0 = ichem 0) */
+  /* &physicsparam / &uwparam, the part the dynamics reads (Main/mod_tendency.F90:148-156; Main/mod_params.F90:476-480) */
+  int32_t ibltyp;         /* 2: the UW PBL is on, TKE (RCM_F_TKE) is carried and transported; anything else: no TKE     */
+  int32_t iuwvadv;        /* 1 (with ibltyp = 2): vadv4d ind = 3 for qc and the tracers, which reshapes the vertical flux
+                           * around the PBL top kpbl handed in with rcm_dyn_set_kpbl (Main/mod_advection.F90:915-957)  */
   int32_t reserved_i[1];
   /* &geoparam */
   double ds;    /* grid spacing [km]                                       */
@@ -238,7 +248,9 @@ typedef struct rcm_cfg {
   double base_state_pressure, logp_lrate, base_state_ts0;
   double mo_anu2;  /* divergence-damping coefficient of filt3d (0.6)      */
   double mo_a0, mo_b0; /* decay / stretching of the zita coordinate (0, 0.5) */
-  double reserved_d[5];
+  double uw_nuk;       /* &uwparam nuk: factor of the horizontal diffusion of TKE (5.0)                              */
+  double uw_tkemin;    /* floor of TKE, uwtkemin of Main/pbllib/mod_pbl_uwtcm.F90:86 (1.0e-3)                        */
+  double reserved_d[3];
 } rcm_cfg;
 
 /* health metrics the reference prints (Main/mod_sound.F90:634-646) */
@@ -316,7 +328,7 @@ int rcm_dyn_step(rcm_dyn* h, int nsteps);
  *   rcm_dyn_get_slice          one member of `atms` (enum rcm_slice), computed on request from the level-b state,
  *                              on the cross grid with the usual lb/ub window.  Valid at any time between steps; omega
  *                              (WPX3D, WB3D) of the hydrostatic core only between the pre- and post-physics calls.
- *   rcm_dyn_set_phys_tend      aten(:,:,:,pc_physic) of one prognostic (RCM_F_U, V: dot grid; T, QV, QC, PP, W: cross
+ *   rcm_dyn_set_phys_tend      aten(:,:,:,pc_physic) of one prognostic (RCM_F_U, V: dot grid; T, QV, QC, PP, W, TKE: cross
  *                              grid; coupled with p* like the reference's).  Stays in effect — also for
  *                              rcm_dyn_step — until replaced or cleared; zero until first set.
  *   rcm_dyn_step_post_physics  the rest of `tend` (advection ... diffusion, the sums, forecast, time filters,
@@ -327,6 +339,13 @@ int rcm_dyn_get_slice(rcm_dyn* h, int slice_id, double* a, const int32_t lb[3], 
 int rcm_dyn_set_phys_tend(rcm_dyn* h, int field, const double* a, const int32_t lb[3], const int32_t ub[3]);
 int rcm_dyn_clear_phys_tend(rcm_dyn* h);
 int rcm_dyn_step_post_physics(rcm_dyn* h);
+
+/* UW-PBL coupling of the transport (ibltyp = 2).  replaces: the `kpbl` array the PBL scheme leaves for vadv4d
+ * (Main/mod_atm_interface.F90:136,1135; Main/mod_advection.F90:66,92,921-956) and aten%tke(:,:,:,pc_physic)
+ * (rcm_dyn_set_phys_tend with RCM_F_TKE, cross grid, kz+1 levels, uncoupled as in Main/mod_tendency.F90:530-531).
+ * kpbl: int32 on the cross interior (window lb/ub as elsewhere, two indices); zero until first set, as getmem2d leaves it
+ * — then ind = 3 is the plain twt interpolation.  A value > kz is an error (the reference calls `fatal`). */
+int rcm_dyn_set_kpbl(rcm_dyn* h, const int32_t* kpbl, const int32_t lb[2], const int32_t ub[2]);
 
 /* Asynchronous form of rcm_dyn_step for drivers that overlap the time loop with their own work (the reference's
  * RCM_run is synchronous: Main/mod_regcm_interface.F90:172-228; its output and boundary input block the loop).

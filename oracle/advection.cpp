@@ -278,6 +278,8 @@ void Oracle::vadv4d(A4& ften, const A4& f, int n1, int n2, int ind) {
                 fg(j, i, k) = d_zero;
             }
           }
+    } else if (ind == 3) {   // :915-957 (oracle/tke.cpp)
+      vadv_ind3([&](int j, int i, int k) { return f(j, i, k, n); });
     } else {
       std::abort();
     }

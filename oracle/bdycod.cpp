@@ -376,6 +376,10 @@ void Oracle::bdyval() {
         else a1_qx(j, ice2, k, n) = qxint * psa(j, ice2);
       }
   }
+  if (uw_on) {   // TKE (ibltyp = 2): the rim copy of :1166-1307 and the block of :2412-2496
+    if (integrating()) bdyval_tke_copy();
+    bdyval_tke();
+  }
   if (ntr > 0) bdyval_tracers(xbctime + dt);   // chem_bdyval (Main/mod_bdycod.F90:2558-2564)
   xbctime = xbctime + dtsec;
 }

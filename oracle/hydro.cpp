@@ -271,6 +271,12 @@ void Oracle::calc_coeff_hydro() {
       }
   if (xkc_raw.d.size() != xkc.d.size()) xkc_raw.alloc(jce1, jce2, ice1, ice2, 1, kz);
   xkc_raw.d = xkc.d;
+  // xkcf (:231-235,245-247) is formed for both cores; with idynamic = 1 only the TKE diffusion reads it
+  for (int i = ici1; i <= ici2; ++i)
+    for (int j = jci1; j <= jci2; ++j) xkcf(j, i, 1) = xkc(j, i, 1);
+  for (int k = 1; k <= kz; ++k)
+    for (int i = ici1; i <= ici2; ++i)
+      for (int j = jci1; j <= jci2; ++j) xkcf(j, i, k + 1) = xkc(j, i, k);
   for (int k = 1; k <= kz; ++k)
     for (int i = idi1; i <= idi2; ++i)
       for (int j = jdi1; j <= jdi2; ++j)
@@ -278,6 +284,9 @@ void Oracle::calc_coeff_hydro() {
   for (int k = 1; k <= kz; ++k)
     for (int i = ici1; i <= ici2; ++i)
       for (int j = jci1; j <= jci2; ++j) xkc(j, i, k) = xkc(j, i, k) * rdxsq * psb(j, i);
+  for (int k = 1; k <= kzp1; ++k)
+    for (int i = ici1; i <= ici2; ++i)
+      for (int j = jci1; j <= jci2; ++j) xkcf(j, i, k) = xkcf(j, i, k) * rdxsq * psb(j, i);
   for (int k = 1; k <= kz; ++k)
     for (int i = idi1; i <= idi2; ++i)
       for (int j = jdi1; j <= jdi2; ++j) xkd(j, i, k) = xkd(j, i, k) * rdxsq * psdotb(j, i);
@@ -461,6 +470,7 @@ void Oracle::tend_hydro() {
   diffu_d(udyn, vdyn, ubd3d, vbd3d);
   diffu_x3d(tdyn, tb3d);
   diffu_x4d(qxdyn, qxb3d, 1, nqx, d_one);
+  tke_tendency();      // ibltyp = 2 (oracle/tke.cpp)
   tracer_tendency();   // ichem = 1 (oracle/tracers.cpp)
   // tendency sums (:285-294,331-335)
   for (int k = 1; k <= kz; ++k)

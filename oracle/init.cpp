@@ -423,6 +423,7 @@ static void copy_out_4d(const A4& src, int n, double* a, const int32_t lb[3], co
 int Oracle::get_state(int field, int level, double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (moloch) return mo_get_state(field, a, lb, ub);
   if (field >= RCM_F_CHI) return tracer_state(field - RCM_F_CHI, level, a, lb, ub, false);
+  if (field == RCM_F_TKE) return tke_state(level, a, lb, ub, false);
   const bool A = (level == RCM_LEVEL_A);
   switch (field) {
     case RCM_F_U: copy_out_3d(A ? a1_u : a2_u, a, lb, ub); return RCM_OK;

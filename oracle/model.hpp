@@ -10,6 +10,7 @@
 #pragma once
 #include <cstdint>
 #include <string>
+#include <functional>
 #include <vector>
 
 #include "../include/regcm_dyn.h"
@@ -40,7 +41,7 @@ struct Oracle {
   int jx = 0, iy = 0, kz = 0, kzp1 = 0, nqx = 2;
   int iqv = 1, iqc = 2, iqfrst = 2, iqlst = 2;
   int idif = 2;
-  int iqxvadv = 1;  // Main/mod_tendency.F90:148
+  int iqxvadv = 1, itrvadv = 2;  // Main/mod_tendency.F90:148-154
   double dx = 0, dx2 = 0, dx4 = 0, dx8 = 0, dx16 = 0, dxsq = 0, rdx = 0,
          rdxsq = 0;
   double dtsec = 0, dt = 0, dt2 = 0;
@@ -155,6 +156,18 @@ struct Oracle {
   inline double phy4(int j, int i, int k, int n) const { return phys_on ? qxphy(j, i, k, n) : d_zero; }
 
   // ---- hydrostatic core (idynamic = 1; oracle/hydro.cpp, oracle/split.cpp) ----
+  // ---- UW-PBL coupling of the transport: TKE, vadv4d ind = 3 (oracle/tke.cpp) ----
+  bool uw_on = false;
+  double tkemin = 0;
+  A3 tke_a, tke_b, tke_c, tkeps, tkedyn, tketen, tkephy;
+  std::vector<int> kpb;   // (jci1:jci2, ici1:ici2)
+  void allocate_tke();
+  void tke_tendency();
+  void bdyval_tke_copy();
+  void bdyval_tke();
+  void vadv_ind3(const std::function<double(int, int, int)>& f);
+  int set_kpbl(const int32_t* k, const int32_t lb[2], const int32_t ub[2]);
+  int tke_state(int level, double* a, const int32_t lb[3], const int32_t ub[3], bool in);
   // ---- tracers (oracle/tracers.cpp) ----
   int ntr = 0;
   std::vector<A3> chia, chib, chic, chix, chib3d, chidyn, chiten, nx_chi;   // atm1%chi, atm2%chi, atmc%chi, atmx%chi, ...

@@ -71,6 +71,7 @@ int Oracle::set_phys(int field, const double* a, const int32_t lb[3], const int3
     case RCM_F_T: dst = &tphy; break;
     case RCM_F_PP: dst = &ppphy; break;
     case RCM_F_W: dst = &wphy; break;
+    case RCM_F_TKE: if (!uw_on) { err = "oracle: TKE is carried with ibltyp = 2 only"; return RCM_ERR_ARG; } dst = &tkephy; break;
     case RCM_F_QV: n4 = iqv; break;
     case RCM_F_QC: n4 = iqc; break;
     default: err = "oracle: no physics tendency for this field"; return RCM_ERR_ARG;
@@ -91,6 +92,7 @@ int Oracle::set_phys(int field, const double* a, const int32_t lb[3], const int3
 void Oracle::clear_phys() {
   if (!phys_on) return;
   for (A3* a : {&uphy, &vphy, &tphy, &ppphy, &wphy}) a->fill(d_zero);
+  if (uw_on) tkephy.fill(d_zero);
   qxphy.fill(d_zero);
 }
 

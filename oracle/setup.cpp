@@ -51,6 +51,7 @@ int Oracle::create(const rcm_cfg& c) {
   allocate_all();
   if (hydro) allocate_hydro();
   allocate_tracers();
+  allocate_tke();
   setup_boundaries(false, false, ba_cr);   // mod_params.F90:1788-1793
   setup_boundaries(true, true, ba_dt);
   return RCM_OK;
@@ -304,6 +305,7 @@ int Oracle::set_bdy(int field, int slot, const double* a, const int32_t lb[3], c
 int Oracle::set_state(int field, int level, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (moloch) return mo_set_state(field, a, lb, ub);
   if (field >= RCM_F_CHI) return tracer_state(field - RCM_F_CHI, level, const_cast<double*>(a), lb, ub, true);
+  if (field == RCM_F_TKE) return tke_state(level, const_cast<double*>(a), lb, ub, true);
   const bool A = (level == RCM_LEVEL_A);
   auto in4 = [&](A4& dst, int n) {
     const int n1 = ub[0] - lb[0] + 1, n2 = ub[1] - lb[1] + 1;

@@ -41,6 +41,8 @@ int orc_array(void* h, const char* name, double** data, int32_t lb[4], int32_t n
   T2(mx2) T2(rmu) T2(rmv) T2(msfu) T2(msfv) T3(xkc) T3(th) T3(tha) T3(thten)
   if (s == "chia0" && o->ntr > 0) v3(v, o->chia[0]); else if (s == "chib0" && o->ntr > 0) v3(v, o->chib[0]); else
   if (s == "chic0" && o->ntr > 0) v3(v, o->chic[0]); else
+  if (o->uw_on && s == "tke_a") v3(v, o->tke_a); else if (o->uw_on && s == "tke_b") v3(v, o->tke_b); else
+  if (o->uw_on && s == "tke_c") v3(v, o->tke_c); else if (s == "xkcf") v3(v, o->xkcf); else
   return RCM_ERR_ARG;
 #undef T1
 #undef T2

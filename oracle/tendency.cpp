@@ -379,6 +379,7 @@ void Oracle::tend() {
   boundary(); lap("boundary");
   // physical_parametrizations: OFF
   diffusion(); lap("diffusion");
+  tke_tendency();      // ibltyp = 2: TKE advection, diffusion, forecast, filter (oracle/tke.cpp)
   tracer_tendency();   // ichem = 1: advection, nudge_chi, diffusion, forecast, negative fix, filter (oracle/tracers.cpp)
   // tendency sums (:285-314,331-335): ten = ten + dyn + phy (aten(pc_physic), zero until set: oracle/physics.cpp)
   for (int k = 1; k <= kz; ++k)

@@ -141,6 +141,8 @@ void Oracle::tracer_tendency() {
         for (int j = jci1; j <= jci2; ++j) dyn(j, i, k) = dyn(j, i, k) + fg(j, i, k);
     // vadv4d, ind = 2 (:895-914): on p*-coupled values, threshold mintr * ps
     fg.fill(d_zero);
+    if (itrvadv == 3) vadv_ind3([&](int j, int i, int k) { return a1(j, i, k); });   // iuwvadv = 1 (Main/mod_tendency.F90:150-154)
+    else
     for (int k = 2; k <= kz; ++k)
       for (int i = ici1; i <= ici2; ++i)
         for (int j = jci1; j <= jci2; ++j) {

@@ -18,6 +18,7 @@ import numpy as np
 
 # enum rcm_field / rcm_static / rcm_work (include/regcm_dyn.h)
 F_U, F_V, F_T, F_QV, F_QC, F_PP, F_W, F_PS, F_PAI = range(9)
+F_TKE = 9        # atm1%tke / atm2%tke (ibltyp = 2), uncoupled, kz + 1 levels
 F_CHI = 16       # tracer n is field F_CHI + n
 R_DSTOR, R_HSTOR, R_TMASK = range(3)
 MAXTR = 8
@@ -57,6 +58,7 @@ class RcmCfg(C.Structure):
         ("nsplit", C.c_int32), ("lstand", C.c_int32),
         ("mo_nadv", C.c_int32), ("mo_nsound", C.c_int32), ("mo_nzfilt", C.c_int32), ("mo_rotllr", C.c_int32),
         ("ntr", C.c_int32),
+        ("ibltyp", C.c_int32), ("iuwvadv", C.c_int32),
         ("reserved_i", C.c_int32 * 1),
         ("ds", C.c_double), ("ptop", C.c_double),
         ("dt", C.c_double),
@@ -67,7 +69,8 @@ class RcmCfg(C.Structure):
         ("bdy_nm", C.c_double), ("bdy_dm", C.c_double),
         ("base_state_pressure", C.c_double), ("logp_lrate", C.c_double), ("base_state_ts0", C.c_double),
         ("mo_anu2", C.c_double), ("mo_a0", C.c_double), ("mo_b0", C.c_double),
-        ("reserved_d", C.c_double * 5),
+        ("uw_nuk", C.c_double), ("uw_tkemin", C.c_double),
+        ("reserved_d", C.c_double * 3),
     ]
 
 
@@ -99,6 +102,7 @@ def default_cfg(idynamic: int = 2, **kw) -> RcmCfg:
     c.nsplit, c.lstand = 2, 1   # Main/mod_params.F90:283-284
     c.mo_nadv, c.mo_nsound, c.mo_nzfilt = 3, 6, 3      # Main/mod_params.F90:296-300
     c.mo_anu2, c.mo_a0, c.mo_b0 = 0.6, 0.0, 0.5        # Share/mod_dynparam.F90:189-190
+    c.uw_nuk, c.uw_tkemin = 5.0, 1.0e-3                # Main/mod_params.F90:480; Main/pbllib/mod_pbl_uwtcm.F90:86
     if idynamic == 2:
         c.gnu1 = c.gnu2 = 0.1
         c.diffu_hgtf = 0
@@ -186,6 +190,7 @@ class CoreLib:
             "set_phys_tend": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
             "clear_phys_tend": ([vp], C.c_int),
             "get_slice": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
+            "set_kpbl": ([vp, C.POINTER(C.c_int32), C.c_int32 * 2, C.c_int32 * 2], C.c_int),
             # restart
             "get_restart": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
             "set_restart": ([vp, C.c_int, _DP, _I3, _I3], C.c_int),
@@ -230,7 +235,7 @@ class DynCore:
             return (jx, iy - 1, kz) if field == F_U else (jx - 1, iy, kz)
         if field in (F_U, F_V):
             return (jx, iy, kz)
-        if field == F_W:
+        if field in (F_W, F_TKE):
             return (jx - 1, iy - 1, kz + 1)
         if field == F_PS:
             return (jx - 1, iy - 1, 1)
@@ -285,6 +290,13 @@ class DynCore:
 
     def clear_phys_tend(self):
         self._check(self.lib.clear_phys_tend(self.h))
+
+    def set_kpbl(self, kpbl: np.ndarray, lb=(2, 2)):
+        """Top of the PBL (level index) on cross points, lb = global index of kpbl[0, 0]; read by vadv4d ind = 3."""
+        k = np.asfortranarray(kpbl, dtype=np.int32)
+        ub = (lb[0] + k.shape[0] - 1, lb[1] + k.shape[1] - 1)
+        I2 = C.c_int32 * 2
+        self._check(self.lib.set_kpbl(self.h, k.ctypes.data_as(C.POINTER(C.c_int32)), I2(*lb), I2(*ub)))
 
     def get_slice(self, sid: int) -> np.ndarray:
         """One slice of `atms` on the whole cross grid (jx-1, iy-1, nk)."""

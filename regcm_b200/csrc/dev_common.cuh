@@ -243,6 +243,37 @@ __device__ __forceinline__ bool tile_edge(const Geom& g, const int j, const int 
   return (g.gl && j == g.jci1) || (g.gr && j == g.jci2) || (g.gb && i == g.ici1) || (g.gt && i == g.ici2);
 }
 
+// vadv4d ind = 3 (Main/mod_advection.F90:915-957; iuwvadv = 1): the value of the p*-coupled scalar `q` carried through
+// interface kk (2..kz) before the multiplication by sigma-dot: the twt interpolation, replaced at the two interfaces
+// around the PBL top kp = kpbl(j,i) >= 4 by an extrapolation along the limited slope of the layer above.
+// q_k = q(kk), q_km1 = q(kk-1): the values the caller already holds.
+__device__ __forceinline__ double vadv3_face(const Geom& g, const Fields& f, const double* __restrict__ q, int j, int i, int kk,
+                                             int kp, double q_k, double q_km1) {
+  const int si = g.si;
+  const long long sk = g.sk;
+  double fg = LD1(&f.twt1[kk]) * q_k + LD1(&f.twt2[kk]) * q_km1;
+  if (kp >= 4 && (kk == kp - 1 || kk == kp)) {
+    auto hs = [&](int k) { return (LD1(&f.sigma[k + 1]) + LD1(&f.sigma[k])) * 0.5; };   // hsigma (Main/mod_params.F90:2008)
+    const int k = kp - 2;
+    const double fp = L3(q, j, i, k + 1), fc = L3(q, j, i, k), fm = L3(q, j, i, k - 1);
+    double slope;
+    if ((fp - fc) > 0.0 && (fc - fm) > 0.0)
+      slope = fmin((fp - fc) / (hs(k + 1) - hs(k)), (fc - fm) / (hs(k) - hs(k - 1)));
+    else if ((fp - fc) < 0.0 && (fc - fm) < 0.0)
+      slope = fmax((fp - fc) / (hs(k + 1) - hs(k)), (fc - fm) / (hs(k) - hs(k - 1)));
+    else
+      slope = 0.0;
+    if (kk == kp - 1) {
+      fg = fc + slope * (LD1(&f.sigma[kp - 1]) - hs(kp - 2));
+    } else {
+      const double fk = L3(q, j, i, kp);
+      if (fabs(fc + slope * (hs(kp - 1) - hs(kp - 2)) - fk) > fabs(fp - fk)) fg = fk;
+      else fg = fc + slope * (LD1(&f.sigma[kp]) - hs(kp - 2));
+    }
+  }
+  return fg;
+}
+
 // idiffu = 2: the nine-point operator o4_c1*(sides) + o4_c2*(corners) + o4_c3*centre with the reference's order of
 // the sums (Main/mod_diffusion.F90:63-65,386-411,592-601,726-735,881-894); pp = (j+1,i+1), mm = (j-1,i-1),
 // mp = (j-1,i+1), pm = (j+1,i-1)

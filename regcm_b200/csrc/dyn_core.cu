@@ -49,6 +49,8 @@ void launch_slice(const Geom&, const Fields&, int id, int hydro, double ptop, do
 void launch_window_strided(bool pack, double* buf, double* p_shifted, int j0, int i0, int k0, int n1, int n2, int nk, long long b1, long long b2, int si, long long sk, cudaStream_t st);
 void launch_window(bool pack, double* buf, double* p_shifted, int j0, int i0, int k0, int n1, int n2, int nk, int si, long long sk, cudaStream_t st);
 void launch_tr(const Geom&, const Fields&, const TrFields&, const StepScalars&, cudaStream_t);
+void launch_tke(const Geom&, const Fields&, const UwFields&, const StepScalars&, cudaStream_t);
+void launch_tke_bdy(const Geom&, const Fields&, const UwFields&, const int2*, int, int, int, cudaStream_t);
 void launch_tr_repair(const Geom&, const TrFields&, const StepScalars&, cudaStream_t);
 void launch_tr_bdyval(const Geom&, const TrFields&, const int2*, int, double, int, int, cudaStream_t);
 void launch_tr_timeint(const Geom&, const double*, const double*, double*, double, int, int, int, int, int, cudaStream_t);
@@ -122,6 +124,9 @@ struct rcm_dyn {
   double* nx[6] = {nullptr};   // staged next record (decoupled)
   // tracers
   TrFields tr{};
+  UwFields uw = {};                       // TKE of the UW PBL (ibltyp = 2)
+  bool uw_on = false;
+  int* kpb = nullptr;                     // kpbl, origin-shifted 2-D (always allocated with ibltyp = 2; f.kpb only with iuwvadv = 1)
   double* tr_b1[RCM_MAXTR] = {nullptr};   // chib1
   double* tr_nx[RCM_MAXTR] = {nullptr};   // staged next record (mixing ratio)
   int64_t neg_chi = 0;
@@ -253,6 +258,7 @@ extern "C" int rcm_dyn_default_cfg(rcm_cfg* c, int idynamic) {
   c->nsplit = 2; c->lstand = 1;  // Main/mod_params.F90:283-284
   c->mo_nadv = 3; c->mo_nsound = 6; c->mo_nzfilt = 3; c->mo_anu2 = 0.6;  // :296-300
   c->mo_a0 = 0.0; c->mo_b0 = 0.5;                                        // Share/mod_dynparam.F90:189-190
+  c->uw_nuk = 5.0; c->uw_tkemin = 1.0e-3;   // Main/mod_params.F90:480; Main/pbllib/mod_pbl_uwtcm.F90:86
   if (idynamic == 2) { c->gnu1 = c->gnu2 = 0.1; c->diffu_hgtf = 0; }
   else { c->gnu1 = c->gnu2 = 0.0625; c->diffu_hgtf = 1; }
   c->ckh = c->adyndif = 1.0;
@@ -473,6 +479,15 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   f.nq_list = dev_alloc_raw<int>(h, (size_t)2 * g.kz * (size_t)g.sk);
   f.nq_cnt = dev_alloc_raw<int>(h, (size_t)2 * g.kz);
   ok = ok && f.hefc && f.hegc && f.hefd && f.hegd && f.tmask && f.cflbits && f.negq && f.nanflag && f.nq_list && f.nq_cnt;
+  if (c.ibltyp == 2 && c.idynamic != 3) {   // UW-PBL coupling of the transport: TKE, kpbl
+    UwFields& uw = h->uw;
+    for (double** p : {&uw.a, &uw.b, &uw.c, &uw.phy}) A3(*p);
+    uw.tkemin = c.uw_tkemin; uw.nuk = c.uw_nuk;
+    int* z = dev_alloc_raw<int>(h, (size_t)g.sk); h->kpb = z ? z + h->off2 : nullptr;
+    ok = ok && z;
+    if (c.iuwvadv == 1) f.kpb = h->kpb;
+    h->uw_on = true;
+  }
   if (c.ntr > 0) {   // tracers
     TrFields& tr = h->tr;
     tr.ntr = c.ntr;
@@ -814,6 +829,7 @@ static int exch_state(rcm_dyn* h) {  // atm1/atm2 all prognostics, width 2 (Main
   std::vector<HaloField> fl = {{f.au, kz, 1}, {f.av, kz, 1}, {f.at, kz, 0}, {f.aqv, kz, 0}, {f.aqc, kz, 0}, {f.app, kz, 0}, {f.aw, kzp1, 0},
                                {f.bu, kz, 1}, {f.bv, kz, 1}, {f.bt, kz, 0}, {f.bqv, kz, 0}, {f.bqc, kz, 0}, {f.bpp, kz, 0}, {f.bw, kzp1, 0}};
   tr_add(h, fl, true);
+  if (h->uw_on) { fl.push_back({h->uw.a, h->g.kzp1, 0}); fl.push_back({h->uw.b, h->g.kzp1, 0}); }   // Main/mod_tendency.F90:870-872,1078-1080
   if (h->halo.exchange(fl, RCM_HALO, h->st))
     return fail(h, RCM_ERR_NCCL, "halo exchange (state) failed");
   return RCM_OK;
@@ -848,6 +864,7 @@ static int exch_h_state(rcm_dyn* h) {   // atm1/atm2 prognostics and p* of both 
   std::vector<HaloField> fl = {{f.au, kz, 1}, {f.av, kz, 1}, {f.at, kz, 0}, {f.aqv, kz, 0}, {f.aqc, kz, 0}, {f.psa - g.sk, 1, 0},
                                {f.bu, kz, 1}, {f.bv, kz, 1}, {f.bt, kz, 0}, {f.bqv, kz, 0}, {f.bqc, kz, 0}, {f.psb - g.sk, 1, 0}};
   tr_add(h, fl, true);
+  if (h->uw_on) { fl.push_back({h->uw.a, h->g.kzp1, 0}); fl.push_back({h->uw.b, h->g.kzp1, 0}); }   // Main/mod_tendency.F90:870-872,1078-1080
   if (h->halo.exchange(fl, RCM_HALO, h->st))
     return fail(h, RCM_ERR_NCCL, "halo exchange (state) failed");
   return RCM_OK;
@@ -863,6 +880,14 @@ static void tr_extents(rcm_dyn* h, int& jclo, int& jchi, int& iclo, int& ichi) {
   const Geom& g = h->g;
   jclo = std::max(1, g.jde1 - RCM_HALO); jchi = std::min(g.jx - 1, g.jde2 + RCM_HALO);
   iclo = std::max(1, g.ide1 - RCM_HALO); ichi = std::min(g.iy - 1, g.ide2 + RCM_HALO);
+}
+// atm1%tke = atm2%tke = tkemin (Main/mod_init.F90:378-380)
+static int init_tke(rcm_dyn* h) {
+  if (!h->uw_on) return RCM_OK;
+  std::vector<double> fill((size_t)h->g.sk * h->g.kzp1, h->uw.tkemin);
+  CUDA_OK(cudaMemcpy(h->uw.a - h->off3, fill.data(), fill.size() * sizeof(double), cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy(h->uw.b - h->off3, fill.data(), fill.size() * sizeof(double), cudaMemcpyHostToDevice));
+  return RCM_OK;
 }
 static int init_tracers(rcm_dyn* h) {
   TrFields& tr = h->tr;
@@ -1275,6 +1300,7 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
   h->day_lastact = 0; h->day_now = 0; h->bdy_lastact = 0; h->bdy_now = 0;
   h->inited = true;
   if ((rc = init_tracers(h))) return rc;
+  if ((rc = init_tke(h))) return rc;
   // first bdyval (Main/mod_regcm_interface.F90:146)
   if ((rc = bdyval(h, f.at, f.aqv, f.aqc))) return rc;
   CUDA_OK(cudaStreamSynchronize(h->st));
@@ -1419,6 +1445,7 @@ static int init_hydro(rcm_dyn* h) {
   }
   h->inited = true;
   if ((rc = init_tracers(h))) return rc;
+  if ((rc = init_tke(h))) return rc;
   // first bdyval (Main/mod_regcm_interface.F90:146)
   if ((rc = bdyval(h, f.at, f.aqv, f.aqc))) return rc;
   CUDA_OK(cudaStreamSynchronize(h->st));
@@ -1431,6 +1458,8 @@ static int bdyval(rcm_dyn* h, const double* oat, const double* oaqv, const doubl
   if (h->hydro) TIMED(KID_BDY, 1, launch_bdyval_ps(h->g, h->f, h->rim_c, h->nrim_c, xt, h->cfg.iboudy, h->st));
   TIMED(KID_BDY, 2, launch_bdyval(h->g, h->f, oat, oaqv, oaqc, h->rim_d, h->nrim_d, h->rim_c, h->nrim_c, xt,
                                   h->lcount > 0 ? 1 : 0, h->cfg.iboudy, h->st));
+  if (h->uw_on)   // TKE rim (Main/mod_bdycod.F90:1166-1307,2412-2496), after the rim winds of this bdyval are in place
+    TIMED(KID_BDY, 2, launch_tke_bdy(h->g, h->f, h->uw, h->rim_c, h->nrim_c, h->lcount > 0 ? 1 : 0, h->cfg.iboudy, h->st));
   if (h->tr.ntr > 0)   // chem_bdyval (Main/mod_bdycod.F90:2558-2564)
     TIMED(KID_BDY, 1, launch_tr_bdyval(h->g, h->tr, h->rim_c, h->nrim_c, xt, h->lcount > 0 ? 1 : 0, h->lcount > 0 ? 1 : 0, h->st));
   h->xbctime = h->xbctime + h->dtsec;
@@ -1600,6 +1629,7 @@ static int tend_hydro(rcm_dyn* h) {
     CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jb, 0));
   }
   if (h->tr.ntr > 0) TIMED(KID_TR, 1, launch_tr(g, f, h->tr, s, h->st));
+  if (h->uw_on) TIMED(KID_TR, 2, launch_tke(g, f, h->uw, s, h->st));   // TKE tendency, forecast, RA filter (in place)
   // splitf reads the new winds one dot row out (Main/mod_split.F90:276-277,312-313); the repair reads the forecast moisture
   TIMED(KID_HALO, 0, rc = exch_h_new(h));
   if (rc) return rc;
@@ -1697,6 +1727,7 @@ static int tend(rcm_dyn* h) {
     CUDA_OK(cudaStreamWaitEvent(h->st, h->ev_jc, 0));
   }
   if (h->tr.ntr > 0) TIMED(KID_TR, 1, launch_tr(g, f, h->tr, s, h->st));
+  if (h->uw_on) TIMED(KID_TR, 2, launch_tke(g, f, h->uw, s, h->st));   // TKE tendency, forecast, RA filter (in place)
   if (!side) TIMED(KID_SND_INIT, 1, launch_snd_init(g, f, s, h->st));
   TIMED(KID_HALO, 0, rc = exch_uvten(h));  // + the first cppd, ct of the step and the moisture forecast
   if (rc) return rc;
@@ -1909,10 +1940,11 @@ static double** phys_ptr(rcm_dyn* h, int field) {
 extern "C" int rcm_dyn_set_phys_tend(rcm_dyn* h, int field, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
   if (h->moloch) return fail(h, RCM_ERR_ARG, "physics tendencies are coupled for idynamic = 1, 2");
-  double** pp = phys_ptr(h, field);
+  double** pp = (field == RCM_F_TKE && h->uw_on) ? &h->uw.phy : phys_ptr(h, field);
   if (!pp || (h->hydro && (field == RCM_F_PP || field == RCM_F_W))) return fail(h, RCM_ERR_ARG, "no physics tendency for this field");
   cudaSetDevice(h->device);
   if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  if (field == RCM_F_TKE) return upload3(h, *pp, a, lb, ub, h->g.kzp1);   // aten%tke(:,:,:,pc_physic), allocated with the handle
   if (!h->f.phy_t) {   // first use: all of them, zero-filled (u and v are added as a pair)
     for (int q : {RCM_F_U, RCM_F_V, RCM_F_T, RCM_F_QV, RCM_F_QC, RCM_F_PP, RCM_F_W}) {
       if (h->hydro && (q == RCM_F_PP || q == RCM_F_W)) continue;
@@ -1933,6 +1965,27 @@ extern "C" int rcm_dyn_clear_phys_tend(rcm_dyn* h) {
     double** pp = phys_ptr(h, q);
     if (pp && *pp) CUDA_OK(cudaMemset(*pp - h->off3, 0, (size_t)h->g.sk * h->g.kzp1 * sizeof(double)));
   }
+  if (h->uw_on) CUDA_OK(cudaMemset(h->uw.phy - h->off3, 0, (size_t)h->g.sk * h->g.kzp1 * sizeof(double)));
+  return RCM_OK;
+}
+
+// kpbl of the PBL scheme for vadv4d ind = 3 (Main/mod_advection.F90:66,92,921-956)
+extern "C" int rcm_dyn_set_kpbl(rcm_dyn* h, const int32_t* kpbl, const int32_t lb[2], const int32_t ub[2]) {
+  if (!h || !kpbl || !lb || !ub) return RCM_ERR_ARG;
+  if (!h->uw_on) return fail(h, RCM_ERR_ARG, "kpbl exists with ibltyp = 2 only (idynamic 1, 2)");
+  cudaSetDevice(h->device);
+  if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  const Geom& g = h->g;
+  std::vector<int> host((size_t)g.sk);
+  CUDA_OK(cudaMemcpy(host.data(), h->kpb - h->off2, host.size() * sizeof(int), cudaMemcpyDeviceToHost));
+  const long long n1 = ub[0] - lb[0] + 1;
+  for (int i = std::max(lb[1], g.ici1); i <= std::min(ub[1], g.ici2); ++i)
+    for (int j = std::max(lb[0], g.jci1); j <= std::min(ub[0], g.jci2); ++j) {
+      const int v = kpbl[(j - lb[0]) + n1 * (i - lb[1])];
+      if (v > g.kz) return fail(h, RCM_ERR_ARG, "kpbl is greater than kz");   // the reference calls fatal (:923-925)
+      host[h->off2 + j + (long long)i * g.si] = v;
+    }
+  CUDA_OK(cudaMemcpy(h->kpb - h->off2, host.data(), host.size() * sizeof(int), cudaMemcpyHostToDevice));
   return RCM_OK;
 }
 
@@ -2005,6 +2058,7 @@ static double* state_ptr(rcm_dyn* h, int field, int level) {
     case RCM_F_W: return A ? f.aw : f.bw;
   }
   if (field >= RCM_F_CHI && field - RCM_F_CHI < h->tr.ntr) return A ? h->tr.a[field - RCM_F_CHI] : h->tr.b[field - RCM_F_CHI];
+  if (field == RCM_F_TKE && h->uw_on) return A ? h->uw.a : h->uw.b;
   return nullptr;
 }
 

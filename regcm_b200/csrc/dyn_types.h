@@ -90,6 +90,14 @@ struct TrFields {
   unsigned long long* negcnt;               // number of negative forecasts of the step
 };
 
+// UW-PBL coupling of the transport (ibltyp = 2): TKE on full levels, NOT coupled with p*
+// (atm1%tke, atm2%tke, atmc%tke; Main/mod_atm_interface.F90:604-606,625-626,656-658)
+struct UwFields {
+  double *a, *b, *c;        // time levels a, b and the unfiltered forecast
+  double* phy;              // aten%tke(:,:,:,pc_physic), zero until set
+  double tkemin, nuk;
+};
+
 struct Fields {
   // prognostic state
   double *au, *av, *at, *aqv, *aqc, *app, *aw;
@@ -140,6 +148,8 @@ struct Fields {
   int *nq_list;                 // [plane * sk + slot] = local offset jl + il*si, plane = n*kz + (k-1)
   int *nq_cnt;                  // [plane]
   int *nanflag;
+  // vadv4d ind = 3 (iuwvadv = 1 with ibltyp = 2): top of the PBL per cross point, 2-D geometry; null = ind 1 / 2
+  const int* kpb;
 };
 
 // ---------------------------------------------------------------------------

@@ -413,6 +413,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
   const double npsb = psa + dps, npsa = psc;
   const double qthr = minqq * psa;          // vadvqv threshold (ps = sfs%psa before the filter)
   const double cthr = minqq * minqq * psa;  // vadv4d ind=1 threshold
+  const int kpb_c = f.kpb ? L2(f.kpb, j, i) : 0;   // top of the PBL for vadv4d ind = 3
   // omega (:1199-1215)
   const double pten = L2(f.pten, j, i);
   const double dummy8 = 1.0 / (s.dx8 * L2(f.msfx, j, i));
@@ -573,7 +574,9 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         if (k < kz) {
           const double aqc_n = L3(f.aqc, j, i, k + 1);
           const double t1 = LD1(&f.twt1[k + 1]), t2 = LD1(&f.twt2[k + 1]);
-          if (svv_n > 0.0) {
+          if (f.kpb) {   // iqxvadv = 3 (Main/mod_tendency.F90:150-153)
+            fl_n = vadv3_face(g, f, f.aqc, j, i, k + 1, kpb_c, aqc_n, ac_c) * svv_n;
+          } else if (svv_n > 0.0) {
             if (ac_c > cthr) fl_n = svv_n * (t1 * aqc_n + t2 * ac_c);
           } else {
             if (aqc_n > cthr) fl_n = svv_n * (t1 * aqc_n + t2 * ac_c);

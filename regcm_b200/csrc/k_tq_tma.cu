@@ -86,6 +86,7 @@ k_tq_tma(const Geom g, const Fields f, const StepScalars s) {
   const double qthr = minqq * psa;           // vadvqv threshold
   const double cthr = minqq * minqq * psa;   // vadv4d ind=1 threshold
   const double beta = 0.53;
+  const int kpb_c = f.kpb ? L2(f.kpb, j, i) : 0;   // top of the PBL for vadv4d ind = 3
 
   double fx_th_k = 0.0, fl_qv_k = 0.0, fl_qc_k = 0.0;
   double tha_k = L3(f.th, j, i, 1) * psa;

@@ -3,7 +3,7 @@
 //                 species, marching k in the reference's order of accumulation:
 //                   decouple            Main/mod_tendency.F90:1029-1034   chi*rpsa
 //                   hadv -> hadvtr      Main/mod_advection.F90:666-720
-//                   vadv -> vadv4d      Main/mod_advection.F90:895-914    ind = 2 (itrvadv, Main/mod_tendency.F90:149)
+//                   vadv -> vadv4d      Main/mod_advection.F90:895-957    ind = 2, or 3 with iuwvadv = 1 (itrvadv, Main/mod_tendency.F90:149-154)
 //                   nudge_chi           Main/chemlib/mod_che_bdyco.F90:898-981   (iboudy 1, 5; exponential tables of
 //                                       setup_che_bdycon :1177-1217; west/east zones sum their neighbours i first)
 //                   diffu_x4d           on chib3d = max(atm2%chi*rpsb, 0)  (Main/mod_slice.F90:198)
@@ -49,6 +49,7 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
   const int nring = d9 ? 0 : ring_count(g, j, i, false);
   const double beta = 0.53;
   const double thr = mintr * psa;
+  const int kpb_c = f.kpb ? L2(f.kpb, j, i) : 0;   // itrvadv = 3 (iuwvadv = 1, Main/mod_tendency.F90:150-154)
 #define RPSB(dj, di) L2(f.rpsb, j + (dj), i + (di))
 
   double fl_k = 0.0;   // vertical flux at the upper interface of level k
@@ -74,7 +75,8 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
     if (k < kz) {
       const double a_n = L3(a1, j, i, k + 1);
       const bool ok = (svv_n > 0.0) ? (ac_c > thr) : (a_n > thr);
-      if (ok) fl_n = svv_n * (LD1(&f.twt1[k + 1]) * a_n + LD1(&f.twt2[k + 1]) * ac_c);
+      if (f.kpb) fl_n = vadv3_face(g, f, a1, j, i, k + 1, kpb_c, a_n, ac_c) * svv_n;
+      else if (ok) fl_n = svv_n * (LD1(&f.twt1[k + 1]) * a_n + LD1(&f.twt2[k + 1]) * ac_c);
       ten = ten - fl_n * xdsk;
     }
     // nudge_chiten

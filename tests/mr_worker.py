@@ -44,7 +44,7 @@ def owned_bounds(core, field):
         return (j1, i1, 1), (j2, i2, kz)
     if field == capi.F_PS:
         return (j1, i1, 1), (min(j2, core.jx - 1), min(i2, core.iy - 1), 1)
-    nk = kz + 1 if field == capi.F_W else kz
+    nk = kz + 1 if field in (capi.F_W, capi.F_TKE) else kz
     return (j1, i1, 1), (min(j2, core.jx - 1), min(i2, core.iy - 1), nk)
 
 
@@ -64,6 +64,7 @@ def main():
     ap.add_argument("--work", action="store_true", help="also dump the per-step work arrays")
     ap.add_argument("--spiky-tracers", action="store_true", help="tracers with sharp edges (drives their negative fix)")
     ap.add_argument("--sharp-q", action="store_true", help="moisture with sharp fronts (drives the negative-q repair)")
+    ap.add_argument("--uw", action="store_true", help="ibltyp = 2 inputs of tests/test_tke.py: TKE state, TKE physics source, kpbl, cloud water")
     ap.add_argument("--out", required=True)
     args = ap.parse_args()
 
@@ -132,6 +133,9 @@ def main():
             q = _spiky(base, n)                    # global array; the library keeps this rank's window
             for lv in (capi.LEVEL_A, capi.LEVEL_B):
                 core.set_state(capi.F_CHI + n, lv, q)
+    if args.uw:
+        from tests.test_tke import load_uw, uw_inputs
+        load_uw(core, case, *uw_inputs(base))      # global arrays; the library keeps this rank's window
     if args.sharp_q:
         from tests.helpers import sharp_moisture
         qv, qc = sharp_moisture(base)          # global arrays; the library keeps this rank's window
@@ -169,6 +173,8 @@ def main():
         core = capi.DynCore(lib, cfg)
         core.comm_init(uid)
         synth.load_case(core, case, stage_next=True)
+        if args.uw:     # kpbl and the physics tendency belong to the caller (kpbl_io of the SAV file), the state is restored below
+            load_uw(core, case, *uw_inputs(base))
         for (f, lv), (lb, a) in sav.items():
             core.set_state(f, lv, a, lb=lb)
         for rid, a in aux.items():
@@ -179,7 +185,7 @@ def main():
         core.step(args.steps)
     out = {"tile": np.array(core.tile())}
     moloch = cfg.idynamic == 3
-    tracers = tuple(capi.F_CHI + n for n in range(cfg.ntr))
+    tracers = tuple(capi.F_CHI + n for n in range(cfg.ntr)) + ((capi.F_TKE,) if cfg.ibltyp == 2 and not moloch else ())
     for fld in (MOLOCH_FIELDS if moloch else HYDRO_FIELDS if cfg.idynamic == 1 else FIELDS) + tracers:
         for lev, tag in (((capi.LEVEL_A, "a"),) if moloch else ((capi.LEVEL_A, "a"), (capi.LEVEL_B, "b"))):
             lb, ub = owned_bounds(core, fld)

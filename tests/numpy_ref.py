@@ -451,14 +451,16 @@ def _wafone_horizontal(pp, wz, fmz, u, v, rmu, rmv, mx2, zdtrdx, zdtrdy, jx, iy,
 
 
 # ---------------------------------------------------------------------------------------------------------
-def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc, ul, dt, gnu2, box, kz, upstream=True, idiffu=1):
+def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc, ul, dt, gnu2, box, kz, upstream=True, idiffu=1,
+                kpb=None, sigma=None):
     """One leapfrog step of ONE tracer away from the lateral zones, written from the Fortran text:
     decouple (Main/mod_tendency.F90:1029-1034), start_advect (Main/mod_advection.F90:109-122: uavg/vavg from the
     p*.u.m fluxes), hadvtr (:666-720), vadv4d ind = 2 (:895-914,946-950), diffu_x4d interior stencil
     (Main/mod_diffusion.F90:658-725 with chib3d = max(atm2%chi*rpsb, 0), Main/mod_slice.F90:198; idiffu = 2: the
     nine-point operator of :881-894 with the weights 4/6, 1/6, -20/6 of :63-65), the sums and the
     forecast (Main/mod_tendency.F90:548-569) and the RAW filter (Main/mod_timefilter.F90:231-278, alpha = gnu2,
-    beta = 0.53, floor 0).  `box` = (j1, j2, i1, i2): interior points at least three rows away from the zones.
+    beta = 0.53, floor 0).  With `kpb` (F array of the PBL top on cross points) and `sigma` (full levels, 1-based F) the
+    vertical flux is vadv4d ind = 3 (:915-957) instead of ind = 2.  `box` = (j1, j2, i1, i2): interior points at least three rows away from the zones.
     Returns (forecast atmc%chi, filtered atm1%chi, filtered atm2%chi) on the box."""
     j1, j2, i1, i2 = box
     K = (1, kz)
@@ -491,6 +493,8 @@ def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc,
     tw1 = twt.s((2, kz), 1)[None, None, :]
     tw2 = twt.s((2, kz), 2)[None, None, :]
     fg = np.where(ok, sv * (tw1 * fk + tw2 * fkm1), 0.0)
+    if kpb is not None:
+        fg = vadv_ind3_faces(c(chia), kpb.s((j1, j2), (i1, i2)), sigma, twt, kz) * sv
     xd = xds.s((1, kz))[None, None, :]
     ten[:, :, :-1] -= fg * xd[:, :, :-1]
     ten[:, :, 1:] += fg * xd[:, :, 1:]
@@ -507,6 +511,93 @@ def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc,
     nb = np.maximum(c(chia) + 0.53 * d, 0.0)
     na = np.maximum(fcp + (0.53 - 1.0) * d, 0.0)
     return fc, na, nb
+
+
+# ---------------------------------------------------------------------------------------------------------
+def vadv_ind3_faces(f, kpb, sigma, twt, kz):
+    """vadv4d ind = 3 (Main/mod_advection.F90:915-957): the value carried through interfaces 2..kz (before the product
+    with sigma-dot) of the p*-coupled scalar f (nj, ni, kz): the twt interpolation, replaced at interfaces kpb-1 and kpb
+    (kpb >= 4) by an extrapolation from level kpb-2 along the limited slope of the layer above.  sigma: F array, full
+    levels 1..kz+1."""
+    sg = lambda k: float(sigma.s(k))                               # noqa: E731
+    hs = lambda k: (sg(k + 1) + sg(k)) * 0.5                       # noqa: E731  (Main/mod_params.F90:2008)
+    fg = np.zeros(f.shape[:2] + (kz + 1,))                         # index = interface number, 2..kz used
+    for k in range(2, kz + 1):
+        fg[:, :, k] = float(twt.s(k, 1)) * f[:, :, k - 1] + float(twt.s(k, 2)) * f[:, :, k - 2]
+    for jj in range(f.shape[0]):
+        for ii in range(f.shape[1]):
+            kp = int(kpb[jj, ii])
+            if kp < 4:
+                continue
+            q = lambda k: f[jj, ii, k - 1]                          # noqa: E731
+            k = kp - 2
+            up, dn = q(k + 1) - q(k), q(k) - q(k - 1)
+            if up > 0.0 and dn > 0.0:
+                slope = min(up / (hs(k + 1) - hs(k)), dn / (hs(k) - hs(k - 1)))
+            elif up < 0.0 and dn < 0.0:
+                slope = max(up / (hs(k + 1) - hs(k)), dn / (hs(k) - hs(k - 1)))
+            else:
+                slope = 0.0
+            k = kp
+            fg[jj, ii, k - 1] = q(k - 2) + slope * (sg(k - 1) - hs(k - 2))
+            if abs(q(k - 2) + slope * (hs(k - 1) - hs(k - 2)) - q(k)) > abs(q(k - 1) - q(k)):
+                fg[jj, ii, k] = q(k)
+            else:
+                fg[jj, ii, k] = q(k - 2) + slope * (sg(k) - hs(k - 2))
+    return fg[:, :, 2:]
+
+
+def tke_step(tkea, tkeb, umc, vmc, psa, rpsa, xmsf, svv, twt, dds, xkcf, tkephy, ul, dt, gnu2, nuk, tkemin, box, kz, upstream=True,
+             idiffu=1):
+    """One leapfrog step of the UW-PBL TKE away from the lateral boundary, written from the Fortran text: hadv3d ind = 1
+    (Main/mod_advection.F90:395-515: winds interpolated to the full levels 2..kz with twt, upstream weights from the
+    half-level winds of level k), vadv3d nk = kzp1 (:755-766) on tke*psa (Main/mod_tendency.F90:1414-1425), diffu_x3df
+    with fac = nuk on atm2%tke (Main/mod_diffusion.F90:523-601, interior stencil; xkcf = the scaled coefficient), the sum
+    tkedyn*rpsa + tkephy, the floored forecast (Main/mod_tendency.F90:518-541) and the RA filter
+    (Main/mod_timefilter.F90:92-110, alpha = gnu2).  tkea / tkeb: atm1 / atm2 TKE (uncoupled) before the step.
+    Returns (atmc%tke, filtered atm1%tke, filtered atm2%tke) on the box, levels 1..kz+1."""
+    j1, j2, i1, i2 = box
+    K, K1 = (1, kz), (1, kz + 1)
+
+    def c(a, dj=0, di=0, k=K):
+        return a.s((j1 + dj, j2 + dj), (i1 + di, i2 + di), k) if len(a.lb) == 3 else a.s((j1 + dj, j2 + dj), (i1 + di, i2 + di))[:, :, None]
+
+    uavg1 = c(umc, 0, 1) + c(umc, 0, 0)
+    uavg2 = c(umc, 1, 1) + c(umc, 1, 0)
+    vavg1 = c(vmc, 1, 0) + c(vmc, 0, 0)
+    vavg2 = c(vmc, 1, 1) + c(vmc, 0, 1)
+    a = lambda dj=0, di=0: c(tkea, dj, di, K1)                     # noqa: E731
+    b = lambda dj=0, di=0: c(tkeb, dj, di, K1)                     # noqa: E731
+    ps = c(psa)
+    ten = np.zeros(a().shape)
+    t1 = twt.s((2, kz), 1)[None, None, :]
+    t2 = twt.s((2, kz), 2)[None, None, :]
+    full = lambda u: t1 * u[:, :, 1:] + t2 * u[:, :, :-1]          # noqa: E731  winds on full levels 2..kz
+    lv = slice(1, kz)                                              # full levels 2..kz
+    f, fjm, fjp, fim, fip = a()[:, :, lv], a(-1, 0)[:, :, lv], a(1, 0)[:, :, lv], a(0, -1)[:, :, lv], a(0, 1)[:, :, lv]
+    if upstream:
+        f1 = (0.5 * ul * (uavg2 + uavg1) / ps)[:, :, 1:]
+        f2 = (0.5 * ul * (vavg2 + vavg1) / ps)[:, :, 1:]
+        fx1, fx2 = (1.0 + f1) * fjm + (1.0 - f1) * f, (1.0 + f1) * f + (1.0 - f1) * fjp
+        fy1, fy2 = (1.0 + f2) * fim + (1.0 - f2) * f, (1.0 + f2) * f + (1.0 - f2) * fip
+    else:
+        fx1, fx2, fy1, fy2 = fjm + f, f + fjp, fim + f, f + fip
+    ten[:, :, lv] -= c(xmsf) * (full(uavg2) * fx2 - full(uavg1) * fx1 + full(vavg2) * fy2 - full(vavg1) * fy1)
+    sv = c(svv, k=K1)
+    tkeps = a() * ps
+    fx = 0.5 * (sv[:, :, :-1] + sv[:, :, 1:]) * (tkeps[:, :, :-1] + tkeps[:, :, 1:])
+    dd = dds.s((1, kz + 1))[None, None, :]
+    ten[:, :, 1:] += fx * dd[:, :, 1:]
+    ten[:, :, :-1] -= fx * dd[:, :, :-1]
+    xk = c(xkcf, k=K1)
+    if idiffu == 2:
+        ten += nuk * xk * (4.0 / 6.0 * (b(1, 0) + b(-1, 0) + b(0, 1) + b(0, -1)) + 1.0 / 6.0 * (b(1, 1) + b(-1, -1) + b(-1, 1) + b(1, -1))
+                           - 20.0 / 6.0 * b())
+    else:
+        ten -= nuk * xk * ((b(2, 0) + b(-2, 0) + b(0, 2) + b(0, -2)) - 4.0 * (b(1, 0) + b(-1, 0) + b(0, 1) + b(0, -1)) + 12.0 * b())
+    fc = np.maximum(tkemin, b() + dt * (ten * c(rpsa) + c(tkephy, k=K1)))
+    d = gnu2 * (fc + b() - 2.0 * a())
+    return fc, fc.copy(), a() + d
 
 
 # ---------------------------------------------------------------------------------------------------------

@@ -282,6 +282,34 @@ def test_tracers_multirank_match_single_rank(emu_lib, tmp_path, idynamic):
     assert negs == ref.diag().neg_chi_points and negs > 0
 
 
+# ---------------------------------------------------------------------------- UW-PBL coupling (TKE, vadv4d ind = 3)
+@pytest.mark.parametrize("idynamic", [2, 1])
+def test_tke_multirank_matches_single_rank(emu_lib, tmp_path, idynamic):
+    """TKE and kpbl on a 2x2 decomposition: both time levels of TKE ride along in the state exchange
+    (Main/mod_tendency.F90:870-872,1078-1080), the rim rule runs on the ghost-extended rim lists."""
+    from tests.test_tke import load_uw, uw_inputs
+    steps = 5
+    run_ranks(4, tmp_path, ["--case", "tiny", "--idynamic", str(idynamic), "--steps", str(steps), "--cpus-j", "2", "--cpus-i", "2",
+                            "--cfg", "ibltyp=2", "--cfg", "iuwvadv=1", "--cfg", "ntr=1", "--uw"])
+    case = synth.make_case("tiny", idynamic=idynamic, ibltyp=2, iuwvadv=1, ntr=1)
+    core = capi.DynCore(emu_lib, case.cfg)
+    synth.load_case(core, case)
+    load_uw(core, case, *uw_inputs(case))
+    core.step(steps)
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    for fld, nk in ((capi.F_TKE, kz + 1), (capi.F_CHI, kz), (capi.F_QC, kz)):
+        for lv, tag in ((0, "a"), (1, "b")):
+            glob = np.full((jx - 1, iy - 1, nk), np.nan)
+            for r in range(4):
+                d = np.load(os.path.join(tmp_path, f"rank{r}.npz"))
+                lb, a = d[f"lb{fld}"], d[f"f{fld}{tag}"]
+                glob[lb[0] - 1:lb[0] - 1 + a.shape[0], lb[1] - 1:lb[1] - 1 + a.shape[1], :] = a
+            want = core.get_state(fld, lv)
+            assert not np.isnan(glob).any()
+            assert np.abs(glob - want).max() <= 1e-12 * np.abs(want).max(), (fld, tag)
+    core.close()
+
+
 # ---------------------------------------------------------------------------- MOLOCH core (idynamic = 3)
 MOLOCH_FIELDS = (capi.F_U, capi.F_V, capi.F_W, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PAI, capi.F_PS)
 

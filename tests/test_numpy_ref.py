@@ -93,15 +93,20 @@ def test_wafone_numpy_vs_oracle():
     assert np.abs(pp.a - want).max() <= 1e-9 * change   # and agrees on the increment, not just on the 300 K background
 
 
-@pytest.mark.parametrize("kw", [{}, {"upstream_mode": 0}, {"idiffu": 2}], ids=["default", "centred", "idiffu2"])
+@pytest.mark.parametrize("kw", [{}, {"upstream_mode": 0}, {"idiffu": 2}, {"ibltyp": 2, "iuwvadv": 1}], ids=["default", "centred", "idiffu2", "ind3"])
 def test_tracer_step_numpy_vs_oracle(kw):
     """hadvtr + vadv4d(ind = 2) + diffu_x4d + forecast + RAW filter of one tracer, away from the lateral
     zones, on the flow of the oracle's 4th step."""
     case = synth.make_case("small", ntr=1, **kw)
     o = pyoracle.make_oracle(case.cfg)
     synth.load_case(o, case)
-    o.step(3)
     jx, iy, kz, nsp = case.cfg.jx, case.cfg.iy, case.cfg.kz, case.cfg.nspgx
+    kpb = sigma = None
+    if kw.get("iuwvadv"):   # vadv4d ind = 3: a PBL top that takes every value 0..kz (>= 4 reshapes the flux)
+        k2 = np.random.default_rng(3).integers(0, kz + 1, size=(jx - 3, iy - 3)).astype(np.int32)
+        o.set_kpbl(k2, lb=(2, 2))
+        kpb, sigma = nr.F(k2, (2, 2)), nr.tap(o, "sigma")
+    o.step(3)
     chia = nr.F(nr.tap(o, "chia0").a.copy(), nr.tap(o, "chia0").lb)
     chib = nr.F(nr.tap(o, "chib0").a.copy(), nr.tap(o, "chib0").lb)
     dt = nr.scalar(o, "dt")
@@ -111,11 +116,46 @@ def test_tracer_step_numpy_vs_oracle(kw):
     box = (nsp + 2, jx - 1 - nsp - 2, nsp + 2, iy - 1 - nsp - 2)
     fc, na, nb = nr.tracer_step(chia, chib, t["ax_umc"], t["ax_vmc"], t["psa"], t["rpsa"], t["rpsb"], t["xmsf"], t["qdot"], t["twt"],
                                 t["xds"], t["xkc"], nr.scalar(o, "ul"), dt, case.cfg.gnu2, box, kz, upstream=case.cfg.upstream_mode != 0,
-                                idiffu=case.cfg.idiffu)
+                                idiffu=case.cfg.idiffu, kpb=kpb, sigma=sigma)
+    if kpb is not None:     # and the reshaping is active: the ind = 2 flux gives a different forecast
+        fc2, _, _ = nr.tracer_step(chia, chib, t["ax_umc"], t["ax_vmc"], t["psa"], t["rpsa"], t["rpsb"], t["xmsf"], t["qdot"], t["twt"],
+                                   t["xds"], t["xkc"], nr.scalar(o, "ul"), dt, case.cfg.gnu2, box, kz)
+        assert np.abs(fc2 - fc).max() > 1e-6 * np.abs(fc).max()
     sl = ((box[0], box[1]), (box[2], box[3]), (1, kz))
     want_c, want_a, want_b = t["chic0"].s(*sl), t["chia0"].s(*sl), t["chib0"].s(*sl)
     assert fc.min() > 0.0 and np.abs(want_c - chib.s(*sl)).max() > 1e-3 * np.abs(want_c).max()   # the step did move the tracer
     sc = np.abs(want_c).max()
+    assert np.abs(fc - want_c).max() <= 1e-12 * sc
+    assert np.abs(na - want_a).max() <= 1e-12 * sc and np.abs(nb - want_b).max() <= 1e-12 * sc
+
+
+@pytest.mark.parametrize("kw", [{}, {"upstream_mode": 0}, {"idiffu": 2}, {"idynamic": 1}], ids=["default", "centred", "idiffu2", "hydro"])
+def test_tke_step_numpy_vs_oracle(kw):
+    """hadv3d(ind = 1) + vadv3d(kz + 1) + diffu_x3df(nuk) + floored forecast + RA filter of the UW-PBL TKE,
+    away from the lateral boundary, on the flow of the oracle's 4th step, with a physics source."""
+    from tests.test_tke import load_uw, uw_inputs
+    case = synth.make_case("small", ibltyp=2, **kw)
+    o = pyoracle.make_oracle(case.cfg)
+    synth.load_case(o, case)
+    tke, src, kpbl, qc = uw_inputs(case)
+    load_uw(o, case, tke, src, kpbl, qc)
+    o.step(3)
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    ta, tb = nr.tap(o, "tke_a"), nr.tap(o, "tke_b")
+    tkea, tkeb = nr.F(ta.a.copy(), ta.lb), nr.F(tb.a.copy(), tb.lb)
+    dt = nr.scalar(o, "dt")
+    psa0 = nr.F(nr.tap(o, "psa").a.copy(), nr.tap(o, "psa").lb)    # idynamic = 1: p* of level a is filtered at the end of the step
+    o.step(1)
+    t = {n: nr.tap(o, n) for n in ("ax_umc", "ax_vmc", "xmsf", "qdot", "twt", "dds", "xkcf", "tke_a", "tke_b", "tke_c")}
+    t["psa"], t["rpsa"] = psa0, nr.F(1.0 / psa0.a, psa0.lb)        # rpsa = 1/psa (Main/mod_tendency.F90:1001-1003)
+    box = (4, jx - 4, 4, iy - 4)
+    fc, na, nb = nr.tke_step(tkea, tkeb, t["ax_umc"], t["ax_vmc"], t["psa"], t["rpsa"], t["xmsf"], t["qdot"], t["twt"], t["dds"], t["xkcf"],
+                             nr.F(src, (1, 1, 1)), nr.scalar(o, "ul"), dt, case.cfg.gnu2, case.cfg.uw_nuk, case.cfg.uw_tkemin, box, kz,
+                             upstream=case.cfg.upstream_mode != 0, idiffu=case.cfg.idiffu)
+    sl = ((box[0], box[1]), (box[2], box[3]), (1, kz + 1))
+    want_c, want_a, want_b = t["tke_c"].s(*sl), t["tke_a"].s(*sl), t["tke_b"].s(*sl)
+    sc = np.abs(want_c).max()
+    assert np.abs(want_c - tkeb.s(*sl)).max() > 1e-3 * sc            # the step did change the TKE
     assert np.abs(fc - want_c).max() <= 1e-12 * sc
     assert np.abs(na - want_a).max() <= 1e-12 * sc and np.abs(nb - want_b).max() <= 1e-12 * sc
 

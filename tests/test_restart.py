@@ -15,6 +15,7 @@ def fields_of(cfg):
         f = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PS)
     else:
         f = (capi.F_U, capi.F_V, capi.F_T, capi.F_QV, capi.F_QC, capi.F_PP, capi.F_W)
+    f = f + ((capi.F_TKE,) if cfg.ibltyp == 2 else ())
     return f + tuple(capi.F_CHI + n for n in range(cfg.ntr)), (capi.LEVEL_A, capi.LEVEL_B)
 
 
@@ -30,9 +31,11 @@ def save(core):
     return sav
 
 
-def restore(lib, case, sav):
+def restore(lib, case, sav, prep=None):
     core = capi.DynCore(lib, case.cfg)
     synth.load_case(core, case)                       # statics, the boundary records that bracket the restart date, init
+    if prep:
+        prep(core, case)                              # what the caller owns: kpbl (kpbl_io of the SAV file), physics tendencies
     for (f, lv), a in sav["state"].items():
         core.set_state(f, lv, a)
     if "dstor" in sav:
@@ -43,14 +46,16 @@ def restore(lib, case, sav):
     return core
 
 
-def check_restart(lib, name, n1, n2, **kw):
+def check_restart(lib, name, n1, n2, prep=None, **kw):
     case = synth.make_case(name, **kw)
     ref = capi.DynCore(lib, case.cfg)
     synth.load_case(ref, case)
+    if prep:
+        prep(ref, case)
     ref.step(n1)
     sav = save(ref)
     ref.step(n2)
-    new = restore(lib, case, sav)
+    new = restore(lib, case, sav, prep)
     assert new.diag().lcount == n1
     new.step(n2)
     flds, levels = fields_of(case.cfg)
@@ -67,6 +72,15 @@ def check_restart(lib, name, n1, n2, **kw):
                          ids=["nh", "nh-tracers", "hydro", "hydro-nsplit3-tracers", "moloch"])
 def test_restart_continues_bit_for_bit(emu_lib, name, kw):
     check_restart(emu_lib, name, 5, 6, **kw)
+
+
+@pytest.mark.parametrize("idynamic", [2, 1])
+def test_restart_with_tke(emu_lib, idynamic):
+    """ibltyp = 2: atm1%tke / atm2%tke travel through get_state / set_state like the other prognostics
+    (atm1_tke_io, atm2_tke_io of Main/mod_savefile.F90); kpbl and the physics tendency are the caller's."""
+    from tests.test_tke import load_uw, uw_inputs
+    check_restart(emu_lib, "tiny", 5, 6, prep=lambda c, case: load_uw(c, case, *uw_inputs(case)), idynamic=idynamic, ibltyp=2,
+                  iuwvadv=1, ntr=1)
 
 
 def test_restart_in_the_start_up_steps(emu_lib):

@@ -1,0 +1,99 @@
+"""UW-PBL coupling of the transport (ibltyp = 2): TKE advection / diffusion / forecast / RA filter
+(Main/mod_tendency.F90:518-544,1414-1425,1544-1548), its boundary rule (Main/mod_bdycod.F90:1166-1307,2412-2496) and
+vadv4d ind = 3 for qc and the tracers around the PBL top kpbl (Main/mod_advection.F90:915-957; iuwvadv = 1).
+
+CPU suite: the CUDA sources through the host harness (tests/emu) against the oracle, bit for bit for idynamic = 2
+(the kernels evaluate the reference's expressions in the reference's order), to the eigen-solver tolerance for
+idynamic = 1.  The oracle itself is pinned by NumPy restatements of the TKE step and of the ind = 3 flux
+(tests/test_numpy_ref.py::test_tke_step_numpy_vs_oracle, ::test_tracer_step_numpy_vs_oracle[ind3]) and by the
+properties of the boundary rule checked here."""
+import numpy as np
+import pytest
+
+from oracle import pyoracle
+from regcm_b200 import capi, synth
+from tests.helpers import make_pair, rel_errors, smooth_qc
+
+NTR = 2
+
+
+def uw_inputs(case, seed=5):
+    """Global arrays: a TKE field with a boundary-layer profile and horizontal structure (both time levels start from
+    it), a physics source, a PBL top that varies between 0 (unset) and kz, and a smooth cloud-water field."""
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    rng = np.random.default_rng(seed)
+    J, I, K = np.meshgrid(np.arange(jx - 1), np.arange(iy - 1), np.arange(kz + 1), indexing="ij")
+    prof = np.exp(-((kz - K) / 4.0) ** 2)                       # largest near the surface (k = kz + 1)
+    tke = 1.0e-3 + 1.5 * prof * (1.0 + 0.6 * np.sin(2 * np.pi * J / 9.0) * np.cos(2 * np.pi * I / 7.0)) ** 2
+    tke[5:8, 6:10, kz - 3:] += 2.0                              # a sharp patch
+    src = 1.0e-3 * prof * (1.0 + np.cos(2 * np.pi * (J + I) / 11.0))
+    kpbl = rng.integers(0, kz + 1, size=(jx - 3, iy - 3)).astype(np.int32)     # cross interior 2..jx-2, 2..iy-2
+    kpbl[::5, ::3] = kz
+    kpbl[1::5, ::4] = 4
+    return np.asfortranarray(tke), np.asfortranarray(src), np.asfortranarray(kpbl), smooth_qc(case)
+
+
+def load_uw(c, case, tke, src, kpbl, qc, with_src=True):
+    for lv in (capi.LEVEL_A, capi.LEVEL_B):
+        c.set_state(capi.F_TKE, lv, tke)
+        c.set_state(capi.F_QC, lv, qc)
+    if with_src:
+        c.set_phys_tend(capi.F_TKE, src[1:-1, 1:-1, :], lb=(2, 2, 1))
+    if case.cfg.iuwvadv == 1:
+        c.set_kpbl(kpbl, lb=(2, 2))
+
+
+def _compare(core, ref, tol, ntr):
+    for name, (linf, _) in rel_errors(core, ref).items():
+        assert linf <= tol, (name, linf)
+    for fld in (capi.F_TKE,) + tuple(capi.F_CHI + n for n in range(ntr)):
+        for lv in (capi.LEVEL_A, capi.LEVEL_B):
+            a, r = core.get_state(fld, lv), ref.get_state(fld, lv)
+            assert np.isfinite(r).all() and np.abs(a - r).max() <= tol * np.abs(r).max(), (fld, lv)
+
+
+@pytest.mark.parametrize("kw", [{}, {"iboudy": 1}, {"iboudy": 0}, {"iboudy": 4}, {"upstream_mode": 0}, {"idiffu": 2},
+                                {"iuwvadv": 1, "ntr": NTR}, {"idynamic": 1}, {"idynamic": 1, "iuwvadv": 1, "ntr": NTR}],
+                         ids=lambda k: "-".join(f"{a}{b}" for a, b in k.items()) or "default")
+def test_emu_tke_bit_exact(emu_lib, kw):
+    case, core, ref = make_pair(emu_lib, "tiny", oracle_checked=True, ibltyp=2, **kw)
+    inp = uw_inputs(case)
+    for c in (core, ref):
+        load_uw(c, case, *inp)
+        c.step(6)
+    _compare(core, ref, 1e-11 if kw.get("idynamic") == 1 else 0.0, kw.get("ntr", 0))
+    t = ref.get_state(capi.F_TKE, capi.LEVEL_A)
+    assert t.min() >= case.cfg.uw_tkemin and np.abs(t - inp[0]).max() > 1e-3      # it moved, and the floor holds
+
+
+def test_emu_tke_through_a_record_change(emu_lib):
+    case, core, ref = make_pair(emu_lib, "tiny", ibltyp=2, iuwvadv=1, ntr=1, ibdyfrq=1)
+    inp = uw_inputs(case)
+    for c in (core, ref):
+        load_uw(c, case, *inp)
+        c.step(34)      # record change at step 30
+    _compare(core, ref, 1e-11, 1)
+
+
+def test_tke_rim_rule():
+    """bdyval (Main/mod_bdycod.F90:2412-2496): rim = tkemin at start; afterwards level 1 = tkemin on the whole rim,
+    levels 3..kz+1 either tkemin (inflow) or the interior neighbour's value (outflow), level 2 of level a untouched."""
+    case = synth.make_case("tiny", ibltyp=2)
+    o = pyoracle.make_oracle(case.cfg)
+    synth.load_case(o, case)
+    tmin = case.cfg.uw_tkemin
+    a0 = o.get_state(capi.F_TKE, capi.LEVEL_A)
+    for a in (a0, o.get_state(capi.F_TKE, capi.LEVEL_B)):
+        assert np.all(a == tmin)                              # init: tkemin everywhere
+    tke, src, kpbl, qc = uw_inputs(case)
+    load_uw(o, case, tke, src, kpbl, qc)
+    o.step(3)
+    a, b = o.get_state(capi.F_TKE, capi.LEVEL_A), o.get_state(capi.F_TKE, capi.LEVEL_B)
+    rim = np.ones(a.shape[:2], bool); rim[1:-1, 1:-1] = False
+    assert np.all(a[rim, 0] == tmin) and np.all(b[rim, 0] == tmin)
+    w, inner = a[0, 1:-1, 2:], a[1, 1:-1, 2:]
+    assert np.all((w == tmin) | (w == inner))
+    assert (w == tmin).any() and (w == inner).any() and (inner != tmin).all()     # both branches occur
+    s, inner_s = a[1:-1, 0, 2:], a[1:-1, 1, 2:]
+    assert np.all((s == tmin) | (s == inner_s))
+    assert np.all(a[0, 1:-1, 1] == tke[0, 1:-1, 1])           # level 2 of the west rim keeps what set_state put there
