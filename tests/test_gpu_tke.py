@@ -1,6 +1,8 @@
 """UW-PBL coupling of the transport (ibltyp = 2: TKE, vadv4d ind = 3) on the GPU through the C ABI against
-the oracle, same cases as tests/test_tke.py.  Tolerance 1e-11 relative L-inf after 8 steps, as for the other
-prognostics (tests/test_gpu_parity.py)."""
+the oracle, same cases as tests/test_tke.py.  TKE alone: 1e-11 relative L-inf after 8 steps, as for the other prognostics
+(tests/test_gpu_parity.py).  With vadv4d ind = 3 the reference's flux selection is a rounding-level tie in about half of
+the columns (tests/test_tke.py, module docstring), so a free-running comparison across libm implementations measures
+that tie, not the kernel: the GPU is compared one step at a time along the oracle's trajectory, from identical input."""
 import numpy as np
 import pytest
 
@@ -21,8 +23,35 @@ def _compare(core, ref, tol, ntr):
             assert np.abs(a - r).max() <= tol * np.abs(r).max(), (fld, lv)
 
 
-@pytest.mark.parametrize("kw", [{}, {"iboudy": 1}, {"iboudy": 4}, {"idiffu": 2}, {"iuwvadv": 1, "ntr": 2}, {"idynamic": 1},
-                                {"idynamic": 1, "iuwvadv": 1, "ntr": 2}],
+def _sync_state(core, ref):
+    from tests.test_restart import fields_of
+    flds, levels = fields_of(ref.cfg)
+    for f in flds:
+        for lv in levels:
+            core.set_state(f, lv, ref.get_state(f, lv))
+
+
+@pytest.mark.parametrize("idynamic", [2, 1])
+def test_gpu_ind3_along_the_oracle_trajectory(cuda_lib, idynamic):
+    case, core, ref = make_pair(cuda_lib, "small", ibltyp=2, iuwvadv=1, ntr=2, idynamic=idynamic)
+    inp = uw_inputs(case)
+    for c in (core, ref):
+        load_uw(c, case, *inp)
+    for n in range(6):
+        if n:
+            _sync_state(core, ref)
+        core.step(1); ref.step(1)
+        _compare(core, ref, 1e-12, 2)
+    # and the reshaping was active: the same six steps without it end somewhere else
+    case0, core0, ref0 = make_pair(cuda_lib, "small", ibltyp=2, iuwvadv=0, ntr=2, idynamic=idynamic)
+    load_uw(ref0, case0, *inp)
+    ref0.step(6)
+    qa, qb = ref.get_state(capi.F_QC), ref0.get_state(capi.F_QC)
+    assert np.abs(qa - qb).max() > 1e-4 * np.abs(qa).max()
+    core.close(); core0.close()
+
+
+@pytest.mark.parametrize("kw", [{}, {"iboudy": 1}, {"iboudy": 4}, {"idiffu": 2}, {"idynamic": 1}],
                          ids=lambda k: "-".join(f"{a}{b}" for a, b in k.items()) or "default")
 def test_gpu_tke_vs_oracle(cuda_lib, kw):
     case, core, ref = make_pair(cuda_lib, "small", ibltyp=2, **kw)
@@ -35,7 +64,7 @@ def test_gpu_tke_vs_oracle(cuda_lib, kw):
 
 
 def test_gpu_tke_record_change(cuda_lib):
-    case, core, ref = make_pair(cuda_lib, "tiny", ibltyp=2, iuwvadv=1, ntr=1, ibdyfrq=1)
+    case, core, ref = make_pair(cuda_lib, "tiny", ibltyp=2, ntr=1, ibdyfrq=1)
     inp = uw_inputs(case)
     for c in (core, ref):
         load_uw(c, case, *inp)

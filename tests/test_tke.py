@@ -6,7 +6,16 @@ CPU suite: the CUDA sources through the host harness (tests/emu) against the ora
 (the kernels evaluate the reference's expressions in the reference's order), to the eigen-solver tolerance for
 idynamic = 1.  The oracle itself is pinned by NumPy restatements of the TKE step and of the ind = 3 flux
 (tests/test_numpy_ref.py::test_tke_step_numpy_vs_oracle, ::test_tracer_step_numpy_vs_oracle[ind3]) and by the
-properties of the boundary rule checked here."""
+properties of the boundary rule checked here.
+
+A property of the reference's ind = 3 flux that shapes these tests: whenever the limited slope is the one of the lower
+layer, slope = (f(kp-1) - f(kp-2)) / (hsigma(kp-1) - hsigma(kp-2)), the extrapolation f(kp-2) + slope*(hsigma(kp-1) -
+hsigma(kp-2)) of Main/mod_advection.F90:946-948 IS f(kp-1) in exact arithmetic, so the test |extrapolation - f(kp)| >
+|f(kp-1) - f(kp)| that picks the flux at interface kp is a tie that rounding decides — in about half of the columns with
+kpbl >= 4.  The two candidates differ at O(1): the scheme amplifies last-bit differences of its input to 1e-3 of qc within
+8 steps (test_ind3_is_rounding_sensitive measures it on the oracle alone).  Same-arithmetic comparisons (host harness vs
+oracle, multi-rank vs single rank) are bit for bit and unaffected; a comparison across libm implementations (GPU vs
+oracle) is meaningful one step at a time from identical input, which is how tests/test_gpu_tke.py does it."""
 import numpy as np
 import pytest
 
@@ -97,3 +106,25 @@ def test_tke_rim_rule():
     s, inner_s = a[1:-1, 0, 2:], a[1:-1, 1, 2:]
     assert np.all((s == tmin) | (s == inner_s))
     assert np.all(a[0, 1:-1, 1] == tke[0, 1:-1, 1])           # level 2 of the west rim keeps what set_state put there
+
+
+def test_ind3_is_rounding_sensitive():
+    """The oracle against itself: T perturbed by 1e-15 relative changes qc by more than 1e-6 after 8 steps with
+    iuwvadv = 1 and by less than 1e-12 with iuwvadv = 0 (see the module docstring for the tie that causes it)."""
+    out = {}
+    for iuw in (0, 1):
+        res = []
+        for eps in (0.0, 1.0e-15):
+            case = synth.make_case("small", ibltyp=2, iuwvadv=iuw)
+            o = pyoracle.make_oracle(case.cfg)
+            synth.load_case(o, case)
+            load_uw(o, case, *uw_inputs(case))
+            if eps:
+                rng = np.random.default_rng(1)
+                for lv in (capi.LEVEL_A, capi.LEVEL_B):
+                    t = o.get_state(capi.F_T, lv)
+                    o.set_state(capi.F_T, lv, t * (1.0 + eps * rng.standard_normal(t.shape)))
+            o.step(8)
+            res.append(o.get_state(capi.F_QC, capi.LEVEL_A))
+        out[iuw] = np.abs(res[0] - res[1]).max() / np.abs(res[0]).max()
+    assert out[0] < 1e-12 < 1e-6 < out[1], out
