@@ -232,7 +232,8 @@ typedef struct rcm_cfg {
   int32_t ibltyp;         /* 2: the UW PBL is on, TKE (RCM_F_TKE) is carried and transported; anything else: no TKE     */
   int32_t iuwvadv;        /* 1 (with ibltyp = 2): vadv4d ind = 3 for qc and the tracers, which reshapes the vertical flux
                            * around the PBL top kpbl handed in with rcm_dyn_set_kpbl (Main/mod_advection.F90:915-957)  */
-  int32_t reserved_i[1];
+  int32_t ipgf;           /* idynamic = 1: 0 = pressure gradient force from p*.Tv (default); 1 = from the deviation of Tv from
+                           * the reference profile t00pg (p/p00pg)^pgfaa1 (Main/mod_tendency.F90:1893-1964,2039-2068) */
   /* &geoparam */
   double ds;    /* grid spacing [km]                                       */
   double ptop;  /* model top pressure [cb]                                 */

@@ -26,6 +26,8 @@ constexpr double rgas = c287 * 1000.0;        // :134
 constexpr double cpd = 3.5 * rgas;            // :144
 constexpr double cvd = 2.5 * rgas;            // :145
 constexpr double regrav = d_one / egrav;      // :182
+// pressure gradient force with ipgf = 1 (Share/mod_constants.F90:359-362)
+constexpr double t00pg = 287.0, p00pg = 101.325, alam = 6.5e-3, pgfaa1 = alam * rgas * regrav;
 constexpr double rcpd = d_one / cpd;          // :183
 constexpr double rovcp = rgas * rcpd;         // :184
 constexpr double rovg = rgas / egrav;         // :187

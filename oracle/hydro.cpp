@@ -13,7 +13,7 @@
 //   hadvuv (hydro branches)         Main/mod_advection.F90:142-168,203-234
 //   vadv3d ind = 1 (hydro)          Main/mod_advection.F90:771-783
 //   curvature / adiabatic (hydro)   Main/mod_tendency.F90:1829-1838,1561-1575
-//   pressure_gradient_force ipgf=0  Main/mod_tendency.F90:1965-2115
+//   pressure_gradient_force ipgf=0,1  Main/mod_tendency.F90:1886-2115
 //   filter_ra_2d                    Main/mod_timefilter.F90:58-73
 //   tend (hydro path)               Main/mod_tendency.F90:212-616
 // The split-explicit scheme (spinit, splitf, spstep, vmodes) is in split.cpp.
@@ -344,7 +344,8 @@ void Oracle::vadv3d_ind1_hydro(A3& ften, const A3& f) {
       }
 }
 
-// Main/mod_tendency.F90:1886-2119, ipgf = 0 branch.  alpha_hyd = 0,
+// Main/mod_tendency.F90:1886-2119, both ipgf branches (ipgf = 1: the reference's first loop runs `do k = - 1 , kz`,
+// :1894 — levels -1 and 0 are outside td / ttld / atm1%t; the levels 1..kz it defines are restated).  alpha_hyd = 0,
 // beta_hyd = 1 - 2*alpha_hyd (Share/mod_constants.F90:319-320); qvd, qcd are
 // atmx%qx(:,:,:,iqv|iqc) (:113-121, ipptls == 1).
 void Oracle::pressure_gradient_force() {
@@ -365,10 +366,19 @@ void Oracle::pressure_gradient_force() {
     for (int j = jce1; j <= jce2; ++j) td(j, ice1, k) = a1_t(j, ice1, k) * (d_one + ep1 * ax_qx(j, ice1, k, iqv));
   for (int k = 1; k <= kz; ++k)
     for (int j = jce1; j <= jce2; ++j) td(j, ice2, k) = a1_t(j, ice2, k) * (d_one + ep1 * ax_qx(j, ice2, k, iqv));
+  const bool pg1 = (cfg.ipgf == 1);
+  if (pg1) {   // ttld (:1901-1902,1909-1910,...): on every point td is defined on
+    if (ttld.d.size() != td.d.size()) ttld.alloc(jce1, jce2, ice1, ice2, 1, kz);
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ice1; i <= ice2; ++i)
+        for (int j = jce1; j <= jce2; ++j)
+          ttld(j, i, k) = td(j, i, k) - psa(j, i) * t00pg * std::pow((hsigma(k) * psa(j, i) + ptop) / p00pg, pgfaa1);
+  }
   for (int k = 1; k <= kz; ++k)
     for (int i = idi1; i <= idi2; ++i)
       for (int j = jdi1; j <= jdi2; ++j) {
         double rtbar = d_rfour * (ax_tv(j - 1, i - 1, k) + ax_tv(j - 1, i, k) + ax_tv(j, i - 1, k) + ax_tv(j, i, k));
+        if (pg1) rtbar = rtbar - t00pg * std::pow((hsigma(k) * psdota(j, i) + ptop) / p00pg, pgfaa1);
         rtbar = rgas * rtbar * psdota(j, i);
         udyn(j, i, k) = udyn(j, i, k) -
                         rtbar * (std::log(d_half * (psa(j, i) + psa(j, i - 1)) * hsigma(k) + ptop) -
@@ -385,14 +395,18 @@ void Oracle::pressure_gradient_force() {
         tvfac(j, i, k) = d_one / (d_one + ax_qx(j, i, k, iqc) / (d_one + ax_qx(j, i, k, iqv)));
   for (int i = ice1; i <= ice2; ++i)
     for (int j = jce1; j <= jce2; ++j) {
-      double tv = td(j, i, kz) * rpsa(j, i) * tvfac(j, i, kz);
-      phi(j, i, kz) = ht(j, i) - rgas * tv * std::log((hsigma(kz) + ptop * rpsa(j, i)) / (d_one + ptop * rpsa(j, i)));
+      const A3& tq = pg1 ? ttld : td;
+      double tv = tq(j, i, kz) * rpsa(j, i) * tvfac(j, i, kz);
+      phi(j, i, kz) = ht(j, i);
+      if (pg1) phi(j, i, kz) = ht(j, i) + rgas * t00pg / pgfaa1 * std::pow((psa(j, i) + ptop) / p00pg, pgfaa1);   // :2046-2047
+      phi(j, i, kz) = phi(j, i, kz) - rgas * tv * std::log((hsigma(kz) + ptop * rpsa(j, i)) / (d_one + ptop * rpsa(j, i)));
     }
   for (int k = 1; k <= kz - 1; ++k) {
     int lev = kz - k;
     for (int i = ice1; i <= ice2; ++i)
       for (int j = jce1; j <= jce2; ++j) {
-        double tvavg = ((td(j, i, lev) * dsigma(lev) + td(j, i, lev + 1) * dsigma(lev + 1)) /
+        const A3& tq = pg1 ? ttld : td;
+        double tvavg = ((tq(j, i, lev) * dsigma(lev) + tq(j, i, lev + 1) * dsigma(lev + 1)) /
                         (psa(j, i) * (dsigma(lev) + dsigma(lev + 1)))) * tvfac(j, i, lev);
         phi(j, i, lev) = phi(j, i, lev + 1) -
                          rgas * tvavg * std::log((hsigma(lev) + ptop * rpsa(j, i)) / (hsigma(lev + 1) + ptop * rpsa(j, i)));

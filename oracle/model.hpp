@@ -185,7 +185,7 @@ struct Oracle {
 
   bool hydro = false;
   A2 pten, pten_raw, rpsc, ptn2d, pt22d;          // mod_tendency.F90:63-66
-  A3 phi, td, tvfac, pf3d, pb3d;        // mod_tendency.F90:57-62, atms%pf3d/pb3d
+  A3 phi, td, ttld, tvfac, pf3d, pb3d;        // mod_tendency.F90:57-62, atms%pf3d/pb3d
   V2dBound xpsb;                        // mod_atm_interface.F90 xpsb
   A2 nx_ps;                             // staged next ps record [hPa]
   double ptntot = 0, pt2tot = 0;

@@ -59,7 +59,7 @@ class RcmCfg(C.Structure):
         ("mo_nadv", C.c_int32), ("mo_nsound", C.c_int32), ("mo_nzfilt", C.c_int32), ("mo_rotllr", C.c_int32),
         ("ntr", C.c_int32),
         ("ibltyp", C.c_int32), ("iuwvadv", C.c_int32),
-        ("reserved_i", C.c_int32 * 1),
+        ("ipgf", C.c_int32),
         ("ds", C.c_double), ("ptop", C.c_double),
         ("dt", C.c_double),
         ("gnu1", C.c_double), ("gnu2", C.c_double), ("ckh", C.c_double), ("adyndif", C.c_double),

@@ -28,6 +28,8 @@ constexpr double cpovr = cpd / rgas;
 constexpr double minqc = 1.0e-10;
 constexpr double tzero = 273.15;
 constexpr double regrav = 1.0 / egrav;
+// pressure gradient force with ipgf = 1 (Share/mod_constants.F90:359-362)
+constexpr double t00pg = 287.0, p00pg = 101.325, alam = 6.5e-3, pgfaa1 = alam * rgas * regrav;
 constexpr double rcpd = 1.0 / cpd;
 constexpr double rovcp = rgas * rcpd;
 constexpr double rovg = rgas / egrav;

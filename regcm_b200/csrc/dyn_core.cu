@@ -328,6 +328,7 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   if (h->moloch && (c.mo_nadv < 1 || c.mo_nsound < 1 || c.kz < 4 || c.ipptls < 0 || c.ipptls > 1))
     return bail(RCM_ERR_ARG, "idynamic=3 needs mo_nadv >= 1, mo_nsound >= 1, kz >= 4, ipptls 0 or 1");
   if (h->hydro && (c.nsplit < 1 || c.nsplit > RCM_MAXSPLIT || c.nsplit > c.kz)) return bail(RCM_ERR_ARG, "nsplit must be 1..4");
+  if (c.ipgf != 0 && c.ipgf != 1) return bail(RCM_ERR_ARG, "ipgf must be 0 or 1");
   if (c.idiffu != 1 && c.idiffu != 2) return bail(RCM_ERR_ARG, "idiffu must be 1 or 2 (3, the flux-limited 6th-order operator, is not implemented)");
   // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)
   if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 4 || c.iboudy == 5 || (c.idynamic != 3 && (c.iboudy == 2 || c.iboudy == 3))))
@@ -1225,7 +1226,7 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
   s.gnu1 = c.gnu1; s.gnu2 = c.gnu2; s.t_extrema = c.t_extrema; s.q_rel_extrema = c.q_rel_extrema;
   s.ptop = ptop;
   s.upstream_mode = c.upstream_mode; s.stability_enhance = c.stability_enhance; s.ipptls = c.ipptls;
-  s.iboudy = c.iboudy; s.ifrayd = c.ifrayd; s.ifupr = c.ifupr; s.idiffu = c.idiffu;
+  s.iboudy = c.iboudy; s.ifrayd = c.ifrayd; s.ifupr = c.ifupr; s.idiffu = c.idiffu; s.ipgf = c.ipgf;
   s.kt_ray = std::min(kz, c.rayndamp); s.ktf_ray = std::min(kzp1, c.rayndamp);
   s.nspgx = c.nspgx; s.nspgd = c.nspgd;
   s.hydro = h->hydro ? 1 : 0; s.nsplit = h->hydro ? c.nsplit : 0; s.integrating = 0;

@@ -61,6 +61,7 @@ struct StepScalars {
   int cq_mode;
   // ---- hydrostatic core (idynamic = 1) ----
   int hydro;     // 1: idynamic = 1
+  int ipgf;      // pressure gradient force scheme of the hydrostatic core (0, 1)
   int integrating;  // rcmtimer%integrating(): lcount > 0
   // split-explicit scheme (Main/mod_split.F90): per mode l = 0..nsplit-1
   int nsplit;

@@ -8,7 +8,7 @@
 //                                             Main/mpplib/mod_mppparam.F90:13811-13862
 //   k_h_rimcopy carries the physical-boundary rows into the double-buffered "next" levels
 //   k_h_prep    compute_omega (cr, pten, qdot) :1127-1156; geopotential phi of
-//               pressure_gradient_force :2033-2097 (ipgf = 0); new_pressure :1428-1460
+//               pressure_gradient_force :2033-2097 (ipgf = 0, 1); new_pressure :1428-1460
 //               with nudge2d Main/mod_bdycod.F90:4597-4766
 //   k_h_uv      hadvuv (hydro) Main/mod_advection.F90:203-234, vadvuv :271-303,
 //               curvature :1829-1838, nudgeuv, diffu_d, pressure_gradient_force
@@ -155,14 +155,18 @@ k_h_prep(const Geom g, const Fields f, const StepScalars s) {
       if (pfd > 0 && k - pfd >= 1) pf_t(k - pfd);
       const double qvd = fmax(L3(f.aqv, j, i, k) * rpsa, minqq);
       const double qcd = fmax(L3(f.aqc, j, i, k) * rpsa, 0.0);
-      const double td = L3(f.at, j, i, k) * (1.0 + ep1 * qvd);
+      double td = L3(f.at, j, i, k) * (1.0 + ep1 * qvd);
       const double tvfac = 1.0 / (1.0 + qcd / (1.0 + qvd));
       const double hs = (LD1(&f.sigma[k + 1]) + LD1(&f.sigma[k])) * 0.5;
+      // ipgf = 1: ttld = td - p*.t00pg.(p/p00pg)^pgfaa1 takes the place of td (:1901-1902,2044,2060-2062)
+      if (s.ipgf == 1) td = td - psa * t00pg * pow_pos((hs * psa + s.ptop) / p00pg, pgfaa1);
       const double ds = LD1(&f.dsigma[k]);
       double phi;
       if (k == kz) {
         const double tv = td * rpsa * tvfac;
-        phi = L2(f.ht, j, i) - rgas * tv * log((hs + ptr) / (1.0 + ptr));
+        phi = L2(f.ht, j, i);
+        if (s.ipgf == 1) phi = L2(f.ht, j, i) + rgas * t00pg / pgfaa1 * pow_pos((psa + s.ptop) / p00pg, pgfaa1);   // :2046-2047
+        phi = phi - rgas * tv * log((hs + ptr) / (1.0 + ptr));
       } else {
         const double tvavg = ((td * ds + td_n * ds_n) / (psa * (ds + ds_n))) * tvfac;
         phi = phi_n - rgas * tvavg * log((hs + ptr) / (hs_n + ptr));
@@ -344,12 +348,13 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
 #undef DU
 #undef DV
     }
-    // ---- pressure gradient force, ipgf = 0 (Main/mod_tendency.F90:1996-2025,2103-2115) ----
+    // ---- pressure gradient force, ipgf = 0 / 1 (Main/mod_tendency.F90:1942-1964,1996-2025,2103-2115) ----
     {
       const double hs = (LD1(&f.sigma[k + 1]) + LD1(&f.sigma[k])) * 0.5;
 #define TV(jj, ii, ra) ((L3(f.at, jj, ii, k) * (ra)) * (1.0 + ep1 * fmax(L3(f.aqv, jj, ii, k) * (ra), minqq)))
       double rtbar = 0.25 * (TV(j - 1, i - 1, ra00) + TV(j - 1, i, ra01) + TV(j, i - 1, ra10) + TV(j, i, ra11));
 #undef TV
+      if (s.ipgf == 1) rtbar = rtbar - t00pg * pow_pos((hs * psdota + s.ptop) / p00pg, pgfaa1);   // :1945-1947
       rtbar = rgas * rtbar * psdota;
       ut = ut - div_r(rtbar * (log(0.5 * (pa11 + pa10) * hs + s.ptop) - log(0.5 * (pa01 + pa00) * hs + s.ptop)), dxm, rdxm);
       vt = vt - div_r(rtbar * (log(0.5 * (pa11 + pa01) * hs + s.ptop) - log(0.5 * (pa00 + pa10) * hs + s.ptop)), dxm, rdxm);
