@@ -446,13 +446,20 @@ void Oracle::tend_hydro() {
   qxten.fill(d_zero); qxdyn.fill(d_zero);
   // advection (:1270-1392), ithadv = 0
   start_advect();
+  if (cfg.isladvec == 1 && (sl_rc = trajcalc_x())) return;   // :1283-1285
   hadvuv_hydro(udyn, vdyn, ax_ud, ax_vd);
   vadvuv(udyn, vdyn, ax_uc, ax_vc);
   hadvt(tdyn, ax_t);
   vadv3d_ind1_hydro(tdyn, a1_t);
+  auto sl = [&](int n) {   // isladvec = 1 (:1361-1363,1378-1380; oracle/sladvection.cpp)
+    slhadv_x([&](int j, int i, int k) -> double& { return qxdyn(j, i, k, n); }, [&](int j, int i, int k) { return a2_qx(j, i, k, n); });
+    hdvg_x([&](int j, int i, int k) -> double& { return qxdyn(j, i, k, n); }, [&](int j, int i, int k) { return a1_qx(j, i, k, n); });
+  };
+  if (cfg.isladvec == 1) sl(iqv); else
   hadvqv(qxdyn, ax_qx, iqv);
   vadvqv(qxdyn, a1_qx, iqv);
   if (cfg.ipptls > 0) {
+    if (cfg.isladvec == 1) { for (int n = iqfrst; n <= iqlst; ++n) sl(n); } else
     hadvqx(qxdyn, ax_qx, iqfrst, iqlst);
     vadv4d(qxdyn, a1_qx, iqfrst, iqlst, iqxvadv);
   }

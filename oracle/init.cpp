@@ -394,6 +394,7 @@ int Oracle::step(int n) {
     }
     tend();
     if (cfl_error) { err = "CFL violation"; return RCM_ERR_CFL; }
+    if (sl_rc) return sl_rc;
     if (alarm_bdy_act()) {
       if (!have_next) { err = "boundary record needed but not staged"; return RCM_ERR_BDY; }
       if (hydro) bdyin_hydro(); else bdyin();

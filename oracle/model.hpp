@@ -168,6 +168,13 @@ struct Oracle {
   void vadv_ind3(const std::function<double(int, int, int)>& f);
   int set_kpbl(const int32_t* k, const int32_t lb[2], const int32_t ub[2]);
   int tke_state(int level, double* a, const int32_t lb[3], const int32_t ub[3], bool in);
+  // ---- semi-Lagrangian advection of moisture and tracers (isladvec = 1; oracle/sladvection.cpp) ----
+  A3 sl_alf, sl_am2, sl_am1, sl_a0, sl_ap1, sl_bm2, sl_bm1, sl_b0, sl_bp1;
+  std::vector<int> sl_xn, sl_xm1, sl_xm2, sl_xp1, sl_yn, sl_ym1, sl_ym2, sl_yp1;
+  int trajcalc_x();
+  int sl_rc = 0;   // RCM_ERR_CFL when a departure point lies more than one cell away (the reference calls fatal)
+  void slhadv_x(const std::function<double&(int, int, int)>& ften, const std::function<double(int, int, int)>& var);
+  void hdvg_x(const std::function<double&(int, int, int)>& ften, const std::function<double(int, int, int)>& var);
   // ---- tracers (oracle/tracers.cpp) ----
   int ntr = 0;
   std::vector<A3> chia, chib, chic, chix, chib3d, chidyn, chiten, nx_chi;   // atm1%chi, atm2%chi, atmc%chi, atmx%chi, ...

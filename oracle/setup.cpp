@@ -27,6 +27,7 @@ int Oracle::create(const rcm_cfg& c) {
   moloch = (c.idynamic == 3);
   if (hydro && (c.nsplit < 1 || c.nsplit > c.kz)) { err = "oracle: nsplit out of range"; return RCM_ERR_ARG; }
   nsplit = hydro ? c.nsplit : 0;
+  if (c.isladvec != 0 && (c.isladvec != 1 || c.idynamic == 3)) { err = "oracle: isladvec must be 0 or 1 (idynamic 1, 2)"; return RCM_ERR_ARG; }
   if (c.ipgf != 0 && c.ipgf != 1) { err = "oracle: ipgf must be 0 or 1"; return RCM_ERR_ARG; }
   if (c.idiffu != 1 && c.idiffu != 2) { err = "oracle: idiffu must be 1 or 2 (3, the flux-limited 6th-order operator, is not restated)"; return RCM_ERR_ARG; }
   // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)

@@ -249,6 +249,7 @@ void Oracle::init_tendencies() {
 
 void Oracle::advection() {
   start_advect();
+  if (cfg.isladvec == 1 && (sl_rc = trajcalc_x())) return;   // :1283-1285
   hadvuv(udyn, vdyn, ax_ud, ax_vd);
   vadvuv(udyn, vdyn, ax_uc, ax_vc);
   hadv3d(ppdyn, ax_pp, 0);
@@ -265,9 +266,15 @@ void Oracle::advection() {
       }
   hadvt(thten, th);
   vadv3d(thten, tha, kz, 0);
+  auto sl = [&](int n) {   // isladvec = 1 (:1361-1363,1378-1380): slhadv_x on atm2%qx, hdvg_x on atm1%qx
+    slhadv_x([&](int j, int i, int k) -> double& { return qxdyn(j, i, k, n); }, [&](int j, int i, int k) { return a2_qx(j, i, k, n); });
+    hdvg_x([&](int j, int i, int k) -> double& { return qxdyn(j, i, k, n); }, [&](int j, int i, int k) { return a1_qx(j, i, k, n); });
+  };
+  if (cfg.isladvec == 1) sl(iqv); else
   hadvqv(qxdyn, ax_qx, iqv);
   vadvqv(qxdyn, a1_qx, iqv);   // all(icup /= 1): physics off
   if (cfg.ipptls > 0) {
+    if (cfg.isladvec == 1) { for (int n = iqfrst; n <= iqlst; ++n) sl(n); } else
     hadvqx(qxdyn, ax_qx, iqfrst, iqlst);
     vadv4d(qxdyn, a1_qx, iqfrst, iqlst, iqxvadv);
   }

@@ -118,6 +118,11 @@ void Oracle::tracer_tendency() {
           ax(j, i, k) = a1(j, i, k) * rpsa(j, i);
           b3(j, i, k) = std::max(a2(j, i, k) * rpsb(j, i), d_zero);
         }
+    if (cfg.isladvec == 1) {   // Main/mod_tendency.F90:1397-1399
+      fg.fill(d_zero);
+      slhadv_x([&](int j, int i, int k) -> double& { return fg(j, i, k); }, [&](int j, int i, int k) { return a2(j, i, k); });
+      hdvg_x([&](int j, int i, int k) -> double& { return fg(j, i, k); }, [&](int j, int i, int k) { return a1(j, i, k); });
+    } else
     // hadvtr (:666-720)
     for (int k = 1; k <= kz; ++k)
       for (int i = ici1; i <= ici2; ++i)

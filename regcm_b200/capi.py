@@ -60,6 +60,7 @@ class RcmCfg(C.Structure):
         ("ntr", C.c_int32),
         ("ibltyp", C.c_int32), ("iuwvadv", C.c_int32),
         ("ipgf", C.c_int32),
+        ("isladvec", C.c_int32), ("iqmsl", C.c_int32),
         ("ds", C.c_double), ("ptop", C.c_double),
         ("dt", C.c_double),
         ("gnu1", C.c_double), ("gnu2", C.c_double), ("ckh", C.c_double), ("adyndif", C.c_double),
@@ -102,6 +103,7 @@ def default_cfg(idynamic: int = 2, **kw) -> RcmCfg:
     c.nsplit, c.lstand = 2, 1   # Main/mod_params.F90:283-284
     c.mo_nadv, c.mo_nsound, c.mo_nzfilt = 3, 6, 3      # Main/mod_params.F90:296-300
     c.mo_anu2, c.mo_a0, c.mo_b0 = 0.6, 0.0, 0.5        # Share/mod_dynparam.F90:189-190
+    c.iqmsl = 1                                        # Main/mod_params.F90:244
     c.uw_nuk, c.uw_tkemin = 5.0, 1.0e-3                # Main/mod_params.F90:480; Main/pbllib/mod_pbl_uwtcm.F90:86
     if idynamic == 2:
         c.gnu1 = c.gnu2 = 0.1

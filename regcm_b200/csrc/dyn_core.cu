@@ -50,6 +50,7 @@ void launch_window_strided(bool pack, double* buf, double* p_shifted, int j0, in
 void launch_window(bool pack, double* buf, double* p_shifted, int j0, int i0, int k0, int n1, int n2, int nk, int si, long long sk, cudaStream_t st);
 void launch_tr(const Geom&, const Fields&, const TrFields&, const StepScalars&, cudaStream_t);
 void launch_tke(const Geom&, const Fields&, const UwFields&, const StepScalars&, cudaStream_t);
+void launch_sl(const Geom&, const Fields&, const TrFields&, const StepScalars&, cudaStream_t);
 void launch_tke_bdy(const Geom&, const Fields&, const UwFields&, const int2*, int, int, int, cudaStream_t);
 void launch_tr_repair(const Geom&, const TrFields&, const StepScalars&, cudaStream_t);
 void launch_tr_bdyval(const Geom&, const TrFields&, const int2*, int, double, int, int, cudaStream_t);
@@ -258,6 +259,7 @@ extern "C" int rcm_dyn_default_cfg(rcm_cfg* c, int idynamic) {
   c->nsplit = 2; c->lstand = 1;  // Main/mod_params.F90:283-284
   c->mo_nadv = 3; c->mo_nsound = 6; c->mo_nzfilt = 3; c->mo_anu2 = 0.6;  // :296-300
   c->mo_a0 = 0.0; c->mo_b0 = 0.5;                                        // Share/mod_dynparam.F90:189-190
+  c->iqmsl = 1;                             // Main/mod_params.F90:244
   c->uw_nuk = 5.0; c->uw_tkemin = 1.0e-3;   // Main/mod_params.F90:480; Main/pbllib/mod_pbl_uwtcm.F90:86
   if (idynamic == 2) { c->gnu1 = c->gnu2 = 0.1; c->diffu_hgtf = 0; }
   else { c->gnu1 = c->gnu2 = 0.0625; c->diffu_hgtf = 1; }
@@ -329,6 +331,8 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
     return bail(RCM_ERR_ARG, "idynamic=3 needs mo_nadv >= 1, mo_nsound >= 1, kz >= 4, ipptls 0 or 1");
   if (h->hydro && (c.nsplit < 1 || c.nsplit > RCM_MAXSPLIT || c.nsplit > c.kz)) return bail(RCM_ERR_ARG, "nsplit must be 1..4");
   if (c.ipgf != 0 && c.ipgf != 1) return bail(RCM_ERR_ARG, "ipgf must be 0 or 1");
+  if (c.isladvec != 0 && (c.isladvec != 1 || c.idynamic == 3 || c.nproc != 1))
+    return bail(RCM_ERR_ARG, "isladvec must be 0 or 1; 1 runs with idynamic 1, 2 on one rank (the departure stencil reaches three cells out)");
   if (c.idiffu != 1 && c.idiffu != 2) return bail(RCM_ERR_ARG, "idiffu must be 1 or 2 (3, the flux-limited 6th-order operator, is not implemented)");
   // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)
   if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 4 || c.iboudy == 5 || (c.idynamic != 3 && (c.iboudy == 2 || c.iboudy == 3))))
@@ -500,6 +504,10 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
     tr.nq_cnt = dev_alloc_raw<int>(h, (size_t)c.ntr * g.kz);
     tr.negcnt = dev_alloc_raw<unsigned long long>(h, 1);
     ok = ok && tr.cefc && tr.cegc && z && tr.nq_list && tr.nq_cnt && tr.negcnt;
+  }
+  if (c.isladvec == 1) {   // scratch of k_sl
+    A3(f.slqv); A3(f.slqc);
+    for (int n = 0; n < c.ntr; ++n) A3(h->tr.sl[n]);
   }
   if (!ok) {
     for (void* p : h->allocs) cudaFree(p);
@@ -1226,7 +1234,7 @@ extern "C" int rcm_dyn_init(rcm_dyn* h) {
   s.gnu1 = c.gnu1; s.gnu2 = c.gnu2; s.t_extrema = c.t_extrema; s.q_rel_extrema = c.q_rel_extrema;
   s.ptop = ptop;
   s.upstream_mode = c.upstream_mode; s.stability_enhance = c.stability_enhance; s.ipptls = c.ipptls;
-  s.iboudy = c.iboudy; s.ifrayd = c.ifrayd; s.ifupr = c.ifupr; s.idiffu = c.idiffu; s.ipgf = c.ipgf;
+  s.iboudy = c.iboudy; s.ifrayd = c.ifrayd; s.ifupr = c.ifupr; s.idiffu = c.idiffu; s.ipgf = c.ipgf; s.isladvec = c.isladvec; s.iqmsl = c.iqmsl;
   s.kt_ray = std::min(kz, c.rayndamp); s.ktf_ray = std::min(kzp1, c.rayndamp);
   s.nspgx = c.nspgx; s.nspgd = c.nspgd;
   s.hydro = h->hydro ? 1 : 0; s.nsplit = h->hydro ? c.nsplit : 0; s.integrating = 0;
@@ -1614,6 +1622,7 @@ static int tend_hydro(rcm_dyn* h) {
   }
   if (h->head_only) { h->mid_step = true; return RCM_OK; }
   h->mid_step = false;
+  if (h->cfg.isladvec == 1) TIMED(KID_TR, 1, launch_sl(g, f, h->tr, s, h->st));   // semi-Lagrangian tendencies of qv, qc, tracers
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_H_UV, 1, launch_h_uv(g, f, s, h->st));
     TIMED(KID_H_TQ, 1, launch_h_tq(g, f, s, h->st));
@@ -1703,6 +1712,7 @@ static int tend(rcm_dyn* h) {
   }
   if (h->head_only) { h->mid_step = true; return RCM_OK; }
   h->mid_step = false;
+  if (h->cfg.isladvec == 1) TIMED(KID_TR, 1, launch_sl(g, f, h->tr, s, h->st));   // semi-Lagrangian tendencies of qv, qc, tracers
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_UV, 1, h->uv_maps ? launch_uv_tma(g, f, s, h->st, h->uv_maps) : launch_uv(g, f, s, h->st));
     TIMED(KID_TQ, 1, h->tq_tma ? launch_tq_tma(g, f, s, h->st) : launch_tq(g, f, s, h->st));
@@ -1906,6 +1916,7 @@ static int finish_steps(rcm_dyn* h) {
   h->cq_mode = nq > 0 ? 2 : 0;   // moisture went negative: the next batch stores the forecast in its first pass
   CUDA_OK(cudaGetLastError());
   if (halo_err) return fail(h, RCM_ERR_NCCL, "halo exchange: timed out waiting for a neighbour's edge data");
+  if (nanf == 2) return fail(h, RCM_ERR_CFL, "SL advection: a departure point lies more than one cell away (decrease dt)");   // Main/mod_sladvection.F90:152-157
   if (nanf || cfl != cfl) return fail(h, RCM_ERR_NAN, "NaN in the acoustic solver");
   if (cfl > 1.0) {
     char buf[128]; std::snprintf(buf, sizeof(buf), "CFL violation: max sigma-dot CFL = %g", cfl);

@@ -49,6 +49,7 @@ struct StepScalars {
   double xgamma, bp, bm, bpxbp, bpxbm, xkd_snd;
   double ptop;
   int upstream_mode, stability_enhance, ipptls, iboudy, ifrayd, ifupr;
+  int isladvec, iqmsl;   // semi-Lagrangian horizontal advection of qv, qc, tracers and its quasi-monotonic limiter
   int idiffu;   // 1: 4th order with the 2nd-order boundary ring; 2: nine-point operator (Main/mod_diffusion.F90)
   int kt_ray;   // min(kz, rayndamp)
   int ktf_ray;  // min(kzp1, rayndamp)
@@ -89,6 +90,7 @@ struct TrFields {
   int* nq_list;                             // negative forecasts per (species, level) plane, as in Fields::nq_list
   int* nq_cnt;
   unsigned long long* negcnt;               // number of negative forecasts of the step
+  double* sl[RCM_MAXTR];                    // isladvec = 1: semi-Lagrangian advection tendency left by k_sl
 };
 
 // UW-PBL coupling of the transport (ibltyp = 2): TKE on full levels, NOT coupled with p*
@@ -151,6 +153,8 @@ struct Fields {
   int *nanflag;
   // vadv4d ind = 3 (iuwvadv = 1 with ibltyp = 2): top of the PBL per cross point, 2-D geometry; null = ind 1 / 2
   const int* kpb;
+  // isladvec = 1: semi-Lagrangian horizontal advection tendencies of qv, qc left by k_sl (null otherwise)
+  double *slqv, *slqc;
 };
 
 // ---------------------------------------------------------------------------

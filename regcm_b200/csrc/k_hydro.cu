@@ -518,8 +518,13 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
       const double q_c = qv_c, q_jm = fmax(L3(f.aqv, j - 1, i, k) * rpsa_jm, minqq),
                    q_jp = fmax(L3(f.aqv, j + 1, i, k) * rpsa_jp, minqq), q_im = fmax(L3(f.aqv, j, i - 1, k) * rpsa_im, minqq),
                    q_ip = fmax(L3(f.aqv, j, i + 1, k) * rpsa_ip, minqq);
-      double fg = hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, q_c, q_jm, q_jp, q_im, q_ip);
-      if (se) { const double qs = fmax(q_c, dlowval); fg = extrema_limit(fg, q_c, q_jm, q_jp, q_im, q_ip, qs, recip_for_div(qs), s.q_rel_extrema); }
+      double fg;
+      if (s.isladvec == 1) {   // slhadv_x(qxdyn, atm2%qx, iqv); hdvg_x(qxdyn, atm1%qx, iqv) (Main/mod_tendency.F90:1361-1363)
+        fg = L3(f.slqv, j, i, k);   // left by k_sl
+      } else {
+        fg = hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, q_c, q_jm, q_jp, q_im, q_ip);
+        if (se) { const double qs = fmax(q_c, dlowval); fg = extrema_limit(fg, q_c, q_jm, q_jp, q_im, q_ip, qs, recip_for_div(qs), s.q_rel_extrema); }
+      }
       double ten = fg;
       if (k >= 2) ten = ten + fl_qv_k * xdsk;
       double fl_n = 0.0;
@@ -574,7 +579,8 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
       if (s.ipptls > 0) {
         const double q_jm = fmax(L3(f.aqc, j - 1, i, k) * rpsa_jm, 0.0), q_jp = fmax(L3(f.aqc, j + 1, i, k) * rpsa_jp, 0.0),
                      q_im = fmax(L3(f.aqc, j, i - 1, k) * rpsa_im, 0.0), q_ip = fmax(L3(f.aqc, j, i + 1, k) * rpsa_ip, 0.0);
-        ten = hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, q_c, q_jm, q_jp, q_im, q_ip);
+        if (s.isladvec == 1) ten = L3(f.slqc, j, i, k);   // :1378-1380, left by k_sl
+        else ten = hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, q_c, q_jm, q_jp, q_im, q_ip);
         if (k >= 2) ten = ten + fl_qc_k * xdsk;
         if (k < kz) {
           const double aqc_n = L3(f.aqc, j, i, k + 1);

@@ -68,7 +68,9 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
     // hadvtr on atmx%chi
     const double q_c = ac_c * rpsa_c, q_jm = L3(a1, j - 1, i, k) * rpsa_jm, q_jp = L3(a1, j + 1, i, k) * rpsa_jp,
                  q_im = L3(a1, j, i - 1, k) * rpsa_im, q_ip = L3(a1, j, i + 1, k) * rpsa_ip;
-    double ten = 0.0 + hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, q_c, q_jm, q_jp, q_im, q_ip);
+    double ten;
+    if (s.isladvec == 1) ten = 0.0 + L3(tr.sl[n], j, i, k);   // left by k_sl: slhadv_x(chidyn, atm2%chi); hdvg_x(chidyn, atm1%chi) (Main/mod_tendency.F90:1397-1399)
+    else ten = 0.0 + hflux(up, f1, f2, xmsf, uavg1, uavg2, vavg1, vavg2, q_c, q_jm, q_jp, q_im, q_ip);
     // vadv4d, ind = 2
     if (k >= 2) ten = ten + fl_k * xdsk;
     double fl_n = 0.0;

@@ -451,8 +451,69 @@ def _wafone_horizontal(pp, wz, fmz, u, v, rmu, rmv, mx2, zdtrdx, zdtrdy, jx, iy,
 
 
 # ---------------------------------------------------------------------------------------------------------
+def sl_tendency(varb, vara, umd, vmd, msfx, msfd, dt, dx, box, kz, iqmsl=1):
+    """Semi-Lagrangian horizontal advection as `tend` applies it to a p*-coupled scalar (isladvec = 1), written from
+    Main/mod_sladvection.F90: adv_velocity(.false.) (:92-114, with the repeated va(j+1,i,k) in vadym1_x), trajcalc_x
+    (:139-221: third-order departure distance, integer cell and fractional part, the four stencil indices per direction,
+    cubic weights), slhadv_x (:347-393: bilinear on the two outer rows, cubic on the two inner ones, cubic across,
+    quasi-monotonic clip, tendency (value - var)/dt when it exceeds dlowval) on time level b, minus hdvg_x (:568-588:
+    var * horizontal divergence of the map-scaled wind, for var > epsilon) on time level a.  umd, vmd = atmx%umd/vmd;
+    msfx, msfd as stored.  Away from the lateral boundary (no index clamping).  Returns the tendency on the box."""
+    j1, j2, i1, i2 = box
+
+    def c(a, dj=0, di=0):
+        return a.s((j1 + dj, j2 + dj), (i1 + di, i2 + di), (1, kz)) if len(a.lb) == 3 else a.s((j1 + dj, j2 + dj), (i1 + di, i2 + di))[:, :, None]
+
+    uadvx = 0.25 * (c(umd) + c(umd, 0, 1) + c(umd, 1, 1) + c(umd, 1, 0)) / c(msfx)
+    uadxp1 = 0.25 * (c(umd, 1, 0) + c(umd, 1, 1) + c(umd, 2, 1) + c(umd, 2, 0)) / c(msfx, 1, 0)
+    uadxm1 = 0.25 * (c(umd) + c(umd, 0, 1) + c(umd, -1, 1) + c(umd, -1, 0)) / c(msfx, -1, 0)
+    vadvy = 0.25 * (c(vmd) + c(vmd, 0, 1) + c(vmd, 1, 1) + c(vmd, 1, 0)) / c(msfx)
+    vadyp1 = 0.25 * (c(vmd, 0, 1) + c(vmd, 1, 1) + c(vmd, 1, 2) + c(vmd, 0, 2)) / c(msfx, 0, 1)
+    vadym1 = 0.25 * (c(vmd) + c(vmd, 0, -1) + c(vmd, 1, 0) + c(vmd, 1, 0)) / c(msfx, 0, -1)
+    dtsq, dtcb = dt * dt, dt * dt * dt
+
+    def depart(w, wp, wm):
+        d1 = 0.5 * (wp - wm) / dx
+        d2 = (wp - 2.0 * w + wm) / (dx * dx)
+        dis = -w * dt + 0.5 * (dtsq * w * d1) - (dtcb * w) * (d1 * d1 + w * d2) / 6.0
+        n = dis / dx
+        npart = np.trunc(n).astype(int)
+        assert np.abs(npart).max() <= 1
+        frac = np.abs((npart * dx - dis) / dx)
+        sgn = np.where(np.signbit(n), -1, 1)
+        return npart, sgn, frac
+
+    xnp, xsn, al = depart(uadvx, uadxp1, uadxm1)
+    ynp, ysn, be = depart(vadvy, vadyp1, vadym1)
+    J = np.arange(j1, j2 + 1)[:, None, None]
+    I = np.arange(i1, i2 + 1)[None, :, None]
+    K = np.arange(kz)[None, None, :]
+    x0 = J + xnp; xm1 = x0 + xsn; xm2 = xm1 + xsn; xp1 = x0 - xsn
+    y0 = I + ynp; ym1 = y0 + ysn; ym2 = ym1 + ysn; yp1 = y0 - ysn
+    V = lambda x, y: varb.a[x - varb.lb[0], y - varb.lb[1], K]          # noqa: E731
+    am2, am1, a0, ap1 = -(al * (1 - al * al)) / 6.0, (al * (1 + al) * (2 - al)) / 2.0, ((1 - al * al) * (2 - al)) / 2.0, -(al * (1 - al) * (2 - al)) / 6.0
+    bm2, bm1, b0, bp1 = -(be * (1 - be * be)) / 6.0, (be * (1 + be) * (2 - be)) / 2.0, ((1 - be * be) * (2 - be)) / 2.0, -(be * (1 - be) * (2 - be)) / 6.0
+    bl1 = al * V(xm1, yp1) + (1.0 - al) * V(x0, yp1)
+    bl2 = al * V(xm1, ym2) + (1.0 - al) * V(x0, ym2)
+    cb1 = am2 * V(xm2, y0) + am1 * V(xm1, y0) + a0 * V(x0, y0) + ap1 * V(xp1, y0)
+    cb2 = am2 * V(xm2, ym1) + am1 * V(xm1, ym1) + a0 * V(x0, ym1) + ap1 * V(xp1, ym1)
+    val = bm2 * bl2 + bm1 * cb2 + b0 * cb1 + bp1 * bl1
+    if iqmsl == 1:
+        four = np.stack([V(x0, y0), V(x0, ym1), V(xm1, y0), V(xm1, ym1)])
+        val = np.clip(val, four.min(axis=0), four.max(axis=0))
+    vb = c(varb)
+    ten = np.where(np.abs(val - vb) > 1.0e-20, (val - vb) / dt, 0.0)
+    ucapf = (c(umd, 1, 1) * c(msfd, 1, 1) + c(umd, 1, 0) * c(msfd, 1, 0)) * 0.5
+    ucapi = (c(umd, 0, 1) * c(msfd, 0, 1) + c(umd) * c(msfd)) * 0.5
+    vcapf = (c(vmd, 1, 1) * c(msfd, 1, 1) + c(vmd, 0, 1) * c(msfd, 0, 1)) * 0.5
+    vcapi = (c(vmd, 1, 0) * c(msfd, 1, 0) + c(vmd) * c(msfd)) * 0.5
+    hdvg = ((ucapf - ucapi) / dx + (vcapf - vcapi) / dx) / (c(msfx) * c(msfx))
+    va = c(vara)
+    return ten - np.where(va > np.finfo(float).eps, va * hdvg, 0.0)
+
+
 def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc, ul, dt, gnu2, box, kz, upstream=True, idiffu=1,
-                kpb=None, sigma=None):
+                kpb=None, sigma=None, sl=None):
     """One leapfrog step of ONE tracer away from the lateral zones, written from the Fortran text:
     decouple (Main/mod_tendency.F90:1029-1034), start_advect (Main/mod_advection.F90:109-122: uavg/vavg from the
     p*.u.m fluxes), hadvtr (:666-720), vadv4d ind = 2 (:895-914,946-950), diffu_x4d interior stencil
@@ -460,7 +521,8 @@ def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc,
     nine-point operator of :881-894 with the weights 4/6, 1/6, -20/6 of :63-65), the sums and the
     forecast (Main/mod_tendency.F90:548-569) and the RAW filter (Main/mod_timefilter.F90:231-278, alpha = gnu2,
     beta = 0.53, floor 0).  With `kpb` (F array of the PBL top on cross points) and `sigma` (full levels, 1-based F) the
-    vertical flux is vadv4d ind = 3 (:915-957) instead of ind = 2.  `box` = (j1, j2, i1, i2): interior points at least three rows away from the zones.
+    vertical flux is vadv4d ind = 3 (:915-957) instead of ind = 2.  With `sl` (dict: umd, vmd, msfx, msfd, dx, iqmsl) the
+    horizontal advection is the semi-Lagrangian one (sl_tendency) instead of hadvtr.  `box` = (j1, j2, i1, i2): interior points at least three rows away from the zones.
     Returns (forecast atmc%chi, filtered atm1%chi, filtered atm2%chi) on the box."""
     j1, j2, i1, i2 = box
     K = (1, kz)
@@ -484,6 +546,8 @@ def tracer_step(chia, chib, umc, vmc, psa, rpsa, rpsb, xmsf, svv, twt, xds, xkc,
     else:
         fx1, fx2, fy1, fy2 = x(-1, 0) + x(), x() + x(1, 0), x(0, -1) + x(), x() + x(0, 1)
     ten = -c(xmsf) * (uavg2 * fx2 - uavg1 * fx1 + vavg2 * fy2 - vavg1 * fy1)
+    if sl is not None:
+        ten = sl_tendency(chib, chia, sl["umd"], sl["vmd"], sl["msfx"], sl["msfd"], dt, sl["dx"], box, kz, sl.get("iqmsl", 1))
     # vadv4d, ind = 2: flux through interface k = 2..kz, zero unless the upwind coupled value exceeds mintr*ps
     fk = c(chia, k=(2, kz))
     fkm1 = c(chia, k=(1, kz - 1))

@@ -93,10 +93,12 @@ def test_wafone_numpy_vs_oracle():
     assert np.abs(pp.a - want).max() <= 1e-9 * change   # and agrees on the increment, not just on the 300 K background
 
 
-@pytest.mark.parametrize("kw", [{}, {"upstream_mode": 0}, {"idiffu": 2}, {"ibltyp": 2, "iuwvadv": 1}], ids=["default", "centred", "idiffu2", "ind3"])
+@pytest.mark.parametrize("kw", [{}, {"upstream_mode": 0}, {"idiffu": 2}, {"ibltyp": 2, "iuwvadv": 1}, {"isladvec": 1}, {"isladvec": 1, "iqmsl": 0},
+                                {"isladvec": 1, "idynamic": 1}], ids=["default", "centred", "idiffu2", "ind3", "sl", "sl-noclip", "sl-hydro"])
 def test_tracer_step_numpy_vs_oracle(kw):
     """hadvtr + vadv4d(ind = 2) + diffu_x4d + forecast + RAW filter of one tracer, away from the lateral
-    zones, on the flow of the oracle's 4th step."""
+    zones, on the flow of the oracle's 4th step.  Variants: centred advection, idiffu = 2, vadv4d ind = 3 (iuwvadv = 1),
+    semi-Lagrangian horizontal advection (isladvec = 1, f4) with and without its limiter and in the hydrostatic core."""
     case = synth.make_case("small", ntr=1, **kw)
     o = pyoracle.make_oracle(case.cfg)
     synth.load_case(o, case)
@@ -107,23 +109,27 @@ def test_tracer_step_numpy_vs_oracle(kw):
         o.set_kpbl(k2, lb=(2, 2))
         kpb, sigma = nr.F(k2, (2, 2)), nr.tap(o, "sigma")
     o.step(3)
-    chia = nr.F(nr.tap(o, "chia0").a.copy(), nr.tap(o, "chia0").lb)
-    chib = nr.F(nr.tap(o, "chib0").a.copy(), nr.tap(o, "chib0").lb)
+    keep = lambda n: nr.F(nr.tap(o, n).a.copy(), nr.tap(o, n).lb)      # noqa: E731
+    chia, chib = keep("chia0"), keep("chib0")
+    psa0, psb0 = keep("psa"), keep("psb")     # idynamic = 1 filters p* at the end of the step; the tendencies saw these
     dt = nr.scalar(o, "dt")
     o.step(1)
     # arrays `tend` leaves behind: decoupled fluxes, sigma-dot and the scaled Smagorinsky coefficient of THIS step
-    t = {n: nr.tap(o, n) for n in ("ax_umc", "ax_vmc", "psa", "rpsa", "rpsb", "xmsf", "qdot", "twt", "xds", "xkc", "chic0", "chia0", "chib0")}
+    t = {n: nr.tap(o, n) for n in ("ax_umc", "ax_vmc", "ax_umd", "ax_vmd", "msfx", "msfd", "xmsf", "qdot", "twt", "xds", "xkc", "chic0", "chia0", "chib0")}
+    t["psa"], t["rpsa"], t["rpsb"] = psa0, nr.F(1.0 / psa0.a, psa0.lb), nr.F(1.0 / psb0.a, psb0.lb)
     box = (nsp + 2, jx - 1 - nsp - 2, nsp + 2, iy - 1 - nsp - 2)
-    fc, na, nb = nr.tracer_step(chia, chib, t["ax_umc"], t["ax_vmc"], t["psa"], t["rpsa"], t["rpsb"], t["xmsf"], t["qdot"], t["twt"],
-                                t["xds"], t["xkc"], nr.scalar(o, "ul"), dt, case.cfg.gnu2, box, kz, upstream=case.cfg.upstream_mode != 0,
-                                idiffu=case.cfg.idiffu, kpb=kpb, sigma=sigma)
-    if kpb is not None:     # and the reshaping is active: the ind = 2 flux gives a different forecast
-        fc2, _, _ = nr.tracer_step(chia, chib, t["ax_umc"], t["ax_vmc"], t["psa"], t["rpsa"], t["rpsb"], t["xmsf"], t["qdot"], t["twt"],
-                                   t["xds"], t["xkc"], nr.scalar(o, "ul"), dt, case.cfg.gnu2, box, kz)
+    sl = None
+    if kw.get("isladvec"):
+        sl = dict(umd=t["ax_umd"], vmd=t["ax_vmd"], msfx=t["msfx"], msfd=t["msfd"], dx=nr.scalar(o, "dx"), iqmsl=case.cfg.iqmsl)
+    args = (chia, chib, t["ax_umc"], t["ax_vmc"], t["psa"], t["rpsa"], t["rpsb"], t["xmsf"], t["qdot"], t["twt"], t["xds"], t["xkc"],
+            nr.scalar(o, "ul"), dt, case.cfg.gnu2, box, kz)
+    fc, na, nb = nr.tracer_step(*args, upstream=case.cfg.upstream_mode != 0, idiffu=case.cfg.idiffu, kpb=kpb, sigma=sigma, sl=sl)
+    if kpb is not None or sl is not None:     # and the option is live: the default scheme gives a different forecast
+        fc2, _, _ = nr.tracer_step(*args)
         assert np.abs(fc2 - fc).max() > 1e-6 * np.abs(fc).max()
-    sl = ((box[0], box[1]), (box[2], box[3]), (1, kz))
-    want_c, want_a, want_b = t["chic0"].s(*sl), t["chia0"].s(*sl), t["chib0"].s(*sl)
-    assert fc.min() > 0.0 and np.abs(want_c - chib.s(*sl)).max() > 1e-3 * np.abs(want_c).max()   # the step did move the tracer
+    box3 = ((box[0], box[1]), (box[2], box[3]), (1, kz))
+    want_c, want_a, want_b = t["chic0"].s(*box3), t["chia0"].s(*box3), t["chib0"].s(*box3)
+    assert fc.min() > 0.0 and np.abs(want_c - chib.s(*box3)).max() > 1e-3 * np.abs(want_c).max()   # the step did move the tracer
     sc = np.abs(want_c).max()
     assert np.abs(fc - want_c).max() <= 1e-12 * sc
     assert np.abs(na - want_a).max() <= 1e-12 * sc and np.abs(nb - want_b).max() <= 1e-12 * sc
