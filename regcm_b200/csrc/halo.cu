@@ -456,6 +456,15 @@ int Halo::exchange_p2p(const std::vector<HaloField>& fl, int width, int estore, 
 int Halo::exchange(const std::vector<HaloField>& fl, int width, cudaStream_t st) {
   if (nproc <= 1) return 0;
   if (!comm) return -5;
+  // the packed message of one exchange holds at most 16 fields (XList, BoxList, buffer capacity): longer lists — the
+  // state of the non-hydrostatic core with tracers and TKE — go in several messages; fields are independent of each other
+  if (fl.size() > 16) {
+    for (size_t q = 0; q < fl.size(); q += 16) {
+      const std::vector<HaloField> part(fl.begin() + q, fl.begin() + std::min(fl.size(), q + 16));
+      if (const int rc = exchange(part, width, st)) return rc;
+    }
+    return 0;
+  }
 #ifndef RCM_EMU
   if (p2p) return exchange_p2p(fl, width, 0, nullptr, st);
 #endif

@@ -113,3 +113,36 @@ def test_hydro_halo_matches_single_gpu(cuda_lib, tmp_path, world, layout, case_n
             a, b = glob[(f, "a")], orc.get_state(f, 0)
             b = b if b.ndim == 3 else b[:, :, None]
             assert float(np.abs(a - b).max()) <= 1e-11 * max(float(np.abs(b).max()), 1e-300), capi.FIELD_NAMES[f]
+
+
+@pytest.mark.parametrize("idynamic", [2, 1])
+def test_uw_idiffu2_halo_matches_single_gpu(cuda_lib, tmp_path, idynamic):
+    """Round-2 options on two GPUs: TKE and kpbl (ibltyp = 2, iuwvadv = 1), one tracer, the nine-point diffusion (idiffu = 2,
+    corner ghost points).  Same library, same arithmetic: the two-GPU result equals the one-GPU result."""
+    import os
+    if ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    from tests.test_tke import load_uw, uw_inputs
+    steps = 5
+    opts = dict(ibltyp=2, iuwvadv=1, ntr=1, idiffu=2)
+    args = ["--case", "small", "--idynamic", str(idynamic), "--steps", str(steps), "--cpus-j", "0", "--cpus-i", "0", "--uw"]
+    for k, v in opts.items():
+        args += ["--cfg", f"{k}={v}"]
+    run_ranks(2, tmp_path, args, lib="cuda")
+    case = synth.make_case("small", idynamic=idynamic, **opts)
+    core = capi.DynCore(cuda_lib, case.cfg)
+    synth.load_case(core, case)
+    load_uw(core, case, *uw_inputs(case))
+    core.step(steps)
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    for fld, nk in ((capi.F_TKE, kz + 1), (capi.F_CHI, kz), (capi.F_QC, kz), (capi.F_T, kz)):
+        for lv, tag in ((0, "a"), (1, "b")):
+            glob = np.full((jx - 1, iy - 1, nk), np.nan)
+            for r in range(2):
+                d = np.load(os.path.join(tmp_path, f"rank{r}.npz"))
+                lb, a = d[f"lb{fld}"], d[f"f{fld}{tag}"]
+                glob[lb[0] - 1:lb[0] - 1 + a.shape[0], lb[1] - 1:lb[1] - 1 + a.shape[1], :] = a
+            want = core.get_state(fld, lv)
+            assert not np.isnan(glob).any()
+            assert np.abs(glob - want).max() <= 1e-12 * np.abs(want).max(), (fld, tag)
+    core.close()

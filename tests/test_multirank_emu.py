@@ -282,6 +282,28 @@ def test_tracers_multirank_match_single_rank(emu_lib, tmp_path, idynamic):
     assert negs == ref.diag().neg_chi_points and negs > 0
 
 
+def test_many_fields_in_one_exchange(emu_lib, tmp_path):
+    """ntr = 8 with TKE: the state exchange of the non-hydrostatic core carries 14 + 16 + 2 = 32 fields, twice what one
+    packed message holds (16): the list is sent in several messages."""
+    steps, ntr = 3, capi.MAXTR
+    run_ranks(2, tmp_path, ["--case", "tiny", "--steps", str(steps), "--cpus-j", "2", "--cpus-i", "1", "--cfg", f"ntr={ntr}", "--cfg", "ibltyp=2"])
+    case = synth.make_case("tiny", ntr=ntr, ibltyp=2)
+    core = capi.DynCore(emu_lib, case.cfg)
+    synth.load_case(core, case)
+    core.step(steps)
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    for fld in (capi.F_T, capi.F_TKE, capi.F_CHI, capi.F_CHI + ntr - 1):
+        nk = kz + 1 if fld == capi.F_TKE else kz
+        glob = np.full((jx - 1, iy - 1, nk), np.nan)
+        for r in range(2):
+            d = np.load(os.path.join(tmp_path, f"rank{r}.npz"))
+            lb, a = d[f"lb{fld}"], d[f"f{fld}a"]
+            glob[lb[0] - 1:lb[0] - 1 + a.shape[0], lb[1] - 1:lb[1] - 1 + a.shape[1], :] = a
+        want = core.get_state(fld, 0)
+        assert not np.isnan(glob).any() and np.abs(glob - want).max() <= 1e-12 * np.abs(want).max(), fld
+    core.close()
+
+
 # ---------------------------------------------------------------------------- UW-PBL coupling (SURVEY §8 f3: TKE, vadv4d ind = 3)
 @pytest.mark.parametrize("idynamic", [2, 1])
 def test_tke_multirank_matches_single_rank(emu_lib, tmp_path, idynamic):
