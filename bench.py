@@ -238,6 +238,9 @@ def run_gpu(args):
     lib = capi.cuda_lib()
     base = synth.CASES[args.workload]
     cfgkw = dict(nproc=world, myid=rank, device=local)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        cfgkw[k] = float(v) if "." in v else int(v)
     # the rank's tile (+ghost rows): ask the library for the decomposition by creating the handle first
     probe_cfg = synth.make_case("tiny").cfg  # only for struct defaults
     del probe_cfg
@@ -419,7 +422,7 @@ def run_gpu(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_desc(args.workload), "istep": istep,
+            "config": {"workload": workload_desc(args.workload) + ("" if not args.opt else " + options " + ",".join(args.opt)), "istep": istep,
                        "decomposition": f"{world} rank(s), set_nproc layout", "l2": "inputs larger than L2 (no flush)"
                        if cells * 8 * 20 > 126e6 else "working set fits L2; not flushed (launch-bound case)",
                        "sim_days_per_day": value / cells * base["dt"]},
@@ -445,6 +448,9 @@ def main():
     ap.add_argument("--workload", default="C4", choices=sorted(synth.CASES))
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
+                    help="rcm_cfg override for supplementary lines (ntr=4, ibltyp=2, idiffu=2, isladvec=1 ...); use with --no-e2e; "
+                         "the headline line is the one without it")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

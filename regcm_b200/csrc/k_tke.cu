@@ -46,7 +46,15 @@ k_tke(const Geom g, const Fields f, const UwFields uw, const StepScalars s) {
   double fx_m = 0.0;                                           // vadv3d flux of loop index k-1
   double xkc_m = 0.0;
   double tke_k = L3(a1, j, i, 1);
+  auto prefetch = [&](int kk) {   // level kk of every streamed field into L2 (see PF3)
+    PF3(f.au, j, i, kk); PF3(f.av, j, i, kk); PF3(f.au, j, i + 1, kk); PF3(f.av, j, i + 1, kk); PF3(f.qdot, j, i, kk); PF3(f.xkc, j, i, kk);
+    PF3(a1, j, i, kk); PF3(a2, j, i, kk); PF3(uw.phy, j, i, kk);
+  };
+  const int pfd = g.pfd;
+  if (pfd > 0)
+    for (int kk = 1; kk <= min(pfd, kzp1); ++kk) prefetch(kk);
   for (int k = 1; k <= kzp1; ++k) {
+    if (pfd > 0 && k + pfd <= kzp1) prefetch(k + pfd);
     const bool half = (k <= kz);
     double uavg1 = 0, uavg2 = 0, vavg1 = 0, vavg2 = 0, xkc_raw = 0;
     if (half) {

@@ -53,7 +53,16 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
 #define RPSB(dj, di) L2(f.rpsb, j + (dj), i + (di))
 
   double fl_k = 0.0;   // vertical flux at the upper interface of level k
+  // request level kk of every streamed field into L2 (see PF3)
+  auto prefetch = [&](int kk) {
+    PF3(f.au, j, i, kk); PF3(f.av, j, i, kk); PF3(f.au, j, i + 1, kk); PF3(f.av, j, i + 1, kk); PF3(f.qdot, j, i, kk); PF3(f.xkc, j, i, kk);
+    PF3(a1, j, i, kk); PF3(a2, j, i, kk);
+  };
+  const int pfd = g.pfd;
+  if (pfd > 0)
+    for (int kk = 1; kk <= min(pfd, kz); ++kk) prefetch(kk);
   for (int k = 1; k <= kz; ++k) {
+    if (pfd > 0 && k + pfd <= kz) prefetch(k + pfd);
     const double ua00 = L3(f.au, j, i, k) * m00, ua01 = L3(f.au, j, i + 1, k) * m01, ua10 = L3(f.au, j + 1, i, k) * m10,
                  ua11 = L3(f.au, j + 1, i + 1, k) * m11;
     const double va00 = L3(f.av, j, i, k) * m00, va01 = L3(f.av, j, i + 1, k) * m01, va10 = L3(f.av, j + 1, i, k) * m10,

@@ -1,0 +1,19 @@
+# call AE: after sharing the departure geometry across species in k_sl and adding the L2 prefetch to k_tr / k_tke
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_sladvec.py tests/test_gpu_tke.py tests/test_gpu_tracers.py -m gpu -q > gpurun_out/r2ae_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/r2ae_pytest.log
+run() { tag=$1; w=$2; shift 2; opts=""; for o in "$@"; do opts="$opts --opt $o"; done
+  timeout 500 python bench.py --workload $w --steps 10 --warmup 3 --no-cpu --no-e2e $opts > gpurun_out/ae_$tag.json 2> gpurun_out/ae_$tag.err
+  python - <<PY
+import json
+try:
+    d=json.loads(open("gpurun_out/ae_$tag.json").read().strip().splitlines()[-1])
+    pk=d["roofline"]["per_kernel"]
+    print("%-12s ms/step %.3f" % ("$tag", d['ms_per_step']), {k:round(x["ms_per_step"],3) for k,x in pk.items() if k in ("k_tr","k_tq","k_uv","k_ppw","k_bdy","k_negq")})
+except Exception as e:
+    print("$tag failed", e); print(open("gpurun_out/ae_$tag.err").read()[-800:])
+PY
+}
+run ntr4 C4 ntr=4
+run tke C4 ibltyp=2
+run sl C4 isladvec=1
+run all C4 ntr=4 ibltyp=2 iuwvadv=1 idiffu=2 isladvec=1
