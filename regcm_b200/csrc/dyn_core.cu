@@ -128,6 +128,7 @@ struct rcm_dyn {
   UwFields uw = {};                       // TKE of the UW PBL (ibltyp = 2)
   bool uw_on = false;
   int* kpb = nullptr;                     // kpbl, origin-shifted 2-D (always allocated with ibltyp = 2; f.kpb only with iuwvadv = 1)
+  std::vector<int> kpb_host;              // its host mirror (rcm_dyn_set_kpbl updates a window and uploads)
   double* tr_b1[RCM_MAXTR] = {nullptr};   // chib1
   double* tr_nx[RCM_MAXTR] = {nullptr};   // staged next record (mixing ratio)
   int64_t neg_chi = 0;
@@ -1988,8 +1989,8 @@ extern "C" int rcm_dyn_set_kpbl(rcm_dyn* h, const int32_t* kpbl, const int32_t l
   cudaSetDevice(h->device);
   if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
   const Geom& g = h->g;
-  std::vector<int> host((size_t)g.sk);
-  CUDA_OK(cudaMemcpy(host.data(), h->kpb - h->off2, host.size() * sizeof(int), cudaMemcpyDeviceToHost));
+  std::vector<int>& host = h->kpb_host;   // host mirror: points outside the caller's window keep their values
+  if (host.size() != (size_t)g.sk) host.assign((size_t)g.sk, 0);
   const long long n1 = ub[0] - lb[0] + 1;
   for (int i = std::max(lb[1], g.ici1); i <= std::min(ub[1], g.ici2); ++i)
     for (int j = std::max(lb[0], g.jci1); j <= std::min(ub[0], g.jci2); ++j) {
