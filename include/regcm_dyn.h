@@ -324,7 +324,14 @@ int rcm_dyn_init(rcm_dyn* h);
  * rcm_dyn_get_state on return. */
 int rcm_dyn_step(rcm_dyn* h, int nsteps);
 
-/* Physics coupling boundary (idynamic = 1, 2).  replaces: the place where `tend` hands over to the physical
+/* Physics coupling boundary.  idynamic = 3 (MOLOCH): `moloch` calls mkslice and physical_parametrizations after the
+ * sound / advection loops and before `boundary` (Main/mod_moloch.F90:393-426); rcm_dyn_step_pre_physics runs up to
+ * there, rcm_dyn_get_slice returns the members of `atms` (aliases of mo_atm, Main/mod_slice.F90:82-100, and the products
+ * of mkslice for idynamic = 3, :107-146; ZQ / ZA / DZQ = mo_atm%zetaf / zeta / dz), rcm_dyn_set_phys_tend takes
+ * mo_atm%tten, qxten, uten, vten (RCM_F_T, QV, QC on the cross grid, U on (jx, iy-1), V on (jx-1, iy); NOT coupled with
+ * anything), rcm_dyn_step_post_physics applies t, u, v, qx += dtsec * tendency with the floors of :1548-1557 (only
+ * once tendencies have been set), then boundary, Rayleigh damping, bdyin / bdyval.
+ * idynamic = 1, 2:  replaces: the place where `tend` hands over to the physical
  * parametrizations and takes their tendencies back (Main/mod_tendency.F90:271 `call physical_parametrizations`,
  * :1682-1820; slices: Main/mod_slice.F90:167-308; sums: Main/mod_tendency.F90:285-314,331-335,404-411).
  *   rcm_dyn_step_pre_physics   everything of `tend` the parametrizations depend on (surface_pressures, decouple,

@@ -241,7 +241,15 @@ struct Oracle {
   A2 msfu, msfv, ulat, vlat, coriou, coriov, hx, hy, mx2, rmu, rmv, p2d;
   A3 m_u, m_v, m_w, m_ux, m_vx, m_wx, m_t, m_pai, m_tetav, m_tvirt, m_p, m_rho,
       m_zeta, m_fmz, m_fmzf, m_deltaw, m_s, m_zdiv2, m_wwkw, m_wz, m_p0, m_ud,
-      m_vd, m_zetau, m_zetav;
+      m_vd, m_zetau, m_zetav, m_zetaf, m_dz;
+  // physics coupling of the MOLOCH core: tendencies of physical_parametrizations, uncoupled
+  bool mo_mid = false, mo_phys_on = false;
+  A3 m_tten, m_uten, m_vten;
+  A4 m_qxten;
+  void moloch_head();
+  void moloch_tail();
+  int mo_set_phys(int field, const double* a, const int32_t lb[3], const int32_t ub[3]);
+  int mo_get_slice(int id, double* a, const int32_t lb[3], const int32_t ub[3]);
   A2 m_wfw, m_zpby, m_zpbw;
   A4 m_qx;
   V3dBound xpaib;

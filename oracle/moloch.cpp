@@ -142,6 +142,19 @@ void Oracle::compute_moloch_static() {
   for (int k = 2; k <= kzp1; ++k)
     for (int i = ice1; i <= ice2; ++i)
       for (int j = jce1; j <= jce2; ++j) m_fmzf(j, i, k) = md_fmz(zita(k), ht(j, i));
+  // zetaf, dz (Main/mod_params.F90:2810-2811,2829-2840): the heights the physics sees as atms%zq, atms%dzq
+  m_zetaf.alloc(jce1, jce2, ice1, ice2, 1, kzp1); m_dz.alloc(jce1, jce2, ice1, ice2, 1, kz);
+  for (int i = ice1; i <= ice2; ++i)
+    for (int j = jce1; j <= jce2; ++j) m_zetaf(j, i, 1) = 48446.4;
+  for (int k = 2; k <= kzp1; ++k) {
+    const double fak = -hzita * bzita(zita(k)) * std::log(std::max(sigma(k), 2.2250738585072014e-308));
+    const double fbk = gzita(zita(k));
+    for (int i = ice1; i <= ice2; ++i)
+      for (int j = jce1; j <= jce2; ++j) m_zetaf(j, i, k) = fak + (fbk - d_one) * ht(j, i) * regrav;
+  }
+  for (int k = 1; k <= kz; ++k)
+    for (int i = ice1; i <= ice2; ++i)
+      for (int j = jce1; j <= jce2; ++j) m_dz(j, i, k) = m_zetaf(j, i, k) - m_zetaf(j, i, k + 1);
   double ztop = -1e300;
   for (double x : m_zeta.d) ztop = std::max(ztop, x);
   rayzd = ztop;
@@ -821,6 +834,13 @@ void Oracle::mo_boundary() {
 
 // ---- Main/mod_moloch.F90:224-481 (physics off) ----
 void Oracle::moloch_step() {
+  if (!mo_mid) moloch_head();
+  mo_mid = false;
+  moloch_tail();
+}
+
+// everything of `moloch` up to `call mkslice` (Main/mod_moloch.F90:296-393)
+void Oracle::moloch_head() {
   A3 &t = m_t, &pai = m_pai, &tetav = m_tetav, &tvirt = m_tvirt, &p = m_p, &rho = m_rho;
   A4& qx = m_qx;
   const int ipptls = cfg.ipptls;
@@ -860,6 +880,32 @@ void Oracle::moloch_step() {
       double zdgz = ht(j, i) * (gzita(d_half * mo_dz) - d_one) + zz1;
       psa(j, i) = p(j, i, kz) * std::exp(zdgz / (rgas * tvirt(j, i, kz)));
     }
+}
+
+// physical_parametrizations' state update (:1548-1557, when tendencies were handed in), boundary, Rayleigh damping
+void Oracle::moloch_tail() {
+  if (mo_phys_on) {
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ici1; i <= ici2; ++i)
+        for (int j = jci1; j <= jci2; ++j) m_t(j, i, k) = m_t(j, i, k) + dtsec * m_tten(j, i, k);
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ici1; i <= ici2; ++i)
+        for (int j = jdi1; j <= jdi2; ++j) m_u(j, i, k) = m_u(j, i, k) + dtsec * m_uten(j, i, k);
+    for (int k = 1; k <= kz; ++k)
+      for (int i = idi1; i <= idi2; ++i)
+        for (int j = jci1; j <= jci2; ++j) m_v(j, i, k) = m_v(j, i, k) + dtsec * m_vten(j, i, k);
+    for (int n = 1; n <= nqx; ++n)
+      for (int k = 1; k <= kz; ++k)
+        for (int i = ici1; i <= ici2; ++i)
+          for (int j = jci1; j <= jci2; ++j) m_qx(j, i, k, n) = m_qx(j, i, k, n) + dtsec * m_qxten(j, i, k, n);
+    for (int n = iqfrst; n <= iqlst; ++n)
+      for (int k = 1; k <= kz; ++k)
+        for (int i = ici1; i <= ici2; ++i)
+          for (int j = jci1; j <= jci2; ++j) m_qx(j, i, k, n) = std::max(m_qx(j, i, k, n), d_zero);
+    for (int k = 1; k <= kz; ++k)
+      for (int i = ici1; i <= ici2; ++i)
+        for (int j = jci1; j <= jci2; ++j) m_qx(j, i, k, iqv) = std::max(m_qx(j, i, k, iqv), minqq);
+  }
   // lateral / damping boundary condition (:417-426)
   mo_boundary();
   if (cfg.ifrayd == 1) {

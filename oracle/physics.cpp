@@ -39,6 +39,10 @@ constexpr double rhmax = 1.01, rhmin = 0.01;   // Main/mod_params.F90:331-332
 // everything `tend` does before physical_parametrizations that the slices depend on; idempotent (a function of the
 // prognostic state only), so that step() afterwards repeats it harmlessly
 void Oracle::pre_physics() {
+  if (moloch) {   // everything up to `call mkslice`; the step itself then resumes behind it
+    if (!mo_mid) { moloch_head(); mo_mid = true; }
+    return;
+  }
   if (hydro) {
     surface_pressures_hydro();
     decouple();
@@ -61,7 +65,85 @@ void Oracle::ensure_phys() {
   phys_on = true;
 }
 
+// MOLOCH: mo_atm%tten, uten, vten, qxten (Main/mod_moloch.F90:1548-1557), not coupled with anything
+int Oracle::mo_set_phys(int field, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (!mo_phys_on) {
+    m_tten.alloc(jci1, jci2, ici1, ici2, 1, kz); m_uten.alloc(jdi1, jdi2, ici1, ici2, 1, kz); m_vten.alloc(jci1, jci2, idi1, idi2, 1, kz);
+    m_qxten.alloc(jci1, jci2, ici1, ici2, 1, kz, 1, nqx);
+    mo_phys_on = true;
+  }
+  A3* dst = nullptr;
+  int n4 = 0;
+  switch (field) {
+    case RCM_F_T: dst = &m_tten; break;
+    case RCM_F_U: dst = &m_uten; break;
+    case RCM_F_V: dst = &m_vten; break;
+    case RCM_F_QV: n4 = iqv; break;
+    case RCM_F_QC: n4 = iqc; break;
+    default: err = "oracle: no physics tendency for this field"; return RCM_ERR_ARG;
+  }
+  const long long n1 = ub[0] - lb[0] + 1, n2 = ub[1] - lb[1] + 1;
+  const int l1 = dst ? dst->l1 : m_qxten.l1, l2 = dst ? dst->l2 : m_qxten.l2, m1 = dst ? dst->n1 : m_qxten.n1, m2 = dst ? dst->n2 : m_qxten.n2;
+  for (int k = std::max(lb[2], 1); k <= std::min(ub[2], kz); ++k)
+    for (int i = std::max(lb[1], l2); i <= std::min(ub[1], l2 + m2 - 1); ++i)
+      for (int j = std::max(lb[0], l1); j <= std::min(ub[0], l1 + m1 - 1); ++j) {
+        const double v = a[(j - lb[0]) + n1 * ((i - lb[1]) + n2 * (long long)(k - lb[2]))];
+        if (dst) (*dst)(j, i, k) = v; else m_qxten(j, i, k, n4) = v;
+      }
+  return RCM_OK;
+}
+
+// the members of `atms` the MOLOCH core hands to the physics: aliases of mo_atm (Main/mod_slice.F90:82-100) and what
+// mkslice computes for idynamic = 3 (:107-146)
+int Oracle::mo_get_slice(int id, double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (id < 0 || id >= RCM_SL_COUNT) { err = "oracle: bad slice id"; return RCM_ERR_ARG; }
+  A3 out; out.alloc(jce1, jce2, ice1, ice2, 1, kzp1);
+  int nk = kz;
+  if (id == RCM_SL_PF3D || id == RCM_SL_WB3D || id == RCM_SL_ZQ) nk = kzp1;
+  if (id == RCM_SL_PS2D) nk = 1;
+  auto inner = [&](int j, int i) { return j >= jci1 && j <= jci2 && i >= ici1 && i <= ici2; };
+  for (int i = ice1; i <= ice2; ++i)
+    for (int j = jce1; j <= jce2; ++j)
+      for (int k = 1; k <= nk; ++k) {
+        double v = d_zero;
+        const double qvv = inner(j, i) ? std::max(m_qx(j, i, std::min(k, kz), iqv), minqq) : m_qx(j, i, std::min(k, kz), iqv);
+        switch (id) {
+          case RCM_SL_TB3D: v = m_t(j, i, k); break;
+          case RCM_SL_QVB3D: v = qvv; break;
+          case RCM_SL_QCB3D: v = inner(j, i) ? std::max(m_qx(j, i, k, iqc), d_zero) : m_qx(j, i, k, iqc); break;
+          case RCM_SL_UBX3D: v = m_ux(j, i, k); break;
+          case RCM_SL_VBX3D: v = m_vx(j, i, k); break;
+          case RCM_SL_PB3D: v = m_p(j, i, k); break;
+          case RCM_SL_PF3D:
+            if (k == 1) v = 100.0;
+            else if (k == kzp1) v = psa(j, i);
+            else v = p00 * std::pow(d_half * (m_pai(j, i, k) + m_pai(j, i, k - 1)), cpovr);
+            break;
+          case RCM_SL_PS2D: v = psa(j, i); break;
+          case RCM_SL_RHOB3D: v = m_rho(j, i, k); break;
+          case RCM_SL_TH3D: v = m_t(j, i, k) * std::pow(p00 / m_p(j, i, k), rovcp); break;
+          case RCM_SL_TV3D: v = m_tvirt(j, i, k); break;
+          case RCM_SL_TP3D: v = inner(j, i) ? m_t(j, i, k) * std::pow(psa(j, i) / m_p(j, i, k), rovcp) : d_zero; break;
+          case RCM_SL_WPX3D: v = inner(j, i) ? -d_half * egrav * m_rho(j, i, k) * (m_w(j, i, k) + m_w(j, i, k + 1)) : d_zero; break;
+          case RCM_SL_WB3D: v = m_w(j, i, k); break;
+          case RCM_SL_ZQ: v = m_zetaf(j, i, k); break;
+          case RCM_SL_ZA: v = m_zeta(j, i, k); break;
+          case RCM_SL_DZQ: v = m_dz(j, i, k); break;
+          case RCM_SL_QSB3D: v = pfwsat(m_t(j, i, k), m_p(j, i, k)); break;
+          case RCM_SL_RHB3D: v = inner(j, i) ? std::min(std::max(qvv / pfwsat(m_t(j, i, k), m_p(j, i, k)), rhmin), rhmax) : d_zero; break;
+        }
+        out(j, i, k) = v;
+      }
+  const long long n1 = ub[0] - lb[0] + 1, n2 = ub[1] - lb[1] + 1;
+  for (int k = std::max(lb[2], 1); k <= std::min(ub[2], nk); ++k)
+    for (int i = std::max(lb[1], ice1); i <= std::min(ub[1], ice2); ++i)
+      for (int j = std::max(lb[0], jce1); j <= std::min(ub[0], jce2); ++j)
+        a[(j - lb[0]) + n1 * ((i - lb[1]) + n2 * (long long)(k - lb[2]))] = out(j, i, k);
+  return RCM_OK;
+}
+
 int Oracle::set_phys(int field, const double* a, const int32_t lb[3], const int32_t ub[3]) {
+  if (moloch) return mo_set_phys(field, a, lb, ub);
   ensure_phys();
   A3* dst = nullptr;
   int n4 = 0;
@@ -90,6 +172,7 @@ int Oracle::set_phys(int field, const double* a, const int32_t lb[3], const int3
 }
 
 void Oracle::clear_phys() {
+  if (moloch) { if (mo_phys_on) { m_tten.fill(d_zero); m_uten.fill(d_zero); m_vten.fill(d_zero); m_qxten.fill(d_zero); } return; }
   if (!phys_on) return;
   for (A3* a : {&uphy, &vphy, &tphy, &ppphy, &wphy}) a->fill(d_zero);
   if (uw_on) tkephy.fill(d_zero);
@@ -98,7 +181,7 @@ void Oracle::clear_phys() {
 
 // One slice of Main/mod_slice.F90:167-308 on the cross grid (values outside the range the reference defines are 0).
 int Oracle::get_slice(int id, double* a, const int32_t lb[3], const int32_t ub[3]) {
-  if (moloch) { err = "oracle: slices are built for idynamic = 1, 2"; return RCM_ERR_ARG; }
+  if (moloch) return mo_get_slice(id, a, lb, ub);
   A3 out; out.alloc(jce1, jce2, ice1, ice2, 1, kzp1);
   const double ptoppa = ptop * d_1000;
   auto rps = [&](int j, int i) { return d_one / psb(j, i); };

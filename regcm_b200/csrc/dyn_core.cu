@@ -51,6 +51,8 @@ void launch_window(bool pack, double* buf, double* p_shifted, int j0, int i0, in
 void launch_tr(const Geom&, const Fields&, const TrFields&, const StepScalars&, cudaStream_t);
 void launch_tke(const Geom&, const Fields&, const UwFields&, const StepScalars&, cudaStream_t);
 void launch_sl(const Geom&, const Fields&, const TrFields&, const StepScalars&, cudaStream_t);
+void launch_mo_phys(const Geom&, const MoFields&, double, cudaStream_t);
+void launch_mo_slice(const Geom&, const MoFields&, int, double*, cudaStream_t);
 void launch_tke_bdy(const Geom&, const Fields&, const UwFields&, const int2*, int, int, int, cudaStream_t);
 void launch_tr_repair(const Geom&, const TrFields&, const StepScalars&, cudaStream_t);
 void launch_tr_bdyval(const Geom&, const TrFields&, const int2*, int, double, int, int, cudaStream_t);
@@ -1952,7 +1954,20 @@ static double** phys_ptr(rcm_dyn* h, int field) {
 
 extern "C" int rcm_dyn_set_phys_tend(rcm_dyn* h, int field, const double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
-  if (h->moloch) return fail(h, RCM_ERR_ARG, "physics tendencies are coupled for idynamic = 1, 2");
+  if (h->moloch) {   // mo_atm%tten, qxten, uten, vten (Main/mod_moloch.F90:1548-1557): uncoupled, u and v on their C-grid points
+    MoFields& m = h->mf;
+    double** pm = field == RCM_F_T ? &m.phy_t : field == RCM_F_QV ? &m.phy_qv : field == RCM_F_QC ? &m.phy_qc : field == RCM_F_U ? &m.phy_u
+                  : field == RCM_F_V ? &m.phy_v : nullptr;
+    if (!pm) return fail(h, RCM_ERR_ARG, "no physics tendency for this field");
+    cudaSetDevice(h->device);
+    if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+    if (!m.phy_t)
+      for (double** q : {&m.phy_t, &m.phy_qv, &m.phy_qc, &m.phy_u, &m.phy_v}) {
+        *q = dev_alloc3(h, h->g.kzp1);
+        if (!*q) return fail(h, RCM_ERR_CUDA, "device memory allocation failed (physics tendencies)");
+      }
+    return upload3(h, *pm, a, lb, ub, h->g.kz);
+  }
   double** pp = (field == RCM_F_TKE && h->uw_on) ? &h->uw.phy : phys_ptr(h, field);
   if (!pp || (h->hydro && (field == RCM_F_PP || field == RCM_F_W))) return fail(h, RCM_ERR_ARG, "no physics tendency for this field");
   cudaSetDevice(h->device);
@@ -1974,6 +1989,11 @@ extern "C" int rcm_dyn_clear_phys_tend(rcm_dyn* h) {
   if (!h) return RCM_ERR_ARG;
   cudaSetDevice(h->device);
   if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  if (h->moloch) {
+    for (double* p : {h->mf.phy_t, h->mf.phy_qv, h->mf.phy_qc, h->mf.phy_u, h->mf.phy_v})
+      if (p) CUDA_OK(cudaMemset(p - h->off3, 0, (size_t)h->g.sk * h->g.kzp1 * sizeof(double)));
+    return RCM_OK;
+  }
   for (int q : {RCM_F_U, RCM_F_V, RCM_F_T, RCM_F_QV, RCM_F_QC, RCM_F_PP, RCM_F_W}) {
     double** pp = phys_ptr(h, q);
     if (pp && *pp) CUDA_OK(cudaMemset(*pp - h->off3, 0, (size_t)h->g.sk * h->g.kzp1 * sizeof(double)));
@@ -2005,12 +2025,11 @@ extern "C" int rcm_dyn_set_kpbl(rcm_dyn* h, const int32_t* kpbl, const int32_t l
 extern "C" int rcm_dyn_step_pre_physics(rcm_dyn* h) {
   if (!h) return RCM_ERR_ARG;
   if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_step_pre_physics before rcm_dyn_init");
-  if (h->moloch) return fail(h, RCM_ERR_ARG, "the pre-/post-physics split is built for idynamic = 1, 2");
   cudaSetDevice(h->device);
   if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
   if (h->mid_step) return RCM_OK;   // already there
   h->head_only = true;
-  const int rc = tend(h);
+  const int rc = h->moloch ? mo_step_one(h) : tend(h);
   h->head_only = false;
   if (rc) return rc;
   CUDA_OK(cudaStreamSynchronize(h->st));
@@ -2027,10 +2046,19 @@ extern "C" int rcm_dyn_step_post_physics(rcm_dyn* h) {
 extern "C" int rcm_dyn_get_slice(rcm_dyn* h, int id, double* a, const int32_t lb[3], const int32_t ub[3]) {
   if (!h || !a) return RCM_ERR_ARG;
   if (!h->inited) return fail(h, RCM_ERR_STATE, "rcm_dyn_get_slice before rcm_dyn_init");
-  if (h->moloch) return fail(h, RCM_ERR_ARG, "slices are built for idynamic = 1, 2");
   if (id < 0 || id >= RCM_SL_COUNT) return fail(h, RCM_ERR_ARG, "bad slice id");
   cudaSetDevice(h->device);
   if (h->pending) { const int rcp_ = finish_steps(h); if (rcp_) return rcp_; }
+  if (h->moloch) {   // aliases of mo_atm and the products of mkslice for idynamic = 3 (Main/mod_slice.F90:82-146)
+    if (!h->slice_buf) { h->slice_buf = dev_alloc3(h, h->g.kzp1); if (!h->slice_buf) return fail(h, RCM_ERR_CUDA, "device memory allocation failed (slice)"); }
+    launch_mo_slice(h->g, h->mf, id, h->slice_buf, h->st);
+    h->launches += 1;
+    int nkm = h->g.kz;
+    if (id == RCM_SL_PF3D || id == RCM_SL_WB3D || id == RCM_SL_ZQ) nkm = h->g.kzp1;
+    int32_t l3m[3] = {lb[0], lb[1], lb[2]}, u3m[3] = {ub[0], ub[1], ub[2]};
+    if (id == RCM_SL_PS2D) { nkm = 1; l3m[2] = u3m[2] = 1; }
+    return download3(h, h->slice_buf, a, l3m, u3m, nkm);
+  }
   if (h->hydro && !h->mid_step && (id == RCM_SL_WPX3D || id == RCM_SL_WB3D))
     return fail(h, RCM_ERR_STATE, "omega of the hydrostatic core exists between rcm_dyn_step_pre_physics and rcm_dyn_step_post_physics");
   if (!h->slice_buf) { h->slice_buf = dev_alloc3(h, h->g.kzp1); if (!h->slice_buf) return fail(h, RCM_ERR_CUDA, "device memory allocation failed (slice)"); }

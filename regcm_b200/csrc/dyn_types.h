@@ -186,4 +186,8 @@ struct MoFields {
   double* rimbuf;
   int* nanflag;
   unsigned long long* psbits;  // [0] max of ps over the interior as ordered bits, [1] complement of the min's bits
+  // physics coupling: mo_atm%tten, qxten, uten, vten handed in by the parametrizations (null until set),
+  // and zetaf (kz+1 levels), the height the physics sees as atms%zq
+  double *phy_t, *phy_qv, *phy_qc, *phy_u, *phy_v;
+  double* zetaf;
 };

@@ -9,6 +9,7 @@
 // values of the relaxation-zone points into a compact buffer, phase b stores them.
 #include "dev_common.cuh"
 #include "launch.h"
+#include "../../include/regcm_dyn.h"
 
 using namespace rcm;
 
@@ -297,4 +298,81 @@ void launch_mo_init_state(const Geom& g, const MoFields& f, const MoScalars& s, 
 void launch_mo_scale2d(const Geom& g, double* a, double c, int j1, int j2, int i1, int i2, cudaStream_t st) {
   dim3 b(32, 4);
   RCM_LAUNCH(k_mo_scale2d, grid2(j2 - j1 + 1, i2 - i1 + 1, b), b, st, g, a, c, j1, j2, i1, i2);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Physics coupling of the MOLOCH core.
+//   k_mo_phys    the state update at the end of physical_parametrizations (Main/mod_moloch.F90:1548-1557): t, u, v, qx
+//                advance by dtsec times the tendencies handed in; hydrometeors floored at 0, qv at minqq
+//   k_mo_slice   one member of `atms` on request: the aliases of mo_atm (Main/mod_slice.F90:82-100) and what mkslice
+//                computes for idynamic = 3 (:107-146)
+__global__ void k_mo_phys(const Geom g, const MoFields f, const double dtsec) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jde1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ide1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = 1 + blockIdx.z;
+  if (j > g.jde2 || i > g.ide2) return;
+  const bool ci = (i >= g.ici1 && i <= g.ici2), cj = (j >= g.jci1 && j <= g.jci2);
+  if (cj && ci) {
+    P3(f.t, j, i, k) = P3(f.t, j, i, k) + dtsec * L3(f.phy_t, j, i, k);
+    const double qv = P3(f.qv, j, i, k) + dtsec * L3(f.phy_qv, j, i, k);
+    const double qc = P3(f.qc, j, i, k) + dtsec * L3(f.phy_qc, j, i, k);
+    P3(f.qc, j, i, k) = fmax(qc, 0.0);
+    P3(f.qv, j, i, k) = fmax(qv, minqq);
+  }
+  if (j >= g.jdi1 && j <= g.jdi2 && ci) P3(f.u, j, i, k) = P3(f.u, j, i, k) + dtsec * L3(f.phy_u, j, i, k);
+  if (cj && i >= g.idi1 && i <= g.idi2) P3(f.v, j, i, k) = P3(f.v, j, i, k) + dtsec * L3(f.phy_v, j, i, k);
+}
+
+__global__ void __launch_bounds__(128) k_mo_slice(const Geom g, const MoFields f, const int id, double* __restrict__ out) {
+  const int si = g.si; const long long sk = g.sk;
+  const int j = g.jce1 + blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = g.ice1 + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j > g.jce2 || i > g.ice2) return;
+  const int kz = g.kz, kzp1 = g.kzp1;
+  const bool inner = (j >= g.jci1 && j <= g.jci2 && i >= g.ici1 && i <= g.ici2);
+  const double ps = L2(f.ps, j, i);
+  int nk = kz;
+  if (id == RCM_SL_PF3D || id == RCM_SL_WB3D || id == RCM_SL_ZQ) nk = kzp1;
+  if (id == RCM_SL_PS2D) nk = 1;
+  for (int k = 1; k <= nk; ++k) {
+    const int kh = min(k, kz);
+    const double qvv = inner ? fmax(L3(f.qv, j, i, kh), minqq) : L3(f.qv, j, i, kh);
+    double v = 0.0;
+    switch (id) {
+      case RCM_SL_TB3D: v = L3(f.t, j, i, k); break;
+      case RCM_SL_QVB3D: v = qvv; break;
+      case RCM_SL_QCB3D: v = inner ? fmax(L3(f.qc, j, i, k), 0.0) : L3(f.qc, j, i, k); break;
+      case RCM_SL_UBX3D: v = L3(f.ux, j, i, k); break;
+      case RCM_SL_VBX3D: v = L3(f.vx, j, i, k); break;
+      case RCM_SL_PB3D: v = L3(f.p, j, i, k); break;
+      case RCM_SL_PF3D:
+        if (k == 1) v = 100.0;
+        else if (k == kzp1) v = ps;
+        else v = p00 * pow(0.5 * (L3(f.pai, j, i, k) + L3(f.pai, j, i, k - 1)), cpovr);
+        break;
+      case RCM_SL_PS2D: v = ps; break;
+      case RCM_SL_RHOB3D: v = L3(f.p, j, i, k) / (rgas * L3(f.t, j, i, k)); break;
+      case RCM_SL_TH3D: v = L3(f.t, j, i, k) * pow(p00 / L3(f.p, j, i, k), rovcp); break;
+      case RCM_SL_TV3D: v = L3(f.tvirt, j, i, k); break;
+      case RCM_SL_TP3D: v = inner ? L3(f.t, j, i, k) * pow(ps / L3(f.p, j, i, k), rovcp) : 0.0; break;
+      case RCM_SL_WPX3D: v = inner ? -0.5 * egrav * (L3(f.p, j, i, k) / (rgas * L3(f.t, j, i, k))) * (L3(f.w, j, i, k) + L3(f.w, j, i, k + 1)) : 0.0; break;
+      case RCM_SL_WB3D: v = L3(f.w, j, i, k); break;
+      case RCM_SL_ZQ: v = L3(f.zetaf, j, i, k); break;
+      case RCM_SL_ZA: v = L3(f.zeta, j, i, k); break;
+      case RCM_SL_DZQ: v = L3(f.zetaf, j, i, k) - L3(f.zetaf, j, i, k + 1); break;
+      case RCM_SL_QSB3D: v = mo_pfwsat(L3(f.t, j, i, k), L3(f.p, j, i, k)); break;
+      case RCM_SL_RHB3D: v = inner ? fmin(fmax(qvv / mo_pfwsat(L3(f.t, j, i, k), L3(f.p, j, i, k)), 0.01), 1.01) : 0.0; break;
+    }
+    P3(out, j, i, k) = v;
+  }
+}
+
+void launch_mo_phys(const Geom& g, const MoFields& f, double dtsec, cudaStream_t st) {
+  dim3 b(32, 4), gr((g.jde2 - g.jde1 + 32) / 32, (g.ide2 - g.ide1 + 4) / 4, g.kz);
+  RCM_LAUNCH(k_mo_phys, gr, b, st, g, f, dtsec);
+}
+void launch_mo_slice(const Geom& g, const MoFields& f, int id, double* out, cudaStream_t st) {
+  dim3 b(32, 4), gr((g.jce2 - g.jce1 + 32) / 32, (g.ice2 - g.ice1 + 4) / 4);
+  RCM_LAUNCH(k_mo_slice, gr, b, st, g, f, id, out);
 }

@@ -64,6 +64,8 @@ def main():
     ap.add_argument("--work", action="store_true", help="also dump the per-step work arrays")
     ap.add_argument("--spiky-tracers", action="store_true", help="tracers with sharp edges (drives their negative fix)")
     ap.add_argument("--sharp-q", action="store_true", help="moisture with sharp fronts (drives the negative-q repair)")
+    ap.add_argument("--phys", action="store_true", help="every step through pre_physics / set_phys_tend / post_physics with the synthetic "
+                    "tendencies of tests/test_physics_coupling.py")
     ap.add_argument("--uw", action="store_true", help="ibltyp = 2 inputs of tests/test_tke.py: TKE state, TKE physics source, kpbl, cloud water")
     ap.add_argument("--out", required=True)
     args = ap.parse_args()
@@ -181,6 +183,14 @@ def main():
             core.set_restart(rid, a, lb=(1, 1, 1) if rid == capi.R_TMASK else clb)
         core.set_clock(d.lcount, d.xbctime)
         core.step(args.steps - args.restart_at)
+    elif args.phys:
+        from tests.test_physics_coupling import _mo_tendencies, _phys_tendencies
+        ten = _mo_tendencies(base) if cfg.idynamic == 3 else _phys_tendencies(base, cfg.idynamic == 1)
+        for n in range(args.steps):
+            core.step_pre_physics()
+            for f, a in ten.items():
+                core.set_phys_tend(f, a * (1.0 + 0.25 * n))      # global arrays; the library keeps this rank's window
+            core.step_post_physics()
     else:
         core.step(args.steps)
     out = {"tile": np.array(core.tile())}

@@ -46,3 +46,38 @@ def test_step_with_physics_tendencies_vs_oracle(cuda_lib, name, idyn):
     again.step(3)
     for f in prognostics(plain):
         np.testing.assert_array_equal(plain.get_state(f), again.get_state(f), err_msg=capi.FIELD_NAMES[f])
+
+
+# ---------------------------------------------------------------------------- MOLOCH core (idynamic = 3)
+def test_moloch_slices_vs_oracle(cuda_lib):
+    case, core, ref = make_pair(cuda_lib, "smallm")
+    core.step(2); ref.step(2)
+    core.step_pre_physics(); ref.step_pre_physics()
+    for sid in range(19):
+        got, want = core.get_slice(sid), ref.get_slice(sid)
+        sc = max(float(np.abs(want).max()), 1e-300)
+        assert float(np.abs(got - want).max()) / sc <= 1e-11, capi.SLICE_NAMES[sid]
+    core.step_post_physics(); ref.step_post_physics()
+    assert max(e[0] for e in rel_errors(core, ref).values()) <= 1e-12
+
+
+def test_moloch_step_with_physics_tendencies_vs_oracle(cuda_lib):
+    from tests.test_physics_coupling import _mo_tendencies
+    case, core, ref = make_pair(cuda_lib, "smallm")
+    _, plain, _ = make_pair(cuda_lib, "smallm")
+    ten = _mo_tendencies(case)
+    for n in range(3):
+        for c in (core, ref):
+            c.step_pre_physics()
+            for f, a in ten.items():
+                c.set_phys_tend(f, a * (1.0 + 0.25 * n))
+            c.step_post_physics()
+        plain.step_pre_physics(); plain.step_post_physics()
+    errs = rel_errors(core, ref)
+    assert max(e[0] for e in errs.values()) <= 1e-12, errs
+    moved = rel_errors(core, plain)
+    assert min(moved[k][0] for k in ("ta", "ua", "va", "qva")) > 1e-8, moved
+    _, again, _ = make_pair(cuda_lib, "smallm")
+    again.step(3)
+    for f in prognostics(plain):
+        np.testing.assert_array_equal(plain.get_state(f), again.get_state(f), err_msg=capi.FIELD_NAMES[f])

@@ -304,6 +304,28 @@ def test_many_fields_in_one_exchange(emu_lib, tmp_path):
     core.close()
 
 
+def test_moloch_physics_coupling_multirank(emu_lib, tmp_path):
+    """The pre-/post-physics split of the MOLOCH core on a 2x2 decomposition with tendencies handed in every step."""
+    from tests.test_physics_coupling import _mo_tendencies
+    steps = 4
+    run_ranks(4, tmp_path, ["--case", "tinym", "--steps", str(steps), "--cpus-j", "2", "--cpus-i", "2", "--phys"])
+    case = synth.make_case("tinym")
+    core = capi.DynCore(emu_lib, case.cfg)
+    synth.load_case(core, case)
+    ten = _mo_tendencies(case)
+    for n in range(steps):
+        core.step_pre_physics()
+        for f, a in ten.items():
+            core.set_phys_tend(f, a * (1.0 + 0.25 * n))
+        core.step_post_physics()
+    glob, _ = assemble_moloch(tmp_path, 4, case.cfg)
+    for f in MOLOCH_FIELDS:
+        want = core.get_state(f)
+        want = want if want.ndim == 3 else want[:, :, None]
+        np.testing.assert_array_equal(glob[f], want, err_msg=capi.FIELD_NAMES[f])
+    core.close()
+
+
 # ---------------------------------------------------------------------------- UW-PBL coupling (SURVEY §8 f3: TKE, vadv4d ind = 3)
 @pytest.mark.parametrize("idynamic", [2, 1])
 def test_tke_multirank_matches_single_rank(emu_lib, tmp_path, idynamic):
