@@ -257,6 +257,7 @@ void Oracle::new_pressure() {
 
 // Main/mod_diffusion.F90:182-211,232-250 (hydrostatic: no dw/dz term)
 void Oracle::calc_coeff_hydro() {
+  if (cfg.idiffu == 3) { calc_coeff6(); return; }
   const A3& ud = ubd3d; const A3& vd = vbd3d;
   xkc.fill(d_zero); xkd.fill(d_zero); xkcf.fill(d_zero);
   for (int k = 1; k <= kz; ++k)

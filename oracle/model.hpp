@@ -350,6 +350,7 @@ struct Oracle {
 
   // ---- mod_diffusion (oracle/diffusion.cpp) ----
   void calc_coeff();
+  void calc_coeff6();
   void diffu_d(A3& ut, A3& vt, const A3& u, const A3& v);
   void diffu_x3d(A3& ften, const A3& f);
   void diffu_x3df(A3& ften, const A3& f, double fac);

@@ -29,7 +29,7 @@ int Oracle::create(const rcm_cfg& c) {
   nsplit = hydro ? c.nsplit : 0;
   if (c.isladvec != 0 && (c.isladvec != 1 || c.idynamic == 3)) { err = "oracle: isladvec must be 0 or 1 (idynamic 1, 2)"; return RCM_ERR_ARG; }
   if (c.ipgf != 0 && c.ipgf != 1) { err = "oracle: ipgf must be 0 or 1"; return RCM_ERR_ARG; }
-  if (c.idiffu != 1 && c.idiffu != 2) { err = "oracle: idiffu must be 1 or 2 (3, the flux-limited 6th-order operator, is not restated)"; return RCM_ERR_ARG; }
+  if (c.idiffu < 1 || c.idiffu > 3) { err = "oracle: idiffu must be 1, 2 or 3"; return RCM_ERR_ARG; }
   // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)
   if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 4 || c.iboudy == 5 || (c.idynamic != 3 && (c.iboudy == 2 || c.iboudy == 3)))) { err = "oracle: iboudy must be 0..5 (2, 3: idynamic 1, 2 only)"; return RCM_ERR_ARG; }
   if (c.nqx != 2) { err = "oracle: nqx must be 2"; return RCM_ERR_ARG; }
@@ -39,7 +39,7 @@ int Oracle::create(const rcm_cfg& c) {
   ptop = c.ptop;
   dtsec = c.dt; dt = c.dt; dt2 = d_two * dt;   // mod_params.F90:1628,1708
   dtbdys = (double)c.ibdyfrq * 3600.0;          // :1631
-  idif = (c.idiffu == 2) ? 1 : 2;               // :1968-1971
+  idif = (c.idiffu == 2) ? 1 : (c.idiffu == 3) ? 3 : 2;   // :1968-1973
   // mod_params.F90:1763-1770
   dx = c.ds * d_1000;
   dx2 = d_two * dx; dx4 = d_four * dx; dx8 = 8.0 * dx; dx16 = 16.0 * dx;

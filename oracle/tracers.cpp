@@ -184,6 +184,26 @@ void Oracle::tracer_tendency() {
       }
     }
     // diffu_x4d(chidyn, chib3d, 1, ntr, 1.0)
+    if (cfg.idiffu == 3) {   // Main/mod_diffusion.F90:895-960: j = jci2 only, clamped stencil, flux sign from b3 / msfd
+      const int j = jci2;
+      for (int k = 1; k <= kz; ++k)
+        for (int i = ici1; i <= ici2; ++i) {
+          auto cl = [&](int v, int hi) { return std::min(std::max(v, 1), hi); };
+          auto F = [&](int jj, int ii) { return b3(jj, ii, k); };
+          auto G = [&](int jj, int ii) { return b3(jj, ii, k) / msfd(jj, ii); };
+          const int jm1 = cl(j - 1, jx - 1), jm2 = cl(j - 2, jx - 1), jm3 = cl(j - 3, jx - 1), jp1 = cl(j + 1, jx - 1), jp2 = cl(j + 2, jx - 1), jp3 = cl(j + 3, jx - 1);
+          const int im1 = cl(i - 1, iy - 1), im2 = cl(i - 2, iy - 1), im3 = cl(i - 3, iy - 1), ip1 = cl(i + 1, iy - 1), ip2 = cl(i + 2, iy - 1), ip3 = cl(i + 3, iy - 1);
+          double x0 = (10.0 * (F(j, i) - F(jm1, i)) + (-5.0) * (F(jp1, i) - F(jm2, i)) + 1.0 * (F(jp2, i) - F(jm3, i)));
+          if (x0 * (G(j, i) - G(jm1, i)) <= d_zero) x0 = d_zero;
+          double x1 = (10.0 * (F(jp1, i) - F(j, i)) + (-5.0) * (F(jp2, i) - F(jm1, i)) + 1.0 * (F(jp3, i) - F(jm2, i)));
+          if (x1 * (G(jp1, i) - G(j, i)) <= d_zero) x1 = d_zero;
+          double y0 = (10.0 * (F(j, i) - F(j, im1)) + (-5.0) * (F(j, ip1) - F(j, im2)) + 1.0 * (F(j, ip2) - F(j, im3)));
+          if (y0 * (G(j, i) - G(j, im1)) <= d_zero) y0 = d_zero;
+          double y1 = (10.0 * (F(j, ip1) - F(j, i)) + (-5.0) * (F(j, ip2) - F(j, im1)) + 1.0 * (F(j, ip3) - F(j, im2)));
+          if (y1 * (G(j, ip1) - G(j, i)) <= d_zero) y1 = d_zero;
+          dyn(j, i, k) = dyn(j, i, k) + d_one * xkc(j, i, k) * ((x1 - x0) + (y1 - y0));
+        }
+    } else
     if (cfg.idiffu == 2) {   // Main/mod_diffusion.F90:881-894
       const double o4_c1 = 4.0 / 6.0, o4_c2 = 1.0 / 6.0, o4_c3 = -20.0 / 6.0;
       for (int k = 1; k <= kz; ++k)

@@ -274,6 +274,9 @@ __device__ __forceinline__ double vadv3_face(const Geom& g, const Fields& f, con
   return fg;
 }
 
+// idiffu = 3: the tendency k_diff6 left for field `fld` at (jdi2 | jci2, i, k)
+#define D6(fld, i, k) LD1(&f.d6[((long long)(fld) * g.kzp1 + ((k) - 1)) * (g.iy + 2) + (i)])
+
 // idiffu = 2: the nine-point operator o4_c1*(sides) + o4_c2*(corners) + o4_c3*centre with the reference's order of
 // the sums (Main/mod_diffusion.F90:63-65,386-411,592-601,726-735,881-894); pp = (j+1,i+1), mm = (j-1,i-1),
 // mp = (j-1,i+1), pm = (j+1,i-1)

@@ -51,6 +51,7 @@ void launch_window(bool pack, double* buf, double* p_shifted, int j0, int i0, in
 void launch_tr(const Geom&, const Fields&, const TrFields&, const StepScalars&, cudaStream_t);
 void launch_tke(const Geom&, const Fields&, const UwFields&, const StepScalars&, cudaStream_t);
 void launch_sl(const Geom&, const Fields&, const TrFields&, const StepScalars&, cudaStream_t);
+void launch_diff6(const Geom&, const Fields&, const TrFields&, const UwFields&, const StepScalars&, int, double, cudaStream_t);
 void launch_mo_phys(const Geom&, const MoFields&, double, cudaStream_t);
 void launch_mo_slice(const Geom&, const MoFields&, int, double*, cudaStream_t);
 void launch_tke_bdy(const Geom&, const Fields&, const UwFields&, const int2*, int, int, int, cudaStream_t);
@@ -336,7 +337,9 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
   if (c.ipgf != 0 && c.ipgf != 1) return bail(RCM_ERR_ARG, "ipgf must be 0 or 1");
   if (c.isladvec != 0 && (c.isladvec != 1 || c.idynamic == 3 || c.nproc != 1))
     return bail(RCM_ERR_ARG, "isladvec must be 0 or 1; 1 runs with idynamic 1, 2 on one rank (the departure stencil reaches three cells out)");
-  if (c.idiffu != 1 && c.idiffu != 2) return bail(RCM_ERR_ARG, "idiffu must be 1 or 2 (3, the flux-limited 6th-order operator, is not implemented)");
+  if (c.idiffu < 1 || c.idiffu > 3) return bail(RCM_ERR_ARG, "idiffu must be 1, 2 or 3");
+  if (c.idiffu == 3 && c.idynamic != 3 && c.nproc != 1)
+    return bail(RCM_ERR_ARG, "idiffu = 3 runs on one rank (its stencil is three cells wide, RCM_HALO is 2)");
   // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)
   if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 4 || c.iboudy == 5 || (c.idynamic != 3 && (c.iboudy == 2 || c.iboudy == 3))))
     return bail(RCM_ERR_ARG, "iboudy must be 0, 1, 4 or 5 (idynamic 1, 2: also 2, 3)");
@@ -507,6 +510,10 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
     tr.nq_cnt = dev_alloc_raw<int>(h, (size_t)c.ntr * g.kz);
     tr.negcnt = dev_alloc_raw<unsigned long long>(h, 1);
     ok = ok && tr.cefc && tr.cegc && z && tr.nq_list && tr.nq_cnt && tr.negcnt;
+  }
+  if (c.idiffu == 3 && c.idynamic != 3) {   // the one column idiffu = 3 acts on (k_diff6)
+    f.d6 = dev_alloc_raw<double>(h, (size_t)(RCM_D6_CHI + RCM_MAXTR) * g.kzp1 * (size_t)(g.iy + 2));
+    ok = ok && f.d6;
   }
   if (c.isladvec == 1) {   // scratch of k_sl
     A3(f.slqv); A3(f.slqc);
@@ -1625,6 +1632,8 @@ static int tend_hydro(rcm_dyn* h) {
   }
   if (h->head_only) { h->mid_step = true; return RCM_OK; }
   h->mid_step = false;
+  if (h->cfg.idiffu == 3)   // diff_6th_coef = diff_6th_factor * 0.015625 / (2 dtsec) (Main/mod_diffusion.F90:78,154)
+    TIMED(KID_XKC, 1, launch_diff6(g, f, h->tr, h->uw, s, h->uw_on ? 1 : 0, 0.12 * 0.015625 / (2.0 * h->dtsec), h->st));
   if (h->cfg.isladvec == 1) TIMED(KID_TR, 1, launch_sl(g, f, h->tr, s, h->st));   // semi-Lagrangian tendencies of qv, qc, tracers
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_H_UV, 1, launch_h_uv(g, f, s, h->st));
@@ -1715,6 +1724,8 @@ static int tend(rcm_dyn* h) {
   }
   if (h->head_only) { h->mid_step = true; return RCM_OK; }
   h->mid_step = false;
+  if (h->cfg.idiffu == 3)   // diff_6th_coef = diff_6th_factor * 0.015625 / (2 dtsec) (Main/mod_diffusion.F90:78,154)
+    TIMED(KID_XKC, 1, launch_diff6(g, f, h->tr, h->uw, s, h->uw_on ? 1 : 0, 0.12 * 0.015625 / (2.0 * h->dtsec), h->st));
   if (h->cfg.isladvec == 1) TIMED(KID_TR, 1, launch_sl(g, f, h->tr, s, h->st));   // semi-Lagrangian tendencies of qv, qc, tracers
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_UV, 1, h->uv_maps ? launch_uv_tma(g, f, s, h->st, h->uv_maps) : launch_uv(g, f, s, h->st));

@@ -155,7 +155,11 @@ struct Fields {
   const int* kpb;
   // isladvec = 1: semi-Lagrangian horizontal advection tendencies of qv, qc left by k_sl (null otherwise)
   double *slqv, *slqc;
+  // idiffu = 3: the diffusion tendencies of the one column the operator acts on (j = jdi2 / jci2), left by k_diff6:
+  // [(field * kzp1 + k - 1) * (iy + 2) + i], fields RCM_D6_* (null otherwise)
+  double* d6;
 };
+enum { RCM_D6_U = 0, RCM_D6_V, RCM_D6_T, RCM_D6_QV, RCM_D6_QC, RCM_D6_PP, RCM_D6_W, RCM_D6_TKE, RCM_D6_CHI };
 
 // ---------------------------------------------------------------------------
 // MOLOCH core (idynamic = 3; Main/mod_moloch.F90, Arakawa C grid, zita levels).

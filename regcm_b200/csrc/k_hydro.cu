@@ -225,9 +225,10 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
   const double psdota = L2(f.psdota, j, i), psdotb = L2(f.psdotb, j, i);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_d, j, i) : 0;
   const int ibs = (s.iboudy == 4) ? L2(f.zone_d, j, i) : 0;   // sponge zone (iboudy = 4)
-  const bool d9 = (s.idiffu == 2);   // nine-point operator on every interior point, no boundary ring
-  const bool dint = !d9 && diff_interior(g, j, i, true);
-  const int nring = d9 ? 0 : ring_count(g, j, i, true);
+  const bool d9 = (s.idiffu == 2);
+  const bool d6on = (s.idiffu == 3) && j == g.jdi2;   // the one column idiffu = 3 acts on (k_diff6)   // nine-point operator on every interior point, no boundary ring
+  const bool dint = (s.idiffu == 1) && diff_interior(g, j, i, true);
+  const int nring = (s.idiffu == 1) ? ring_count(g, j, i, true) : 0;
   // cross points around the dot: 11=(j,i) 10=(j,i-1) 01=(j-1,i) 00=(j-1,i-1)
   const double pa11 = L2(f.psa, j, i), pa10 = L2(f.psa, j, i - 1), pa01 = L2(f.psa, j - 1, i), pa00 = L2(f.psa, j - 1, i - 1);
   const double ra11 = L2(f.rpsa, j, i), ra10 = L2(f.rpsa, j, i - 1), ra01 = L2(f.rpsa, j - 1, i), ra00 = L2(f.rpsa, j - 1, i - 1);
@@ -345,6 +346,7 @@ k_h_uv(const Geom g, const Fields f, const StepScalars s) {
         ut = ut + xkd * lap9(du_c, du_jm, du_jp, du_im, du_ip, DU(1, 1), DU(-1, -1), DU(-1, 1), DU(1, -1));
         vt = vt + xkd * lap9(dv_c, dv_jm, dv_jp, dv_im, dv_ip, DV(1, 1), DV(-1, -1), DV(-1, 1), DV(1, -1));
       }
+      if (d6on) { ut = ut + D6(RCM_D6_U, i, k); vt = vt + D6(RCM_D6_V, i, k); }
 #undef DU
 #undef DV
     }
@@ -409,9 +411,10 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
   const double r00 = L2(f.rpsda, j, i), r01 = L2(f.rpsda, j, i + 1), r10 = L2(f.rpsda, j + 1, i), r11 = L2(f.rpsda, j + 1, i + 1);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_c, j, i) : 0;
   const int ibs = (s.iboudy == 4) ? L2(f.zone_c, j, i) : 0;   // sponge zone (iboudy = 4)
-  const bool d9 = (s.idiffu == 2);   // nine-point operator on every interior point, no boundary ring
-  const bool dint = !d9 && diff_interior(g, j, i, false);
-  const int nring = d9 ? 0 : ring_count(g, j, i, false);
+  const bool d9 = (s.idiffu == 2);
+  const bool d6on = (s.idiffu == 3) && j == g.jci2;   // the one column idiffu = 3 acts on (k_diff6)   // nine-point operator on every interior point, no boundary ring
+  const bool dint = (s.idiffu == 1) && diff_interior(g, j, i, false);
+  const int nring = (s.idiffu == 1) ? ring_count(g, j, i, false) : 0;
   const double beta = 0.53;
   // p* after filter_ra_2d (Main/mod_tendency.F90:420): floors of the qv filter
   const double dps = s.gnu1 * (psc + psb - 2.0 * psa);
@@ -503,6 +506,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         for (int r = 0; r < nring; ++r) ten = ten + xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * (d_c));
         if (d9) ten = ten + xkc * lap9(d_c, d_jm, d_jp, d_im, d_ip, L3(f.bt, j + 1, i + 1, k) * RPSB(1, 1), L3(f.bt, j - 1, i - 1, k) * RPSB(-1, -1),
                                        L3(f.bt, j - 1, i + 1, k) * RPSB(-1, 1), L3(f.bt, j + 1, i - 1, k) * RPSB(1, -1));
+        if (d6on) ten = ten + D6(RCM_D6_T, i, k);
       }
       if (ibs > 0) ten = ten + LD1(&f.hefc[ibs]) * L3(f.xtbt, j, i, k);   // sponge3d on tten (iboudy = 4)
       if (f.phy_t) ten = ten + L3(f.phy_t, j, i, k);   // Main/mod_tendency.F90:285-287
@@ -556,6 +560,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         for (int r = 0; r < nring; ++r) ten = ten + 1.0 * xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * d_c);
         if (d9) ten = ten + 1.0 * xkc * lap9(d_c, d_jm, d_jp, d_im, d_ip, fmax(L3(f.bqv, j + 1, i + 1, k) * RPSB(1, 1), minqq), fmax(L3(f.bqv, j - 1, i - 1, k) * RPSB(-1, -1), minqq),
                                              fmax(L3(f.bqv, j - 1, i + 1, k) * RPSB(-1, 1), minqq), fmax(L3(f.bqv, j + 1, i - 1, k) * RPSB(1, -1), minqq));
+        if (d6on) ten = ten + D6(RCM_D6_QV, i, k);
       }
       if (ibs > 0) ten = ten + LD1(&f.hefc[ibs]) * L3(f.xqbt, j, i, k);   // sponge4d on qxten(iqv)
       if (f.phy_qv) ten = ten + L3(f.phy_qv, j, i, k);   // :292-294
@@ -608,6 +613,7 @@ k_h_tq(const Geom g, const Fields f, const StepScalars s) {
         for (int r = 0; r < nring; ++r) ten = ten + 1.0 * xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * d_c);
         if (d9) ten = ten + 1.0 * xkc * lap9(d_c, d_jm, d_jp, d_im, d_ip, fmax(L3(f.bqc, j + 1, i + 1, k) * RPSB(1, 1), 0.0), fmax(L3(f.bqc, j - 1, i - 1, k) * RPSB(-1, -1), 0.0),
                                              fmax(L3(f.bqc, j - 1, i + 1, k) * RPSB(-1, 1), 0.0), fmax(L3(f.bqc, j + 1, i - 1, k) * RPSB(1, -1), 0.0));
+        if (d6on) ten = ten + D6(RCM_D6_QC, i, k);
       }
       if (f.phy_qc) ten = ten + L3(f.phy_qc, j, i, k);
       if (s.ipptls <= 0) ten = 0.0;  // Main/mod_tendency.F90:331-335

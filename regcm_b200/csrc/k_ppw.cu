@@ -37,9 +37,10 @@ k_ppw(const Geom g, const Fields f, const StepScalars s) {
   const double ex = L2(f.ex, j, i), crx = L2(f.crx, j, i), cry = L2(f.cry, j, i);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_c, j, i) : 0;
   const int ibs = (s.iboudy == 4) ? L2(f.zone_c, j, i) : 0;   // sponge zone (iboudy = 4)
-  const bool d9 = (s.idiffu == 2);   // nine-point operator on every interior point, no boundary ring
-  const bool dint = !d9 && diff_interior(g, j, i, false);
-  const int nring = d9 ? 0 : ring_count(g, j, i, false);
+  const bool d9 = (s.idiffu == 2);
+  const bool d6on = (s.idiffu == 3) && j == g.jci2;   // the one column idiffu = 3 acts on (k_diff6)   // nine-point operator on every interior point, no boundary ring
+  const bool dint = (s.idiffu == 1) && diff_interior(g, j, i, false);
+  const int nring = (s.idiffu == 1) ? ring_count(g, j, i, false) : 0;
 
   // ---- carried state (level k-1 values and interface fluxes) ----
   double uavg1_m = 0, uavg2_m = 0, vavg1_m = 0, vavg2_m = 0;  // uavg at k-1

@@ -39,8 +39,9 @@ k_tke(const Geom g, const Fields f, const UwFields uw, const StepScalars s) {
   const double xmsf = L2(f.xmsf, j, i);
   const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i), m11 = L2(f.msfd, j + 1, i + 1);
   const bool d9 = (s.idiffu == 2);
-  const bool dint = !d9 && diff_interior(g, j, i, false);
-  const int nring = d9 ? 0 : ring_count(g, j, i, false);
+  const bool d6on = (s.idiffu == 3) && j == g.jci2;   // the one column idiffu = 3 acts on (k_diff6)
+  const bool dint = (s.idiffu == 1) && diff_interior(g, j, i, false);
+  const int nring = (s.idiffu == 1) ? ring_count(g, j, i, false) : 0;
 
   double uavg1_m = 0, uavg2_m = 0, vavg1_m = 0, vavg2_m = 0;   // half level k-1
   double fx_m = 0.0;                                           // vadv3d flux of loop index k-1
@@ -110,6 +111,7 @@ k_tke(const Geom g, const Fields f, const UwFields uw, const StepScalars s) {
       for (int r = 0; r < nring; ++r) ten = ten + uw.nuk * xkcf * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * (b_c));
       if (d9) ten = ten + uw.nuk * xkcf * lap9(b_c, d_jm, d_jp, d_im, d_ip, L3(a2, j + 1, i + 1, k), L3(a2, j - 1, i - 1, k),
                                                L3(a2, j - 1, i + 1, k), L3(a2, j + 1, i - 1, k));
+      if (d6on) ten = ten + D6(RCM_D6_TKE, i, k);
     }
     const double tsum = 0.0 + ten * rpsa_c + L3(uw.phy, j, i, k);
     P3(uw.c, j, i, k) = fmax(uw.tkemin, b_c + dt * tsum);

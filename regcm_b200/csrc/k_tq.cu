@@ -44,9 +44,10 @@ k_tq(const Geom g, const Fields f, const StepScalars s) {
   const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i), m11 = L2(f.msfd, j + 1, i + 1);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_c, j, i) : 0;
   const int ibs = (s.iboudy == 4) ? L2(f.zone_c, j, i) : 0;   // sponge zone (iboudy = 4)
-  const bool d9 = (s.idiffu == 2);   // nine-point operator on every interior point, no boundary ring
-  const bool dint = !d9 && diff_interior(g, j, i, false);
-  const int nring = d9 ? 0 : ring_count(g, j, i, false);
+  const bool d9 = (s.idiffu == 2);
+  const bool d6on = (s.idiffu == 3) && j == g.jci2;   // the one column idiffu = 3 acts on (k_diff6)   // nine-point operator on every interior point, no boundary ring
+  const bool dint = (s.idiffu == 1) && diff_interior(g, j, i, false);
+  const int nring = (s.idiffu == 1) ? ring_count(g, j, i, false) : 0;
   const double qthr = minqq * psa;           // vadvqv threshold
   const double cthr = minqq * minqq * psa;   // vadv4d ind=1 threshold
   const double beta = 0.53;

@@ -44,9 +44,10 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
   const double m00 = L2(f.msfd, j, i), m01 = L2(f.msfd, j, i + 1), m10 = L2(f.msfd, j + 1, i), m11 = L2(f.msfd, j + 1, i + 1);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_c, j, i) : 0;
   const bool we = ib > 0 && L2(tr.ztype, j, i) != 0;
-  const bool d9 = (s.idiffu == 2);   // nine-point operator on every interior point, no boundary ring
-  const bool dint = !d9 && diff_interior(g, j, i, false);
-  const int nring = d9 ? 0 : ring_count(g, j, i, false);
+  const bool d9 = (s.idiffu == 2);
+  const bool d6on = (s.idiffu == 3) && j == g.jci2;   // the one column idiffu = 3 acts on (k_diff6)   // nine-point operator on every interior point, no boundary ring
+  const bool dint = (s.idiffu == 1) && diff_interior(g, j, i, false);
+  const int nring = (s.idiffu == 1) ? ring_count(g, j, i, false) : 0;
   const double beta = 0.53;
   const double thr = mintr * psa;
   const int kpb_c = f.kpb ? L2(f.kpb, j, i) : 0;   // itrvadv = 3 (iuwvadv = 1, Main/mod_tendency.F90:150-154)
@@ -115,6 +116,7 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
       for (int r = 0; r < nring; ++r) ten = ten + 1.0 * xkc * (1.0 * (d_jp + d_jm + d_ip + d_im) + (-4.0) * d_c);
       if (d9) ten = ten + 1.0 * xkc * lap9(d_c, d_jm, d_jp, d_im, d_ip, fmax(L3(a2, j + 1, i + 1, k) * RPSB(1, 1), 0.0), fmax(L3(a2, j - 1, i - 1, k) * RPSB(-1, -1), 0.0),
                                            fmax(L3(a2, j - 1, i + 1, k) * RPSB(-1, 1), 0.0), fmax(L3(a2, j + 1, i - 1, k) * RPSB(1, -1), 0.0));
+      if (d6on) ten = ten + D6(RCM_D6_CHI + n, i, k);
     }
     // chiten = chiten + chidyn + chiphy; forecast; the value filtered for a negative forecast is provisional
     // (k_tr_repair redoes it)

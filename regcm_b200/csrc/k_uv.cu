@@ -43,9 +43,10 @@ k_uv(const Geom g, const Fields f, const StepScalars s) {
   const double psdotb = L2(f.psdotb, j, i);
   const int ib = (s.iboudy == 1 || s.iboudy == 5) ? L2(f.zone_d, j, i) : 0;
   const int ibs = (s.iboudy == 4) ? L2(f.zone_d, j, i) : 0;   // sponge zone (iboudy = 4)
-  const bool d9 = (s.idiffu == 2);   // nine-point operator on every interior point, no boundary ring
-  const bool dint = !d9 && diff_interior(g, j, i, true);
-  const int nring = d9 ? 0 : ring_count(g, j, i, true);
+  const bool d9 = (s.idiffu == 2);
+  const bool d6on = (s.idiffu == 3) && j == g.jdi2;   // the one column idiffu = 3 acts on (k_diff6)   // nine-point operator on every interior point, no boundary ring
+  const bool dint = (s.idiffu == 1) && diff_interior(g, j, i, true);
+  const int nring = (s.idiffu == 1) ? ring_count(g, j, i, true) : 0;
 
   // vertical-advection flux at the upper interface of level k (full level k)
   double uu_k = 0.0, vv_k = 0.0;  // uu(1) = 0: loop starts at k = 2

@@ -51,3 +51,22 @@ def test_gpu_idiffu2_differs_from_idiffu1(cuda_lib):
         out.append([c.get_state(f) for f in range(7)])
         c.close()
     assert any(np.abs(a - b).max() > 1e-9 * np.abs(a).max() for a, b in zip(*out))
+
+
+@pytest.mark.parametrize("kw", [{}, {"ntr": 2, "ibltyp": 2}, {"idynamic": 1}], ids=lambda k: "-".join(f"{a}{b}" for a, b in k.items()) or "default")
+def test_gpu_idiffu3_vs_oracle(cuda_lib, kw):
+    """idiffu = 3 as this snapshot of the reference has it (one column, clamped stencil; tests/test_idiffu3.py)."""
+    case, core, ref = make_pair(cuda_lib, "small", idiffu=3, **kw)
+    if kw.get("ibltyp") == 2:
+        from tests.test_tke import load_uw, uw_inputs
+        for c in (core, ref):
+            load_uw(c, case, *uw_inputs(case))
+    core.step(8); ref.step(8)
+    errs = rel_errors(core, ref)
+    assert max(e[0] for e in errs.values()) <= TOL, errs
+    extra = [capi.F_CHI + n for n in range(kw.get("ntr", 0))] + ([capi.F_TKE] if kw.get("ibltyp") == 2 else [])
+    for fld in extra:
+        for lv in (capi.LEVEL_A, capi.LEVEL_B):
+            a, r = core.get_state(fld, lv), ref.get_state(fld, lv)
+            assert np.abs(a - r).max() <= TOL * np.abs(r).max()
+    core.close()
