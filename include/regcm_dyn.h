@@ -236,8 +236,9 @@ typedef struct rcm_cfg {
                            * around the PBL top kpbl handed in with rcm_dyn_set_kpbl (Main/mod_advection.F90:915-957)  */
   int32_t ipgf;           /* idynamic = 1: 0 = pressure gradient force from p*.Tv (default); 1 = from the deviation of Tv from
                            * the reference profile t00pg (p/p00pg)^pgfaa1 (Main/mod_tendency.F90:1893-1964,2039-2068) */
-  int32_t isladvec;       /* 1: semi-Lagrangian horizontal advection of qv, qc and the tracers (idynamic 1, 2; one rank:
-                           * the departure stencil reaches three cells out; Main/mod_sladvection.F90)                  */
+  int32_t isladvec;       /* 1: semi-Lagrangian horizontal advection of qv, qc and the tracers (idynamic 1, 2;
+                           * Main/mod_sladvection.F90).  On a decomposed domain the tiles get four ghost rows and the
+                           * level-b species travel three rows wide before the operator (the departure stencil's reach) */
   int32_t iqmsl;          /* 1: quasi-monotonic limiter of the semi-Lagrangian interpolation (default 1)              */
   /* &geoparam */
   double ds;    /* grid spacing [km]                                       */

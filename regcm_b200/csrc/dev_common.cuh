@@ -218,7 +218,7 @@ __device__ __forceinline__ void negq_note(const Geom& g, const Fields& f, const 
     if (MODE != 0) {
       const int plane = n * g.kz + (k - 1);
       const int slot = atomicAdd(f.nq_cnt + plane, 1);
-      f.nq_list[(long long)plane * sk + slot] = (j - (g.jde1 - RCM_HALO)) + (i - (g.ide1 - RCM_HALO)) * si;
+      f.nq_list[(long long)plane * sk + slot] = (j - (g.jde1 - g.hw)) + (i - (g.ide1 - g.hw)) * si;
     }
   }
 }

@@ -335,8 +335,8 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
     return bail(RCM_ERR_ARG, "idynamic=3 needs mo_nadv >= 1, mo_nsound >= 1, kz >= 4, ipptls 0 or 1");
   if (h->hydro && (c.nsplit < 1 || c.nsplit > RCM_MAXSPLIT || c.nsplit > c.kz)) return bail(RCM_ERR_ARG, "nsplit must be 1..4");
   if (c.ipgf != 0 && c.ipgf != 1) return bail(RCM_ERR_ARG, "ipgf must be 0 or 1");
-  if (c.isladvec != 0 && (c.isladvec != 1 || c.idynamic == 3 || c.nproc != 1))
-    return bail(RCM_ERR_ARG, "isladvec must be 0 or 1; 1 runs with idynamic 1, 2 on one rank (the departure stencil reaches three cells out)");
+  if (c.isladvec != 0 && (c.isladvec != 1 || c.idynamic == 3))
+    return bail(RCM_ERR_ARG, "isladvec must be 0 or 1; 1 runs with idynamic 1, 2");
   if (c.idiffu < 1 || c.idiffu > 3) return bail(RCM_ERR_ARG, "idiffu must be 1, 2 or 3");
   if (c.idiffu == 3 && c.idynamic != 3 && c.nproc != 1)
     return bail(RCM_ERR_ARG, "idiffu = 3 runs on one rank (its stencil is three cells wide, RCM_HALO is 2)");
@@ -394,14 +394,15 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
       if (n < 3 || (q > 0 && q < ci - 1 && n < need)) return bail(RCM_ERR_ARG, "tile too narrow along i for the halo width (interior tiles need >= 6 points with ifupr = 1; all tiles >= 3)");
     }
   }
-  h->nj_pad = ((nj + 2 * RCM_HALO + 15) / 16) * 16;
-  h->ni_pad = ni + 2 * RCM_HALO;
+  g.hw = (c.isladvec == 1 && c.nproc > 1) ? 4 : RCM_HALO;   // even, so that the 16-byte alignment of the staged tiles does not move
+  h->nj_pad = ((nj + 2 * g.hw + 15) / 16) * 16;
+  h->ni_pad = ni + 2 * g.hw;
   g.si = h->nj_pad;
   g.sk = (long long)h->nj_pad * h->ni_pad;
   // the kernels index with 32-bit arithmetic (dev_common.cuh): the largest element index of a field must fit
-  if ((long long)(g.jde2 + RCM_EHALO + 16) + (long long)std::max(g.si, g.esi) * (g.ide2 + RCM_EHALO + 2) + g.sk * (long long)(g.kzp1 + 2) >= (1LL << 31))
+  if ((long long)(g.jde2 + RCM_EHALO + 16) + (long long)std::max(g.si, g.esi) * (g.ide2 + RCM_EHALO + 4) + g.sk * (long long)(g.kzp1 + 2) >= (1LL << 31))
     return bail(RCM_ERR_ARG, "tile too large for 32-bit element indices (more than 2^31 elements per field incl. the origin shift)");
-  h->off2 = -((long long)(g.jde1 - RCM_HALO) + (long long)g.si * (g.ide1 - RCM_HALO));
+  h->off2 = -((long long)(g.jde1 - g.hw) + (long long)g.si * (g.ide1 - g.hw));
   h->off3 = h->off2 - g.sk;
   g.esi = ((nj + 2 * RCM_EHALO + 15) / 16) * 16;
   g.pfd = 2;
@@ -627,7 +628,7 @@ static int copy3d(rcm_dyn* h, double* dev_shifted, const double* host, const int
   cudaPitchedPtr hp = make_cudaPitchedPtr((void*)host, n1 * sizeof(double), n1, n2);
   cudaPitchedPtr dp = make_cudaPitchedPtr((void*)(dev_shifted - h->off3), (size_t)g.si * sizeof(double), (size_t)g.si, (size_t)h->ni_pad);
   cudaPos hpos = make_cudaPos((size_t)(jlo - lb[0]) * sizeof(double), (size_t)(ilo - lb[1]), (size_t)(klo - lb[2]));
-  cudaPos dpos = make_cudaPos((size_t)(jlo - (g.jde1 - RCM_HALO)) * sizeof(double), (size_t)(ilo - (g.ide1 - RCM_HALO)), (size_t)(klo - 1));
+  cudaPos dpos = make_cudaPos((size_t)(jlo - (g.jde1 - g.hw)) * sizeof(double), (size_t)(ilo - (g.ide1 - g.hw)), (size_t)(klo - 1));
   p.srcPtr = to_device ? hp : dp; p.srcPos = to_device ? hpos : dpos;
   p.dstPtr = to_device ? dp : hp; p.dstPos = to_device ? dpos : hpos;
   p.extent = make_cudaExtent((size_t)(jhi - jlo + 1) * sizeof(double), (size_t)(ihi - ilo + 1), (size_t)(khi - klo + 1));
@@ -851,6 +852,18 @@ static int exch_state(rcm_dyn* h) {  // atm1/atm2 all prognostics, width 2 (Main
   if (h->uw_on) { fl.push_back({h->uw.a, h->g.kzp1, 0}); fl.push_back({h->uw.b, h->g.kzp1, 0}); }   // Main/mod_tendency.F90:870-872,1078-1080
   if (h->halo.exchange(fl, RCM_HALO, h->st))
     return fail(h, RCM_ERR_NCCL, "halo exchange (state) failed");
+  return RCM_OK;
+}
+// Semi-Lagrangian advection on a decomposed domain: the departure stencil reads atm2%qx / atm2%chi three cells out
+// (Main/mod_sladvection.F90:139-221,347-393; the reference allocates those two with the `sl` ghost width,
+// Main/mod_atm_interface.F90:650-668, and exchanges them four wide, Main/mod_tendency.F90:1073-1077,1085-1089), so the tile is
+// allocated with g.hw = 4 ghost rows and the level-b species travel once more per step, three rows wide.
+static int exch_sl(rcm_dyn* h) {
+  if (h->cfg.nproc <= 1) return RCM_OK;
+  std::vector<HaloField> fl = {{h->f.bqv, h->g.kz, 0}, {h->f.bqc, h->g.kz, 0}};
+  for (int n = 0; n < h->tr.ntr; ++n) fl.push_back({h->tr.b[n], h->g.kz, 0});
+  if (h->halo.exchange(fl, 3, h->st))
+    return fail(h, RCM_ERR_NCCL, "halo exchange (semi-Lagrangian species) failed");
   return RCM_OK;
 }
 // ---- hydrostatic core (the reference's call sites: Main/mod_tendency.F90:866-869, Main/mod_split.F90:197-198,
@@ -1634,7 +1647,10 @@ static int tend_hydro(rcm_dyn* h) {
   h->mid_step = false;
   if (h->cfg.idiffu == 3)   // diff_6th_coef = diff_6th_factor * 0.015625 / (2 dtsec) (Main/mod_diffusion.F90:78,154)
     TIMED(KID_XKC, 1, launch_diff6(g, f, h->tr, h->uw, s, h->uw_on ? 1 : 0, 0.12 * 0.015625 / (2.0 * h->dtsec), h->st));
-  if (h->cfg.isladvec == 1) TIMED(KID_TR, 1, launch_sl(g, f, h->tr, s, h->st));   // semi-Lagrangian tendencies of qv, qc, tracers
+  if (h->cfg.isladvec == 1) {   // semi-Lagrangian tendencies of qv, qc, tracers
+    if (const int rc = exch_sl(h)) return rc;
+    TIMED(KID_TR, 1, launch_sl(g, f, h->tr, s, h->st));
+  }
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_H_UV, 1, launch_h_uv(g, f, s, h->st));
     TIMED(KID_H_TQ, 1, launch_h_tq(g, f, s, h->st));
@@ -1726,7 +1742,10 @@ static int tend(rcm_dyn* h) {
   h->mid_step = false;
   if (h->cfg.idiffu == 3)   // diff_6th_coef = diff_6th_factor * 0.015625 / (2 dtsec) (Main/mod_diffusion.F90:78,154)
     TIMED(KID_XKC, 1, launch_diff6(g, f, h->tr, h->uw, s, h->uw_on ? 1 : 0, 0.12 * 0.015625 / (2.0 * h->dtsec), h->st));
-  if (h->cfg.isladvec == 1) TIMED(KID_TR, 1, launch_sl(g, f, h->tr, s, h->st));   // semi-Lagrangian tendencies of qv, qc, tracers
+  if (h->cfg.isladvec == 1) {   // semi-Lagrangian tendencies of qv, qc, tracers
+    if (const int rc = exch_sl(h)) return rc;
+    TIMED(KID_TR, 1, launch_sl(g, f, h->tr, s, h->st));
+  }
   if (h->prof_on || !h->overlap_slow) {
     TIMED(KID_UV, 1, h->uv_maps ? launch_uv_tma(g, f, s, h->st, h->uv_maps) : launch_uv(g, f, s, h->st));
     TIMED(KID_TQ, 1, h->tq_tma ? launch_tq_tma(g, f, s, h->st) : launch_tq(g, f, s, h->st));

@@ -33,6 +33,8 @@ struct Geom {
   int kc_uv, kc_tq, kc_ppw;  // levels per thread of the slow-tendency kernels (>= kz: one thread marches the whole column)
   int pfd;       // L2 prefetch distance (levels ahead) of the column-marching kernels; 0 = off
   int pfd_wfwd, pfd_wback;   // the same for the two acoustic sweeps, which want different distances (profiles/r2_measurements.md, call O)
+  int hw;        // ghost rows ALLOCATED around the tile: RCM_HALO, or 4 on a decomposed domain with isladvec = 1 (the departure
+                 // stencil of Main/mod_sladvection.F90:139-221 reaches three cells out); the exchanges of the state stay RCM_HALO wide
 };
 
 // per-step scalars

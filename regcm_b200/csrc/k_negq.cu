@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(256) k_negq_repair(const Geom g, const Fields 
   P.cq = n == 0 ? f.cqv : f.cqc;
   P.bq = n == 0 ? f.bqv : f.bqc;
   P.list = f.nq_list + (long long)plane * g.sk;
-  P.jl0 = g.jde1 - RCM_HALO; P.il0 = g.ide1 - RCM_HALO;
+  P.jl0 = g.jde1 - g.hw; P.il0 = g.ide1 - g.hw;
 #ifdef RCM_EMU
   // host harness: threads run one after the other, so thread 0 plays the whole block
   if (threadIdx.x != 0) return;

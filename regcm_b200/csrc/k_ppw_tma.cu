@@ -31,7 +31,7 @@ k_ppw_tma(const Geom g, const Fields f, const StepScalars s) {
   const bool valid = (j0 + tx <= g.jci2) && (i0 + ty <= g.ici2);
   const int j = min(j0 + tx, g.jci2), i = min(i0 + ty, g.ici2);
   const int kz = g.kz, kzp1 = g.kzp1;
-  const int jlo = g.jde1 - RCM_HALO;
+  const int jlo = g.jde1 - g.hw;
   int jstart = (j0 - 2) - (((j0 - 2) - jlo) & 1);
   jstart = min(jstart, jlo + si - kTW);
   const int ihi = g.ide2 + RCM_HALO;

@@ -50,7 +50,7 @@ k_snd_wfwd_tma(const Geom g, const Fields f, const StepScalars s) {
   const int j = min(j0 + tx, g.jci2), i = min(i0 + ty, g.ici2);
   const int kz = g.kz, kzp1 = g.kzp1;
   const double dts = s.dts, dx = s.dx, xgamma = s.xgamma, bp = s.bp, bm = s.bm, bpxbp = s.bpxbp, bpxbm = s.bpxbm;
-  const int jlo = g.jde1 - RCM_HALO;
+  const int jlo = g.jde1 - g.hw;
   int jstart = (j0 - 1) - (((j0 - 1) - jlo) & 1);
   jstart = min(jstart, jlo + si - kTW);
   const int ihi = g.ide2 + RCM_HALO;

@@ -127,7 +127,7 @@ k_tr(const Geom g, const Fields f, const TrFields tr, const StepScalars s) {
       atomicAdd(tr.negcnt, 1ULL);
       const int plane = n * kz + (k - 1);
       const int slot = atomicAdd(tr.nq_cnt + plane, 1);
-      tr.nq_list[(long long)plane * sk + slot] = (j - (g.jde1 - RCM_HALO)) + (i - (g.ide1 - RCM_HALO)) * si;
+      tr.nq_list[(long long)plane * sk + slot] = (j - (g.jde1 - g.hw)) + (i - (g.ide1 - g.hw)) * si;
       cq = 0.0;
     }
     const double d = s.gnu2 * (cq + b_c - 2.0 * ac_c);
@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(256) k_tr_repair(const Geom g, const TrFields 
   double* cq = tr.c[n];
   const double* bq = tr.b[n];
   const int* list = tr.nq_list + (long long)plane * sk;
-  const int jl0 = g.jde1 - RCM_HALO, il0 = g.ide1 - RCM_HALO;
+  const int jl0 = g.jde1 - g.hw, il0 = g.ide1 - g.hw;
   auto value = [&](int jj, int ii) {   // atmc%chi as the sweep sees it: atm2%chi on the physical boundary cells (:564-569)
     const bool bdy = (jj <= g.jcross1 || jj >= g.jcross2 || ii <= g.icross1 || ii >= g.icross2);
     return bdy ? P3(bq, jj, ii, k) : TQ_LOAD(&P3(cq, jj, ii, k));

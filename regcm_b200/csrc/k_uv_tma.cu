@@ -40,7 +40,7 @@ k_uv_tma(const Geom g, const Fields f, const StepScalars s) {
   const int kz = g.kz;
   // first column of the tile rows: j0-2 rounded down to an even array index (16-byte
   // aligned source), and kept inside the pitched row
-  const int jlo = g.jde1 - RCM_HALO;
+  const int jlo = g.jde1 - g.hw;
   int jstart = (j0 - 2) - (((j0 - 2) - jlo) & 1);
   jstart = min(jstart, jlo + si - kTW);
   const int ihi = g.ide2 + RCM_HALO;

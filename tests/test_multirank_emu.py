@@ -282,6 +282,37 @@ def test_tracers_multirank_match_single_rank(emu_lib, tmp_path, idynamic):
     assert negs == ref.diag().neg_chi_points and negs > 0
 
 
+@pytest.mark.parametrize("idynamic,world,layout", [(2, 4, (2, 2)), (2, 2, (2, 1)), (2, 3, (3, 1)), (1, 4, (2, 2)), (1, 2, (1, 2))])
+def test_sladvec_multirank_matches_single_rank(emu_lib, tmp_path, idynamic, world, layout):
+    """isladvec = 1 on a decomposed domain: the departure stencil reads atm2%qx / atm2%chi three cells out
+    (Main/mod_sladvection.F90:139-221,347-393), the reference exchanges them four wide (Main/mod_tendency.F90:1073-1077,
+    1085-1089).  Here the tile is allocated with four ghost rows and the level-b species travel three rows wide before
+    k_sl; the assembled result equals the single rank bit for bit (to the eigen-solver tolerance for idynamic = 1)."""
+    steps, ntr = 5, 2
+    run_ranks(world, tmp_path, ["--case", "tiny", "--idynamic", str(idynamic), "--steps", str(steps), "--cpus-j", str(layout[0]),
+                                "--cpus-i", str(layout[1]), "--cfg", f"ntr={ntr}", "--cfg", "isladvec=1"])
+    case = synth.make_case("tiny", idynamic=idynamic, ntr=ntr, isladvec=1)
+    core = capi.DynCore(emu_lib, case.cfg)
+    synth.load_case(core, case)
+    core.step(steps)
+    base = synth.make_case("tiny", idynamic=idynamic, ntr=ntr)
+    plain = capi.DynCore(emu_lib, base.cfg); synth.load_case(plain, base); plain.step(steps)
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    for fld in (capi.F_U, capi.F_T, capi.F_QV, capi.F_QC, capi.F_CHI, capi.F_CHI + ntr - 1):
+        dot = fld in (capi.F_U, capi.F_V)
+        for lv, tag in ((0, "a"), (1, "b")):
+            glob = np.full((jx if dot else jx - 1, iy if dot else iy - 1, kz), np.nan)
+            for r in range(world):
+                d = np.load(os.path.join(tmp_path, f"rank{r}.npz"))
+                lb, a = d[f"lb{fld}"], d[f"f{fld}{tag}"]
+                glob[lb[0] - 1:lb[0] - 1 + a.shape[0], lb[1] - 1:lb[1] - 1 + a.shape[1], :] = a
+            want = core.get_state(fld, lv)
+            assert not np.isnan(glob).any()
+            assert np.abs(glob - want).max() <= (1e-11 if idynamic == 1 else 0.0) * np.abs(want).max(), (fld, tag)
+    assert np.abs(core.get_state(capi.F_QV) - plain.get_state(capi.F_QV)).max() > 1e-6 * plain.get_state(capi.F_QV).max()   # the switch is live
+    core.close(); plain.close()
+
+
 def test_many_fields_in_one_exchange(emu_lib, tmp_path):
     """ntr = 8 with TKE: the state exchange of the non-hydrostatic core carries 14 + 16 + 2 = 32 fields, twice what one
     packed message holds (16): the list is sent in several messages."""

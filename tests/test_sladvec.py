@@ -64,10 +64,6 @@ def test_create_rejects_sladvec_where_it_is_not_built(emu_lib):
     cfg.isladvec = 1                                   # the reference switches it off for the MOLOCH core (mod_params.F90:1158-1162)
     with pytest.raises(capi.RcmError):
         capi.DynCore(emu_lib, cfg)
-    cfg = synth.make_case("tiny", records=()).cfg
-    cfg.isladvec, cfg.nproc, cfg.cpus_j, cfg.cpus_i = 1, 4, 2, 2     # three cells of halo would be needed
-    with pytest.raises(capi.RcmError):
-        capi.DynCore(emu_lib, cfg)
 
 
 @pytest.mark.gpu
