@@ -203,7 +203,8 @@ typedef struct rcm_cfg {
   int32_t idiffu;   /* 1 = 4th order with the 2nd-order boundary ring, 2 = nine-point operator on every interior point
                      * (Main/mod_diffusion.F90:266-411,523-601,658-735,792-894); 3 = flux-limited 6th order as this snapshot
                      * of the reference has it: on the single column j = jdi2 / jci2 its loops run over (:421,611,745,902),
-                     * one rank, idynamic 1, 2 */
+                     * one rank (the bounds are per tile: under MPI the reference's result depends on the decomposition),
+                     * idynamic 1, 2 */
   int32_t ipptls;   /* >0: hydrometeors advected, water loading in w       */
   /* &nonhydroparam */
   int32_t ifupr;    /* upper radiative boundary condition                  */

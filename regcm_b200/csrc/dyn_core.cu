@@ -339,7 +339,7 @@ extern "C" int rcm_dyn_create(const rcm_cfg* cfg, rcm_dyn** out) {
     return bail(RCM_ERR_ARG, "isladvec must be 0 or 1; 1 runs with idynamic 1, 2");
   if (c.idiffu < 1 || c.idiffu > 3) return bail(RCM_ERR_ARG, "idiffu must be 1, 2 or 3");
   if (c.idiffu == 3 && c.idynamic != 3 && c.nproc != 1)
-    return bail(RCM_ERR_ARG, "idiffu = 3 runs on one rank (its stencil is three cells wide, RCM_HALO is 2)");
+    return bail(RCM_ERR_ARG, "idiffu = 3 runs on one rank (the reference applies it to the last column of EVERY tile: the result would depend on the decomposition)");
   // 0 fixed, 1 / 5 relaxation, 4 sponge; sigma-coordinate cores also 2 (time-dependent, no relaxation) and 3 (2 + inflow/outflow)
   if (!(c.iboudy == 0 || c.iboudy == 1 || c.iboudy == 4 || c.iboudy == 5 || (c.idynamic != 3 && (c.iboudy == 2 || c.iboudy == 3))))
     return bail(RCM_ERR_ARG, "iboudy must be 0, 1, 4 or 5 (idynamic 1, 2: also 2, 3)");

@@ -4,7 +4,8 @@
 // to the grid (:414-426), the coefficients are xkc = xkcf = diff_6th_coef * p*, xkd = diff_6th_coef * p*dot (:154,174-183).
 //   k_diff6   one thread per (i, level, field): the tendency fac * xk * ((x1 - x0) + (y1 - y0)) of that one column into
 //             Fields::d6; k_uv / k_tq / k_ppw / k_tr / k_tke / k_h_* add it where their diffusion term stands (D6).
-// One rank (the stencil is three cells wide).  diffu_x3df multiplies by xkc(j,i,k) for k up to kzp1, one level beyond the
+// One rank: jdi2 / jci2 are per-tile bounds in the reference, so under MPI its operator acts on the last column of every
+// tile and the answer depends on the decomposition; rcm_dyn_create refuses that.  diffu_x3df multiplies by xkc(j,i,k) for k up to kzp1, one level beyond the
 // array (:646); xkc does not depend on k, so level kzp1 takes the value of the other levels.
 #include "dev_common.cuh"
 #include "launch.h"
