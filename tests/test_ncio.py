@@ -177,3 +177,60 @@ def test_gpu_files_in_sav_out(cuda_lib, tmp_path, name, kw):
             np.testing.assert_array_equal(a.get_state(f, lv), b.get_state(f, lv), err_msg=f"files vs arrays: {f} level {lv}")
             np.testing.assert_array_equal(c.get_state(f, lv), b.get_state(f, lv), err_msg=f"restart: {f} level {lv}")
     a.close(); b.close(); c.close()
+
+
+# ---------------------------------------------------------------------------- the time loop with files on both sides
+def _write_long_case(tmp_path, case):
+    """Five hourly records: 22, 23 h of 31 January in the file of the start date, 0, 1, 2 h of 1 February in the next one."""
+    cfg = case.cfg
+    ncio.write_domain(str(tmp_path / "case_DOMAIN000.nc"), cfg, case.statics)
+    r = [case.bdy[s] for s in (capi.BDY_B0, capi.BDY_B1, capi.BDY_NEXT)]
+    mix = lambda a, b, w: {f: np.asfortranarray((1 - w) * a[f] + w * b[f]) for f in a}
+    recs = [r[0], r[1], r[2], mix(r[1], r[2], 0.4), mix(r[0], r[2], 0.7)]
+    h0 = _hours(START)
+    ncio.write_icbc(ncio.icbc_name(str(tmp_path), "case", START), cfg, [h0, h0 + 1], recs[:2])
+    ncio.write_icbc(ncio.icbc_name(str(tmp_path), "case", (1990, 2, 1, 0)), cfg, [h0 + 2, h0 + 3, h0 + 4], recs[2:])
+    return recs
+
+
+@pytest.mark.parametrize("name,kw", [("tiny", {}), ("tiny", {"idynamic": 1}), ("tinym", {})], ids=["nh", "hydro", "moloch"])
+def test_time_loop_with_files_and_restart(emu_lib, tmp_path, name, kw):
+    """driver.Run = RCM_initialize / RCM_run for a dynamics-only run: three boundary intervals across the month change of the
+    ICBC files equal the same run fed from arrays record by record; stopped at a SAV date and continued from the SAV file in
+    a new process image (ifrest), it equals the uninterrupted run bit for bit."""
+    from regcm_b200 import driver
+    from tests.test_restart import fields_of
+    case = synth.make_case(name, ibdyfrq=1, **kw)
+    cfg = case.cfg
+    recs = _write_long_case(tmp_path, case)
+    spr = int(round(3600.0 / cfg.dt))
+    total = 3 * spr + 2
+    run = driver.Run(emu_lib, cfg, str(tmp_path), str(tmp_path), "case", START, dirout=str(tmp_path))
+    run.run(total, sav_dates=[(1990, 2, 1, 0)])
+    # arrays, record by record
+    ref = capi.DynCore(emu_lib, cfg)
+    for sid, a in case.statics.items():
+        ref.set_static(sid, a)
+    for slot, rec in ((capi.BDY_B0, recs[0]), (capi.BDY_B1, recs[1]), (capi.BDY_NEXT, recs[2])):
+        for fid in ncio.bdy_fields(cfg):
+            ref.set_bdy(fid, slot, rec[fid])
+    ref.init()
+    ref.step(spr)
+    for k in (3, 4):
+        for fid in ncio.bdy_fields(cfg):
+            ref.set_bdy(fid, capi.BDY_NEXT, recs[k][fid])
+        ref.step(spr if k == 3 else spr + 2)
+    flds, levels = fields_of(cfg)
+    for f in flds:
+        for lv in levels:
+            np.testing.assert_array_equal(run.core.get_state(f, lv), ref.get_state(f, lv), err_msg=f"loop: {f} level {lv}")
+    # restart from the SAV file written two intervals in
+    again = driver.Run(emu_lib, cfg, str(tmp_path), str(tmp_path), "case", START, dirout=str(tmp_path), restart_from=(1990, 2, 1, 0))
+    assert again.lcount == 2 * spr
+    again.run(total - 2 * spr)
+    for f in flds:
+        for lv in levels:
+            np.testing.assert_array_equal(again.core.get_state(f, lv), ref.get_state(f, lv), err_msg=f"restart: {f} level {lv}")
+    with pytest.raises(ncio.NcioError):
+        again.run(2 * spr)                              # the boundary data end before the run does
+    run.close(); again.close(); ref.close()
