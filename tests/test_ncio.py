@@ -198,6 +198,17 @@ def test_time_loop_with_files_and_restart(emu_lib, tmp_path, name, kw):
     """driver.Run = RCM_initialize / RCM_run for a dynamics-only run: three boundary intervals across the month change of the
     ICBC files equal the same run fed from arrays record by record; stopped at a SAV date and continued from the SAV file in
     a new process image (ifrest), it equals the uninterrupted run bit for bit."""
+    _time_loop(emu_lib, tmp_path, name, kw)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,kw", [("small", {}), ("small", {"idynamic": 1}), ("smallm", {})], ids=["nh", "hydro", "moloch"])
+def test_gpu_time_loop_with_files_and_restart(cuda_lib, tmp_path, name, kw):
+    """The same on the GPU library: here the read-ahead record really travels on the staging stream while the steps run."""
+    _time_loop(cuda_lib, tmp_path, name, kw)
+
+
+def _time_loop(emu_lib, tmp_path, name, kw):
     from regcm_b200 import driver
     from tests.test_restart import fields_of
     case = synth.make_case(name, ibdyfrq=1, **kw)
