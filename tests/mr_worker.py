@@ -67,6 +67,8 @@ def main():
     ap.add_argument("--phys", action="store_true", help="every step through pre_physics / set_phys_tend / post_physics with the synthetic "
                     "tendencies of tests/test_physics_coupling.py")
     ap.add_argument("--uw", action="store_true", help="ibltyp = 2 inputs of tests/test_tke.py: TKE state, TKE physics source, kpbl, cloud water")
+    ap.add_argument("--from-files", default="", help="directory with case_DOMAIN000.nc / case_ICBC.*.nc written by tests/test_ncio.py: every "
+                    "rank reads the files itself (the reference's do_parallel_netcdf_in path) and hands the library global arrays")
     ap.add_argument("--out", required=True)
     args = ap.parse_args()
 
@@ -128,7 +130,18 @@ def main():
     win = tile_window(core.tile(), cfg.jx, cfg.iy)
     case = synth.make_case(args.case, window=win, ibdyfrq=args.ibdyfrq, **over)
     case.cfg = cfg
-    synth.load_case(core, case, stage_next=True)
+    if args.from_files:
+        from regcm_b200 import ncio
+        from tests.test_ncio import START, _hours
+        ncio.load_domain(core, ncio.read_domain_info(os.path.join(args.from_files, "case_DOMAIN000.nc"), cfg))
+        rd = ncio.IcbcReader(args.from_files, "case", cfg, START)
+        units = "hours since 1949-12-01 00:00:00 UTC"
+        for slot, k in ((capi.BDY_B0, 0), (capi.BDY_B1, 1), (capi.BDY_NEXT, 2)):
+            rd.feed(core, slot, ncio.timeval2date(_hours(START) + k * cfg.ibdyfrq, units))
+        core.init()
+        rd.close()
+    else:
+        synth.load_case(core, case, stage_next=True)
     if args.spiky_tracers:
         from tests.test_tracers import _spiky
         for n in range(cfg.ntr):

@@ -245,3 +245,28 @@ def _time_loop(emu_lib, tmp_path, name, kw):
     with pytest.raises(ncio.NcioError):
         again.run(2 * spr)                              # the boundary data end before the run does
     run.close(); again.close(); ref.close()
+
+
+@pytest.mark.parametrize("name,idynamic,world,layout", [("tiny", 2, 4, (2, 2)), ("tiny", 1, 2, (2, 1)), ("tinym", 3, 2, (1, 2))], ids=["nh-2x2", "hydro-2x1", "moloch-1x2"])
+def test_ranks_reading_the_files_themselves(emu_lib, tmp_path, name, idynamic, world, layout):
+    """Decomposed run, every rank reading DOMAIN and ICBC itself and handing the library the global arrays (it keeps its
+    window): the assembled result equals the single rank fed from arrays."""
+    import os
+    from tests.test_multirank_emu import run_ranks
+    case = synth.make_case(name, ibdyfrq=1, idynamic=idynamic)
+    _write_case(tmp_path, case)
+    steps = 5
+    run_ranks(world, tmp_path, ["--case", name, "--idynamic", str(idynamic), "--ibdyfrq", "1", "--steps", str(steps), "--cpus-j", str(layout[0]),
+                                "--cpus-i", str(layout[1]), "--from-files", str(tmp_path)])
+    ref = capi.DynCore(emu_lib, case.cfg); synth.load_case(ref, case); ref.step(steps)
+    jx, iy, kz = case.cfg.jx, case.cfg.iy, case.cfg.kz
+    for fld in (capi.F_T, capi.F_QV):
+        glob = np.full((jx - 1, iy - 1, kz), np.nan)
+        for r in range(world):
+            d = np.load(os.path.join(tmp_path, f"rank{r}.npz"))
+            lb, a = d[f"lb{fld}"], d[f"f{fld}a"]
+            glob[lb[0] - 1:lb[0] - 1 + a.shape[0], lb[1] - 1:lb[1] - 1 + a.shape[1], :] = a
+        want = ref.get_state(fld, 0)
+        assert not np.isnan(glob).any()
+        assert np.abs(glob - want).max() <= (0.0 if idynamic == 2 else 1e-11) * np.abs(want).max(), fld
+    ref.close()
